@@ -1,0 +1,242 @@
+/*
+ * rtw.h — C ABI of the B200 path-tracing backend (drop-in boundary).
+ *
+ * The reference (Terence-23/RayTracing-in-a-weekend, Rust/ tree) has no FFI: its render path is
+ * entered through four Rust functions that take a `Scene`, a `Viewport` and an integrator
+ * closure and return `Img = Vec<Vec<Rgb<f32>>>`:
+ *     Viewport::render          Rust/src/viewport.rs:430   (stratified, serial)
+ *     Viewport::render_no_rand  Rust/src/viewport.rs:479   (1 centre ray / pixel)
+ *     async_render              Rust/src/viewport.rs:215   (row tasks, random jitter, motion blur)
+ *     render_multi              Rust/src/viewport.rs:249   (frames start_frame..start_frame+n)
+ * This header is what a Rust `extern "C"` block (rust_shim/src/ffi.rs), a ctypes loader
+ * (raytracing-in-a-weekend_b200/_abi.py) or a C++ caller (include/rtw_scene.hpp) binds instead.
+ * Every struct is plain data: counts, floats and pointers to caller-owned arrays. The library
+ * deep-copies at rtw_scene_create and owns device memory until rtw_scene_destroy.
+ *
+ * No entry point falls back to the CPU: when no CUDA device is usable every call returns
+ * RTW_E_CUDA and rtw_last_error() says why.
+ */
+#ifndef RTW_H
+#define RTW_H
+
+#include <stdint.h>
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define RTW_ABI_VERSION 1
+
+/* ---- error codes (negative; 0 = ok). The reference panics/unwraps instead (viewport.rs:242). */
+enum {
+    RTW_OK = 0,
+    RTW_E_INVALID = -1,   /* bad argument / inconsistent scene description */
+    RTW_E_CUDA = -2,      /* CUDA runtime error or no device */
+    RTW_E_NOMEM = -3,
+    RTW_E_UNSUPPORTED = -4
+};
+
+/* ---- Material  (Rust/src/objects/materials.rs:15-20; on_hit :105-154) */
+typedef struct rtw_material {
+    float metallicness;   /* 0 = lambertian, 1 = mirror, between = blend of directions */
+    float opacity;        /* > 0 selects the dielectric branch; the value is otherwise unused */
+    float ir;             /* refraction index */
+    float emitted[3];     /* `emmited` in the reference */
+} rtw_material;
+
+/* ---- PerlinNoise tables (Rust/src/texture.rs:63-69). `ranfloat` is dead in the reference. */
+typedef struct rtw_noise {
+    float    ranvec[256][3];
+    uint32_t perm_x[256];
+    uint32_t perm_y[256];
+    uint32_t perm_z[256];
+} rtw_noise;
+
+/* ---- ImageTexture (Rust/src/texture.rs:21-27). `width` is the reference's `row`,
+ *      `height` its `col`; texel (x,y) = rgb[(y*width + x)*3 .. +3]  (texture.rs:265). */
+typedef struct rtw_texture {
+    uint32_t     width;
+    uint32_t     height;
+    const float* rgb;          /* width*height*3 floats, caller-owned */
+    int32_t      noise_id;     /* -1 = None; else index into rtw_scene_desc.noises */
+    float        noise_scale;
+} rtw_texture;
+
+/* ---- Sphere (Rust/src/objects/sphere.rs:13-20) */
+typedef struct rtw_sphere {
+    float    origin[3];
+    float    radius;
+    float    col_mod[3];
+    float    velocity[3];
+    uint32_t mat_id;
+    uint32_t tex_id;
+} rtw_sphere;
+
+/* ---- Quad (Rust/src/objects/quad.rs:8-20). normal/d/w are re-derived as quad.rs:93-105.
+ *      `velocity` is stored and never read by the reference (quad.rs:37-81); kept for layout parity. */
+typedef struct rtw_quad {
+    float    origin[3];
+    float    u[3];
+    float    v[3];
+    float    velocity[3];
+    uint32_t mat_id;
+    uint32_t tex_id;
+} rtw_quad;
+
+/* ---- Instance (Rust/src/objects/instance.rs:28-39). An instance owns a range of the scene's
+ *      sphere and quad arrays (those ranges lie after the top-level primitives). */
+enum { RTW_DENSITY_SURFACE = 0,        /* dist_fn = surface        instance.rs:21-23 */
+       RTW_DENSITY_CONST   = 1 };      /* dist_fn = const_density  instance.rs:24-26 */
+typedef struct rtw_instance {
+    uint32_t first_sphere, n_spheres;
+    uint32_t first_quad,   n_quads;
+    float    translation[3];
+    float    rotation[3];              /* Euler angles fed to Vec3::rotated (vec3.rs:161-181) */
+    uint32_t density_kind;
+    float    density;
+} rtw_instance;
+
+/* ---- Scene (Rust/src/viewport.rs:79-88). spheres[0..n_top_spheres) and quads[0..n_top_quads)
+ *      are Scene.spheres / Scene.quads; the rest belong to instances. */
+typedef struct rtw_scene_desc {
+    uint32_t abi_version;              /* = RTW_ABI_VERSION */
+    uint32_t n_spheres, n_top_spheres;
+    uint32_t n_quads,   n_top_quads;
+    uint32_t n_instances;
+    uint32_t n_materials, n_textures, n_noises;
+    const rtw_sphere*   spheres;
+    const rtw_quad*     quads;
+    const rtw_instance* instances;
+    const rtw_material* materials;
+    const rtw_texture*  textures;
+    const rtw_noise*    noises;
+    float background[3];               /* Scene.background_color, viewport.rs:87 */
+} rtw_scene_desc;
+
+/* ---- Camera: the derived (private) fields of Viewport (viewport.rs:48-77). Fill by hand or
+ *      with rtw_camera_init, which restates Viewport::new (viewport.rs:308-401). */
+typedef struct rtw_camera {
+    uint32_t width, height;
+    float origin[3];
+    float pixel00[3];                  /* `upper_left_corner` (a direction; origin NOT added) */
+    float delta_u[3], delta_v[3];      /* p_delta_u / p_delta_v */
+    float u[3], v[3];                  /* lens basis */
+    float lens_radius;
+} rtw_camera;
+
+/* ---- integrators: the closures the reference passes as `ray_color` */
+enum {
+    RTW_INT_GRADIENT   = 0,  /* ray_color_gradient   viewport/ray_color.rs:12-41   mint 1e-3 maxt 1e5 */
+    RTW_INT_D          = 1,  /* ray_color_d          main.rs:17-46                 mint 1e-3 maxt 1e3 */
+    RTW_INT_BG_COLOR   = 2,  /* ray_color_bg_color   viewport/ray_color.rs:43-92   mint 1e-3 maxt 1e4 */
+    RTW_INT_NORMAL     = 3,  /* first-hit normal shading, viewport.rs:524-554      mint 0    maxt 1e3 */
+    RTW_INT_ALBEDO     = 4,  /* first-hit col_mod (miss -> background)             mint 1e-3 maxt 1e5 */
+    RTW_INT_GLASS_TEST = 5   /* glass_tests.rs:8-55: non-mirror hit -> yellow, miss -> blue; 1e-3,1e3 */
+};
+
+/* ---- which reference render loop to mirror */
+enum {
+    RTW_MODE_RANDOM     = 0, /* async_render/render_row  viewport.rs:270-305 */
+    RTW_MODE_STRATIFIED = 1, /* Viewport::render         viewport.rs:430-478  (time = 0) */
+    RTW_MODE_NO_RAND    = 2  /* Viewport::render_no_rand viewport.rs:479-516  (1 ray/pixel) */
+};
+
+enum {
+    RTW_OUT_RESOLVED = 0,    /* mean over samples, then powf(1/gamma) (viewport.rs:207-213,301) */
+    RTW_OUT_SUM      = 1     /* raw per-pixel f32 sums of this call's sample range (multi-GPU) */
+};
+
+enum {
+    RTW_FLAG_ORDERED_ONLY = 1u   /* reserved */
+};
+
+typedef struct rtw_render_opts {
+    uint32_t samples;        /* Viewport.samples (total over all devices) */
+    uint32_t depth;          /* Viewport.depth */
+    float    gamma;          /* Viewport.gamma; resolve applies powf(1/gamma) */
+    uint32_t integrator;     /* RTW_INT_* */
+    uint32_t mode;           /* RTW_MODE_* */
+    float    shutter_speed;  /* Viewport.shutter_speed */
+    float    fps;            /* Viewport.fps */
+    uint32_t frame;          /* Viewport.frame */
+    uint64_t seed;           /* Philox key; the reference is unseeded (thread_rng) */
+    float    mint, maxt;     /* used only when maxt > 0; else the integrator's own constants */
+    /* sharding: this call renders samples [sample_begin, sample_begin+sample_count)
+     * of rows [row_begin, row_begin+row_count). sample_count == 0 means "all"; row_count == 0 means
+     * "all rows". The output buffer holds row_count*width*3 floats. */
+    uint32_t sample_begin, sample_count;
+    uint32_t row_begin, row_count;
+    uint32_t output;         /* RTW_OUT_* */
+    uint32_t flags;
+} rtw_render_opts;
+
+typedef struct rtw_stats {
+    uint64_t paths;          /* camera samples traced by the last render call */
+    uint64_t rays;           /* path segments (Scene::collision_normal equivalents) */
+    uint64_t nan_paths;      /* samples whose radiance was non-finite */
+    uint64_t gpu_launches;   /* kernels launched by the last render call */
+    float    kernel_ms;      /* device time of the trace kernel(s), CUDA events */
+    float    total_ms;       /* device time incl. resolve and D2H copy when there is one */
+} rtw_stats;
+
+typedef struct rtw_scene rtw_scene;   /* opaque: device-resident flattened scene + BVH */
+
+/* --- library */
+int         rtw_abi_version(void);
+const char* rtw_last_error(void);               /* thread-local message of the last failure */
+int         rtw_device_count(void);             /* 0 when no CUDA device is visible */
+
+/* --- camera helpers (host only) */
+/* Viewport::new (viewport.rs:308-401): aspect_ratio is width/height as f32; height is derived
+ * as (width / aspect) truncated. vfov in degrees. */
+int rtw_camera_init(rtw_camera* cam, uint32_t width, float aspect_ratio, float vfov_deg,
+                    const float origin[3], const float direction[3], const float vup[3],
+                    float lens_radius);
+/* Viewport::new_from_res (viewport.rs:402-428) */
+int rtw_camera_init_res(rtw_camera* cam, uint32_t width, uint32_t height, float vfov_deg,
+                        const float origin[3], const float direction[3], const float vup[3],
+                        float lens_radius);
+void rtw_render_opts_default(rtw_render_opts* o);   /* samples 1, depth 10, gamma 2, fps 30 ... */
+
+/* --- scene lifetime. `device` = CUDA ordinal, or -1 for the calling thread's current device.
+ * Replaces Scene::new / new_sphere / new_quad (viewport.rs:89-135): flattens, builds the
+ * two-level SAH BVH on the host and uploads. */
+int  rtw_scene_create(const rtw_scene_desc* desc, int device, rtw_scene** out);
+void rtw_scene_destroy(rtw_scene* scene);
+
+/* --- render. Blocking; `out_rgb` is HOST memory (rows top to bottom, [row][col][rgb], like Img).
+ * Replaces Viewport::render / render_no_rand / async_render depending on opts->mode. */
+int rtw_render(rtw_scene* scene, const rtw_camera* cam, const rtw_render_opts* opts,
+               float* out_rgb);
+/* Same, but `d_out_rgb` is DEVICE memory on the scene's device and `stream` a cudaStream_t
+ * (0 = default stream); returns after enqueueing (no host sync) so callers can chain a
+ * collective on the same stream. Stats of this call become valid after the stream syncs. */
+int rtw_render_device(rtw_scene* scene, const rtw_camera* cam, const rtw_render_opts* opts,
+                      float* d_out_rgb, void* stream);
+/* render_multi (viewport.rs:249-269): frames first_frame..first_frame+n_frames into
+ * out_rgb[n_frames][H][W][3] (host). */
+int rtw_render_frames(rtw_scene* scene, const rtw_camera* cam, const rtw_render_opts* opts,
+                      uint32_t first_frame, uint32_t n_frames, float* out_rgb);
+/* Resolve a (reduced) RTW_OUT_SUM buffer in place on the device: /= total_samples, powf(1/gamma)
+ * (render_row's last line, viewport.rs:301). n_pixels = rows*width. */
+int rtw_resolve_device(float* d_rgb, uint64_t n_pixels, uint32_t total_samples, float gamma,
+                       int device, void* stream);
+/* write_img_f32's quantiser (Rust/src/write_img.rs:6-19): (x*255) clamp round, NaN -> 0. Device in, device out. */
+int rtw_quantize_device(const float* d_rgb, uint8_t* d_rgb8, uint64_t n_values, int device,
+                        void* stream);
+
+int rtw_get_stats(rtw_scene* scene, rtw_stats* out);
+
+/* --- introspection used by tests and the bench (sizes of what was uploaded) */
+typedef struct rtw_scene_info {
+    uint32_t n_tlas_nodes, n_blas_nodes, n_tlas_leaves, n_flattened_instances;
+    uint32_t bvh_max_depth;
+    uint64_t device_bytes;
+} rtw_scene_info;
+int rtw_scene_get_info(rtw_scene* scene, rtw_scene_info* out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RTW_H */

@@ -1,0 +1,105 @@
+"""CudaBackend: the product's only renderer — a thin ctypes layer over librtw_b200.so (include/rtw.h).
+
+`torch` is optional here and only used for device buffers / streams when the caller wants the
+image to stay on the GPU (multi-GPU reduce); plain renders go host buffer -> rtw_render.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+
+from . import _abi as A
+
+
+def _f3(v):
+    return (C.c_float * 3)(*[float(x) for x in v])
+
+
+class CudaSceneHandle:
+    def __init__(self, lib, fs, device: int):
+        self._lib = lib
+        self._fs = fs
+        self._h = C.c_void_p()
+        A.check(lib.rtw_scene_create(C.byref(fs.desc), device, C.byref(self._h)))
+        self.device = device
+
+    def close(self):
+        if self._h:
+            self._lib.rtw_scene_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    @staticmethod
+    def out_shape(cam, o):
+        rows = o.row_count if o.row_count else cam.height
+        return (rows, cam.width, 3)
+
+    def render(self, cam, o) -> np.ndarray:
+        out = np.empty(self.out_shape(cam, o), dtype=np.float32)
+        A.check(self._lib.rtw_render(self._h, C.byref(cam), C.byref(o), out.ctypes.data_as(C.c_void_p)))
+        return out
+
+    def render_into(self, cam, o, host_out: np.ndarray) -> None:
+        """Render into a caller-owned host buffer (e.g. pinned memory)."""
+        A.check(self._lib.rtw_render(self._h, C.byref(cam), C.byref(o), C.c_void_p(host_out.ctypes.data)))
+
+    def render_device(self, cam, o, d_ptr: int, stream: int = 0) -> None:
+        """Enqueue a render into device memory `d_ptr` on CUDA stream `stream` (no host sync)."""
+        A.check(self._lib.rtw_render_device(self._h, C.byref(cam), C.byref(o), C.c_void_p(d_ptr),
+                                            C.c_void_p(stream)))
+
+    def render_frames(self, cam, o, first_frame: int, n_frames: int) -> np.ndarray:
+        rows = o.row_count if o.row_count else cam.height
+        out = np.empty((n_frames, rows, cam.width, 3), dtype=np.float32)
+        A.check(self._lib.rtw_render_frames(self._h, C.byref(cam), C.byref(o), first_frame, n_frames,
+                                            out.ctypes.data_as(C.c_void_p)))
+        return out
+
+    def stats(self) -> A.rtw_stats:
+        st = A.rtw_stats()
+        A.check(self._lib.rtw_get_stats(self._h, C.byref(st)))
+        return st
+
+    def info(self) -> A.rtw_scene_info:
+        inf = A.rtw_scene_info()
+        A.check(self._lib.rtw_scene_get_info(self._h, C.byref(inf)))
+        return inf
+
+
+class CudaBackend:
+    name = "cuda"
+
+    def __init__(self, device: int = -1):
+        self.lib = A.load_library()
+        self.device = device
+
+    def device_count(self) -> int:
+        return int(self.lib.rtw_device_count())
+
+    def camera_init(self, width, aspect_ratio, vfov, origin, direction, vup, lens_radius) -> A.rtw_camera:
+        cam = A.rtw_camera()
+        A.check(self.lib.rtw_camera_init(C.byref(cam), width, aspect_ratio, vfov, _f3(origin), _f3(direction),
+                                         _f3(vup), lens_radius))
+        return cam
+
+    def scene(self, scene) -> CudaSceneHandle:
+        key = ("cuda", self.device)
+        h = scene._backend_cache.get(key)
+        if h is None:
+            h = CudaSceneHandle(self.lib, scene.flatten(), self.device)
+            scene._backend_cache[key] = h
+        return h
+
+    def resolve_device(self, d_ptr: int, n_pixels: int, total_samples: int, gamma: float, stream: int = 0):
+        A.check(self.lib.rtw_resolve_device(C.c_void_p(d_ptr), n_pixels, total_samples, gamma, self.device,
+                                            C.c_void_p(stream)))
+
+    def quantize_device(self, d_rgb: int, d_rgb8: int, n_values: int, stream: int = 0):
+        A.check(self.lib.rtw_quantize_device(C.c_void_p(d_rgb), C.c_void_p(d_rgb8), n_values, self.device,
+                                             C.c_void_p(stream)))
