@@ -148,7 +148,12 @@ enum {
 };
 
 enum {
-    RTW_FLAG_ORDERED_ONLY = 1u   /* reserved */
+    /* Use the kernels compiled with -fmad=false: no a*b+c contraction, i.e. the same f32 operation
+     * sequence rustc emits for the reference (parity runs). Default: nvcc's FFMA contraction. */
+    RTW_FLAG_STRICT_FP = 1u,
+    /* Render through the wavefront pipeline (generate / extend / shade / accumulate kernels with
+     * ray queues in HBM) instead of the default path-regenerating megakernel. */
+    RTW_FLAG_WAVEFRONT = 2u
 };
 
 typedef struct rtw_render_opts {

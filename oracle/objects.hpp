@@ -26,8 +26,11 @@ using OptHit = std::optional<Hit>;
 
 // `min_hit == None || min_hit > i` (aabb.rs:136,148; viewport.rs:145): Option<Hit> ordering via
 // Hit::partial_cmp on t (objects.rs:44-48); strict, so the first of two equal t wins.
-inline void keep_closer(OptHit& min_hit, const OptHit& i) {
+// `tie` (optional) is raised when two candidates have exactly equal t: the reference's winner then
+// depends on its random BVH build order, so such pixels are unpinned.
+inline void keep_closer(OptHit& min_hit, const OptHit& i, bool* tie = nullptr) {
     if (!i) return;
+    if (tie && min_hit && min_hit->t == i->t) *tie = true;
     if (!min_hit || min_hit->t > i->t) min_hit = i;
 }
 

@@ -90,11 +90,13 @@ int oracle_scene_create(const rtw_scene_desc* d, uint32_t build_seed, oracle_sce
 
 void oracle_scene_destroy(oracle_scene* s) { delete s; }
 
-int oracle_render(oracle_scene* s, const rtw_camera* cam, const rtw_render_opts* opts, float* out,
-                  uint32_t threads, oracle_stats* st) {
+// `tie_mask` (optional, rows*width bytes): 1 where some closest-hit decision of the pixel was taken
+// between exactly equal t — the reference's result there depends on its random build order.
+int oracle_render_ex(oracle_scene* s, const rtw_camera* cam, const rtw_render_opts* opts, float* out,
+                     uint32_t threads, oracle_stats* st, uint8_t* tie_mask) {
     if (!s || !cam || !opts || !out) return RTW_E_INVALID;
     auto t0 = std::chrono::steady_clock::now();
-    RenderResult r = render(s->scene, *cam, *opts, out, threads);
+    RenderResult r = render(s->scene, *cam, *opts, out, threads, tie_mask);
     double sec = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
     if (st) {
         st->paths = r.paths; st->rays = r.rays; st->nan_paths = r.nan_paths;
@@ -104,6 +106,11 @@ int oracle_render(oracle_scene* s, const rtw_camera* cam, const rtw_render_opts*
         st->threads = threads ? threads : std::max(1u, std::thread::hardware_concurrency());
     }
     return RTW_OK;
+}
+
+int oracle_render(oracle_scene* s, const rtw_camera* cam, const rtw_render_opts* opts, float* out,
+                  uint32_t threads, oracle_stats* st) {
+    return oracle_render_ex(s, cam, opts, out, threads, st, nullptr);
 }
 
 int oracle_camera_init(rtw_camera* cam, uint32_t width, float aspect_ratio, float vfov_deg, const float origin[3],

@@ -114,7 +114,7 @@ inline Vec3 v3(const float* p) { return Vec3(p[0], p[1], p[2]); }
 // Viewport::render (:455-470) and render_no_rand (:502-508).
 inline Vec3 sample_pixel(const Scene& scene, const rtw_camera& cam, const rtw_render_opts& o,
                          const IntegratorCfg& ig, uint32_t i, uint32_t j, uint32_t s, uint32_t s_root,
-                         Counters* ctr, bool count) {
+                         Counters* ctr, bool count, bool* tie = nullptr) {
     PathRng rng;
     rng.k0 = (uint32_t)o.seed; rng.k1 = (uint32_t)(o.seed >> 32);
     rng.pixel = j * cam.width + i; rng.sample = s; rng.block = 0;
@@ -137,7 +137,9 @@ inline Vec3 sample_pixel(const Scene& scene, const rtw_camera& cam, const rtw_re
                             dv * ((float)j + (((float)y + c.f[1]) / (float)s_root)));
         }
     }
-    return ray_color(r, scene, o.depth, ig, cx);
+    Vec3 c = ray_color(r, scene, o.depth, ig, cx);
+    if (tie && cx.tie) *tie = true;
+    return c;
 }
 
 // Effective sample count of a mode (Viewport::render rounds up to a square, viewport.rs:443).
@@ -155,7 +157,7 @@ inline uint32_t effective_samples(const rtw_render_opts& o, uint32_t* s_root_out
 // Row-parallel over `threads` std::threads, one task per image row like async_render
 // (viewport.rs:236-244).
 inline RenderResult render(const Scene& scene, const rtw_camera& cam, const rtw_render_opts& o, float* out,
-                           unsigned threads) {
+                           unsigned threads, uint8_t* tie_mask = nullptr) {
     IntegratorCfg ig = integrator_cfg(o);
     uint32_t s_root = 1;
     uint32_t total = effective_samples(o, &s_root);
@@ -173,8 +175,9 @@ inline RenderResult render(const Scene& scene, const rtw_camera& cam, const rtw_
             uint32_t j = r0 + jr;
             for (uint32_t i = 0; i < cam.width; ++i) {
                 Vec3 color(0.f, 0.f, 0.f);
+                bool tie = false;
                 for (uint32_t s = s0; s < s0 + sn; ++s) {
-                    Vec3 c = sample_pixel(scene, cam, o, ig, i, j, s, s_root, &res.ctr, true);
+                    Vec3 c = sample_pixel(scene, cam, o, ig, i, j, s, s_root, &res.ctr, true, &tie);
                     if (!(std::isfinite(c.x) && std::isfinite(c.y) && std::isfinite(c.z))) ++res.nan_paths;
                     color += c;
                     ++res.paths;
@@ -184,6 +187,7 @@ inline RenderResult render(const Scene& scene, const rtw_camera& cam, const rtw_
                     if (o.mode == RTW_MODE_NO_RAND) px = gamma_correct(color, inv_g);           // viewport.rs:508
                     else px = gamma_correct(color / (float)total, inv_g);                        // :301, :472
                 }
+                if (tie_mask) tie_mask[(size_t)jr * cam.width + i] = tie ? 1 : 0;
                 float* d = out + ((size_t)jr * cam.width + i) * 3;
                 d[0] = px.x; d[1] = px.y; d[2] = px.z;
             }

@@ -22,7 +22,7 @@ struct TraceCtx {
     PathRng* rng = nullptr;
     uint32_t bounce = 0;
     Counters* ctr = nullptr;
-    bool ordered = false;     // false = faithful (visit both children, shade every candidate)
+    bool tie = false;         // set when a closest-hit decision was made between equal t (unpinned by the reference)
 };
 
 // Build-time randomness (`random::<Axis>()`, aabb.rs:42, qaabb.rs:134, iaabb.rs:87): a private
@@ -73,9 +73,9 @@ struct Bvh {
         if (!slab_test(box, r, mint, maxt, cx.ctr ? &cx.ctr->slab_tests : nullptr)) return std::nullopt;
         OptHit min_hit;
         if (!aabbs.empty()) {
-            for (const Bvh& c : aabbs) keep_closer(min_hit, c.collision_normal(r, mint, maxt, cx));
+            for (const Bvh& c : aabbs) keep_closer(min_hit, c.collision_normal(r, mint, maxt, cx), &cx.tie);
         } else {
-            for (const Prim* p : prims) keep_closer(min_hit, PrimTraits<Prim>::collide(*p, r, mint, maxt, cx));
+            for (const Prim* p : prims) keep_closer(min_hit, PrimTraits<Prim>::collide(*p, r, mint, maxt, cx), &cx.tie);
         }
         return min_hit;
     }
@@ -123,8 +123,8 @@ struct Instance {
 
     OptHit inner(const Ray& r, float mint, float maxt, TraceCtx& cx) const {   // instance.rs:262-271
         OptHit min_hit;
-        keep_closer(min_hit, saabb.collision_normal(r, mint, maxt, cx));
-        keep_closer(min_hit, qaabb.collision_normal(r, mint, maxt, cx));
+        keep_closer(min_hit, saabb.collision_normal(r, mint, maxt, cx), &cx.tie);
+        keep_closer(min_hit, qaabb.collision_normal(r, mint, maxt, cx), &cx.tie);
         return min_hit;
     }
 
@@ -209,9 +209,9 @@ struct Scene {
     OptHit collision_normal(const Ray& r, float mint, float maxt, TraceCtx& cx) const {
         if (cx.ctr) ++cx.ctr->rays;
         OptHit min_hit;
-        keep_closer(min_hit, aabb.collision_normal(r, mint, maxt, cx));
-        keep_closer(min_hit, qaabb.collision_normal(r, mint, maxt, cx));
-        keep_closer(min_hit, iaabb.collision_normal(r, mint, maxt, cx));
+        keep_closer(min_hit, aabb.collision_normal(r, mint, maxt, cx), &cx.tie);
+        keep_closer(min_hit, qaabb.collision_normal(r, mint, maxt, cx), &cx.tie);
+        keep_closer(min_hit, iaabb.collision_normal(r, mint, maxt, cx), &cx.tie);
         return min_hit;
     }
 };

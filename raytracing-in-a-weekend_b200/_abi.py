@@ -24,6 +24,8 @@ RTW_INT_GRADIENT, RTW_INT_D, RTW_INT_BG_COLOR, RTW_INT_NORMAL, RTW_INT_ALBEDO, R
 RTW_MODE_RANDOM, RTW_MODE_STRATIFIED, RTW_MODE_NO_RAND = range(3)
 # outputs
 RTW_OUT_RESOLVED, RTW_OUT_SUM = 0, 1
+# flags
+RTW_FLAG_STRICT_FP, RTW_FLAG_WAVEFRONT = 1, 2
 
 f32, u32, i32, u64 = C.c_float, C.c_uint32, C.c_int32, C.c_uint64
 f3 = f32 * 3

@@ -1,0 +1,364 @@
+// rtw_api.cu — the extern "C" boundary declared in include/rtw.h: scene upload, render calls,
+// resolve/quantise kernels, stats. The only product entry points; nothing here (or anywhere in
+// this library) can compute a pixel without a CUDA device.
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <new>
+#include <string>
+#include <vector>
+#include "rtw_host.h"
+#include "rtw_kernels.h"
+
+using namespace rtw;
+
+namespace {
+
+thread_local std::string g_err;
+int fail(int code, const std::string& msg) { g_err = msg; return code; }
+int cuda_fail(cudaError_t e, const char* what) {
+    g_err = std::string(what) + ": " + cudaGetErrorString(e);
+    cudaGetLastError();
+    return e == cudaErrorMemoryAllocation ? RTW_E_NOMEM : RTW_E_CUDA;
+}
+#define CK(call)                                              \
+    do {                                                      \
+        cudaError_t e__ = (call);                             \
+        if (e__ != cudaSuccess) return cuda_fail(e__, #call); \
+    } while (0)
+
+// viewport.rs:207-213 + :301 — mean over the samples, then powf(1/gamma) per channel, no clamp.
+__global__ void resolve_kernel(float* __restrict__ rgb, unsigned long long n_values, float total, float inv_gamma) {
+    unsigned long long k = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
+    const unsigned long long stride = (unsigned long long)gridDim.x * blockDim.x;
+    for (; k < n_values; k += stride) rgb[k] = powf(rgb[k] / total, inv_gamma);
+}
+
+// write_img_f32 (Rust/src/write_img.rs:6-19): (x*255).clamp(0,255).round() as u8; NaN -> 0.
+__global__ void quantize_kernel(const float* __restrict__ rgb, uint8_t* __restrict__ out, unsigned long long n_values) {
+    unsigned long long k = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
+    const unsigned long long stride = (unsigned long long)gridDim.x * blockDim.x;
+    for (; k < n_values; k += stride) {
+        float x = rgb[k] * 255.0f;
+        uint8_t q = 0;
+        if (x == x) {
+            x = x < 0.0f ? 0.0f : (x > 255.0f ? 255.0f : x);
+            q = (uint8_t)roundf(x);
+        }
+        out[k] = q;
+    }
+}
+
+int grid_for(unsigned long long n, int block) {
+    unsigned long long g = (n + block - 1) / block;
+    if (g < 1) g = 1;
+    if (g > 148ull * 16) g = 148ull * 16;
+    return (int)g;
+}
+
+}  // namespace
+
+struct rtw_scene {
+    int device = 0;
+    int sm_count = 0;
+    int occ_fast = 0, occ_strict = 0;
+    Scene d{};                            // device pointers
+    std::vector<void*> allocs;
+    std::vector<cudaArray_t> arrays;
+    std::vector<cudaTextureObject_t> texobjs;
+    rtw_scene_info info{};
+    cudaStream_t stream = nullptr;        // used by rtw_render / rtw_render_frames
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev2 = nullptr;
+    Counters* d_ctr = nullptr;
+    uint32_t* d_work = nullptr;
+    Counters* h_ctr = nullptr;            // pinned
+    float* d_img = nullptr; size_t d_img_floats = 0;
+    bool have_stats = false;
+    uint64_t launches = 0;
+
+    ~rtw_scene() {
+        cudaSetDevice(device);
+        for (auto t : texobjs) cudaDestroyTextureObject(t);
+        for (auto a : arrays) cudaFreeArray(a);
+        for (auto p : allocs) cudaFree(p);
+        if (d_img) cudaFree(d_img);
+        if (d_ctr) cudaFree(d_ctr);
+        if (d_work) cudaFree(d_work);
+        if (h_ctr) cudaFreeHost(h_ctr);
+        if (ev0) cudaEventDestroy(ev0);
+        if (ev1) cudaEventDestroy(ev1);
+        if (ev2) cudaEventDestroy(ev2);
+        if (stream) cudaStreamDestroy(stream);
+    }
+};
+
+namespace {
+
+template <class T>
+int upload(rtw_scene* s, const std::vector<T>& v, const T** out) {
+    size_t bytes = std::max<size_t>(v.size(), 1) * sizeof(T);
+    void* p = nullptr;
+    CK(cudaMalloc(&p, bytes));
+    s->allocs.push_back(p);
+    s->info.device_bytes += bytes;
+    if (!v.empty()) CK(cudaMemcpy(p, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice));
+    *out = static_cast<const T*>(p);
+    return RTW_OK;
+}
+
+int upload_scene(rtw_scene* s, HostScene& hs) {
+    int rc;
+    // image textures -> cudaArray + texture object (point filter, unnormalised coords)
+    for (size_t i = 0; i < hs.textures.size(); ++i) {
+        Texture& t = hs.textures[i];
+        t.obj = 0; t.texels = nullptr;
+        if (t.n_texels == 1u) continue;
+        cudaDeviceProp* unused = nullptr; (void)unused;
+        int max_w = 0, max_h = 0;
+        CK(cudaDeviceGetAttribute(&max_w, cudaDevAttrMaxTexture2DWidth, s->device));
+        CK(cudaDeviceGetAttribute(&max_h, cudaDevAttrMaxTexture2DHeight, s->device));
+        if ((int)t.width > max_w || (int)t.height > max_h) return fail(RTW_E_UNSUPPORTED, "texture exceeds the 2D texture limits");
+        cudaChannelFormatDesc cd = cudaCreateChannelDesc<float4>();
+        cudaArray_t arr = nullptr;
+        CK(cudaMallocArray(&arr, &cd, t.width, t.height));
+        s->arrays.push_back(arr);
+        s->info.device_bytes += (uint64_t)t.n_texels * sizeof(float4);
+        CK(cudaMemcpy2DToArray(arr, 0, 0, hs.texels[i].data(), t.width * sizeof(float4), t.width * sizeof(float4),
+                               t.height, cudaMemcpyHostToDevice));
+        cudaResourceDesc rd; std::memset(&rd, 0, sizeof rd);
+        rd.resType = cudaResourceTypeArray; rd.res.array.array = arr;
+        cudaTextureDesc td; std::memset(&td, 0, sizeof td);
+        td.addressMode[0] = td.addressMode[1] = cudaAddressModeClamp;
+        td.filterMode = cudaFilterModePoint; td.readMode = cudaReadModeElementType; td.normalizedCoords = 0;
+        cudaTextureObject_t obj = 0;
+        CK(cudaCreateTextureObject(&obj, &rd, &td, nullptr));
+        s->texobjs.push_back(obj);
+        t.obj = obj;
+    }
+    Scene& d = s->d;
+    if ((rc = upload(s, hs.nodes, &d.nodes))) return rc;
+    if ((rc = upload(s, hs.spheres, &d.spheres))) return rc;
+    if ((rc = upload(s, hs.sphere_vel, &d.sphere_vel))) return rc;
+    if ((rc = upload(s, hs.sphere_col, &d.sphere_col))) return rc;
+    if ((rc = upload(s, hs.sphere_ids, &d.sphere_ids))) return rc;
+    if ((rc = upload(s, hs.sphere_box, &d.sphere_box))) return rc;
+    if ((rc = upload(s, hs.quads, &d.quads))) return rc;
+    if ((rc = upload(s, hs.quad_ids, &d.quad_ids))) return rc;
+    if ((rc = upload(s, hs.instances, &d.instances))) return rc;
+    if ((rc = upload(s, hs.moving, &d.moving))) return rc;
+    if ((rc = upload(s, hs.materials, &d.materials))) return rc;
+    if ((rc = upload(s, hs.textures, &d.textures))) return rc;
+    if ((rc = upload(s, hs.noises, &d.noises))) return rc;
+    d.top = hs.top;
+    std::memcpy(d.background, hs.background, sizeof d.background);
+    d.n_noises = (uint32_t)hs.noises.size();
+    return RTW_OK;
+}
+
+// Work decomposition (see MegaLaunch): enough items to balance, chunks short enough that the tail
+// is small, long enough that the three REDs per lane per item are noise.
+MegaLaunch plan_mega(const rtw_scene* s, const RenderParams& P, bool strict) {
+    MegaLaunch L;
+    L.block = RTW_MEGA_BLOCK;
+    int occ = strict ? s->occ_strict : s->occ_fast;
+    if (occ < 1) occ = 1;
+    L.grid = s->sm_count * occ;
+    L.tiles_x = (P.cam.width + 7u) / 8u;
+    L.tiles_y = (P.row_count + 3u) / 4u;
+    const uint64_t tiles = (uint64_t)L.tiles_x * L.tiles_y;
+    const uint64_t resident_warps = (uint64_t)L.grid * (RTW_MEGA_BLOCK / 32);
+    uint64_t want_chunks = (16 * resident_warps + tiles - 1) / tiles;       // >= 16 items per resident warp
+    if (want_chunks < 1) want_chunks = 1;
+    if (want_chunks > P.sample_count) want_chunks = P.sample_count;
+    uint32_t chunk = (uint32_t)((P.sample_count + want_chunks - 1) / want_chunks);
+    if (chunk > 64u) chunk = 64u;
+    if (chunk < 1u) chunk = 1u;
+    L.chunk = chunk;
+    L.n_chunks = (P.sample_count + chunk - 1u) / chunk;
+    L.n_items = (uint32_t)std::min<uint64_t>(tiles * L.n_chunks, 0xFFFFFFF0ull);
+    const uint64_t max_useful_blocks = ((uint64_t)L.n_items + (RTW_MEGA_BLOCK / 32) - 1) / (RTW_MEGA_BLOCK / 32);
+    if ((uint64_t)L.grid > max_useful_blocks) L.grid = (int)std::max<uint64_t>(1, max_useful_blocks);
+    return L;
+}
+
+// Enqueue one render on `st` into device buffer d_out (row_count*W*3 floats).
+int enqueue_render(rtw_scene* s, const rtw_camera* cam, const rtw_render_opts* o, float* d_out, cudaStream_t st) {
+    RenderParams P; uint32_t total = 0; std::string err;
+    int rc = make_render_params(cam, o, P, total, err);
+    if (rc) return fail(rc, err);
+    const bool strict = (o->flags & RTW_FLAG_STRICT_FP) != 0;
+    MegaLaunch L = plan_mega(s, P, strict);
+    if ((uint64_t)L.tiles_x * L.tiles_y * L.n_chunks > 0xFFFFFFF0ull) return fail(RTW_E_UNSUPPORTED, "too many work items; shard the render");
+    const size_t n_values = (size_t)P.row_count * cam->width * 3u;
+    CK(cudaMemsetAsync(d_out, 0, n_values * sizeof(float), st));
+    CK(cudaMemsetAsync(s->d_ctr, 0, sizeof(Counters), st));
+    CK(cudaMemsetAsync(s->d_work, 0, sizeof(uint32_t), st));
+    CK(cudaEventRecord(s->ev0, st));
+    CK(strict ? launch_mega_strict(s->d, P, d_out, s->d_ctr, s->d_work, L, st)
+              : launch_mega_fast(s->d, P, d_out, s->d_ctr, s->d_work, L, st));
+    CK(cudaEventRecord(s->ev1, st));
+    s->launches = 1;
+    if (o->output == RTW_OUT_RESOLVED) {
+        resolve_kernel<<<grid_for(n_values, 256), 256, 0, st>>>(d_out, n_values, (float)total, 1.0f / o->gamma);
+        CK(cudaGetLastError());
+        s->launches += 1;
+    }
+    CK(cudaMemcpyAsync(s->h_ctr, s->d_ctr, sizeof(Counters), cudaMemcpyDeviceToHost, st));
+    CK(cudaEventRecord(s->ev2, st));
+    s->have_stats = true;
+    return RTW_OK;
+}
+
+int ensure_img(rtw_scene* s, size_t floats) {
+    if (s->d_img_floats >= floats) return RTW_OK;
+    if (s->d_img) { cudaFree(s->d_img); s->d_img = nullptr; s->d_img_floats = 0; }
+    CK(cudaMalloc(&s->d_img, floats * sizeof(float)));
+    s->d_img_floats = floats;
+    return RTW_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int rtw_abi_version(void) { return RTW_ABI_VERSION; }
+const char* rtw_last_error(void) { return g_err.c_str(); }
+
+int rtw_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+    return n;
+}
+
+int rtw_camera_init(rtw_camera* cam, uint32_t width, float aspect_ratio, float vfov_deg, const float origin[3],
+                    const float direction[3], const float vup[3], float lens_radius) {
+    if (!cam || !origin || !direction || !vup || width == 0 || !(aspect_ratio > 0.0f)) return fail(RTW_E_INVALID, "bad camera arguments");
+    camera_init(cam, width, aspect_ratio, vfov_deg, origin, direction, vup, lens_radius);
+    return RTW_OK;
+}
+int rtw_camera_init_res(rtw_camera* cam, uint32_t width, uint32_t height, float vfov_deg, const float origin[3],
+                        const float direction[3], const float vup[3], float lens_radius) {
+    if (height == 0) return fail(RTW_E_INVALID, "bad camera arguments");
+    return rtw_camera_init(cam, width, (float)width / (float)height, vfov_deg, origin, direction, vup, lens_radius);   // viewport.rs:402-428
+}
+
+void rtw_render_opts_default(rtw_render_opts* o) {
+    if (!o) return;
+    std::memset(o, 0, sizeof *o);
+    o->samples = 1; o->depth = 10; o->gamma = 2.0f;
+    o->integrator = RTW_INT_GRADIENT; o->mode = RTW_MODE_RANDOM;
+    o->shutter_speed = 0.0f; o->fps = 30.0f; o->frame = 0;   // viewport.rs:394-398
+    o->seed = 1; o->output = RTW_OUT_RESOLVED;
+}
+
+int rtw_scene_create(const rtw_scene_desc* desc, int device, rtw_scene** out) {
+    if (!out) return fail(RTW_E_INVALID, "null out pointer");
+    *out = nullptr;
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0) {
+        cudaGetLastError();
+        return fail(RTW_E_CUDA, std::string("no usable CUDA device (") + (e != cudaSuccess ? cudaGetErrorString(e) : "count 0") +
+                                    "); this library has no CPU path");
+    }
+    if (device < 0) { CK(cudaGetDevice(&device)); }
+    if (device >= ndev) return fail(RTW_E_INVALID, "device ordinal out of range");
+    HostScene hs; std::string err;
+    int rc = build_host_scene(desc, hs, err);
+    if (rc) return fail(rc, err);
+    CK(cudaSetDevice(device));
+    rtw_scene* s = new (std::nothrow) rtw_scene();
+    if (!s) return fail(RTW_E_NOMEM, "out of host memory");
+    s->device = device;
+    s->info = hs.info;
+    s->info.device_bytes = 0;
+    auto bail = [&](int code) { delete s; return code; };
+    if ((rc = upload_scene(s, hs))) return bail(rc);
+    cudaError_t ce;
+    if ((ce = cudaDeviceGetAttribute(&s->sm_count, cudaDevAttrMultiProcessorCount, device)) != cudaSuccess) return bail(cuda_fail(ce, "sm count"));
+    if ((ce = mega_occupancy_fast(&s->occ_fast)) != cudaSuccess) return bail(cuda_fail(ce, "occupancy(fast)"));
+    if ((ce = mega_occupancy_strict(&s->occ_strict)) != cudaSuccess) return bail(cuda_fail(ce, "occupancy(strict)"));
+    if ((ce = cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking)) != cudaSuccess) return bail(cuda_fail(ce, "stream"));
+    if ((ce = cudaEventCreate(&s->ev0)) != cudaSuccess || (ce = cudaEventCreate(&s->ev1)) != cudaSuccess ||
+        (ce = cudaEventCreate(&s->ev2)) != cudaSuccess) return bail(cuda_fail(ce, "events"));
+    if ((ce = cudaMalloc(&s->d_ctr, sizeof(Counters))) != cudaSuccess) return bail(cuda_fail(ce, "counters"));
+    if ((ce = cudaMalloc(&s->d_work, sizeof(uint32_t))) != cudaSuccess) return bail(cuda_fail(ce, "work counter"));
+    if ((ce = cudaMallocHost(&s->h_ctr, sizeof(Counters))) != cudaSuccess) return bail(cuda_fail(ce, "pinned counters"));
+    std::memset(s->h_ctr, 0, sizeof(Counters));
+    *out = s;
+    return RTW_OK;
+}
+
+void rtw_scene_destroy(rtw_scene* scene) { delete scene; }
+
+int rtw_render_device(rtw_scene* scene, const rtw_camera* cam, const rtw_render_opts* opts, float* d_out_rgb, void* stream) {
+    if (!scene || !cam || !opts || !d_out_rgb) return fail(RTW_E_INVALID, "null argument");
+    CK(cudaSetDevice(scene->device));
+    return enqueue_render(scene, cam, opts, d_out_rgb, static_cast<cudaStream_t>(stream));
+}
+
+int rtw_render(rtw_scene* scene, const rtw_camera* cam, const rtw_render_opts* opts, float* out_rgb) {
+    if (!scene || !cam || !opts || !out_rgb) return fail(RTW_E_INVALID, "null argument");
+    CK(cudaSetDevice(scene->device));
+    const uint32_t rows = opts->row_count ? opts->row_count : cam->height;
+    const size_t n_values = (size_t)rows * cam->width * 3u;
+    int rc = ensure_img(scene, n_values);
+    if (rc) return rc;
+    if ((rc = enqueue_render(scene, cam, opts, scene->d_img, scene->stream))) return rc;
+    CK(cudaMemcpyAsync(out_rgb, scene->d_img, n_values * sizeof(float), cudaMemcpyDeviceToHost, scene->stream));
+    CK(cudaEventRecord(scene->ev2, scene->stream));
+    CK(cudaStreamSynchronize(scene->stream));
+    return RTW_OK;
+}
+
+int rtw_render_frames(rtw_scene* scene, const rtw_camera* cam, const rtw_render_opts* opts, uint32_t first_frame,
+                      uint32_t n_frames, float* out_rgb) {
+    if (!scene || !cam || !opts || !out_rgb) return fail(RTW_E_INVALID, "null argument");
+    const uint32_t rows = opts->row_count ? opts->row_count : cam->height;
+    const size_t n_values = (size_t)rows * cam->width * 3u;
+    rtw_render_opts o = *opts;
+    for (uint32_t k = 0; k < n_frames; ++k) {   // render_multi (viewport.rs:256-267): only `frame` changes
+        o.frame = first_frame + k;
+        int rc = rtw_render(scene, cam, &o, out_rgb + (size_t)k * n_values);
+        if (rc) return rc;
+    }
+    return RTW_OK;
+}
+
+int rtw_resolve_device(float* d_rgb, uint64_t n_pixels, uint32_t total_samples, float gamma, int device, void* stream) {
+    if (!d_rgb || total_samples == 0 || !(gamma > 0.0f)) return fail(RTW_E_INVALID, "bad resolve arguments");
+    if (device >= 0) CK(cudaSetDevice(device));
+    const unsigned long long n = n_pixels * 3ull;
+    resolve_kernel<<<grid_for(n, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(d_rgb, n, (float)total_samples, 1.0f / gamma);
+    CK(cudaGetLastError());
+    return RTW_OK;
+}
+
+int rtw_quantize_device(const float* d_rgb, uint8_t* d_rgb8, uint64_t n_values, int device, void* stream) {
+    if (!d_rgb || !d_rgb8) return fail(RTW_E_INVALID, "null argument");
+    if (device >= 0) CK(cudaSetDevice(device));
+    quantize_kernel<<<grid_for(n_values, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(d_rgb, d_rgb8, n_values);
+    CK(cudaGetLastError());
+    return RTW_OK;
+}
+
+int rtw_get_stats(rtw_scene* scene, rtw_stats* out) {
+    if (!scene || !out) return fail(RTW_E_INVALID, "null argument");
+    std::memset(out, 0, sizeof *out);
+    if (!scene->have_stats) return RTW_OK;
+    CK(cudaSetDevice(scene->device));
+    CK(cudaEventSynchronize(scene->ev2));
+    out->paths = scene->h_ctr->paths; out->rays = scene->h_ctr->rays; out->nan_paths = scene->h_ctr->nan_paths;
+    out->gpu_launches = scene->launches;
+    CK(cudaEventElapsedTime(&out->kernel_ms, scene->ev0, scene->ev1));
+    CK(cudaEventElapsedTime(&out->total_ms, scene->ev0, scene->ev2));
+    return RTW_OK;
+}
+
+int rtw_scene_get_info(rtw_scene* scene, rtw_scene_info* out) {
+    if (!scene || !out) return fail(RTW_E_INVALID, "null argument");
+    *out = scene->info;
+    return RTW_OK;
+}
+
+}  // extern "C"

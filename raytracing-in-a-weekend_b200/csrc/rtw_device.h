@@ -1,0 +1,231 @@
+// rtw_device.h — plain-data layout of the device-resident scene, f32 vector algebra and the
+// counter-based RNG shared by every kernel of librtw_b200.so.
+//
+// Everything here is `__host__ __device__` so that the host-side scene builder (scene_build.cpp)
+// and the kernels (rtw_kernels.cu) agree on one definition. The arithmetic restates
+// Rust/src/vec3.rs of Terence-23/RayTracing-in-a-weekend operation by operation (left-to-right
+// products and sums); rtw_kernels.cu is compiled twice, once with -fmad=false (RTW_FLAG_STRICT_FP:
+// no a*b+c contraction, like rustc) and once with nvcc's default contraction (the fast build).
+#pragma once
+#include <stdint.h>
+#include <math.h>
+#include <string.h>
+#include <cuda_runtime.h>   // float4, uint4, cudaTextureObject_t (host and device)
+
+#if defined(__CUDACC__)
+#define RTW_HD __host__ __device__ __forceinline__
+#define RTW_HD_NOINL inline __host__ __device__ __noinline__
+#else
+#define RTW_HD inline
+#define RTW_HD_NOINL inline
+#endif
+
+namespace rtw {
+
+// ------------------------------------------------------------------ Vec3 (vec3.rs:10-262)
+struct V3 { float x, y, z; };
+RTW_HD V3 v3(float x, float y, float z) { V3 r; r.x = x; r.y = y; r.z = z; return r; }
+RTW_HD V3 operator-(V3 a) { return v3(-a.x, -a.y, -a.z); }
+RTW_HD V3 operator+(V3 a, V3 b) { return v3(a.x + b.x, a.y + b.y, a.z + b.z); }
+RTW_HD V3 operator-(V3 a, V3 b) { return v3(a.x - b.x, a.y - b.y, a.z - b.z); }
+RTW_HD V3 operator*(V3 a, float s) { return v3(a.x * s, a.y * s, a.z * s); }
+RTW_HD V3 operator*(V3 a, V3 b) { return v3(a.x * b.x, a.y * b.y, a.z * b.z); }
+RTW_HD V3 operator/(V3 a, float s) { return v3(a.x / s, a.y / s, a.z / s); }
+RTW_HD float dot(V3 a, V3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }            // vec3.rs:194-196
+RTW_HD V3 cross(V3 a, V3 b) {                                                           // vec3.rs:197-203
+    return v3(a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x);
+}
+RTW_HD float length(V3 a) { return sqrtf(a.x * a.x + a.y * a.y + a.z * a.z); }          // vec3.rs:191-193
+RTW_HD float length2(V3 a) { return a.x * a.x + a.y * a.y + a.z * a.z; }                // vec3.rs:188-190
+RTW_HD V3 unit(V3 a) { return a / length(a); }                                           // vec3.rs:204-206
+RTW_HD V3 reflect(V3 v, V3 n) { return v - n * 2.0f * dot(v, n); }                       // vec3.rs:256-258
+RTW_HD bool close_to_zero(V3 a) {                                                        // vec3.rs:259-261
+    return fabsf(a.x) < 1e-7f && fabsf(a.y) < 1e-7f && fabsf(a.z) < 1e-7f;
+}
+RTW_HD bool finite3(V3 a) { return isfinite(a.x) && isfinite(a.y) && isfinite(a.z); }
+
+// bit casts
+RTW_HD uint32_t f2u(float f) {
+#if defined(__CUDA_ARCH__)
+    return __float_as_uint(f);
+#else
+    uint32_t u; memcpy(&u, &f, 4); return u;
+#endif
+}
+RTW_HD float u2f(uint32_t u) {
+#if defined(__CUDA_ARCH__)
+    return __uint_as_float(u);
+#else
+    float f; memcpy(&f, &u, 4); return f;
+#endif
+}
+
+// ------------------------------------------------------------------ child / primitive references
+// A reference names either an internal BVH node or one primitive: top 2 bits = kind.
+enum : uint32_t { KIND_NODE = 0u, KIND_SPHERE = 1u, KIND_QUAD = 2u, KIND_INSTANCE = 3u };
+static const uint32_t REF_NONE = 0xFFFFFFFFu;
+RTW_HD uint32_t ref_kind(uint32_t r) { return r >> 30; }
+RTW_HD uint32_t ref_index(uint32_t r) { return r & 0x3FFFFFFFu; }
+RTW_HD uint32_t make_ref(uint32_t kind, uint32_t idx) { return (kind << 30) | idx; }
+
+// ------------------------------------------------------------------ scene records (all 16-byte aligned)
+// BVH node = both children's boxes + both child references: 64 B, fetched as four 128-bit loads.
+//   n0 = (lo0.x lo0.y lo0.z hi0.x)  n1 = (hi0.y hi0.z lo1.x lo1.y)  n2 = (lo1.z hi1.x hi1.y hi1.z)
+//   n3 = (bits c0, bits c1, 0, 0)
+struct Node { float4 n0, n1, n2; uint4 n3; };
+
+// One traversable level (the scene top level, or the inside of one instance): root reference +
+// root box (the reference slab-tests every BVH root: aabb.rs:109-126) + the level's moving
+// spheres, which live outside the tree (their t=0 box is tested with the un-shrunk
+// interval).
+struct Level {
+    float lo[3]; uint32_t root;        // REF_NONE when the level is empty (aabb.rs:106)
+    float hi[3]; uint32_t mov_first;   // range in Scene::moving
+    uint32_t mov_count, pad0, pad1, pad2;
+};
+
+// Instance (instance.rs:28-39): translation, the reference's Euler map for -rotation (world ->
+// local) and +rotation (local -> world) as coefficient rows (see rot_apply), its level.
+struct Instance {
+    float t[3]; float density;
+    float inv_rows[12];
+    float fwd_rows[12];
+    uint32_t flags;                    // bit0: const-density volume, bit1: rotation == 0
+    uint32_t index;                    // position in Scene.instances (selects the volume RNG stream)
+    uint32_t pad0, pad1;
+    Level level;
+};
+enum : uint32_t { INST_VOLUME = 1u, INST_ROT_IDENTITY = 2u };
+
+struct Quad {   // quad.rs:8-20 with normal/d/w derived as quad.rs:93-105. 64 B.
+    float4 q0;  // normal.xyz, d
+    float4 q1;  // origin.xyz, u.x
+    float4 q2;  // u.y u.z v.x v.y
+    float4 q3;  // v.z, w.xyz
+};
+
+struct Material {  // materials.rs:15-20
+    float metallicness, opacity, ir, pad;
+    float emitted[3]; float pad1;
+};
+
+struct Texture {   // texture.rs:21-27 (`row` = width, `col` = height)
+    uint32_t width, height;
+    int32_t noise_id; float noise_scale;
+    float solid[3]; uint32_t n_texels;
+    cudaTextureObject_t obj;           // float4 texels, point filter, unnormalised coords; 0 for 1x1
+    const float4* texels;              // linear copy (host builds; device keeps it for 1-row fallbacks)
+};
+
+struct Noise {     // texture.rs:63-69; perms stored & 255 (index is masked anyway, texture.rs:171-174)
+    float4 ranvec[256];
+    uint8_t perm[3][256];
+};
+
+struct Scene {
+    const Node* nodes;
+    const float4* spheres;        // origin.xyz, radius
+    const float4* sphere_vel;     // velocity.xyz, 0   (read only for moving spheres)
+    const float4* sphere_col;     // col_mod.xyz, bits(flags: bit0 moving)
+    const uint2* sphere_ids;      // mat_id, tex_id
+    const float4* sphere_box;     // 2 per sphere: t=0 leaf box lo, hi (aabb.rs:27-38), moving only
+    const Quad* quads;
+    const uint2* quad_ids;
+    const Instance* instances;
+    const uint32_t* moving;       // sphere indices
+    const Material* materials;
+    const Texture* textures;
+    const Noise* noises;
+    Level top;
+    float background[3];
+    uint32_t n_noises;
+};
+
+// ------------------------------------------------------------------ Vec3::rotated (vec3.rs:161-181)
+// The reference's Euler map is linear; per instance the host stores, for each output row, the
+// factors in the reference's own evaluation order:
+//   x' = (x*r0)*r1 + y*r2 + z*r3            r = (cb, cc, sa*sb*cc - sa*cc, ca*sb*cc + sa*sc)
+//   y' = (x*r4)*r5 + y*r6 + z*r7            r = (cb, sc, sa*sb*sc + ca*cc, ca*sb*sc - sa*cc)
+//   z' = x*r8 + (y*r9)*r10 + (z*r11)*r10    r = (-sb, sa, cb, ca)
+RTW_HD V3 rot_apply(const float* r, V3 p) {
+    V3 o;
+    o.x = p.x * r[0] * r[1] + p.y * r[2] + p.z * r[3];
+    o.y = p.x * r[4] * r[5] + p.y * r[6] + p.z * r[7];
+    o.z = p.x * r[8] + p.y * r[9] * r[10] + p.z * r[11] * r[10];
+    return o;
+}
+
+// ------------------------------------------------------------------ Philox4x32-10
+// Stream discipline (shared with the test oracle so renders can be compared sample for sample;
+// the reference itself is unseeded):
+//   key = seed; counter = (pixel index, global sample index, block, stream)
+//   stream 0: camera block, lens-disk blocks, then per bounce one block (dielectric coin) or one
+//             block per random_unit_vec rejection turn — consumed in path order;
+//   stream 1+k: volume of instance k, block = (bounce << 16) | j, j = 0 free-flight xi,
+//             j >= 1 rejection turns of the scatter normal.
+struct U4 { uint32_t x, y, z, w; };
+RTW_HD void mulhilo(uint32_t a, uint32_t b, uint32_t& hi, uint32_t& lo) {
+#if defined(__CUDA_ARCH__)
+    hi = __umulhi(a, b); lo = a * b;
+#else
+    uint64_t p = (uint64_t)a * b; hi = (uint32_t)(p >> 32); lo = (uint32_t)p;
+#endif
+}
+RTW_HD U4 philox4x32_10(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, uint32_t k0, uint32_t k1) {
+#pragma unroll
+    for (int r = 0; r < 10; ++r) {
+        uint32_t hi0, lo0, hi1, lo1;
+        mulhilo(0xD2511F53u, c0, hi0, lo0);
+        mulhilo(0xCD9E8D57u, c2, hi1, lo1);
+        uint32_t n0 = hi1 ^ c1 ^ k0, n2 = hi0 ^ c3 ^ k1;
+        c0 = n0; c1 = lo1; c2 = n2; c3 = lo0;
+        k0 += 0x9E3779B9u; k1 += 0xBB67AE85u;
+    }
+    U4 o; o.x = c0; o.y = c1; o.z = c2; o.w = c3; return o;
+}
+// rand 0.8.5 Standard f32: 24 random bits in [0,1)
+RTW_HD float u32_to_unit(uint32_t w) { return (float)(w >> 8) * (1.0f / 16777216.0f); }
+
+struct PathRng {
+    uint32_t k0, k1, pixel, sample, block;
+    RTW_HD float4 at(uint32_t blk, uint32_t stream) const {
+        U4 p = philox4x32_10(pixel, sample, blk, stream, k0, k1);
+        return make_float4(u32_to_unit(p.x), u32_to_unit(p.y), u32_to_unit(p.z), u32_to_unit(p.w));
+    }
+    RTW_HD float4 next4() { return at(block++, 0u); }
+};
+
+// vec3.rs:216-238: Vec3::random(-1,1) -> reject outside the unit ball -> unit()
+RTW_HD V3 random_unit_vec(PathRng& rng) {
+    for (;;) {
+        float4 r = rng.next4();
+        V3 p = v3(r.x * (1.0f - -1.0f) + -1.0f, r.y * (1.0f - -1.0f) + -1.0f, r.z * (1.0f - -1.0f) + -1.0f);
+        if (p.x * p.x + p.y * p.y + p.z * p.z <= 1.0f) return unit(p);
+    }
+}
+RTW_HD V3 random_unit_vec_stream(const PathRng& rng, uint32_t base_block, uint32_t stream) {
+    for (uint32_t turn = 0;; ++turn) {
+        float4 r = rng.at(base_block | (turn + 1u), stream);
+        V3 p = v3(r.x * (1.0f - -1.0f) + -1.0f, r.y * (1.0f - -1.0f) + -1.0f, r.z * (1.0f - -1.0f) + -1.0f);
+        if (p.x * p.x + p.y * p.y + p.z * p.z <= 1.0f) return unit(p);
+    }
+}
+// vec3.rs:240-254: two candidate points per block
+RTW_HD V3 random_in_unit_disk(PathRng& rng) {
+    for (;;) {
+        float4 r = rng.next4();
+        V3 p = v3(r.x * 2.0f - 1.0f, r.y * 2.0f - 1.0f, 0.f);
+        if (p.x * p.x + p.y * p.y <= 1.0f) return p;
+        V3 q = v3(r.z * 2.0f - 1.0f, r.w * 2.0f - 1.0f, 0.f);
+        if (q.x * q.x + q.y * q.y <= 1.0f) return q;
+    }
+}
+
+// ------------------------------------------------------------------ read-only loads
+#if defined(__CUDA_ARCH__)
+#define RTW_LDG(p) __ldg(p)
+#else
+#define RTW_LDG(p) (*(p))
+#endif
+
+}  // namespace rtw

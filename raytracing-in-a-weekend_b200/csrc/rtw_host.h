@@ -1,0 +1,46 @@
+// rtw_host.h — host-side flattened scene: what rtw_scene_create builds from an rtw_scene_desc
+// before uploading. Replaces Scene::new / AABB::new / QuadAABB::new / IAABB::new
+// (Rust/src/viewport.rs:120-135, objects/aabb/aabb.rs:20-71, qaabb.rs:127-163, iaabb.rs:80-116):
+// one two-level SAH BVH instead of three random-axis median-split trees plus two per instance.
+#pragma once
+#include <string>
+#include <vector>
+#include "rtw_device.h"
+#include "../../include/rtw.h"
+
+namespace rtw {
+
+struct HostScene {
+    std::vector<Node> nodes;
+    std::vector<float4> spheres, sphere_vel, sphere_col, sphere_box;
+    std::vector<uint2> sphere_ids;
+    std::vector<Quad> quads;
+    std::vector<uint2> quad_ids;
+    std::vector<Instance> instances;
+    std::vector<uint32_t> moving;
+    std::vector<Material> materials;
+    std::vector<Texture> textures;                 // obj / texels pointers are filled by the uploader
+    std::vector<std::vector<float4>> texels;       // per texture, RGBA f32 (A = 0)
+    std::vector<Noise> noises;
+    Level top;
+    float background[3];
+    rtw_scene_info info;
+
+    // A Scene whose pointers address the vectors above (host memory): what the CPU-side unit
+    // tests of the traversal code walk. The product uploads the same arrays to the device.
+    Scene host_view();
+};
+
+// Validates `d`, flattens it and builds the BVH. Returns RTW_OK or RTW_E_*; `err` explains.
+int build_host_scene(const rtw_scene_desc* d, HostScene& out, std::string& err);
+
+// Viewport::new (viewport.rs:308-401)
+void camera_init(rtw_camera* cam, uint32_t width, float aspect_ratio, float vfov_deg, const float origin[3],
+                 const float direction[3], const float vup[3], float lens_radius);
+
+// Integrator constants + derived launch parameters. Returns RTW_OK or RTW_E_INVALID.
+struct RenderParams;
+int make_render_params(const rtw_camera* cam, const rtw_render_opts* o, RenderParams& P, uint32_t& total_samples,
+                       std::string& err);
+
+}  // namespace rtw

@@ -1,0 +1,343 @@
+// rtw_shade.h — "generate" and "shade/scatter": camera rays, the Hit of the winning primitive
+// (normal, UV, texel, Perlin), the uber-material and the integrators, as an iterative path state
+// machine.
+//
+// Restates, for one path:
+//   render_row / Viewport::render / render_no_rand loop bodies   Rust/src/viewport.rs:287-300,455-470,502-508
+//   Sphere / Quad::collision_normal after the root is accepted    objects/sphere.rs:124-146, quad.rs:61-80
+//   Instance::collision_normal hit mapping + volume scatter       objects/instance.rs:280-307
+//   ImageTexture::color_at, PerlinNoise::noise / perlin_interp    texture.rs:86-108,154-179,259-267
+//   Material::on_hit, refract, reflectance, diffuse               objects/materials.rs:89-154,213-228
+//   ray_color_gradient / ray_color_bg_color / ray_color_d         viewport/ray_color.rs:12-92, main.rs:17-46
+// The recursion L = emitted + col_mod * L(next) becomes rad += thr*emitted; thr *= col_mod.
+#pragma once
+#include "rtw_trace.h"
+#include "../../include/rtw.h"
+
+namespace rtw {
+
+// Per-launch constants (kernel parameter).
+struct RenderParams {
+    rtw_camera cam;
+    uint32_t integrator, mode;
+    uint32_t depth;
+    uint32_t s_root;          // STRATIFIED: ceil(sqrt(samples))
+    float mint, maxt;
+    float time0;              // frame / fps
+    float shutter_speed;
+    uint32_t k0, k1;          // Philox key
+    uint32_t row_begin, row_count;
+    uint32_t sample_begin, sample_count;
+};
+
+struct Hit {   // objects.rs:16-22
+    float t;
+    V3 normal, point, col_mod;
+    float metallicness, opacity, ir;
+    V3 emitted;
+};
+
+// ------------------------------------------------------------------ texture.rs
+// perlin_interp (texture.rs:86-108)
+RTW_HD float perlin_interp(const V3 c[2][2][2], float u, float v, float w) {
+    float uu = u * u * (3.0f - 2.0f * u);
+    float vv = v * v * (3.0f - 2.0f * v);
+    float ww = w * w * (3.0f - 2.0f * w);
+    float accum = 0.0f;
+#pragma unroll
+    for (int ii = 0; ii < 2; ++ii)
+#pragma unroll
+        for (int jj = 0; jj < 2; ++jj)
+#pragma unroll
+            for (int kk = 0; kk < 2; ++kk) {
+                float i = (float)ii, j = (float)jj, k = (float)kk;
+                V3 weight_v = v3(u - i, v - j, w - k);
+                accum += (i * uu + (1.0f - i) * (1.0f - uu)) * (j * vv + (1.0f - j) * (1.0f - vv)) *
+                         (k * ww + (1.0f - k) * (1.0f - ww)) * dot(c[ii][jj][kk], weight_v);
+            }
+    return accum;
+}
+RTW_HD int floor_to_int(float f) {
+#if defined(__CUDA_ARCH__)
+    return __float2int_rd(f);
+#else
+    float fl = floorf(f);
+    if (!(fl == fl)) return 0;
+    if (fl >= 2147483648.0f) return 2147483647;
+    if (fl <= -2147483648.0f) return (int)0x80000000;
+    return (int)fl;
+#endif
+}
+// PerlinNoise::noise (texture.rs:154-179). `nz` may point at shared memory (staged tables).
+RTW_HD float perlin_noise(const Noise* nz, V3 p) {
+    float u = p.x - floorf(p.x), v = p.y - floorf(p.y), w = p.z - floorf(p.z);
+    int i = floor_to_int(p.x), j = floor_to_int(p.y), k = floor_to_int(p.z);
+    V3 c[2][2][2];
+#pragma unroll
+    for (int di = 0; di < 2; ++di)
+#pragma unroll
+        for (int dj = 0; dj < 2; ++dj)
+#pragma unroll
+            for (int dk = 0; dk < 2; ++dk) {
+                uint32_t idx = (uint32_t)(nz->perm[0][(i + di) & 255] ^ nz->perm[1][(j + dj) & 255] ^
+                                          nz->perm[2][(k + dk) & 255]) & 255u;
+                float4 rv = nz->ranvec[idx];
+                c[di][dj][dk] = v3(rv.x, rv.y, rv.z);
+            }
+    return perlin_interp(c, u, v, w);
+}
+
+// `f32 as usize` saturates: negative / NaN -> 0 (sphere.rs:137-138)
+RTW_HD uint32_t to_usize(float f) {
+    if (!(f > 0.0f)) return 0u;
+    if (f >= 4294967040.0f) return 0xFFFFFFFFu;
+    return (uint32_t)f;
+}
+
+// ImageTexture::color_at (texture.rs:259-267)
+RTW_HD V3 texture_color_at(const Scene& sc, const Noise* noise_tables, const Texture& tx, uint32_t x, uint32_t y, V3 p) {
+    float noise_mult = 1.0f;
+    if (tx.noise_id >= 0) noise_mult = perlin_noise(&noise_tables[tx.noise_id], p / tx.noise_scale);
+    V3 texel;
+    if (tx.n_texels == 1u) {
+        texel = v3(tx.solid[0], tx.solid[1], tx.solid[2]);
+    } else {
+        // idx = y*row + x, kept inside the image (the reference would panic past the end)
+        uint64_t idx = (uint64_t)y * tx.width + x;
+        if (idx >= tx.n_texels) idx = tx.n_texels - 1u;
+#if defined(__CUDA_ARCH__)
+        uint32_t yy = (uint32_t)(idx / tx.width), xx = (uint32_t)(idx - (uint64_t)yy * tx.width);
+        float4 t = tex2D<float4>(tx.obj, (float)xx + 0.5f, (float)yy + 0.5f);
+#else
+        float4 t = tx.texels[idx];
+#endif
+        texel = v3(t.x, t.y, t.z);
+    }
+    return texel * noise_mult;
+}
+
+// ------------------------------------------------------------------ Hit of the winning primitive
+RTW_HD void load_material(const Scene& sc, uint32_t mat_id, Hit& h) {
+    const float4* mp = reinterpret_cast<const float4*>(&sc.materials[mat_id]);
+    float4 m0 = RTW_LDG(mp), m1 = RTW_LDG(mp + 1);
+    h.metallicness = m0.x; h.opacity = m0.y; h.ir = m0.z;
+    h.emitted = v3(m1.x, m1.y, m1.z);
+}
+
+// sphere.rs:124-146
+RTW_HD void eval_sphere(const Scene& sc, const Noise* nt, uint32_t idx, const Ray& r, float t, Hit& h) {
+    float4 s = RTW_LDG(&sc.spheres[idx]);
+    float4 col = RTW_LDG(&sc.sphere_col[idx]);
+    uint2 ids = RTW_LDG(&sc.sphere_ids[idx]);
+    V3 c = v3(s.x, s.y, s.z);
+    if (f2u(col.w) & 1u) {
+        float4 vel = RTW_LDG(&sc.sphere_vel[idx]);
+        c = c + v3(vel.x, vel.y, vel.z) * r.time;
+    }
+    V3 p = r.o + r.d * t;
+    V3 normal = unit(p - c);
+    const Texture& tx = sc.textures[ids.y];
+    uint32_t tex_x = 0u, tex_y = 0u;
+    if (tx.n_texels != 1u) {
+        const float PI = 3.14159265358979323846f, FRAC_1_PI = 0.31830988618379067154f;
+        float u = (atan2f(-normal.z, normal.x) + PI) * FRAC_1_PI * 0.5f;
+        float v = 1.0f - (FRAC_1_PI * acosf(-normal.y));
+        tex_x = to_usize(floorf(u * (float)(tx.width - 1u)));
+        tex_y = to_usize(floorf(v * (float)(tx.height - 1u)));
+    }
+    h.t = t; h.normal = normal; h.point = p;
+    h.col_mod = texture_color_at(sc, nt, tx, tex_x, tex_y, p) * v3(col.x, col.y, col.z);
+    load_material(sc, ids.x, h);
+}
+
+// quad.rs:61-80
+RTW_HD void eval_quad(const Scene& sc, const Noise* nt, uint32_t idx, const Ray& r, float t, Hit& h) {
+    const Quad* qp = &sc.quads[idx];
+    float4 q0 = RTW_LDG(&qp->q0), q1 = RTW_LDG(&qp->q1), q2 = RTW_LDG(&qp->q2), q3 = RTW_LDG(&qp->q3);
+    uint2 ids = RTW_LDG(&sc.quad_ids[idx]);
+    V3 p = r.o + r.d * t;
+    const Texture& tx = sc.textures[ids.y];
+    uint32_t tex_x = 0u, tex_y = 0u;
+    if (tx.n_texels != 1u) {
+        V3 planar = p - v3(q1.x, q1.y, q1.z);
+        V3 u = v3(q1.w, q2.x, q2.y), v = v3(q2.z, q2.w, q3.x), w = v3(q3.y, q3.z, q3.w);
+        float alfa = dot(w, cross(planar, v));
+        float beta = dot(w, cross(u, planar));
+        tex_x = alfa != 1.0f ? to_usize(floorf(alfa * (float)tx.width)) : tx.width - 1u;
+        tex_y = beta != 1.0f ? to_usize(floorf(beta * (float)tx.height)) : tx.height - 1u;
+    }
+    h.t = t; h.normal = v3(q0.x, q0.y, q0.z); h.point = p;
+    h.col_mod = texture_color_at(sc, nt, tx, tex_x, tex_y, p);
+    load_material(sc, ids.x, h);
+}
+
+RTW_HD void eval_prim(const Scene& sc, const Noise* nt, uint32_t ref, const Ray& r, float t, Hit& h) {
+    if (ref_kind(ref) == KIND_SPHERE) eval_sphere(sc, nt, ref_index(ref), r, t, h);
+    else eval_quad(sc, nt, ref_index(ref), r, t, h);
+}
+
+// The full Hit for the result of trace(): Scene::collision_normal's return value.
+RTW_HD void eval_hit(const TraceCtx& cx, const Noise* nt, const Best& b, const Ray& r, Hit& h) {
+    const Scene& sc = *cx.sc;
+    if (ref_kind(b.ref) != KIND_INSTANCE) { eval_prim(sc, nt, b.ref, r, b.t, h); return; }
+    // instance.rs:257-307
+    const Instance& in = sc.instances[ref_index(b.ref)];
+    Ray l = to_local(in, r);
+    eval_prim(sc, nt, b.inner, l, b.t, h);
+    if (in.flags & INST_VOLUME) {
+        float distance = volume_distance(in, cx);
+        if (distance >= 0.0f) {
+            // scatter inside the medium: entry-face t, col_mod and material are kept (instance.rs:295-299)
+            h.point = h.point + l.d * distance;
+            h.normal = random_unit_vec_stream(*cx.rng, cx.bounce << 16, 1u + in.index);
+        }
+    }
+    if (!(in.flags & INST_ROT_IDENTITY)) {
+        h.point = rot_apply(in.fwd_rows, h.point);
+        h.normal = rot_apply(in.fwd_rows, h.normal);
+    }
+    h.point = h.point + v3(in.t[0], in.t[1], in.t[2]);
+}
+
+// ------------------------------------------------------------------ materials.rs
+RTW_HD V3 refract(V3 uv, V3 n, float etai_over_etat) {           // materials.rs:89-97
+    float cos_theta = dot(-uv, n);
+    if (cos_theta > 1.0f) cos_theta = 1.0f;
+    V3 r_out_perp = (uv + n * cos_theta) * etai_over_etat;
+    V3 r_out_parallel = n * -sqrtf(fabsf(1.0f - length2(r_out_perp)));
+    return r_out_perp + r_out_parallel;
+}
+RTW_HD float reflectance(float cosine, float ref_idx) {          // materials.rs:98-103
+    float r0 = (1.0f - ref_idx) / (1.0f + ref_idx);
+    r0 = r0 * r0;
+    float x = 1.0f - cosine;
+    float x2 = x * x;
+    float x4 = x2 * x2;
+    return r0 + (1.0f - r0) * (x * x4);
+}
+
+// Material::on_hit (materials.rs:105-154): next direction and cos_theta.
+RTW_HD V3 on_hit(const Hit& h, const Ray& r, PathRng& rng, float& cos_theta) {
+    if (h.opacity > 0.0f) {
+        V3 n; bool front_face;
+        if (dot(r.d, h.normal) > 0.0f) { n = -h.normal; front_face = false; }
+        else { n = h.normal; front_face = true; }
+        float refraction_ratio = front_face ? 1.0f / h.ir : h.ir;
+        V3 unit_direction = unit(r.d);
+        float ct = dot(-unit_direction, n);
+        if (ct > 1.0f) ct = 1.0f;
+        float sin_theta = sqrtf(1.0f - ct * ct);
+        bool cannot_refract = refraction_ratio * sin_theta > 1.0f;
+        float refl = reflectance(ct, refraction_ratio);
+        float coin = rng.next4().x;
+        cos_theta = 0.0f;
+        return (cannot_refract || refl > coin) ? reflect(unit_direction, n)
+                                               : refract(unit_direction, n, refraction_ratio);
+    }
+    // diffuse (materials.rs:213-228)
+    V3 target = h.normal + random_unit_vec(rng);
+    V3 sc = close_to_zero(target) ? h.normal : target;
+    V3 refl = reflect(unit(r.d), h.normal);
+    cos_theta = h.metallicness != 1.0f ? dot(sc, h.normal) : 0.0f;
+    return refl * h.metallicness + sc * (1.0f - h.metallicness);
+}
+
+// ------------------------------------------------------------------ camera (viewport.rs)
+RTW_HD V3 ld3(const float* p) { return v3(p[0], p[1], p[2]); }
+
+RTW_HD V3 sky_gradient(V3 d) {   // ray_color.rs:38-40
+    V3 ud = unit(d);
+    float t = 0.5f * (ud.y + 1.0f);
+    return v3((1.0f - t) + t * 0.5f, (1.0f - t) + t * 0.7f, 1.0f);
+}
+
+// One path in flight.
+struct Path {
+    Ray ray;
+    V3 thr, rad;
+    PathRng rng;
+    uint32_t depth_left, bounce;
+    bool poison;     // pdf == 0 -> colour*0/0 = NaN all the way up
+};
+
+// Loop bodies of render_row (viewport.rs:287-300), Viewport::render (:455-470) and
+// render_no_rand (:502-508): the camera ray of sample `s` of pixel (i, j).
+RTW_HD void generate(const RenderParams& P, uint32_t i, uint32_t j, uint32_t s, Path& p) {
+    p.rng.k0 = P.k0; p.rng.k1 = P.k1;
+    p.rng.pixel = j * P.cam.width + i; p.rng.sample = s; p.rng.block = 0u;
+    V3 origin = ld3(P.cam.origin), p00 = ld3(P.cam.pixel00), du = ld3(P.cam.delta_u), dv = ld3(P.cam.delta_v);
+    if (P.mode == RTW_MODE_NO_RAND) {
+        p.ray.o = origin;
+        p.ray.d = p00 + du * (float)i + dv * (float)j;
+        p.ray.time = 0.0f;
+    } else {
+        float4 c = p.rng.next4();
+        V3 rp = v3(0.f, 0.f, 0.f);
+        if (P.cam.lens_radius != 0.0f) rp = random_in_unit_disk(p.rng);
+        p.ray.o = origin + (ld3(P.cam.u) * rp.x + ld3(P.cam.v) * rp.y) * P.cam.lens_radius;
+        if (P.mode == RTW_MODE_RANDOM) {
+            p.ray.d = p00 + du * ((float)i + c.x) + dv * ((float)j + c.y);
+            p.ray.time = P.time0 + P.shutter_speed * c.z;
+        } else {
+            uint32_t x = s / P.s_root, y = s % P.s_root;
+            float sr = (float)P.s_root;
+            p.ray.d = p00 + du * ((float)i + (((float)x + c.x) / sr)) + dv * ((float)j + (((float)y + c.y) / sr));
+            p.ray.time = 0.0f;
+        }
+    }
+    p.thr = v3(1.f, 1.f, 1.f); p.rad = v3(0.f, 0.f, 0.f);
+    p.depth_left = P.depth; p.bounce = 0u; p.poison = false;
+}
+
+// One segment of one path: extend + shade. Returns true when the path is finished (p.rad final).
+// `rays` counts Scene::collision_normal equivalents.
+RTW_HD bool path_step(const Scene& sc, const Noise* nt, const RenderParams& P, Path& p, uint32_t& rays) {
+    const uint32_t ig = P.integrator;
+    const bool first_hit = (ig == RTW_INT_NORMAL || ig == RTW_INT_ALBEDO);
+    if (!first_hit && p.depth_left < 1u) return true;               // ray_color.rs:14-16
+    TraceCtx cx; cx.sc = &sc; cx.rng = &p.rng; cx.bounce = p.bounce; cx.mint = P.mint; cx.maxt = P.maxt;
+    Best b = trace(cx, p.ray);
+    ++rays;
+    if (b.ref == REF_NONE) {                                        // miss
+        V3 bg;
+        if (ig == RTW_INT_BG_COLOR || ig == RTW_INT_ALBEDO) bg = ld3(sc.background);   // ray_color.rs:91
+        else if (ig == RTW_INT_GLASS_TEST) bg = v3(0.f, 0.f, 1.f);                     // glass_tests.rs:54
+        else bg = sky_gradient(p.ray.d);
+        p.rad = p.rad + p.thr * bg;
+        return true;
+    }
+    Hit h;
+    eval_hit(cx, nt, b, p.ray, h);
+    if (first_hit) {                                                // viewport.rs:524-554
+        if (ig == RTW_INT_NORMAL)
+            p.rad = v3(0.5f * (h.normal.x + 1.0f), 0.5f * (h.normal.y + 1.0f), 0.5f * (h.normal.z + 1.0f));
+        else p.rad = h.col_mod;
+        return true;
+    }
+    if (ig == RTW_INT_GLASS_TEST && h.metallicness != 1.0f) {       // glass_tests.rs:17-19
+        p.rad = p.rad + p.thr * v3(1.f, 1.f, 0.f);
+        return true;
+    }
+    bool front = !(dot(p.ray.d, h.normal) > 0.0f);
+    float cos_theta;
+    V3 nd = on_hit(h, p.ray, p.rng, cos_theta);
+    if (close_to_zero(nd)) nd = front ? h.normal : h.normal * -1.0f;   // ray_color.rs:62-64
+    if (ig == RTW_INT_BG_COLOR) {                                   // ray_color.rs:67-88
+        p.rad = p.rad + p.thr * h.emitted;
+        if (h.metallicness != 1.0f) {
+            float pdf = cos_theta > 0.0f ? cos_theta * 0.31830988618379067154f : 0.0f;   // materials.rs:5-13
+            if (!(pdf > 0.0f)) p.poison = true;
+        }
+    }
+    p.thr = p.thr * h.col_mod;
+    p.ray.o = h.point; p.ray.d = nd;
+    p.bounce += 1u; p.depth_left -= 1u;
+    return false;
+}
+
+RTW_HD V3 path_result(const Path& p) {
+    if (p.poison) { float n = u2f(0x7FC00000u); return v3(n, n, n); }
+    return p.rad;
+}
+
+}  // namespace rtw

@@ -1,0 +1,413 @@
+// scene_build.cpp — host side of rtw_scene_create: validate the rtw_scene_desc, derive the
+// per-primitive quantities the reference derives in its constructors, compute every primitive's
+// reference leaf box, build the two-level SAH BVH and lay everything out as the SoA arrays of
+// rtw_device.h. Host-only C++ (no CUDA calls); compiled with -ffp-contract=off so the derived
+// f32 values equal the reference's (rustc never fuses a*b+c).
+//
+//   Quad::new            Rust/src/objects/quad.rs:85-106     normal, d, w
+//   AABB leaf box        objects/aabb/aabb.rs:27-38          origin +- radius at time 0
+//   QuadAABB::from, pad  objects/aabb/qaabb.rs:19-61,107-126 corners, padded to 1e-5
+//   IAABB::from          objects/aabb/iaabb.rs:23-76         rotated corners of the inner boxes + T
+//   Vec3::rotated        vec3.rs:161-181                     the Euler map (not a rotation for x/z)
+//   Viewport::new        viewport.rs:308-401                 camera basis
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+#include <limits>
+#include "rtw_host.h"
+#include "rtw_shade.h"
+
+namespace rtw {
+
+namespace {
+
+inline float minf(float a, float b) { return a <= b ? a : b; }   // objects.rs:78-91
+inline float maxf(float a, float b) { return a >= b ? a : b; }
+
+struct Box { float lo[3], hi[3]; };
+inline Box box_empty() {
+    Box b;
+    for (int a = 0; a < 3; ++a) { b.lo[a] = std::numeric_limits<float>::infinity(); b.hi[a] = -b.lo[a]; }
+    return b;
+}
+inline void box_grow(Box& b, const Box& o) {
+    for (int a = 0; a < 3; ++a) { b.lo[a] = minf(b.lo[a], o.lo[a]); b.hi[a] = maxf(b.hi[a], o.hi[a]); }
+}
+inline float box_area(const Box& b) {
+    double dx = (double)b.hi[0] - b.lo[0], dy = (double)b.hi[1] - b.lo[1], dz = (double)b.hi[2] - b.lo[2];
+    if (!(dx >= 0) || !(dy >= 0) || !(dz >= 0)) return 0.f;
+    return (float)(2.0 * (dx * dy + dy * dz + dz * dx));
+}
+
+struct BuildPrim { uint32_t ref; Box box; float c[3]; };
+
+// vec3.rs:161-181 as coefficient rows (see rot_apply in rtw_device.h)
+void euler_rows(const float rot[3], float r[12]) {
+    float sa = std::sin(rot[0]), ca = std::cos(rot[0]);
+    float sb = std::sin(rot[1]), cb = std::cos(rot[1]);
+    float sc = std::sin(rot[2]), cc = std::cos(rot[2]);
+    r[0] = cb; r[1] = cc; r[2] = sa * sb * cc - sa * cc; r[3] = ca * sb * cc + sa * sc;
+    r[4] = cb; r[5] = sc; r[6] = sa * sb * sc + ca * cc; r[7] = ca * sb * sc - sa * cc;
+    r[8] = -sb; r[9] = sa; r[10] = cb; r[11] = ca;
+}
+
+bool finite3(const float* p) { return std::isfinite(p[0]) && std::isfinite(p[1]) && std::isfinite(p[2]); }
+
+struct Builder {
+    std::vector<Node>& nodes;
+    uint32_t max_depth = 0;
+    explicit Builder(std::vector<Node>& n) : nodes(n) {}
+
+    static void write_child(Node& n, int which, const Box& b, uint32_t ref) {
+        if (which == 0) {
+            n.n0 = make_float4(b.lo[0], b.lo[1], b.lo[2], b.hi[0]);
+            n.n1.x = b.hi[1]; n.n1.y = b.hi[2];
+            n.n3.x = ref;
+        } else {
+            n.n1.z = b.lo[0]; n.n1.w = b.lo[1];
+            n.n2 = make_float4(b.lo[2], b.hi[0], b.hi[1], b.hi[2]);
+            n.n3.y = ref;
+        }
+    }
+
+    // Top-down SAH over [begin, end): full sweep on each axis, one primitive per leaf (a leaf is
+    // just the primitive's reference inside its parent). Falls back to a median split when the
+    // remaining depth budget (the traversal stack, RTW_STACK) gets tight.
+    uint32_t build(std::vector<BuildPrim>& p, size_t begin, size_t end, uint32_t depth, Box& out_box) {
+        size_t n = end - begin;
+        max_depth = std::max(max_depth, depth);
+        if (n == 1) { out_box = p[begin].box; return p[begin].ref; }
+        Box cb = box_empty();
+        for (size_t i = begin; i < end; ++i)
+            for (int a = 0; a < 3; ++a) { cb.lo[a] = minf(cb.lo[a], p[i].c[a]); cb.hi[a] = maxf(cb.hi[a], p[i].c[a]); }
+        uint32_t levels_needed = 1; while (((size_t)1 << levels_needed) < n) ++levels_needed;
+        bool force_median = depth + levels_needed + 2 >= (uint32_t)RTW_STACK;
+        int best_axis = -1; size_t best_k = 0; float best_cost = std::numeric_limits<float>::infinity();
+        if (!force_median) {
+            std::vector<float> right_area(n);
+            for (int axis = 0; axis < 3; ++axis) {
+                if (!(cb.hi[axis] > cb.lo[axis])) continue;
+                std::stable_sort(p.begin() + begin, p.begin() + end,
+                                 [axis](const BuildPrim& a, const BuildPrim& b) { return a.c[axis] < b.c[axis]; });
+                Box rb = box_empty();
+                for (size_t i = n; i-- > 1;) { box_grow(rb, p[begin + i].box); right_area[i] = box_area(rb); }
+                Box lb = box_empty();
+                for (size_t k = 1; k < n; ++k) {
+                    box_grow(lb, p[begin + k - 1].box);
+                    float cost = box_area(lb) * (float)k + right_area[k] * (float)(n - k);
+                    if (cost < best_cost) { best_cost = cost; best_axis = axis; best_k = k; }
+                }
+            }
+        }
+        if (best_axis < 0) {   // median split along the widest centroid axis (or index order if all equal)
+            int axis = 0; float w = -1.f;
+            for (int a = 0; a < 3; ++a) { float e = cb.hi[a] - cb.lo[a]; if (e > w) { w = e; axis = a; } }
+            best_axis = axis; best_k = n / 2;
+        }
+        std::stable_sort(p.begin() + begin, p.begin() + end,
+                         [best_axis](const BuildPrim& a, const BuildPrim& b) { return a.c[best_axis] < b.c[best_axis]; });
+        uint32_t me = (uint32_t)nodes.size();
+        nodes.emplace_back();
+        std::memset(&nodes[me], 0, sizeof(Node));
+        Box b0, b1;
+        uint32_t c0 = build(p, begin, begin + best_k, depth + 1, b0);
+        uint32_t c1 = build(p, begin + best_k, end, depth + 1, b1);
+        write_child(nodes[me], 0, b0, c0);
+        write_child(nodes[me], 1, b1, c1);
+        out_box = b0; box_grow(out_box, b1);
+        return make_ref(KIND_NODE, me);
+    }
+
+    Level level(std::vector<BuildPrim>& prims, uint32_t mov_first, uint32_t mov_count) {
+        Level lv; std::memset(&lv, 0, sizeof lv);
+        lv.mov_first = mov_first; lv.mov_count = mov_count;
+        if (prims.empty()) { lv.root = REF_NONE; return lv; }
+        Box rb;
+        lv.root = build(prims, 0, prims.size(), 0, rb);
+        for (int a = 0; a < 3; ++a) { lv.lo[a] = rb.lo[a]; lv.hi[a] = rb.hi[a]; }
+        return lv;
+    }
+};
+
+BuildPrim make_prim(uint32_t ref, const Box& b) {
+    BuildPrim p; p.ref = ref; p.box = b;
+    for (int a = 0; a < 3; ++a) p.c[a] = 0.5f * b.lo[a] + 0.5f * b.hi[a];
+    return p;
+}
+
+}  // namespace
+
+Scene HostScene::host_view() {
+    Scene s; std::memset(&s, 0, sizeof s);
+    s.nodes = nodes.data();
+    s.spheres = spheres.data(); s.sphere_vel = sphere_vel.data(); s.sphere_col = sphere_col.data();
+    s.sphere_ids = sphere_ids.data(); s.sphere_box = sphere_box.data();
+    s.quads = quads.data(); s.quad_ids = quad_ids.data();
+    s.instances = instances.data(); s.moving = moving.data();
+    s.materials = materials.data();
+    for (size_t i = 0; i < textures.size(); ++i) { textures[i].texels = texels[i].data(); textures[i].obj = 0; }
+    s.textures = textures.data(); s.noises = noises.data();
+    s.top = top;
+    std::memcpy(s.background, background, sizeof background);
+    s.n_noises = (uint32_t)noises.size();
+    return s;
+}
+
+int build_host_scene(const rtw_scene_desc* d, HostScene& hs, std::string& err) {
+    if (!d) { err = "null scene description"; return RTW_E_INVALID; }
+    if (d->abi_version != RTW_ABI_VERSION) { err = "abi_version mismatch"; return RTW_E_INVALID; }
+    if (d->n_top_spheres > d->n_spheres || d->n_top_quads > d->n_quads) { err = "n_top_* exceeds n_*"; return RTW_E_INVALID; }
+    if ((d->n_spheres && !d->spheres) || (d->n_quads && !d->quads) || (d->n_instances && !d->instances) ||
+        (d->n_materials && !d->materials) || (d->n_textures && !d->textures) || (d->n_noises && !d->noises)) {
+        err = "null array with non-zero count"; return RTW_E_INVALID;
+    }
+    if (d->n_spheres >= (1u << 30) || d->n_quads >= (1u << 30) || d->n_instances >= (1u << 30)) {
+        err = "too many primitives"; return RTW_E_UNSUPPORTED;
+    }
+    if ((d->n_spheres || d->n_quads) && (d->n_materials == 0 || d->n_textures == 0)) {
+        err = "primitives need at least one material and one texture"; return RTW_E_INVALID;
+    }
+
+    // ---- materials, noises, textures
+    hs.materials.resize(d->n_materials);
+    for (uint32_t i = 0; i < d->n_materials; ++i) {
+        const rtw_material& m = d->materials[i];
+        Material& o = hs.materials[i]; std::memset(&o, 0, sizeof o);
+        o.metallicness = m.metallicness; o.opacity = m.opacity; o.ir = m.ir;
+        o.emitted[0] = m.emitted[0]; o.emitted[1] = m.emitted[1]; o.emitted[2] = m.emitted[2];
+    }
+    hs.noises.resize(d->n_noises);
+    for (uint32_t i = 0; i < d->n_noises; ++i) {
+        for (int k = 0; k < 256; ++k) {
+            hs.noises[i].ranvec[k] = make_float4(d->noises[i].ranvec[k][0], d->noises[i].ranvec[k][1], d->noises[i].ranvec[k][2], 0.f);
+            hs.noises[i].perm[0][k] = (uint8_t)(d->noises[i].perm_x[k] & 255u);
+            hs.noises[i].perm[1][k] = (uint8_t)(d->noises[i].perm_y[k] & 255u);
+            hs.noises[i].perm[2][k] = (uint8_t)(d->noises[i].perm_z[k] & 255u);
+        }
+    }
+    hs.textures.resize(d->n_textures);
+    hs.texels.resize(d->n_textures);
+    for (uint32_t i = 0; i < d->n_textures; ++i) {
+        const rtw_texture& t = d->textures[i];
+        if (t.width == 0 || t.height == 0 || !t.rgb) { err = "texture with zero size or null texels"; return RTW_E_INVALID; }
+        if ((uint64_t)t.width * t.height >= (1ull << 31)) { err = "texture too large"; return RTW_E_UNSUPPORTED; }
+        if (t.noise_id >= 0 && (uint32_t)t.noise_id >= d->n_noises) { err = "texture noise_id out of range"; return RTW_E_INVALID; }
+        Texture& o = hs.textures[i]; std::memset(&o, 0, sizeof o);
+        o.width = t.width; o.height = t.height; o.noise_id = t.noise_id < 0 ? -1 : t.noise_id; o.noise_scale = t.noise_scale;
+        o.n_texels = t.width * t.height;
+        o.solid[0] = t.rgb[0]; o.solid[1] = t.rgb[1]; o.solid[2] = t.rgb[2];
+        std::vector<float4>& tv = hs.texels[i];
+        tv.resize(o.n_texels);
+        for (uint32_t k = 0; k < o.n_texels; ++k) tv[k] = make_float4(t.rgb[3 * k], t.rgb[3 * k + 1], t.rgb[3 * k + 2], 0.f);
+    }
+
+    // ---- spheres
+    const uint32_t ns = d->n_spheres, nq = d->n_quads;
+    hs.spheres.resize(ns); hs.sphere_vel.resize(ns); hs.sphere_col.resize(ns); hs.sphere_ids.resize(ns);
+    hs.sphere_box.resize(2 * (size_t)ns);
+    std::vector<Box> sbox(ns), qbox(nq);
+    std::vector<uint8_t> smoving(ns);
+    for (uint32_t i = 0; i < ns; ++i) {
+        const rtw_sphere& s = d->spheres[i];
+        if (s.mat_id >= d->n_materials || s.tex_id >= d->n_textures) { err = "sphere material/texture id out of range"; return RTW_E_INVALID; }
+        if (!finite3(s.origin) || !std::isfinite(s.radius) || !finite3(s.velocity)) { err = "non-finite sphere"; return RTW_E_INVALID; }
+        bool mv = s.velocity[0] != 0.f || s.velocity[1] != 0.f || s.velocity[2] != 0.f;
+        smoving[i] = mv;
+        hs.spheres[i] = make_float4(s.origin[0], s.origin[1], s.origin[2], s.radius);
+        hs.sphere_vel[i] = make_float4(s.velocity[0], s.velocity[1], s.velocity[2], 0.f);
+        hs.sphere_col[i] = make_float4(s.col_mod[0], s.col_mod[1], s.col_mod[2], u2f(mv ? 1u : 0u));
+        hs.sphere_ids[i] = make_uint2(s.mat_id, s.tex_id);
+        for (int a = 0; a < 3; ++a) {   // aabb.rs:27-38: Interval::new(o - r, o + r)
+            float x1 = s.origin[a] - s.radius, x2 = s.origin[a] + s.radius;
+            sbox[i].lo[a] = minf(x1, x2); sbox[i].hi[a] = maxf(x1, x2);
+        }
+        hs.sphere_box[2 * i] = make_float4(sbox[i].lo[0], sbox[i].lo[1], sbox[i].lo[2], 0.f);
+        hs.sphere_box[2 * i + 1] = make_float4(sbox[i].hi[0], sbox[i].hi[1], sbox[i].hi[2], 0.f);
+    }
+    // ---- quads
+    hs.quads.resize(nq); hs.quad_ids.resize(nq);
+    for (uint32_t i = 0; i < nq; ++i) {
+        const rtw_quad& q = d->quads[i];
+        if (q.mat_id >= d->n_materials || q.tex_id >= d->n_textures) { err = "quad material/texture id out of range"; return RTW_E_INVALID; }
+        if (!finite3(q.origin) || !finite3(q.u) || !finite3(q.v)) { err = "non-finite quad"; return RTW_E_INVALID; }
+        V3 Q = v3(q.origin[0], q.origin[1], q.origin[2]), u = v3(q.u[0], q.u[1], q.u[2]), v = v3(q.v[0], q.v[1], q.v[2]);
+        V3 n = cross(u, v);                      // quad.rs:93
+        V3 normal = unit(n);                     // :99
+        float dd = dot(normal, Q);               // :100
+        V3 w = n / dot(n, n);                    // :101
+        Quad& o = hs.quads[i];
+        o.q0 = make_float4(normal.x, normal.y, normal.z, dd);
+        o.q1 = make_float4(Q.x, Q.y, Q.z, u.x);
+        o.q2 = make_float4(u.y, u.z, v.x, v.y);
+        o.q3 = make_float4(v.z, w.x, w.y, w.z);
+        hs.quad_ids[i] = make_uint2(q.mat_id, q.tex_id);
+        // qaabb.rs:19-61: box of the four corners, then pad() :107-126
+        V3 op = Q + u + v, vc = Q + v, uc = Q + u;
+        const float P4[4][3] = {{op.x, op.y, op.z}, {vc.x, vc.y, vc.z}, {uc.x, uc.y, uc.z}, {Q.x, Q.y, Q.z}};
+        for (int a = 0; a < 3; ++a) {
+            float mn = minf(minf(P4[0][a], P4[1][a]), minf(P4[2][a], P4[3][a]));
+            float mx = maxf(maxf(P4[0][a], P4[1][a]), maxf(P4[2][a], P4[3][a]));
+            const float MIN_SIZE_DIR = 0.00001f;
+            if (mx - mn < MIN_SIZE_DIR) {
+                float center = (mx - mn) / 2.0f + mn;
+                mn = center - 0.5f * MIN_SIZE_DIR; mx = center + 0.5f * MIN_SIZE_DIR;
+            }
+            qbox[i].lo[a] = mn; qbox[i].hi[a] = mx;
+        }
+    }
+
+    // ---- instances
+    Builder bld(hs.nodes);
+    hs.instances.resize(d->n_instances);
+    std::vector<BuildPrim> top;
+    std::vector<uint32_t> top_moving;
+    auto add_sphere = [&](uint32_t i, std::vector<BuildPrim>& prims, std::vector<uint32_t>& mov) {
+        if (smoving[i]) mov.push_back(i); else prims.push_back(make_prim(make_ref(KIND_SPHERE, i), sbox[i]));
+    };
+    for (uint32_t i = 0; i < d->n_top_spheres; ++i) add_sphere(i, top, top_moving);
+    for (uint32_t i = 0; i < d->n_top_quads; ++i) top.push_back(make_prim(make_ref(KIND_QUAD, i), qbox[i]));
+    uint32_t n_flat = 0, blas_nodes_before = 0;
+    std::vector<std::pair<uint32_t, Box>> inst_leaves;
+    std::vector<std::vector<uint32_t>> inst_moving(d->n_instances);
+    std::vector<std::vector<BuildPrim>> inst_prims(d->n_instances);
+    for (uint32_t k = 0; k < d->n_instances; ++k) {
+        const rtw_instance& in = d->instances[k];
+        if ((uint64_t)in.first_sphere + in.n_spheres > ns || (uint64_t)in.first_quad + in.n_quads > nq) {
+            err = "instance primitive range out of bounds"; return RTW_E_INVALID;
+        }
+        if (in.n_spheres && in.first_sphere < d->n_top_spheres) { err = "instance sphere range overlaps top-level spheres"; return RTW_E_INVALID; }
+        if (in.n_quads && in.first_quad < d->n_top_quads) { err = "instance quad range overlaps top-level quads"; return RTW_E_INVALID; }
+        if (!finite3(in.translation) || !finite3(in.rotation) || std::isnan(in.density)) { err = "non-finite instance"; return RTW_E_INVALID; }
+        if (in.density_kind != RTW_DENSITY_SURFACE && in.density_kind != RTW_DENSITY_CONST) { err = "unknown density_kind"; return RTW_E_INVALID; }
+        Instance& o = hs.instances[k]; std::memset(&o, 0, sizeof o);
+        o.index = k; o.density = in.density;
+        for (int a = 0; a < 3; ++a) o.t[a] = in.translation[a];
+        bool rot0 = in.rotation[0] == 0.f && in.rotation[1] == 0.f && in.rotation[2] == 0.f;
+        bool t0 = in.translation[0] == 0.f && in.translation[1] == 0.f && in.translation[2] == 0.f;
+        float neg[3] = {-in.rotation[0], -in.rotation[1], -in.rotation[2]};
+        euler_rows(neg, o.inv_rows);              // instance.rs:258  .rotated(-self.rotation)
+        euler_rows(in.rotation, o.fwd_rows);      // instance.rs:303-306
+        if (rot0) o.flags |= INST_ROT_IDENTITY;
+        if (in.density_kind == RTW_DENSITY_CONST) o.flags |= INST_VOLUME;
+        o.level.root = REF_NONE;
+        if (rot0 && t0 && in.density_kind == RTW_DENSITY_SURFACE) {
+            // An untransformed surface instance is exactly its primitives: rotated(0) and "- 0" are
+            // identities in f32, so they join the top level (C5's 400 ground boxes).
+            for (uint32_t i = 0; i < in.n_spheres; ++i) add_sphere(in.first_sphere + i, top, top_moving);
+            for (uint32_t i = 0; i < in.n_quads; ++i) top.push_back(make_prim(make_ref(KIND_QUAD, in.first_quad + i), qbox[in.first_quad + i]));
+            ++n_flat;
+            continue;
+        }
+        for (uint32_t i = 0; i < in.n_spheres; ++i) add_sphere(in.first_sphere + i, inst_prims[k], inst_moving[k]);
+        for (uint32_t i = 0; i < in.n_quads; ++i) inst_prims[k].push_back(make_prim(make_ref(KIND_QUAD, in.first_quad + i), qbox[in.first_quad + i]));
+        // iaabb.rs:23-76: (qaabb box U saabb box); an empty inner BVH contributes [0,0] (aabb.rs:75-83)
+        Box sb, qb;
+        if (in.n_spheres) { sb = box_empty(); for (uint32_t i = 0; i < in.n_spheres; ++i) box_grow(sb, sbox[in.first_sphere + i]); }
+        else { for (int a = 0; a < 3; ++a) sb.lo[a] = sb.hi[a] = 0.f; }
+        if (in.n_quads) { qb = box_empty(); for (uint32_t i = 0; i < in.n_quads; ++i) box_grow(qb, qbox[in.first_quad + i]); }
+        else { for (int a = 0; a < 3; ++a) qb.lo[a] = qb.hi[a] = 0.f; }
+        Box ub = qb; box_grow(ub, sb);
+        Box lb = box_empty();
+        for (int c = 0; c < 8; ++c) {
+            V3 p = v3((c & 4) ? ub.hi[0] : ub.lo[0], (c & 2) ? ub.hi[1] : ub.lo[1], (c & 1) ? ub.hi[2] : ub.lo[2]);
+            V3 r = rot_apply(o.fwd_rows, p);
+            lb.lo[0] = minf(lb.lo[0], r.x); lb.lo[1] = minf(lb.lo[1], r.y); lb.lo[2] = minf(lb.lo[2], r.z);
+            lb.hi[0] = maxf(lb.hi[0], r.x); lb.hi[1] = maxf(lb.hi[1], r.y); lb.hi[2] = maxf(lb.hi[2], r.z);
+        }
+        for (int a = 0; a < 3; ++a) { lb.lo[a] = lb.lo[a] + in.translation[a]; lb.hi[a] = lb.hi[a] + in.translation[a]; }
+        if (!finite3(lb.lo) || !finite3(lb.hi)) { err = "instance bounds are not finite"; return RTW_E_INVALID; }
+        inst_leaves.push_back({k, lb});
+    }
+    // ---- levels: top first (its nodes lead the array and stay hot), then each instance
+    for (auto& il : inst_leaves) top.push_back(make_prim(make_ref(KIND_INSTANCE, il.first), il.second));
+    hs.info = rtw_scene_info{};
+    hs.info.n_tlas_leaves = (uint32_t)top.size();
+    hs.moving = top_moving;
+    hs.top = bld.level(top, 0u, (uint32_t)top_moving.size());
+    hs.info.n_tlas_nodes = (uint32_t)hs.nodes.size();
+    uint32_t top_depth = bld.max_depth, inner_depth = 0;
+    blas_nodes_before = (uint32_t)hs.nodes.size();
+    for (auto& il : inst_leaves) {
+        uint32_t k = il.first;
+        uint32_t mf = (uint32_t)hs.moving.size();
+        hs.moving.insert(hs.moving.end(), inst_moving[k].begin(), inst_moving[k].end());
+        bld.max_depth = 0;
+        hs.instances[k].level = bld.level(inst_prims[k], mf, (uint32_t)inst_moving[k].size());
+        inner_depth = std::max(inner_depth, bld.max_depth);
+    }
+    hs.info.n_blas_nodes = (uint32_t)hs.nodes.size() - blas_nodes_before;
+    hs.info.n_flattened_instances = n_flat;
+    hs.info.bvh_max_depth = top_depth + inner_depth;
+    if (top_depth >= (uint32_t)RTW_STACK || inner_depth >= (uint32_t)RTW_STACK) { err = "BVH deeper than the traversal stack"; return RTW_E_UNSUPPORTED; }
+    if (hs.nodes.empty()) { hs.nodes.emplace_back(); std::memset(&hs.nodes[0], 0, sizeof(Node)); }
+    if (hs.moving.empty()) hs.moving.push_back(0u);
+    for (int a = 0; a < 3; ++a) hs.background[a] = d->background[a];
+    return RTW_OK;
+}
+
+// Viewport::new (viewport.rs:308-401). `upper_left_corner` is a direction: the origin is not added.
+void camera_init(rtw_camera* cam, uint32_t width, float aspect_ratio, float vfov, const float origin[3],
+                 const float direction[3], const float vup[3], float lens_radius) {
+    V3 c_dir = v3(direction[0], direction[1], direction[2]), c_vup = v3(vup[0], vup[1], vup[2]);
+    V3 w = -c_dir;
+    V3 u = unit(cross(c_vup, w));
+    V3 v = cross(w, u);
+    uint64_t height = (uint64_t)((float)width / aspect_ratio);
+    float h = std::tan(vfov * 3.14159265358979323846f / 360.0f);
+    float viewport_height = 2.0f * h;
+    float viewport_width = aspect_ratio * viewport_height;
+    V3 viewport_u = u * viewport_width;
+    V3 viewport_v = -v * viewport_height;
+    V3 pixel_delta_u = viewport_u / (float)width;
+    V3 pixel_delta_v = viewport_v / (float)height;
+    V3 viewport_upper_left = -w - viewport_u / 2.0f - viewport_v / 2.0f;
+    V3 pixel00_loc = viewport_upper_left + (pixel_delta_u + pixel_delta_v) * 0.5f;
+    std::memset(cam, 0, sizeof *cam);
+    cam->width = width; cam->height = (uint32_t)height;
+    auto put = [](float* d, V3 s) { d[0] = s.x; d[1] = s.y; d[2] = s.z; };
+    put(cam->origin, v3(origin[0], origin[1], origin[2])); put(cam->pixel00, pixel00_loc);
+    put(cam->delta_u, pixel_delta_u); put(cam->delta_v, pixel_delta_v);
+    put(cam->u, u); put(cam->v, v);
+    cam->lens_radius = lens_radius;
+}
+
+int make_render_params(const rtw_camera* cam, const rtw_render_opts* o, RenderParams& P, uint32_t& total,
+                       std::string& err) {
+    if (!cam || !o) { err = "null camera / options"; return RTW_E_INVALID; }
+    if (cam->width == 0 || cam->height == 0) { err = "empty image"; return RTW_E_INVALID; }
+    if ((uint64_t)cam->width * cam->height >= (1ull << 32)) { err = "image too large"; return RTW_E_UNSUPPORTED; }
+    std::memset(&P, 0, sizeof P);
+    P.cam = *cam;
+    P.integrator = o->integrator; P.mode = o->mode; P.depth = o->depth;
+    switch (o->integrator) {   // the constants each reference closure hard-codes
+        case RTW_INT_GRADIENT:   P.mint = 0.001f; P.maxt = 100000.0f; break;   // ray_color.rs:17-18
+        case RTW_INT_D:          P.mint = 0.001f; P.maxt = 1000.0f; break;     // main.rs:22-23
+        case RTW_INT_BG_COLOR:   P.mint = 0.001f; P.maxt = 10000.0f; break;    // ray_color.rs:48-49
+        case RTW_INT_NORMAL:     P.mint = 0.0f;   P.maxt = 1000.0f; break;     // viewport.rs:525-526
+        case RTW_INT_ALBEDO:     P.mint = 0.001f; P.maxt = 100000.0f; break;
+        case RTW_INT_GLASS_TEST: P.mint = 0.001f; P.maxt = 1000.0f; break;     // glass_tests.rs:13-14
+        default: err = "unknown integrator"; return RTW_E_INVALID;
+    }
+    if (o->maxt > 0.0f) { P.mint = o->mint; P.maxt = o->maxt; }
+    P.s_root = 1; total = o->samples;
+    if (o->mode == RTW_MODE_NO_RAND) total = 1;
+    else if (o->mode == RTW_MODE_STRATIFIED) {    // viewport.rs:443
+        P.s_root = (uint32_t)std::ceil(std::sqrt((float)o->samples));
+        total = P.s_root * P.s_root;
+    } else if (o->mode != RTW_MODE_RANDOM) { err = "unknown mode"; return RTW_E_INVALID; }
+    if (total == 0) { err = "samples must be > 0"; return RTW_E_INVALID; }
+    if (!(o->gamma > 0.0f) && o->output == RTW_OUT_RESOLVED) { err = "gamma must be > 0"; return RTW_E_INVALID; }
+    P.time0 = (float)o->frame / o->fps;           // viewport.rs:279
+    P.shutter_speed = o->shutter_speed;
+    P.k0 = (uint32_t)o->seed; P.k1 = (uint32_t)(o->seed >> 32);
+    P.sample_begin = o->sample_count ? o->sample_begin : 0u;
+    P.sample_count = o->sample_count ? o->sample_count : total;
+    P.row_begin = o->row_count ? o->row_begin : 0u;
+    P.row_count = o->row_count ? o->row_count : cam->height;
+    if ((uint64_t)P.sample_begin + P.sample_count > total) { err = "sample range exceeds the sample count"; return RTW_E_INVALID; }
+    if ((uint64_t)P.row_begin + P.row_count > cam->height) { err = "row range exceeds the image"; return RTW_E_INVALID; }
+    if (o->output != RTW_OUT_RESOLVED && o->output != RTW_OUT_SUM) { err = "unknown output kind"; return RTW_E_INVALID; }
+    return RTW_OK;
+}
+
+}  // namespace rtw

@@ -86,6 +86,7 @@ class Viewport:
         self.number_of_frames = 1
         self.start_frame = 0
         self.seed = 1                # the reference is unseeded; SURVEY §8d "Render RNG"
+        self.flags = 0               # RTW_FLAG_* (STRICT_FP for parity runs, WAVEFRONT)
 
     @staticmethod
     def new(width, aspect_ratio, samples, depth, gamma, vfov=None, origin=None, direction=None,
@@ -114,7 +115,7 @@ class Viewport:
         o.seed = self.seed
         o.mint, o.maxt = 0.0, 0.0
         o.sample_begin = o.sample_count = o.row_begin = o.row_count = 0
-        o.output, o.flags = A.RTW_OUT_RESOLVED, 0
+        o.output, o.flags = A.RTW_OUT_RESOLVED, int(self.flags)
         return o
 
     # ---- the reference's render entry points

@@ -56,6 +56,9 @@ def load_oracle(fast: bool = False):
     lib.oracle_render.restype = C.c_int
     lib.oracle_render.argtypes = [C.c_void_p, P(A.rtw_camera), P(A.rtw_render_opts), C.c_void_p, C.c_uint32,
                                   P(oracle_stats)]
+    lib.oracle_render_ex.restype = C.c_int
+    lib.oracle_render_ex.argtypes = [C.c_void_p, P(A.rtw_camera), P(A.rtw_render_opts), C.c_void_p, C.c_uint32,
+                                     P(oracle_stats), C.c_void_p]
     lib.oracle_camera_init.restype = C.c_int
     lib.oracle_camera_init.argtypes = [P(A.rtw_camera), C.c_uint32, C.c_float, C.c_float, f32p, f32p, f32p,
                                        C.c_float]
@@ -105,8 +108,10 @@ class OracleSceneHandle:
     def render(self, cam, o) -> np.ndarray:
         rows = o.row_count if o.row_count else cam.height
         out = np.empty((rows, cam.width, 3), dtype=np.float32)
-        rc = self._lib.oracle_render(self._h, C.byref(cam), C.byref(o), out.ctypes.data_as(C.c_void_p),
-                                     self.threads, C.byref(self.last))
+        # per pixel: was some closest-hit decision taken between equal t (unpinned by the reference)?
+        self.last_tie = np.zeros((rows, cam.width), dtype=np.uint8)
+        rc = self._lib.oracle_render_ex(self._h, C.byref(cam), C.byref(o), out.ctypes.data_as(C.c_void_p),
+                                        self.threads, C.byref(self.last), self.last_tie.ctypes.data_as(C.c_void_p))
         if rc != 0:
             raise ValueError(f"oracle_render failed: {rc}")
         return out
