@@ -1,0 +1,376 @@
+#!/usr/bin/env python
+"""bench.py — the headline measurement: Mpaths/s (+ Mrays/s) on the Next-Week final scene (C5),
+800x800, 10000 spp, depth 50, on N B200s of one node, next to the host-CPU renderer.
+
+    python bench.py --gpus N --steps K --warmup W            (N>1: launched by torchrun, one rank per GPU)
+    python bench.py --impl reference --gpus N --steps K --warmup W   (CPU arm: the oracle port, all host threads)
+
+A "step" is one whole frame of the workload: every rank renders its sample range of every pixel
+into a per-GPU f32 sum buffer (the megakernel), one NCCL reduce(sum) to rank 0, resolve (/spp,
+powf(1/gamma)) there. Total work per step is fixed as N grows => "scaling": "strong".
+  value  = paths of K frames / device time (CUDA events on the launching stream, max over ranks),
+           scene resident in HBM, image left on the device.
+  e2e    = the same frame through the C ABI with HOST buffers: rtw_scene_create (flatten, SAH BVH,
+           H2D of the scene arrays and textures) + render + D2H of the image + destroy, every step.
+One JSON line on stdout (rank 0).
+"""
+from __future__ import annotations
+
+import argparse
+import ctypes as C
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+for _p in (ROOT, os.path.join(ROOT, "tests")):
+    if _p not in sys.path:
+        sys.path.insert(0, _p)
+
+import numpy as np  # noqa: E402
+
+METRIC = "Mpaths/s, Next-Week final scene 800x800 (C5), 10000 spp, depth 50"
+UNIT = "Mpaths/s"
+
+# Algorithmic work per operation (DESIGN.md "Roofline"): flop and bytes of scene data.
+COST = {"node": (56.0, 64.0),        # two child-box slab tests, one 64-B node
+        "sphere": (36.0, 16.0),      # sphere.rs:100-123, (origin, radius)
+        "quad": (49.0, 64.0),        # quad.rs:38-60, 64-B record
+        "instance": (60.0, 160.0),   # ray -> local and hit -> world (two 3x3 Euler maps + T)
+        "hit": (190.0, 64.0)}        # Hit evaluation + uber-material scatter (+70 on accept, +120 shade)
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--config", default="C5", help="C1..C5 (C5 is the headline; others for exploration)")
+    ap.add_argument("--spp", type=int, default=0, help="override samples per pixel (0 = the config's own)")
+    ap.add_argument("--e2e-steps", type=int, default=0, help="timed e2e steps (0 = same as --steps)")
+    ap.add_argument("--cpu-seconds", type=float, default=15.0, help="target CPU time of the cpu_baseline sample")
+    ap.add_argument("--flags", type=int, default=0)
+    return ap.parse_args()
+
+
+# ----------------------------------------------------------------------------- clocks
+class ClockSampler:
+    """nvidia-smi clocks + throttle reasons sampled during the timed region (B200_PROFILING.md)."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index, self.proc, self.lines = index, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "200"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for ln in self.proc.stdout:
+            self.lines.append(ln.strip())
+
+    def stop(self) -> dict:
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0])); mx.append(float(f[1]))
+            except ValueError:
+                continue
+            for n, v in zip(names, f[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+# ----------------------------------------------------------------------------- workload
+def make_job(args):
+    from rtw_b200 import scenes
+    kw = {}
+    if args.spp:
+        kw["samples"] = args.spp
+    job = scenes.CONFIGS[args.config](**kw)
+    job.viewport.flags = args.flags
+    return job
+
+
+def workload_name(job) -> str:
+    vp = job.viewport
+    return f"{job.name}: {job.note or job.name} ({vp.width}x{vp.height}, {vp.samples} spp, depth {vp.depth})"
+
+
+# ----------------------------------------------------------------------------- CPU arm
+def cpu_sample(job, target_s: float, fast: bool = True):
+    """Time the CPU oracle (the port of the reference's renderer; row-parallel over every host thread
+    like async_render's one-task-per-row, viewport.rs:236-240) on a bounded sample of the workload:
+    the full frame at n spp, n chosen so the sample costs about `target_s` seconds."""
+    from oracle_backend import OracleBackend
+    from rtw_b200 import _abi as A
+    orc = OracleBackend(threads=0, fast=fast)
+    vp = job.viewport
+    h = orc.scene(job.scene)
+    cam = vp.camera(orc)
+    o = vp.opts(job.ray_color, job.mode)
+    o.output = A.RTW_OUT_SUM
+    o.sample_begin, o.sample_count = 0, 1
+    h.render(cam, o)
+    t1 = h.stats().seconds
+    paths, rays, secs, spp = h.stats().paths, h.stats().rays, t1, 1
+    extra = int(min(vp.samples - 1, max(0, round(target_s / max(t1, 1e-6)) - 1)))
+    if extra > 0:
+        o.sample_begin, o.sample_count = 1, extra
+        h.render(cam, o)
+        st = h.stats()
+        paths += st.paths; rays += st.rays; secs += st.seconds; spp += extra
+    threads = h.stats().threads
+    return {"paths": paths, "rays": rays, "seconds": secs, "spp": spp, "threads": int(threads),
+            "sample": f"{vp.width}x{vp.height} full frame x {spp} of {vp.samples} spp, depth {vp.depth}"}
+
+
+def cpu_baseline_obj(s) -> dict:
+    return {"value": s["paths"] / s["seconds"] / 1e6, "unit": UNIT, "cores": s["threads"], "kind": "port",
+            "sample": s["sample"], "mrays_per_s": s["rays"] / s["seconds"] / 1e6, "seconds": s["seconds"]}
+
+
+def run_reference(args):
+    """--impl reference: the reference's CPU renderer for this path. The Rust crate cannot be built
+    here (no cargo/rustc on the image), so this is the oracle port (oracle/, -O3 -march=native),
+    with every host thread, each step a bounded sample of the same workload."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    job = make_job(args)
+    per_step = max(2.0, min(args.cpu_seconds, 120.0 / max(1, args.steps + args.warmup)))
+    for _ in range(args.warmup):
+        cpu_sample(job, per_step)
+    tot_paths = tot_rays = 0
+    tot_s = 0.0
+    last = None
+    for _ in range(args.steps):
+        last = cpu_sample(job, per_step)
+        tot_paths += last["paths"]; tot_rays += last["rays"]; tot_s += last["seconds"]
+    val = tot_paths / tot_s / 1e6
+    vp = job.viewport
+    line = {"impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": tot_s / args.steps * 1e3, "higher_is_better": True,
+            "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": workload_name(job), "step": last["sample"], "host_threads": last["threads"]},
+            "mrays_per_s": tot_rays / tot_s / 1e6,
+            "cpu_baseline": {"value": val, "unit": UNIT, "cores": last["threads"], "kind": "port", "sample": last["sample"]},
+            "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "full_frame_seconds_extrapolated": vp.width * vp.height * vp.samples / (val * 1e6)}
+    print(json.dumps(line), flush=True)
+
+
+# ----------------------------------------------------------------------------- GPU arm
+def run_b200(args):
+    import torch
+    import torch.distributed as dist
+    import rtw_b200
+    from rtw_b200 import _abi as A
+    from rtw_b200.backend import CudaBackend
+    from rtw_b200.sharding import sample_range
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the product has no CPU path (use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    dev = torch.device("cuda", local)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+
+    job = make_job(args)
+    vp = job.viewport
+    be = CudaBackend(device=local)
+    rtw_b200.set_default_backend(be)
+    h = be.scene(job.scene)
+    cam = vp.camera(be)
+    W, H, spp = cam.width, cam.height, vp.samples
+    begin, count = sample_range(spp, world, rank)
+    o = vp.opts(job.ray_color, job.mode)
+    o.output = A.RTW_OUT_SUM
+    o.sample_begin, o.sample_count = begin, count
+    buf = torch.empty((H, W, 3), dtype=torch.float32, device=dev)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)      # > 126 MB L2
+    stream = torch.cuda.current_stream().cuda_stream
+
+    def step(collect=None):
+        flush.zero_()                                   # L2 flush between steps
+        if count > 0:
+            h.render_device(cam, o, buf.data_ptr(), stream)
+        else:
+            buf.zero_()
+        if world > 1:
+            dist.reduce(buf, dst=0, op=dist.ReduceOp.SUM)
+        if rank == 0:
+            be.resolve_device(buf.data_ptr(), H * W, spp, vp.gamma, stream)
+        if collect is not None and count > 0:
+            st = h.stats()                              # syncs on this step's last event
+            collect.append((st.kernel_ms, st.rays, st.paths, st.nan_paths))
+
+    for _ in range(args.warmup):
+        step()
+    torch.cuda.synchronize()
+    sampler = ClockSampler(local) if rank == 0 else None
+    if sampler:
+        sampler.start()
+    per_step = []
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier(); torch.cuda.synchronize()
+    ev0.record()
+    for _ in range(args.steps):
+        step(per_step)
+    ev1.record()
+    torch.cuda.synchronize(); barrier()
+    clocks = sampler.stop() if sampler else None
+    ms = torch.tensor([ev0.elapsed_time(ev1)], dtype=torch.float64, device=dev)
+    tot = torch.tensor([sum(p[1] for p in per_step), sum(p[2] for p in per_step), sum(p[3] for p in per_step)],
+                       dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        dist.all_reduce(tot, op=dist.ReduceOp.SUM)
+    elapsed_ms = float(ms.item())
+    rays_total, paths_total, nan_total = (float(x) for x in tot.tolist())
+    image_mean = None
+    if rank == 0:
+        img = buf.cpu().numpy()
+        fin = np.isfinite(img)
+        image_mean = float(img[fin].mean())
+
+    # ---- e2e: the C-ABI call a host program makes, host buffers, every step from scratch
+    fs = job.scene.flatten()
+    host_out = torch.empty((H, W, 3), dtype=torch.float32).pin_memory()
+    lib = be.lib
+    e2e_steps = args.e2e_steps or args.steps
+
+    def e2e_step():
+        hd = C.c_void_p()
+        A.check(lib.rtw_scene_create(C.byref(fs.desc), local, C.byref(hd)))
+        try:
+            if world == 1:
+                o2 = vp.opts(job.ray_color, job.mode)
+                A.check(lib.rtw_render(hd, C.byref(cam), C.byref(o2), C.c_void_p(host_out.data_ptr())))
+            else:
+                if count > 0:
+                    A.check(lib.rtw_render_device(hd, C.byref(cam), C.byref(o), C.c_void_p(buf.data_ptr()), C.c_void_p(stream)))
+                else:
+                    buf.zero_()
+                dist.reduce(buf, dst=0, op=dist.ReduceOp.SUM)
+                if rank == 0:
+                    be.resolve_device(buf.data_ptr(), H * W, spp, vp.gamma, stream)
+                    host_out.copy_(buf, non_blocking=True)
+                torch.cuda.synchronize()
+            inf = A.rtw_scene_info()
+            A.check(lib.rtw_scene_get_info(hd, C.byref(inf)))
+            return int(inf.device_bytes)
+        finally:
+            lib.rtw_scene_destroy(hd)
+
+    e2e_step()
+    barrier(); torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        h2d = e2e_step()
+    torch.cuda.synchronize(); barrier()
+    e2e_s = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
+    e2e_s = float(e2e_s.item())
+
+    # ---- rank 0: algorithmic work per ray (instrumented kernel), roofline denominators, CPU baseline
+    if rank == 0:
+        oc = vp.opts(job.ray_color, job.mode)
+        oc.output = A.RTW_OUT_SUM
+        oc.flags |= A.RTW_FLAG_COUNT_WORK
+        oc.sample_begin, oc.sample_count = 0, min(16, spp)
+        h.render_device(cam, oc, buf.data_ptr(), stream)
+        wc = h.stats()
+        per_ray = {"node": wc.nodes / wc.rays, "sphere": wc.sphere_tests / wc.rays, "quad": wc.quad_tests / wc.rays,
+                   "instance": wc.instance_tests / wc.rays, "hit": wc.hits / wc.rays}
+        flop_per_ray = sum(per_ray[k] * COST[k][0] for k in COST)
+        bytes_per_ray = sum(per_ray[k] * COST[k][1] for k in COST)
+        fp32_peak = be.microbench(A.RTW_BENCH_FP32)
+        l2_peak = be.microbench(A.RTW_BENCH_L2)
+        peaks_file = os.path.join(ROOT, "MEASURED_PEAKS.json")
+        hbm_peak, hbm_src = 6650.0, "fallback"
+        if os.path.exists(peaks_file):
+            try:
+                hbm_peak, hbm_src = float(json.load(open(peaks_file))["hbm_gbs"]), "measured"
+            except Exception:
+                pass
+        # dominant kernel = mega_kernel: average launch duration over the timed region, rank 0
+        k_ms = statistics.mean(p[0] for p in per_step) if per_step else float("nan")
+        rays_launch = statistics.mean(p[1] for p in per_step) if per_step else 0.0
+        paths_launch = statistics.mean(p[2] for p in per_step) if per_step else 0.0
+        tflops = flop_per_ray * rays_launch / (k_ms * 1e-3) / 1e12
+        l2_gbs = bytes_per_ray * rays_launch / (k_ms * 1e-3) / 1e9
+        hbm_bytes_launch = paths_launch / max(1, 32 * 64) * 0 + H * W * 3 * 4 * 2.0   # framebuffer RED traffic only (lower bound)
+        cands = [("fp32", tflops, fp32_peak, "TFLOP/s"), ("l2", l2_gbs, l2_peak, "GB/s")]
+        bname, bach, bpeak, bunit = max(cands, key=lambda c: c[1] / c[2])
+        roofline = {"kernel": "mega_kernel", "bound": bname, "achieved": bach, "peak": bpeak, "unit": bunit,
+                    "frac": bach / bpeak, "traffic": None, "peak_source": "rtw_microbench on this GPU (MEASURED_PEAKS.json has no fp32/L2 entry)",
+                    "kernel_ms_per_launch": k_ms, "rays_per_launch": rays_launch,
+                    "per_ray": {**per_ray, "flop": flop_per_ray, "scene_bytes": bytes_per_ray},
+                    "all": {"fp32": {"achieved": tflops, "peak": fp32_peak, "unit": "TFLOP/s", "frac": tflops / fp32_peak},
+                            "l2": {"achieved": l2_gbs, "peak": l2_peak, "unit": "GB/s", "frac": l2_gbs / l2_peak},
+                            "hbm": {"achieved": hbm_bytes_launch / (k_ms * 1e-3) / 1e9, "peak": hbm_peak, "unit": "GB/s",
+                                    "frac": hbm_bytes_launch / (k_ms * 1e-3) / 1e9 / hbm_peak, "peak_source": hbm_src,
+                                    "note": "scene (<10 MB) is L1/L2-resident; only the framebuffer REDs reach HBM"}}}
+        cpu = cpu_baseline_obj(cpu_sample(job, args.cpu_seconds)) if world == 1 else None
+        paths_frame = W * H * spp
+        val = paths_frame * args.steps / (elapsed_ms * 1e-3) / 1e6
+        line = {"metric": METRIC, "value": val, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+                "ms_per_step": elapsed_ms / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+                "dtype": "f32", "data": "synthetic",
+                "config": {"workload": workload_name(job), "partition": f"sample range x{world} + NCCL reduce(sum) to rank 0",
+                           "l2": "256 MiB memset between steps (inside the timed region)", "pipeline": "megakernel",
+                           "fp": "strict (-fmad=false)" if args.flags & 1 else "fast (FFMA contraction)"},
+                "mrays_per_s": rays_total / (elapsed_ms * 1e-3) / 1e6, "rays_per_path": rays_total / max(1.0, paths_total),
+                "nan_paths": nan_total, "image_mean": image_mean,
+                "e2e": {"value": paths_frame * e2e_steps / e2e_s / 1e6, "unit": UNIT, "h2d_bytes_per_step": h2d * world,
+                        "d2h_bytes_per_step": H * W * 3 * 4, "ms_per_step": e2e_s / e2e_steps * 1e3, "steps": e2e_steps,
+                        "what": "rtw_scene_create + rtw_render(host out) + rtw_scene_destroy per step"},
+                "gpu_launches": args.steps * (world + 1), "clocks": clocks, "roofline": roofline}
+        if cpu is not None:
+            line["cpu_baseline"] = cpu
+        print(json.dumps(line), flush=True)
+    barrier()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    a = parse_args()
+    if a.impl == "reference":
+        run_reference(a)
+    else:
+        run_b200(a)

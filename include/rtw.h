@@ -153,7 +153,10 @@ enum {
     RTW_FLAG_STRICT_FP = 1u,
     /* Render through the wavefront pipeline (generate / extend / shade / accumulate kernels with
      * ray queues in HBM) instead of the default path-regenerating megakernel. */
-    RTW_FLAG_WAVEFRONT = 2u
+    RTW_FLAG_WAVEFRONT = 2u,
+    /* Use the instrumented build of the fast kernels, which also counts BVH node visits and
+     * primitive tests (rtw_stats.nodes ...): the algorithmic work behind the roofline. Slower. */
+    RTW_FLAG_COUNT_WORK = 4u
 };
 
 typedef struct rtw_render_opts {
@@ -183,6 +186,10 @@ typedef struct rtw_stats {
     uint64_t gpu_launches;   /* kernels launched by the last render call */
     float    kernel_ms;      /* device time of the trace kernel(s), CUDA events */
     float    total_ms;       /* device time incl. resolve and D2H copy when there is one */
+    /* filled only by RTW_FLAG_COUNT_WORK renders, else 0 */
+    uint64_t nodes;          /* BVH nodes visited (each = two child-box slab tests, 64 B) */
+    uint64_t sphere_tests, quad_tests, instance_tests;
+    uint64_t hits;           /* segments that ended on a surface (Hit evaluated + scatter) */
 } rtw_stats;
 
 typedef struct rtw_scene rtw_scene;   /* opaque: device-resident flattened scene + BVH */
@@ -232,6 +239,13 @@ int rtw_quantize_device(const float* d_rgb, uint8_t* d_rgb8, uint64_t n_values, 
                         void* stream);
 
 int rtw_get_stats(rtw_scene* scene, rtw_stats* out);
+
+/* --- device micro-benchmarks: the denominators of the FP32 and L2 rooflines, which
+ * MEASURED_PEAKS.json does not carry. which = RTW_BENCH_FP32 -> TFLOP/s of dependent-free FFMA
+ * chains on every SM; RTW_BENCH_L2 -> GB/s of 128-bit read-only loads over a 32 MiB (L2-resident)
+ * buffer; RTW_BENCH_HBM -> GB/s of the same loads over 2 GiB. Best of `reps` launches. */
+enum { RTW_BENCH_FP32 = 0, RTW_BENCH_L2 = 1, RTW_BENCH_HBM = 2 };
+int rtw_microbench(int device, int which, int reps, double* out_value);
 
 /* --- introspection used by tests and the bench (sizes of what was uploaded) */
 typedef struct rtw_scene_info {

@@ -96,6 +96,12 @@ class CudaBackend:
             scene._backend_cache[key] = h
         return h
 
+    def microbench(self, which: int, reps: int = 3) -> float:
+        """FP32 TFLOP/s / L2 GB/s / HBM GB/s of this device (roofline denominators)."""
+        v = C.c_double()
+        A.check(self.lib.rtw_microbench(self.device, which, reps, C.byref(v)))
+        return float(v.value)
+
     def resolve_device(self, d_ptr: int, n_pixels: int, total_samples: int, gamma: float, stream: int = 0):
         A.check(self.lib.rtw_resolve_device(C.c_void_p(d_ptr), n_pixels, total_samples, gamma, self.device,
                                             C.c_void_p(stream)))

@@ -49,6 +49,31 @@ __global__ void quantize_kernel(const float* __restrict__ rgb, uint8_t* __restri
     }
 }
 
+// ---- micro-benchmarks (rtw_microbench): denominators for the FP32 and L2 rooflines
+__global__ void bench_fp32_kernel(float* out, int iters, float a, float b) {
+    float x0 = threadIdx.x * 1e-3f, x1 = x0 + 1.f, x2 = x0 + 2.f, x3 = x0 + 3.f, x4 = x0 + 4.f, x5 = x0 + 5.f,
+          x6 = x0 + 6.f, x7 = x0 + 7.f;
+    for (int i = 0; i < iters; ++i) {   // 8 independent FFMA chains per thread
+        x0 = fmaf(x0, a, b); x1 = fmaf(x1, a, b); x2 = fmaf(x2, a, b); x3 = fmaf(x3, a, b);
+        x4 = fmaf(x4, a, b); x5 = fmaf(x5, a, b); x6 = fmaf(x6, a, b); x7 = fmaf(x7, a, b);
+    }
+    float s = x0 + x1 + x2 + x3 + x4 + x5 + x6 + x7;
+    if (s == 123.456f) out[0] = s;
+}
+__global__ void bench_read_kernel(const uint4* __restrict__ buf, unsigned long long n_vec, int passes, unsigned* out) {
+    unsigned acc = 0;
+    const unsigned long long stride = (unsigned long long)gridDim.x * blockDim.x;
+    for (int p = 0; p < passes; ++p) {
+        // rotate the block -> slice mapping every pass so that no SM re-reads what its L1 holds
+        const unsigned blk = (blockIdx.x + (unsigned)p * 61u) % gridDim.x;
+        for (unsigned long long k = (unsigned long long)blk * blockDim.x + threadIdx.x; k < n_vec; k += stride) {
+            uint4 v = __ldg(&buf[k]);
+            acc ^= v.x ^ v.y ^ v.z ^ v.w;
+        }
+    }
+    if (acc == 0x12345678u) out[0] = acc;
+}
+
 int grid_for(unsigned long long n, int block) {
     unsigned long long g = (n + block - 1) / block;
     if (g < 1) g = 1;
@@ -61,7 +86,7 @@ int grid_for(unsigned long long n, int block) {
 struct rtw_scene {
     int device = 0;
     int sm_count = 0;
-    int occ_fast = 0, occ_strict = 0;
+    int occ_fast = 0, occ_strict = 0, occ_count = 0;
     Scene d{};                            // device pointers
     std::vector<void*> allocs;
     std::vector<cudaArray_t> arrays;
@@ -157,10 +182,10 @@ int upload_scene(rtw_scene* s, HostScene& hs) {
 
 // Work decomposition (see MegaLaunch): enough items to balance, chunks short enough that the tail
 // is small, long enough that the three REDs per lane per item are noise.
-MegaLaunch plan_mega(const rtw_scene* s, const RenderParams& P, bool strict) {
+MegaLaunch plan_mega(const rtw_scene* s, const RenderParams& P, int variant) {
     MegaLaunch L;
     L.block = RTW_MEGA_BLOCK;
-    int occ = strict ? s->occ_strict : s->occ_fast;
+    int occ = variant == 1 ? s->occ_strict : variant == 2 ? s->occ_count : s->occ_fast;
     if (occ < 1) occ = 1;
     L.grid = s->sm_count * occ;
     L.tiles_x = (P.cam.width + 7u) / 8u;
@@ -186,16 +211,18 @@ int enqueue_render(rtw_scene* s, const rtw_camera* cam, const rtw_render_opts* o
     RenderParams P; uint32_t total = 0; std::string err;
     int rc = make_render_params(cam, o, P, total, err);
     if (rc) return fail(rc, err);
-    const bool strict = (o->flags & RTW_FLAG_STRICT_FP) != 0;
-    MegaLaunch L = plan_mega(s, P, strict);
+    if (o->flags & RTW_FLAG_WAVEFRONT) return fail(RTW_E_UNSUPPORTED, "wavefront pipeline not built in this version");
+    const int variant = (o->flags & RTW_FLAG_STRICT_FP) ? 1 : (o->flags & RTW_FLAG_COUNT_WORK) ? 2 : 0;
+    MegaLaunch L = plan_mega(s, P, variant);
     if ((uint64_t)L.tiles_x * L.tiles_y * L.n_chunks > 0xFFFFFFF0ull) return fail(RTW_E_UNSUPPORTED, "too many work items; shard the render");
     const size_t n_values = (size_t)P.row_count * cam->width * 3u;
     CK(cudaMemsetAsync(d_out, 0, n_values * sizeof(float), st));
     CK(cudaMemsetAsync(s->d_ctr, 0, sizeof(Counters), st));
     CK(cudaMemsetAsync(s->d_work, 0, sizeof(uint32_t), st));
     CK(cudaEventRecord(s->ev0, st));
-    CK(strict ? launch_mega_strict(s->d, P, d_out, s->d_ctr, s->d_work, L, st)
-              : launch_mega_fast(s->d, P, d_out, s->d_ctr, s->d_work, L, st));
+    CK(variant == 1   ? launch_mega_strict(s->d, P, d_out, s->d_ctr, s->d_work, L, st)
+       : variant == 2 ? launch_mega_count(s->d, P, d_out, s->d_ctr, s->d_work, L, st)
+                      : launch_mega_fast(s->d, P, d_out, s->d_ctr, s->d_work, L, st));
     CK(cudaEventRecord(s->ev1, st));
     s->launches = 1;
     if (o->output == RTW_OUT_RESOLVED) {
@@ -278,6 +305,7 @@ int rtw_scene_create(const rtw_scene_desc* desc, int device, rtw_scene** out) {
     if ((ce = cudaDeviceGetAttribute(&s->sm_count, cudaDevAttrMultiProcessorCount, device)) != cudaSuccess) return bail(cuda_fail(ce, "sm count"));
     if ((ce = mega_occupancy_fast(&s->occ_fast)) != cudaSuccess) return bail(cuda_fail(ce, "occupancy(fast)"));
     if ((ce = mega_occupancy_strict(&s->occ_strict)) != cudaSuccess) return bail(cuda_fail(ce, "occupancy(strict)"));
+    if ((ce = mega_occupancy_count(&s->occ_count)) != cudaSuccess) return bail(cuda_fail(ce, "occupancy(count)"));
     if ((ce = cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking)) != cudaSuccess) return bail(cuda_fail(ce, "stream"));
     if ((ce = cudaEventCreate(&s->ev0)) != cudaSuccess || (ce = cudaEventCreate(&s->ev1)) != cudaSuccess ||
         (ce = cudaEventCreate(&s->ev2)) != cudaSuccess) return bail(cuda_fail(ce, "events"));
@@ -350,8 +378,56 @@ int rtw_get_stats(rtw_scene* scene, rtw_stats* out) {
     CK(cudaEventSynchronize(scene->ev2));
     out->paths = scene->h_ctr->paths; out->rays = scene->h_ctr->rays; out->nan_paths = scene->h_ctr->nan_paths;
     out->gpu_launches = scene->launches;
+    out->nodes = scene->h_ctr->nodes; out->sphere_tests = scene->h_ctr->spheres; out->quad_tests = scene->h_ctr->quads;
+    out->instance_tests = scene->h_ctr->instances; out->hits = scene->h_ctr->hits;
     CK(cudaEventElapsedTime(&out->kernel_ms, scene->ev0, scene->ev1));
     CK(cudaEventElapsedTime(&out->total_ms, scene->ev0, scene->ev2));
+    return RTW_OK;
+}
+
+int rtw_microbench(int device, int which, int reps, double* out_value) {
+    if (!out_value || reps < 1) return fail(RTW_E_INVALID, "bad microbench arguments");
+    if (device >= 0) CK(cudaSetDevice(device));
+    int sms = 0, dev = 0;
+    CK(cudaGetDevice(&dev));
+    CK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    cudaEvent_t e0, e1;
+    CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
+    double best = 0.0;
+    if (which == RTW_BENCH_FP32) {
+        float* d = nullptr; CK(cudaMalloc(&d, 16));
+        const int iters = 1 << 16, block = 256, grid = sms * 8;
+        for (int r = 0; r < reps + 1; ++r) {
+            CK(cudaEventRecord(e0));
+            bench_fp32_kernel<<<grid, block>>>(d, iters, 1.0000001f, 1e-7f);
+            CK(cudaEventRecord(e1)); CK(cudaEventSynchronize(e1));
+            float ms = 0; CK(cudaEventElapsedTime(&ms, e0, e1));
+            double tf = 2.0 * 8.0 * iters * (double)grid * block / (ms * 1e-3) / 1e12;
+            if (r > 0 && tf > best) best = tf;
+        }
+        cudaFree(d);
+    } else if (which == RTW_BENCH_L2 || which == RTW_BENCH_HBM) {
+        const size_t bytes = which == RTW_BENCH_L2 ? (32ull << 20) : (2ull << 30);
+        const int passes = which == RTW_BENCH_L2 ? 64 : 1;
+        uint4* d = nullptr; unsigned* o = nullptr;
+        CK(cudaMalloc(&d, bytes)); CK(cudaMalloc(&o, 16));
+        CK(cudaMemset(d, 1, bytes));
+        for (int r = 0; r < reps + 1; ++r) {
+            CK(cudaEventRecord(e0));
+            bench_read_kernel<<<sms * 8, 512>>>(d, bytes / 16, passes, o);
+            CK(cudaEventRecord(e1)); CK(cudaEventSynchronize(e1));
+            float ms = 0; CK(cudaEventElapsedTime(&ms, e0, e1));
+            double gbs = (double)bytes * passes / (ms * 1e-3) / 1e9;
+            if (r > 0 && gbs > best) best = gbs;
+        }
+        cudaFree(d); cudaFree(o);
+    } else {
+        cudaEventDestroy(e0); cudaEventDestroy(e1);
+        return fail(RTW_E_INVALID, "unknown microbench");
+    }
+    cudaEventDestroy(e0); cudaEventDestroy(e1);
+    CK(cudaGetLastError());
+    *out_value = best;
     return RTW_OK;
 }
 

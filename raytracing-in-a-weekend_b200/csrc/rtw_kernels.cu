@@ -10,7 +10,7 @@
 // image textures go through texture objects. Per-pixel sums leave the SM as three f32 REDs per
 // lane per item. No tensor cores: nothing here is a contraction.
 //
-// Compiled twice (see rtw_kernels.h): RTW_VARIANT = fast | strict.
+// Compiled three times (see rtw_kernels.h): RTW_VARIANT = fast | strict | count.
 #include "rtw_kernels.h"
 
 #ifndef RTW_VARIANT
@@ -46,6 +46,12 @@ mega_kernel(const Scene sc, const RenderParams P, float* __restrict__ sum, Count
     const uint32_t lane = threadIdx.x & 31u;
     const uint32_t W = P.cam.width;
     uint32_t n_paths = 0, n_rays = 0, n_nan = 0;
+#if defined(RTW_COUNT_WORK)
+    Work wk = {0u, 0u, 0u, 0u, 0u};
+    Work* const wp = &wk;
+#else
+    Work* const wp = nullptr;
+#endif
 
     for (;;) {
         uint32_t item = 0;
@@ -70,7 +76,7 @@ mega_kernel(const Scene sc, const RenderParams P, float* __restrict__ sum, Count
                     ++s;
                     alive = true;
                 }
-                if (path_step(sc, nt, P, path, n_rays)) {
+                if (path_step(sc, nt, P, path, n_rays, wp)) {
                     V3 c = path_result(path);
                     if (!finite3(c)) ++n_nan;
                     acc = acc + c;
@@ -91,6 +97,14 @@ mega_kernel(const Scene sc, const RenderParams P, float* __restrict__ sum, Count
         atomicAdd(&ctr->rays, r);
         if (n) atomicAdd(&ctr->nan_paths, n);
     }
+#if defined(RTW_COUNT_WORK)
+    unsigned long long w0 = warp_sum_u64(wk.nodes), w1 = warp_sum_u64(wk.spheres), w2 = warp_sum_u64(wk.quads),
+                       w3 = warp_sum_u64(wk.instances), w4 = warp_sum_u64(wk.hits);
+    if (lane == 0) {
+        atomicAdd(&ctr->nodes, w0); atomicAdd(&ctr->spheres, w1); atomicAdd(&ctr->quads, w2);
+        atomicAdd(&ctr->instances, w3); atomicAdd(&ctr->hits, w4);
+    }
+#endif
 }
 
 }  // namespace variant

@@ -1,6 +1,7 @@
 // rtw_kernels.h — launch interface of rtw_kernels.cu. That file is compiled twice:
 //   fast   : nvcc default (a*b+c contracts to FFMA)             -> launch_*_fast
 //   strict : -fmad=false -DRTW_STRICT_FP (rustc-like arithmetic) -> launch_*_strict
+//   count  : fast + -DRTW_COUNT_WORK (node/primitive test counters) -> launch_*_count
 // selected per render call by RTW_FLAG_STRICT_FP.
 #pragma once
 #include <cuda_runtime.h>
@@ -8,7 +9,10 @@
 
 namespace rtw {
 
-struct Counters { unsigned long long paths, rays, nan_paths, pad; };
+struct Counters {
+    unsigned long long paths, rays, nan_paths;
+    unsigned long long nodes, spheres, quads, instances, hits;   // only from the RTW_COUNT_WORK build
+};
 
 // Work decomposition of the path-regenerating megakernel: an item is one 8x4 pixel tile x one
 // chunk of consecutive samples; warps pull items from a global counter.
@@ -30,5 +34,6 @@ struct MegaLaunch {
 
 RTW_DECLARE_VARIANT(fast)
 RTW_DECLARE_VARIANT(strict)
+RTW_DECLARE_VARIANT(count)    // fast + algorithmic work counters (RTW_FLAG_COUNT_WORK)
 
 }  // namespace rtw

@@ -291,11 +291,12 @@ RTW_HD void generate(const RenderParams& P, uint32_t i, uint32_t j, uint32_t s, 
 
 // One segment of one path: extend + shade. Returns true when the path is finished (p.rad final).
 // `rays` counts Scene::collision_normal equivalents.
-RTW_HD bool path_step(const Scene& sc, const Noise* nt, const RenderParams& P, Path& p, uint32_t& rays) {
+RTW_HD bool path_step(const Scene& sc, const Noise* nt, const RenderParams& P, Path& p, uint32_t& rays,
+                      Work* work = nullptr) {
     const uint32_t ig = P.integrator;
     const bool first_hit = (ig == RTW_INT_NORMAL || ig == RTW_INT_ALBEDO);
     if (!first_hit && p.depth_left < 1u) return true;               // ray_color.rs:14-16
-    TraceCtx cx; cx.sc = &sc; cx.rng = &p.rng; cx.bounce = p.bounce; cx.mint = P.mint; cx.maxt = P.maxt;
+    TraceCtx cx; cx.sc = &sc; cx.rng = &p.rng; cx.bounce = p.bounce; cx.mint = P.mint; cx.maxt = P.maxt; cx.work = work;
     Best b = trace(cx, p.ray);
     ++rays;
     if (b.ref == REF_NONE) {                                        // miss
@@ -306,6 +307,7 @@ RTW_HD bool path_step(const Scene& sc, const Noise* nt, const RenderParams& P, P
         p.rad = p.rad + p.thr * bg;
         return true;
     }
+    RTW_COUNT(cx, hits);
     Hit h;
     eval_hit(cx, nt, b, p.ray, h);
     if (first_hit) {                                                // viewport.rs:524-554

@@ -115,26 +115,40 @@ struct Best {
 };
 RTW_HD bool closer(float t, uint32_t ref, const Best& b) { return t < b.t || (t == b.t && ref < b.ref); }
 
+// Algorithmic work of a traversal, counted only by the instrumented kernel build
+// (-DRTW_COUNT_WORK, RTW_FLAG_COUNT_WORK): the per-ray figures bench.py's roofline uses.
+struct Work { uint32_t nodes, spheres, quads, instances, hits; };
+#if defined(RTW_COUNT_WORK)
+#define RTW_COUNT(cx, field) (++(cx).work->field)
+#else
+#define RTW_COUNT(cx, field) ((void)0)
+#endif
+
 struct TraceCtx {
     const Scene* sc;
     const PathRng* rng;
     uint32_t bounce;
     float mint, maxt;   // the integrator's interval (un-shrunk)
+    Work* work;         // null unless RTW_COUNT_WORK
 };
 
 #define RTW_STACK 32
 
 // Leaf test of one sphere/quad against the current best (static spheres only; moving ones are
 // handled by test_moving).
-RTW_HD void test_prim(const Scene& sc, uint32_t ref, const Ray& r, const RayK& k, float mint, Best& best) {
+RTW_HD void test_prim(const TraceCtx& cx, uint32_t ref, const Ray& r, const RayK& k, Best& best) {
+    const Scene& sc = *cx.sc;
+    const float mint = cx.mint;
     uint32_t idx = ref_index(ref);
     float t;
     if (ref_kind(ref) == KIND_SPHERE) {
+        RTW_COUNT(cx, spheres);
         float4 s = RTW_LDG(&sc.spheres[idx]);
         if (sphere_t(v3(s.x, s.y, s.z), s.w, r, k.a, mint, best.t, t) && closer(t, ref, best)) {
             best.t = t; best.ref = ref; best.inner = REF_NONE;
         }
     } else {
+        RTW_COUNT(cx, quads);
         float al, be;
         if (quad_t(&sc.quads[idx], r, mint, best.t, t, al, be) && closer(t, ref, best)) {
             best.t = t; best.ref = ref; best.inner = REF_NONE;
@@ -144,9 +158,11 @@ RTW_HD void test_prim(const Scene& sc, uint32_t ref, const Ray& r, const RayK& k
 
 // Moving spheres of a level: t=0 leaf box against the un-shrunk interval (aabb.rs:27-38,109-126),
 // then the sphere at its position at ray time (sphere.rs:100).
-RTW_HD void test_moving(const Scene& sc, const Level& lv, const Ray& r, const RayK& k, float mint, float maxt,
-                        Best& best) {
+RTW_HD void test_moving(const TraceCtx& cx, const Level& lv, const Ray& r, const RayK& k, Best& best) {
+    const Scene& sc = *cx.sc;
+    const float mint = cx.mint, maxt = cx.maxt;
     for (uint32_t m = 0; m < lv.mov_count; ++m) {
+        RTW_COUNT(cx, spheres);
         uint32_t idx = RTW_LDG(&sc.moving[lv.mov_first + m]);
         float4 lo = RTW_LDG(&sc.sphere_box[2 * idx]), hi = RTW_LDG(&sc.sphere_box[2 * idx + 1]);
         float tn;
@@ -165,10 +181,11 @@ RTW_HD void test_moving(const Scene& sc, const Level& lv, const Ray& r, const Ra
 // Walk one instance-local level (spheres and quads only). ANY = stop at the first hit (the volume
 // re-traversal of instance.rs:284-294 only asks whether anything is hit).
 template <bool ANY>
-RTW_HD bool walk_inner(const Scene& sc, const Level& lv, const Ray& r, const RayK& k, float mint, float maxt,
-                       Best& best) {
+RTW_HD bool walk_inner(const TraceCtx& cx, const Level& lv, const Ray& r, const RayK& k, Best& best) {
+    const Scene& sc = *cx.sc;
+    const float mint = cx.mint;
     if (lv.mov_count) {
-        test_moving(sc, lv, r, k, mint, maxt, best);
+        test_moving(cx, lv, r, k, best);
         if (ANY && best.ref != REF_NONE) return true;
     }
     if (lv.root == REF_NONE) return best.ref != REF_NONE;
@@ -180,6 +197,7 @@ RTW_HD bool walk_inner(const Scene& sc, const Level& lv, const Ray& r, const Ray
     uint32_t cur = lv.root;
     for (;;) {
         if (ref_kind(cur) == KIND_NODE) {
+            RTW_COUNT(cx, nodes);
             const Node* np = &sc.nodes[cur];
             float4 n0 = RTW_LDG(&np->n0), n1 = RTW_LDG(&np->n1), n2 = RTW_LDG(&np->n2);
             uint4 n3 = RTW_LDG(&np->n3);
@@ -195,7 +213,7 @@ RTW_HD bool walk_inner(const Scene& sc, const Level& lv, const Ray& r, const Ray
             if (h0) { cur = n3.x; continue; }
             if (h1) { cur = n3.y; continue; }
         } else {
-            test_prim(sc, cur, r, k, mint, best);
+            test_prim(cx, cur, r, k, best);
             if (ANY && best.ref != REF_NONE) return true;
         }
         if (sp == 0) break;
@@ -221,18 +239,19 @@ RTW_HD float volume_distance(const Instance& in, const TraceCtx& cx) {
 
 RTW_HD void test_instance(const TraceCtx& cx, uint32_t ref, const Ray& r, Best& best) {
     const Scene& sc = *cx.sc;
+    RTW_COUNT(cx, instances);
     const Instance& in = sc.instances[ref_index(ref)];
     Ray l = to_local(in, r);
     RayK k = ray_constants(l);
     Best ib; ib.t = best.t; ib.ref = REF_NONE; ib.inner = REF_NONE;
-    if (!walk_inner<false>(sc, in.level, l, k, cx.mint, cx.maxt, ib)) return;
+    if (!walk_inner<false>(cx, in.level, l, k, ib)) return;
     if (in.flags & INST_VOLUME) {
         float distance = volume_distance(in, cx);
         if (distance >= 0.0f) {
             Ray l2 = l;
             l2.o = (l.o + l.d * ib.t) + l.d * distance;
             Best any; any.t = cx.maxt; any.ref = REF_NONE; any.inner = REF_NONE;
-            if (!walk_inner<true>(sc, in.level, l2, k, cx.mint, cx.maxt, any)) return;
+            if (!walk_inner<true>(cx, in.level, l2, k, any)) return;
         }
     }
     if (closer(ib.t, ref, best)) { best.t = ib.t; best.ref = ref; best.inner = ib.ref; }
@@ -244,7 +263,7 @@ RTW_HD Best trace(const TraceCtx& cx, const Ray& r) {
     const Level& lv = sc.top;
     Best best; best.t = cx.maxt; best.ref = REF_NONE; best.inner = REF_NONE;
     RayK k = ray_constants(r);
-    if (lv.mov_count) test_moving(sc, lv, r, k, cx.mint, cx.maxt, best);
+    if (lv.mov_count) test_moving(cx, lv, r, k, best);
     if (lv.root == REF_NONE) return best;
     float tn;
     if (!slab(v3(lv.lo[0], lv.lo[1], lv.lo[2]), v3(lv.hi[0], lv.hi[1], lv.hi[2]), r, k, cx.mint, best.t, tn))
@@ -255,6 +274,7 @@ RTW_HD Best trace(const TraceCtx& cx, const Ray& r) {
     for (;;) {
         uint32_t kind = ref_kind(cur);
         if (kind == KIND_NODE) {
+            RTW_COUNT(cx, nodes);
             const Node* np = &sc.nodes[cur];
             float4 n0 = RTW_LDG(&np->n0), n1 = RTW_LDG(&np->n1), n2 = RTW_LDG(&np->n2);
             uint4 n3 = RTW_LDG(&np->n3);
@@ -272,7 +292,7 @@ RTW_HD Best trace(const TraceCtx& cx, const Ray& r) {
         } else if (kind == KIND_INSTANCE) {
             test_instance(cx, cur, r, best);
         } else {
-            test_prim(sc, cur, r, k, cx.mint, best);
+            test_prim(cx, cur, r, k, best);
         }
         if (sp == 0) break;
         cur = stack[--sp];

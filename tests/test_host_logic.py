@@ -1,0 +1,161 @@
+"""Host logic of the product, on the CPU: scene flattening (Python mirror -> rtw_scene_desc), the host
+scene builder (validation, derived quad/instance quantities, reference leaf boxes, two-level SAH BVH)
+and — through tests/emu/ — the very traversal / shading headers the CUDA kernels are compiled from,
+built for the host and compared with the oracle. The emulator is test infrastructure; the product
+never loads it (test_abi.py checks the product refuses to run without a GPU)."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+import rtw_b200
+from rtw_b200 import _abi as A, scenes
+from rtw_b200.scene import SCATTER_M, ImageTexture, Instance, Quad, Scene, Sphere, Vec3, const_density
+from rtw_b200.viewport import Viewport
+
+
+@pytest.fixture(scope="module")
+def emu():
+    from emu_backend import EmuBackend
+    return EmuBackend()
+
+
+def _small(job, w, h, spp):
+    vp = job.viewport
+    nv = type(vp).new_from_res(w, h, spp, vp.depth, 1.0, vp.vfov, vp.origin, vp.direction, vp.vup, None, vp.lens_radius)
+    nv.shutter_speed, nv.fps, nv.frame = vp.shutter_speed, vp.fps, vp.frame
+    job.viewport = nv
+    return job
+
+
+ALL = dict(scenes.REFERENCE_TESTS)
+ALL.update(scenes.CONFIGS)
+ALL["C4_smoke"] = lambda **k: scenes.config_c4(smoke=True, **k)
+
+
+@pytest.mark.parametrize("name", sorted(ALL))
+def test_traversal_headers_match_oracle(name, oracle, emu):
+    """Same closest hit (bit for bit outside tie pixels) and same path radiance as the oracle: the
+    ordered, shrinking-interval SAH traversal is equivalent to the reference's visit-everything walk."""
+    job = _small(ALL[name](), 64, 48, 3)
+    vp = job.viewport
+    for ig in (A.RTW_INT_NORMAL, A.RTW_INT_ALBEDO):
+        ref = vp._run(ig, job.scene, A.RTW_MODE_NO_RAND, oracle)
+        tie = oracle.scene(job.scene).last_tie.astype(bool)
+        got = vp._run(ig, job.scene, A.RTW_MODE_NO_RAND, emu)
+        assert np.array_equal(got[~tie], ref[~tie], equal_nan=True)
+    ref = vp._run(job.ray_color, job.scene, job.mode, oracle)
+    tie = oracle.scene(job.scene).last_tie.astype(bool)
+    got = vp._run(job.ray_color, job.scene, job.mode, emu)
+    so, se = oracle.scene(job.scene).stats(), emu.scene(job.scene).stats()
+    if not tie.any():
+        assert (se["paths"], se["rays"], se["nan_paths"]) == (so.paths, so.rays, so.nan_paths)
+    ok = ~tie
+    assert np.array_equal(np.isfinite(got[ok]), np.isfinite(ref[ok]))
+    fin = np.isfinite(ref) & ok[..., None]
+    scale = max(1.0, float(np.abs(ref[fin]).max()))
+    assert np.all(np.abs(got[fin] - ref[fin]) <= 2e-6 * scale + 1e-5 * np.abs(ref[fin]))
+
+
+def test_stratified_and_lens_and_frames(oracle, emu):
+    job = scenes.camera_test("depth_of_field", width=40, height=30, samples=5)      # s_root = 3 -> 9 samples
+    ref = job.render(oracle)
+    got = job.render(emu)
+    assert emu.scene(job.scene).stats()["paths"] == 40 * 30 * 9
+    assert np.allclose(got, ref, rtol=1e-5, atol=1e-6)
+    job = _small(scenes.ltr_scene(), 48, 27, 2)
+    job.viewport.frame, job.viewport.fps, job.viewport.shutter_speed = 7, 15.0, 0.5
+    assert np.allclose(job.render(emu), job.render(oracle), rtol=1e-5, atol=1e-6)
+
+
+def test_sample_and_row_ranges_compose(emu):
+    """RTW_OUT_SUM over sample sub-ranges adds up to the whole; row ranges are slices."""
+    job = _small(scenes.config_c4(), 32, 32, 6)
+    vp, be = job.viewport, emu
+    h, cam = be.scene(job.scene), vp.camera(be)
+    o = vp.opts(job.ray_color, job.mode)
+    o.output = A.RTW_OUT_SUM
+    full = h.render(cam, o)
+    o.sample_begin, o.sample_count = 0, 4
+    a = h.render(cam, o)
+    o.sample_begin, o.sample_count = 4, 2
+    b = h.render(cam, o)
+    assert np.allclose(a + b, full, rtol=1e-6, atol=1e-6)
+    o.sample_begin, o.sample_count, o.row_begin, o.row_count = 0, 0, 8, 5
+    assert np.array_equal(h.render(cam, o), full[8:13])
+
+
+def test_scene_info_and_identity_instance_flattening(emu):
+    job = _small(scenes.config_c5(), 16, 16, 1)
+    job.render(emu)
+    inf = emu.scene(job.scene).info()
+    assert inf.n_flattened_instances == 400                       # the untransformed ground boxes
+    assert inf.n_tlas_leaves == 6 + 1 + 2400 + 3 - 1              # 5 static spheres + quad + box quads + 3 instances
+    assert inf.n_tlas_nodes == inf.n_tlas_leaves - 1
+    assert inf.n_blas_nodes == 999                                # the 1000-sphere cluster; 1-sphere volumes need no node
+    assert 0 < inf.bvh_max_depth < 2 * 32
+
+
+def _desc_rc(scene, mutate=None):
+    from emu_backend import load_emu
+    fs = scene.flatten()
+    if mutate:
+        mutate(fs.desc)
+    cam = A.rtw_camera(); cam.width = cam.height = 2
+    o = A.rtw_render_opts(); o.samples, o.depth, o.gamma, o.fps = 1, 1, 1.0, 30.0
+    out = np.zeros((2, 2, 3), dtype=np.float32)
+    return load_emu().emu_render(C.byref(fs.desc), C.byref(cam), C.byref(o), out.ctypes.data_as(C.c_void_p), None, None)
+
+
+def test_scene_validation_errors():
+    sc = scenes.config_c4().scene
+    assert _desc_rc(sc) == 0
+    assert _desc_rc(sc, lambda d: setattr(d, "abi_version", 99)) == A.RTW_E_INVALID
+    assert _desc_rc(sc, lambda d: setattr(d, "n_top_quads", d.n_quads + 1)) == A.RTW_E_INVALID
+
+    def bad_mat(d): d.quads[0].mat_id = 1000
+    assert _desc_rc(sc, bad_mat) == A.RTW_E_INVALID
+
+    def bad_range(d): d.instances[0].n_quads = 10 ** 6
+    assert _desc_rc(sc, bad_range) == A.RTW_E_INVALID
+
+    def nan_sphere(d): d.spheres[0].radius = float("nan")
+    assert _desc_rc(scenes.config_c1().scene, nan_sphere) == A.RTW_E_INVALID
+
+
+def test_empty_and_single_primitive_scenes(oracle, emu):
+    vp = Viewport.new_from_res(12, 9, 2, 5, 1.0)
+    empty = Scene.new([], [], [])
+    empty.background_color = Vec3(0.25, 0.5, 0.75)
+    assert np.array_equal(vp.render_no_rand(rtw_b200.ray_color_albedo, empty, emu),
+                          vp.render_no_rand(rtw_b200.ray_color_albedo, empty, oracle))
+    one = Scene.new_sphere([Sphere.new(Vec3(0, 0, -1), 0.5)])
+    assert np.array_equal(vp.render_no_rand(rtw_b200.ray_color_normal, one, emu),
+                          vp.render_no_rand(rtw_b200.ray_color_normal, one, oracle))
+    inst = Instance.new_sphere([])                               # an instance with nothing inside (box = [0,0])
+    inst.translate(Vec3(0, 0, -3))
+    sc = Scene.new([], [Quad.new(Vec3(-1, -1, -2), Vec3(2, 0, 0), Vec3(0, 2, 0), SCATTER_M, (0, 0, 0),
+                                  ImageTexture.from_color((0.3, 0.6, 0.9)))], [inst])
+    assert np.array_equal(vp.render_no_rand(rtw_b200.ray_color_albedo, sc, emu),
+                          vp.render_no_rand(rtw_b200.ray_color_albedo, sc, oracle))
+
+
+def test_axis_aligned_rays_use_the_literal_slab_rule(oracle, emu):
+    """Direction components that are exactly 0 (objects.rs:126-135): a 1x1 image looking down -z."""
+    vp = Viewport.new_from_res(1, 1, 1, 5, 1.0)
+    sc = Scene.new([Sphere.new(Vec3(0, 0, -3), 1.0)], [Quad.new(Vec3(-1, -1, -5), Vec3(2, 0, 0), Vec3(0, 2, 0), SCATTER_M,
+                   (0, 0, 0), ImageTexture.from_color((1, 0, 0)))], [])
+    cam = vp.camera(oracle)
+    assert cam.pixel00[0] == 0.0 and cam.pixel00[1] == 0.0
+    for ig in (rtw_b200.ray_color_normal, rtw_b200.ray_color_albedo, rtw_b200.ray_color_gradient):
+        assert np.array_equal(vp.render_no_rand(ig, sc, emu), vp.render_no_rand(ig, sc, oracle))
+
+
+def test_deep_bvh_falls_back_to_a_balanced_split(emu):
+    """2048 collinear, nested-size spheres would make a SAH tree deeper than the traversal stack; the
+    builder's median-split guard keeps it below RTW_STACK."""
+    sp = [Sphere.new(Vec3(0, 0, -float(2 ** (i / 64.0))), float(2 ** (i / 64.0)) * 0.9) for i in range(1024)]
+    vp = Viewport.new_from_res(8, 8, 1, 3, 1.0)
+    sc = Scene.new_sphere(sp)
+    vp.render_no_rand(rtw_b200.ray_color_normal, sc, emu)
+    assert emu.scene(sc).info().bvh_max_depth < 32

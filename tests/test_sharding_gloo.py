@@ -1,0 +1,73 @@
+"""world_size-2 `gloo` tests (CPU) of the multi-GPU host logic in rtw_b200.sharding: sample-range split +
+reduce(sum) + resolve, row-band split + gather, frame dealing. The renderer behind it here is the CPU
+oracle (test infrastructure); on the GPU box the same functions drive librtw_b200.so over NCCL."""
+import os
+import socket
+import sys
+
+import numpy as np
+import pytest
+import torch.multiprocessing as mp
+
+from rtw_b200 import sharding
+from rtw_b200 import _abi as A
+
+
+def test_partitions_cover_everything_once():
+    for total in (1, 7, 100, 10000):
+        for world in (1, 2, 3, 8):
+            r = [sharding.sample_range(total, world, k) for k in range(world)]
+            assert r[0][0] == 0 and sum(c for _, c in r) == total
+            assert all(r[k][0] + r[k][1] == r[k + 1][0] for k in range(world - 1))
+    rows = sorted(sum((sharding.row_bands(601, 8, k, band=8) for k in range(8)), []))
+    assert rows[0][0] == 0 and sum(c for _, c in rows) == 601
+    assert all(a + c == b for (a, c), (b, _) in zip(rows, rows[1:]))
+    fr = sorted(sum((sharding.frames_for_rank(5, 20, 8, k) for k in range(8)), []))
+    assert fr == list(range(5, 25))
+    assert sharding.effective_samples(500, A.RTW_MODE_STRATIFIED) == 529 and sharding.effective_samples(9, A.RTW_MODE_NO_RAND) == 1
+
+
+def _free_port():
+    s = socket.socket(); s.bind(("127.0.0.1", 0)); p = s.getsockname()[1]; s.close()
+    return p
+
+
+def _worker(rank, world, port, outdir):
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    sys.path[:0] = [root, os.path.join(root, "tests")]
+    import torch.distributed as dist
+    from rtw_b200 import scenes
+    from oracle_backend import OracleBackend
+    os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        be = OracleBackend(threads=2)
+        job = scenes.config_c4(width=40, height=40, samples=6)
+        img = sharding.render_samples_sharded(job.viewport, job.ray_color, job.scene, job.mode, backend=be)
+        tiles = sharding.render_tiles_sharded(job.viewport, job.ray_color, job.scene, job.mode, backend=be, band=8)
+        anim = scenes.ltr_scene(samples=2, width=32, height=18, frames=5)
+        frames = sharding.render_multi_sharded(anim.viewport, anim.ray_color, anim.scene, backend=be)
+        if rank == 0:
+            np.savez(os.path.join(outdir, "out.npz"), img=img, tiles=tiles, frames=np.stack(frames))
+        else:
+            assert img is None and tiles is None and frames is None
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.timeout(300)
+def test_world_size_2_gloo(tmp_path, oracle):
+    from rtw_b200 import scenes
+    world = 2
+    mp.spawn(_worker, args=(world, _free_port(), str(tmp_path)), nprocs=world, join=True)
+    got = np.load(os.path.join(str(tmp_path), "out.npz"))
+    job = scenes.config_c4(width=40, height=40, samples=6)
+    single = job.render(oracle)
+    fin = np.isfinite(single)
+    assert np.array_equal(np.isfinite(got["img"]), fin)
+    assert np.allclose(got["img"][fin], single[fin], rtol=2e-6, atol=1e-7)      # f32 summation order only
+    assert np.array_equal(got["tiles"], single, equal_nan=True)                # bands: bit-identical
+    anim = scenes.ltr_scene(samples=2, width=32, height=18, frames=5)
+    h = oracle.scene(anim.scene)
+    want = h.render_frames(anim.viewport.camera(oracle), anim.viewport.opts(anim.ray_color, A.RTW_MODE_RANDOM), 0, 5)
+    assert np.array_equal(got["frames"], want, equal_nan=True)
