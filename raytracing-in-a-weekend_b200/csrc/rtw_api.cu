@@ -3,6 +3,7 @@
 // this library) can compute a pixel without a CUDA device.
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <new>
 #include <string>
@@ -87,6 +88,8 @@ struct rtw_scene {
     int device = 0;
     int sm_count = 0;
     int occ_fast = 0, occ_strict = 0, occ_count = 0;
+    uint32_t stack_words = 0;
+    size_t smem_bytes = 0;
     Scene d{};                            // device pointers
     std::vector<void*> allocs;
     std::vector<cudaArray_t> arrays;
@@ -100,6 +103,14 @@ struct rtw_scene {
     float* d_img = nullptr; size_t d_img_floats = 0;
     bool have_stats = false;
     uint64_t launches = 0;
+    // wavefront pipeline state (allocated on first use)
+    WfPool pool{};
+    WfCounters* d_wc = nullptr;
+    WfCounters* h_wc = nullptr;           // pinned, 4 slots
+    cudaEvent_t wf_ev[4] = {nullptr, nullptr, nullptr, nullptr};
+    int occ_wf[3] = {0, 0, 0};
+    bool last_wavefront = false;
+    uint64_t wf_paths = 0;
 
     ~rtw_scene() {
         cudaSetDevice(device);
@@ -107,6 +118,9 @@ struct rtw_scene {
         for (auto a : arrays) cudaFreeArray(a);
         for (auto p : allocs) cudaFree(p);
         if (d_img) cudaFree(d_img);
+        if (d_wc) cudaFree(d_wc);
+        if (h_wc) cudaFreeHost(h_wc);
+        for (auto e : wf_ev) if (e) cudaEventDestroy(e);
         if (d_ctr) cudaFree(d_ctr);
         if (d_work) cudaFree(d_work);
         if (h_ctr) cudaFreeHost(h_ctr);
@@ -182,12 +196,25 @@ int upload_scene(rtw_scene* s, HostScene& hs) {
 
 // Work decomposition (see MegaLaunch): enough items to balance, chunks short enough that the tail
 // is small, long enough that the three REDs per lane per item are noise.
+// Tuning knob of the extend phase (see rtw_kernels.cu); RTW_REFILL_BELOW in the environment overrides.
+uint32_t g_refill_below = 0xFFFFFFFFu;
+uint32_t refill_below_default() {
+    if (g_refill_below == 0xFFFFFFFFu) {
+        const char* e = std::getenv("RTW_REFILL_BELOW");
+        g_refill_below = e ? (uint32_t)std::atoi(e) : 16u;
+    }
+    return g_refill_below;
+}
+
 MegaLaunch plan_mega(const rtw_scene* s, const RenderParams& P, int variant) {
     MegaLaunch L;
     L.block = RTW_MEGA_BLOCK;
     int occ = variant == 1 ? s->occ_strict : variant == 2 ? s->occ_count : s->occ_fast;
     if (occ < 1) occ = 1;
     L.grid = s->sm_count * occ;
+    L.stack_words = s->stack_words;
+    L.smem_bytes = s->smem_bytes;
+    L.refill_below = refill_below_default();
     L.tiles_x = (P.cam.width + 7u) / 8u;
     L.tiles_y = (P.row_count + 3u) / 4u;
     const uint64_t tiles = (uint64_t)L.tiles_x * L.tiles_y;
@@ -196,7 +223,7 @@ MegaLaunch plan_mega(const rtw_scene* s, const RenderParams& P, int variant) {
     if (want_chunks < 1) want_chunks = 1;
     if (want_chunks > P.sample_count) want_chunks = P.sample_count;
     uint32_t chunk = (uint32_t)((P.sample_count + want_chunks - 1) / want_chunks);
-    if (chunk > 64u) chunk = 64u;
+    if (chunk > 256u) chunk = 256u;
     if (chunk < 1u) chunk = 1u;
     L.chunk = chunk;
     L.n_chunks = (P.sample_count + chunk - 1u) / chunk;
@@ -206,12 +233,98 @@ MegaLaunch plan_mega(const rtw_scene* s, const RenderParams& P, int variant) {
     return L;
 }
 
+uint32_t env_u32(const char* name, uint32_t dflt) {
+    const char* e = std::getenv(name);
+    return e ? (uint32_t)std::strtoul(e, nullptr, 10) : dflt;
+}
+
+template <class T>
+int pool_alloc(rtw_scene* s, T** p, size_t n) {
+    void* q = nullptr;
+    CK(cudaMalloc(&q, n * sizeof(T)));
+    s->allocs.push_back(q);
+    s->info.device_bytes += n * sizeof(T);
+    *p = static_cast<T*>(q);
+    return RTW_OK;
+}
+
+int ensure_pool(rtw_scene* s) {
+    if (s->pool.capacity) return RTW_OK;
+    uint32_t cap = env_u32("RTW_WF_POOL", 1u << 21);
+    cap = std::max(cap, 4096u) & ~127u;
+    int rc;
+    if ((rc = pool_alloc(s, &s->pool.ray_o, cap)) || (rc = pool_alloc(s, &s->pool.ray_d, cap)) ||
+        (rc = pool_alloc(s, &s->pool.id, cap)) || (rc = pool_alloc(s, &s->pool.hit, cap)) ||
+        (rc = pool_alloc(s, &s->pool.thr, cap)) || (rc = pool_alloc(s, &s->pool.rad, cap)) ||
+        (rc = pool_alloc(s, &s->pool.queue[0], cap)) || (rc = pool_alloc(s, &s->pool.queue[1], cap))) return rc;
+    CK(cudaMalloc(&s->d_wc, sizeof(WfCounters)));
+    CK(cudaMallocHost(&s->h_wc, 4 * sizeof(WfCounters)));
+    for (auto& e : s->wf_ev) CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    CK(wf_extend_occupancy_fast(&s->occ_wf[0], s->smem_bytes));
+    CK(wf_extend_occupancy_strict(&s->occ_wf[1], s->smem_bytes));
+    CK(wf_extend_occupancy_count(&s->occ_wf[2], s->smem_bytes));
+    s->pool.capacity = cap;
+    return RTW_OK;
+}
+
+// The wavefront render: fill the pool, then extend + shade until every slot has run dry. The host
+// stays two batches of iterations ahead of the device and reads the queue length of finished
+// batches from pinned memory, so the call returns only when the frame is complete.
+int enqueue_wavefront(rtw_scene* s, const RenderParams& P, int variant, float* d_out, cudaStream_t st) {
+    int rc = ensure_pool(s);
+    if (rc) return rc;
+    WfLaunch L{};
+    L.tiles_x = (P.cam.width + 7u) / 8u;
+    L.tiles_y = (P.row_count + 3u) / 4u;
+    L.stack_words = s->stack_words;
+    L.smem_bytes = s->smem_bytes;
+    L.fetch_min = std::min(32u, std::max(1u, env_u32("RTW_WF_FETCH_MIN", 8u)));
+    L.extend_grid = s->sm_count * std::max(1, s->occ_wf[variant]);
+    L.shade_grid = (int)(s->pool.capacity / RTW_WF_SHADE_BLOCK);
+    WfCounters init{};
+    init.total_paths = 32ull * L.tiles_x * L.tiles_y * P.sample_count;
+    s->h_wc[0] = init;
+    CK(cudaMemcpyAsync(s->d_wc, &s->h_wc[0], sizeof(WfCounters), cudaMemcpyHostToDevice, st));
+    auto extend = [&](uint32_t cur) {
+        return variant == 1   ? launch_wf_extend_strict(s->d, P, s->pool, s->d_wc, s->d_ctr, cur, L, st)
+               : variant == 2 ? launch_wf_extend_count(s->d, P, s->pool, s->d_wc, s->d_ctr, cur, L, st)
+                              : launch_wf_extend_fast(s->d, P, s->pool, s->d_wc, s->d_ctr, cur, L, st);
+    };
+    auto shade = [&](uint32_t cur, int init_pass) {
+        return variant == 1   ? launch_wf_shade_strict(s->d, P, s->pool, s->d_wc, s->d_ctr, d_out, cur, init_pass, L, st)
+               : variant == 2 ? launch_wf_shade_count(s->d, P, s->pool, s->d_wc, s->d_ctr, d_out, cur, init_pass, L, st)
+                              : launch_wf_shade_fast(s->d, P, s->pool, s->d_wc, s->d_ctr, d_out, cur, init_pass, L, st);
+    };
+    CK(shade(1u, 1));                       // first fill: writes queue[0]
+    s->launches += 1;
+    const uint32_t batch = std::max(1u, env_u32("RTW_WF_BATCH", 8u));
+    uint32_t it = 0;
+    for (uint32_t k = 0;; ++k) {
+        for (uint32_t b = 0; b < batch; ++b, ++it) {
+            CK(extend(it & 1u));
+            CK(shade(it & 1u, 0));
+        }
+        s->launches += 2ull * batch;
+        // after `batch` iterations the live queue is queue[it & 1]
+        CK(cudaMemcpyAsync(&s->h_wc[k & 3u], s->d_wc, sizeof(WfCounters), cudaMemcpyDeviceToHost, st));
+        CK(cudaEventRecord(s->wf_ev[k & 3u], st));
+        if (k >= 2u) {
+            const uint32_t j = (k - 2u) & 3u;
+            CK(cudaEventSynchronize(s->wf_ev[j]));
+            const uint32_t live_q = ((k - 1u) * batch) & 1u;       // `it` after batch k-2
+            if (s->h_wc[j].n_queue[live_q] == 0u && s->h_wc[j].next_path >= s->h_wc[j].total_paths) break;
+        }
+    }
+    s->wf_paths = (uint64_t)P.cam.width * P.row_count * P.sample_count;
+    if (!first_hit_integrator(P.integrator) && P.depth < 1u) s->wf_paths = s->wf_paths;   // black frame, still counted
+    return RTW_OK;
+}
+
 // Enqueue one render on `st` into device buffer d_out (row_count*W*3 floats).
 int enqueue_render(rtw_scene* s, const rtw_camera* cam, const rtw_render_opts* o, float* d_out, cudaStream_t st) {
     RenderParams P; uint32_t total = 0; std::string err;
     int rc = make_render_params(cam, o, P, total, err);
     if (rc) return fail(rc, err);
-    if (o->flags & RTW_FLAG_WAVEFRONT) return fail(RTW_E_UNSUPPORTED, "wavefront pipeline not built in this version");
     const int variant = (o->flags & RTW_FLAG_STRICT_FP) ? 1 : (o->flags & RTW_FLAG_COUNT_WORK) ? 2 : 0;
     MegaLaunch L = plan_mega(s, P, variant);
     if ((uint64_t)L.tiles_x * L.tiles_y * L.n_chunks > 0xFFFFFFF0ull) return fail(RTW_E_UNSUPPORTED, "too many work items; shard the render");
@@ -220,11 +333,17 @@ int enqueue_render(rtw_scene* s, const rtw_camera* cam, const rtw_render_opts* o
     CK(cudaMemsetAsync(s->d_ctr, 0, sizeof(Counters), st));
     CK(cudaMemsetAsync(s->d_work, 0, sizeof(uint32_t), st));
     CK(cudaEventRecord(s->ev0, st));
-    CK(variant == 1   ? launch_mega_strict(s->d, P, d_out, s->d_ctr, s->d_work, L, st)
-       : variant == 2 ? launch_mega_count(s->d, P, d_out, s->d_ctr, s->d_work, L, st)
-                      : launch_mega_fast(s->d, P, d_out, s->d_ctr, s->d_work, L, st));
+    s->last_wavefront = (o->flags & RTW_FLAG_WAVEFRONT) != 0;
+    if (s->last_wavefront) {
+        s->launches = 0;
+        if ((rc = enqueue_wavefront(s, P, variant, d_out, st))) return rc;
+    } else {
+        CK(variant == 1   ? launch_mega_strict(s->d, P, d_out, s->d_ctr, s->d_work, L, st)
+           : variant == 2 ? launch_mega_count(s->d, P, d_out, s->d_ctr, s->d_work, L, st)
+                          : launch_mega_fast(s->d, P, d_out, s->d_ctr, s->d_work, L, st));
+        s->launches = 1;
+    }
     CK(cudaEventRecord(s->ev1, st));
-    s->launches = 1;
     if (o->output == RTW_OUT_RESOLVED) {
         resolve_kernel<<<grid_for(n_values, 256), 256, 0, st>>>(d_out, n_values, (float)total, 1.0f / o->gamma);
         CK(cudaGetLastError());
@@ -303,9 +422,11 @@ int rtw_scene_create(const rtw_scene_desc* desc, int device, rtw_scene** out) {
     if ((rc = upload_scene(s, hs))) return bail(rc);
     cudaError_t ce;
     if ((ce = cudaDeviceGetAttribute(&s->sm_count, cudaDevAttrMultiProcessorCount, device)) != cudaSuccess) return bail(cuda_fail(ce, "sm count"));
-    if ((ce = mega_occupancy_fast(&s->occ_fast)) != cudaSuccess) return bail(cuda_fail(ce, "occupancy(fast)"));
-    if ((ce = mega_occupancy_strict(&s->occ_strict)) != cudaSuccess) return bail(cuda_fail(ce, "occupancy(strict)"));
-    if ((ce = mega_occupancy_count(&s->occ_count)) != cudaSuccess) return bail(cuda_fail(ce, "occupancy(count)"));
+    s->stack_words = stack_words(hs.top_depth, hs.inner_depth);
+    s->smem_bytes = (size_t)s->stack_words * RTW_MEGA_BLOCK * sizeof(uint32_t);
+    if ((ce = mega_occupancy_fast(&s->occ_fast, s->smem_bytes)) != cudaSuccess) return bail(cuda_fail(ce, "occupancy(fast)"));
+    if ((ce = mega_occupancy_strict(&s->occ_strict, s->smem_bytes)) != cudaSuccess) return bail(cuda_fail(ce, "occupancy(strict)"));
+    if ((ce = mega_occupancy_count(&s->occ_count, s->smem_bytes)) != cudaSuccess) return bail(cuda_fail(ce, "occupancy(count)"));
     if ((ce = cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking)) != cudaSuccess) return bail(cuda_fail(ce, "stream"));
     if ((ce = cudaEventCreate(&s->ev0)) != cudaSuccess || (ce = cudaEventCreate(&s->ev1)) != cudaSuccess ||
         (ce = cudaEventCreate(&s->ev2)) != cudaSuccess) return bail(cuda_fail(ce, "events"));
@@ -376,7 +497,7 @@ int rtw_get_stats(rtw_scene* scene, rtw_stats* out) {
     if (!scene->have_stats) return RTW_OK;
     CK(cudaSetDevice(scene->device));
     CK(cudaEventSynchronize(scene->ev2));
-    out->paths = scene->h_ctr->paths; out->rays = scene->h_ctr->rays; out->nan_paths = scene->h_ctr->nan_paths;
+    out->paths = scene->last_wavefront ? scene->wf_paths : scene->h_ctr->paths; out->rays = scene->h_ctr->rays; out->nan_paths = scene->h_ctr->nan_paths;
     out->gpu_launches = scene->launches;
     out->nodes = scene->h_ctr->nodes; out->sphere_tests = scene->h_ctr->spheres; out->quad_tests = scene->h_ctr->quads;
     out->instance_tests = scene->h_ctr->instances; out->hits = scene->h_ctr->hits;

@@ -203,13 +203,6 @@ RTW_HD V3 random_unit_vec(PathRng& rng) {
         if (p.x * p.x + p.y * p.y + p.z * p.z <= 1.0f) return unit(p);
     }
 }
-RTW_HD V3 random_unit_vec_stream(const PathRng& rng, uint32_t base_block, uint32_t stream) {
-    for (uint32_t turn = 0;; ++turn) {
-        float4 r = rng.at(base_block | (turn + 1u), stream);
-        V3 p = v3(r.x * (1.0f - -1.0f) + -1.0f, r.y * (1.0f - -1.0f) + -1.0f, r.z * (1.0f - -1.0f) + -1.0f);
-        if (p.x * p.x + p.y * p.y + p.z * p.z <= 1.0f) return unit(p);
-    }
-}
 // vec3.rs:240-254: two candidate points per block
 RTW_HD V3 random_in_unit_disk(PathRng& rng) {
     for (;;) {

@@ -25,6 +25,7 @@ struct HostScene {
     Level top;
     float background[3];
     rtw_scene_info info;
+    uint32_t top_depth = 0, inner_depth = 0;   // deepest node chain of the top level / of any instance (-> stack_words)
 
     // A Scene whose pointers address the vectors above (host memory): what the CPU-side unit
     // tests of the traversal code walk. The product uploads the same arrays to the device.

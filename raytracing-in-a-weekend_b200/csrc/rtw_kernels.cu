@@ -2,13 +2,19 @@
 // as an iterative loop, BVH traversal, material scatter, texture sampling and accumulation.
 // Replaces render_row / async_render (Rust/src/viewport.rs:215-305) and everything below them.
 //
-// Megakernel with path regeneration: one warp owns an 8x4 pixel tile x a chunk of samples; every
-// lane carries one path in registers and, the moment its path ends (miss, depth exhausted), starts
-// its pixel's next sample, so all lanes stay in the extend/shade loop until the item is done.
-// Scene data (BVH nodes 64 B, primitives 16-64 B) is read through the read-only path (LDG.128,
-// L1/L2 resident: the whole C5 scene is < 0.5 MB); Perlin tables are staged in shared memory;
-// image textures go through texture objects. Per-pixel sums leave the SM as three f32 REDs per
-// lane per item. No tensor cores: nothing here is a contraction.
+// Persistent-lane megakernel: a warp owns an 8x4 pixel tile x a chunk of samples (32*chunk paths).
+// Every lane carries one path in registers; the warp alternates between three warp-synchronous
+// phases so that the 32 lanes always execute the same code:
+//   refill  lanes without a path take the item's next (pixel, sample) and generate its camera ray
+//   extend  all lanes walk the two-level BVH in one loop (rtw_trace.h): lanes on a node step
+//           together, then leaves / instance entry / exit; the loop is left early when fewer than
+//           `refill_below` lanes still walk and others wait to be shaded (their state stays put)
+//   shade   lanes whose search ended evaluate the Hit, scatter (next segment) or finish the path
+// The traversal stack is a per-thread column in shared memory; scene data (BVH nodes 64 B,
+// primitives 16-64 B) is read through the read-only path (LDG.128, L1/L2 resident: the whole C5
+// scene is < 0.5 MB); Perlin tables are staged in shared memory; image textures go through
+// texture objects. Finished paths add into the warp's tile sums in shared memory; the tile leaves
+// the SM as three f32 REDs per pixel per item. No tensor cores: nothing here is a contraction.
 //
 // Compiled three times (see rtw_kernels.h): RTW_VARIANT = fast | strict | count.
 #include "rtw_kernels.h"
@@ -31,8 +37,10 @@ __device__ __forceinline__ unsigned long long warp_sum_u64(unsigned long long v)
 __global__ void __launch_bounds__(RTW_MEGA_BLOCK)
 mega_kernel(const Scene sc, const RenderParams P, float* __restrict__ sum, Counters* __restrict__ ctr,
             uint32_t* __restrict__ work, const MegaLaunch L) {
-    // ---- stage the Perlin tables (texture.rs:63-69) in shared memory
+    extern __shared__ uint32_t s_stack[];                 // [stack_words][RTW_MEGA_BLOCK]
     __shared__ Noise s_noise[RTW_SMEM_NOISES];
+    __shared__ float s_acc[RTW_MEGA_BLOCK / 32][3][32];   // per warp: the tile's 32 pixel sums
+    // ---- stage the Perlin tables (texture.rs:63-69) in shared memory
     const Noise* nt = sc.noises;
     if (sc.n_noises > 0 && sc.n_noises <= RTW_SMEM_NOISES) {
         const uint32_t* src = reinterpret_cast<const uint32_t*>(sc.noises);
@@ -43,8 +51,11 @@ mega_kernel(const Scene sc, const RenderParams P, float* __restrict__ sum, Count
     }
     __syncthreads();
 
-    const uint32_t lane = threadIdx.x & 31u;
+    const uint32_t FULL = 0xFFFFFFFFu;
+    const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    const uint32_t lt_mask = (1u << lane) - 1u;
     const uint32_t W = P.cam.width;
+    Stack S; S.base = s_stack + threadIdx.x; S.stride = RTW_MEGA_BLOCK;
     uint32_t n_paths = 0, n_rays = 0, n_nan = 0;
 #if defined(RTW_COUNT_WORK)
     Work wk = {0u, 0u, 0u, 0u, 0u};
@@ -56,38 +67,83 @@ mega_kernel(const Scene sc, const RenderParams P, float* __restrict__ sum, Count
     for (;;) {
         uint32_t item = 0;
         if (lane == 0) item = atomicAdd(work, 1u);
-        item = __shfl_sync(0xFFFFFFFFu, item, 0);
+        item = __shfl_sync(FULL, item, 0);
         if (item >= L.n_items) break;
         const uint32_t chunk = item % L.n_chunks, tile = item / L.n_chunks;
         const uint32_t tx = tile % L.tiles_x, ty = tile / L.tiles_x;
-        const uint32_t i = tx * 8u + (lane & 7u), jr = ty * 4u + (lane >> 3);
-        const bool valid = i < W && jr < P.row_count;
-        const uint32_t j = P.row_begin + jr;
-        uint32_t s = P.sample_begin + chunk * L.chunk;
-        const uint32_t s_end = min(s + L.chunk, P.sample_begin + P.sample_count);
-        V3 acc = v3(0.f, 0.f, 0.f);
-        if (valid) {
-            Path path;
-            bool alive = false;
-            for (;;) {
-                if (!alive) {
-                    if (s >= s_end) break;
-                    generate(P, i, j, s, path);
-                    ++s;
-                    alive = true;
-                }
-                if (path_step(sc, nt, P, path, n_rays, wp)) {
-                    V3 c = path_result(path);
-                    if (!finite3(c)) ++n_nan;
-                    acc = acc + c;
-                    ++n_paths;
-                    alive = false;
+        const uint32_t s0 = P.sample_begin + chunk * L.chunk;
+        const uint32_t ns = min(L.chunk, P.sample_begin + P.sample_count - s0);
+        const uint32_t n_total = ns * 32u;                // paths of this item, handed out in order
+        uint32_t next = 0;                                // warp-uniform
+        s_acc[warp][0][lane] = 0.f; s_acc[warp][1][lane] = 0.f; s_acc[warp][2][lane] = 0.f;
+        __syncwarp();
+
+        Path path;
+        Trav T;
+        T.cur = CUR_DONE;
+        TraceCtx cx = path_ctx(sc, P, path, wp);
+        uint32_t pix = 0;
+        bool alive = false;
+        for (;;) {
+            // ---- refill: every free lane takes the item's next path (generate, viewport.rs:287-298)
+            const uint32_t want = __ballot_sync(FULL, !alive);
+            if (want != 0u && next < n_total) {
+                const uint32_t n = next + __popc(want & lt_mask);
+                next += __popc(want);
+                if (!alive && n < n_total) {
+                    pix = n & 31u;
+                    const uint32_t i = tx * 8u + (pix & 7u), jr = ty * 4u + (pix >> 3);
+                    if (i < W && jr < P.row_count) {
+                        generate(P, i, P.row_begin + jr, s0 + (n >> 5), path);
+                        alive = true;
+                        cx = path_ctx(sc, P, path, wp);
+                        if (!segment_begin(cx, P, path, T, S)) T.cur = CUR_DONE;   // depth 0: nothing to trace
+                        else ++n_rays;
+                    }
                 }
             }
-            float* px = sum + ((size_t)jr * W + i) * 3u;
-            atomicAdd(px + 0, acc.x);
-            atomicAdd(px + 1, acc.y);
-            atomicAdd(px + 2, acc.z);
+            if (!__any_sync(FULL, alive)) {
+                if (next >= n_total) break;
+                continue;
+            }
+            // ---- extend: warp-synchronous walk; all lanes on a node step together, then the rest
+            for (;;) {
+                const uint32_t walking = __ballot_sync(FULL, T.cur != CUR_DONE);
+                if (walking == 0u) break;
+                if ((uint32_t)__popc(walking) < L.refill_below && next < n_total &&
+                    __any_sync(FULL, alive && T.cur == CUR_DONE)) break;
+                if (T.cur < NODE_LIMIT) trav_step_node(cx, T, S);
+                if (T.cur >= NODE_LIMIT && T.cur != CUR_DONE) trav_step_other(cx, path.ray.time, T, S);
+            }
+            // ---- shade / scatter every lane whose search is over
+            if (alive && T.cur == CUR_DONE) {
+                bool finished = true;
+                if (first_hit_integrator(P.integrator) || path.depth_left >= 1u) finished = segment_end(cx, nt, P, path, T);
+                if (!finished) {
+                    cx.bounce = P.depth - path.depth_left;
+                    if (segment_begin(cx, P, path, T, S)) ++n_rays; else finished = true;
+                }
+                if (finished) {
+                    V3 c = path_result(path);
+                    if (!finite3(c)) ++n_nan;
+                    atomicAdd(&s_acc[warp][0][pix], c.x);
+                    atomicAdd(&s_acc[warp][1][pix], c.y);
+                    atomicAdd(&s_acc[warp][2][pix], c.z);
+                    ++n_paths;
+                    alive = false;
+                    T.cur = CUR_DONE;
+                }
+            }
+        }
+        __syncwarp();
+        {
+            const uint32_t i = tx * 8u + (lane & 7u), jr = ty * 4u + (lane >> 3);
+            if (i < W && jr < P.row_count) {
+                float* px = sum + ((size_t)jr * W + i) * 3u;
+                atomicAdd(px + 0, s_acc[warp][0][lane]);
+                atomicAdd(px + 1, s_acc[warp][1][lane]);
+                atomicAdd(px + 2, s_acc[warp][2][lane]);
+            }
         }
         __syncwarp();
     }
@@ -107,19 +163,213 @@ mega_kernel(const Scene sc, const RenderParams P, float* __restrict__ sum, Count
 #endif
 }
 
+// =====================================================================================
+// Wavefront pipeline (see rtw_kernels.h): extend + shade over a pool of path slots in HBM.
+// =====================================================================================
+
+// extend: Scene::collision_normal for every ray of queue[cur]. Persistent warps; a lane whose
+// search is over stores its hit and, once `fetch_min` lanes of the warp are idle, the idle lanes
+// take the next rays of the queue (one atomic per fetch), so the walk loop stays populated.
+__global__ void __launch_bounds__(RTW_WF_BLOCK)
+wf_extend_kernel(const Scene sc, const RenderParams P, const WfPool pool, WfCounters* __restrict__ wc,
+                 Counters* __restrict__ ctr, const uint32_t cur, const WfLaunch L) {
+    extern __shared__ uint32_t s_stack[];                 // [stack_words][RTW_WF_BLOCK]
+    const uint32_t FULL = 0xFFFFFFFFu;
+    const uint32_t lane = threadIdx.x & 31u;
+    const uint32_t lt_mask = (1u << lane) - 1u;
+    Stack S; S.base = s_stack + threadIdx.x; S.stride = RTW_WF_BLOCK;
+    if (blockIdx.x == 0 && threadIdx.x == 0) wc->n_queue[cur ^ 1u] = 0u;   // shade of this iteration appends there
+    const uint32_t n = wc->n_queue[cur];
+    const uint32_t* __restrict__ q = pool.queue[cur];
+#if defined(RTW_COUNT_WORK)
+    Work wk = {0u, 0u, 0u, 0u, 0u};
+    Work* const wp = &wk;
+#else
+    Work* const wp = nullptr;
+#endif
+    TraceCtx cx; cx.sc = &sc; cx.k0 = P.k0; cx.k1 = P.k1; cx.pixel = 0u; cx.sample = 0u; cx.bounce = 0u;
+    cx.mint = P.mint; cx.maxt = P.maxt; cx.work = wp;
+    Trav T; T.cur = CUR_DONE;
+    uint32_t slot = 0u;
+    float time = 0.f;
+    bool busy = false, more = n > 0u;
+    for (;;) {
+        const uint32_t idle = __ballot_sync(FULL, !busy);
+        if (idle == FULL && !more) break;
+        if (more && (uint32_t)__popc(idle) >= L.fetch_min) {
+            const uint32_t cnt = __popc(idle);
+            uint32_t base = 0u;
+            if (lane == 0u) base = atomicAdd(&wc->head, cnt);
+            base = __shfl_sync(FULL, base, 0);
+            more = base + cnt < n;
+            const uint32_t my = base + __popc(idle & lt_mask);
+            if (!busy && my < n) {
+                slot = q[my];
+                const float4 ro = pool.ray_o[slot], rd = pool.ray_d[slot];
+                const uint2 id = pool.id[slot];
+                Ray r; r.o = v3(ro.x, ro.y, ro.z); r.d = v3(rd.x, rd.y, rd.z); r.time = ro.w;
+                time = ro.w;
+                cx.pixel = id.x; cx.sample = id.y; cx.bounce = f2u(rd.w);
+                trav_begin(cx, r, T, S);
+                busy = true;
+            }
+        }
+        if (T.cur < NODE_LIMIT) trav_step_node(cx, T, S);
+        if (T.cur >= NODE_LIMIT && T.cur != CUR_DONE) trav_step_other(cx, time, T, S);
+        if (busy && T.cur == CUR_DONE) {
+            pool.hit[slot] = make_uint4(f2u(T.t), T.ref, T.inner, 0u);
+            busy = false;
+        }
+    }
+#if defined(RTW_COUNT_WORK)
+    unsigned long long w0 = warp_sum_u64(wk.nodes), w1 = warp_sum_u64(wk.spheres), w2 = warp_sum_u64(wk.quads),
+                       w3 = warp_sum_u64(wk.instances);
+    if (lane == 0) {
+        atomicAdd(&ctr->nodes, w0); atomicAdd(&ctr->spheres, w1); atomicAdd(&ctr->quads, w2); atomicAdd(&ctr->instances, w3);
+    }
+#endif
+}
+
+// shade: one thread per entry of queue[cur] (or, with init != 0, per pool slot: first fill).
+__global__ void __launch_bounds__(RTW_WF_SHADE_BLOCK)
+wf_shade_kernel(const Scene sc, const RenderParams P, const WfPool pool, WfCounters* __restrict__ wc,
+                Counters* __restrict__ ctr, float* __restrict__ sum, const uint32_t cur, const int init, const WfLaunch L) {
+    const uint32_t FULL = 0xFFFFFFFFu;
+    const uint32_t lane = threadIdx.x & 31u;
+    const uint32_t lt_mask = (1u << lane) - 1u;
+    const uint32_t e = blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t n = init ? pool.capacity : wc->n_queue[cur];
+    if ((blockIdx.x * blockDim.x) >= n) return;            // whole block beyond the queue
+    if (e == 0u) {
+        wc->head = 0u;                                      // this iteration's extend is over
+        wc->iterations += 1ull;
+        if (!init) atomicAdd(&ctr->rays, (unsigned long long)n);
+    }
+    const bool have = e < n;
+    const uint32_t slot = have ? (init ? e : pool.queue[cur][e]) : 0u;
+    const uint32_t W = P.cam.width;
+#if defined(RTW_COUNT_WORK)
+    Work wk = {0u, 0u, 0u, 0u, 0u};
+    Work* const wp = &wk;
+#else
+    Work* const wp = nullptr;
+#endif
+    Path path;
+    bool alive = false;
+    uint32_t n_nan = 0u;
+    if (have && !init) {
+        const float4 ro = pool.ray_o[slot], rd = pool.ray_d[slot];
+        const uint2 id = pool.id[slot];
+        const uint4 hit = pool.hit[slot];
+        const float4 thr = pool.thr[slot], rad = pool.rad[slot];
+        path.ray.time = ro.w;
+        path.thr = v3(thr.x, thr.y, thr.z); path.rad = v3(rad.x, rad.y, rad.z);
+        path.pixel = id.x; path.sample = id.y; path.block = f2u(thr.w);
+        const uint32_t dl = f2u(rad.w);
+        path.depth_left = dl & 0x7FFFFFFFu; path.poison = (dl >> 31) != 0u;
+        Trav T;
+        T.o = v3(ro.x, ro.y, ro.z); T.d = v3(rd.x, rd.y, rd.z);
+        T.t = u2f(hit.x); T.ref = hit.y; T.inner = hit.z;
+        TraceCtx cx = path_ctx(sc, P, path, wp);
+        bool finished = segment_end(cx, sc.noises, P, path, T);
+        if (!finished && path.depth_left < 1u) finished = true;   // ray_color.rs:14-16: the next call returns black
+        if (finished) {
+            V3 c = path_result(path);
+            if (!finite3(c)) ++n_nan;
+            float* px = sum + ((size_t)path.pixel - (size_t)P.row_begin * W) * 3u;
+            atomicAdd(px + 0, c.x); atomicAdd(px + 1, c.y); atomicAdd(px + 2, c.z);
+        } else {
+            alive = true;
+        }
+    }
+    // ---- regeneration: free slots take the next camera samples, tile-major so that primary rays of a warp stay coherent
+    bool need = have && !alive;
+    const unsigned long long total = wc->total_paths;
+    const bool path_dead_on_arrival = !first_hit_integrator(P.integrator) && P.depth < 1u;
+    for (;;) {
+        const uint32_t m = __ballot_sync(FULL, need);
+        if (m == 0u) break;
+        unsigned long long base = 0ull;
+        if (lane == 0u) base = atomicAdd(&wc->next_path, (unsigned long long)__popc(m));
+        base = __shfl_sync(FULL, base, 0);
+        if (base >= total) break;
+        if (need) {
+            const unsigned long long k = base + __popc(m & lt_mask);
+            if (k >= total) { need = false; }
+            else {
+                const uint32_t pix = (uint32_t)(k & 31ull);
+                const unsigned long long g = k >> 5;
+                const uint32_t tile = (uint32_t)(g / P.sample_count), s = P.sample_begin + (uint32_t)(g % P.sample_count);
+                const uint32_t tx = tile % L.tiles_x, ty = tile / L.tiles_x;
+                const uint32_t i = tx * 8u + (pix & 7u), jr = ty * 4u + (pix >> 3);
+                if (i < W && jr < P.row_count && !path_dead_on_arrival) {
+                    generate(P, i, P.row_begin + jr, s, path);
+                    alive = true; need = false;
+                }
+            }
+        }
+    }
+    if (alive) {
+        pool.ray_o[slot] = make_float4(path.ray.o.x, path.ray.o.y, path.ray.o.z, path.ray.time);
+        pool.ray_d[slot] = make_float4(path.ray.d.x, path.ray.d.y, path.ray.d.z, u2f(P.depth - path.depth_left));
+        pool.id[slot] = make_uint2(path.pixel, path.sample);
+        pool.thr[slot] = make_float4(path.thr.x, path.thr.y, path.thr.z, u2f(path.block));
+        pool.rad[slot] = make_float4(path.rad.x, path.rad.y, path.rad.z,
+                                     u2f(path.depth_left | (path.poison ? 0x80000000u : 0u)));
+    }
+    const uint32_t live = __ballot_sync(FULL, alive);
+    if (live != 0u) {
+        uint32_t base = 0u;
+        if (lane == 0u) base = atomicAdd(&wc->n_queue[cur ^ 1u], (uint32_t)__popc(live));
+        base = __shfl_sync(FULL, base, 0);
+        if (alive) pool.queue[cur ^ 1u][base + __popc(live & lt_mask)] = slot;
+    }
+    if (__any_sync(FULL, n_nan != 0u)) {
+        unsigned long long nn = warp_sum_u64(n_nan);
+        if (lane == 0u) atomicAdd(&ctr->nan_paths, nn);
+    }
+#if defined(RTW_COUNT_WORK)
+    unsigned long long w4 = warp_sum_u64(wk.hits);
+    if (lane == 0 && w4) atomicAdd(&ctr->hits, w4);
+#endif
+}
+
 }  // namespace variant
 
 #define RTW_FN(name) RTW_CAT(RTW_CAT(name, _), RTW_VARIANT)
 
 cudaError_t RTW_FN(launch_mega)(const Scene& sc, const RenderParams& P, float* d_sum, Counters* d_ctr,
                                 uint32_t* d_work, const MegaLaunch& L, cudaStream_t st) {
-    RTW_CAT(variant_, RTW_VARIANT)::mega_kernel<<<L.grid, L.block, 0, st>>>(sc, P, d_sum, d_ctr, d_work, L);
+    RTW_CAT(variant_, RTW_VARIANT)::mega_kernel<<<L.grid, L.block, L.smem_bytes, st>>>(sc, P, d_sum, d_ctr, d_work, L);
     return cudaGetLastError();
 }
 
-cudaError_t RTW_FN(mega_occupancy)(int* blocks_per_sm) {
+cudaError_t RTW_FN(launch_wf_extend)(const Scene& sc, const RenderParams& P, const WfPool& pool, WfCounters* d_wc,
+                                     Counters* d_ctr, uint32_t cur, const WfLaunch& L, cudaStream_t st) {
+    RTW_CAT(variant_, RTW_VARIANT)::wf_extend_kernel<<<L.extend_grid, RTW_WF_BLOCK, L.smem_bytes, st>>>(sc, P, pool, d_wc, d_ctr, cur, L);
+    return cudaGetLastError();
+}
+
+cudaError_t RTW_FN(launch_wf_shade)(const Scene& sc, const RenderParams& P, const WfPool& pool, WfCounters* d_wc,
+                                    Counters* d_ctr, float* d_sum, uint32_t cur, int init, const WfLaunch& L, cudaStream_t st) {
+    RTW_CAT(variant_, RTW_VARIANT)::wf_shade_kernel<<<L.shade_grid, RTW_WF_SHADE_BLOCK, 0, st>>>(sc, P, pool, d_wc, d_ctr, d_sum, cur, init, L);
+    return cudaGetLastError();
+}
+
+cudaError_t RTW_FN(wf_extend_occupancy)(int* blocks_per_sm, size_t smem_bytes) {
+    cudaError_t e = cudaFuncSetAttribute(RTW_CAT(variant_, RTW_VARIANT)::wf_extend_kernel,
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes);
+    if (e != cudaSuccess) return e;
+    return cudaOccupancyMaxActiveBlocksPerMultiprocessor(blocks_per_sm, RTW_CAT(variant_, RTW_VARIANT)::wf_extend_kernel,
+                                                         RTW_WF_BLOCK, smem_bytes);
+}
+
+cudaError_t RTW_FN(mega_occupancy)(int* blocks_per_sm, size_t smem_bytes) {
+    cudaError_t e = cudaFuncSetAttribute(RTW_CAT(variant_, RTW_VARIANT)::mega_kernel,
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes);
+    if (e != cudaSuccess) return e;
     return cudaOccupancyMaxActiveBlocksPerMultiprocessor(blocks_per_sm, RTW_CAT(variant_, RTW_VARIANT)::mega_kernel,
-                                                         RTW_MEGA_BLOCK, 0);
+                                                         RTW_MEGA_BLOCK, smem_bytes);
 }
 
 }  // namespace rtw

@@ -1,8 +1,8 @@
-// rtw_kernels.h — launch interface of rtw_kernels.cu. That file is compiled twice:
+// rtw_kernels.h — launch interface of rtw_kernels.cu. That file is compiled three times:
 //   fast   : nvcc default (a*b+c contracts to FFMA)             -> launch_*_fast
 //   strict : -fmad=false -DRTW_STRICT_FP (rustc-like arithmetic) -> launch_*_strict
 //   count  : fast + -DRTW_COUNT_WORK (node/primitive test counters) -> launch_*_count
-// selected per render call by RTW_FLAG_STRICT_FP.
+// selected per render call by RTW_FLAG_STRICT_FP / RTW_FLAG_COUNT_WORK.
 #pragma once
 #include <cuda_runtime.h>
 #include "rtw_shade.h"
@@ -14,15 +14,52 @@ struct Counters {
     unsigned long long nodes, spheres, quads, instances, hits;   // only from the RTW_COUNT_WORK build
 };
 
-// Work decomposition of the path-regenerating megakernel: an item is one 8x4 pixel tile x one
-// chunk of consecutive samples; warps pull items from a global counter.
+// Work decomposition of the persistent-lane megakernel: an item is one 8x4 pixel tile x one chunk
+// of consecutive samples (32 * chunk paths); warps pull items from a global counter and hand the
+// item's paths to whichever lane is free.
 struct MegaLaunch {
     uint32_t chunk;        // samples per item
     uint32_t n_chunks;
     uint32_t tiles_x, tiles_y;
     uint32_t n_items;
+    uint32_t stack_words;  // per-thread traversal stack depth (stack_words(), rtw_trace.h)
+    uint32_t refill_below; // leave the traversal loop to shade/refill when fewer lanes than this still traverse
     int grid, block;
+    size_t smem_bytes;     // dynamic shared memory: stack_words * block * 4
 };
+
+// ---- wavefront pipeline (RTW_FLAG_WAVEFRONT): a pool of path slots in HBM, SoA, and two queues of
+// slot indices. One iteration = extend (persistent warps pull rays from queue[cur], walk the BVH,
+// store the closest hit) + shade (one thread per queue entry: miss / Hit / scatter; finished paths
+// add their radiance to the frame and the slot takes the next camera sample; live slots are
+// appended to queue[cur^1] with one warp-aggregated atomic).
+struct WfPool {
+    float4* ray_o;       // origin.xyz, time
+    float4* ray_d;       // direction.xyz, bits(bounce)
+    uint2*  id;          // pixel index, sample index (Philox counter words 0/1)
+    uint4*  hit;         // bits(t), ref, inner, 0       (extend -> shade)
+    float4* thr;         // throughput.xyz, bits(next Philox block)
+    float4* rad;         // radiance.xyz, bits(depth_left | poison << 31)
+    uint32_t* queue[2];
+    uint32_t capacity;
+};
+struct WfCounters {
+    uint32_t n_queue[2];             // entries of queue[k]
+    uint32_t head;                   // extend's fetch cursor into queue[cur]
+    uint32_t pad;
+    unsigned long long next_path;    // next camera sample to hand out (tile-major order)
+    unsigned long long total_paths;  // 32 * tiles * samples of this render (edge-tile padding included)
+    unsigned long long iterations;
+};
+struct WfLaunch {
+    uint32_t tiles_x, tiles_y;
+    uint32_t stack_words;
+    uint32_t fetch_min;              // extend fetches new rays when at least this many lanes are idle
+    int extend_grid, shade_grid;
+    size_t smem_bytes;
+};
+#define RTW_WF_BLOCK 128
+#define RTW_WF_SHADE_BLOCK 128
 
 #define RTW_MEGA_BLOCK 128
 #define RTW_SMEM_NOISES 2
@@ -30,7 +67,13 @@ struct MegaLaunch {
 #define RTW_DECLARE_VARIANT(SUFFIX)                                                                          \
     cudaError_t launch_mega_##SUFFIX(const Scene& sc, const RenderParams& P, float* d_sum, Counters* d_ctr,  \
                                      uint32_t* d_work, const MegaLaunch& L, cudaStream_t st);                \
-    cudaError_t mega_occupancy_##SUFFIX(int* blocks_per_sm);
+    cudaError_t mega_occupancy_##SUFFIX(int* blocks_per_sm, size_t smem_bytes);                              \
+    cudaError_t launch_wf_extend_##SUFFIX(const Scene& sc, const RenderParams& P, const WfPool& pool, WfCounters* d_wc,   \
+                                          Counters* d_ctr, uint32_t cur, const WfLaunch& L, cudaStream_t st);            \
+    cudaError_t launch_wf_shade_##SUFFIX(const Scene& sc, const RenderParams& P, const WfPool& pool, WfCounters* d_wc,    \
+                                         Counters* d_ctr, float* d_sum, uint32_t cur, int init, const WfLaunch& L,       \
+                                         cudaStream_t st);                                                               \
+    cudaError_t wf_extend_occupancy_##SUFFIX(int* blocks_per_sm, size_t smem_bytes);
 
 RTW_DECLARE_VARIANT(fast)
 RTW_DECLARE_VARIANT(strict)

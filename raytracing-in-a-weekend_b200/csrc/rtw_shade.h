@@ -189,7 +189,7 @@ RTW_HD void eval_hit(const TraceCtx& cx, const Noise* nt, const Best& b, const R
         if (distance >= 0.0f) {
             // scatter inside the medium: entry-face t, col_mod and material are kept (instance.rs:295-299)
             h.point = h.point + l.d * distance;
-            h.normal = random_unit_vec_stream(*cx.rng, cx.bounce << 16, 1u + in.index);
+            h.normal = random_unit_vec_stream(cx, cx.bounce << 16, 1u + in.index);
         }
     }
     if (!(in.flags & INST_ROT_IDENTITY)) {
@@ -251,29 +251,37 @@ RTW_HD V3 sky_gradient(V3 d) {   // ray_color.rs:38-40
     return v3((1.0f - t) + t * 0.5f, (1.0f - t) + t * 0.7f, 1.0f);
 }
 
-// One path in flight.
+// One path in flight. The Philox key lives in RenderParams (uniform); the counter here.
 struct Path {
-    Ray ray;
+    Ray ray;         // the segment about to be traced (dead while a Trav carries it)
     V3 thr, rad;
-    PathRng rng;
-    uint32_t depth_left, bounce;
+    uint32_t pixel, sample, block;   // Philox counter words 0/1 and the next stream-0 block
+    uint32_t depth_left;
     bool poison;     // pdf == 0 -> colour*0/0 = NaN all the way up
 };
+RTW_HD PathRng path_rng(const RenderParams& P, const Path& p) {
+    PathRng r; r.k0 = P.k0; r.k1 = P.k1; r.pixel = p.pixel; r.sample = p.sample; r.block = p.block; return r;
+}
+RTW_HD TraceCtx path_ctx(const Scene& sc, const RenderParams& P, const Path& p, Work* work) {
+    TraceCtx cx; cx.sc = &sc; cx.k0 = P.k0; cx.k1 = P.k1; cx.pixel = p.pixel; cx.sample = p.sample;
+    cx.bounce = P.depth - p.depth_left; cx.mint = P.mint; cx.maxt = P.maxt; cx.work = work;
+    return cx;
+}
 
 // Loop bodies of render_row (viewport.rs:287-300), Viewport::render (:455-470) and
 // render_no_rand (:502-508): the camera ray of sample `s` of pixel (i, j).
 RTW_HD void generate(const RenderParams& P, uint32_t i, uint32_t j, uint32_t s, Path& p) {
-    p.rng.k0 = P.k0; p.rng.k1 = P.k1;
-    p.rng.pixel = j * P.cam.width + i; p.rng.sample = s; p.rng.block = 0u;
+    p.pixel = j * P.cam.width + i; p.sample = s; p.block = 0u;
+    PathRng rng = path_rng(P, p);
     V3 origin = ld3(P.cam.origin), p00 = ld3(P.cam.pixel00), du = ld3(P.cam.delta_u), dv = ld3(P.cam.delta_v);
     if (P.mode == RTW_MODE_NO_RAND) {
         p.ray.o = origin;
         p.ray.d = p00 + du * (float)i + dv * (float)j;
         p.ray.time = 0.0f;
     } else {
-        float4 c = p.rng.next4();
+        float4 c = rng.next4();
         V3 rp = v3(0.f, 0.f, 0.f);
-        if (P.cam.lens_radius != 0.0f) rp = random_in_unit_disk(p.rng);
+        if (P.cam.lens_radius != 0.0f) rp = random_in_unit_disk(rng);
         p.ray.o = origin + (ld3(P.cam.u) * rp.x + ld3(P.cam.v) * rp.y) * P.cam.lens_radius;
         if (P.mode == RTW_MODE_RANDOM) {
             p.ray.d = p00 + du * ((float)i + c.x) + dv * ((float)j + c.y);
@@ -285,32 +293,40 @@ RTW_HD void generate(const RenderParams& P, uint32_t i, uint32_t j, uint32_t s, 
             p.ray.time = 0.0f;
         }
     }
+    p.block = rng.block;
     p.thr = v3(1.f, 1.f, 1.f); p.rad = v3(0.f, 0.f, 0.f);
-    p.depth_left = P.depth; p.bounce = 0u; p.poison = false;
+    p.depth_left = P.depth; p.poison = false;
 }
 
-// One segment of one path: extend + shade. Returns true when the path is finished (p.rad final).
-// `rays` counts Scene::collision_normal equivalents.
-RTW_HD bool path_step(const Scene& sc, const Noise* nt, const RenderParams& P, Path& p, uint32_t& rays,
-                      Work* work = nullptr) {
+RTW_HD bool first_hit_integrator(uint32_t ig) { return ig == RTW_INT_NORMAL || ig == RTW_INT_ALBEDO; }
+
+// A path segment is: segment_begin (depth check, ray_color.rs:14-16; start the search) -> the search
+// (rtw_trace.h, driven by the caller) -> segment_end (miss / Hit / scatter). segment_begin returns
+// false when the path is over before tracing; segment_end returns true when the path is finished
+// (p.rad final), else p.ray is the next segment.
+RTW_HD bool segment_begin(const TraceCtx& cx, const RenderParams& P, const Path& p, Trav& T, const Stack& S) {
+    if (!first_hit_integrator(P.integrator) && p.depth_left < 1u) return false;
+    trav_begin(cx, p.ray, T, S);
+    return true;
+}
+
+RTW_HD bool segment_end(const TraceCtx& cx, const Noise* nt, const RenderParams& P, Path& p, const Trav& T) {
+    const Scene& sc = *cx.sc;
     const uint32_t ig = P.integrator;
-    const bool first_hit = (ig == RTW_INT_NORMAL || ig == RTW_INT_ALBEDO);
-    if (!first_hit && p.depth_left < 1u) return true;               // ray_color.rs:14-16
-    TraceCtx cx; cx.sc = &sc; cx.rng = &p.rng; cx.bounce = p.bounce; cx.mint = P.mint; cx.maxt = P.maxt; cx.work = work;
-    Best b = trace(cx, p.ray);
-    ++rays;
+    Ray ray; ray.o = T.o; ray.d = T.d; ray.time = p.ray.time;      // back in the world frame
+    const Best b = trav_result(T);
     if (b.ref == REF_NONE) {                                        // miss
         V3 bg;
         if (ig == RTW_INT_BG_COLOR || ig == RTW_INT_ALBEDO) bg = ld3(sc.background);   // ray_color.rs:91
         else if (ig == RTW_INT_GLASS_TEST) bg = v3(0.f, 0.f, 1.f);                     // glass_tests.rs:54
-        else bg = sky_gradient(p.ray.d);
+        else bg = sky_gradient(ray.d);
         p.rad = p.rad + p.thr * bg;
         return true;
     }
     RTW_COUNT(cx, hits);
     Hit h;
-    eval_hit(cx, nt, b, p.ray, h);
-    if (first_hit) {                                                // viewport.rs:524-554
+    eval_hit(cx, nt, b, ray, h);
+    if (first_hit_integrator(ig)) {                                 // viewport.rs:524-554
         if (ig == RTW_INT_NORMAL)
             p.rad = v3(0.5f * (h.normal.x + 1.0f), 0.5f * (h.normal.y + 1.0f), 0.5f * (h.normal.z + 1.0f));
         else p.rad = h.col_mod;
@@ -320,9 +336,11 @@ RTW_HD bool path_step(const Scene& sc, const Noise* nt, const RenderParams& P, P
         p.rad = p.rad + p.thr * v3(1.f, 1.f, 0.f);
         return true;
     }
-    bool front = !(dot(p.ray.d, h.normal) > 0.0f);
+    bool front = !(dot(ray.d, h.normal) > 0.0f);
     float cos_theta;
-    V3 nd = on_hit(h, p.ray, p.rng, cos_theta);
+    PathRng rng = path_rng(P, p);
+    V3 nd = on_hit(h, ray, rng, cos_theta);
+    p.block = rng.block;
     if (close_to_zero(nd)) nd = front ? h.normal : h.normal * -1.0f;   // ray_color.rs:62-64
     if (ig == RTW_INT_BG_COLOR) {                                   // ray_color.rs:67-88
         p.rad = p.rad + p.thr * h.emitted;
@@ -333,8 +351,23 @@ RTW_HD bool path_step(const Scene& sc, const Noise* nt, const RenderParams& P, P
     }
     p.thr = p.thr * h.col_mod;
     p.ray.o = h.point; p.ray.d = nd;
-    p.bounce += 1u; p.depth_left -= 1u;
+    p.depth_left -= 1u;
     return false;
+}
+
+// Scalar form of one segment (the host emulator): returns true when the path is finished.
+// `rays` counts Scene::collision_normal equivalents.
+RTW_HD bool path_step(const Scene& sc, const Noise* nt, const RenderParams& P, Path& p, uint32_t& rays,
+                      const Stack& S, Work* work = nullptr) {
+    TraceCtx cx = path_ctx(sc, P, p, work);
+    Trav T;
+    if (!segment_begin(cx, P, p, T, S)) return true;
+    while (T.cur != CUR_DONE) {
+        if (T.cur < NODE_LIMIT) trav_step_node(cx, T, S);
+        else trav_step_other(cx, p.ray.time, T, S);
+    }
+    ++rays;
+    return segment_end(cx, nt, P, p, T);
 }
 
 RTW_HD V3 path_result(const Path& p) {

@@ -14,26 +14,20 @@
 //     interval;
 //   * equal t is resolved by the lowest reference (class S < Q < I, then index), where the
 //     reference's own order depends on its random build axis.
+//
+// The walk is ONE state machine over both levels (Trav): entering an instance pushes the world
+// frame of the ray on the traversal stack and carries on in the same loop with the local ray, so
+// that all 32 lanes of a warp execute the same node / leaf code whatever level each of them is in
+// (the first version recursed into a second loop per instance and ran at 7 of 32 lanes active,
+// profiles/r1a_*). The kernels drive it warp-synchronously (trav_step_node for every lane that
+// sits on a node, then trav_step_other); trace() below is the scalar driver the host-side
+// emulator (tests/emu) uses.
 #pragma once
 #include "rtw_device.h"
 
 namespace rtw {
 
 struct Ray { V3 o, d; float time; };
-
-// per-ray constants of one frame (world or instance-local)
-struct RayK {
-    V3 inv;       // 1/d per axis (objects.rs:136)
-    float a;      // d.d (sphere.rs:103)
-    bool slow;    // some |1/d| is not finite (d == 0 or denormal): use the literal slab rule
-};
-RTW_HD RayK ray_constants(const Ray& r) {
-    RayK k;
-    k.inv = v3(1.0f / r.d.x, 1.0f / r.d.y, 1.0f / r.d.z);
-    k.a = dot(r.d, r.d);
-    k.slow = !(isfinite(k.inv.x) && isfinite(k.inv.y) && isfinite(k.inv.z));
-    return k;
-}
 
 // objects.rs:78-141 minf/maxf
 RTW_HD float ref_minf(float a, float b) { return a <= b ? a : b; }
@@ -50,38 +44,25 @@ RTW_HD bool axis_interval(float mn, float mx, float a, float b, float& lo, float
     lo = ref_minf(x1, x2); hi = ref_maxf(x1, x2);
     return true;
 }
-RTW_HD_NOINL bool slab_slow(V3 lo, V3 hi, const Ray& r, float mint, float maxt, float& tnear) {
+RTW_HD_NOINL bool slab_slow(V3 lo, V3 hi, V3 o, V3 d, float mint, float maxt, float& tnear) {
     float x0, x1, y0, y1, z0, z1;
-    if (!axis_interval(lo.x, hi.x, r.d.x, r.o.x, x0, x1)) return false;
-    if (!axis_interval(lo.y, hi.y, r.d.y, r.o.y, y0, y1)) return false;
-    if (!axis_interval(lo.z, hi.z, r.d.z, r.o.z, z0, z1)) return false;
+    if (!axis_interval(lo.x, hi.x, d.x, o.x, x0, x1)) return false;
+    if (!axis_interval(lo.y, hi.y, d.y, o.y, y0, y1)) return false;
+    if (!axis_interval(lo.z, hi.z, d.z, o.z, z0, z1)) return false;
     float mn = ref_maxf(ref_maxf(x0, y0), ref_maxf(z0, mint));
     float mx = ref_minf(ref_minf(x1, y1), ref_minf(z1, maxt));
     tnear = mn;
     return !(mn > mx);
 }
-// The slab test of AABB/QuadAABB/IAABB::collision_normal (aabb.rs:109-126): miss iff
-// max(tx0,ty0,tz0,mint) > min(tx1,ty1,tz1,maxt). With finite 1/d no NaN can arise, so
-// fminf/fmaxf equal the reference's minf/maxf.
-RTW_HD bool slab(V3 lo, V3 hi, const Ray& r, const RayK& k, float mint, float maxt, float& tnear) {
-    if (k.slow) return slab_slow(lo, hi, r, mint, maxt, tnear);
-    float x1 = (lo.x - r.o.x) * k.inv.x, x2 = (hi.x - r.o.x) * k.inv.x;
-    float y1 = (lo.y - r.o.y) * k.inv.y, y2 = (hi.y - r.o.y) * k.inv.y;
-    float z1 = (lo.z - r.o.z) * k.inv.z, z2 = (hi.z - r.o.z) * k.inv.z;
-    float mn = fmaxf(fmaxf(fminf(x1, x2), fminf(y1, y2)), fmaxf(fminf(z1, z2), mint));
-    float mx = fminf(fminf(fmaxf(x1, x2), fmaxf(y1, y2)), fminf(fmaxf(z1, z2), maxt));
-    tnear = mn;
-    return !(mn > mx);
-}
 
 // Sphere::collision_normal up to the accepted root (sphere.rs:100-123). `c` = centre at ray time.
-RTW_HD bool sphere_t(V3 c, float radius, const Ray& r, float a, float mint, float maxt, float& t) {
-    V3 oc = r.o - c;
-    float b = dot(oc, r.d);
+RTW_HD bool sphere_t(V3 c, float radius, V3 o, V3 d, float a, float mint, float maxt, float& t) {
+    V3 oc = o - c;
+    float b = dot(oc, d);
     float cc = dot(oc, oc) - radius * radius;
-    float d = b * b - a * cc;
-    if (d < 0.0f) return false;
-    float sq = sqrtf(d);
+    float disc = b * b - a * cc;
+    if (disc < 0.0f) return false;
+    float sq = sqrtf(disc);
     float x = (-b - sq) / a;
     if (x < mint) x = (-b + sq) / a;
     if (x < mint || x > maxt) return false;
@@ -90,30 +71,30 @@ RTW_HD bool sphere_t(V3 c, float radius, const Ray& r, float a, float mint, floa
 }
 
 // Quad::collision_normal up to the inside test (quad.rs:38-60).
-RTW_HD bool quad_t(const Quad* qp, const Ray& r, float mint, float maxt, float& t, float& alfa, float& beta) {
+RTW_HD bool quad_t(const Quad* qp, V3 o, V3 d, float mint, float maxt, float& t) {
     float4 q0 = RTW_LDG(&qp->q0), q1 = RTW_LDG(&qp->q1), q2 = RTW_LDG(&qp->q2), q3 = RTW_LDG(&qp->q3);
     V3 n = v3(q0.x, q0.y, q0.z);
-    float den = dot(n, r.d);
+    float den = dot(n, d);
     if (fabsf(den) <= 1e-8f) return false;
-    float tt = (q0.w - dot(n, r.o)) / den;
+    float tt = (q0.w - dot(n, o)) / den;
     if (tt < mint || tt > maxt) return false;
-    V3 p = r.o + r.d * tt;
+    V3 p = o + d * tt;
     V3 planar = p - v3(q1.x, q1.y, q1.z);
     V3 u = v3(q1.w, q2.x, q2.y), v = v3(q2.z, q2.w, q3.x), w = v3(q3.y, q3.z, q3.w);
     float al = dot(w, cross(planar, v));
     float be = dot(w, cross(u, planar));
     if (al < 0.0f || al > 1.0f || be < 0.0f || be > 1.0f) return false;
-    t = tt; alfa = al; beta = be;
+    t = tt;
     return true;
 }
 
-// best candidate so far. `t` doubles as the shrunk upper bound of the search interval.
+// Result of a search. At top level an instance hit is (KIND_INSTANCE, k) + the primitive inside.
 struct Best {
     float t;
-    uint32_t ref;     // REF_NONE = nothing yet; at top level an instance hit is (KIND_INSTANCE, k)
-    uint32_t inner;   // for instance hits: the primitive inside the instance
+    uint32_t ref;     // REF_NONE = miss
+    uint32_t inner;
 };
-RTW_HD bool closer(float t, uint32_t ref, const Best& b) { return t < b.t || (t == b.t && ref < b.ref); }
+RTW_HD bool closer(float t, uint32_t ref, float bt, uint32_t bref) { return t < bt || (t == bt && ref < bref); }
 
 // Algorithmic work of a traversal, counted only by the instrumented kernel build
 // (-DRTW_COUNT_WORK, RTW_FLAG_COUNT_WORK): the per-ray figures bench.py's roofline uses.
@@ -124,105 +105,290 @@ struct Work { uint32_t nodes, spheres, quads, instances, hits; };
 #define RTW_COUNT(cx, field) ((void)0)
 #endif
 
+// What the search needs besides the ray: the scene, the path's RNG identity (the volume free
+// flight of instance.rs:24-26 draws from a per-instance Philox stream) and the integrator's interval.
 struct TraceCtx {
     const Scene* sc;
-    const PathRng* rng;
+    uint32_t k0, k1, pixel, sample;   // Philox key and counter words 0/1 of this path
     uint32_t bounce;
-    float mint, maxt;   // the integrator's interval (un-shrunk)
-    Work* work;         // null unless RTW_COUNT_WORK
+    float mint, maxt;                 // the integrator's interval (un-shrunk)
+    Work* work;                       // null unless RTW_COUNT_WORK
 };
+RTW_HD float4 ctx_rand(const TraceCtx& cx, uint32_t blk, uint32_t stream) {
+    U4 p = philox4x32_10(cx.pixel, cx.sample, blk, stream, cx.k0, cx.k1);
+    return make_float4(u32_to_unit(p.x), u32_to_unit(p.y), u32_to_unit(p.z), u32_to_unit(p.w));
+}
 
-#define RTW_STACK 32
-
-// Leaf test of one sphere/quad against the current best (static spheres only; moving ones are
-// handled by test_moving).
-RTW_HD void test_prim(const TraceCtx& cx, uint32_t ref, const Ray& r, const RayK& k, Best& best) {
-    const Scene& sc = *cx.sc;
-    const float mint = cx.mint;
-    uint32_t idx = ref_index(ref);
-    float t;
-    if (ref_kind(ref) == KIND_SPHERE) {
-        RTW_COUNT(cx, spheres);
-        float4 s = RTW_LDG(&sc.spheres[idx]);
-        if (sphere_t(v3(s.x, s.y, s.z), s.w, r, k.a, mint, best.t, t) && closer(t, ref, best)) {
-            best.t = t; best.ref = ref; best.inner = REF_NONE;
-        }
-    } else {
-        RTW_COUNT(cx, quads);
-        float al, be;
-        if (quad_t(&sc.quads[idx], r, mint, best.t, t, al, be) && closer(t, ref, best)) {
-            best.t = t; best.ref = ref; best.inner = REF_NONE;
-        }
+// random_unit_vec (vec3.rs:216-238) drawn from a side stream: block = base | turn, turn = 1, 2, ...
+RTW_HD V3 random_unit_vec_stream(const TraceCtx& cx, uint32_t base_block, uint32_t stream) {
+    for (uint32_t turn = 0;; ++turn) {
+        float4 r = ctx_rand(cx, base_block | (turn + 1u), stream);
+        V3 p = v3(r.x * (1.0f - -1.0f) + -1.0f, r.y * (1.0f - -1.0f) + -1.0f, r.z * (1.0f - -1.0f) + -1.0f);
+        if (p.x * p.x + p.y * p.y + p.z * p.z <= 1.0f) return unit(p);
     }
+}
+
+// The traversal stack: per-thread column of 32-bit words. On the device it lives in shared memory,
+// word w of thread t at base[w * stride] with base = &smem[t], stride = block size (conflict-free);
+// the host emulator passes a plain array (stride 1). Depth needed: see stack_words().
+struct Stack {
+    uint32_t* base;
+    uint32_t stride;
+    RTW_HD void push(uint32_t& sp, uint32_t v) const { base[sp * stride] = v; ++sp; }
+    RTW_HD uint32_t pop(uint32_t& sp) const { --sp; return base[sp * stride]; }
+};
+// bottom sentinel + top pushes + world frame (10) + sentinel + probe frame (2 + sentinel) + inner pushes
+#define RTW_STACK 32   // deepest node chain the builder allows per level (scene_build.cpp)
+RTW_HD uint32_t stack_words(uint32_t top_depth, uint32_t inner_depth) { return top_depth + inner_depth + 16u; }
+
+static const uint32_t CUR_DONE = 0xFFFFFFFFu;   // nothing left to do
+static const uint32_t CUR_EXIT = 0xFFFFFFFEu;   // sentinel: the level being walked is exhausted
+static const uint32_t NODE_LIMIT = 0x40000000u; // refs below this are internal nodes (KIND_NODE == 0)
+
+enum : uint32_t { TRAV_TOP = 0u, TRAV_INNER = 1u, TRAV_PROBE = 2u };
+
+// One ray's search state.
+struct Trav {
+    V3 o, d;              // the ray in the frame being walked (world, or instance-local)
+    V3 inv;               // 1/d per axis (objects.rs:136)
+    float a;              // d.d (sphere.rs:103)
+    float t;              // best t of the level being walked == upper end of its search interval
+    uint32_t ref;         // ... and its primitive (REF_NONE: none yet)
+    float top_t;          // while inside an instance: the top level's best
+    uint32_t top_ref;
+    uint32_t inner;       // the top level's best's primitive inside its instance
+    uint32_t cur;         // next reference to process, CUR_EXIT or CUR_DONE
+    uint32_t inst;        // instance being walked (reference), REF_NONE at top level
+    uint32_t sp;
+    uint32_t mode;        // TRAV_*  | 4 when some 1/d is not finite (literal slab rule)
+};
+RTW_HD bool trav_slow(const Trav& T) { return (T.mode & 4u) != 0u; }
+RTW_HD void trav_set_ray(Trav& T, V3 o, V3 d) {
+    T.o = o; T.d = d;
+    T.inv = v3(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);
+    T.a = dot(d, d);
+    bool slow = !(isfinite(T.inv.x) && isfinite(T.inv.y) && isfinite(T.inv.z));
+    T.mode = (T.mode & 3u) | (slow ? 4u : 0u);
+}
+
+// The slab test of AABB/QuadAABB/IAABB::collision_normal (aabb.rs:109-126): miss iff
+// max(tx0,ty0,tz0,mint) > min(tx1,ty1,tz1,maxt). With finite 1/d no NaN can arise, so
+// fminf/fmaxf equal the reference's minf/maxf.
+RTW_HD bool slab(V3 lo, V3 hi, const Trav& T, float mint, float maxt, float& tnear) {
+    if (trav_slow(T)) return slab_slow(lo, hi, T.o, T.d, mint, maxt, tnear);
+    float x1 = (lo.x - T.o.x) * T.inv.x, x2 = (hi.x - T.o.x) * T.inv.x;
+    float y1 = (lo.y - T.o.y) * T.inv.y, y2 = (hi.y - T.o.y) * T.inv.y;
+    float z1 = (lo.z - T.o.z) * T.inv.z, z2 = (hi.z - T.o.z) * T.inv.z;
+    float mn = fmaxf(fmaxf(fminf(x1, x2), fminf(y1, y2)), fmaxf(fminf(z1, z2), mint));
+    float mx = fminf(fminf(fmaxf(x1, x2), fmaxf(y1, y2)), fminf(fmaxf(z1, z2), maxt));
+    tnear = mn;
+    return !(mn > mx);
 }
 
 // Moving spheres of a level: t=0 leaf box against the un-shrunk interval (aabb.rs:27-38,109-126),
 // then the sphere at its position at ray time (sphere.rs:100).
-RTW_HD void test_moving(const TraceCtx& cx, const Level& lv, const Ray& r, const RayK& k, Best& best) {
+RTW_HD void test_moving(const TraceCtx& cx, const Level& lv, float time, Trav& T) {
     const Scene& sc = *cx.sc;
-    const float mint = cx.mint, maxt = cx.maxt;
     for (uint32_t m = 0; m < lv.mov_count; ++m) {
         RTW_COUNT(cx, spheres);
         uint32_t idx = RTW_LDG(&sc.moving[lv.mov_first + m]);
         float4 lo = RTW_LDG(&sc.sphere_box[2 * idx]), hi = RTW_LDG(&sc.sphere_box[2 * idx + 1]);
         float tn;
-        if (!slab(v3(lo.x, lo.y, lo.z), v3(hi.x, hi.y, hi.z), r, k, mint, maxt, tn)) continue;
+        if (!slab(v3(lo.x, lo.y, lo.z), v3(hi.x, hi.y, hi.z), T, cx.mint, cx.maxt, tn)) continue;
         float4 s = RTW_LDG(&sc.spheres[idx]);
         float4 vel = RTW_LDG(&sc.sphere_vel[idx]);
-        V3 c = v3(s.x, s.y, s.z) + v3(vel.x, vel.y, vel.z) * r.time;
+        V3 c = v3(s.x, s.y, s.z) + v3(vel.x, vel.y, vel.z) * time;
         float t;
         uint32_t ref = make_ref(KIND_SPHERE, idx);
-        if (sphere_t(c, s.w, r, k.a, mint, best.t, t) && closer(t, ref, best)) {
-            best.t = t; best.ref = ref; best.inner = REF_NONE;
-        }
+        if (sphere_t(c, s.w, T.o, T.d, T.a, cx.mint, T.t, t) && closer(t, ref, T.t, T.ref)) { T.t = t; T.ref = ref; }
     }
 }
 
-// Walk one instance-local level (spheres and quads only). ANY = stop at the first hit (the volume
-// re-traversal of instance.rs:284-294 only asks whether anything is hit).
-template <bool ANY>
-RTW_HD bool walk_inner(const TraceCtx& cx, const Level& lv, const Ray& r, const RayK& k, Best& best) {
-    const Scene& sc = *cx.sc;
-    const float mint = cx.mint;
+// Start walking a level with the ray currently in T: its moving spheres, then its root box
+// (the reference slab-tests every BVH root, aabb.rs:109-126; an empty BVH is a miss, aabb.rs:106).
+// The level's sentinel must already be on the stack.
+RTW_HD void trav_begin_level(const TraceCtx& cx, const Level& lv, float time, Trav& T, const Stack& S) {
     if (lv.mov_count) {
-        test_moving(cx, lv, r, k, best);
-        if (ANY && best.ref != REF_NONE) return true;
+        test_moving(cx, lv, time, T);
+        if ((T.mode & 3u) == TRAV_PROBE && T.ref != REF_NONE) { T.cur = S.pop(T.sp); return; }
     }
-    if (lv.root == REF_NONE) return best.ref != REF_NONE;
     float tn;
-    if (!slab(v3(lv.lo[0], lv.lo[1], lv.lo[2]), v3(lv.hi[0], lv.hi[1], lv.hi[2]), r, k, mint, best.t, tn))
-        return best.ref != REF_NONE;
-    uint32_t stack[RTW_STACK];
-    int sp = 0;
-    uint32_t cur = lv.root;
-    for (;;) {
-        if (ref_kind(cur) == KIND_NODE) {
-            RTW_COUNT(cx, nodes);
-            const Node* np = &sc.nodes[cur];
-            float4 n0 = RTW_LDG(&np->n0), n1 = RTW_LDG(&np->n1), n2 = RTW_LDG(&np->n2);
-            uint4 n3 = RTW_LDG(&np->n3);
-            float t0, t1;
-            bool h0 = slab(v3(n0.x, n0.y, n0.z), v3(n0.w, n1.x, n1.y), r, k, mint, best.t, t0);
-            bool h1 = slab(v3(n1.z, n1.w, n2.x), v3(n2.y, n2.z, n2.w), r, k, mint, best.t, t1);
-            if (h0 && h1) {
-                bool swap = t1 < t0;
-                stack[sp++] = swap ? n3.x : n3.y;
-                cur = swap ? n3.y : n3.x;
-                continue;
-            }
-            if (h0) { cur = n3.x; continue; }
-            if (h1) { cur = n3.y; continue; }
-        } else {
-            test_prim(cx, cur, r, k, best);
-            if (ANY && best.ref != REF_NONE) return true;
-        }
-        if (sp == 0) break;
-        cur = stack[--sp];
+    if (lv.root == REF_NONE ||
+        !slab(v3(lv.lo[0], lv.lo[1], lv.lo[2]), v3(lv.hi[0], lv.hi[1], lv.hi[2]), T, cx.mint, T.t, tn)) {
+        T.cur = S.pop(T.sp);
+        return;
     }
-    return best.ref != REF_NONE;
+    T.cur = lv.root;
 }
 
-// Instance::collision_normal up to "is there a hit and at what t" (instance.rs:250-302).
+// Scene::collision_normal (viewport.rs:136-150): start the search of `r`.
+RTW_HD void trav_begin(const TraceCtx& cx, const Ray& r, Trav& T, const Stack& S) {
+    T.mode = TRAV_TOP;
+    trav_set_ray(T, r.o, r.d);
+    T.t = cx.maxt; T.ref = REF_NONE; T.inner = REF_NONE;
+    T.top_t = 0.0f; T.top_ref = REF_NONE;
+    T.inst = REF_NONE; T.sp = 0u;
+    S.push(T.sp, CUR_EXIT);
+    trav_begin_level(cx, cx.sc->top, r.time, T, S);
+}
+
+// One static sphere / quad leaf against the level's best so far.
+RTW_HD void trav_test_prim(const TraceCtx& cx, uint32_t ref, Trav& T) {
+    const Scene& sc = *cx.sc;
+    const uint32_t idx = ref_index(ref);
+    float t;
+    bool hit;
+    if (ref_kind(ref) == KIND_SPHERE) {
+        RTW_COUNT(cx, spheres);
+        float4 s = RTW_LDG(&sc.spheres[idx]);
+        hit = sphere_t(v3(s.x, s.y, s.z), s.w, T.o, T.d, T.a, cx.mint, T.t, t);
+    } else {
+        RTW_COUNT(cx, quads);
+        hit = quad_t(&sc.quads[idx], T.o, T.d, cx.mint, T.t, t);
+    }
+    if (hit && closer(t, ref, T.t, T.ref)) { T.t = t; T.ref = ref; }
+}
+RTW_HD bool ref_is_prim(uint32_t r) { return (r - NODE_LIMIT) < 0x80000000u; }   // KIND_SPHERE or KIND_QUAD
+
+// T.cur is an internal node: both child boxes; sphere / quad children whose box is crossed are
+// tested on the spot (they are leaves: nothing to descend into), node / instance children are
+// visited nearer first with the other one stacked.
+RTW_HD void trav_step_node(const TraceCtx& cx, Trav& T, const Stack& S) {
+    RTW_COUNT(cx, nodes);
+    const Node* np = &cx.sc->nodes[T.cur];
+    float4 n0 = RTW_LDG(&np->n0), n1 = RTW_LDG(&np->n1), n2 = RTW_LDG(&np->n2);
+    uint4 n3 = RTW_LDG(&np->n3);
+    float t0, t1;
+    bool h0 = slab(v3(n0.x, n0.y, n0.z), v3(n0.w, n1.x, n1.y), T, cx.mint, T.t, t0);
+    bool h1 = slab(v3(n1.z, n1.w, n2.x), v3(n2.y, n2.z, n2.w), T, cx.mint, T.t, t1);
+    const bool p0 = h0 && ref_is_prim(n3.x), p1 = h1 && ref_is_prim(n3.y);
+    if (p0 || p1) {
+        uint32_t pa = p0 ? n3.x : n3.y, pb = (p0 && p1) ? n3.y : REF_NONE;
+#if defined(__CUDA_ARCH__)
+#pragma unroll 1
+#endif
+        for (int k = 0; k < 2 && pa != REF_NONE; ++k) { trav_test_prim(cx, pa, T); pa = pb; pb = REF_NONE; }
+        h0 = h0 && !p0; h1 = h1 && !p1;
+        if ((T.mode & 3u) == TRAV_PROBE && T.ref != REF_NONE) {   // instance.rs:284-294 only asks "anything?"
+            while (S.pop(T.sp) != CUR_EXIT) {}
+            T.cur = CUR_EXIT;
+            return;
+        }
+    }
+    if (h0 && h1) {
+        bool swap = t1 < t0;
+        S.push(T.sp, swap ? n3.x : n3.y);
+        T.cur = swap ? n3.y : n3.x;
+    } else if (h0) {
+        T.cur = n3.x;
+    } else if (h1) {
+        T.cur = n3.y;
+    } else {
+        T.cur = S.pop(T.sp);
+    }
+}
+
+// Instance::collision_normal, first half (instance.rs:250-271): ray -> local frame, walk the inside.
+RTW_HD void trav_enter_instance(const TraceCtx& cx, float time, Trav& T, const Stack& S) {
+    RTW_COUNT(cx, instances);
+    const Instance& in = cx.sc->instances[ref_index(T.cur)];
+    // world frame of the ray: restored by trav_leave_instance
+    S.push(T.sp, f2u(T.o.x)); S.push(T.sp, f2u(T.o.y)); S.push(T.sp, f2u(T.o.z));
+    S.push(T.sp, f2u(T.d.x)); S.push(T.sp, f2u(T.d.y)); S.push(T.sp, f2u(T.d.z));
+    S.push(T.sp, f2u(T.inv.x)); S.push(T.sp, f2u(T.inv.y)); S.push(T.sp, f2u(T.inv.z));
+    S.push(T.sp, f2u(T.a));
+    S.push(T.sp, CUR_EXIT);
+    V3 o = T.o - v3(in.t[0], in.t[1], in.t[2]);
+    V3 d = T.d;
+    if (!(in.flags & INST_ROT_IDENTITY)) { o = rot_apply(in.inv_rows, o); d = rot_apply(in.inv_rows, d); }
+    T.inst = T.cur;
+    T.top_t = T.t; T.top_ref = T.ref;     // T.t stays: the inner search starts from the same bound
+    T.ref = REF_NONE;
+    T.mode = TRAV_INNER;
+    trav_set_ray(T, o, d);
+    trav_begin_level(cx, in.level, time, T, S);
+}
+
+// const_density (instance.rs:24-26): ln(xi) / -density, xi from the instance's volume stream.
+RTW_HD float volume_distance(const Instance& in, const TraceCtx& cx) {
+    float xi = ctx_rand(cx, (cx.bounce << 16) | 0u, 1u + in.index).x;
+    return logf(xi) / -in.density;
+}
+
+// The sentinel of the level being walked came off the stack.
+//   top level:  the search is over.
+//   instance:   instance.rs:272-302 — no inner hit => miss; a constant-density volume re-traverses
+//               from a point `distance` behind the entry face and only counts if that probe hits
+//               anything (the entry-face t is kept); then back to the world frame.
+RTW_HD void trav_level_finished(const TraceCtx& cx, float time, Trav& T, const Stack& S) {
+    const uint32_t mode = T.mode & 3u;
+    if (mode == TRAV_TOP) { T.cur = CUR_DONE; return; }
+    const Instance& in = cx.sc->instances[ref_index(T.inst)];
+    bool hit;
+    if (mode == TRAV_INNER) {
+        hit = T.ref != REF_NONE;
+        if (hit && (in.flags & INST_VOLUME)) {
+            float distance = volume_distance(in, cx);
+            if (distance >= 0.0f) {
+                S.push(T.sp, f2u(T.t)); S.push(T.sp, T.ref); S.push(T.sp, CUR_EXIT);
+                T.o = (T.o + T.d * T.t) + T.d * distance;       // same direction: inv, a unchanged
+                T.t = cx.maxt; T.ref = REF_NONE;
+                T.mode = (T.mode & 4u) | TRAV_PROBE;
+                trav_begin_level(cx, in.level, time, T, S);
+                return;
+            }
+        }
+    } else {
+        hit = T.ref != REF_NONE;                                  // the probe found something
+        T.ref = S.pop(T.sp); T.t = u2f(S.pop(T.sp));              // the inner closest hit again
+    }
+    // leave the instance
+    T.a = u2f(S.pop(T.sp));
+    T.inv.z = u2f(S.pop(T.sp)); T.inv.y = u2f(S.pop(T.sp)); T.inv.x = u2f(S.pop(T.sp));
+    T.d.z = u2f(S.pop(T.sp)); T.d.y = u2f(S.pop(T.sp)); T.d.x = u2f(S.pop(T.sp));
+    T.o.z = u2f(S.pop(T.sp)); T.o.y = u2f(S.pop(T.sp)); T.o.x = u2f(S.pop(T.sp));
+    bool slow = !(isfinite(T.inv.x) && isfinite(T.inv.y) && isfinite(T.inv.z));
+    T.mode = TRAV_TOP | (slow ? 4u : 0u);
+    if (hit && closer(T.t, T.inst, T.top_t, T.top_ref)) { T.inner = T.ref; T.ref = T.inst; }
+    else { T.t = T.top_t; T.ref = T.top_ref; }
+    T.inst = REF_NONE;
+    T.cur = S.pop(T.sp);
+}
+
+// T.cur is anything but an internal node: an instance leaf, the sentinel, or a sphere / quad that is
+// the root of its level. Events are chained until the lane is back on a node (or done), so that a
+// single-primitive instance (C5's two volumes) costs one step, not five.
+RTW_HD void trav_step_other(const TraceCtx& cx, float time, Trav& T, const Stack& S) {
+    do {
+        const uint32_t cur = T.cur;
+        if (cur == CUR_EXIT) trav_level_finished(cx, time, T, S);
+        else if (ref_kind(cur) == KIND_INSTANCE) trav_enter_instance(cx, time, T, S);
+        else {
+            trav_test_prim(cx, cur, T);
+            if ((T.mode & 3u) == TRAV_PROBE && T.ref != REF_NONE) {
+                while (S.pop(T.sp) != CUR_EXIT) {}
+                T.cur = CUR_EXIT;
+            } else {
+                T.cur = S.pop(T.sp);
+            }
+        }
+    } while (T.cur >= NODE_LIMIT && T.cur != CUR_DONE);
+}
+
+RTW_HD Best trav_result(const Trav& T) { Best b; b.t = T.t; b.ref = T.ref; b.inner = T.inner; return b; }
+
+// Scalar driver (host emulator, and any caller that does not schedule the steps itself).
+RTW_HD Best trace(const TraceCtx& cx, const Ray& r, const Stack& S) {
+    Trav T;
+    trav_begin(cx, r, T, S);
+    while (T.cur != CUR_DONE) {
+        if (T.cur < NODE_LIMIT) trav_step_node(cx, T, S);
+        else trav_step_other(cx, r.time, T, S);
+    }
+    return trav_result(T);
+}
+
+// Instance::collision_normal's frame change for the Hit evaluation (instance.rs:257-258).
 RTW_HD Ray to_local(const Instance& in, const Ray& r) {
     Ray l;
     V3 o = r.o - v3(in.t[0], in.t[1], in.t[2]);
@@ -230,74 +396,6 @@ RTW_HD Ray to_local(const Instance& in, const Ray& r) {
     else { l.o = rot_apply(in.inv_rows, o); l.d = rot_apply(in.inv_rows, r.d); }
     l.time = r.time;
     return l;
-}
-// const_density (instance.rs:24-26): ln(xi) / -density, xi from the instance's volume stream.
-RTW_HD float volume_distance(const Instance& in, const TraceCtx& cx) {
-    float xi = cx.rng->at((cx.bounce << 16) | 0u, 1u + in.index).x;
-    return logf(xi) / -in.density;
-}
-
-RTW_HD void test_instance(const TraceCtx& cx, uint32_t ref, const Ray& r, Best& best) {
-    const Scene& sc = *cx.sc;
-    RTW_COUNT(cx, instances);
-    const Instance& in = sc.instances[ref_index(ref)];
-    Ray l = to_local(in, r);
-    RayK k = ray_constants(l);
-    Best ib; ib.t = best.t; ib.ref = REF_NONE; ib.inner = REF_NONE;
-    if (!walk_inner<false>(cx, in.level, l, k, ib)) return;
-    if (in.flags & INST_VOLUME) {
-        float distance = volume_distance(in, cx);
-        if (distance >= 0.0f) {
-            Ray l2 = l;
-            l2.o = (l.o + l.d * ib.t) + l.d * distance;
-            Best any; any.t = cx.maxt; any.ref = REF_NONE; any.inner = REF_NONE;
-            if (!walk_inner<true>(cx, in.level, l2, k, any)) return;
-        }
-    }
-    if (closer(ib.t, ref, best)) { best.t = ib.t; best.ref = ref; best.inner = ib.ref; }
-}
-
-// Scene::collision_normal (viewport.rs:136-150): closest of everything.
-RTW_HD Best trace(const TraceCtx& cx, const Ray& r) {
-    const Scene& sc = *cx.sc;
-    const Level& lv = sc.top;
-    Best best; best.t = cx.maxt; best.ref = REF_NONE; best.inner = REF_NONE;
-    RayK k = ray_constants(r);
-    if (lv.mov_count) test_moving(cx, lv, r, k, best);
-    if (lv.root == REF_NONE) return best;
-    float tn;
-    if (!slab(v3(lv.lo[0], lv.lo[1], lv.lo[2]), v3(lv.hi[0], lv.hi[1], lv.hi[2]), r, k, cx.mint, best.t, tn))
-        return best;
-    uint32_t stack[RTW_STACK];
-    int sp = 0;
-    uint32_t cur = lv.root;
-    for (;;) {
-        uint32_t kind = ref_kind(cur);
-        if (kind == KIND_NODE) {
-            RTW_COUNT(cx, nodes);
-            const Node* np = &sc.nodes[cur];
-            float4 n0 = RTW_LDG(&np->n0), n1 = RTW_LDG(&np->n1), n2 = RTW_LDG(&np->n2);
-            uint4 n3 = RTW_LDG(&np->n3);
-            float t0, t1;
-            bool h0 = slab(v3(n0.x, n0.y, n0.z), v3(n0.w, n1.x, n1.y), r, k, cx.mint, best.t, t0);
-            bool h1 = slab(v3(n1.z, n1.w, n2.x), v3(n2.y, n2.z, n2.w), r, k, cx.mint, best.t, t1);
-            if (h0 && h1) {
-                bool swap = t1 < t0;
-                stack[sp++] = swap ? n3.x : n3.y;
-                cur = swap ? n3.y : n3.x;
-                continue;
-            }
-            if (h0) { cur = n3.x; continue; }
-            if (h1) { cur = n3.y; continue; }
-        } else if (kind == KIND_INSTANCE) {
-            test_instance(cx, cur, r, best);
-        } else {
-            test_prim(cx, cur, r, k, best);
-        }
-        if (sp == 0) break;
-        cur = stack[--sp];
-    }
-    return best;
 }
 
 }  // namespace rtw

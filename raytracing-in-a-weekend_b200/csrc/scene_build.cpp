@@ -338,6 +338,7 @@ int build_host_scene(const rtw_scene_desc* d, HostScene& hs, std::string& err) {
     hs.info.n_blas_nodes = (uint32_t)hs.nodes.size() - blas_nodes_before;
     hs.info.n_flattened_instances = n_flat;
     hs.info.bvh_max_depth = top_depth + inner_depth;
+    hs.top_depth = top_depth; hs.inner_depth = inner_depth;
     if (top_depth >= (uint32_t)RTW_STACK || inner_depth >= (uint32_t)RTW_STACK) { err = "BVH deeper than the traversal stack"; return RTW_E_UNSUPPORTED; }
     if (hs.nodes.empty()) { hs.nodes.emplace_back(); std::memset(&hs.nodes[0], 0, sizeof(Node)); }
     if (hs.moving.empty()) hs.moving.push_back(0u);

@@ -5,6 +5,7 @@
 #include <cmath>
 #include <cstring>
 #include <string>
+#include <vector>
 #include "../../raytracing-in-a-weekend_b200/csrc/rtw_host.h"
 #include "../../raytracing-in-a-weekend_b200/csrc/rtw_shade.h"
 
@@ -21,6 +22,8 @@ extern "C" int emu_render(const rtw_scene_desc* d, const rtw_camera* cam, const 
     rc = make_render_params(cam, o, P, total, err);
     if (rc) { std::fprintf(stderr, "emu: %s\n", err.c_str()); return rc; }
     uint64_t paths = 0, nan = 0; uint32_t rays32 = 0; uint64_t rays = 0;
+    std::vector<uint32_t> stack_mem(stack_words(hs.top_depth, hs.inner_depth));
+    Stack S; S.base = stack_mem.data(); S.stride = 1u;
     for (uint32_t jr = 0; jr < P.row_count; ++jr)
         for (uint32_t i = 0; i < cam->width; ++i) {
             V3 acc = v3(0, 0, 0);
@@ -28,7 +31,7 @@ extern "C" int emu_render(const rtw_scene_desc* d, const rtw_camera* cam, const 
                 Path p;
                 generate(P, i, P.row_begin + jr, s, p);
                 rays32 = 0;
-                while (!path_step(sc, sc.noises, P, p, rays32)) {}
+                while (!path_step(sc, sc.noises, P, p, rays32, S)) {}
                 rays += rays32;
                 V3 c = path_result(p);
                 if (!finite3(c)) ++nan;

@@ -48,14 +48,19 @@ def _first_hit(job, ig, oracle, cuda):
     return err[np.broadcast_to(ok, err.shape)], tie.mean()
 
 
+PIPES = pytest.mark.parametrize("pipe", [0, A.RTW_FLAG_WAVEFRONT], ids=["megakernel", "wavefront"])
+
+
+@PIPES
 @pytest.mark.parametrize("name", sorted(ALL))
 @pytest.mark.parametrize("ig", [A.RTW_INT_NORMAL, A.RTW_INT_ALBEDO])
-def test_first_hit_parity(name, ig, oracle, cuda):
+def test_first_hit_parity(name, ig, pipe, oracle, cuda):
     job = ALL[name]()
     if not name.startswith("glass10"):
         job = _small(job, 200, 150)
     else:
         job.viewport.flags = A.RTW_FLAG_STRICT_FP
+    job.viewport.flags |= pipe
     err, tie_frac = _first_hit(job, ig, oracle, cuda)
     # libm differences (atan2f/acosf/logf on device vs glibc) can flip a texel or a volume decision
     # on a handful of pixels; everything else must be inside 1e-5.
@@ -63,8 +68,9 @@ def test_first_hit_parity(name, ig, oracle, cuda):
     assert tie_frac < 0.12
 
 
+@PIPES
 @pytest.mark.parametrize("name", sorted(ALL))
-def test_path_parity_sample_for_sample(name, oracle, cuda):
+def test_path_parity_sample_for_sample(name, pipe, oracle, cuda):
     """Same Philox stream on both sides: low-spp renders agree except where a float-level
     difference flips a discrete decision along a path."""
     job = ALL[name]()
@@ -73,6 +79,7 @@ def test_path_parity_sample_for_sample(name, oracle, cuda):
     else:
         job = _small(job, 120, 90, spp=4)
     vp = job.viewport
+    vp.flags |= pipe
     vp.gamma = 1.0      # compare linear radiance (gamma only hides or NaNs negative Perlin values)
     ref = vp._run(job.ray_color, job.scene, job.mode, oracle)
     got = vp._run(job.ray_color, job.scene, job.mode, cuda)
@@ -98,3 +105,21 @@ def test_fast_kernels_agree_statistically(oracle, cuda):
     fin = np.isfinite(strict) & np.isfinite(fast)
     assert fin.mean() > 0.95
     assert abs(fast[fin].mean() / strict[fin].mean() - 1.0) < 5e-3
+
+
+def test_pipelines_agree(cuda):
+    """Megakernel and wavefront run the same per-path arithmetic with the same Philox streams: the
+    strict builds agree path for path, so the images differ only by f32 summation order."""
+    job = _small(scenes.config_c5(), 160, 120, spp=16)
+    vp = job.viewport
+    vp.gamma = 1.0
+    mega = vp._run(job.ray_color, job.scene, job.mode, cuda)
+    sm = cuda.scene(job.scene).stats()
+    vp.flags |= A.RTW_FLAG_WAVEFRONT
+    wave = vp._run(job.ray_color, job.scene, job.mode, cuda)
+    sw = cuda.scene(job.scene).stats()
+    assert (sm.paths, sm.rays, sm.nan_paths) == (sw.paths, sw.rays, sw.nan_paths)
+    assert sw.gpu_launches >= 3
+    fin = np.isfinite(mega) & np.isfinite(wave)
+    assert np.array_equal(np.isfinite(mega), np.isfinite(wave))
+    assert np.allclose(mega[fin], wave[fin], rtol=1e-5, atol=1e-6)
