@@ -186,6 +186,10 @@ def run_reference(args):
 
 
 # ----------------------------------------------------------------------------- GPU arm
+def wavefront_probe(per_step) -> bool:
+    return bool(per_step) and per_step[0][5] > 0
+
+
 def run_b200(args):
     import torch
     import torch.distributed as dist
@@ -235,7 +239,8 @@ def run_b200(args):
             be.resolve_device(buf.data_ptr(), H * W, spp, vp.gamma, stream)
         if collect is not None and count > 0:
             st = h.stats()                              # syncs on this step's last event
-            collect.append((st.kernel_ms, st.rays, st.paths, st.nan_paths))
+            collect.append((st.kernel_ms, st.rays, st.paths, st.nan_paths, st.gpu_launches, st.iterations,
+                            st.extend_ms, st.shade_ms))
 
     for _ in range(args.warmup):
         step()
@@ -316,8 +321,7 @@ def run_b200(args):
         wc = h.stats()
         per_ray = {"node": wc.nodes / wc.rays, "sphere": wc.sphere_tests / wc.rays, "quad": wc.quad_tests / wc.rays,
                    "instance": wc.instance_tests / wc.rays, "hit": wc.hits / wc.rays}
-        flop_per_ray = sum(per_ray[k] * COST[k][0] for k in COST)
-        bytes_per_ray = sum(per_ray[k] * COST[k][1] for k in COST)
+        sched = h.sched_stats() if wavefront_probe(per_step) else None
         fp32_peak = be.microbench(A.RTW_BENCH_FP32)
         l2_peak = be.microbench(A.RTW_BENCH_L2)
         peaks_file = os.path.join(ROOT, "MEASURED_PEAKS.json")
@@ -327,24 +331,44 @@ def run_b200(args):
                 hbm_peak, hbm_src = float(json.load(open(peaks_file))["hbm_gbs"]), "measured"
             except Exception:
                 pass
-        # dominant kernel = mega_kernel: average launch duration over the timed region, rank 0
-        k_ms = statistics.mean(p[0] for p in per_step) if per_step else float("nan")
-        rays_launch = statistics.mean(p[1] for p in per_step) if per_step else 0.0
-        paths_launch = statistics.mean(p[2] for p in per_step) if per_step else 0.0
+        # dominant kernel: average launch duration over the timed region, rank 0, CUDA events recorded by
+        # the library on the launching stream (wavefront: every 8th extend/shade launch is bracketed)
+        wavefront = bool(per_step) and per_step[0][5] > 0
+        rays_step = statistics.mean(p[1] for p in per_step) if per_step else 0.0
+        if wavefront:
+            kname = "wf_extend_kernel"
+            iters = statistics.mean(p[5] for p in per_step)
+            k_ms = statistics.mean(p[6] for p in per_step)
+            shade_ms = statistics.mean(p[7] for p in per_step)
+            rays_launch = rays_step / iters
+            work_keys = ("node", "sphere", "quad", "instance")     # the Hit/scatter work runs in wf_shade_kernel
+        else:
+            kname, iters, shade_ms = "mega_kernel", 0, 0.0
+            k_ms = statistics.mean(p[0] for p in per_step) if per_step else float("nan")
+            rays_launch = rays_step
+            work_keys = tuple(COST)
+        flop_per_ray = sum(per_ray[k] * COST[k][0] for k in work_keys)
+        bytes_per_ray = sum(per_ray[k] * COST[k][1] for k in work_keys)
         tflops = flop_per_ray * rays_launch / (k_ms * 1e-3) / 1e12
         l2_gbs = bytes_per_ray * rays_launch / (k_ms * 1e-3) / 1e9
-        hbm_bytes_launch = paths_launch / max(1, 32 * 64) * 0 + H * W * 3 * 4 * 2.0   # framebuffer RED traffic only (lower bound)
+        state_bytes = 216.0 if wavefront else 0.0     # path records streamed per ray, else REDs only
+        step_ms = elapsed_ms / args.steps
+        hbm_gbs = (state_bytes * rays_step + H * W * 3 * 4 * 2.0) / (step_ms * 1e-3) / 1e9
         cands = [("fp32", tflops, fp32_peak, "TFLOP/s"), ("l2", l2_gbs, l2_peak, "GB/s")]
         bname, bach, bpeak, bunit = max(cands, key=lambda c: c[1] / c[2])
-        roofline = {"kernel": "mega_kernel", "bound": bname, "achieved": bach, "peak": bpeak, "unit": bunit,
+        roofline = {"kernel": kname, "bound": bname, "achieved": bach, "peak": bpeak, "unit": bunit,
                     "frac": bach / bpeak, "traffic": None, "peak_source": "rtw_microbench on this GPU (MEASURED_PEAKS.json has no fp32/L2 entry)",
                     "kernel_ms_per_launch": k_ms, "rays_per_launch": rays_launch,
+                    "launches_per_step": iters if wavefront else 1,
+                    "share_of_step": (k_ms * iters / step_ms) if wavefront else (k_ms / step_ms),
+                    "shade_ms_per_launch": shade_ms,
                     "per_ray": {**per_ray, "flop": flop_per_ray, "scene_bytes": bytes_per_ray},
+                    "extend_warp_scheduling": sched,
                     "all": {"fp32": {"achieved": tflops, "peak": fp32_peak, "unit": "TFLOP/s", "frac": tflops / fp32_peak},
                             "l2": {"achieved": l2_gbs, "peak": l2_peak, "unit": "GB/s", "frac": l2_gbs / l2_peak},
-                            "hbm": {"achieved": hbm_bytes_launch / (k_ms * 1e-3) / 1e9, "peak": hbm_peak, "unit": "GB/s",
-                                    "frac": hbm_bytes_launch / (k_ms * 1e-3) / 1e9 / hbm_peak, "peak_source": hbm_src,
-                                    "note": "scene (<10 MB) is L1/L2-resident; only the framebuffer REDs reach HBM"}}}
+                            "hbm": {"achieved": hbm_gbs, "peak": hbm_peak, "unit": "GB/s", "frac": hbm_gbs / hbm_peak,
+                                    "peak_source": hbm_src,
+                                    "note": "whole step: path records streamed by extend+shade (216 B/ray) + framebuffer REDs; the scene (<10 MB) is L1/L2-resident"}}}
         cpu = cpu_baseline_obj(cpu_sample(job, args.cpu_seconds)) if world == 1 else None
         paths_frame = W * H * spp
         val = paths_frame * args.steps / (elapsed_ms * 1e-3) / 1e6
@@ -352,14 +376,14 @@ def run_b200(args):
                 "ms_per_step": elapsed_ms / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
                 "dtype": "f32", "data": "synthetic",
                 "config": {"workload": workload_name(job), "partition": f"sample range x{world} + NCCL reduce(sum) to rank 0",
-                           "l2": "256 MiB memset between steps (inside the timed region)", "pipeline": "megakernel",
+                           "l2": "256 MiB memset between steps (inside the timed region)", "pipeline": "wavefront (extend + shade kernels over path queues in HBM)" if wavefront else "megakernel",
                            "fp": "strict (-fmad=false)" if args.flags & 1 else "fast (FFMA contraction)"},
                 "mrays_per_s": rays_total / (elapsed_ms * 1e-3) / 1e6, "rays_per_path": rays_total / max(1.0, paths_total),
                 "nan_paths": nan_total, "image_mean": image_mean,
                 "e2e": {"value": paths_frame * e2e_steps / e2e_s / 1e6, "unit": UNIT, "h2d_bytes_per_step": h2d * world,
                         "d2h_bytes_per_step": H * W * 3 * 4, "ms_per_step": e2e_s / e2e_steps * 1e3, "steps": e2e_steps,
                         "what": "rtw_scene_create + rtw_render(host out) + rtw_scene_destroy per step"},
-                "gpu_launches": args.steps * (world + 1), "clocks": clocks, "roofline": roofline}
+                "gpu_launches": int(sum(p[4] for p in per_step)) + args.steps, "clocks": clocks, "roofline": roofline}
         if cpu is not None:
             line["cpu_baseline"] = cpu
         print(json.dumps(line), flush=True)

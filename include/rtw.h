@@ -151,9 +151,11 @@ enum {
     /* Use the kernels compiled with -fmad=false: no a*b+c contraction, i.e. the same f32 operation
      * sequence rustc emits for the reference (parity runs). Default: nvcc's FFMA contraction. */
     RTW_FLAG_STRICT_FP = 1u,
-    /* Render through the wavefront pipeline (generate / extend / shade / accumulate kernels with
-     * ray queues in HBM) instead of the default path-regenerating megakernel. */
+    /* Pipeline choice. Default (neither flag): the wavefront pipeline (extend / shade kernels over
+     * path queues in HBM) for renders of at least 2^18 paths, the single persistent-lane megakernel
+     * below that. The flags force one or the other. */
     RTW_FLAG_WAVEFRONT = 2u,
+    RTW_FLAG_MEGAKERNEL = 8u,
     /* Use the instrumented build of the fast kernels, which also counts BVH node visits and
      * primitive tests (rtw_stats.nodes ...): the algorithmic work behind the roofline. Slower. */
     RTW_FLAG_COUNT_WORK = 4u
@@ -190,6 +192,10 @@ typedef struct rtw_stats {
     uint64_t nodes;          /* BVH nodes visited (each = two child-box slab tests, 64 B) */
     uint64_t sphere_tests, quad_tests, instance_tests;
     uint64_t hits;           /* segments that ended on a surface (Hit evaluated + scatter) */
+    /* wavefront renders only, else 0 */
+    uint64_t iterations;     /* extend + shade rounds */
+    float    extend_ms;      /* mean device time of one wf_extend launch (CUDA events, sampled every 8th round) */
+    float    shade_ms;       /* mean device time of one wf_shade launch (same samples) */
 } rtw_stats;
 
 typedef struct rtw_scene rtw_scene;   /* opaque: device-resident flattened scene + BVH */
@@ -239,6 +245,11 @@ int rtw_quantize_device(const float* d_rgb, uint8_t* d_rgb8, uint64_t n_values, 
                         void* stream);
 
 int rtw_get_stats(rtw_scene* scene, rtw_stats* out);
+/* Warp-scheduling counters of the wavefront extend kernel, filled by RTW_FLAG_COUNT_WORK |
+ * RTW_FLAG_WAVEFRONT renders: out[0] = loop iterations (per warp, summed); then for the step kinds
+ * node, primitive, instance-event, fetch: out[1+k] = times the kind ran, out[5+k] = lanes it ran
+ * with in total. A tuning aid (lanes/steps/32 = SIMD efficiency of that kind). */
+int rtw_get_sched_stats(rtw_scene* scene, uint64_t out[9]);
 
 /* --- device micro-benchmarks: the denominators of the FP32 and L2 rooflines, which
  * MEASURED_PEAKS.json does not carry. which = RTW_BENCH_FP32 -> TFLOP/s of dependent-free FFMA

@@ -25,7 +25,7 @@ RTW_MODE_RANDOM, RTW_MODE_STRATIFIED, RTW_MODE_NO_RAND = range(3)
 # outputs
 RTW_OUT_RESOLVED, RTW_OUT_SUM = 0, 1
 # flags
-RTW_FLAG_STRICT_FP, RTW_FLAG_WAVEFRONT, RTW_FLAG_COUNT_WORK = 1, 2, 4
+RTW_FLAG_STRICT_FP, RTW_FLAG_WAVEFRONT, RTW_FLAG_COUNT_WORK, RTW_FLAG_MEGAKERNEL = 1, 2, 4, 8
 RTW_BENCH_FP32, RTW_BENCH_L2, RTW_BENCH_HBM = 0, 1, 2
 
 f32, u32, i32, u64 = C.c_float, C.c_uint32, C.c_int32, C.c_uint64
@@ -85,7 +85,8 @@ class rtw_render_opts(C.Structure):
 class rtw_stats(C.Structure):
     _fields_ = [("paths", u64), ("rays", u64), ("nan_paths", u64), ("gpu_launches", u64),
                 ("kernel_ms", f32), ("total_ms", f32),
-                ("nodes", u64), ("sphere_tests", u64), ("quad_tests", u64), ("instance_tests", u64), ("hits", u64)]
+                ("nodes", u64), ("sphere_tests", u64), ("quad_tests", u64), ("instance_tests", u64), ("hits", u64),
+                ("iterations", u64), ("extend_ms", f32), ("shade_ms", f32)]
 
 
 class rtw_scene_info(C.Structure):
@@ -110,6 +111,7 @@ SYMBOLS = {
     "rtw_resolve_device": (C.c_int, [C.c_void_p, u64, u32, f32, C.c_int, C.c_void_p]),
     "rtw_quantize_device": (C.c_int, [C.c_void_p, C.c_void_p, u64, C.c_int, C.c_void_p]),
     "rtw_get_stats": (C.c_int, [C.c_void_p, P(rtw_stats)]),
+    "rtw_get_sched_stats": (C.c_int, [C.c_void_p, P(u64)]),
     "rtw_microbench": (C.c_int, [C.c_int, C.c_int, C.c_int, P(C.c_double)]),
     "rtw_scene_get_info": (C.c_int, [C.c_void_p, P(rtw_scene_info)]),
 }

@@ -66,6 +66,17 @@ class CudaSceneHandle:
         A.check(self._lib.rtw_get_stats(self._h, C.byref(st)))
         return st
 
+    def sched_stats(self) -> dict:
+        """Warp-scheduling counters of the last COUNT_WORK | WAVEFRONT render (tuning aid)."""
+        out = (C.c_uint64 * 9)()
+        A.check(self._lib.rtw_get_sched_stats(self._h, out))
+        kinds = ("node", "prim", "event", "fetch")
+        d = {"iterations": int(out[0])}
+        for k, name in enumerate(kinds):
+            steps, lanes = int(out[1 + k]), int(out[5 + k])
+            d[name] = {"steps": steps, "lanes": lanes, "lanes_per_step": lanes / steps if steps else 0.0}
+        return d
+
     def info(self) -> A.rtw_scene_info:
         inf = A.rtw_scene_info()
         A.check(self._lib.rtw_scene_get_info(self._h, C.byref(inf)))

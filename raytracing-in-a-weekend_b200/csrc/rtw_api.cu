@@ -110,7 +110,10 @@ struct rtw_scene {
     cudaEvent_t wf_ev[4] = {nullptr, nullptr, nullptr, nullptr};
     int occ_wf[3] = {0, 0, 0};
     bool last_wavefront = false;
-    uint64_t wf_paths = 0;
+    uint64_t wf_paths = 0, wf_iterations = 0;
+    static const int kTimed = 32;             // sampled (extend, shade) launches timed with events per render
+    cudaEvent_t wf_t[kTimed][3] = {};
+    int wf_timed = 0;
 
     ~rtw_scene() {
         cudaSetDevice(device);
@@ -121,6 +124,7 @@ struct rtw_scene {
         if (d_wc) cudaFree(d_wc);
         if (h_wc) cudaFreeHost(h_wc);
         for (auto e : wf_ev) if (e) cudaEventDestroy(e);
+        for (auto& t : wf_t) for (auto e : t) if (e) cudaEventDestroy(e);
         if (d_ctr) cudaFree(d_ctr);
         if (d_work) cudaFree(d_work);
         if (h_ctr) cudaFreeHost(h_ctr);
@@ -201,7 +205,7 @@ uint32_t g_refill_below = 0xFFFFFFFFu;
 uint32_t refill_below_default() {
     if (g_refill_below == 0xFFFFFFFFu) {
         const char* e = std::getenv("RTW_REFILL_BELOW");
-        g_refill_below = e ? (uint32_t)std::atoi(e) : 16u;
+        g_refill_below = e ? (uint32_t)std::atoi(e) : 1u;
     }
     return g_refill_below;
 }
@@ -251,15 +255,18 @@ int pool_alloc(rtw_scene* s, T** p, size_t n) {
 int ensure_pool(rtw_scene* s) {
     if (s->pool.capacity) return RTW_OK;
     uint32_t cap = env_u32("RTW_WF_POOL", 1u << 21);
-    cap = std::max(cap, 4096u) & ~127u;
+    cap = std::max(cap, 4096u) & ~255u;
     int rc;
-    if ((rc = pool_alloc(s, &s->pool.ray_o, cap)) || (rc = pool_alloc(s, &s->pool.ray_d, cap)) ||
-        (rc = pool_alloc(s, &s->pool.id, cap)) || (rc = pool_alloc(s, &s->pool.hit, cap)) ||
-        (rc = pool_alloc(s, &s->pool.thr, cap)) || (rc = pool_alloc(s, &s->pool.rad, cap)) ||
-        (rc = pool_alloc(s, &s->pool.queue[0], cap)) || (rc = pool_alloc(s, &s->pool.queue[1], cap))) return rc;
+    for (int k = 0; k < 2; ++k) {
+        WfQueue& q = s->pool.q[k];
+        if ((rc = pool_alloc(s, &q.o, cap)) || (rc = pool_alloc(s, &q.d, cap)) || (rc = pool_alloc(s, &q.id, cap)) ||
+            (rc = pool_alloc(s, &q.thr, cap)) || (rc = pool_alloc(s, &q.rad, cap))) return rc;
+    }
+    if ((rc = pool_alloc(s, &s->pool.hit, cap))) return rc;
     CK(cudaMalloc(&s->d_wc, sizeof(WfCounters)));
     CK(cudaMallocHost(&s->h_wc, 4 * sizeof(WfCounters)));
     for (auto& e : s->wf_ev) CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    for (auto& t : s->wf_t) for (auto& e : t) CK(cudaEventCreate(&e));
     CK(wf_extend_occupancy_fast(&s->occ_wf[0], s->smem_bytes));
     CK(wf_extend_occupancy_strict(&s->occ_wf[1], s->smem_bytes));
     CK(wf_extend_occupancy_count(&s->occ_wf[2], s->smem_bytes));
@@ -278,7 +285,8 @@ int enqueue_wavefront(rtw_scene* s, const RenderParams& P, int variant, float* d
     L.tiles_y = (P.row_count + 3u) / 4u;
     L.stack_words = s->stack_words;
     L.smem_bytes = s->smem_bytes;
-    L.fetch_min = std::min(32u, std::max(1u, env_u32("RTW_WF_FETCH_MIN", 8u)));
+    L.fetch_min = std::min(32u, std::max(1u, env_u32("RTW_WF_FETCH_MIN", 16u)));
+    L.chunk = std::max(32u, env_u32("RTW_WF_CHUNK", 32u));
     L.extend_grid = s->sm_count * std::max(1, s->occ_wf[variant]);
     L.shade_grid = (int)(s->pool.capacity / RTW_WF_SHADE_BLOCK);
     WfCounters init{};
@@ -295,14 +303,21 @@ int enqueue_wavefront(rtw_scene* s, const RenderParams& P, int variant, float* d
                : variant == 2 ? launch_wf_shade_count(s->d, P, s->pool, s->d_wc, s->d_ctr, d_out, cur, init_pass, L, st)
                               : launch_wf_shade_fast(s->d, P, s->pool, s->d_wc, s->d_ctr, d_out, cur, init_pass, L, st);
     };
+    s->wf_timed = 0;
     CK(shade(1u, 1));                       // first fill: writes queue[0]
     s->launches += 1;
     const uint32_t batch = std::max(1u, env_u32("RTW_WF_BATCH", 8u));
     uint32_t it = 0;
     for (uint32_t k = 0;; ++k) {
         for (uint32_t b = 0; b < batch; ++b, ++it) {
+            // every 8th round, from the 4th on, is bracketed with events (the last kTimed samples are kept)
+            const bool timed = (it & 7u) == 3u;
+            cudaEvent_t* te = s->wf_t[s->wf_timed % rtw_scene::kTimed];
+            if (timed) CK(cudaEventRecord(te[0], st));
             CK(extend(it & 1u));
+            if (timed) CK(cudaEventRecord(te[1], st));
             CK(shade(it & 1u, 0));
+            if (timed) { CK(cudaEventRecord(te[2], st)); ++s->wf_timed; }
         }
         s->launches += 2ull * batch;
         // after `batch` iterations the live queue is queue[it & 1]
@@ -315,6 +330,7 @@ int enqueue_wavefront(rtw_scene* s, const RenderParams& P, int variant, float* d
             if (s->h_wc[j].n_queue[live_q] == 0u && s->h_wc[j].next_path >= s->h_wc[j].total_paths) break;
         }
     }
+    s->wf_iterations = it;
     s->wf_paths = (uint64_t)P.cam.width * P.row_count * P.sample_count;
     if (!first_hit_integrator(P.integrator) && P.depth < 1u) s->wf_paths = s->wf_paths;   // black frame, still counted
     return RTW_OK;
@@ -333,7 +349,9 @@ int enqueue_render(rtw_scene* s, const rtw_camera* cam, const rtw_render_opts* o
     CK(cudaMemsetAsync(s->d_ctr, 0, sizeof(Counters), st));
     CK(cudaMemsetAsync(s->d_work, 0, sizeof(uint32_t), st));
     CK(cudaEventRecord(s->ev0, st));
-    s->last_wavefront = (o->flags & RTW_FLAG_WAVEFRONT) != 0;
+    if ((o->flags & RTW_FLAG_WAVEFRONT) && (o->flags & RTW_FLAG_MEGAKERNEL)) return fail(RTW_E_INVALID, "both pipeline flags set");
+    const uint64_t n_paths = (uint64_t)cam->width * P.row_count * P.sample_count;
+    s->last_wavefront = (o->flags & RTW_FLAG_WAVEFRONT) || (!(o->flags & RTW_FLAG_MEGAKERNEL) && n_paths >= (1ull << 18));
     if (s->last_wavefront) {
         s->launches = 0;
         if ((rc = enqueue_wavefront(s, P, variant, d_out, st))) return rc;
@@ -501,8 +519,31 @@ int rtw_get_stats(rtw_scene* scene, rtw_stats* out) {
     out->gpu_launches = scene->launches;
     out->nodes = scene->h_ctr->nodes; out->sphere_tests = scene->h_ctr->spheres; out->quad_tests = scene->h_ctr->quads;
     out->instance_tests = scene->h_ctr->instances; out->hits = scene->h_ctr->hits;
+    if (scene->last_wavefront) {
+        out->iterations = scene->wf_iterations;
+        const int n = std::min(scene->wf_timed, (int)rtw_scene::kTimed);
+        double se = 0.0, ss = 0.0;
+        for (int k = 0; k < n; ++k) {
+            float a = 0.f, b = 0.f;
+            CK(cudaEventElapsedTime(&a, scene->wf_t[k][0], scene->wf_t[k][1]));
+            CK(cudaEventElapsedTime(&b, scene->wf_t[k][1], scene->wf_t[k][2]));
+            se += a; ss += b;
+        }
+        if (n > 0) { out->extend_ms = (float)(se / n); out->shade_ms = (float)(ss / n); }
+    }
     CK(cudaEventElapsedTime(&out->kernel_ms, scene->ev0, scene->ev1));
     CK(cudaEventElapsedTime(&out->total_ms, scene->ev0, scene->ev2));
+    return RTW_OK;
+}
+
+int rtw_get_sched_stats(rtw_scene* scene, uint64_t out[9]) {
+    if (!scene || !out) return fail(RTW_E_INVALID, "null argument");
+    std::memset(out, 0, 9 * sizeof(uint64_t));
+    if (!scene->have_stats) return RTW_OK;
+    CK(cudaSetDevice(scene->device));
+    CK(cudaEventSynchronize(scene->ev2));
+    out[0] = scene->h_ctr->sched_iters;
+    for (int k = 0; k < 4; ++k) { out[1 + k] = scene->h_ctr->sched_steps[k]; out[5 + k] = scene->h_ctr->sched_lanes[k]; }
     return RTW_OK;
 }
 

@@ -95,7 +95,8 @@ struct Instance {
     uint32_t pad0, pad1;
     Level level;
 };
-enum : uint32_t { INST_VOLUME = 1u, INST_ROT_IDENTITY = 2u };
+enum : uint32_t { INST_VOLUME = 1u, INST_ROT_IDENTITY = 2u,
+                  INST_ONE_SPHERE = 4u };   // the level is exactly one static sphere (Instance::new_sphere of one sphere)
 
 struct Quad {   // quad.rs:8-20 with normal/d/w derived as quad.rs:93-105. 64 B.
     float4 q0;  // normal.xyz, d

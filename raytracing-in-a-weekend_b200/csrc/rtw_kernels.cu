@@ -112,7 +112,7 @@ mega_kernel(const Scene sc, const RenderParams P, float* __restrict__ sum, Count
                 if (walking == 0u) break;
                 if ((uint32_t)__popc(walking) < L.refill_below && next < n_total &&
                     __any_sync(FULL, alive && T.cur == CUR_DONE)) break;
-                if (T.cur < NODE_LIMIT) trav_step_node(cx, T, S);
+                if (T.cur < NODE_LIMIT) trav_step_node<true>(cx, T, S);
                 if (T.cur >= NODE_LIMIT && T.cur != CUR_DONE) trav_step_other(cx, path.ray.time, T, S);
             }
             // ---- shade / scatter every lane whose search is over
@@ -167,9 +167,13 @@ mega_kernel(const Scene sc, const RenderParams P, float* __restrict__ sum, Count
 // Wavefront pipeline (see rtw_kernels.h): extend + shade over a pool of path slots in HBM.
 // =====================================================================================
 
-// extend: Scene::collision_normal for every ray of queue[cur]. Persistent warps; a lane whose
-// search is over stores its hit and, once `fetch_min` lanes of the warp are idle, the idle lanes
-// take the next rays of the queue (one atomic per fetch), so the walk loop stays populated.
+__device__ __forceinline__ void prefetch_l1(const void* p) { asm volatile("prefetch.global.L1 [%0];" ::"l"(p)); }
+
+// extend: Scene::collision_normal for every ray of queue[cur]. Persistent warps. A warp reserves
+// `chunk` consecutive queue positions with one atomic; whenever `fetch_min` of its lanes are idle
+// they take the next positions of the chunk (already prefetched into L1) and join the walk loop,
+// so the loop stays populated while the rays differ wildly in length. A lane whose search is over
+// stores (t, primitive) at its ray's position.
 __global__ void __launch_bounds__(RTW_WF_BLOCK)
 wf_extend_kernel(const Scene sc, const RenderParams P, const WfPool pool, WfCounters* __restrict__ wc,
                  Counters* __restrict__ ctr, const uint32_t cur, const WfLaunch L) {
@@ -180,7 +184,7 @@ wf_extend_kernel(const Scene sc, const RenderParams P, const WfPool pool, WfCoun
     Stack S; S.base = s_stack + threadIdx.x; S.stride = RTW_WF_BLOCK;
     if (blockIdx.x == 0 && threadIdx.x == 0) wc->n_queue[cur ^ 1u] = 0u;   // shade of this iteration appends there
     const uint32_t n = wc->n_queue[cur];
-    const uint32_t* __restrict__ q = pool.queue[cur];
+    const WfQueue q = pool.q[cur];
 #if defined(RTW_COUNT_WORK)
     Work wk = {0u, 0u, 0u, 0u, 0u};
     Work* const wp = &wk;
@@ -189,35 +193,69 @@ wf_extend_kernel(const Scene sc, const RenderParams P, const WfPool pool, WfCoun
 #endif
     TraceCtx cx; cx.sc = &sc; cx.k0 = P.k0; cx.k1 = P.k1; cx.pixel = 0u; cx.sample = 0u; cx.bounce = 0u;
     cx.mint = P.mint; cx.maxt = P.maxt; cx.work = wp;
+#if defined(RTW_COUNT_WORK)
+    uint32_t sc_iters = 0u, sc_steps[4] = {0u, 0u, 0u, 0u}, sc_lanes[4] = {0u, 0u, 0u, 0u};
+#define SCHED_COUNT(what, k, n) SCHED_COUNT_##what(k, n)
+#define SCHED_COUNT_iters(k, n) (++sc_iters)
+#define SCHED_COUNT_step(k, n) (++sc_steps[k], sc_lanes[k] += (uint32_t)(n))
+#else
+#define SCHED_COUNT(what, k, n) ((void)0)
+#endif
     Trav T; T.cur = CUR_DONE;
-    uint32_t slot = 0u;
+    uint32_t pos = 0u;
     float time = 0.f;
     bool busy = false, more = n > 0u;
+    uint32_t c_pos = 0u, c_end = 0u;                      // the warp's reserved chunk (uniform)
     for (;;) {
         const uint32_t idle = __ballot_sync(FULL, !busy);
         if (idle == FULL && !more) break;
         if (more && (uint32_t)__popc(idle) >= L.fetch_min) {
-            const uint32_t cnt = __popc(idle);
-            uint32_t base = 0u;
-            if (lane == 0u) base = atomicAdd(&wc->head, cnt);
-            base = __shfl_sync(FULL, base, 0);
-            more = base + cnt < n;
-            const uint32_t my = base + __popc(idle & lt_mask);
-            if (!busy && my < n) {
-                slot = q[my];
-                const float4 ro = pool.ray_o[slot], rd = pool.ray_d[slot];
-                const uint2 id = pool.id[slot];
+            if (c_pos >= c_end) {
+                uint32_t base = 0u;
+                if (lane == 0u) base = atomicAdd(&wc->head, L.chunk);
+                base = __shfl_sync(FULL, base, 0);
+                c_pos = base; c_end = min(base + L.chunk, n);
+                if (base >= n) { more = false; c_end = c_pos; }
+            }
+            const uint32_t take = min((uint32_t)__popc(idle), c_end - c_pos);
+            SCHED_COUNT(step, 3, take);
+            const uint32_t rank = __popc(idle & lt_mask);
+            if (!busy && rank < take) {
+                pos = c_pos + rank;
+                const float4 ro = q.o[pos], rd = q.d[pos];
+                const uint2 id = q.id[pos];
                 Ray r; r.o = v3(ro.x, ro.y, ro.z); r.d = v3(rd.x, rd.y, rd.z); r.time = ro.w;
                 time = ro.w;
                 cx.pixel = id.x; cx.sample = id.y; cx.bounce = f2u(rd.w);
                 trav_begin(cx, r, T, S);
                 busy = true;
             }
+            c_pos += take;
+            if (c_pos + lane < c_end) {                   // the next positions of the chunk -> L1
+                prefetch_l1(&q.o[c_pos + lane]); prefetch_l1(&q.d[c_pos + lane]);
+                if ((lane & 1u) == 0u) prefetch_l1(&q.id[c_pos + lane]);
+            }
         }
-        if (T.cur < NODE_LIMIT) trav_step_node(cx, T, S);
-        if (T.cur >= NODE_LIMIT && T.cur != CUR_DONE) trav_step_other(cx, time, T, S);
+        // ---- one step of ONE kind per iteration: the kind most lanes are waiting for. Lanes in
+        // other states sit the iteration out, so that the rarer, dearer steps (primitive tests,
+        // instance entry / exit) run with many lanes at once instead of after every node step.
+        const uint32_t on_node = __ballot_sync(FULL, T.cur < NODE_LIMIT);
+        const uint32_t on_prim = __ballot_sync(FULL, ref_is_prim(T.cur));
+        const uint32_t on_event = __ballot_sync(FULL, ref_is_event(T.cur));
+        const int cn = __popc(on_node), cp = __popc(on_prim), ce = __popc(on_event);
+        SCHED_COUNT(iters, 0, 0);
+        if (cn >= cp && cn >= ce) {
+            SCHED_COUNT(step, 0, cn);
+            if (T.cur < NODE_LIMIT) trav_step_node<false>(cx, T, S);
+        } else if (cp >= ce) {
+            SCHED_COUNT(step, 1, cp);
+            if (ref_is_prim(T.cur)) trav_step_prim(cx, T, S);
+        } else {
+            SCHED_COUNT(step, 2, ce);
+            if (ref_is_event(T.cur)) trav_step_event(cx, time, T, S);
+        }
         if (busy && T.cur == CUR_DONE) {
-            pool.hit[slot] = make_uint4(f2u(T.t), T.ref, T.inner, 0u);
+            pool.hit[pos] = make_uint4(f2u(T.t), T.ref, T.inner, 0u);
             busy = false;
         }
     }
@@ -226,28 +264,53 @@ wf_extend_kernel(const Scene sc, const RenderParams P, const WfPool pool, WfCoun
                        w3 = warp_sum_u64(wk.instances);
     if (lane == 0) {
         atomicAdd(&ctr->nodes, w0); atomicAdd(&ctr->spheres, w1); atomicAdd(&ctr->quads, w2); atomicAdd(&ctr->instances, w3);
+        atomicAdd(&ctr->sched_iters, (unsigned long long)sc_iters);
+        for (int k = 0; k < 4; ++k) {
+            atomicAdd(&ctr->sched_steps[k], (unsigned long long)sc_steps[k]);
+            atomicAdd(&ctr->sched_lanes[k], (unsigned long long)sc_lanes[k]);
+        }
     }
 #endif
+#undef SCHED_COUNT
 }
 
-// shade: one thread per entry of queue[cur] (or, with init != 0, per pool slot: first fill).
+// Exclusive prefix of one flag per thread over the block + the block total, via ballots.
+// Returns this thread's rank among the flagged threads; *total is valid for every thread.
+__device__ __forceinline__ uint32_t block_rank(bool flag, uint32_t* s_warp /*[blockDim/32 + 1]*/, uint32_t* total) {
+    const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
+    const uint32_t m = __ballot_sync(0xFFFFFFFFu, flag);
+    if (lane == 0u) s_warp[warp] = __popc(m);
+    __syncthreads();
+    uint32_t before = 0u, all = 0u;
+    for (uint32_t w = 0; w < nw; ++w) { const uint32_t c = s_warp[w]; all += c; if (w < warp) before += c; }
+    __syncthreads();
+    *total = all;
+    return before + __popc(m & ((1u << lane) - 1u));
+}
+
+// shade: one thread per queue position (all `capacity` of them, so that empty positions can start
+// camera samples too and the queue refills to capacity every iteration). init != 0: first fill.
 __global__ void __launch_bounds__(RTW_WF_SHADE_BLOCK)
 wf_shade_kernel(const Scene sc, const RenderParams P, const WfPool pool, WfCounters* __restrict__ wc,
                 Counters* __restrict__ ctr, float* __restrict__ sum, const uint32_t cur, const int init, const WfLaunch L) {
-    const uint32_t FULL = 0xFFFFFFFFu;
-    const uint32_t lane = threadIdx.x & 31u;
-    const uint32_t lt_mask = (1u << lane) - 1u;
+    __shared__ uint32_t s_warp[RTW_WF_SHADE_BLOCK / 32];
+    __shared__ unsigned long long s_base_path;
+    __shared__ uint32_t s_base_q;
     const uint32_t e = blockIdx.x * blockDim.x + threadIdx.x;
-    const uint32_t n = init ? pool.capacity : wc->n_queue[cur];
-    if ((blockIdx.x * blockDim.x) >= n) return;            // whole block beyond the queue
+    const uint32_t n = init ? 0u : wc->n_queue[cur];
+    const unsigned long long total = wc->total_paths;
+    // nothing to shade and nothing left to start: the whole block leaves (next_path only grows)
+    __shared__ int s_skip;
+    if (threadIdx.x == 0u) s_skip = (blockIdx.x * blockDim.x >= n && wc->next_path >= total) ? 1 : 0;
+    __syncthreads();
+    if (s_skip) return;
     if (e == 0u) {
         wc->head = 0u;                                      // this iteration's extend is over
         wc->iterations += 1ull;
         if (!init) atomicAdd(&ctr->rays, (unsigned long long)n);
     }
-    const bool have = e < n;
-    const uint32_t slot = have ? (init ? e : pool.queue[cur][e]) : 0u;
     const uint32_t W = P.cam.width;
+    const WfQueue qi = pool.q[cur], qo = pool.q[cur ^ 1u];
 #if defined(RTW_COUNT_WORK)
     Work wk = {0u, 0u, 0u, 0u, 0u};
     Work* const wp = &wk;
@@ -257,11 +320,11 @@ wf_shade_kernel(const Scene sc, const RenderParams P, const WfPool pool, WfCount
     Path path;
     bool alive = false;
     uint32_t n_nan = 0u;
-    if (have && !init) {
-        const float4 ro = pool.ray_o[slot], rd = pool.ray_d[slot];
-        const uint2 id = pool.id[slot];
-        const uint4 hit = pool.hit[slot];
-        const float4 thr = pool.thr[slot], rad = pool.rad[slot];
+    if (e < n) {
+        const float4 ro = qi.o[e], rd = qi.d[e];
+        const uint2 id = qi.id[e];
+        const uint4 hit = pool.hit[e];
+        const float4 thr = qi.thr[e], rad = qi.rad[e];
         path.ray.time = ro.w;
         path.thr = v3(thr.x, thr.y, thr.z); path.rad = v3(rad.x, rad.y, rad.z);
         path.pixel = id.x; path.sample = id.y; path.block = f2u(thr.w);
@@ -282,55 +345,46 @@ wf_shade_kernel(const Scene sc, const RenderParams P, const WfPool pool, WfCount
             alive = true;
         }
     }
-    // ---- regeneration: free slots take the next camera samples, tile-major so that primary rays of a warp stay coherent
-    bool need = have && !alive;
-    const unsigned long long total = wc->total_paths;
-    const bool path_dead_on_arrival = !first_hit_integrator(P.integrator) && P.depth < 1u;
-    for (;;) {
-        const uint32_t m = __ballot_sync(FULL, need);
-        if (m == 0u) break;
-        unsigned long long base = 0ull;
-        if (lane == 0u) base = atomicAdd(&wc->next_path, (unsigned long long)__popc(m));
-        base = __shfl_sync(FULL, base, 0);
-        if (base >= total) break;
-        if (need) {
-            const unsigned long long k = base + __popc(m & lt_mask);
-            if (k >= total) { need = false; }
-            else {
-                const uint32_t pix = (uint32_t)(k & 31ull);
-                const unsigned long long g = k >> 5;
-                const uint32_t tile = (uint32_t)(g / P.sample_count), s = P.sample_begin + (uint32_t)(g % P.sample_count);
-                const uint32_t tx = tile % L.tiles_x, ty = tile / L.tiles_x;
-                const uint32_t i = tx * 8u + (pix & 7u), jr = ty * 4u + (pix >> 3);
-                if (i < W && jr < P.row_count && !path_dead_on_arrival) {
-                    generate(P, i, P.row_begin + jr, s, path);
-                    alive = true; need = false;
-                }
+    // ---- regeneration: free threads take the next camera samples, tile-major (8x4 pixels x one
+    // sample per 32 consecutive indices) so that the primary rays of a warp stay coherent
+    const bool need = !alive && !(!first_hit_integrator(P.integrator) && P.depth < 1u);
+    uint32_t n_need;
+    const uint32_t r_need = block_rank(need, s_warp, &n_need);
+    if (n_need != 0u) {
+        if (threadIdx.x == 0u) s_base_path = atomicAdd(&wc->next_path, (unsigned long long)n_need);
+        __syncthreads();
+        const unsigned long long k = s_base_path + r_need;
+        if (need && k < total) {
+            const uint32_t pix = (uint32_t)(k & 31ull);
+            const unsigned long long g = k >> 5;
+            const uint32_t tile = (uint32_t)(g / P.sample_count), s = P.sample_begin + (uint32_t)(g % P.sample_count);
+            const uint32_t tx = tile % L.tiles_x, ty = tile / L.tiles_x;
+            const uint32_t i = tx * 8u + (pix & 7u), jr = ty * 4u + (pix >> 3);
+            if (i < W && jr < P.row_count) {
+                generate(P, i, P.row_begin + jr, s, path);
+                alive = true;
             }
         }
     }
-    if (alive) {
-        pool.ray_o[slot] = make_float4(path.ray.o.x, path.ray.o.y, path.ray.o.z, path.ray.time);
-        pool.ray_d[slot] = make_float4(path.ray.d.x, path.ray.d.y, path.ray.d.z, u2f(P.depth - path.depth_left));
-        pool.id[slot] = make_uint2(path.pixel, path.sample);
-        pool.thr[slot] = make_float4(path.thr.x, path.thr.y, path.thr.z, u2f(path.block));
-        pool.rad[slot] = make_float4(path.rad.x, path.rad.y, path.rad.z,
-                                     u2f(path.depth_left | (path.poison ? 0x80000000u : 0u)));
+    // ---- append the live paths to the next queue
+    uint32_t n_live;
+    const uint32_t r_live = block_rank(alive, s_warp, &n_live);
+    if (n_live != 0u) {
+        if (threadIdx.x == 0u) s_base_q = atomicAdd(&wc->n_queue[cur ^ 1u], n_live);
+        __syncthreads();
+        if (alive) {
+            const uint32_t o = s_base_q + r_live;
+            qo.o[o] = make_float4(path.ray.o.x, path.ray.o.y, path.ray.o.z, path.ray.time);
+            qo.d[o] = make_float4(path.ray.d.x, path.ray.d.y, path.ray.d.z, u2f(P.depth - path.depth_left));
+            qo.id[o] = make_uint2(path.pixel, path.sample);
+            qo.thr[o] = make_float4(path.thr.x, path.thr.y, path.thr.z, u2f(path.block));
+            qo.rad[o] = make_float4(path.rad.x, path.rad.y, path.rad.z,
+                                    u2f(path.depth_left | (path.poison ? 0x80000000u : 0u)));
+        }
     }
-    const uint32_t live = __ballot_sync(FULL, alive);
-    if (live != 0u) {
-        uint32_t base = 0u;
-        if (lane == 0u) base = atomicAdd(&wc->n_queue[cur ^ 1u], (uint32_t)__popc(live));
-        base = __shfl_sync(FULL, base, 0);
-        if (alive) pool.queue[cur ^ 1u][base + __popc(live & lt_mask)] = slot;
-    }
-    if (__any_sync(FULL, n_nan != 0u)) {
-        unsigned long long nn = warp_sum_u64(n_nan);
-        if (lane == 0u) atomicAdd(&ctr->nan_paths, nn);
-    }
+    if (n_nan != 0u) atomicAdd(&ctr->nan_paths, (unsigned long long)n_nan);
 #if defined(RTW_COUNT_WORK)
-    unsigned long long w4 = warp_sum_u64(wk.hits);
-    if (lane == 0 && w4) atomicAdd(&ctr->hits, w4);
+    if (wk.hits) atomicAdd(&ctr->hits, (unsigned long long)wk.hits);
 #endif
 }
 

@@ -12,6 +12,9 @@ namespace rtw {
 struct Counters {
     unsigned long long paths, rays, nan_paths;
     unsigned long long nodes, spheres, quads, instances, hits;   // only from the RTW_COUNT_WORK build
+    // warp scheduling of wf_extend (RTW_COUNT_WORK build): iterations, and per step kind how often
+    // it ran and with how many lanes in total. [0] node [1] prim [2] event [3] fetch
+    unsigned long long sched_iters, sched_steps[4], sched_lanes[4];
 };
 
 // Work decomposition of the persistent-lane megakernel: an item is one 8x4 pixel tile x one chunk
@@ -28,24 +31,28 @@ struct MegaLaunch {
     size_t smem_bytes;     // dynamic shared memory: stack_words * block * 4
 };
 
-// ---- wavefront pipeline (RTW_FLAG_WAVEFRONT): a pool of path slots in HBM, SoA, and two queues of
-// slot indices. One iteration = extend (persistent warps pull rays from queue[cur], walk the BVH,
-// store the closest hit) + shade (one thread per queue entry: miss / Hit / scatter; finished paths
-// add their radiance to the frame and the slot takes the next camera sample; live slots are
-// appended to queue[cur^1] with one warp-aggregated atomic).
-struct WfPool {
-    float4* ray_o;       // origin.xyz, time
-    float4* ray_d;       // direction.xyz, bits(bounce)
+// ---- wavefront pipeline (RTW_FLAG_WAVEFRONT): the paths in flight live in HBM as two queues of
+// path records (SoA), streamed back and forth. One iteration =
+//   extend  persistent warps pull consecutive rays of queue[cur] (chunk reservation + L1 prefetch),
+//           walk the BVH and store the closest hit at the ray's queue position;
+//   shade   one thread per position: miss / Hit / scatter. A finished path adds its radiance to
+//           the frame and its thread starts the next camera sample; every live path is appended
+//           to queue[cur^1] (ballot + one atomic per block), so the queue stays dense and full.
+struct WfQueue {
+    float4* o;           // origin.xyz, time
+    float4* d;           // direction.xyz, bits(bounce)
     uint2*  id;          // pixel index, sample index (Philox counter words 0/1)
-    uint4*  hit;         // bits(t), ref, inner, 0       (extend -> shade)
     float4* thr;         // throughput.xyz, bits(next Philox block)
     float4* rad;         // radiance.xyz, bits(depth_left | poison << 31)
-    uint32_t* queue[2];
+};
+struct WfPool {
+    WfQueue q[2];
+    uint4*  hit;         // bits(t), ref, inner, 0   (extend -> shade, by queue position)
     uint32_t capacity;
 };
 struct WfCounters {
     uint32_t n_queue[2];             // entries of queue[k]
-    uint32_t head;                   // extend's fetch cursor into queue[cur]
+    uint32_t head;                   // extend's reservation cursor into queue[cur]
     uint32_t pad;
     unsigned long long next_path;    // next camera sample to hand out (tile-major order)
     unsigned long long total_paths;  // 32 * tiles * samples of this render (edge-tile padding included)
@@ -55,11 +62,12 @@ struct WfLaunch {
     uint32_t tiles_x, tiles_y;
     uint32_t stack_words;
     uint32_t fetch_min;              // extend fetches new rays when at least this many lanes are idle
+    uint32_t chunk;                  // queue positions a warp reserves per atomic
     int extend_grid, shade_grid;
     size_t smem_bytes;
 };
 #define RTW_WF_BLOCK 128
-#define RTW_WF_SHADE_BLOCK 128
+#define RTW_WF_SHADE_BLOCK 256
 
 #define RTW_MEGA_BLOCK 128
 #define RTW_SMEM_NOISES 2

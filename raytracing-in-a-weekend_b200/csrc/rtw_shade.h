@@ -363,7 +363,7 @@ RTW_HD bool path_step(const Scene& sc, const Noise* nt, const RenderParams& P, P
     Trav T;
     if (!segment_begin(cx, P, p, T, S)) return true;
     while (T.cur != CUR_DONE) {
-        if (T.cur < NODE_LIMIT) trav_step_node(cx, T, S);
+        if (T.cur < NODE_LIMIT) trav_step_node<true>(cx, T, S);
         else trav_step_other(cx, p.ray.time, T, S);
     }
     ++rays;

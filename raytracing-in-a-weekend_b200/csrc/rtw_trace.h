@@ -174,15 +174,18 @@ RTW_HD void trav_set_ray(Trav& T, V3 o, V3 d) {
 // The slab test of AABB/QuadAABB/IAABB::collision_normal (aabb.rs:109-126): miss iff
 // max(tx0,ty0,tz0,mint) > min(tx1,ty1,tz1,maxt). With finite 1/d no NaN can arise, so
 // fminf/fmaxf equal the reference's minf/maxf.
-RTW_HD bool slab(V3 lo, V3 hi, const Trav& T, float mint, float maxt, float& tnear) {
-    if (trav_slow(T)) return slab_slow(lo, hi, T.o, T.d, mint, maxt, tnear);
-    float x1 = (lo.x - T.o.x) * T.inv.x, x2 = (hi.x - T.o.x) * T.inv.x;
-    float y1 = (lo.y - T.o.y) * T.inv.y, y2 = (hi.y - T.o.y) * T.inv.y;
-    float z1 = (lo.z - T.o.z) * T.inv.z, z2 = (hi.z - T.o.z) * T.inv.z;
+RTW_HD bool slab_ray(V3 lo, V3 hi, V3 o, V3 d, V3 inv, bool slow, float mint, float maxt, float& tnear) {
+    if (slow) return slab_slow(lo, hi, o, d, mint, maxt, tnear);
+    float x1 = (lo.x - o.x) * inv.x, x2 = (hi.x - o.x) * inv.x;
+    float y1 = (lo.y - o.y) * inv.y, y2 = (hi.y - o.y) * inv.y;
+    float z1 = (lo.z - o.z) * inv.z, z2 = (hi.z - o.z) * inv.z;
     float mn = fmaxf(fmaxf(fminf(x1, x2), fminf(y1, y2)), fmaxf(fminf(z1, z2), mint));
     float mx = fminf(fminf(fmaxf(x1, x2), fmaxf(y1, y2)), fminf(fmaxf(z1, z2), maxt));
     tnear = mn;
     return !(mn > mx);
+}
+RTW_HD bool slab(V3 lo, V3 hi, const Trav& T, float mint, float maxt, float& tnear) {
+    return slab_ray(lo, hi, T.o, T.d, T.inv, trav_slow(T), mint, maxt, tnear);
 }
 
 // Moving spheres of a level: t=0 leaf box against the un-shrunk interval (aabb.rs:27-38,109-126),
@@ -253,6 +256,7 @@ RTW_HD bool ref_is_prim(uint32_t r) { return (r - NODE_LIMIT) < 0x80000000u; }  
 // T.cur is an internal node: both child boxes; sphere / quad children whose box is crossed are
 // tested on the spot (they are leaves: nothing to descend into), node / instance children are
 // visited nearer first with the other one stacked.
+template <bool INLINE_PRIMS>
 RTW_HD void trav_step_node(const TraceCtx& cx, Trav& T, const Stack& S) {
     RTW_COUNT(cx, nodes);
     const Node* np = &cx.sc->nodes[T.cur];
@@ -261,7 +265,7 @@ RTW_HD void trav_step_node(const TraceCtx& cx, Trav& T, const Stack& S) {
     float t0, t1;
     bool h0 = slab(v3(n0.x, n0.y, n0.z), v3(n0.w, n1.x, n1.y), T, cx.mint, T.t, t0);
     bool h1 = slab(v3(n1.z, n1.w, n2.x), v3(n2.y, n2.z, n2.w), T, cx.mint, T.t, t1);
-    const bool p0 = h0 && ref_is_prim(n3.x), p1 = h1 && ref_is_prim(n3.y);
+    const bool p0 = INLINE_PRIMS && h0 && ref_is_prim(n3.x), p1 = INLINE_PRIMS && h1 && ref_is_prim(n3.y);
     if (p0 || p1) {
         uint32_t pa = p0 ? n3.x : n3.y, pb = (p0 && p1) ? n3.y : REF_NONE;
 #if defined(__CUDA_ARCH__)
@@ -288,31 +292,75 @@ RTW_HD void trav_step_node(const TraceCtx& cx, Trav& T, const Stack& S) {
     }
 }
 
+// const_density (instance.rs:24-26): ln(xi) / -density, xi from the instance's volume stream.
+RTW_HD float volume_distance(const Instance& in, const TraceCtx& cx) {
+    float xi = ctx_rand(cx, (cx.bounce << 16) | 0u, 1u + in.index).x;
+    return logf(xi) / -in.density;
+}
+
+// Instance::collision_normal for an instance that holds exactly one static sphere (C5's two
+// volumes; Instance::new_sphere of one sphere): the same steps as the general walk — frame change,
+// root (= leaf) box, sphere, constant-density probe (instance.rs:250-302) — without touching the
+// traversal state.
+RTW_HD void trav_one_sphere_instance(const TraceCtx& cx, const Instance& in, uint32_t iref, Trav& T) {
+    V3 o = T.o - v3(in.t[0], in.t[1], in.t[2]);
+    V3 d = T.d, inv = T.inv;
+    float a = T.a;
+    bool slow = trav_slow(T);
+    if (!(in.flags & INST_ROT_IDENTITY)) {
+        o = rot_apply(in.inv_rows, o); d = rot_apply(in.inv_rows, d);
+        inv = v3(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);
+        a = dot(d, d);
+        slow = !(isfinite(inv.x) && isfinite(inv.y) && isfinite(inv.z));
+    }
+    const Level& lv = in.level;
+    const V3 lo = v3(lv.lo[0], lv.lo[1], lv.lo[2]), hi = v3(lv.hi[0], lv.hi[1], lv.hi[2]);
+    float tn, t;
+    if (!slab_ray(lo, hi, o, d, inv, slow, cx.mint, T.t, tn)) return;
+    RTW_COUNT(cx, spheres);
+    const float4 s = RTW_LDG(&cx.sc->spheres[ref_index(lv.root)]);
+    const V3 c = v3(s.x, s.y, s.z);
+    if (!sphere_t(c, s.w, o, d, a, cx.mint, T.t, t)) return;
+    if (in.flags & INST_VOLUME) {
+        float distance = volume_distance(in, cx);
+        if (distance >= 0.0f) {
+            V3 o2 = (o + d * t) + d * distance;
+            float t2;
+            if (!slab_ray(lo, hi, o2, d, inv, slow, cx.mint, cx.maxt, tn)) return;
+            RTW_COUNT(cx, spheres);
+            if (!sphere_t(c, s.w, o2, d, a, cx.mint, cx.maxt, t2)) return;
+        }
+    }
+    if (closer(t, iref, T.t, T.ref)) { T.t = t; T.ref = iref; T.inner = lv.root; }
+}
+
 // Instance::collision_normal, first half (instance.rs:250-271): ray -> local frame, walk the inside.
 RTW_HD void trav_enter_instance(const TraceCtx& cx, float time, Trav& T, const Stack& S) {
     RTW_COUNT(cx, instances);
     const Instance& in = cx.sc->instances[ref_index(T.cur)];
-    // world frame of the ray: restored by trav_leave_instance
+    if (in.flags & INST_ONE_SPHERE) {
+        trav_one_sphere_instance(cx, in, T.cur, T);
+        T.cur = S.pop(T.sp);
+        return;
+    }
+    // world frame of the ray: restored by trav_level_finished
     S.push(T.sp, f2u(T.o.x)); S.push(T.sp, f2u(T.o.y)); S.push(T.sp, f2u(T.o.z));
     S.push(T.sp, f2u(T.d.x)); S.push(T.sp, f2u(T.d.y)); S.push(T.sp, f2u(T.d.z));
     S.push(T.sp, f2u(T.inv.x)); S.push(T.sp, f2u(T.inv.y)); S.push(T.sp, f2u(T.inv.z));
     S.push(T.sp, f2u(T.a));
     S.push(T.sp, CUR_EXIT);
     V3 o = T.o - v3(in.t[0], in.t[1], in.t[2]);
-    V3 d = T.d;
-    if (!(in.flags & INST_ROT_IDENTITY)) { o = rot_apply(in.inv_rows, o); d = rot_apply(in.inv_rows, d); }
     T.inst = T.cur;
     T.top_t = T.t; T.top_ref = T.ref;     // T.t stays: the inner search starts from the same bound
     T.ref = REF_NONE;
-    T.mode = TRAV_INNER;
-    trav_set_ray(T, o, d);
+    if (in.flags & INST_ROT_IDENTITY) {
+        T.o = o;                           // same direction: inv, a and the slow flag stand
+        T.mode = (T.mode & 4u) | TRAV_INNER;
+    } else {
+        T.mode = TRAV_INNER;
+        trav_set_ray(T, rot_apply(in.inv_rows, o), rot_apply(in.inv_rows, T.d));
+    }
     trav_begin_level(cx, in.level, time, T, S);
-}
-
-// const_density (instance.rs:24-26): ln(xi) / -density, xi from the instance's volume stream.
-RTW_HD float volume_distance(const Instance& in, const TraceCtx& cx) {
-    float xi = ctx_rand(cx, (cx.bounce << 16) | 0u, 1u + in.index).x;
-    return logf(xi) / -in.density;
 }
 
 // The sentinel of the level being walked came off the stack.
@@ -355,23 +403,33 @@ RTW_HD void trav_level_finished(const TraceCtx& cx, float time, Trav& T, const S
     T.cur = S.pop(T.sp);
 }
 
-// T.cur is anything but an internal node: an instance leaf, the sentinel, or a sphere / quad that is
-// the root of its level. Events are chained until the lane is back on a node (or done), so that a
-// single-primitive instance (C5's two volumes) costs one step, not five.
+// T.cur is a sphere / quad leaf (a child left on the stack by the non-inlining node step, or the
+// root of a one-primitive level).
+RTW_HD void trav_step_prim(const TraceCtx& cx, Trav& T, const Stack& S) {
+    trav_test_prim(cx, T.cur, T);
+    if ((T.mode & 3u) == TRAV_PROBE && T.ref != REF_NONE) {     // instance.rs:284-294 only asks "anything?"
+        while (S.pop(T.sp) != CUR_EXIT) {}
+        T.cur = CUR_EXIT;
+    } else {
+        T.cur = S.pop(T.sp);
+    }
+}
+
+// T.cur is an instance leaf or the sentinel. Such events are chained until the lane is back on a
+// node or a primitive (or done).
+RTW_HD bool ref_is_event(uint32_t r) { return r >= 0xC0000000u && r != CUR_DONE; }   // KIND_INSTANCE range incl. CUR_EXIT
+RTW_HD void trav_step_event(const TraceCtx& cx, float time, Trav& T, const Stack& S) {
+    do {
+        if (T.cur == CUR_EXIT) trav_level_finished(cx, time, T, S);
+        else trav_enter_instance(cx, time, T, S);
+    } while (ref_is_event(T.cur));
+}
+
+// Anything but an internal node, in one call (drivers that do not schedule step kinds separately).
 RTW_HD void trav_step_other(const TraceCtx& cx, float time, Trav& T, const Stack& S) {
     do {
-        const uint32_t cur = T.cur;
-        if (cur == CUR_EXIT) trav_level_finished(cx, time, T, S);
-        else if (ref_kind(cur) == KIND_INSTANCE) trav_enter_instance(cx, time, T, S);
-        else {
-            trav_test_prim(cx, cur, T);
-            if ((T.mode & 3u) == TRAV_PROBE && T.ref != REF_NONE) {
-                while (S.pop(T.sp) != CUR_EXIT) {}
-                T.cur = CUR_EXIT;
-            } else {
-                T.cur = S.pop(T.sp);
-            }
-        }
+        if (ref_is_prim(T.cur)) trav_step_prim(cx, T, S);
+        else trav_step_event(cx, time, T, S);
     } while (T.cur >= NODE_LIMIT && T.cur != CUR_DONE);
 }
 
@@ -382,7 +440,7 @@ RTW_HD Best trace(const TraceCtx& cx, const Ray& r, const Stack& S) {
     Trav T;
     trav_begin(cx, r, T, S);
     while (T.cur != CUR_DONE) {
-        if (T.cur < NODE_LIMIT) trav_step_node(cx, T, S);
+        if (T.cur < NODE_LIMIT) trav_step_node<true>(cx, T, S);
         else trav_step_other(cx, r.time, T, S);
     }
     return trav_result(T);

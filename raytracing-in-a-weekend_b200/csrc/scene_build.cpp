@@ -289,6 +289,7 @@ int build_host_scene(const rtw_scene_desc* d, HostScene& hs, std::string& err) {
         euler_rows(in.rotation, o.fwd_rows);      // instance.rs:303-306
         if (rot0) o.flags |= INST_ROT_IDENTITY;
         if (in.density_kind == RTW_DENSITY_CONST) o.flags |= INST_VOLUME;
+        if (in.n_spheres == 1 && in.n_quads == 0 && !smoving[in.first_sphere]) o.flags |= INST_ONE_SPHERE;
         o.level.root = REF_NONE;
         if (rot0 && t0 && in.density_kind == RTW_DENSITY_SURFACE) {
             // An untransformed surface instance is exactly its primitives: rotated(0) and "- 0" are

@@ -48,7 +48,7 @@ def _first_hit(job, ig, oracle, cuda):
     return err[np.broadcast_to(ok, err.shape)], tie.mean()
 
 
-PIPES = pytest.mark.parametrize("pipe", [0, A.RTW_FLAG_WAVEFRONT], ids=["megakernel", "wavefront"])
+PIPES = pytest.mark.parametrize("pipe", [A.RTW_FLAG_MEGAKERNEL, A.RTW_FLAG_WAVEFRONT], ids=["megakernel", "wavefront"])
 
 
 @PIPES
@@ -113,9 +113,10 @@ def test_pipelines_agree(cuda):
     job = _small(scenes.config_c5(), 160, 120, spp=16)
     vp = job.viewport
     vp.gamma = 1.0
+    vp.flags |= A.RTW_FLAG_MEGAKERNEL
     mega = vp._run(job.ray_color, job.scene, job.mode, cuda)
     sm = cuda.scene(job.scene).stats()
-    vp.flags |= A.RTW_FLAG_WAVEFRONT
+    vp.flags = (vp.flags & ~A.RTW_FLAG_MEGAKERNEL) | A.RTW_FLAG_WAVEFRONT
     wave = vp._run(job.ray_color, job.scene, job.mode, cuda)
     sw = cuda.scene(job.scene).stats()
     assert (sm.paths, sm.rays, sm.nan_paths) == (sw.paths, sw.rays, sw.nan_paths)
