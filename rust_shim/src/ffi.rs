@@ -1,0 +1,64 @@
+//! `extern "C"` declarations of include/rtw.h (ABI version 1). SOURCE ONLY: never compiled in this
+//! repository's build image (no Rust toolchain). Field order and types mirror the C structs.
+#![allow(non_camel_case_types, dead_code)]
+use std::os::raw::{c_char, c_int, c_void};
+
+pub const RTW_ABI_VERSION: u32 = 1;
+pub const RTW_OK: c_int = 0;
+
+#[repr(C)] #[derive(Clone, Copy)]
+pub struct rtw_material { pub metallicness: f32, pub opacity: f32, pub ir: f32, pub emitted: [f32; 3] }
+#[repr(C)]
+pub struct rtw_noise { pub ranvec: [[f32; 3]; 256], pub perm_x: [u32; 256], pub perm_y: [u32; 256], pub perm_z: [u32; 256] }
+#[repr(C)] #[derive(Clone, Copy)]
+pub struct rtw_texture { pub width: u32, pub height: u32, pub rgb: *const f32, pub noise_id: i32, pub noise_scale: f32 }
+#[repr(C)] #[derive(Clone, Copy)]
+pub struct rtw_sphere { pub origin: [f32; 3], pub radius: f32, pub col_mod: [f32; 3], pub velocity: [f32; 3], pub mat_id: u32, pub tex_id: u32 }
+#[repr(C)] #[derive(Clone, Copy)]
+pub struct rtw_quad { pub origin: [f32; 3], pub u: [f32; 3], pub v: [f32; 3], pub velocity: [f32; 3], pub mat_id: u32, pub tex_id: u32 }
+#[repr(C)] #[derive(Clone, Copy)]
+pub struct rtw_instance {
+    pub first_sphere: u32, pub n_spheres: u32, pub first_quad: u32, pub n_quads: u32,
+    pub translation: [f32; 3], pub rotation: [f32; 3], pub density_kind: u32, pub density: f32,
+}
+#[repr(C)]
+pub struct rtw_scene_desc {
+    pub abi_version: u32,
+    pub n_spheres: u32, pub n_top_spheres: u32, pub n_quads: u32, pub n_top_quads: u32, pub n_instances: u32,
+    pub n_materials: u32, pub n_textures: u32, pub n_noises: u32,
+    pub spheres: *const rtw_sphere, pub quads: *const rtw_quad, pub instances: *const rtw_instance,
+    pub materials: *const rtw_material, pub textures: *const rtw_texture, pub noises: *const rtw_noise,
+    pub background: [f32; 3],
+}
+#[repr(C)] #[derive(Clone, Copy, Default)]
+pub struct rtw_camera {
+    pub width: u32, pub height: u32, pub origin: [f32; 3], pub pixel00: [f32; 3],
+    pub delta_u: [f32; 3], pub delta_v: [f32; 3], pub u: [f32; 3], pub v: [f32; 3], pub lens_radius: f32,
+}
+#[repr(C)] #[derive(Clone, Copy)]
+pub struct rtw_render_opts {
+    pub samples: u32, pub depth: u32, pub gamma: f32, pub integrator: u32, pub mode: u32,
+    pub shutter_speed: f32, pub fps: f32, pub frame: u32, pub seed: u64, pub mint: f32, pub maxt: f32,
+    pub sample_begin: u32, pub sample_count: u32, pub row_begin: u32, pub row_count: u32,
+    pub output: u32, pub flags: u32,
+}
+#[repr(C)] #[derive(Clone, Copy, Default)]
+pub struct rtw_stats {
+    pub paths: u64, pub rays: u64, pub nan_paths: u64, pub gpu_launches: u64, pub kernel_ms: f32, pub total_ms: f32,
+    pub nodes: u64, pub sphere_tests: u64, pub quad_tests: u64, pub instance_tests: u64, pub hits: u64,
+    pub iterations: u64, pub extend_ms: f32, pub shade_ms: f32,
+}
+pub enum rtw_scene {}
+
+extern "C" {
+    pub fn rtw_abi_version() -> c_int;
+    pub fn rtw_last_error() -> *const c_char;
+    pub fn rtw_device_count() -> c_int;
+    pub fn rtw_render_opts_default(o: *mut rtw_render_opts);
+    pub fn rtw_scene_create(desc: *const rtw_scene_desc, device: c_int, out: *mut *mut rtw_scene) -> c_int;
+    pub fn rtw_scene_destroy(scene: *mut rtw_scene);
+    pub fn rtw_render(scene: *mut rtw_scene, cam: *const rtw_camera, opts: *const rtw_render_opts, out_rgb: *mut f32) -> c_int;
+    pub fn rtw_render_device(scene: *mut rtw_scene, cam: *const rtw_camera, opts: *const rtw_render_opts, d_out: *mut f32, stream: *mut c_void) -> c_int;
+    pub fn rtw_render_frames(scene: *mut rtw_scene, cam: *const rtw_camera, opts: *const rtw_render_opts, first: u32, n: u32, out_rgb: *mut f32) -> c_int;
+    pub fn rtw_get_stats(scene: *mut rtw_scene, out: *mut rtw_stats) -> c_int;
+}
