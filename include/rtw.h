@@ -248,8 +248,9 @@ int rtw_get_stats(rtw_scene* scene, rtw_stats* out);
 /* Warp-scheduling counters of the wavefront extend kernel, filled by RTW_FLAG_COUNT_WORK |
  * RTW_FLAG_WAVEFRONT renders: out[0] = loop iterations (per warp, summed); then for the step kinds
  * node, primitive, instance-event, fetch: out[1+k] = times the kind ran, out[5+k] = lanes it ran
- * with in total. A tuning aid (lanes/steps/32 = SIMD efficiency of that kind). */
-int rtw_get_sched_stats(rtw_scene* scene, uint64_t out[9]);
+ * with in total; out[9+k] = warp cycles spent inside steps of that kind, out[13] = warp cycles in
+ * the rest of the loop (ballots, stores). A tuning aid (lanes/steps/32 = SIMD efficiency). */
+int rtw_get_sched_stats(rtw_scene* scene, uint64_t out[14]);
 
 /* --- device micro-benchmarks: the denominators of the FP32 and L2 rooflines, which
  * MEASURED_PEAKS.json does not carry. which = RTW_BENCH_FP32 -> TFLOP/s of dependent-free FFMA

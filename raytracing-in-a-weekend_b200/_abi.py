@@ -10,7 +10,7 @@ import ctypes as C
 import os
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "csrc", "librtw_b200.so")
+LIB_PATH = os.environ.get("RTW_B200_LIB") or os.path.join(HERE, "csrc", "librtw_b200.so")   # env override: tuning builds
 
 RTW_ABI_VERSION = 1
 

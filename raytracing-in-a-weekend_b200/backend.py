@@ -68,13 +68,15 @@ class CudaSceneHandle:
 
     def sched_stats(self) -> dict:
         """Warp-scheduling counters of the last COUNT_WORK | WAVEFRONT render (tuning aid)."""
-        out = (C.c_uint64 * 9)()
+        out = (C.c_uint64 * 14)()
         A.check(self._lib.rtw_get_sched_stats(self._h, out))
         kinds = ("node", "prim", "event", "fetch")
         d = {"iterations": int(out[0])}
         for k, name in enumerate(kinds):
             steps, lanes = int(out[1 + k]), int(out[5 + k])
-            d[name] = {"steps": steps, "lanes": lanes, "lanes_per_step": lanes / steps if steps else 0.0}
+            d[name] = {"steps": steps, "lanes": lanes, "lanes_per_step": lanes / steps if steps else 0.0,
+                       "cycles": int(out[9 + k]), "cycles_per_step": int(out[9 + k]) / steps if steps else 0.0}
+        d["loop_cycles"] = int(out[13])
         return d
 
     def info(self) -> A.rtw_scene_info:

@@ -188,6 +188,7 @@ int upload_scene(rtw_scene* s, HostScene& hs) {
     if ((rc = upload(s, hs.quads, &d.quads))) return rc;
     if ((rc = upload(s, hs.quad_ids, &d.quad_ids))) return rc;
     if ((rc = upload(s, hs.instances, &d.instances))) return rc;
+    if ((rc = upload(s, hs.one_sphere, &d.one_sphere))) return rc;
     if ((rc = upload(s, hs.moving, &d.moving))) return rc;
     if ((rc = upload(s, hs.materials, &d.materials))) return rc;
     if ((rc = upload(s, hs.textures, &d.textures))) return rc;
@@ -536,14 +537,15 @@ int rtw_get_stats(rtw_scene* scene, rtw_stats* out) {
     return RTW_OK;
 }
 
-int rtw_get_sched_stats(rtw_scene* scene, uint64_t out[9]) {
+int rtw_get_sched_stats(rtw_scene* scene, uint64_t out[14]) {
     if (!scene || !out) return fail(RTW_E_INVALID, "null argument");
-    std::memset(out, 0, 9 * sizeof(uint64_t));
+    std::memset(out, 0, 14 * sizeof(uint64_t));
     if (!scene->have_stats) return RTW_OK;
     CK(cudaSetDevice(scene->device));
     CK(cudaEventSynchronize(scene->ev2));
     out[0] = scene->h_ctr->sched_iters;
     for (int k = 0; k < 4; ++k) { out[1 + k] = scene->h_ctr->sched_steps[k]; out[5 + k] = scene->h_ctr->sched_lanes[k]; }
+    for (int k = 0; k < 5; ++k) out[9 + k] = scene->h_ctr->sched_cycles[k];
     return RTW_OK;
 }
 

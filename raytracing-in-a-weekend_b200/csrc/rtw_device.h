@@ -67,12 +67,19 @@ static const uint32_t REF_NONE = 0xFFFFFFFFu;
 RTW_HD uint32_t ref_kind(uint32_t r) { return r >> 30; }
 RTW_HD uint32_t ref_index(uint32_t r) { return r & 0x3FFFFFFFu; }
 RTW_HD uint32_t make_ref(uint32_t kind, uint32_t idx) { return (kind << 30) | idx; }
+// Inside the BVH (node children, traversal stack) the reference of an instance that holds exactly
+// one static sphere carries this bit, so that the walk can treat it as a primitive test rather than
+// a level change. Search results always carry the plain reference.
+static const uint32_t REF_ONE_SPHERE_INSTANCE = 0x20000000u;
+RTW_HD uint32_t instance_index(uint32_t r) { return r & 0x1FFFFFFFu; }
 
 // ------------------------------------------------------------------ scene records (all 16-byte aligned)
-// BVH node = both children's boxes + both child references: 64 B, fetched as four 128-bit loads.
-//   n0 = (lo0.x lo0.y lo0.z hi0.x)  n1 = (hi0.y hi0.z lo1.x lo1.y)  n2 = (lo1.z hi1.x hi1.y hi1.z)
-//   n3 = (bits c0, bits c1, 0, 0)
-struct Node { float4 n0, n1, n2; uint4 n3; };
+// BVH node, 4-wide: the boxes of up to four children, one component per float4 (lane c of each
+// vector belongs to child c), and their references: 128 B = one L1/L2 line, eight 128-bit loads.
+// An unused slot has reference REF_NONE and the box [+inf,+inf]^3, which fails the slab test for
+// every ray. A child box is the child's own reference box (a primitive's leaf box, an instance's
+// world box, or the union for an inner node).
+struct Node { float4 lox, loy, loz, hix, hiy, hiz; uint4 ref; uint4 pad; };
 
 // One traversable level (the scene top level, or the inside of one instance): root reference +
 // root box (the reference slab-tests every BVH root: aabb.rs:109-126) + the level's moving
@@ -133,6 +140,7 @@ struct Scene {
     const Quad* quads;
     const uint2* quad_ids;
     const Instance* instances;
+    const float4* one_sphere;     // 4 per instance, valid for INST_ONE_SPHERE ones: (T, density) (centre, radius) (box lo, bits flags) (box hi, bits index)
     const uint32_t* moving;       // sphere indices
     const Material* materials;
     const Texture* textures;

@@ -17,6 +17,7 @@ struct HostScene {
     std::vector<Quad> quads;
     std::vector<uint2> quad_ids;
     std::vector<Instance> instances;
+    std::vector<float4> one_sphere;
     std::vector<uint32_t> moving;
     std::vector<Material> materials;
     std::vector<Texture> textures;                 // obj / texels pointers are filled by the uploader

@@ -174,7 +174,7 @@ __device__ __forceinline__ void prefetch_l1(const void* p) { asm volatile("prefe
 // they take the next positions of the chunk (already prefetched into L1) and join the walk loop,
 // so the loop stays populated while the rays differ wildly in length. A lane whose search is over
 // stores (t, primitive) at its ray's position.
-__global__ void __launch_bounds__(RTW_WF_BLOCK)
+__global__ void __launch_bounds__(RTW_WF_BLOCK, RTW_WF_EXTEND_MINB)
 wf_extend_kernel(const Scene sc, const RenderParams P, const WfPool pool, WfCounters* __restrict__ wc,
                  Counters* __restrict__ ctr, const uint32_t cur, const WfLaunch L) {
     extern __shared__ uint32_t s_stack[];                 // [stack_words][RTW_WF_BLOCK]
@@ -198,8 +198,15 @@ wf_extend_kernel(const Scene sc, const RenderParams P, const WfPool pool, WfCoun
 #define SCHED_COUNT(what, k, n) SCHED_COUNT_##what(k, n)
 #define SCHED_COUNT_iters(k, n) (++sc_iters)
 #define SCHED_COUNT_step(k, n) (++sc_steps[k], sc_lanes[k] += (uint32_t)(n))
+    unsigned long long sc_cyc[5] = {0ull, 0ull, 0ull, 0ull, 0ull};
+    long long sc_t0 = clock64(), sc_t1;
+    int sc_kind = 4;
+#define SCHED_TIME_BEGIN(k) (sc_t1 = clock64(), sc_cyc[4] += (unsigned long long)(sc_t1 - sc_t0), sc_t0 = sc_t1, sc_kind = (k))
+#define SCHED_TIME_END() (sc_t1 = clock64(), sc_cyc[sc_kind] += (unsigned long long)(sc_t1 - sc_t0), sc_t0 = sc_t1, sc_kind = 4)
 #else
 #define SCHED_COUNT(what, k, n) ((void)0)
+#define SCHED_TIME_BEGIN(k) ((void)0)
+#define SCHED_TIME_END() ((void)0)
 #endif
     Trav T; T.cur = CUR_DONE;
     uint32_t pos = 0u;
@@ -219,6 +226,7 @@ wf_extend_kernel(const Scene sc, const RenderParams P, const WfPool pool, WfCoun
             }
             const uint32_t take = min((uint32_t)__popc(idle), c_end - c_pos);
             SCHED_COUNT(step, 3, take);
+            SCHED_TIME_BEGIN(3);
             const uint32_t rank = __popc(idle & lt_mask);
             if (!busy && rank < take) {
                 pos = c_pos + rank;
@@ -235,24 +243,32 @@ wf_extend_kernel(const Scene sc, const RenderParams P, const WfPool pool, WfCoun
                 prefetch_l1(&q.o[c_pos + lane]); prefetch_l1(&q.d[c_pos + lane]);
                 if ((lane & 1u) == 0u) prefetch_l1(&q.id[c_pos + lane]);
             }
+            __syncwarp();
+            SCHED_TIME_END();
         }
         // ---- one step of ONE kind per iteration: the kind most lanes are waiting for. Lanes in
-        // other states sit the iteration out, so that the rarer, dearer steps (primitive tests,
-        // instance entry / exit) run with many lanes at once instead of after every node step.
+        // other states sit the iteration out, so that the rarer, dearer steps (leaf tests, instance
+        // entry / exit) run with many lanes at once instead of after every node step.
         const uint32_t on_node = __ballot_sync(FULL, T.cur < NODE_LIMIT);
-        const uint32_t on_prim = __ballot_sync(FULL, ref_is_prim(T.cur));
+        const uint32_t on_prim = __ballot_sync(FULL, ref_is_leaf_test(T.cur));
         const uint32_t on_event = __ballot_sync(FULL, ref_is_event(T.cur));
         const int cn = __popc(on_node), cp = __popc(on_prim), ce = __popc(on_event);
         SCHED_COUNT(iters, 0, 0);
         if (cn >= cp && cn >= ce) {
             SCHED_COUNT(step, 0, cn);
+            SCHED_TIME_BEGIN(0);
             if (T.cur < NODE_LIMIT) trav_step_node<false>(cx, T, S);
+            SCHED_TIME_END();
         } else if (cp >= ce) {
             SCHED_COUNT(step, 1, cp);
-            if (ref_is_prim(T.cur)) trav_step_prim(cx, T, S);
+            SCHED_TIME_BEGIN(1);
+            if (ref_is_leaf_test(T.cur)) trav_step_prim(cx, T, S);
+            SCHED_TIME_END();
         } else {
             SCHED_COUNT(step, 2, ce);
+            SCHED_TIME_BEGIN(2);
             if (ref_is_event(T.cur)) trav_step_event(cx, time, T, S);
+            SCHED_TIME_END();
         }
         if (busy && T.cur == CUR_DONE) {
             pool.hit[pos] = make_uint4(f2u(T.t), T.ref, T.inner, 0u);
@@ -269,9 +285,13 @@ wf_extend_kernel(const Scene sc, const RenderParams P, const WfPool pool, WfCoun
             atomicAdd(&ctr->sched_steps[k], (unsigned long long)sc_steps[k]);
             atomicAdd(&ctr->sched_lanes[k], (unsigned long long)sc_lanes[k]);
         }
+        sc_cyc[4] += (unsigned long long)(clock64() - sc_t0);
+        for (int k = 0; k < 5; ++k) atomicAdd(&ctr->sched_cycles[k], sc_cyc[k]);
     }
 #endif
 #undef SCHED_COUNT
+#undef SCHED_TIME_BEGIN
+#undef SCHED_TIME_END
 }
 
 // Exclusive prefix of one flag per thread over the block + the block total, via ballots.

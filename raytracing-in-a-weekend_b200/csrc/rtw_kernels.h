@@ -15,6 +15,7 @@ struct Counters {
     // warp scheduling of wf_extend (RTW_COUNT_WORK build): iterations, and per step kind how often
     // it ran and with how many lanes in total. [0] node [1] prim [2] event [3] fetch
     unsigned long long sched_iters, sched_steps[4], sched_lanes[4];
+    unsigned long long sched_cycles[5];   // warp cycles inside node / prim / event / fetch steps, and in the rest of the loop
 };
 
 // Work decomposition of the persistent-lane megakernel: an item is one 8x4 pixel tile x one chunk
@@ -67,6 +68,9 @@ struct WfLaunch {
     size_t smem_bytes;
 };
 #define RTW_WF_BLOCK 128
+#ifndef RTW_WF_EXTEND_MINB
+#define RTW_WF_EXTEND_MINB 1      // min resident blocks per SM asked of the compiler for wf_extend (register cap)
+#endif
 #define RTW_WF_SHADE_BLOCK 256
 
 #define RTW_MEGA_BLOCK 128

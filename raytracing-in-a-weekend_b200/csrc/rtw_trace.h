@@ -231,7 +231,7 @@ RTW_HD void trav_begin(const TraceCtx& cx, const Ray& r, Trav& T, const Stack& S
     T.t = cx.maxt; T.ref = REF_NONE; T.inner = REF_NONE;
     T.top_t = 0.0f; T.top_ref = REF_NONE;
     T.inst = REF_NONE; T.sp = 0u;
-    S.push(T.sp, CUR_EXIT);
+    S.push(T.sp, CUR_DONE);               // bottom of the stack: popping it ends the search
     trav_begin_level(cx, cx.sc->top, r.time, T, S);
 }
 
@@ -252,44 +252,98 @@ RTW_HD void trav_test_prim(const TraceCtx& cx, uint32_t ref, Trav& T) {
     if (hit && closer(t, ref, T.t, T.ref)) { T.t = t; T.ref = ref; }
 }
 RTW_HD bool ref_is_prim(uint32_t r) { return (r - NODE_LIMIT) < 0x80000000u; }   // KIND_SPHERE or KIND_QUAD
+RTW_HD bool ref_is_one_sphere_instance(uint32_t r) { return r >= 0xE0000000u && r < CUR_EXIT; }
+// what trav_step_prim handles: sphere, quad, one-sphere instance
+RTW_HD bool ref_is_leaf_test(uint32_t r) { return ref_is_prim(r) || ref_is_one_sphere_instance(r); }
 
-// T.cur is an internal node: both child boxes; sphere / quad children whose box is crossed are
-// tested on the spot (they are leaves: nothing to descend into), node / instance children are
-// visited nearer first with the other one stacked.
+// Slab tests of the four child boxes of a node: tn[c] = entry parameter if child c is crossed
+// within [mint, maxt], else +inf. Strict build / host: the reference's own operation order,
+// (bound - origin) * (1/d). Fast device build: one FFMA per plane, bound * (1/d) - origin * (1/d)
+// (differs from the reference by a rounding of the origin term: the box moves by ~1 ulp of |o|).
+RTW_HD void slab4(const Node* np, const Trav& T, float mint, float maxt, float tn[4]) {
+    const float4 lox = RTW_LDG(&np->lox), loy = RTW_LDG(&np->loy), loz = RTW_LDG(&np->loz);
+    const float4 hix = RTW_LDG(&np->hix), hiy = RTW_LDG(&np->hiy), hiz = RTW_LDG(&np->hiz);
+    const float LX[4] = {lox.x, lox.y, lox.z, lox.w}, LY[4] = {loy.x, loy.y, loy.z, loy.w}, LZ[4] = {loz.x, loz.y, loz.z, loz.w};
+    const float HX[4] = {hix.x, hix.y, hix.z, hix.w}, HY[4] = {hiy.x, hiy.y, hiy.z, hiy.w}, HZ[4] = {hiz.x, hiz.y, hiz.z, hiz.w};
+    if (trav_slow(T)) {
+        for (int c = 0; c < 4; ++c) {
+            float t;
+            bool h = slab_slow(v3(LX[c], LY[c], LZ[c]), v3(HX[c], HY[c], HZ[c]), T.o, T.d, mint, maxt, t);
+            tn[c] = h ? t : INFINITY;
+        }
+        return;
+    }
+#if defined(__CUDA_ARCH__) && !defined(RTW_STRICT_FP)
+    const float nx = -T.o.x * T.inv.x, ny = -T.o.y * T.inv.y, nz = -T.o.z * T.inv.z;
+#endif
+#if defined(__CUDA_ARCH__)
+#pragma unroll
+#endif
+    for (int c = 0; c < 4; ++c) {
+#if defined(__CUDA_ARCH__) && !defined(RTW_STRICT_FP)
+        float x1 = fmaf(LX[c], T.inv.x, nx), x2 = fmaf(HX[c], T.inv.x, nx);
+        float y1 = fmaf(LY[c], T.inv.y, ny), y2 = fmaf(HY[c], T.inv.y, ny);
+        float z1 = fmaf(LZ[c], T.inv.z, nz), z2 = fmaf(HZ[c], T.inv.z, nz);
+#else
+        float x1 = (LX[c] - T.o.x) * T.inv.x, x2 = (HX[c] - T.o.x) * T.inv.x;
+        float y1 = (LY[c] - T.o.y) * T.inv.y, y2 = (HY[c] - T.o.y) * T.inv.y;
+        float z1 = (LZ[c] - T.o.z) * T.inv.z, z2 = (HZ[c] - T.o.z) * T.inv.z;
+#endif
+        float mn = fmaxf(fmaxf(fminf(x1, x2), fminf(y1, y2)), fmaxf(fminf(z1, z2), mint));
+        float mx = fminf(fminf(fmaxf(x1, x2), fmaxf(y1, y2)), fminf(fmaxf(z1, z2), maxt));
+        tn[c] = (mn > mx) ? INFINITY : mn;
+    }
+}
+
+RTW_HD void cswap(float& ta, uint32_t& ra, float& tb, uint32_t& rb) {
+    const bool sw = tb < ta;
+    const float t = sw ? tb : ta; const uint32_t r = sw ? rb : ra;
+    tb = sw ? ta : tb; rb = sw ? ra : rb;
+    ta = t; ra = r;
+}
+
+// T.cur is an internal node: four child boxes. The crossed children are visited nearest first, the
+// others stacked farthest first. INLINE_PRIMS: sphere / quad children whose box is crossed are
+// tested on the spot (they are leaves: nothing to descend into); otherwise they are visited like
+// any other child (trav_step_prim), which lets a warp batch them.
 template <bool INLINE_PRIMS>
 RTW_HD void trav_step_node(const TraceCtx& cx, Trav& T, const Stack& S) {
     RTW_COUNT(cx, nodes);
     const Node* np = &cx.sc->nodes[T.cur];
-    float4 n0 = RTW_LDG(&np->n0), n1 = RTW_LDG(&np->n1), n2 = RTW_LDG(&np->n2);
-    uint4 n3 = RTW_LDG(&np->n3);
-    float t0, t1;
-    bool h0 = slab(v3(n0.x, n0.y, n0.z), v3(n0.w, n1.x, n1.y), T, cx.mint, T.t, t0);
-    bool h1 = slab(v3(n1.z, n1.w, n2.x), v3(n2.y, n2.z, n2.w), T, cx.mint, T.t, t1);
-    const bool p0 = INLINE_PRIMS && h0 && ref_is_prim(n3.x), p1 = INLINE_PRIMS && h1 && ref_is_prim(n3.y);
-    if (p0 || p1) {
-        uint32_t pa = p0 ? n3.x : n3.y, pb = (p0 && p1) ? n3.y : REF_NONE;
+    const uint4 rr = RTW_LDG(&np->ref);
+    float tn[4];
+    slab4(np, T, cx.mint, T.t, tn);
+    uint32_t rf[4] = {rr.x, rr.y, rr.z, rr.w};
+    if (INLINE_PRIMS) {
+        bool any = false;
 #if defined(__CUDA_ARCH__)
-#pragma unroll 1
+#pragma unroll
 #endif
-        for (int k = 0; k < 2 && pa != REF_NONE; ++k) { trav_test_prim(cx, pa, T); pa = pb; pb = REF_NONE; }
-        h0 = h0 && !p0; h1 = h1 && !p1;
-        if ((T.mode & 3u) == TRAV_PROBE && T.ref != REF_NONE) {   // instance.rs:284-294 only asks "anything?"
+        for (int c = 0; c < 4; ++c)
+            if (tn[c] < INFINITY && ref_is_prim(rf[c])) { trav_test_prim(cx, rf[c], T); tn[c] = INFINITY; any = true; }
+        if (any && (T.mode & 3u) == TRAV_PROBE && T.ref != REF_NONE) {   // instance.rs:284-294 only asks "anything?"
             while (S.pop(T.sp) != CUR_EXIT) {}
             T.cur = CUR_EXIT;
             return;
         }
     }
-    if (h0 && h1) {
-        bool swap = t1 < t0;
-        S.push(T.sp, swap ? n3.x : n3.y);
-        T.cur = swap ? n3.y : n3.x;
-    } else if (h0) {
-        T.cur = n3.x;
-    } else if (h1) {
-        T.cur = n3.y;
-    } else {
-        T.cur = S.pop(T.sp);
+    // children flagged by the builder (constant-density volumes) go last whatever their distance:
+    // their hit is far behind the entry face and costs a free-flight draw, which the shrunk
+    // interval of a nearer surface hit usually spares
+    const uint32_t late = RTW_LDG(&np->pad.x);
+    if (late != 0u) {
+#if defined(__CUDA_ARCH__)
+#pragma unroll
+#endif
+        for (int c = 0; c < 4; ++c) if (((late >> c) & 1u) && tn[c] < INFINITY) tn[c] = 3.0e38f;
     }
+    cswap(tn[0], rf[0], tn[1], rf[1]); cswap(tn[2], rf[2], tn[3], rf[3]);
+    cswap(tn[0], rf[0], tn[2], rf[2]); cswap(tn[1], rf[1], tn[3], rf[3]);
+    cswap(tn[1], rf[1], tn[2], rf[2]);
+    if (tn[3] < INFINITY) S.push(T.sp, rf[3]);
+    if (tn[2] < INFINITY) S.push(T.sp, rf[2]);
+    if (tn[1] < INFINITY) S.push(T.sp, rf[1]);
+    T.cur = tn[0] < INFINITY ? rf[0] : S.pop(T.sp);
 }
 
 // const_density (instance.rs:24-26): ln(xi) / -density, xi from the instance's volume stream.
@@ -302,27 +356,32 @@ RTW_HD float volume_distance(const Instance& in, const TraceCtx& cx) {
 // volumes; Instance::new_sphere of one sphere): the same steps as the general walk — frame change,
 // root (= leaf) box, sphere, constant-density probe (instance.rs:250-302) — without touching the
 // traversal state.
-RTW_HD void trav_one_sphere_instance(const TraceCtx& cx, const Instance& in, uint32_t iref, Trav& T) {
-    V3 o = T.o - v3(in.t[0], in.t[1], in.t[2]);
+RTW_HD void trav_one_sphere_instance(const TraceCtx& cx, uint32_t iref, Trav& T) {
+    const uint32_t k = instance_index(iref);
+    const float4* rec = cx.sc->one_sphere + 4u * k;       // one 64-B record: no dependent loads
+    const float4 r0 = RTW_LDG(rec), s = RTW_LDG(rec + 1), r2 = RTW_LDG(rec + 2), r3 = RTW_LDG(rec + 3);
+    const uint32_t flags = f2u(r2.w);
+    V3 o = T.o - v3(r0.x, r0.y, r0.z);
     V3 d = T.d, inv = T.inv;
     float a = T.a;
     bool slow = trav_slow(T);
-    if (!(in.flags & INST_ROT_IDENTITY)) {
+    if (!(flags & INST_ROT_IDENTITY)) {
+        const Instance& in = cx.sc->instances[k];
         o = rot_apply(in.inv_rows, o); d = rot_apply(in.inv_rows, d);
         inv = v3(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);
         a = dot(d, d);
         slow = !(isfinite(inv.x) && isfinite(inv.y) && isfinite(inv.z));
     }
-    const Level& lv = in.level;
-    const V3 lo = v3(lv.lo[0], lv.lo[1], lv.lo[2]), hi = v3(lv.hi[0], lv.hi[1], lv.hi[2]);
+    const V3 lo = v3(r2.x, r2.y, r2.z), hi = v3(r3.x, r3.y, r3.z);
     float tn, t;
     if (!slab_ray(lo, hi, o, d, inv, slow, cx.mint, T.t, tn)) return;
     RTW_COUNT(cx, spheres);
-    const float4 s = RTW_LDG(&cx.sc->spheres[ref_index(lv.root)]);
     const V3 c = v3(s.x, s.y, s.z);
     if (!sphere_t(c, s.w, o, d, a, cx.mint, T.t, t)) return;
-    if (in.flags & INST_VOLUME) {
-        float distance = volume_distance(in, cx);
+    if (flags & INST_VOLUME) {
+        // const_density (instance.rs:24-26), as volume_distance()
+        float xi = ctx_rand(cx, (cx.bounce << 16) | 0u, 1u + f2u(r3.w)).x;
+        float distance = logf(xi) / -r0.w;
         if (distance >= 0.0f) {
             V3 o2 = (o + d * t) + d * distance;
             float t2;
@@ -331,18 +390,13 @@ RTW_HD void trav_one_sphere_instance(const TraceCtx& cx, const Instance& in, uin
             if (!sphere_t(c, s.w, o2, d, a, cx.mint, cx.maxt, t2)) return;
         }
     }
-    if (closer(t, iref, T.t, T.ref)) { T.t = t; T.ref = iref; T.inner = lv.root; }
+    if (closer(t, iref, T.t, T.ref)) { T.t = t; T.ref = iref; T.inner = cx.sc->instances[k].level.root; }
 }
 
 // Instance::collision_normal, first half (instance.rs:250-271): ray -> local frame, walk the inside.
 RTW_HD void trav_enter_instance(const TraceCtx& cx, float time, Trav& T, const Stack& S) {
     RTW_COUNT(cx, instances);
-    const Instance& in = cx.sc->instances[ref_index(T.cur)];
-    if (in.flags & INST_ONE_SPHERE) {
-        trav_one_sphere_instance(cx, in, T.cur, T);
-        T.cur = S.pop(T.sp);
-        return;
-    }
+    const Instance& in = cx.sc->instances[instance_index(T.cur)];
     // world frame of the ray: restored by trav_level_finished
     S.push(T.sp, f2u(T.o.x)); S.push(T.sp, f2u(T.o.y)); S.push(T.sp, f2u(T.o.z));
     S.push(T.sp, f2u(T.d.x)); S.push(T.sp, f2u(T.d.y)); S.push(T.sp, f2u(T.d.z));
@@ -371,7 +425,7 @@ RTW_HD void trav_enter_instance(const TraceCtx& cx, float time, Trav& T, const S
 RTW_HD void trav_level_finished(const TraceCtx& cx, float time, Trav& T, const Stack& S) {
     const uint32_t mode = T.mode & 3u;
     if (mode == TRAV_TOP) { T.cur = CUR_DONE; return; }
-    const Instance& in = cx.sc->instances[ref_index(T.inst)];
+    const Instance& in = cx.sc->instances[instance_index(T.inst)];
     bool hit;
     if (mode == TRAV_INNER) {
         hit = T.ref != REF_NONE;
@@ -403,9 +457,16 @@ RTW_HD void trav_level_finished(const TraceCtx& cx, float time, Trav& T, const S
     T.cur = S.pop(T.sp);
 }
 
-// T.cur is a sphere / quad leaf (a child left on the stack by the non-inlining node step, or the
-// root of a one-primitive level).
+// T.cur is a leaf test: a sphere / quad (a child left on the stack by the non-inlining node step,
+// or the root of a one-primitive level) or an instance that holds exactly one sphere.
 RTW_HD void trav_step_prim(const TraceCtx& cx, Trav& T, const Stack& S) {
+    if (ref_is_one_sphere_instance(T.cur)) {
+        RTW_COUNT(cx, instances);
+        const uint32_t iref = T.cur & ~REF_ONE_SPHERE_INSTANCE;
+        trav_one_sphere_instance(cx, iref, T);
+        T.cur = S.pop(T.sp);
+        return;
+    }
     trav_test_prim(cx, T.cur, T);
     if ((T.mode & 3u) == TRAV_PROBE && T.ref != REF_NONE) {     // instance.rs:284-294 only asks "anything?"
         while (S.pop(T.sp) != CUR_EXIT) {}
@@ -415,9 +476,9 @@ RTW_HD void trav_step_prim(const TraceCtx& cx, Trav& T, const Stack& S) {
     }
 }
 
-// T.cur is an instance leaf or the sentinel. Such events are chained until the lane is back on a
-// node or a primitive (or done).
-RTW_HD bool ref_is_event(uint32_t r) { return r >= 0xC0000000u && r != CUR_DONE; }   // KIND_INSTANCE range incl. CUR_EXIT
+// T.cur is an instance leaf (a level change) or the sentinel. Such events are chained until the
+// lane is back on a node or a leaf test (or done).
+RTW_HD bool ref_is_event(uint32_t r) { return (r >= 0xC0000000u && r < 0xE0000000u) || r == CUR_EXIT; }
 RTW_HD void trav_step_event(const TraceCtx& cx, float time, Trav& T, const Stack& S) {
     do {
         if (T.cur == CUR_EXIT) trav_level_finished(cx, time, T, S);
@@ -428,7 +489,7 @@ RTW_HD void trav_step_event(const TraceCtx& cx, float time, Trav& T, const Stack
 // Anything but an internal node, in one call (drivers that do not schedule step kinds separately).
 RTW_HD void trav_step_other(const TraceCtx& cx, float time, Trav& T, const Stack& S) {
     do {
-        if (ref_is_prim(T.cur)) trav_step_prim(cx, T, S);
+        if (ref_is_leaf_test(T.cur)) trav_step_prim(cx, T, S);
         else trav_step_event(cx, time, T, S);
     } while (T.cur >= NODE_LIMIT && T.cur != CUR_DONE);
 }

@@ -53,30 +53,24 @@ void euler_rows(const float rot[3], float r[12]) {
 
 bool finite3(const float* p) { return std::isfinite(p[0]) && std::isfinite(p[1]) && std::isfinite(p[2]); }
 
+// Two-step build per level: a binary top-down SAH tree (full sweep on each axis, one primitive per
+// leaf), then a collapse into 4-wide nodes: a node adopts its grandchildren, largest box first,
+// until it has four children. Leaves are never merged: every primitive stays reachable through its
+// own reference box, which is what the traversal slab-tests before the primitive (N16).
 struct Builder {
+    struct BNode { Box b[2]; uint32_t c[2]; };        // c: REF of a leaf, or BIN | index into bin
+    static const uint32_t BIN = 0x80000000u;          // marks a binary inner node in BNode::c (temporary)
     std::vector<Node>& nodes;
-    uint32_t max_depth = 0;
+    std::vector<BNode> bin;
+    uint32_t max_pushes = 0;                           // deepest stack use of the level built last
+    const std::vector<uint8_t>* late_instances = nullptr;   // per instance: constant-density volume
     explicit Builder(std::vector<Node>& n) : nodes(n) {}
 
-    static void write_child(Node& n, int which, const Box& b, uint32_t ref) {
-        if (which == 0) {
-            n.n0 = make_float4(b.lo[0], b.lo[1], b.lo[2], b.hi[0]);
-            n.n1.x = b.hi[1]; n.n1.y = b.hi[2];
-            n.n3.x = ref;
-        } else {
-            n.n1.z = b.lo[0]; n.n1.w = b.lo[1];
-            n.n2 = make_float4(b.lo[2], b.hi[0], b.hi[1], b.hi[2]);
-            n.n3.y = ref;
-        }
-    }
-
-    // Top-down SAH over [begin, end): full sweep on each axis, one primitive per leaf (a leaf is
-    // just the primitive's reference inside its parent). Falls back to a median split when the
-    // remaining depth budget (the traversal stack, RTW_STACK) gets tight.
-    uint32_t build(std::vector<BuildPrim>& p, size_t begin, size_t end, uint32_t depth, Box& out_box) {
+    // Top-down SAH over [begin, end). Falls back to a median split when the remaining depth budget
+    // (RTW_STACK binary levels) gets tight. Returns a leaf REF, or BIN | binary node index.
+    uint32_t build(std::vector<BuildPrim>& p, size_t begin, size_t end, uint32_t depth, Box& out_box, bool& is_bin) {
         size_t n = end - begin;
-        max_depth = std::max(max_depth, depth);
-        if (n == 1) { out_box = p[begin].box; return p[begin].ref; }
+        if (n == 1) { out_box = p[begin].box; is_bin = false; return p[begin].ref; }
         Box cb = box_empty();
         for (size_t i = begin; i < end; ++i)
             for (int a = 0; a < 3; ++a) { cb.lo[a] = minf(cb.lo[a], p[i].c[a]); cb.hi[a] = maxf(cb.hi[a], p[i].c[a]); }
@@ -106,24 +100,74 @@ struct Builder {
         }
         std::stable_sort(p.begin() + begin, p.begin() + end,
                          [best_axis](const BuildPrim& a, const BuildPrim& b) { return a.c[best_axis] < b.c[best_axis]; });
+        uint32_t me = (uint32_t)bin.size();
+        bin.emplace_back();
+        Box b0, b1; bool bin0, bin1;
+        uint32_t c0 = build(p, begin, begin + best_k, depth + 1, b0, bin0);
+        uint32_t c1 = build(p, begin + best_k, end, depth + 1, b1, bin1);
+        bin[me].b[0] = b0; bin[me].b[1] = b1;
+        bin[me].c[0] = c0; bin[me].c[1] = c1;
+        binflag.resize(bin.size() * 2, 0);
+        binflag[2 * me] = bin0; binflag[2 * me + 1] = bin1;
+        out_box = b0; box_grow(out_box, b1);
+        is_bin = true;
+        return me;
+    }
+    std::vector<uint8_t> binflag;                      // binflag[2*i+k]: child k of bin[i] is a binary node
+
+    // Emit the 4-wide node for binary node `b`; returns its reference and the stack words a walk
+    // below it can need (siblings left on the stack at every level).
+    uint32_t emit4(uint32_t b, uint32_t& pushes) {
+        struct Child { Box box; uint32_t c; bool is_bin; };
+        Child ch[4]; int n = 2;
+        for (int k = 0; k < 2; ++k) { ch[k].box = bin[b].b[k]; ch[k].c = bin[b].c[k]; ch[k].is_bin = binflag[2 * b + k] != 0; }
+        while (n < 4) {
+            int pick = -1; float area = -1.f;
+            for (int k = 0; k < n; ++k) if (ch[k].is_bin) { float a = box_area(ch[k].box); if (a > area) { area = a; pick = k; } }
+            if (pick < 0) break;
+            uint32_t g = ch[pick].c;
+            Child a, c;
+            a.box = bin[g].b[0]; a.c = bin[g].c[0]; a.is_bin = binflag[2 * g] != 0;
+            c.box = bin[g].b[1]; c.c = bin[g].c[1]; c.is_bin = binflag[2 * g + 1] != 0;
+            ch[pick] = a; ch[n++] = c;
+        }
         uint32_t me = (uint32_t)nodes.size();
         nodes.emplace_back();
-        std::memset(&nodes[me], 0, sizeof(Node));
-        Box b0, b1;
-        uint32_t c0 = build(p, begin, begin + best_k, depth + 1, b0);
-        uint32_t c1 = build(p, begin + best_k, end, depth + 1, b1);
-        write_child(nodes[me], 0, b0, c0);
-        write_child(nodes[me], 1, b1, c1);
-        out_box = b0; box_grow(out_box, b1);
+        const float inf = std::numeric_limits<float>::infinity();
+        float lo[3][4], hi[3][4]; uint32_t ref[4];
+        uint32_t below = 0;
+        for (int k = 0; k < 4; ++k) {
+            if (k < n) {
+                for (int a = 0; a < 3; ++a) { lo[a][k] = ch[k].box.lo[a]; hi[a][k] = ch[k].box.hi[a]; }
+                if (ch[k].is_bin) { uint32_t pb = 0; ref[k] = emit4(ch[k].c, pb); below = std::max(below, pb); }
+                else ref[k] = ch[k].c;
+            } else {
+                for (int a = 0; a < 3; ++a) { lo[a][k] = inf; hi[a][k] = inf; }
+                ref[k] = REF_NONE;
+            }
+        }
+        Node& nd = nodes[me];
+        nd.lox = make_float4(lo[0][0], lo[0][1], lo[0][2], lo[0][3]); nd.loy = make_float4(lo[1][0], lo[1][1], lo[1][2], lo[1][3]);
+        nd.loz = make_float4(lo[2][0], lo[2][1], lo[2][2], lo[2][3]); nd.hix = make_float4(hi[0][0], hi[0][1], hi[0][2], hi[0][3]);
+        nd.hiy = make_float4(hi[1][0], hi[1][1], hi[1][2], hi[1][3]); nd.hiz = make_float4(hi[2][0], hi[2][1], hi[2][2], hi[2][3]);
+        nd.ref = make_uint4(ref[0], ref[1], ref[2], ref[3]);
+        uint32_t late = 0u;                              // visit-last flags, see trav_step_node
+        for (int k = 0; k < n; ++k)
+            if (ref_kind(ref[k]) == KIND_INSTANCE && late_instances && (*late_instances)[instance_index(ref[k])]) late |= 1u << k;
+        nd.pad = make_uint4(late, 0u, 0u, 0u);
+        pushes = (uint32_t)(n - 1) + below;
         return make_ref(KIND_NODE, me);
     }
 
     Level level(std::vector<BuildPrim>& prims, uint32_t mov_first, uint32_t mov_count) {
         Level lv; std::memset(&lv, 0, sizeof lv);
         lv.mov_first = mov_first; lv.mov_count = mov_count;
+        max_pushes = 0;
         if (prims.empty()) { lv.root = REF_NONE; return lv; }
-        Box rb;
-        lv.root = build(prims, 0, prims.size(), 0, rb);
+        bin.clear(); binflag.clear();
+        Box rb; bool is_bin;
+        uint32_t r = build(prims, 0, prims.size(), 0, rb, is_bin);
+        lv.root = is_bin ? emit4(r, max_pushes) : r;
         for (int a = 0; a < 3; ++a) { lv.lo[a] = rb.lo[a]; lv.hi[a] = rb.hi[a]; }
         return lv;
     }
@@ -143,7 +187,7 @@ Scene HostScene::host_view() {
     s.spheres = spheres.data(); s.sphere_vel = sphere_vel.data(); s.sphere_col = sphere_col.data();
     s.sphere_ids = sphere_ids.data(); s.sphere_box = sphere_box.data();
     s.quads = quads.data(); s.quad_ids = quad_ids.data();
-    s.instances = instances.data(); s.moving = moving.data();
+    s.instances = instances.data(); s.one_sphere = one_sphere.data(); s.moving = moving.data();
     s.materials = materials.data();
     for (size_t i = 0; i < textures.size(); ++i) { textures[i].texels = texels[i].data(); textures[i].obj = 0; }
     s.textures = textures.data(); s.noises = noises.data();
@@ -161,7 +205,7 @@ int build_host_scene(const rtw_scene_desc* d, HostScene& hs, std::string& err) {
         (d->n_materials && !d->materials) || (d->n_textures && !d->textures) || (d->n_noises && !d->noises)) {
         err = "null array with non-zero count"; return RTW_E_INVALID;
     }
-    if (d->n_spheres >= (1u << 30) || d->n_quads >= (1u << 30) || d->n_instances >= (1u << 30)) {
+    if (d->n_spheres >= (1u << 30) || d->n_quads >= (1u << 30) || d->n_instances >= (1u << 29) - 2u) {
         err = "too many primitives"; return RTW_E_UNSUPPORTED;
     }
     if ((d->n_spheres || d->n_quads) && (d->n_materials == 0 || d->n_textures == 0)) {
@@ -319,28 +363,41 @@ int build_host_scene(const rtw_scene_desc* d, HostScene& hs, std::string& err) {
         if (!finite3(lb.lo) || !finite3(lb.hi)) { err = "instance bounds are not finite"; return RTW_E_INVALID; }
         inst_leaves.push_back({k, lb});
     }
+    std::vector<uint8_t> late(d->n_instances, 0);
+    for (uint32_t k = 0; k < d->n_instances; ++k) late[k] = d->instances[k].density_kind == RTW_DENSITY_CONST;
+    bld.late_instances = &late;
     // ---- levels: top first (its nodes lead the array and stay hot), then each instance
-    for (auto& il : inst_leaves) top.push_back(make_prim(make_ref(KIND_INSTANCE, il.first), il.second));
+    for (auto& il : inst_leaves)
+        top.push_back(make_prim(make_ref(KIND_INSTANCE, il.first) | ((hs.instances[il.first].flags & INST_ONE_SPHERE) ? REF_ONE_SPHERE_INSTANCE : 0u), il.second));
     hs.info = rtw_scene_info{};
     hs.info.n_tlas_leaves = (uint32_t)top.size();
     hs.moving = top_moving;
     hs.top = bld.level(top, 0u, (uint32_t)top_moving.size());
     hs.info.n_tlas_nodes = (uint32_t)hs.nodes.size();
-    uint32_t top_depth = bld.max_depth, inner_depth = 0;
+    uint32_t top_depth = bld.max_pushes, inner_depth = 0;
     blas_nodes_before = (uint32_t)hs.nodes.size();
     for (auto& il : inst_leaves) {
         uint32_t k = il.first;
         uint32_t mf = (uint32_t)hs.moving.size();
         hs.moving.insert(hs.moving.end(), inst_moving[k].begin(), inst_moving[k].end());
-        bld.max_depth = 0;
         hs.instances[k].level = bld.level(inst_prims[k], mf, (uint32_t)inst_moving[k].size());
-        inner_depth = std::max(inner_depth, bld.max_depth);
+        inner_depth = std::max(inner_depth, bld.max_pushes);
+    }
+    hs.one_sphere.assign(4 * (size_t)std::max<uint32_t>(d->n_instances, 1u), make_float4(0.f, 0.f, 0.f, 0.f));
+    for (uint32_t k = 0; k < d->n_instances; ++k) {
+        const Instance& in = hs.instances[k];
+        if (!(in.flags & INST_ONE_SPHERE)) continue;
+        const float4 sp = hs.spheres[ref_index(in.level.root)];
+        hs.one_sphere[4 * k + 0] = make_float4(in.t[0], in.t[1], in.t[2], in.density);
+        hs.one_sphere[4 * k + 1] = sp;
+        hs.one_sphere[4 * k + 2] = make_float4(in.level.lo[0], in.level.lo[1], in.level.lo[2], u2f(in.flags));
+        hs.one_sphere[4 * k + 3] = make_float4(in.level.hi[0], in.level.hi[1], in.level.hi[2], u2f(in.index));
     }
     hs.info.n_blas_nodes = (uint32_t)hs.nodes.size() - blas_nodes_before;
     hs.info.n_flattened_instances = n_flat;
     hs.info.bvh_max_depth = top_depth + inner_depth;
     hs.top_depth = top_depth; hs.inner_depth = inner_depth;
-    if (top_depth >= (uint32_t)RTW_STACK || inner_depth >= (uint32_t)RTW_STACK) { err = "BVH deeper than the traversal stack"; return RTW_E_UNSUPPORTED; }
+    if (stack_words(top_depth, inner_depth) > 160u) { err = "BVH deeper than the traversal stack"; return RTW_E_UNSUPPORTED; }
     if (hs.nodes.empty()) { hs.nodes.emplace_back(); std::memset(&hs.nodes[0], 0, sizeof(Node)); }
     if (hs.moving.empty()) hs.moving.push_back(0u);
     for (int a = 0; a < 3; ++a) hs.background[a] = d->background[a];
