@@ -180,6 +180,7 @@ int upload_scene(rtw_scene* s, HostScene& hs) {
     }
     Scene& d = s->d;
     if ((rc = upload(s, hs.nodes, &d.nodes))) return rc;
+    if ((rc = upload(s, hs.nodes16, &d.nodes16))) return rc;
     if ((rc = upload(s, hs.spheres, &d.spheres))) return rc;
     if ((rc = upload(s, hs.sphere_vel, &d.sphere_vel))) return rc;
     if ((rc = upload(s, hs.sphere_col, &d.sphere_col))) return rc;
@@ -288,7 +289,7 @@ int enqueue_wavefront(rtw_scene* s, const RenderParams& P, int variant, float* d
     L.smem_bytes = s->smem_bytes;
     L.fetch_min = std::min(32u, std::max(1u, env_u32("RTW_WF_FETCH_MIN", 16u)));
     L.chunk = std::max(32u, env_u32("RTW_WF_CHUNK", 32u));
-    L.extend_grid = s->sm_count * std::max(1, s->occ_wf[variant]);
+    L.extend_grid = s->sm_count * std::max(1, std::min(s->occ_wf[variant], (int)env_u32("RTW_WF_MAX_BLOCKS", 64u)));
     L.shade_grid = (int)(s->pool.capacity / RTW_WF_SHADE_BLOCK);
     WfCounters init{};
     init.total_paths = 32ull * L.tiles_x * L.tiles_y * P.sample_count;

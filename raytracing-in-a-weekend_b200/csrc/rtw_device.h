@@ -71,7 +71,11 @@ RTW_HD uint32_t make_ref(uint32_t kind, uint32_t idx) { return (kind << 30) | id
 // one static sphere carries this bit, so that the walk can treat it as a primitive test rather than
 // a level change. Search results always carry the plain reference.
 static const uint32_t REF_ONE_SPHERE_INSTANCE = 0x20000000u;
-RTW_HD uint32_t instance_index(uint32_t r) { return r & 0x1FFFFFFFu; }
+// ... and the reference of a constant-density volume instance carries this one: such children are
+// visited last among their siblings (see trav_step_node).
+static const uint32_t REF_LATE_INSTANCE = 0x10000000u;
+static const uint32_t REF_INSTANCE_FLAGS = 0x30000000u;
+RTW_HD uint32_t instance_index(uint32_t r) { return r & 0x0FFFFFFFu; }
 
 // ------------------------------------------------------------------ scene records (all 16-byte aligned)
 // BVH node, 4-wide: the boxes of up to four children, one component per float4 (lane c of each
@@ -80,6 +84,13 @@ RTW_HD uint32_t instance_index(uint32_t r) { return r & 0x1FFFFFFFu; }
 // every ray. A child box is the child's own reference box (a primitive's leaf box, an instance's
 // world box, or the union for an inner node).
 struct Node { float4 lox, loy, loz, hix, hiy, hiz; uint4 ref; uint4 pad; };
+// The same node with the boxes as IEEE half floats, rounded outwards (lo down, hi up): 64 B, four
+// 128-bit loads. a = (lox[4], loy[4]) b = (loz[4], hix[4]) c = (hiy[4], hiz[4]), two halves per
+// word, child 0 in the low half of the first word. Used by the fast kernels: what bounds the walk
+// is the number of 16-byte L1 accesses per node (every lane reads a different node), so halving
+// the node halves the dominant cost. The boxes only grow, so no hit is lost; the strict kernels
+// keep the exact f32 boxes (the reference's own leaf boxes).
+struct Node16 { uint4 a, b, c; uint4 ref; };
 
 // One traversable level (the scene top level, or the inside of one instance): root reference +
 // root box (the reference slab-tests every BVH root: aabb.rs:109-126) + the level's moving
@@ -132,6 +143,7 @@ struct Noise {     // texture.rs:63-69; perms stored & 255 (index is masked anyw
 
 struct Scene {
     const Node* nodes;
+    const Node16* nodes16;        // same topology, same indices
     const float4* spheres;        // origin.xyz, radius
     const float4* sphere_vel;     // velocity.xyz, 0   (read only for moving spheres)
     const float4* sphere_col;     // col_mod.xyz, bits(flags: bit0 moving)

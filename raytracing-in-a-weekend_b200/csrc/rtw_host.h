@@ -12,6 +12,7 @@ namespace rtw {
 
 struct HostScene {
     std::vector<Node> nodes;
+    std::vector<Node16> nodes16;
     std::vector<float4> spheres, sphere_vel, sphere_col, sphere_box;
     std::vector<uint2> sphere_ids;
     std::vector<Quad> quads;

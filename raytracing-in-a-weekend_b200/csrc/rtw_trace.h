@@ -24,6 +24,9 @@
 // emulator (tests/emu) uses.
 #pragma once
 #include "rtw_device.h"
+#if defined(__CUDACC__)
+#include <cuda_fp16.h>
+#endif
 
 namespace rtw {
 
@@ -256,15 +259,43 @@ RTW_HD bool ref_is_one_sphere_instance(uint32_t r) { return r >= 0xE0000000u && 
 // what trav_step_prim handles: sphere, quad, one-sphere instance
 RTW_HD bool ref_is_leaf_test(uint32_t r) { return ref_is_prim(r) || ref_is_one_sphere_instance(r); }
 
-// Slab tests of the four child boxes of a node: tn[c] = entry parameter if child c is crossed
-// within [mint, maxt], else +inf. Strict build / host: the reference's own operation order,
-// (bound - origin) * (1/d). Fast device build: one FFMA per plane, bound * (1/d) - origin * (1/d)
-// (differs from the reference by a rounding of the origin term: the box moves by ~1 ulp of |o|).
-RTW_HD void slab4(const Node* np, const Trav& T, float mint, float maxt, float tn[4]) {
+// Slab tests of the four child boxes of node `idx`: tn[c] = entry parameter if child c is crossed
+// within [mint, maxt], else +inf; rr = the child references.
+//   strict build / host: exact f32 boxes, the reference's own operation order, (bound - o) * (1/d);
+//   fast device build: half-float boxes (Node16, rounded outwards) and one FFMA per plane,
+//   bound * (1/d) - o * (1/d).
+#if defined(__CUDA_ARCH__) && !defined(RTW_STRICT_FP)
+#define RTW_FAST_NODES 1
+#endif
+RTW_HD void slab4(const Scene& sc, uint32_t idx, const Trav& T, float mint, float maxt, float tn[4], uint4& rr) {
+#if defined(RTW_FAST_NODES)
+    const Node16* np = &sc.nodes16[idx];
+    const uint4 a = RTW_LDG(&np->a), b = RTW_LDG(&np->b), c4 = RTW_LDG(&np->c);
+    rr = RTW_LDG(&np->ref);
+    float LX[4], LY[4], LZ[4], HX[4], HY[4], HZ[4];
+    {
+        float2 f;
+        f = __half22float2(*reinterpret_cast<const __half2*>(&a.x)); LX[0] = f.x; LX[1] = f.y;
+        f = __half22float2(*reinterpret_cast<const __half2*>(&a.y)); LX[2] = f.x; LX[3] = f.y;
+        f = __half22float2(*reinterpret_cast<const __half2*>(&a.z)); LY[0] = f.x; LY[1] = f.y;
+        f = __half22float2(*reinterpret_cast<const __half2*>(&a.w)); LY[2] = f.x; LY[3] = f.y;
+        f = __half22float2(*reinterpret_cast<const __half2*>(&b.x)); LZ[0] = f.x; LZ[1] = f.y;
+        f = __half22float2(*reinterpret_cast<const __half2*>(&b.y)); LZ[2] = f.x; LZ[3] = f.y;
+        f = __half22float2(*reinterpret_cast<const __half2*>(&b.z)); HX[0] = f.x; HX[1] = f.y;
+        f = __half22float2(*reinterpret_cast<const __half2*>(&b.w)); HX[2] = f.x; HX[3] = f.y;
+        f = __half22float2(*reinterpret_cast<const __half2*>(&c4.x)); HY[0] = f.x; HY[1] = f.y;
+        f = __half22float2(*reinterpret_cast<const __half2*>(&c4.y)); HY[2] = f.x; HY[3] = f.y;
+        f = __half22float2(*reinterpret_cast<const __half2*>(&c4.z)); HZ[0] = f.x; HZ[1] = f.y;
+        f = __half22float2(*reinterpret_cast<const __half2*>(&c4.w)); HZ[2] = f.x; HZ[3] = f.y;
+    }
+#else
+    const Node* np = &sc.nodes[idx];
     const float4 lox = RTW_LDG(&np->lox), loy = RTW_LDG(&np->loy), loz = RTW_LDG(&np->loz);
     const float4 hix = RTW_LDG(&np->hix), hiy = RTW_LDG(&np->hiy), hiz = RTW_LDG(&np->hiz);
+    rr = RTW_LDG(&np->ref);
     const float LX[4] = {lox.x, lox.y, lox.z, lox.w}, LY[4] = {loy.x, loy.y, loy.z, loy.w}, LZ[4] = {loz.x, loz.y, loz.z, loz.w};
     const float HX[4] = {hix.x, hix.y, hix.z, hix.w}, HY[4] = {hiy.x, hiy.y, hiy.z, hiy.w}, HZ[4] = {hiz.x, hiz.y, hiz.z, hiz.w};
+#endif
     if (trav_slow(T)) {
         for (int c = 0; c < 4; ++c) {
             float t;
@@ -273,14 +304,14 @@ RTW_HD void slab4(const Node* np, const Trav& T, float mint, float maxt, float t
         }
         return;
     }
-#if defined(__CUDA_ARCH__) && !defined(RTW_STRICT_FP)
+#if defined(RTW_FAST_NODES)
     const float nx = -T.o.x * T.inv.x, ny = -T.o.y * T.inv.y, nz = -T.o.z * T.inv.z;
 #endif
 #if defined(__CUDA_ARCH__)
 #pragma unroll
 #endif
     for (int c = 0; c < 4; ++c) {
-#if defined(__CUDA_ARCH__) && !defined(RTW_STRICT_FP)
+#if defined(RTW_FAST_NODES)
         float x1 = fmaf(LX[c], T.inv.x, nx), x2 = fmaf(HX[c], T.inv.x, nx);
         float y1 = fmaf(LY[c], T.inv.y, ny), y2 = fmaf(HY[c], T.inv.y, ny);
         float z1 = fmaf(LZ[c], T.inv.z, nz), z2 = fmaf(HZ[c], T.inv.z, nz);
@@ -309,10 +340,9 @@ RTW_HD void cswap(float& ta, uint32_t& ra, float& tb, uint32_t& rb) {
 template <bool INLINE_PRIMS>
 RTW_HD void trav_step_node(const TraceCtx& cx, Trav& T, const Stack& S) {
     RTW_COUNT(cx, nodes);
-    const Node* np = &cx.sc->nodes[T.cur];
-    const uint4 rr = RTW_LDG(&np->ref);
+    uint4 rr;
     float tn[4];
-    slab4(np, T, cx.mint, T.t, tn);
+    slab4(*cx.sc, T.cur, T, cx.mint, T.t, tn, rr);
     uint32_t rf[4] = {rr.x, rr.y, rr.z, rr.w};
     if (INLINE_PRIMS) {
         bool any = false;
@@ -327,16 +357,14 @@ RTW_HD void trav_step_node(const TraceCtx& cx, Trav& T, const Stack& S) {
             return;
         }
     }
-    // children flagged by the builder (constant-density volumes) go last whatever their distance:
-    // their hit is far behind the entry face and costs a free-flight draw, which the shrunk
-    // interval of a nearer surface hit usually spares
-    const uint32_t late = RTW_LDG(&np->pad.x);
-    if (late != 0u) {
+    // constant-density volumes (REF_LATE_INSTANCE) go last whatever their distance: their hit is far
+    // behind the entry face and costs a free-flight draw, which the shrunk interval of a nearer
+    // surface hit usually spares
 #if defined(__CUDA_ARCH__)
 #pragma unroll
 #endif
-        for (int c = 0; c < 4; ++c) if (((late >> c) & 1u) && tn[c] < INFINITY) tn[c] = 3.0e38f;
-    }
+    for (int c = 0; c < 4; ++c)
+        if ((rf[c] & 0xD0000000u) == 0xD0000000u && tn[c] < INFINITY) tn[c] = 3.0e38f;
     cswap(tn[0], rf[0], tn[1], rf[1]); cswap(tn[2], rf[2], tn[3], rf[3]);
     cswap(tn[0], rf[0], tn[2], rf[2]); cswap(tn[1], rf[1], tn[3], rf[3]);
     cswap(tn[1], rf[1], tn[2], rf[2]);
@@ -404,7 +432,7 @@ RTW_HD void trav_enter_instance(const TraceCtx& cx, float time, Trav& T, const S
     S.push(T.sp, f2u(T.a));
     S.push(T.sp, CUR_EXIT);
     V3 o = T.o - v3(in.t[0], in.t[1], in.t[2]);
-    T.inst = T.cur;
+    T.inst = T.cur & ~REF_INSTANCE_FLAGS;
     T.top_t = T.t; T.top_ref = T.ref;     // T.t stays: the inner search starts from the same bound
     T.ref = REF_NONE;
     if (in.flags & INST_ROT_IDENTITY) {
@@ -462,7 +490,7 @@ RTW_HD void trav_level_finished(const TraceCtx& cx, float time, Trav& T, const S
 RTW_HD void trav_step_prim(const TraceCtx& cx, Trav& T, const Stack& S) {
     if (ref_is_one_sphere_instance(T.cur)) {
         RTW_COUNT(cx, instances);
-        const uint32_t iref = T.cur & ~REF_ONE_SPHERE_INSTANCE;
+        const uint32_t iref = T.cur & ~REF_INSTANCE_FLAGS;
         trav_one_sphere_instance(cx, iref, T);
         T.cur = S.pop(T.sp);
         return;

@@ -14,6 +14,7 @@
 #include <cmath>
 #include <cstring>
 #include <limits>
+#include <cuda_fp16.h>
 #include "rtw_host.h"
 #include "rtw_shade.h"
 
@@ -37,6 +38,14 @@ inline float box_area(const Box& b) {
     double dx = (double)b.hi[0] - b.lo[0], dy = (double)b.hi[1] - b.lo[1], dz = (double)b.hi[2] - b.lo[2];
     if (!(dx >= 0) || !(dy >= 0) || !(dz >= 0)) return 0.f;
     return (float)(2.0 * (dx * dy + dy * dz + dz * dx));
+}
+
+// two floats -> two IEEE halves in one word (first in the low half), rounded towards -inf / +inf
+inline uint32_t pack_half2_rd(float a, float b) {
+    return (uint32_t)__half_as_ushort(__float2half_rd(a)) | ((uint32_t)__half_as_ushort(__float2half_rd(b)) << 16);
+}
+inline uint32_t pack_half2_ru(float a, float b) {
+    return (uint32_t)__half_as_ushort(__float2half_ru(a)) | ((uint32_t)__half_as_ushort(__float2half_ru(b)) << 16);
 }
 
 struct BuildPrim { uint32_t ref; Box box; float c[3]; };
@@ -63,7 +72,6 @@ struct Builder {
     std::vector<Node>& nodes;
     std::vector<BNode> bin;
     uint32_t max_pushes = 0;                           // deepest stack use of the level built last
-    const std::vector<uint8_t>* late_instances = nullptr;   // per instance: constant-density volume
     explicit Builder(std::vector<Node>& n) : nodes(n) {}
 
     // Top-down SAH over [begin, end). Falls back to a median split when the remaining depth budget
@@ -151,10 +159,7 @@ struct Builder {
         nd.loz = make_float4(lo[2][0], lo[2][1], lo[2][2], lo[2][3]); nd.hix = make_float4(hi[0][0], hi[0][1], hi[0][2], hi[0][3]);
         nd.hiy = make_float4(hi[1][0], hi[1][1], hi[1][2], hi[1][3]); nd.hiz = make_float4(hi[2][0], hi[2][1], hi[2][2], hi[2][3]);
         nd.ref = make_uint4(ref[0], ref[1], ref[2], ref[3]);
-        uint32_t late = 0u;                              // visit-last flags, see trav_step_node
-        for (int k = 0; k < n; ++k)
-            if (ref_kind(ref[k]) == KIND_INSTANCE && late_instances && (*late_instances)[instance_index(ref[k])]) late |= 1u << k;
-        nd.pad = make_uint4(late, 0u, 0u, 0u);
+        nd.pad = make_uint4(0u, 0u, 0u, 0u);
         pushes = (uint32_t)(n - 1) + below;
         return make_ref(KIND_NODE, me);
     }
@@ -183,7 +188,7 @@ BuildPrim make_prim(uint32_t ref, const Box& b) {
 
 Scene HostScene::host_view() {
     Scene s; std::memset(&s, 0, sizeof s);
-    s.nodes = nodes.data();
+    s.nodes = nodes.data(); s.nodes16 = nodes16.data();
     s.spheres = spheres.data(); s.sphere_vel = sphere_vel.data(); s.sphere_col = sphere_col.data();
     s.sphere_ids = sphere_ids.data(); s.sphere_box = sphere_box.data();
     s.quads = quads.data(); s.quad_ids = quad_ids.data();
@@ -205,7 +210,7 @@ int build_host_scene(const rtw_scene_desc* d, HostScene& hs, std::string& err) {
         (d->n_materials && !d->materials) || (d->n_textures && !d->textures) || (d->n_noises && !d->noises)) {
         err = "null array with non-zero count"; return RTW_E_INVALID;
     }
-    if (d->n_spheres >= (1u << 30) || d->n_quads >= (1u << 30) || d->n_instances >= (1u << 29) - 2u) {
+    if (d->n_spheres >= (1u << 30) || d->n_quads >= (1u << 30) || d->n_instances >= (1u << 28) - 2u) {
         err = "too many primitives"; return RTW_E_UNSUPPORTED;
     }
     if ((d->n_spheres || d->n_quads) && (d->n_materials == 0 || d->n_textures == 0)) {
@@ -363,12 +368,11 @@ int build_host_scene(const rtw_scene_desc* d, HostScene& hs, std::string& err) {
         if (!finite3(lb.lo) || !finite3(lb.hi)) { err = "instance bounds are not finite"; return RTW_E_INVALID; }
         inst_leaves.push_back({k, lb});
     }
-    std::vector<uint8_t> late(d->n_instances, 0);
-    for (uint32_t k = 0; k < d->n_instances; ++k) late[k] = d->instances[k].density_kind == RTW_DENSITY_CONST;
-    bld.late_instances = &late;
     // ---- levels: top first (its nodes lead the array and stay hot), then each instance
     for (auto& il : inst_leaves)
-        top.push_back(make_prim(make_ref(KIND_INSTANCE, il.first) | ((hs.instances[il.first].flags & INST_ONE_SPHERE) ? REF_ONE_SPHERE_INSTANCE : 0u), il.second));
+        top.push_back(make_prim(make_ref(KIND_INSTANCE, il.first) |
+                                ((hs.instances[il.first].flags & INST_ONE_SPHERE) ? REF_ONE_SPHERE_INSTANCE : 0u) |
+                                ((hs.instances[il.first].flags & INST_VOLUME) ? REF_LATE_INSTANCE : 0u), il.second));
     hs.info = rtw_scene_info{};
     hs.info.n_tlas_leaves = (uint32_t)top.size();
     hs.moving = top_moving;
@@ -382,6 +386,17 @@ int build_host_scene(const rtw_scene_desc* d, HostScene& hs, std::string& err) {
         hs.moving.insert(hs.moving.end(), inst_moving[k].begin(), inst_moving[k].end());
         hs.instances[k].level = bld.level(inst_prims[k], mf, (uint32_t)inst_moving[k].size());
         inner_depth = std::max(inner_depth, bld.max_pushes);
+    }
+    // the half-float copy of the nodes (fast kernels): boxes rounded outwards
+    hs.nodes16.resize(hs.nodes.size());
+    for (size_t i = 0; i < hs.nodes.size(); ++i) {
+        const Node& n = hs.nodes[i];
+        auto dn = [](float4 v) { return make_uint2(pack_half2_rd(v.x, v.y), pack_half2_rd(v.z, v.w)); };
+        auto up = [](float4 v) { return make_uint2(pack_half2_ru(v.x, v.y), pack_half2_ru(v.z, v.w)); };
+        uint2 lx = dn(n.lox), ly = dn(n.loy), lz = dn(n.loz), hx = up(n.hix), hy = up(n.hiy), hz = up(n.hiz);
+        Node16& o = hs.nodes16[i];
+        o.a = make_uint4(lx.x, lx.y, ly.x, ly.y); o.b = make_uint4(lz.x, lz.y, hx.x, hx.y); o.c = make_uint4(hy.x, hy.y, hz.x, hz.y);
+        o.ref = n.ref;
     }
     hs.one_sphere.assign(4 * (size_t)std::max<uint32_t>(d->n_instances, 1u), make_float4(0.f, 0.f, 0.f, 0.f));
     for (uint32_t k = 0; k < d->n_instances; ++k) {
@@ -398,7 +413,7 @@ int build_host_scene(const rtw_scene_desc* d, HostScene& hs, std::string& err) {
     hs.info.bvh_max_depth = top_depth + inner_depth;
     hs.top_depth = top_depth; hs.inner_depth = inner_depth;
     if (stack_words(top_depth, inner_depth) > 160u) { err = "BVH deeper than the traversal stack"; return RTW_E_UNSUPPORTED; }
-    if (hs.nodes.empty()) { hs.nodes.emplace_back(); std::memset(&hs.nodes[0], 0, sizeof(Node)); }
+    if (hs.nodes.empty()) { hs.nodes.emplace_back(); std::memset(&hs.nodes[0], 0, sizeof(Node)); hs.nodes16.emplace_back(); std::memset(&hs.nodes16[0], 0, sizeof(Node16)); }
     if (hs.moving.empty()) hs.moving.push_back(0u);
     for (int a = 0; a < 3; ++a) hs.background[a] = d->background[a];
     return RTW_OK;
