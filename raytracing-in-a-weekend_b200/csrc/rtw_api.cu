@@ -257,14 +257,15 @@ int pool_alloc(rtw_scene* s, T** p, size_t n) {
 int ensure_pool(rtw_scene* s) {
     if (s->pool.capacity) return RTW_OK;
     uint32_t cap = env_u32("RTW_WF_POOL", 1u << 21);
-    cap = std::max(cap, 4096u) & ~255u;
+    cap = std::max(cap, 4096u) & ~255u;           // a multiple of 32, so a warp's slots advance through the tile-major sample order together
     int rc;
-    for (int k = 0; k < 2; ++k) {
-        WfQueue& q = s->pool.q[k];
+    {
+        WfQueue& q = s->pool.q;
         if ((rc = pool_alloc(s, &q.o, cap)) || (rc = pool_alloc(s, &q.d, cap)) || (rc = pool_alloc(s, &q.id, cap)) ||
             (rc = pool_alloc(s, &q.thr, cap)) || (rc = pool_alloc(s, &q.rad, cap))) return rc;
     }
     if ((rc = pool_alloc(s, &s->pool.hit, cap))) return rc;
+    if ((rc = pool_alloc(s, &s->pool.supply, (size_t)cap / 16u))) return rc;      // 2 words per warp of 32 slots
     CK(cudaMalloc(&s->d_wc, sizeof(WfCounters)));
     CK(cudaMallocHost(&s->h_wc, 4 * sizeof(WfCounters)));
     for (auto& e : s->wf_ev) CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
@@ -289,24 +290,26 @@ int enqueue_wavefront(rtw_scene* s, const RenderParams& P, int variant, float* d
     L.smem_bytes = s->smem_bytes;
     L.fetch_min = std::min(32u, std::max(1u, env_u32("RTW_WF_FETCH_MIN", 16u)));
     L.chunk = std::max(32u, env_u32("RTW_WF_CHUNK", 32u));
+    L.supply_chunk = std::max(32u, env_u32("RTW_WF_SUPPLY_CHUNK", 128u)) & ~31u;
+    CK(cudaMemsetAsync(s->pool.supply, 0, (size_t)s->pool.capacity / 16u * sizeof(unsigned long long), st));
     L.extend_grid = s->sm_count * std::max(1, std::min(s->occ_wf[variant], (int)env_u32("RTW_WF_MAX_BLOCKS", 64u)));
     L.shade_grid = (int)(s->pool.capacity / RTW_WF_SHADE_BLOCK);
     WfCounters init{};
     init.total_paths = 32ull * L.tiles_x * L.tiles_y * P.sample_count;
     s->h_wc[0] = init;
     CK(cudaMemcpyAsync(s->d_wc, &s->h_wc[0], sizeof(WfCounters), cudaMemcpyHostToDevice, st));
-    auto extend = [&](uint32_t cur) {
-        return variant == 1   ? launch_wf_extend_strict(s->d, P, s->pool, s->d_wc, s->d_ctr, cur, L, st)
-               : variant == 2 ? launch_wf_extend_count(s->d, P, s->pool, s->d_wc, s->d_ctr, cur, L, st)
-                              : launch_wf_extend_fast(s->d, P, s->pool, s->d_wc, s->d_ctr, cur, L, st);
+    auto extend = [&]() {
+        return variant == 1   ? launch_wf_extend_strict(s->d, P, s->pool, s->d_wc, s->d_ctr, L, st)
+               : variant == 2 ? launch_wf_extend_count(s->d, P, s->pool, s->d_wc, s->d_ctr, L, st)
+                              : launch_wf_extend_fast(s->d, P, s->pool, s->d_wc, s->d_ctr, L, st);
     };
-    auto shade = [&](uint32_t cur, int init_pass) {
-        return variant == 1   ? launch_wf_shade_strict(s->d, P, s->pool, s->d_wc, s->d_ctr, d_out, cur, init_pass, L, st)
-               : variant == 2 ? launch_wf_shade_count(s->d, P, s->pool, s->d_wc, s->d_ctr, d_out, cur, init_pass, L, st)
-                              : launch_wf_shade_fast(s->d, P, s->pool, s->d_wc, s->d_ctr, d_out, cur, init_pass, L, st);
+    auto shade = [&](uint32_t mark, int init_pass) {
+        return variant == 1   ? launch_wf_shade_strict(s->d, P, s->pool, s->d_wc, s->d_ctr, d_out, mark, init_pass, L, st)
+               : variant == 2 ? launch_wf_shade_count(s->d, P, s->pool, s->d_wc, s->d_ctr, d_out, mark, init_pass, L, st)
+                              : launch_wf_shade_fast(s->d, P, s->pool, s->d_wc, s->d_ctr, d_out, mark, init_pass, L, st);
     };
     s->wf_timed = 0;
-    CK(shade(1u, 1));                       // first fill: writes queue[0]
+    CK(shade(0u, 1));                       // first fill
     s->launches += 1;
     const uint32_t batch = std::max(1u, env_u32("RTW_WF_BATCH", 8u));
     uint32_t it = 0;
@@ -316,20 +319,19 @@ int enqueue_wavefront(rtw_scene* s, const RenderParams& P, int variant, float* d
             const bool timed = (it & 7u) == 3u;
             cudaEvent_t* te = s->wf_t[s->wf_timed % rtw_scene::kTimed];
             if (timed) CK(cudaEventRecord(te[0], st));
-            CK(extend(it & 1u));
+            CK(extend());
             if (timed) CK(cudaEventRecord(te[1], st));
-            CK(shade(it & 1u, 0));
+            CK(shade(it + 1u, 0));
             if (timed) { CK(cudaEventRecord(te[2], st)); ++s->wf_timed; }
         }
         s->launches += 2ull * batch;
-        // after `batch` iterations the live queue is queue[it & 1]
         CK(cudaMemcpyAsync(&s->h_wc[k & 3u], s->d_wc, sizeof(WfCounters), cudaMemcpyDeviceToHost, st));
         CK(cudaEventRecord(s->wf_ev[k & 3u], st));
         if (k >= 2u) {
             const uint32_t j = (k - 2u) & 3u;
             CK(cudaEventSynchronize(s->wf_ev[j]));
-            const uint32_t live_q = ((k - 1u) * batch) & 1u;       // `it` after batch k-2
-            if (s->h_wc[j].n_queue[live_q] == 0u && s->h_wc[j].next_path >= s->h_wc[j].total_paths) break;
+            // the last shade of batch k-2 carried mark (k-1)*batch: no live slot after it => the frame is done
+            if (s->h_wc[j].live_mark != (k - 1u) * batch) break;
         }
     }
     s->wf_iterations = it;

@@ -176,15 +176,15 @@ __device__ __forceinline__ void prefetch_l1(const void* p) { asm volatile("prefe
 // stores (t, primitive) at its ray's position.
 __global__ void __launch_bounds__(RTW_WF_BLOCK, RTW_WF_EXTEND_MINB)
 wf_extend_kernel(const Scene sc, const RenderParams P, const WfPool pool, WfCounters* __restrict__ wc,
-                 Counters* __restrict__ ctr, const uint32_t cur, const WfLaunch L) {
+                 Counters* __restrict__ ctr, const WfLaunch L) {
     extern __shared__ uint32_t s_stack[];                 // [stack_words][RTW_WF_BLOCK]
     const uint32_t FULL = 0xFFFFFFFFu;
     const uint32_t lane = threadIdx.x & 31u;
     const uint32_t lt_mask = (1u << lane) - 1u;
     Stack S; S.base = s_stack + threadIdx.x; S.stride = RTW_WF_BLOCK;
-    if (blockIdx.x == 0 && threadIdx.x == 0) wc->n_queue[cur ^ 1u] = 0u;   // shade of this iteration appends there
-    const uint32_t n = wc->n_queue[cur];
-    const WfQueue q = pool.q[cur];
+    const uint32_t n = pool.capacity;
+    const WfQueue q = pool.q;
+    uint32_t n_rays = 0u;
 #if defined(RTW_COUNT_WORK)
     Work wk = {0u, 0u, 0u, 0u, 0u};
     Work* const wp = &wk;
@@ -229,14 +229,18 @@ wf_extend_kernel(const Scene sc, const RenderParams P, const WfPool pool, WfCoun
             SCHED_TIME_BEGIN(3);
             const uint32_t rank = __popc(idle & lt_mask);
             if (!busy && rank < take) {
-                pos = c_pos + rank;
-                const float4 ro = q.o[pos], rd = q.d[pos];
-                const uint2 id = q.id[pos];
-                Ray r; r.o = v3(ro.x, ro.y, ro.z); r.d = v3(rd.x, rd.y, rd.z); r.time = ro.w;
-                time = ro.w;
-                cx.pixel = id.x; cx.sample = id.y; cx.bounce = f2u(rd.w);
-                trav_begin(cx, r, T, S);
-                busy = true;
+                const float4 rd = q.d[c_pos + rank];
+                if (f2u(rd.w) != WF_DEAD) {               // dead slots only exist once the sample supply has run out
+                    pos = c_pos + rank;
+                    const float4 ro = q.o[pos];
+                    const uint2 id = q.id[pos];
+                    Ray r; r.o = v3(ro.x, ro.y, ro.z); r.d = v3(rd.x, rd.y, rd.z); r.time = ro.w;
+                    time = ro.w;
+                    cx.pixel = id.x; cx.sample = id.y; cx.bounce = f2u(rd.w);
+                    trav_begin(cx, r, T, S);
+                    busy = true;
+                    ++n_rays;
+                }
             }
             c_pos += take;
             if (c_pos + lane < c_end) {                   // the next positions of the chunk -> L1
@@ -275,6 +279,10 @@ wf_extend_kernel(const Scene sc, const RenderParams P, const WfPool pool, WfCoun
             busy = false;
         }
     }
+    {
+        const unsigned long long r = warp_sum_u64(n_rays);
+        if (lane == 0u && r != 0ull) atomicAdd(&ctr->rays, r);
+    }
 #if defined(RTW_COUNT_WORK)
     unsigned long long w0 = warp_sum_u64(wk.nodes), w1 = warp_sum_u64(wk.spheres), w2 = warp_sum_u64(wk.quads),
                        w3 = warp_sum_u64(wk.instances);
@@ -294,115 +302,110 @@ wf_extend_kernel(const Scene sc, const RenderParams P, const WfPool pool, WfCoun
 #undef SCHED_TIME_END
 }
 
-// Exclusive prefix of one flag per thread over the block + the block total, via ballots.
-// Returns this thread's rank among the flagged threads; *total is valid for every thread.
-__device__ __forceinline__ uint32_t block_rank(bool flag, uint32_t* s_warp /*[blockDim/32 + 1]*/, uint32_t* total) {
-    const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
-    const uint32_t m = __ballot_sync(0xFFFFFFFFu, flag);
-    if (lane == 0u) s_warp[warp] = __popc(m);
-    __syncthreads();
-    uint32_t before = 0u, all = 0u;
-    for (uint32_t w = 0; w < nw; ++w) { const uint32_t c = s_warp[w]; all += c; if (w < warp) before += c; }
-    __syncthreads();
-    *total = all;
-    return before + __popc(m & ((1u << lane) - 1u));
-}
-
-// shade: one thread per queue position (all `capacity` of them, so that empty positions can start
-// camera samples too and the queue refills to capacity every iteration). init != 0: first fill.
+// shade: one thread per pool slot, record rewritten in place. init != 0: first fill.
 __global__ void __launch_bounds__(RTW_WF_SHADE_BLOCK)
 wf_shade_kernel(const Scene sc, const RenderParams P, const WfPool pool, WfCounters* __restrict__ wc,
-                Counters* __restrict__ ctr, float* __restrict__ sum, const uint32_t cur, const int init, const WfLaunch L) {
-    __shared__ uint32_t s_warp[RTW_WF_SHADE_BLOCK / 32];
-    __shared__ unsigned long long s_base_path;
-    __shared__ uint32_t s_base_q;
+                Counters* __restrict__ ctr, float* __restrict__ sum, const uint32_t mark, const int init, const WfLaunch L) {
     const uint32_t e = blockIdx.x * blockDim.x + threadIdx.x;
-    const uint32_t n = init ? 0u : wc->n_queue[cur];
-    const unsigned long long total = wc->total_paths;
-    // nothing to shade and nothing left to start: the whole block leaves (next_path only grows)
-    __shared__ int s_skip;
-    if (threadIdx.x == 0u) s_skip = (blockIdx.x * blockDim.x >= n && wc->next_path >= total) ? 1 : 0;
-    __syncthreads();
-    if (s_skip) return;
     if (e == 0u) {
         wc->head = 0u;                                      // this iteration's extend is over
         wc->iterations += 1ull;
-        if (!init) atomicAdd(&ctr->rays, (unsigned long long)n);
     }
+    const WfQueue q = pool.q;                               // grid * block == capacity (a multiple of 256)
     const uint32_t W = P.cam.width;
-    const WfQueue qi = pool.q[cur], qo = pool.q[cur ^ 1u];
+    const unsigned long long total = wc->total_paths;
 #if defined(RTW_COUNT_WORK)
     Work wk = {0u, 0u, 0u, 0u, 0u};
     Work* const wp = &wk;
 #else
     Work* const wp = nullptr;
 #endif
+    const uint32_t FULL = 0xFFFFFFFFu;
+    const uint32_t lane = threadIdx.x & 31u;
     Path path;
-    bool alive = false;
-    uint32_t n_nan = 0u;
-    if (e < n) {
-        const float4 ro = qi.o[e], rd = qi.d[e];
-        const uint2 id = qi.id[e];
-        const uint4 hit = pool.hit[e];
-        const float4 thr = qi.thr[e], rad = qi.rad[e];
-        path.ray.time = ro.w;
-        path.thr = v3(thr.x, thr.y, thr.z); path.rad = v3(rad.x, rad.y, rad.z);
-        path.pixel = id.x; path.sample = id.y; path.block = f2u(thr.w);
-        const uint32_t dl = f2u(rad.w);
-        path.depth_left = dl & 0x7FFFFFFFu; path.poison = (dl >> 31) != 0u;
-        Trav T;
-        T.o = v3(ro.x, ro.y, ro.z); T.d = v3(rd.x, rd.y, rd.z);
-        T.t = u2f(hit.x); T.ref = hit.y; T.inner = hit.z;
-        TraceCtx cx = path_ctx(sc, P, path, wp);
-        bool finished = segment_end(cx, sc.noises, P, path, T);
-        if (!finished && path.depth_left < 1u) finished = true;   // ray_color.rs:14-16: the next call returns black
-        if (finished) {
-            V3 c = path_result(path);
-            if (!finite3(c)) ++n_nan;
-            float* px = sum + ((size_t)path.pixel - (size_t)P.row_begin * W) * 3u;
-            atomicAdd(px + 0, c.x); atomicAdd(px + 1, c.y); atomicAdd(px + 2, c.z);
-        } else {
-            alive = true;
+    bool alive = false, was_live = false;
+    if (!init) {
+        const float4 rd = q.d[e];
+        was_live = f2u(rd.w) != WF_DEAD;
+        if (was_live) {
+            const float4 ro = q.o[e];
+            const uint2 id = q.id[e];
+            const uint4 hit = pool.hit[e];
+            const float4 thr = q.thr[e], rad = q.rad[e];
+            path.ray.time = ro.w;
+            path.thr = v3(thr.x, thr.y, thr.z); path.rad = v3(rad.x, rad.y, rad.z);
+            path.pixel = id.x; path.sample = id.y; path.block = f2u(thr.w);
+            const uint32_t dl = f2u(rad.w);
+            path.depth_left = dl & 0x7FFFFFFFu; path.poison = (dl >> 31) != 0u;
+            Trav T;
+            T.o = v3(ro.x, ro.y, ro.z); T.d = v3(rd.x, rd.y, rd.z);
+            T.t = u2f(hit.x); T.ref = hit.y; T.inner = hit.z;
+            TraceCtx cx = path_ctx(sc, P, path, wp);
+            bool finished = segment_end(cx, sc.noises, P, path, T);
+            if (!finished && path.depth_left < 1u) finished = true;   // ray_color.rs:14-16: the next call returns black
+            if (finished) {
+                V3 c = path_result(path);
+                if (!finite3(c)) atomicAdd(&ctr->nan_paths, 1ull);
+                float* px = sum + ((size_t)path.pixel - (size_t)P.row_begin * W) * 3u;
+                atomicAdd(px + 0, c.x); atomicAdd(px + 1, c.y); atomicAdd(px + 2, c.z);
+            } else {
+                alive = true;
+            }
         }
     }
-    // ---- regeneration: free threads take the next camera samples, tile-major (8x4 pixels x one
-    // sample per 32 consecutive indices) so that the primary rays of a warp stay coherent
+    // ---- regeneration: free slots take the next camera samples of the warp's reserved range.
+    // 32 consecutive indices = one 8x4 tile x one sample, so primary rays that start together are coherent.
     const bool need = !alive && !(!first_hit_integrator(P.integrator) && P.depth < 1u);
-    uint32_t n_need;
-    const uint32_t r_need = block_rank(need, s_warp, &n_need);
-    if (n_need != 0u) {
-        if (threadIdx.x == 0u) s_base_path = atomicAdd(&wc->next_path, (unsigned long long)n_need);
-        __syncthreads();
-        const unsigned long long k = s_base_path + r_need;
-        if (need && k < total) {
+    const uint32_t m = __ballot_sync(FULL, need);
+    if (m != 0u) {
+        unsigned long long* sup = pool.supply + 2u * (e >> 5);
+        unsigned long long nx = sup[0], en = sup[1];                  // same address for the whole warp
+        const uint32_t cnt = __popc(m), rank = __popc(m & ((1u << lane) - 1u));
+        const unsigned long long avail = en - nx;
+        unsigned long long base = 0ull, bend = 0ull;
+        if (avail < cnt) {                                            // refill: one atomic per warp per supply_chunk samples
+            if (lane == 0u) {                                         // (no atomic once the cursor has passed the end)
+                base = *reinterpret_cast<volatile unsigned long long*>(&wc->next_path);
+                if (base < total) base = atomicAdd(&wc->next_path, (unsigned long long)L.supply_chunk);
+            }
+            base = __shfl_sync(FULL, base, 0);
+            if (base > total) base = total;
+            bend = base + L.supply_chunk < total ? base + L.supply_chunk : total;
+        }
+        unsigned long long k = ~0ull;
+        if (need) {
+            if (rank < avail) k = nx + rank;
+            else if (base + (rank - avail) < bend) k = base + (rank - avail);
+        }
+        if (avail < cnt) { nx = base + (cnt - avail) < bend ? base + (cnt - avail) : bend; en = bend; }
+        else nx += cnt;
+        if (lane == 0u) { sup[0] = nx; sup[1] = en; }
+        if (k != ~0ull) {
             const uint32_t pix = (uint32_t)(k & 31ull);
             const unsigned long long g = k >> 5;
             const uint32_t tile = (uint32_t)(g / P.sample_count), s = P.sample_begin + (uint32_t)(g % P.sample_count);
             const uint32_t tx = tile % L.tiles_x, ty = tile / L.tiles_x;
             const uint32_t i = tx * 8u + (pix & 7u), jr = ty * 4u + (pix >> 3);
-            if (i < W && jr < P.row_count) {
+            if (i < W && jr < P.row_count) {                          // edge tiles are padded; such an index is dropped
                 generate(P, i, P.row_begin + jr, s, path);
                 alive = true;
             }
         }
     }
-    // ---- append the live paths to the next queue
-    uint32_t n_live;
-    const uint32_t r_live = block_rank(alive, s_warp, &n_live);
-    if (n_live != 0u) {
-        if (threadIdx.x == 0u) s_base_q = atomicAdd(&wc->n_queue[cur ^ 1u], n_live);
-        __syncthreads();
-        if (alive) {
-            const uint32_t o = s_base_q + r_live;
-            qo.o[o] = make_float4(path.ray.o.x, path.ray.o.y, path.ray.o.z, path.ray.time);
-            qo.d[o] = make_float4(path.ray.d.x, path.ray.d.y, path.ray.d.z, u2f(P.depth - path.depth_left));
-            qo.id[o] = make_uint2(path.pixel, path.sample);
-            qo.thr[o] = make_float4(path.thr.x, path.thr.y, path.thr.z, u2f(path.block));
-            qo.rad[o] = make_float4(path.rad.x, path.rad.y, path.rad.z,
-                                    u2f(path.depth_left | (path.poison ? 0x80000000u : 0u)));
-        }
+    if (!alive && !was_live && !init) return;                         // dead before, dead now: nothing to write
+    if (alive) {
+        q.o[e] = make_float4(path.ray.o.x, path.ray.o.y, path.ray.o.z, path.ray.time);
+        q.d[e] = make_float4(path.ray.d.x, path.ray.d.y, path.ray.d.z, u2f(P.depth - path.depth_left));
+        q.id[e] = make_uint2(path.pixel, path.sample);
+        q.thr[e] = make_float4(path.thr.x, path.thr.y, path.thr.z, u2f(path.block));
+        q.rad[e] = make_float4(path.rad.x, path.rad.y, path.rad.z,
+                               u2f(path.depth_left | (path.poison ? 0x80000000u : 0u)));
+        const uint32_t am = __activemask();
+        // same value from every warp; read first (L2) so that only the first few warps store
+        if (lane == (uint32_t)(__ffs(am) - 1) && __ldcg(&wc->live_mark) != mark) wc->live_mark = mark;
+    } else {
+        q.d[e] = make_float4(0.f, 0.f, 0.f, u2f(WF_DEAD));
     }
-    if (n_nan != 0u) atomicAdd(&ctr->nan_paths, (unsigned long long)n_nan);
 #if defined(RTW_COUNT_WORK)
     if (wk.hits) atomicAdd(&ctr->hits, (unsigned long long)wk.hits);
 #endif
@@ -419,14 +422,14 @@ cudaError_t RTW_FN(launch_mega)(const Scene& sc, const RenderParams& P, float* d
 }
 
 cudaError_t RTW_FN(launch_wf_extend)(const Scene& sc, const RenderParams& P, const WfPool& pool, WfCounters* d_wc,
-                                     Counters* d_ctr, uint32_t cur, const WfLaunch& L, cudaStream_t st) {
-    RTW_CAT(variant_, RTW_VARIANT)::wf_extend_kernel<<<L.extend_grid, RTW_WF_BLOCK, L.smem_bytes, st>>>(sc, P, pool, d_wc, d_ctr, cur, L);
+                                     Counters* d_ctr, const WfLaunch& L, cudaStream_t st) {
+    RTW_CAT(variant_, RTW_VARIANT)::wf_extend_kernel<<<L.extend_grid, RTW_WF_BLOCK, L.smem_bytes, st>>>(sc, P, pool, d_wc, d_ctr, L);
     return cudaGetLastError();
 }
 
 cudaError_t RTW_FN(launch_wf_shade)(const Scene& sc, const RenderParams& P, const WfPool& pool, WfCounters* d_wc,
-                                    Counters* d_ctr, float* d_sum, uint32_t cur, int init, const WfLaunch& L, cudaStream_t st) {
-    RTW_CAT(variant_, RTW_VARIANT)::wf_shade_kernel<<<L.shade_grid, RTW_WF_SHADE_BLOCK, 0, st>>>(sc, P, pool, d_wc, d_ctr, d_sum, cur, init, L);
+                                    Counters* d_ctr, float* d_sum, uint32_t mark, int init, const WfLaunch& L, cudaStream_t st) {
+    RTW_CAT(variant_, RTW_VARIANT)::wf_shade_kernel<<<L.shade_grid, RTW_WF_SHADE_BLOCK, 0, st>>>(sc, P, pool, d_wc, d_ctr, d_sum, mark, init, L);
     return cudaGetLastError();
 }
 

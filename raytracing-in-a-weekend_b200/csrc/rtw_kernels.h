@@ -32,30 +32,34 @@ struct MegaLaunch {
     size_t smem_bytes;     // dynamic shared memory: stack_words * block * 4
 };
 
-// ---- wavefront pipeline (RTW_FLAG_WAVEFRONT): the paths in flight live in HBM as two queues of
-// path records (SoA), streamed back and forth. One iteration =
-//   extend  persistent warps pull consecutive rays of queue[cur] (chunk reservation + L1 prefetch),
-//           walk the BVH and store the closest hit at the ray's queue position;
-//   shade   one thread per position: miss / Hit / scatter. A finished path adds its radiance to
-//           the frame and its thread starts the next camera sample; every live path is appended
-//           to queue[cur^1] (ballot + one atomic per block), so the queue stays dense and full.
+// ---- wavefront pipeline (RTW_FLAG_WAVEFRONT): the paths in flight live in HBM as a pool of
+// `capacity` path records (SoA), one fixed slot per shade thread. One iteration =
+//   extend  persistent warps pull consecutive slots (chunk reservation + L1 prefetch), walk the BVH
+//           for the live ones and store the closest hit in the slot;
+//   shade   one thread per slot: miss / Hit / scatter, record rewritten in place. A finished path
+//           adds its radiance to the frame and its thread starts the next camera sample of the
+//           frame's tile-major sample order. Samples are handed out from a per-warp range of
+//           `supply_chunk` indices (ballot ranks inside the warp; one atomic on the global cursor
+//           per refill), so nothing has to be compacted while the supply lasts: every slot stays
+//           live. A slot that finds the supply exhausted is marked dead.
 struct WfQueue {
     float4* o;           // origin.xyz, time
-    float4* d;           // direction.xyz, bits(bounce)
+    float4* d;           // direction.xyz, bits(bounce) (WF_DEAD: empty slot)
     uint2*  id;          // pixel index, sample index (Philox counter words 0/1)
     float4* thr;         // throughput.xyz, bits(next Philox block)
     float4* rad;         // radiance.xyz, bits(depth_left | poison << 31)
 };
+#define WF_DEAD 0xFFFFFFFFu
 struct WfPool {
-    WfQueue q[2];
-    uint4*  hit;         // bits(t), ref, inner, 0   (extend -> shade, by queue position)
+    WfQueue q;
+    uint4*  hit;         // bits(t), ref, inner, 0   (extend -> shade)
+    unsigned long long* supply;   // per shade warp: [next, end) of its reserved sample indices
     uint32_t capacity;
 };
 struct WfCounters {
-    uint32_t n_queue[2];             // entries of queue[k]
-    uint32_t head;                   // extend's reservation cursor into queue[cur]
-    uint32_t pad;
-    unsigned long long next_path;    // next camera sample to hand out (tile-major order)
+    uint32_t head;                   // extend's reservation cursor into the pool
+    uint32_t live_mark;              // = `mark` of the last shade launch that left a live slot
+    unsigned long long next_path;    // global cursor into the tile-major sample order
     unsigned long long total_paths;  // 32 * tiles * samples of this render (edge-tile padding included)
     unsigned long long iterations;
 };
@@ -63,7 +67,8 @@ struct WfLaunch {
     uint32_t tiles_x, tiles_y;
     uint32_t stack_words;
     uint32_t fetch_min;              // extend fetches new rays when at least this many lanes are idle
-    uint32_t chunk;                  // queue positions a warp reserves per atomic
+    uint32_t chunk;                  // pool slots an extend warp reserves per atomic
+    uint32_t supply_chunk;           // sample indices a shade warp reserves per atomic
     int extend_grid, shade_grid;
     size_t smem_bytes;
 };
@@ -71,7 +76,7 @@ struct WfLaunch {
 #ifndef RTW_WF_EXTEND_MINB
 #define RTW_WF_EXTEND_MINB 1      // min resident blocks per SM asked of the compiler for wf_extend (register cap)
 #endif
-#define RTW_WF_SHADE_BLOCK 256
+#define RTW_WF_SHADE_BLOCK 128
 
 #define RTW_MEGA_BLOCK 128
 #define RTW_SMEM_NOISES 2
@@ -81,9 +86,9 @@ struct WfLaunch {
                                      uint32_t* d_work, const MegaLaunch& L, cudaStream_t st);                \
     cudaError_t mega_occupancy_##SUFFIX(int* blocks_per_sm, size_t smem_bytes);                              \
     cudaError_t launch_wf_extend_##SUFFIX(const Scene& sc, const RenderParams& P, const WfPool& pool, WfCounters* d_wc,   \
-                                          Counters* d_ctr, uint32_t cur, const WfLaunch& L, cudaStream_t st);            \
+                                          Counters* d_ctr, const WfLaunch& L, cudaStream_t st);                          \
     cudaError_t launch_wf_shade_##SUFFIX(const Scene& sc, const RenderParams& P, const WfPool& pool, WfCounters* d_wc,    \
-                                         Counters* d_ctr, float* d_sum, uint32_t cur, int init, const WfLaunch& L,       \
+                                         Counters* d_ctr, float* d_sum, uint32_t mark, int init, const WfLaunch& L,      \
                                          cudaStream_t st);                                                               \
     cudaError_t wf_extend_occupancy_##SUFFIX(int* blocks_per_sm, size_t smem_bytes);
 
