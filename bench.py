@@ -316,7 +316,7 @@ def run_b200(args):
         oc = vp.opts(job.ray_color, job.mode)
         oc.output = A.RTW_OUT_SUM
         oc.flags |= A.RTW_FLAG_COUNT_WORK
-        oc.sample_begin, oc.sample_count = 0, min(16, spp)
+        oc.sample_begin, oc.sample_count = 0, min(256, spp)
         h.render_device(cam, oc, buf.data_ptr(), stream)
         wc = h.stats()
         per_ray = {"node": wc.nodes / wc.rays, "sphere": wc.sphere_tests / wc.rays, "quad": wc.quad_tests / wc.rays,

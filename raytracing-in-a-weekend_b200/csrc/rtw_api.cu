@@ -91,6 +91,9 @@ struct rtw_scene {
     uint32_t stack_words = 0;
     size_t smem_bytes = 0;
     Scene d{};                            // device pointers
+    Scene d_cur{};                        // what the current render walks: d, or d with top = top_inside
+    Level top_all{}, top_inside{};
+    std::vector<HostScene::Enclosing> enclosing;
     std::vector<void*> allocs;
     std::vector<cudaArray_t> arrays;
     std::vector<cudaTextureObject_t> texobjs;
@@ -113,7 +116,9 @@ struct rtw_scene {
     uint64_t wf_paths = 0, wf_iterations = 0;
     static const int kTimed = 32;             // sampled (extend, shade) launches timed with events per render
     cudaEvent_t wf_t[kTimed][3] = {};
-    int wf_timed = 0;
+    int wf_timed = 0;                         // samples recorded this render
+    int wf_harvested = 0;                     // ... of which already folded into the sums below
+    double wf_extend_sum = 0.0, wf_shade_sum = 0.0;
 
     ~rtw_scene() {
         cudaSetDevice(device);
@@ -195,6 +200,7 @@ int upload_scene(rtw_scene* s, HostScene& hs) {
     if ((rc = upload(s, hs.textures, &d.textures))) return rc;
     if ((rc = upload(s, hs.noises, &d.noises))) return rc;
     d.top = hs.top;
+    s->top_all = hs.top; s->top_inside = hs.top_inside; s->enclosing = hs.enclosing;
     std::memcpy(d.background, hs.background, sizeof d.background);
     d.n_noises = (uint32_t)hs.noises.size();
     return RTW_OK;
@@ -289,8 +295,10 @@ int enqueue_wavefront(rtw_scene* s, const RenderParams& P, int variant, float* d
     L.stack_words = s->stack_words;
     L.smem_bytes = s->smem_bytes;
     L.fetch_min = std::min(32u, std::max(1u, env_u32("RTW_WF_FETCH_MIN", 16u)));
-    L.chunk = std::max(32u, env_u32("RTW_WF_CHUNK", 32u));
+    L.chunk = std::max(32u, env_u32("RTW_WF_CHUNK", 64u));
     L.supply_chunk = std::max(32u, env_u32("RTW_WF_SUPPLY_CHUNK", 128u)) & ~31u;
+    L.sample_major = env_u32("RTW_WF_SAMPLE_MAJOR", 0u) ? 1u : 0u;
+    L.index32 = ((unsigned long long)L.tiles_x * L.tiles_y * P.sample_count < (1ull << 32)) ? 1u : 0u;
     CK(cudaMemsetAsync(s->pool.supply, 0, (size_t)s->pool.capacity / 16u * sizeof(unsigned long long), st));
     L.extend_grid = s->sm_count * std::max(1, std::min(s->occ_wf[variant], (int)env_u32("RTW_WF_MAX_BLOCKS", 64u)));
     L.shade_grid = (int)(s->pool.capacity / RTW_WF_SHADE_BLOCK);
@@ -299,25 +307,33 @@ int enqueue_wavefront(rtw_scene* s, const RenderParams& P, int variant, float* d
     s->h_wc[0] = init;
     CK(cudaMemcpyAsync(s->d_wc, &s->h_wc[0], sizeof(WfCounters), cudaMemcpyHostToDevice, st));
     auto extend = [&]() {
-        return variant == 1   ? launch_wf_extend_strict(s->d, P, s->pool, s->d_wc, s->d_ctr, L, st)
-               : variant == 2 ? launch_wf_extend_count(s->d, P, s->pool, s->d_wc, s->d_ctr, L, st)
-                              : launch_wf_extend_fast(s->d, P, s->pool, s->d_wc, s->d_ctr, L, st);
+        return variant == 1   ? launch_wf_extend_strict(s->d_cur, P, s->pool, s->d_wc, s->d_ctr, L, st)
+               : variant == 2 ? launch_wf_extend_count(s->d_cur, P, s->pool, s->d_wc, s->d_ctr, L, st)
+                              : launch_wf_extend_fast(s->d_cur, P, s->pool, s->d_wc, s->d_ctr, L, st);
     };
     auto shade = [&](uint32_t mark, int init_pass) {
-        return variant == 1   ? launch_wf_shade_strict(s->d, P, s->pool, s->d_wc, s->d_ctr, d_out, mark, init_pass, L, st)
-               : variant == 2 ? launch_wf_shade_count(s->d, P, s->pool, s->d_wc, s->d_ctr, d_out, mark, init_pass, L, st)
-                              : launch_wf_shade_fast(s->d, P, s->pool, s->d_wc, s->d_ctr, d_out, mark, init_pass, L, st);
+        return variant == 1   ? launch_wf_shade_strict(s->d_cur, P, s->pool, s->d_wc, s->d_ctr, d_out, mark, init_pass, L, st)
+               : variant == 2 ? launch_wf_shade_count(s->d_cur, P, s->pool, s->d_wc, s->d_ctr, d_out, mark, init_pass, L, st)
+                              : launch_wf_shade_fast(s->d_cur, P, s->pool, s->d_wc, s->d_ctr, d_out, mark, init_pass, L, st);
     };
-    s->wf_timed = 0;
+    s->wf_timed = 0; s->wf_harvested = 0; s->wf_extend_sum = 0.0; s->wf_shade_sum = 0.0;
     CK(shade(0u, 1));                       // first fill
     s->launches += 1;
     const uint32_t batch = std::max(1u, env_u32("RTW_WF_BATCH", 8u));
     uint32_t it = 0;
     for (uint32_t k = 0;; ++k) {
         for (uint32_t b = 0; b < batch; ++b, ++it) {
-            // every 8th round, from the 4th on, is bracketed with events (the last kTimed samples are kept)
+            // every 8th round, from the 4th on, is bracketed with events. A ring slot about to be reused
+            // was recorded kTimed*8 rounds ago (the host runs at most three batches ahead), so its
+            // events are complete: its times go into the running sums => the mean covers the whole render.
             const bool timed = (it & 7u) == 3u;
             cudaEvent_t* te = s->wf_t[s->wf_timed % rtw_scene::kTimed];
+            if (timed && s->wf_timed >= rtw_scene::kTimed) {
+                float a = 0.f, b = 0.f;
+                CK(cudaEventElapsedTime(&a, te[0], te[1]));
+                CK(cudaEventElapsedTime(&b, te[1], te[2]));
+                s->wf_extend_sum += a; s->wf_shade_sum += b; ++s->wf_harvested;
+            }
             if (timed) CK(cudaEventRecord(te[0], st));
             CK(extend());
             if (timed) CK(cudaEventRecord(te[1], st));
@@ -346,6 +362,23 @@ int enqueue_render(rtw_scene* s, const rtw_camera* cam, const rtw_render_opts* o
     int rc = make_render_params(cam, o, P, total, err);
     if (rc) return fail(rc, err);
     const int variant = (o->flags & RTW_FLAG_STRICT_FP) ? 1 : (o->flags & RTW_FLAG_COUNT_WORK) ? 2 : 0;
+    // Enclosing volumes (rtw_host.h): when the camera (lens included) and every moving sphere over the
+    // shutter interval stay inside each of them, no ray of this render starts outside => they cannot
+    // return a hit (instance.rs:280-300) and the fast kernels walk the top level built without them.
+    s->d_cur = s->d;
+    if (variant != 1 && !s->enclosing.empty() && !env_u32("RTW_KEEP_ENCLOSING", 0u)) {
+        const float lens = std::fabs(cam->lens_radius) *
+                           (std::sqrt(cam->u[0] * cam->u[0] + cam->u[1] * cam->u[1] + cam->u[2] * cam->u[2]) +
+                            std::sqrt(cam->v[0] * cam->v[0] + cam->v[1] * cam->v[1] + cam->v[2] * cam->v[2]));
+        const float tmax = std::fabs(P.time0) + std::fabs(P.shutter_speed);
+        bool inside = true;
+        for (const auto& e : s->enclosing) {
+            float d2 = 0.f;
+            for (int a = 0; a < 3; ++a) { const float x = cam->origin[a] - e.c[a]; d2 += x * x; }
+            if (!(std::sqrt(d2) + lens < e.r) || !(e.mov_far + e.mov_speed * tmax < e.r)) inside = false;
+        }
+        if (inside) s->d_cur.top = s->top_inside;
+    }
     MegaLaunch L = plan_mega(s, P, variant);
     if ((uint64_t)L.tiles_x * L.tiles_y * L.n_chunks > 0xFFFFFFF0ull) return fail(RTW_E_UNSUPPORTED, "too many work items; shard the render");
     const size_t n_values = (size_t)P.row_count * cam->width * 3u;
@@ -360,9 +393,9 @@ int enqueue_render(rtw_scene* s, const rtw_camera* cam, const rtw_render_opts* o
         s->launches = 0;
         if ((rc = enqueue_wavefront(s, P, variant, d_out, st))) return rc;
     } else {
-        CK(variant == 1   ? launch_mega_strict(s->d, P, d_out, s->d_ctr, s->d_work, L, st)
-           : variant == 2 ? launch_mega_count(s->d, P, d_out, s->d_ctr, s->d_work, L, st)
-                          : launch_mega_fast(s->d, P, d_out, s->d_ctr, s->d_work, L, st));
+        CK(variant == 1   ? launch_mega_strict(s->d_cur, P, d_out, s->d_ctr, s->d_work, L, st)
+           : variant == 2 ? launch_mega_count(s->d_cur, P, d_out, s->d_ctr, s->d_work, L, st)
+                          : launch_mega_fast(s->d_cur, P, d_out, s->d_ctr, s->d_work, L, st));
         s->launches = 1;
     }
     CK(cudaEventRecord(s->ev1, st));
@@ -525,14 +558,16 @@ int rtw_get_stats(rtw_scene* scene, rtw_stats* out) {
     out->instance_tests = scene->h_ctr->instances; out->hits = scene->h_ctr->hits;
     if (scene->last_wavefront) {
         out->iterations = scene->wf_iterations;
-        const int n = std::min(scene->wf_timed, (int)rtw_scene::kTimed);
-        double se = 0.0, ss = 0.0;
-        for (int k = 0; k < n; ++k) {
+        // the samples still in the ring (the last kTimed at most) join the sums harvested on the way
+        double se = scene->wf_extend_sum, ss = scene->wf_shade_sum;
+        for (int k = scene->wf_harvested; k < scene->wf_timed; ++k) {
             float a = 0.f, b = 0.f;
-            CK(cudaEventElapsedTime(&a, scene->wf_t[k][0], scene->wf_t[k][1]));
-            CK(cudaEventElapsedTime(&b, scene->wf_t[k][1], scene->wf_t[k][2]));
+            cudaEvent_t* te = scene->wf_t[k % rtw_scene::kTimed];
+            CK(cudaEventElapsedTime(&a, te[0], te[1]));
+            CK(cudaEventElapsedTime(&b, te[1], te[2]));
             se += a; ss += b;
         }
+        const int n = scene->wf_timed;
         if (n > 0) { out->extend_ms = (float)(se / n); out->shade_ms = (float)(ss / n); }
     }
     CK(cudaEventElapsedTime(&out->kernel_ms, scene->ev0, scene->ev1));

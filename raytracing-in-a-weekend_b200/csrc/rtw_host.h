@@ -25,6 +25,15 @@ struct HostScene {
     std::vector<std::vector<float4>> texels;       // per texture, RGBA f32 (A = 0)
     std::vector<Noise> noises;
     Level top;
+    // Enclosing volumes: a constant-density instance made of one sphere only scatters rays
+    // that enter it from outside (instance.rs:280-300: a ray that starts inside meets the exit face,
+    // probes from there outwards and finds nothing => None). When such a sphere contains every other
+    // primitive of the scene, and the camera, no ray of a render ever starts outside it, so it can
+    // never return a hit: `top_inside` is the top level built without those instances. The fast
+    // kernels walk it when the camera test passes (rtw_api.cu); the strict ones walk `top`.
+    struct Enclosing { float c[3]; float r; float mov_far, mov_speed; };
+    std::vector<Enclosing> enclosing;
+    Level top_inside;            // valid when !enclosing.empty()
     float background[3];
     rtw_scene_info info;
     uint32_t top_depth = 0, inner_depth = 0;   // deepest node chain of the top level / of any instance (-> stack_words)

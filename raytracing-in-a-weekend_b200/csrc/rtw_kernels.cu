@@ -252,26 +252,45 @@ wf_extend_kernel(const Scene sc, const RenderParams P, const WfPool pool, WfCoun
         }
         // ---- one step of ONE kind per iteration: the kind most lanes are waiting for. Lanes in
         // other states sit the iteration out, so that the rarer, dearer steps (leaf tests, instance
-        // entry / exit) run with many lanes at once instead of after every node step.
-        const uint32_t on_node = __ballot_sync(FULL, T.cur < NODE_LIMIT);
-        const uint32_t on_prim = __ballot_sync(FULL, ref_is_leaf_test(T.cur));
-        const uint32_t on_event = __ballot_sync(FULL, ref_is_event(T.cur));
-        const int cn = __popc(on_node), cp = __popc(on_prim), ce = __popc(on_event);
+        // entry / exit) run with many lanes at once instead of after every node step. Voting sphere
+        // tests, quad tests and one-sphere instances as separate kinds (-DRTW_SPLIT_KINDS) makes each
+        // leaf step uniform but starves the rarer kinds: -11 % on C5 (profiles/r1h_ab.txt), so all
+        // leaf tests are one kind and the tests themselves are branch-free instead (rtw_trace.h).
+        const uint32_t cur = T.cur;
+#if !defined(RTW_SPLIT_KINDS)
+        const uint32_t kind = cur < NODE_LIMIT ? 0u : ref_is_event(cur) ? 4u : cur == CUR_DONE ? 5u : 1u;
+#else
+        const uint32_t kind = cur < NODE_LIMIT ? 0u
+                              : ref_is_event(cur) ? 4u
+                              : ref_is_one_sphere_instance(cur) ? 3u
+                              : cur == CUR_DONE ? 5u
+                              : (cur >> 30);                 // KIND_SPHERE = 1, KIND_QUAD = 2
+#endif
+        const int c0 = __popc(__ballot_sync(FULL, kind == 0u)), c1 = __popc(__ballot_sync(FULL, kind == 1u)),
+                  c4 = __popc(__ballot_sync(FULL, kind == 4u));
+        uint32_t best = 0u; int cb = c0;
+        if (c1 > cb) { best = 1u; cb = c1; }
+#if defined(RTW_SPLIT_KINDS)
+        const int c2 = __popc(__ballot_sync(FULL, kind == 2u)), c3 = __popc(__ballot_sync(FULL, kind == 3u));
+        if (c2 > cb) { best = 2u; cb = c2; }
+        if (c3 > cb) { best = 3u; cb = c3; }
+#endif
+        if (c4 > cb) { best = 4u; cb = c4; }
         SCHED_COUNT(iters, 0, 0);
-        if (cn >= cp && cn >= ce) {
-            SCHED_COUNT(step, 0, cn);
+        if (best == 0u) {
+            SCHED_COUNT(step, 0, cb);
             SCHED_TIME_BEGIN(0);
-            if (T.cur < NODE_LIMIT) trav_step_node<false>(cx, T, S);
+            if (kind == 0u) trav_step_node<RTW_WF_INLINE_PRIMS != 0>(cx, T, S);
             SCHED_TIME_END();
-        } else if (cp >= ce) {
-            SCHED_COUNT(step, 1, cp);
+        } else if (best != 4u) {
+            SCHED_COUNT(step, 1, cb);
             SCHED_TIME_BEGIN(1);
-            if (ref_is_leaf_test(T.cur)) trav_step_prim(cx, T, S);
+            if (kind == best) trav_step_prim(cx, T, S);
             SCHED_TIME_END();
         } else {
-            SCHED_COUNT(step, 2, ce);
+            SCHED_COUNT(step, 2, cb);
             SCHED_TIME_BEGIN(2);
-            if (ref_is_event(T.cur)) trav_step_event(cx, time, T, S);
+            if (kind == 4u) trav_step_event(cx, time, T, S);
             SCHED_TIME_END();
         }
         if (busy && T.cur == CUR_DONE) {
@@ -383,7 +402,17 @@ wf_shade_kernel(const Scene sc, const RenderParams P, const WfPool pool, WfCount
         if (k != ~0ull) {
             const uint32_t pix = (uint32_t)(k & 31ull);
             const unsigned long long g = k >> 5;
-            const uint32_t tile = (uint32_t)(g / P.sample_count), s = P.sample_begin + (uint32_t)(g % P.sample_count);
+            uint32_t tile, s;
+            if (L.sample_major) {                                     // the whole frame once per sample
+                const uint32_t nt = L.tiles_x * L.tiles_y;
+                if (L.index32) { const uint32_t g32 = (uint32_t)g; s = g32 / nt; tile = g32 - s * nt; }
+                else { s = (uint32_t)(g / nt); tile = (uint32_t)(g % nt); }
+                s += P.sample_begin;
+            } else {                                                  // every sample of a tile, then the next tile
+                if (L.index32) { const uint32_t g32 = (uint32_t)g; tile = g32 / P.sample_count; s = g32 - tile * P.sample_count; }
+                else { tile = (uint32_t)(g / P.sample_count); s = (uint32_t)(g % P.sample_count); }
+                s += P.sample_begin;
+            }
             const uint32_t tx = tile % L.tiles_x, ty = tile / L.tiles_x;
             const uint32_t i = tx * 8u + (pix & 7u), jr = ty * 4u + (pix >> 3);
             if (i < W && jr < P.row_count) {                          // edge tiles are padded; such an index is dropped

@@ -69,12 +69,17 @@ struct WfLaunch {
     uint32_t fetch_min;              // extend fetches new rays when at least this many lanes are idle
     uint32_t chunk;                  // pool slots an extend warp reserves per atomic
     uint32_t supply_chunk;           // sample indices a shade warp reserves per atomic
+    uint32_t sample_major;           // order of the sample supply: 0 = tile-major (all samples of a tile, then the next tile), 1 = sample-major
+    uint32_t index32;                // tiles * samples < 2^32: 32-bit index arithmetic
     int extend_grid, shade_grid;
     size_t smem_bytes;
 };
 #define RTW_WF_BLOCK 128
 #ifndef RTW_WF_EXTEND_MINB
-#define RTW_WF_EXTEND_MINB 1      // min resident blocks per SM asked of the compiler for wf_extend (register cap)
+#define RTW_WF_EXTEND_MINB 6      // min resident blocks per SM asked of the compiler for wf_extend (80 registers, no spills; +2.2 % over 5 blocks, profiles/r1h_ab_inline_minblocks.txt)
+#endif
+#ifndef RTW_WF_INLINE_PRIMS
+#define RTW_WF_INLINE_PRIMS 0     // 1: wf_extend tests sphere / quad children inside the node step (A/B)
 #endif
 #define RTW_WF_SHADE_BLOCK 128
 

@@ -58,8 +58,43 @@ RTW_HD_NOINL bool slab_slow(V3 lo, V3 hi, V3 o, V3 d, float mint, float maxt, fl
     return !(mn > mx);
 }
 
+// The fast device build (nvcc's default contraction, no -DRTW_STRICT_FP) may reorder and
+// approximate within ~1 ulp; the strict build and the host keep the reference's operation order.
+#if defined(__CUDA_ARCH__) && !defined(RTW_STRICT_FP)
+#define RTW_FAST_NODES 1
+#endif
+
+#if defined(RTW_FAST_NODES)
+// 1/x and sqrt(x) from the SFU approximations plus one Newton step (<= 1 ulp, no slow-path branch).
+__device__ __forceinline__ float fast_rcp(float x) {
+    float r;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return fmaf(fmaf(-x, r, 1.0f), r, r);
+}
+__device__ __forceinline__ float fast_sqrt_pos(float x) {   // x > 0
+    float rs;
+    asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(rs) : "f"(x));
+    const float s = x * rs;
+    return fmaf(fmaf(-s, s, x), 0.5f * rs, s);
+}
+#endif
+
 // Sphere::collision_normal up to the accepted root (sphere.rs:100-123). `c` = centre at ray time.
 RTW_HD bool sphere_t(V3 c, float radius, V3 o, V3 d, float a, float mint, float maxt, float& t) {
+#if defined(RTW_FAST_NODES) && !defined(RTW_NO_FASTPRIM)
+    // same roots, branch-free: both candidates from one reciprocal, selected afterwards, so that the
+    // lanes of a warp run one straight instruction sequence instead of four nested branches
+    const V3 oc = o - c;
+    const float b = dot(oc, d);
+    const float cc = dot(oc, oc) - radius * radius;
+    const float disc = b * b - a * cc;
+    const float sq = fast_sqrt_pos(fmaxf(disc, 1e-30f));
+    const float ia = fast_rcp(a);
+    const float x1 = (-b - sq) * ia, x2 = (sq - b) * ia;
+    const float x = x1 < mint ? x2 : x1;
+    t = x;
+    return disc >= 0.0f && x >= mint && x <= maxt;
+#else
     V3 oc = o - c;
     float b = dot(oc, d);
     float cc = dot(oc, oc) - radius * radius;
@@ -71,6 +106,7 @@ RTW_HD bool sphere_t(V3 c, float radius, V3 o, V3 d, float a, float mint, float 
     if (x < mint || x > maxt) return false;
     t = x;
     return true;
+#endif
 }
 
 // Quad::collision_normal up to the inside test (quad.rs:38-60).
@@ -78,6 +114,18 @@ RTW_HD bool quad_t(const Quad* qp, V3 o, V3 d, float mint, float maxt, float& t)
     float4 q0 = RTW_LDG(&qp->q0), q1 = RTW_LDG(&qp->q1), q2 = RTW_LDG(&qp->q2), q3 = RTW_LDG(&qp->q3);
     V3 n = v3(q0.x, q0.y, q0.z);
     float den = dot(n, d);
+#if defined(RTW_FAST_NODES) && !defined(RTW_NO_FASTPRIM)
+    {   // the same tests, evaluated without early exits (one straight sequence per warp)
+        const float tt = (q0.w - dot(n, o)) * fast_rcp(den);
+        const V3 p = o + d * tt;
+        const V3 planar = p - v3(q1.x, q1.y, q1.z);
+        const V3 u = v3(q1.w, q2.x, q2.y), v = v3(q2.z, q2.w, q3.x), w = v3(q3.y, q3.z, q3.w);
+        const float al = dot(w, cross(planar, v));
+        const float be = dot(w, cross(u, planar));
+        t = tt;
+        return fabsf(den) > 1e-8f && tt >= mint && tt <= maxt && al >= 0.0f && al <= 1.0f && be >= 0.0f && be <= 1.0f;
+    }
+#endif
     if (fabsf(den) <= 1e-8f) return false;
     float tt = (q0.w - dot(n, o)) / den;
     if (tt < mint || tt > maxt) return false;
@@ -264,9 +312,6 @@ RTW_HD bool ref_is_leaf_test(uint32_t r) { return ref_is_prim(r) || ref_is_one_s
 //   strict build / host: exact f32 boxes, the reference's own operation order, (bound - o) * (1/d);
 //   fast device build: half-float boxes (Node16, rounded outwards) and one FFMA per plane,
 //   bound * (1/d) - o * (1/d).
-#if defined(__CUDA_ARCH__) && !defined(RTW_STRICT_FP)
-#define RTW_FAST_NODES 1
-#endif
 RTW_HD void slab4(const Scene& sc, uint32_t idx, const Trav& T, float mint, float maxt, float tn[4], uint4& rr) {
 #if defined(RTW_FAST_NODES)
     const Node16* np = &sc.nodes16[idx];
@@ -401,10 +446,21 @@ RTW_HD void trav_one_sphere_instance(const TraceCtx& cx, uint32_t iref, Trav& T)
         slow = !(isfinite(inv.x) && isfinite(inv.y) && isfinite(inv.z));
     }
     const V3 lo = v3(r2.x, r2.y, r2.z), hi = v3(r3.x, r3.y, r3.z);
+    const V3 c = v3(s.x, s.y, s.z);
     float tn, t;
+#if defined(RTW_FAST_NODES) && !defined(RTW_NO_VOLSKIP)
+    // A ray that starts inside a constant-density sphere meets the exit face first; the probe then
+    // starts on or beyond that face heading outwards and finds nothing, so the reference returns
+    // None (instance.rs:280-300, SURVEY N14: only rays entering from outside can scatter). The
+    // fast build takes that exit before the square root, the free-flight draw and the logarithm;
+    // the strict build walks the literal sequence.
+    if ((flags & INST_VOLUME) && r0.w > 0.0f) {
+        const V3 oc = o - c;
+        if (dot(oc, oc) - s.w * s.w < 0.0f) return;
+    }
+#endif
     if (!slab_ray(lo, hi, o, d, inv, slow, cx.mint, T.t, tn)) return;
     RTW_COUNT(cx, spheres);
-    const V3 c = v3(s.x, s.y, s.z);
     if (!sphere_t(c, s.w, o, d, a, cx.mint, T.t, t)) return;
     if (flags & INST_VOLUME) {
         // const_density (instance.rs:24-26), as volume_distance()

@@ -379,6 +379,51 @@ int build_host_scene(const rtw_scene_desc* d, HostScene& hs, std::string& err) {
     hs.top = bld.level(top, 0u, (uint32_t)top_moving.size());
     hs.info.n_tlas_nodes = (uint32_t)hs.nodes.size();
     uint32_t top_depth = bld.max_pushes, inner_depth = 0;
+    // ---- enclosing volumes (see rtw_host.h): one-sphere constant-density instances, not rotated,
+    // whose sphere contains every other leaf box of the top level with a 0.1 % margin
+    {
+        std::vector<char> drop(top.size(), 0);
+        auto far_corner = [](const Box& b, const float c[3]) {
+            float d2 = 0.f;
+            for (int a = 0; a < 3; ++a) { float e = std::max(std::fabs(b.lo[a] - c[a]), std::fabs(b.hi[a] - c[a])); d2 += e * e; }
+            return std::sqrt(d2);
+        };
+        for (size_t i = 0; i < top.size(); ++i) {
+            if (ref_kind(top[i].ref) != KIND_INSTANCE) continue;
+            const Instance& in = hs.instances[instance_index(top[i].ref)];
+            const uint32_t need = INST_ONE_SPHERE | INST_VOLUME | INST_ROT_IDENTITY;
+            if ((in.flags & need) != need || !(in.density > 0.f)) continue;
+            const rtw_instance& di = d->instances[in.index];
+            const float4 sp = hs.spheres[di.first_sphere];
+            HostScene::Enclosing e;
+            for (int a = 0; a < 3; ++a) e.c[a] = (&sp.x)[a] + in.t[a];
+            e.r = std::fabs(sp.w) * 0.999f;
+            e.mov_far = 0.f; e.mov_speed = 0.f;
+            bool ok = true;
+            for (size_t j = 0; j < top.size() && ok; ++j)
+                if (j != i && !(far_corner(top[j].box, e.c) < e.r)) ok = false;
+            auto moving_ok = [&](const std::vector<uint32_t>& mv) {
+                for (uint32_t m : mv) {
+                    e.mov_far = std::max(e.mov_far, far_corner(sbox[m], e.c));
+                    const float4 v = hs.sphere_vel[m];
+                    e.mov_speed = std::max(e.mov_speed, std::sqrt(v.x * v.x + v.y * v.y + v.z * v.z));
+                }
+            };
+            moving_ok(top_moving);
+            // moving spheres inside transformed instances: their boxes are not in world space; such a
+            // scene keeps the volume (nothing in the reference's scenes does this)
+            for (auto& il : inst_leaves) if (!inst_moving[il.first].empty()) ok = false;
+            if (!ok || !(e.mov_far < e.r)) continue;
+            drop[i] = 1;
+            hs.enclosing.push_back(e);
+        }
+        if (!hs.enclosing.empty()) {
+            std::vector<BuildPrim> rest;
+            for (size_t i = 0; i < top.size(); ++i) if (!drop[i]) rest.push_back(top[i]);
+            hs.top_inside = bld.level(rest, 0u, (uint32_t)top_moving.size());
+            top_depth = std::max(top_depth, bld.max_pushes);   // (info.n_tlas_nodes stays the full top level's count)
+        }
+    }
     blas_nodes_before = (uint32_t)hs.nodes.size();
     for (auto& il : inst_leaves) {
         uint32_t k = il.first;

@@ -124,3 +124,24 @@ def test_pipelines_agree(cuda):
     fin = np.isfinite(mega) & np.isfinite(wave)
     assert np.array_equal(np.isfinite(mega), np.isfinite(wave))
     assert np.allclose(mega[fin], wave[fin], rtol=1e-5, atol=1e-6)
+
+
+def test_enclosing_volume_elimination(cuda, monkeypatch):
+    """C5's global fog (a one-sphere constant-density instance around the whole scene and the camera)
+    can never scatter a ray that starts inside it (instance.rs:280-300). The fast kernels
+    walk a top level built without it; RTW_KEEP_ENCLOSING=1 keeps it. Same estimator: the images agree
+    statistically, and with the volume kept every ray pays one more instance test."""
+    job = _small(scenes.config_c5(), 200, 200, spp=64)
+    vp = job.viewport
+    vp.gamma = 1.0
+    vp.flags = A.RTW_FLAG_COUNT_WORK
+    fast = vp._run(job.ray_color, job.scene, job.mode, cuda)
+    s0 = cuda.scene(job.scene).stats()
+    monkeypatch.setenv("RTW_KEEP_ENCLOSING", "1")
+    kept = vp._run(job.ray_color, job.scene, job.mode, cuda)
+    s1 = cuda.scene(job.scene).stats()
+    fin = np.isfinite(fast) & np.isfinite(kept)
+    assert fin.mean() > 0.95
+    assert abs(fast[fin].mean() / kept[fin].mean() - 1.0) < 5e-3
+    assert s0.paths == s1.paths
+    assert s1.instance_tests > s0.instance_tests + 0.5 * s0.rays
