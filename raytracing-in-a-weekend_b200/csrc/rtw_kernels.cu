@@ -209,6 +209,9 @@ wf_extend_kernel(const Scene sc, const RenderParams P, const WfPool pool, WfCoun
 #define SCHED_TIME_END() ((void)0)
 #endif
     Trav T; T.cur = CUR_DONE;
+#if RTW_WF_PENDING
+    uint32_t pend = REF_NONE;                             // the lane's parked leaf test
+#endif
     uint32_t pos = 0u;
     float time = 0.f;
     bool busy = false, more = n > 0u;
@@ -252,48 +255,81 @@ wf_extend_kernel(const Scene sc, const RenderParams P, const WfPool pool, WfCoun
         }
         // ---- one step of ONE kind per iteration: the kind most lanes are waiting for. Lanes in
         // other states sit the iteration out, so that the rarer, dearer steps (leaf tests, instance
-        // entry / exit) run with many lanes at once instead of after every node step. Voting sphere
-        // tests, quad tests and one-sphere instances as separate kinds (-DRTW_SPLIT_KINDS) makes each
-        // leaf step uniform but starves the rarer kinds: -11 % on C5 (profiles/r1h_ab.txt), so all
-        // leaf tests are one kind and the tests themselves are branch-free instead (rtw_trace.h).
+        // entry / exit) run with many lanes at once instead of after every node step. (Voting sphere
+        // tests, quad tests and one-sphere instances as separate kinds starves the rarer ones: -11 %
+        // on C5, profiles/r1h_ab_split_fastprim_volskip.txt; the tests are branch-free instead.)
+#if RTW_WF_PENDING
+        // A lane that pops a leaf test does not wait for a leaf step: it parks the test in `pend`
+        // and carries on with the next reference, so it keeps taking node steps; the parked test
+        // runs in the next leaf step, which every lane with a parked test joins. Only a second leaf,
+        // an instance entry, a level exit or the end of the search force the parked test first. The
+        // closest hit does not depend on the order of the tests (closer() breaks ties by reference).
+        if (pend == REF_NONE && ref_is_leaf_test(T.cur)) { pend = T.cur; T.cur = S.pop(T.sp); }
         const uint32_t cur = T.cur;
-#if !defined(RTW_SPLIT_KINDS)
-        const uint32_t kind = cur < NODE_LIMIT ? 0u : ref_is_event(cur) ? 4u : cur == CUR_DONE ? 5u : 1u;
-#else
-        const uint32_t kind = cur < NODE_LIMIT ? 0u
-                              : ref_is_event(cur) ? 4u
-                              : ref_is_one_sphere_instance(cur) ? 3u
-                              : cur == CUR_DONE ? 5u
-                              : (cur >> 30);                 // KIND_SPHERE = 1, KIND_QUAD = 2
-#endif
-        const int c0 = __popc(__ballot_sync(FULL, kind == 0u)), c1 = __popc(__ballot_sync(FULL, kind == 1u)),
-                  c4 = __popc(__ballot_sync(FULL, kind == 4u));
-        uint32_t best = 0u; int cb = c0;
-        if (c1 > cb) { best = 1u; cb = c1; }
-#if defined(RTW_SPLIT_KINDS)
-        const int c2 = __popc(__ballot_sync(FULL, kind == 2u)), c3 = __popc(__ballot_sync(FULL, kind == 3u));
-        if (c2 > cb) { best = 2u; cb = c2; }
-        if (c3 > cb) { best = 3u; cb = c3; }
-#endif
-        if (c4 > cb) { best = 4u; cb = c4; }
+        const bool has_p = pend != REF_NONE;
+        const bool on_node = cur < NODE_LIMIT;
+        const bool must_p = has_p && !on_node;
+        const bool on_event = !has_p && ref_is_event(cur);
+        const int cn = __popc(__ballot_sync(FULL, on_node)), cm = __popc(__ballot_sync(FULL, must_p)),
+                  ce = __popc(__ballot_sync(FULL, on_event));
         SCHED_COUNT(iters, 0, 0);
-        if (best == 0u) {
-            SCHED_COUNT(step, 0, cb);
+        if (cn >= cm && cn >= ce) {
+            SCHED_COUNT(step, 0, cn);
             SCHED_TIME_BEGIN(0);
-            if (kind == 0u) trav_step_node<RTW_WF_INLINE_PRIMS != 0>(cx, T, S);
+            if (on_node) trav_step_node<false>(cx, T, S);
             SCHED_TIME_END();
-        } else if (best != 4u) {
-            SCHED_COUNT(step, 1, cb);
+        } else if (cm >= ce) {
+            SCHED_COUNT(step, 1, __popc(__ballot_sync(FULL, has_p)));
             SCHED_TIME_BEGIN(1);
-            if (kind == best) trav_step_prim(cx, T, S);
+            if (has_p) { trav_test_parked(cx, pend, T, S); pend = REF_NONE; }
             SCHED_TIME_END();
         } else {
-            SCHED_COUNT(step, 2, cb);
+            SCHED_COUNT(step, 2, ce);
             SCHED_TIME_BEGIN(2);
-            if (kind == 4u) trav_step_event(cx, time, T, S);
+            if (on_event) trav_step_event(cx, time, T, S);
+            SCHED_TIME_END();
+        }
+        if (busy && T.cur == CUR_DONE && pend == REF_NONE) {
+#else
+        const uint32_t cur = T.cur;
+        const bool on_node = cur < NODE_LIMIT, on_event = ref_is_event(cur), on_prim = !on_node && !on_event && cur != CUR_DONE;
+        const int cn = __popc(__ballot_sync(FULL, on_node)), cp = __popc(__ballot_sync(FULL, on_prim)),
+                  ce = __popc(__ballot_sync(FULL, on_event));
+        SCHED_COUNT(iters, 0, 0);
+        if (cn >= cp && cn >= ce) {
+            SCHED_COUNT(step, 0, cn);
+            SCHED_TIME_BEGIN(0);
+            if (on_node) {
+                trav_step_node<false>(cx, T, S);
+#if RTW_WF_PREFETCH
+                if (T.cur < NODE_LIMIT) prefetch_l1(&sc.nodes16[T.cur]);
+                else if ((T.cur >> 30) == KIND_SPHERE) prefetch_l1(&sc.spheres[ref_index(T.cur)]);
+                else if ((T.cur >> 30) == KIND_QUAD) prefetch_l1(&sc.quads[ref_index(T.cur)]);
+#endif
+            }
+#if RTW_WF_NODE_BURST > 1
+#pragma unroll 1
+            for (int burst = 1; burst < RTW_WF_NODE_BURST; ++burst) {
+                const bool again = T.cur < NODE_LIMIT;
+                if (__popc(__ballot_sync(FULL, again)) < cn - (cn >> 2)) break;   // most of the node lanes are still on nodes
+                SCHED_COUNT(step, 0, cn);
+                if (again) trav_step_node<false>(cx, T, S);
+            }
+#endif
+            SCHED_TIME_END();
+        } else if (cp >= ce) {
+            SCHED_COUNT(step, 1, cp);
+            SCHED_TIME_BEGIN(1);
+            if (on_prim) trav_step_prim(cx, T, S);
+            SCHED_TIME_END();
+        } else {
+            SCHED_COUNT(step, 2, ce);
+            SCHED_TIME_BEGIN(2);
+            if (on_event) trav_step_event(cx, time, T, S);
             SCHED_TIME_END();
         }
         if (busy && T.cur == CUR_DONE) {
+#endif
             pool.hit[pos] = make_uint4(f2u(T.t), T.ref, T.inner, 0u);
             busy = false;
         }
@@ -322,7 +358,7 @@ wf_extend_kernel(const Scene sc, const RenderParams P, const WfPool pool, WfCoun
 }
 
 // shade: one thread per pool slot, record rewritten in place. init != 0: first fill.
-__global__ void __launch_bounds__(RTW_WF_SHADE_BLOCK)
+__global__ void __launch_bounds__(RTW_WF_SHADE_BLOCK, RTW_WF_SHADE_MINB)
 wf_shade_kernel(const Scene sc, const RenderParams P, const WfPool pool, WfCounters* __restrict__ wc,
                 Counters* __restrict__ ctr, float* __restrict__ sum, const uint32_t mark, const int init, const WfLaunch L) {
     const uint32_t e = blockIdx.x * blockDim.x + threadIdx.x;

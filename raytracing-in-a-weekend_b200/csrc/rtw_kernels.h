@@ -78,8 +78,18 @@ struct WfLaunch {
 #ifndef RTW_WF_EXTEND_MINB
 #define RTW_WF_EXTEND_MINB 6      // min resident blocks per SM asked of the compiler for wf_extend (80 registers, no spills; +2.2 % over 5 blocks, profiles/r1h_ab_inline_minblocks.txt)
 #endif
-#ifndef RTW_WF_INLINE_PRIMS
-#define RTW_WF_INLINE_PRIMS 0     // 1: wf_extend tests sphere / quad children inside the node step (A/B)
+#ifndef RTW_WF_PENDING
+#define RTW_WF_PENDING 0          // 1: wf_extend parks a popped leaf test and keeps walking nodes (see the kernel); A/B: leaf steps
+                                  // run with 15.7 instead of 13.2 lanes, node steps unchanged (16.0 vs 15.6), +2 % node visits, -4 % overall
+#endif
+#ifndef RTW_WF_PREFETCH
+#define RTW_WF_PREFETCH 0         // 1: the node step prefetches the record it will visit next into L1
+#endif
+#ifndef RTW_WF_NODE_BURST
+#define RTW_WF_NODE_BURST 3       // node steps per vote while the node lanes keep their majority
+#endif
+#ifndef RTW_WF_SHADE_MINB
+#define RTW_WF_SHADE_MINB 10      // min resident blocks per SM asked of the compiler for wf_shade
 #endif
 #define RTW_WF_SHADE_BLOCK 128
 

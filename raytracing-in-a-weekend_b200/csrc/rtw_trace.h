@@ -560,6 +560,21 @@ RTW_HD void trav_step_prim(const TraceCtx& cx, Trav& T, const Stack& S) {
     }
 }
 
+// The same for a leaf test that was taken off the stack earlier (`ref`), T.cur being whatever came
+// off the stack after it (wf_extend parks leaf tests so that its lanes keep taking node steps).
+RTW_HD void trav_test_parked(const TraceCtx& cx, uint32_t ref, Trav& T, const Stack& S) {
+    if (ref_is_one_sphere_instance(ref)) {
+        RTW_COUNT(cx, instances);
+        trav_one_sphere_instance(cx, ref & ~REF_INSTANCE_FLAGS, T);
+        return;
+    }
+    trav_test_prim(cx, ref, T);
+    if ((T.mode & 3u) == TRAV_PROBE && T.ref != REF_NONE && T.cur != CUR_EXIT) {   // instance.rs:284-294 only asks "anything?"
+        while (S.pop(T.sp) != CUR_EXIT) {}
+        T.cur = CUR_EXIT;
+    }
+}
+
 // T.cur is an instance leaf (a level change) or the sentinel. Such events are chained until the
 // lane is back on a node or a leaf test (or done).
 RTW_HD bool ref_is_event(uint32_t r) { return (r >= 0xC0000000u && r < 0xE0000000u) || r == CUR_EXIT; }
