@@ -22,6 +22,29 @@
 
 namespace rtw {
 
+// The fast device build (nvcc's default contraction, no -DRTW_STRICT_FP) may reorder and
+// approximate within ~1 ulp; the strict build and the host keep the reference's operation order.
+#if defined(__CUDA_ARCH__) && !defined(RTW_STRICT_FP)
+#define RTW_FAST_NODES 1
+// 1/x, sqrt(x) and 1/sqrt(x) from the SFU approximations plus one Newton step (<= 1 ulp, no slow-path branch).
+__device__ __forceinline__ float fast_rcp(float x) {
+    float r;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return fmaf(fmaf(-x, r, 1.0f), r, r);
+}
+__device__ __forceinline__ float fast_rsqrt(float x) {
+    float rs;
+    asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(rs) : "f"(x));
+    return rs * fmaf(-0.5f * x, rs * rs, 1.5f);
+}
+__device__ __forceinline__ float fast_sqrt_pos(float x) {   // x > 0
+    float rs;
+    asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(rs) : "f"(x));
+    const float s = x * rs;
+    return fmaf(fmaf(-s, s, x), 0.5f * rs, s);
+}
+#endif
+
 // ------------------------------------------------------------------ Vec3 (vec3.rs:10-262)
 struct V3 { float x, y, z; };
 RTW_HD V3 v3(float x, float y, float z) { V3 r; r.x = x; r.y = y; r.z = z; return r; }
@@ -30,14 +53,22 @@ RTW_HD V3 operator+(V3 a, V3 b) { return v3(a.x + b.x, a.y + b.y, a.z + b.z); }
 RTW_HD V3 operator-(V3 a, V3 b) { return v3(a.x - b.x, a.y - b.y, a.z - b.z); }
 RTW_HD V3 operator*(V3 a, float s) { return v3(a.x * s, a.y * s, a.z * s); }
 RTW_HD V3 operator*(V3 a, V3 b) { return v3(a.x * b.x, a.y * b.y, a.z * b.z); }
+#if defined(RTW_FAST_NODES) && !defined(RTW_NO_FASTVEC)
+RTW_HD V3 operator/(V3 a, float s) { const float r = fast_rcp(s); return v3(a.x * r, a.y * r, a.z * r); }
+#else
 RTW_HD V3 operator/(V3 a, float s) { return v3(a.x / s, a.y / s, a.z / s); }
+#endif
 RTW_HD float dot(V3 a, V3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }            // vec3.rs:194-196
 RTW_HD V3 cross(V3 a, V3 b) {                                                           // vec3.rs:197-203
     return v3(a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x);
 }
 RTW_HD float length(V3 a) { return sqrtf(a.x * a.x + a.y * a.y + a.z * a.z); }          // vec3.rs:191-193
 RTW_HD float length2(V3 a) { return a.x * a.x + a.y * a.y + a.z * a.z; }                // vec3.rs:188-190
+#if defined(RTW_FAST_NODES) && !defined(RTW_NO_FASTVEC)
+RTW_HD V3 unit(V3 a) { const float r = fast_rsqrt(a.x * a.x + a.y * a.y + a.z * a.z); return v3(a.x * r, a.y * r, a.z * r); }
+#else
 RTW_HD V3 unit(V3 a) { return a / length(a); }                                           // vec3.rs:204-206
+#endif
 RTW_HD V3 reflect(V3 v, V3 n) { return v - n * 2.0f * dot(v, n); }                       // vec3.rs:256-258
 RTW_HD bool close_to_zero(V3 a) {                                                        // vec3.rs:259-261
     return fabsf(a.x) < 1e-7f && fabsf(a.y) < 1e-7f && fabsf(a.z) < 1e-7f;

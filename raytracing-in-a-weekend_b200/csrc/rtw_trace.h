@@ -58,27 +58,6 @@ RTW_HD_NOINL bool slab_slow(V3 lo, V3 hi, V3 o, V3 d, float mint, float maxt, fl
     return !(mn > mx);
 }
 
-// The fast device build (nvcc's default contraction, no -DRTW_STRICT_FP) may reorder and
-// approximate within ~1 ulp; the strict build and the host keep the reference's operation order.
-#if defined(__CUDA_ARCH__) && !defined(RTW_STRICT_FP)
-#define RTW_FAST_NODES 1
-#endif
-
-#if defined(RTW_FAST_NODES)
-// 1/x and sqrt(x) from the SFU approximations plus one Newton step (<= 1 ulp, no slow-path branch).
-__device__ __forceinline__ float fast_rcp(float x) {
-    float r;
-    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
-    return fmaf(fmaf(-x, r, 1.0f), r, r);
-}
-__device__ __forceinline__ float fast_sqrt_pos(float x) {   // x > 0
-    float rs;
-    asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(rs) : "f"(x));
-    const float s = x * rs;
-    return fmaf(fmaf(-s, s, x), 0.5f * rs, s);
-}
-#endif
-
 // Sphere::collision_normal up to the accepted root (sphere.rs:100-123). `c` = centre at ray time.
 RTW_HD bool sphere_t(V3 c, float radius, V3 o, V3 d, float a, float mint, float maxt, float& t) {
 #if defined(RTW_FAST_NODES) && !defined(RTW_NO_FASTPRIM)
@@ -402,14 +381,18 @@ RTW_HD void trav_step_node(const TraceCtx& cx, Trav& T, const Stack& S) {
             return;
         }
     }
-    // constant-density volumes (REF_LATE_INSTANCE) go last whatever their distance: their hit is far
-    // behind the entry face and costs a free-flight draw, which the shrunk interval of a nearer
-    // surface hit usually spares
+    // -DRTW_LATE_VOLUMES: constant-density volumes (REF_LATE_INSTANCE) go last whatever their distance
+    // (their hit costs a free-flight draw, which the shrunk interval of a nearer surface hit usually
+    // spares). It paid while C5's global fog was walked by every ray; with enclosing volumes dropped
+    // from the top level (rtw_host.h) the four extra tests per node step cost more than they save
+    // (+4 % without, profiles/r1h_ab_fastvec_nolate.txt).
+#if defined(RTW_LATE_VOLUMES)
 #if defined(__CUDA_ARCH__)
 #pragma unroll
 #endif
     for (int c = 0; c < 4; ++c)
         if ((rf[c] & 0xD0000000u) == 0xD0000000u && tn[c] < INFINITY) tn[c] = 3.0e38f;
+#endif
     cswap(tn[0], rf[0], tn[1], rf[1]); cswap(tn[2], rf[2], tn[3], rf[3]);
     cswap(tn[0], rf[0], tn[2], rf[2]); cswap(tn[1], rf[1], tn[3], rf[3]);
     cswap(tn[1], rf[1], tn[2], rf[2]);
