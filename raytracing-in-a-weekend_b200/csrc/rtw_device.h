@@ -248,6 +248,24 @@ struct PathRng {
 };
 
 // vec3.rs:216-238: Vec3::random(-1,1) -> reject outside the unit ball -> unit()
+#if defined(RTW_FAST_NODES) && !defined(RTW_NO_DIRECT_SPHERE)
+// Fast build: the same distribution without the rejection loop. A point of U[-1,1]^3 kept inside the
+// unit ball and normalised is uniform on the sphere; so is (sqrt(1-z^2) cos phi, sqrt(1-z^2) sin phi, z)
+// with z = 1-2u, phi = 2 pi v. The loop makes a warp wait for its unluckiest lane (about five Philox
+// blocks for 16 diffuse lanes against 1.9 on average per lane); one block always suffices here. The
+// strict build keeps the reference's loop and with it the oracle's Philox stream, sample for sample.
+__device__ __forceinline__ V3 sphere_point(float u, float v) {
+    const float z = fmaf(-2.0f, u, 1.0f);
+    const float r = sqrtf(fmaxf(0.0f, fmaf(-z, z, 1.0f)));
+    float sn, cs;
+    __sincosf(6.283185307179586f * (v - 0.5f), &sn, &cs);
+    return v3(r * cs, r * sn, z);
+}
+RTW_HD V3 random_unit_vec(PathRng& rng) {
+    const float4 r = rng.next4();
+    return sphere_point(r.x, r.y);
+}
+#else
 RTW_HD V3 random_unit_vec(PathRng& rng) {
     for (;;) {
         float4 r = rng.next4();
@@ -255,6 +273,7 @@ RTW_HD V3 random_unit_vec(PathRng& rng) {
         if (p.x * p.x + p.y * p.y + p.z * p.z <= 1.0f) return unit(p);
     }
 }
+#endif
 // vec3.rs:240-254: two candidate points per block
 RTW_HD V3 random_in_unit_disk(PathRng& rng) {
     for (;;) {

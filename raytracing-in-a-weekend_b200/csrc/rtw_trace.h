@@ -151,6 +151,12 @@ RTW_HD float4 ctx_rand(const TraceCtx& cx, uint32_t blk, uint32_t stream) {
 
 // random_unit_vec (vec3.rs:216-238) drawn from a side stream: block = base | turn, turn = 1, 2, ...
 RTW_HD V3 random_unit_vec_stream(const TraceCtx& cx, uint32_t base_block, uint32_t stream) {
+#if defined(RTW_FAST_NODES) && !defined(RTW_NO_DIRECT_SPHERE)
+    {
+        const float4 r = ctx_rand(cx, base_block | 1u, stream);
+        return sphere_point(r.x, r.y);
+    }
+#endif
     for (uint32_t turn = 0;; ++turn) {
         float4 r = ctx_rand(cx, base_block | (turn + 1u), stream);
         V3 p = v3(r.x * (1.0f - -1.0f) + -1.0f, r.y * (1.0f - -1.0f) + -1.0f, r.z * (1.0f - -1.0f) + -1.0f);
