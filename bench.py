@@ -37,7 +37,7 @@ METRIC = "Mpaths/s, Next-Week final scene 800x800 (C5), 10000 spp, depth 50"
 UNIT = "Mpaths/s"
 
 # Algorithmic work per operation (DESIGN.md "Roofline"): flop and bytes of scene data.
-COST = {"node": (56.0, 64.0),        # two child-box slab tests, one 64-B node
+COST = {"node": (112.0, 64.0),       # four child-box slab tests (28 flop each, objects.rs:125-140), one 64-B half-float node
         "sphere": (36.0, 16.0),      # sphere.rs:100-123, (origin, radius)
         "quad": (49.0, 64.0),        # quad.rs:38-60, 64-B record
         "instance": (60.0, 160.0),   # ray -> local and hit -> world (two 3x3 Euler maps + T)
@@ -354,10 +354,21 @@ def run_b200(args):
         state_bytes = 216.0 if wavefront else 0.0     # path records streamed per ray, else REDs only
         step_ms = elapsed_ms / args.steps
         hbm_gbs = (state_bytes * rays_step + H * W * 3 * 4 * 2.0) / (step_ms * 1e-3) / 1e9
-        cands = [("fp32", tflops, fp32_peak, "TFLOP/s"), ("l2", l2_gbs, l2_peak, "GB/s")]
+        # the kernel's own HBM stream (wavefront: 40 B of ray record read + 16 B of hit record written per ray)
+        k_hbm_bytes = 56.0 if wavefront else 0.0
+        k_hbm_gbs = k_hbm_bytes * rays_launch / (k_ms * 1e-3) / 1e9
+        cands = [("fp32", tflops, fp32_peak, "TFLOP/s"), ("l2", l2_gbs, l2_peak, "GB/s"), ("hbm", k_hbm_gbs, hbm_peak, "GB/s")]
         bname, bach, bpeak, bunit = max(cands, key=lambda c: c[1] / c[2])
+        traffic, traffic_src = None, None
+        try:      # DRAM bytes of the dominant kernel per launch, from the committed ncu --set full capture
+            tj = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))[kname]
+            traffic, traffic_src = float(tj["dram_bytes_per_launch"]), tj["source"]
+        except Exception:
+            pass
         roofline = {"kernel": kname, "bound": bname, "achieved": bach, "peak": bpeak, "unit": bunit,
-                    "frac": bach / bpeak, "traffic": None, "peak_source": "rtw_microbench on this GPU (MEASURED_PEAKS.json has no fp32/L2 entry)",
+                    "frac": bach / bpeak, "traffic": traffic, "traffic_source": traffic_src,
+                    "algorithmic_hbm_bytes_per_launch": k_hbm_bytes * rays_launch,
+                    "peak_source": "rtw_microbench on this GPU for fp32 and L2 (MEASURED_PEAKS.json has neither); MEASURED_PEAKS.json hbm_gbs for HBM" if hbm_src == "measured" else "rtw_microbench on this GPU for fp32 and L2; B200_PROFILING.md fallback for HBM",
                     "kernel_ms_per_launch": k_ms, "rays_per_launch": rays_launch,
                     "launches_per_step": iters if wavefront else 1,
                     "share_of_step": (k_ms * iters / step_ms) if wavefront else (k_ms / step_ms),
@@ -366,6 +377,7 @@ def run_b200(args):
                     "extend_warp_scheduling": sched,
                     "all": {"fp32": {"achieved": tflops, "peak": fp32_peak, "unit": "TFLOP/s", "frac": tflops / fp32_peak},
                             "l2": {"achieved": l2_gbs, "peak": l2_peak, "unit": "GB/s", "frac": l2_gbs / l2_peak},
+                            "hbm_kernel": {"achieved": k_hbm_gbs, "peak": hbm_peak, "unit": "GB/s", "frac": k_hbm_gbs / hbm_peak},
                             "hbm": {"achieved": hbm_gbs, "peak": hbm_peak, "unit": "GB/s", "frac": hbm_gbs / hbm_peak,
                                     "peak_source": hbm_src,
                                     "note": "whole step: path records streamed by extend+shade (216 B/ray) + framebuffer REDs; the scene (<10 MB) is L1/L2-resident"}}}
