@@ -244,6 +244,15 @@ int rtw_resolve_device(float* d_rgb, uint64_t n_pixels, uint32_t total_samples, 
 int rtw_quantize_device(const float* d_rgb, uint8_t* d_rgb8, uint64_t n_values, int device,
                         void* stream);
 
+/* The same quantiser for a HOST image the caller already holds (what write_img_f32 receives):
+ * H2D, quantise on the device, D2H. `device` < 0 = current device. */
+int rtw_quantize(const float* rgb, uint8_t* rgb8, uint64_t n_values, int device);
+/* rtw_render followed by write_img_f32's quantiser, fused on the device: only the 8-bit image
+ * crosses PCIe (a quarter of the bytes). `out_rgb8` is HOST memory, rows*width*3 bytes; the
+ * caller PNG-encodes it (write_img.rs:19 `img.save`). opts->output must be RTW_OUT_RESOLVED. */
+int rtw_render_rgb8(rtw_scene* scene, const rtw_camera* cam, const rtw_render_opts* opts,
+                    uint8_t* out_rgb8);
+
 int rtw_get_stats(rtw_scene* scene, rtw_stats* out);
 /* Warp-scheduling counters of the wavefront extend kernel, filled by RTW_FLAG_COUNT_WORK |
  * RTW_FLAG_WAVEFRONT renders: out[0] = loop iterations (per warp, summed); then for the step kinds

@@ -161,4 +161,17 @@ int oracle_collide(oracle_scene* s, const float origin[3], const float dir[3], f
     return RTW_OK;
 }
 
+// write_img_f32's per-channel conversion (Rust/src/write_img.rs:12-14):
+//   (x * 255.0).clamp(0.0, 255.0).round() as u8
+// f32::clamp keeps NaN, f32::round rounds half away from zero, `as u8` saturates and maps NaN to 0.
+void oracle_quantize(const float* rgb, uint8_t* out, uint64_t n_values) {
+    for (uint64_t k = 0; k < n_values; ++k) {
+        float x = rgb[k] * 255.0f;
+        if (x < 0.0f) x = 0.0f;          // clamp: NaN fails both comparisons and stays NaN
+        if (x > 255.0f) x = 255.0f;
+        x = std::round(x);               // half away from zero, like f32::round
+        out[k] = (x != x) ? (uint8_t)0 : (uint8_t)x;
+    }
+}
+
 }  // extern "C"

@@ -12,4 +12,6 @@ from .viewport import (Viewport, async_render, get_default_backend, ray_color_al
                        ray_color_d, ray_color_glass_test, ray_color_gradient, ray_color_normal, render_multi,
                        set_default_backend)
 
+from .write_img import quantize, write_img, write_img_f32
+
 __all__ = [n for n in dir() if not n.startswith("_")]

@@ -49,6 +49,13 @@ class CudaSceneHandle:
         """Render into a caller-owned host buffer (e.g. pinned memory)."""
         A.check(self._lib.rtw_render(self._h, C.byref(cam), C.byref(o), C.c_void_p(host_out.ctypes.data)))
 
+    def render_rgb8(self, cam, o) -> np.ndarray:
+        """Render + write_img_f32's quantiser fused on the device (write_img.rs:6-19): H x W x 3 uint8."""
+        rows = o.row_count if o.row_count else cam.height
+        out = np.empty((rows, cam.width, 3), dtype=np.uint8)
+        A.check(self._lib.rtw_render_rgb8(self._h, C.byref(cam), C.byref(o), C.c_void_p(out.ctypes.data)))
+        return out
+
     def render_device(self, cam, o, d_ptr: int, stream: int = 0) -> None:
         """Enqueue a render into device memory `d_ptr` on CUDA stream `stream` (no host sync)."""
         A.check(self._lib.rtw_render_device(self._h, C.byref(cam), C.byref(o), C.c_void_p(d_ptr),
@@ -118,6 +125,13 @@ class CudaBackend:
     def resolve_device(self, d_ptr: int, n_pixels: int, total_samples: int, gamma: float, stream: int = 0):
         A.check(self.lib.rtw_resolve_device(C.c_void_p(d_ptr), n_pixels, total_samples, gamma, self.device,
                                             C.c_void_p(stream)))
+
+    def quantize(self, img: np.ndarray) -> np.ndarray:
+        """write_img_f32's f32 -> u8 conversion (write_img.rs:12-14) of a host image, on the device."""
+        src = np.ascontiguousarray(img, dtype=np.float32)
+        out = np.empty(src.shape, dtype=np.uint8)
+        A.check(self.lib.rtw_quantize(C.c_void_p(src.ctypes.data), C.c_void_p(out.ctypes.data), src.size, self.device))
+        return out
 
     def quantize_device(self, d_rgb: int, d_rgb8: int, n_values: int, stream: int = 0):
         A.check(self.lib.rtw_quantize_device(C.c_void_p(d_rgb), C.c_void_p(d_rgb8), n_values, self.device,

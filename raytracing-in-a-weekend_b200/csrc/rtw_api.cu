@@ -546,6 +546,45 @@ int rtw_quantize_device(const float* d_rgb, uint8_t* d_rgb8, uint64_t n_values, 
     return RTW_OK;
 }
 
+int rtw_quantize(const float* rgb, uint8_t* rgb8, uint64_t n_values, int device) {
+    if (!rgb || !rgb8) return fail(RTW_E_INVALID, "null argument");
+    if (n_values == 0) return RTW_OK;
+    if (device >= 0) CK(cudaSetDevice(device));
+    float* d_in = nullptr; uint8_t* d_out = nullptr;
+    cudaError_t e = cudaMalloc(&d_in, n_values * sizeof(float));
+    if (e != cudaSuccess) return cuda_fail(e, "cudaMalloc");
+    if ((e = cudaMalloc(&d_out, n_values)) != cudaSuccess) { cudaFree(d_in); return cuda_fail(e, "cudaMalloc"); }
+    e = cudaMemcpy(d_in, rgb, n_values * sizeof(float), cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) {
+        quantize_kernel<<<grid_for(n_values, 256), 256>>>(d_in, d_out, n_values);
+        e = cudaGetLastError();
+    }
+    if (e == cudaSuccess) e = cudaMemcpy(rgb8, d_out, n_values, cudaMemcpyDeviceToHost);
+    cudaFree(d_in); cudaFree(d_out);
+    if (e != cudaSuccess) return cuda_fail(e, "rtw_quantize");
+    return RTW_OK;
+}
+
+int rtw_render_rgb8(rtw_scene* scene, const rtw_camera* cam, const rtw_render_opts* opts, uint8_t* out_rgb8) {
+    if (!scene || !cam || !opts || !out_rgb8) return fail(RTW_E_INVALID, "null argument");
+    if (opts->output != RTW_OUT_RESOLVED) return fail(RTW_E_INVALID, "rtw_render_rgb8 needs RTW_OUT_RESOLVED");
+    CK(cudaSetDevice(scene->device));
+    const uint32_t rows = opts->row_count ? opts->row_count : cam->height;
+    const size_t n_values = (size_t)rows * cam->width * 3u;
+    // the f32 image, then its 8-bit copy behind it in the same allocation
+    int rc = ensure_img(scene, n_values + (n_values + 3u) / 4u);
+    if (rc) return rc;
+    if ((rc = enqueue_render(scene, cam, opts, scene->d_img, scene->stream))) return rc;
+    uint8_t* d8 = reinterpret_cast<uint8_t*>(scene->d_img + n_values);
+    quantize_kernel<<<grid_for(n_values, 256), 256, 0, scene->stream>>>(scene->d_img, d8, n_values);
+    CK(cudaGetLastError());
+    scene->launches += 1;
+    CK(cudaMemcpyAsync(out_rgb8, d8, n_values, cudaMemcpyDeviceToHost, scene->stream));
+    CK(cudaEventRecord(scene->ev2, scene->stream));
+    CK(cudaStreamSynchronize(scene->stream));
+    return RTW_OK;
+}
+
 int rtw_get_stats(rtw_scene* scene, rtw_stats* out) {
     if (!scene || !out) return fail(RTW_E_INVALID, "null argument");
     std::memset(out, 0, sizeof *out);

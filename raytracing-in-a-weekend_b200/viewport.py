@@ -127,6 +127,12 @@ class Viewport:
         """Viewport::render (viewport.rs:430-478): ceil(sqrt(samples))^2 stratified samples."""
         return self._run(ray_color, scene, A.RTW_MODE_STRATIFIED, backend)
 
+    def render_rgb8(self, ray_color, scene: Scene, mode: int = A.RTW_MODE_RANDOM, backend=None) -> np.ndarray:
+        """A render followed by write_img_f32's quantiser (write_img.rs:6-19), fused on the device:
+        the H x W x 3 uint8 image that `img.save` would encode."""
+        be = backend or get_default_backend()
+        return be.scene(scene).render_rgb8(self.camera(be), self.opts(ray_color, mode))
+
     def render_no_rand(self, ray_color, scene: Scene, backend=None) -> np.ndarray:
         """Viewport::render_no_rand (viewport.rs:479-516)."""
         return self._run(ray_color, scene, A.RTW_MODE_NO_RAND, backend)

@@ -74,6 +74,8 @@ def load_oracle(fast: bool = False):
     lib.oracle_refract.argtypes = [f32p, f32p, C.c_float, f32p]
     lib.oracle_interval_intersect.restype = C.c_int
     lib.oracle_interval_intersect.argtypes = [C.c_float, C.c_float, C.c_float, C.c_float, f32p]
+    lib.oracle_quantize.restype = None
+    lib.oracle_quantize.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64]
     lib.oracle_collide.restype = C.c_int
     lib.oracle_collide.argtypes = [C.c_void_p, f32p, f32p, C.c_float, C.c_float, C.c_float, C.c_uint64,
                                    C.c_uint32, C.c_uint32, C.c_uint32, P(oracle_hit)]
@@ -147,6 +149,13 @@ class OracleBackend:
         self.lib.oracle_camera_init(C.byref(cam), width, aspect_ratio, vfov, _f3(origin), _f3(direction),
                                     _f3(vup), lens_radius)
         return cam
+
+    def quantize(self, img: np.ndarray) -> np.ndarray:
+        """write_img_f32's conversion (write_img.rs:12-14), CPU restatement."""
+        src = np.ascontiguousarray(img, dtype=np.float32)
+        out = np.empty(src.shape, dtype=np.uint8)
+        self.lib.oracle_quantize(src.ctypes.data_as(C.c_void_p), out.ctypes.data_as(C.c_void_p), src.size)
+        return out
 
     def scene(self, scene) -> OracleSceneHandle:
         key = ("oracle", self.build_seed, self.fast)
