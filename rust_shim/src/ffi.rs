@@ -60,5 +60,9 @@ extern "C" {
     pub fn rtw_render(scene: *mut rtw_scene, cam: *const rtw_camera, opts: *const rtw_render_opts, out_rgb: *mut f32) -> c_int;
     pub fn rtw_render_device(scene: *mut rtw_scene, cam: *const rtw_camera, opts: *const rtw_render_opts, d_out: *mut f32, stream: *mut c_void) -> c_int;
     pub fn rtw_render_frames(scene: *mut rtw_scene, cam: *const rtw_camera, opts: *const rtw_render_opts, first: u32, n: u32, out_rgb: *mut f32) -> c_int;
+    /// write_img_f32's quantiser (write_img.rs:12-14) for a host image, run on the device.
+    pub fn rtw_quantize(rgb: *const f32, rgb8: *mut u8, n_values: u64, device: c_int) -> c_int;
+    /// rtw_render + that quantiser fused on the device; `out_rgb8` is host memory (H*W*3 bytes).
+    pub fn rtw_render_rgb8(scene: *mut rtw_scene, cam: *const rtw_camera, opts: *const rtw_render_opts, out_rgb8: *mut u8) -> c_int;
     pub fn rtw_get_stats(scene: *mut rtw_scene, out: *mut rtw_stats) -> c_int;
 }
