@@ -223,6 +223,15 @@ void rtw_render_opts_default(rtw_render_opts* o);   /* samples 1, depth 10, gamm
 int  rtw_scene_create(const rtw_scene_desc* desc, int device, rtw_scene** out);
 void rtw_scene_destroy(rtw_scene* scene);
 
+/* Optional on-device BVH rebuild (BASELINE north_star; replaces AABB::new / QuadAABB::new /
+ * IAABB::new, objects/aabb/aabb.rs:20-71, qaabb.rs:127-163, iaabb.rs:80-116, for callers that
+ * rebuild per frame): every level with two or more leaves is rebuilt on the GPU as an LBVH (Morton
+ * sort + Karras tree + 4-wide collapse) and walked from now on. Same leaves, same leaf boxes: the
+ * closest hit of every ray is unchanged. `out_build_ms` (may be NULL) = device time of the build. */
+int rtw_scene_rebuild_lbvh(rtw_scene* scene, float* out_build_ms);
+/* Walk the host SAH tree built by rtw_scene_create again. */
+int rtw_scene_use_sah(rtw_scene* scene);
+
 /* --- render. Blocking; `out_rgb` is HOST memory (rows top to bottom, [row][col][rgb], like Img).
  * Replaces Viewport::render / render_no_rand / async_render depending on opts->mode. */
 int rtw_render(rtw_scene* scene, const rtw_camera* cam, const rtw_render_opts* opts,

@@ -68,6 +68,16 @@ class CudaSceneHandle:
                                             out.ctypes.data_as(C.c_void_p)))
         return out
 
+    def rebuild_lbvh(self) -> float:
+        """Rebuild every BVH level on the device (LBVH) and walk it from now on; returns the build's device ms."""
+        ms = C.c_float(0.0)
+        A.check(self._lib.rtw_scene_rebuild_lbvh(self._h, C.byref(ms)))
+        return float(ms.value)
+
+    def use_sah(self) -> None:
+        """Back to the host SAH tree built at scene creation."""
+        A.check(self._lib.rtw_scene_use_sah(self._h))
+
     def stats(self) -> A.rtw_stats:
         st = A.rtw_stats()
         A.check(self._lib.rtw_get_stats(self._h, C.byref(st)))

@@ -10,6 +10,7 @@
 #include <vector>
 #include "rtw_host.h"
 #include "rtw_kernels.h"
+#include "rtw_lbvh_driver.h"
 
 using namespace rtw;
 
@@ -93,6 +94,17 @@ struct rtw_scene {
     Scene d{};                            // device pointers
     Scene d_cur{};                        // what the current render walks: d, or d with top = top_inside
     Level top_all{}, top_inside{};
+    // optional on-device LBVH rebuild (rtw_lbvh.h): the leaves of every level, the node arrays with
+    // room for the rebuilt levels behind the SAH nodes, and the SAH levels to go back to
+    std::vector<LbvhLeaf> lb_leaves_h;
+    std::vector<LbvhLevelDesc> lb_levels;
+    std::vector<Level> sah_inst_levels;       // per instance
+    Level sah_top{}, sah_top_inside{};
+    uint32_t sah_top_depth = 0, sah_inner_depth = 0, n_sah_nodes = 0;
+    LbvhLeaf* lb_leaves_d = nullptr;
+    Node* lb_nodes = nullptr; Node16* lb_nodes16 = nullptr;
+    LbvhLevelOut* lb_out_d = nullptr;
+    LbvhScratch lb_scratch;
     std::vector<HostScene::Enclosing> enclosing;
     std::vector<void*> allocs;
     std::vector<cudaArray_t> arrays;
@@ -126,6 +138,10 @@ struct rtw_scene {
         for (auto a : arrays) cudaFreeArray(a);
         for (auto p : allocs) cudaFree(p);
         if (d_img) cudaFree(d_img);
+        if (lb_leaves_d) cudaFree(lb_leaves_d);
+        if (lb_nodes) cudaFree(lb_nodes);
+        if (lb_nodes16) cudaFree(lb_nodes16);
+        if (lb_out_d) cudaFree(lb_out_d);
         if (d_wc) cudaFree(d_wc);
         if (h_wc) cudaFreeHost(h_wc);
         for (auto e : wf_ev) if (e) cudaEventDestroy(e);
@@ -201,6 +217,11 @@ int upload_scene(rtw_scene* s, HostScene& hs) {
     if ((rc = upload(s, hs.noises, &d.noises))) return rc;
     d.top = hs.top;
     s->top_all = hs.top; s->top_inside = hs.top_inside; s->enclosing = hs.enclosing;
+    s->lb_leaves_h = hs.lbvh_leaves; s->lb_levels = hs.lbvh_levels;
+    s->sah_top = hs.top; s->sah_top_inside = hs.top_inside;
+    s->sah_inst_levels.resize(hs.instances.size());
+    for (size_t k = 0; k < hs.instances.size(); ++k) s->sah_inst_levels[k] = hs.instances[k].level;
+    s->sah_top_depth = hs.top_depth; s->sah_inner_depth = hs.inner_depth; s->n_sah_nodes = (uint32_t)hs.nodes.size();
     std::memcpy(d.background, hs.background, sizeof d.background);
     d.n_noises = (uint32_t)hs.noises.size();
     return RTW_OK;
@@ -544,6 +565,105 @@ int rtw_quantize_device(const float* d_rgb, uint8_t* d_rgb8, uint64_t n_values, 
     quantize_kernel<<<grid_for(n_values, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(d_rgb, d_rgb8, n_values);
     CK(cudaGetLastError());
     return RTW_OK;
+}
+
+namespace {
+// stack depth, shared-memory size and the occupancies that depend on it
+int refresh_launch_limits(rtw_scene* s, uint32_t top_depth, uint32_t inner_depth) {
+    const uint32_t words = stack_words(top_depth, inner_depth);
+    if (words > 160u) return fail(RTW_E_UNSUPPORTED, "BVH deeper than the traversal stack");
+    s->stack_words = words;
+    s->smem_bytes = (size_t)words * RTW_MEGA_BLOCK * sizeof(uint32_t);
+    CK(mega_occupancy_fast(&s->occ_fast, s->smem_bytes));
+    CK(mega_occupancy_strict(&s->occ_strict, s->smem_bytes));
+    CK(mega_occupancy_count(&s->occ_count, s->smem_bytes));
+    if (s->pool.capacity) {
+        CK(wf_extend_occupancy_fast(&s->occ_wf[0], s->smem_bytes));
+        CK(wf_extend_occupancy_strict(&s->occ_wf[1], s->smem_bytes));
+        CK(wf_extend_occupancy_count(&s->occ_wf[2], s->smem_bytes));
+    }
+    return RTW_OK;
+}
+int set_instance_level(rtw_scene* s, uint32_t k, const Level& lv) {
+    Instance* base = const_cast<Instance*>(s->d.instances);
+    CK(cudaMemcpyAsync(reinterpret_cast<char*>(base + k) + offsetof(Instance, level), &lv, sizeof(Level),
+                       cudaMemcpyHostToDevice, s->stream));
+    return RTW_OK;
+}
+}  // namespace
+
+int rtw_scene_rebuild_lbvh(rtw_scene* s, float* out_build_ms) {
+    if (!s) return fail(RTW_E_INVALID, "null argument");
+    CK(cudaSetDevice(s->device));
+    uint32_t extra = 0;
+    for (const auto& lv : s->lb_levels) if (lv.count >= 2u) extra += lv.count - 1u;
+    if (out_build_ms) *out_build_ms = 0.f;
+    if (extra == 0u) return RTW_OK;                       // nothing but one-primitive levels
+    const size_t n_total = (size_t)s->n_sah_nodes + extra;
+    if (!s->lb_nodes) {
+        // the node arrays grow once: SAH nodes stay in front (their references remain valid), the
+        // rebuilt levels go behind them
+        CK(cudaMalloc(reinterpret_cast<void**>(&s->lb_nodes), n_total * sizeof(Node)));
+        CK(cudaMalloc(reinterpret_cast<void**>(&s->lb_nodes16), n_total * sizeof(Node16)));
+        CK(cudaMemcpy(s->lb_nodes, s->d.nodes, (size_t)s->n_sah_nodes * sizeof(Node), cudaMemcpyDeviceToDevice));
+        CK(cudaMemcpy(s->lb_nodes16, s->d.nodes16, (size_t)s->n_sah_nodes * sizeof(Node16), cudaMemcpyDeviceToDevice));
+        CK(cudaMalloc(reinterpret_cast<void**>(&s->lb_leaves_d), s->lb_leaves_h.size() * sizeof(LbvhLeaf)));
+        CK(cudaMemcpy(s->lb_leaves_d, s->lb_leaves_h.data(), s->lb_leaves_h.size() * sizeof(LbvhLeaf), cudaMemcpyHostToDevice));
+        CK(cudaMalloc(reinterpret_cast<void**>(&s->lb_out_d), s->lb_levels.size() * sizeof(LbvhLevelOut)));
+        s->info.device_bytes += n_total * (sizeof(Node) + sizeof(Node16)) + s->lb_leaves_h.size() * sizeof(LbvhLeaf);
+        s->d.nodes = s->lb_nodes; s->d.nodes16 = s->lb_nodes16;
+    }
+    CK(cudaStreamSynchronize(s->stream));
+    CK(cudaEventRecord(s->ev0, s->stream));
+    uint32_t base = s->n_sah_nodes;
+    std::vector<uint32_t> level_base(s->lb_levels.size(), 0u);
+    for (size_t i = 0; i < s->lb_levels.size(); ++i) {
+        const LbvhLevelDesc& lv = s->lb_levels[i];
+        if (lv.count < 2u) continue;
+        level_base[i] = base;
+        cudaError_t e = lbvh_build_level(s->lb_leaves_d + lv.first, lv.count, base, s->lb_nodes, s->lb_nodes16,
+                                         s->lb_scratch, s->lb_out_d + i, s->stream);
+        if (e != cudaSuccess) return cuda_fail(e, "lbvh_build_level");
+        base += lv.count - 1u;
+    }
+    CK(cudaEventRecord(s->ev1, s->stream));
+    std::vector<LbvhLevelOut> out(s->lb_levels.size());
+    CK(cudaMemcpyAsync(out.data(), s->lb_out_d, out.size() * sizeof(LbvhLevelOut), cudaMemcpyDeviceToHost, s->stream));
+    CK(cudaStreamSynchronize(s->stream));
+    if (out_build_ms) CK(cudaEventElapsedTime(out_build_ms, s->ev0, s->ev1));
+    // stack bound first: if the rebuilt trees are too deep the scene keeps walking the SAH levels
+    uint32_t top_depth = s->sah_top_depth, inner_depth = s->sah_inner_depth;
+    for (size_t i = 0; i < s->lb_levels.size(); ++i) {
+        if (s->lb_levels[i].count < 2u) continue;
+        const uint32_t pushes = lbvh_pushes(out[i].max_depth);
+        if (s->lb_levels[i].owner < 0) top_depth = std::max(top_depth, pushes); else inner_depth = std::max(inner_depth, pushes);
+    }
+    int rc = refresh_launch_limits(s, top_depth, inner_depth);
+    if (rc) return rc;
+    for (size_t i = 0; i < s->lb_levels.size(); ++i) {
+        const LbvhLevelDesc& lv = s->lb_levels[i];
+        if (lv.count < 2u) continue;
+        Level L = lv.owner == -1 ? s->sah_top : lv.owner == -2 ? s->sah_top_inside : s->sah_inst_levels[lv.owner];
+        L.root = out[i].root;
+        for (int a = 0; a < 3; ++a) { L.lo[a] = out[i].lo[a]; L.hi[a] = out[i].hi[a]; }
+        if (lv.owner == -1) { s->top_all = L; s->d.top = L; }
+        else if (lv.owner == -2) s->top_inside = L;
+        else if ((rc = set_instance_level(s, (uint32_t)lv.owner, L))) return rc;
+    }
+    CK(cudaStreamSynchronize(s->stream));
+    return RTW_OK;
+}
+
+int rtw_scene_use_sah(rtw_scene* s) {
+    if (!s) return fail(RTW_E_INVALID, "null argument");
+    CK(cudaSetDevice(s->device));
+    CK(cudaStreamSynchronize(s->stream));
+    s->top_all = s->sah_top; s->d.top = s->sah_top; s->top_inside = s->sah_top_inside;
+    int rc;
+    for (const auto& lv : s->lb_levels)
+        if (lv.owner >= 0 && (rc = set_instance_level(s, (uint32_t)lv.owner, s->sah_inst_levels[lv.owner]))) return rc;
+    CK(cudaStreamSynchronize(s->stream));
+    return refresh_launch_limits(s, s->sah_top_depth, s->sah_inner_depth);
 }
 
 int rtw_quantize(const float* rgb, uint8_t* rgb8, uint64_t n_values, int device) {

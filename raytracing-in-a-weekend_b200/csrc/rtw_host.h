@@ -6,6 +6,7 @@
 #include <string>
 #include <vector>
 #include "rtw_device.h"
+#include "rtw_lbvh.h"
 #include "../../include/rtw.h"
 
 namespace rtw {
@@ -35,6 +36,9 @@ struct HostScene {
     std::vector<Enclosing> enclosing;
     Level top_inside;            // valid when !enclosing.empty()
     float background[3];
+    // the leaves of every level, for the optional on-device LBVH rebuild (rtw_lbvh.h)
+    std::vector<LbvhLeaf> lbvh_leaves;
+    std::vector<LbvhLevelDesc> lbvh_levels;
     rtw_scene_info info;
     uint32_t top_depth = 0, inner_depth = 0;   // deepest node chain of the top level / of any instance (-> stack_words)
 

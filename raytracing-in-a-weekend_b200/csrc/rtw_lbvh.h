@@ -1,0 +1,184 @@
+// rtw_lbvh.h — the optional on-GPU rebuild of the BVH (BASELINE north_star: "host SAH build, plus an
+// optional on-GPU LBVH rebuild"). It replaces the reference's builders AABB::new /
+// QuadAABB::new / IAABB::new (Rust/src/objects/aabb/aabb.rs:20-71, qaabb.rs:127-163,
+// iaabb.rs:80-116: random-axis median split, sort + deep clone at every level) for callers that
+// rebuild per frame.
+//
+// Per level (the scene's top level, the top level without enclosing volumes, every instance):
+//   1. Morton code (30 bits) of every leaf's box centre inside the level's centroid bounds
+//   2. radix sort of (code, leaf)
+//   3. Karras 2012 binary radix tree over the sorted codes (ties broken by position)
+//   4. bottom-up box fit (second arrival at a node computes it)
+//   5. collapse to the 4-wide nodes the traversal walks (rtw_device.h Node / Node16): an internal
+//      node at even depth becomes a wide node and adopts the children of its internal children
+// Leaves keep the primitive's own reference leaf box as the child box stored in their parent, exactly
+// as in the host SAH build, so the closest hit of a ray is the same whatever tree it walks
+// (rtw_trace.h: every primitive is reached through its own box; ties go to the lowest reference).
+//
+// The per-element steps are __host__ __device__: rtw_lbvh.cu runs them as kernels, the host-side
+// test emulator (tests/emu) runs them in plain loops.
+#pragma once
+#include "rtw_device.h"
+#if defined(__CUDACC__) || defined(RTW_LBVH_HOST_FP16)
+#include <cuda_fp16.h>
+#endif
+
+namespace rtw {
+
+struct LbvhLeaf {          // one traversable leaf of a level: reference + its reference leaf box
+    float lo[3]; uint32_t ref;
+    float hi[3]; uint32_t pad;
+};
+struct LbvhLevelDesc {     // a level's range in the concatenated leaf array
+    uint32_t first, count;
+    int32_t owner;         // -1: scene top level, -2: top level without enclosing volumes, k >= 0: instance k
+    uint32_t pad;
+};
+
+RTW_HD uint32_t lbvh_expand10(uint32_t v) {      // 10 bits -> every third bit
+    v = (v * 0x00010001u) & 0xFF0000FFu;
+    v = (v * 0x00000101u) & 0x0F00F00Fu;
+    v = (v * 0x00000011u) & 0xC30C30C3u;
+    v = (v * 0x00000005u) & 0x49249249u;
+    return v;
+}
+// centre of the leaf box, normalised to the level's centroid bounds [clo, clo + 1/cinv]
+RTW_HD uint32_t lbvh_morton(const LbvhLeaf& l, const float clo[3], const float cinv[3]) {
+    uint32_t q[3];
+    for (int a = 0; a < 3; ++a) {
+        float c = 0.5f * l.lo[a] + 0.5f * l.hi[a];
+        float u = (c - clo[a]) * cinv[a];
+        u = !(u > 0.0f) ? 0.0f : (u > 1.0f ? 1.0f : u);      // NaN -> 0
+        float s = u * 1024.0f;
+        q[a] = s >= 1023.0f ? 1023u : (uint32_t)s;
+    }
+    return (lbvh_expand10(q[0]) << 2) | (lbvh_expand10(q[1]) << 1) | lbvh_expand10(q[2]);
+}
+
+RTW_HD int lbvh_clz(uint32_t x) {
+#if defined(__CUDA_ARCH__)
+    return __clz((int)x);
+#else
+    return x ? __builtin_clz(x) : 32;
+#endif
+}
+// common-prefix length of sorted keys i and j (Karras 2012, with the index as tie-break); -1 outside
+RTW_HD int lbvh_delta(const uint32_t* codes, int n, int i, int j) {
+    if (j < 0 || j >= n) return -1;
+    const uint32_t a = codes[i], b = codes[j];
+    return a != b ? lbvh_clz(a ^ b) : 32 + lbvh_clz((uint32_t)i ^ (uint32_t)j);
+}
+
+// A child of a binary node: >= 0 is an internal node, < 0 is the sorted leaf ~child.
+// Internal node i of n - 1 (n >= 2 leaves): its children and their parent links.
+RTW_HD void lbvh_karras(const uint32_t* codes, int n, int i, int* left, int* right, int* parent_internal,
+                        int* parent_leaf) {
+    const int d = lbvh_delta(codes, n, i, i + 1) - lbvh_delta(codes, n, i, i - 1) >= 0 ? 1 : -1;
+    const int dmin = lbvh_delta(codes, n, i, i - d);
+    int lmax = 2;
+    while (lbvh_delta(codes, n, i, i + lmax * d) > dmin) lmax <<= 1;
+    int l = 0;
+    for (int t = lmax >> 1; t >= 1; t >>= 1)
+        if (lbvh_delta(codes, n, i, i + (l + t) * d) > dmin) l += t;
+    const int j = i + l * d;
+    const int dnode = lbvh_delta(codes, n, i, j);
+    int s = 0;
+    for (int t = (l + 1) >> 1;; t = (t + 1) >> 1) {
+        if (lbvh_delta(codes, n, i, i + (s + t) * d) > dnode) s += t;
+        if (t == 1) break;
+    }
+    const int gamma = i + s * d + (d < 0 ? -1 : 0);
+    const int lo = i < j ? i : j, hi = i < j ? j : i;
+    const int lc = lo == gamma ? ~gamma : gamma;
+    const int rc = hi == gamma + 1 ? ~(gamma + 1) : gamma + 1;
+    left[i] = lc; right[i] = rc;
+    if (lc < 0) parent_leaf[~lc] = i; else parent_internal[lc] = i;
+    if (rc < 0) parent_leaf[~rc] = i; else parent_internal[rc] = i;
+    if (i == 0) parent_internal[0] = -1;
+}
+
+struct LbvhBox { float lo[3], hi[3]; };
+RTW_HD LbvhBox lbvh_union(const LbvhBox& a, const LbvhBox& b) {
+    LbvhBox r;
+    for (int k = 0; k < 3; ++k) { r.lo[k] = a.lo[k] <= b.lo[k] ? a.lo[k] : b.lo[k]; r.hi[k] = a.hi[k] >= b.hi[k] ? a.hi[k] : b.hi[k]; }
+    return r;
+}
+RTW_HD LbvhBox lbvh_leaf_box(const LbvhLeaf& l) {
+    LbvhBox r;
+    for (int k = 0; k < 3; ++k) { r.lo[k] = l.lo[k]; r.hi[k] = l.hi[k]; }
+    return r;
+}
+
+// What the fit / emit steps read: the level's sorted leaves and its binary tree.
+struct LbvhTree {
+    const LbvhLeaf* leaves;     // the level's leaves (unsorted), indexed through `order`
+    const uint32_t* order;      // sorted position -> leaf index
+    const int* left; const int* right;
+    const LbvhBox* ibox;        // box of every internal node
+    const uint32_t* wide_index; // exclusive scan of the wide flags: internal node -> position among the level's wide nodes
+    uint32_t node_base;         // index of the level's first wide node in Scene::nodes / nodes16
+};
+RTW_HD LbvhBox lbvh_child_box(const LbvhTree& t, int c) {
+    return c < 0 ? lbvh_leaf_box(t.leaves[t.order[~c]]) : t.ibox[c];
+}
+
+// depth of internal node i (root = 0) by walking the parent links
+RTW_HD uint32_t lbvh_depth(const int* parent_internal, int i) {
+    uint32_t d = 0;
+    for (int p = parent_internal[i]; p >= 0; p = parent_internal[p]) ++d;
+    return d;
+}
+
+#if defined(__CUDACC__) || defined(RTW_LBVH_HOST_FP16)
+RTW_HD uint32_t lbvh_half2_rd(float a, float b) {   // two floats -> two halves rounded towards -inf
+    return (uint32_t)__half_as_ushort(__float2half_rd(a)) | ((uint32_t)__half_as_ushort(__float2half_rd(b)) << 16);
+}
+RTW_HD uint32_t lbvh_half2_ru(float a, float b) {   // ... towards +inf
+    return (uint32_t)__half_as_ushort(__float2half_ru(a)) | ((uint32_t)__half_as_ushort(__float2half_ru(b)) << 16);
+}
+
+// Wide node of internal node i (even depth): its children are the children of i, with an internal
+// child replaced by that child's two children. Writes both node formats at node_base + wide_index[i].
+RTW_HD void lbvh_emit(const LbvhTree& t, int i, Node* nodes, Node16* nodes16) {
+    int cand[4]; int n = 0;
+    const int two[2] = {t.left[i], t.right[i]};
+    for (int k = 0; k < 2; ++k) {
+        const int c = two[k];
+        if (c < 0) cand[n++] = c;
+        else { cand[n++] = t.left[c]; cand[n++] = t.right[c]; }
+    }
+    const float inf = INFINITY;
+    float lo[3][4], hi[3][4]; uint32_t ref[4];
+    for (int k = 0; k < 4; ++k) {
+        if (k < n) {
+            const int c = cand[k];
+            const LbvhBox b = lbvh_child_box(t, c);
+            for (int a = 0; a < 3; ++a) { lo[a][k] = b.lo[a]; hi[a][k] = b.hi[a]; }
+            ref[k] = c < 0 ? t.leaves[t.order[~c]].ref : make_ref(KIND_NODE, t.node_base + t.wide_index[c]);
+        } else {
+            for (int a = 0; a < 3; ++a) { lo[a][k] = inf; hi[a][k] = inf; }
+            ref[k] = REF_NONE;
+        }
+    }
+    const uint32_t me = t.node_base + t.wide_index[i];
+    Node& nd = nodes[me];
+    nd.lox = make_float4(lo[0][0], lo[0][1], lo[0][2], lo[0][3]); nd.loy = make_float4(lo[1][0], lo[1][1], lo[1][2], lo[1][3]);
+    nd.loz = make_float4(lo[2][0], lo[2][1], lo[2][2], lo[2][3]); nd.hix = make_float4(hi[0][0], hi[0][1], hi[0][2], hi[0][3]);
+    nd.hiy = make_float4(hi[1][0], hi[1][1], hi[1][2], hi[1][3]); nd.hiz = make_float4(hi[2][0], hi[2][1], hi[2][2], hi[2][3]);
+    nd.ref = make_uint4(ref[0], ref[1], ref[2], ref[3]);
+    nd.pad = make_uint4(0u, 0u, 0u, 0u);
+    Node16& h = nodes16[me];
+    h.a = make_uint4(lbvh_half2_rd(lo[0][0], lo[0][1]), lbvh_half2_rd(lo[0][2], lo[0][3]),
+                     lbvh_half2_rd(lo[1][0], lo[1][1]), lbvh_half2_rd(lo[1][2], lo[1][3]));
+    h.b = make_uint4(lbvh_half2_rd(lo[2][0], lo[2][1]), lbvh_half2_rd(lo[2][2], lo[2][3]),
+                     lbvh_half2_ru(hi[0][0], hi[0][1]), lbvh_half2_ru(hi[0][2], hi[0][3]));
+    h.c = make_uint4(lbvh_half2_ru(hi[1][0], hi[1][1]), lbvh_half2_ru(hi[1][2], hi[1][3]),
+                     lbvh_half2_ru(hi[2][0], hi[2][1]), lbvh_half2_ru(hi[2][2], hi[2][3]));
+    h.ref = nd.ref;
+}
+#endif
+
+// Stack words a walk below a level built this way can need: three siblings per wide level.
+RTW_HD uint32_t lbvh_pushes(uint32_t max_binary_depth) { return 3u * (max_binary_depth / 2u + 1u); }
+
+}  // namespace rtw

@@ -368,6 +368,15 @@ int build_host_scene(const rtw_scene_desc* d, HostScene& hs, std::string& err) {
         if (!finite3(lb.lo) || !finite3(lb.hi)) { err = "instance bounds are not finite"; return RTW_E_INVALID; }
         inst_leaves.push_back({k, lb});
     }
+    auto record_level = [&](const std::vector<BuildPrim>& prims, int32_t owner) {
+        LbvhLevelDesc lv; lv.first = (uint32_t)hs.lbvh_leaves.size(); lv.count = (uint32_t)prims.size(); lv.owner = owner; lv.pad = 0u;
+        for (const BuildPrim& p : prims) {
+            LbvhLeaf l; l.ref = p.ref; l.pad = 0u;
+            for (int a = 0; a < 3; ++a) { l.lo[a] = p.box.lo[a]; l.hi[a] = p.box.hi[a]; }
+            hs.lbvh_leaves.push_back(l);
+        }
+        hs.lbvh_levels.push_back(lv);
+    };
     // ---- levels: top first (its nodes lead the array and stay hot), then each instance
     for (auto& il : inst_leaves)
         top.push_back(make_prim(make_ref(KIND_INSTANCE, il.first) |
@@ -377,6 +386,7 @@ int build_host_scene(const rtw_scene_desc* d, HostScene& hs, std::string& err) {
     hs.info.n_tlas_leaves = (uint32_t)top.size();
     hs.moving = top_moving;
     hs.top = bld.level(top, 0u, (uint32_t)top_moving.size());
+    record_level(top, -1);
     hs.info.n_tlas_nodes = (uint32_t)hs.nodes.size();
     uint32_t top_depth = bld.max_pushes, inner_depth = 0;
     // ---- enclosing volumes (see rtw_host.h): one-sphere constant-density instances, not rotated,
@@ -421,6 +431,7 @@ int build_host_scene(const rtw_scene_desc* d, HostScene& hs, std::string& err) {
             std::vector<BuildPrim> rest;
             for (size_t i = 0; i < top.size(); ++i) if (!drop[i]) rest.push_back(top[i]);
             hs.top_inside = bld.level(rest, 0u, (uint32_t)top_moving.size());
+            record_level(rest, -2);
             top_depth = std::max(top_depth, bld.max_pushes);   // (info.n_tlas_nodes stays the full top level's count)
         }
     }
@@ -430,6 +441,7 @@ int build_host_scene(const rtw_scene_desc* d, HostScene& hs, std::string& err) {
         uint32_t mf = (uint32_t)hs.moving.size();
         hs.moving.insert(hs.moving.end(), inst_moving[k].begin(), inst_moving[k].end());
         hs.instances[k].level = bld.level(inst_prims[k], mf, (uint32_t)inst_moving[k].size());
+        record_level(inst_prims[k], (int32_t)k);
         inner_depth = std::max(inner_depth, bld.max_pushes);
     }
     // the half-float copy of the nodes (fast kernels): boxes rounded outwards

@@ -6,16 +6,78 @@
 #include <cstring>
 #include <string>
 #include <vector>
+#define RTW_LBVH_HOST_FP16 1
+#include <algorithm>
 #include "../../raytracing-in-a-weekend_b200/csrc/rtw_host.h"
 #include "../../raytracing-in-a-weekend_b200/csrc/rtw_shade.h"
 
 using namespace rtw;
 
+// The LBVH rebuild of rtw_lbvh.cu, step for step, in plain loops over the same __host__ __device__
+// element functions (rtw_lbvh.h): every level with two or more leaves is rebuilt behind the SAH nodes
+// and becomes the level that is walked.
+static void lbvh_rebuild_host(HostScene& hs) {
+    uint32_t top_depth = hs.top_depth, inner_depth = hs.inner_depth;
+    for (const LbvhLevelDesc& lv : hs.lbvh_levels) {
+        const int n = (int)lv.count;
+        if (n < 2) continue;
+        const LbvhLeaf* leaves = hs.lbvh_leaves.data() + lv.first;
+        float clo[3], chi[3], cinv[3];
+        for (int a = 0; a < 3; ++a) { clo[a] = INFINITY; chi[a] = -INFINITY; }
+        for (int i = 0; i < n; ++i)
+            for (int a = 0; a < 3; ++a) {
+                float c = 0.5f * leaves[i].lo[a] + 0.5f * leaves[i].hi[a];
+                if (c == c) { clo[a] = std::min(clo[a], c); chi[a] = std::max(chi[a], c); }
+            }
+        for (int a = 0; a < 3; ++a) cinv[a] = chi[a] > clo[a] ? 1.0f / (chi[a] - clo[a]) : 0.0f;
+        std::vector<uint32_t> codes(n), order(n), sorted(n);
+        for (int i = 0; i < n; ++i) { codes[i] = lbvh_morton(leaves[i], clo, cinv); order[i] = (uint32_t)i; }
+        std::stable_sort(order.begin(), order.end(), [&](uint32_t a, uint32_t b) { return codes[a] < codes[b]; });
+        for (int i = 0; i < n; ++i) sorted[i] = codes[order[i]];
+        std::vector<int> left(n - 1), right(n - 1), parent_i(n - 1, -1), parent_l(n, -1);
+        for (int i = 0; i < n - 1; ++i) lbvh_karras(sorted.data(), n, i, left.data(), right.data(), parent_i.data(), parent_l.data());
+        std::vector<LbvhBox> ibox(n - 1);
+        std::vector<uint32_t> flag(n - 1, 0u);
+        LbvhTree t; t.leaves = leaves; t.order = order.data(); t.left = left.data(); t.right = right.data();
+        t.ibox = ibox.data();
+        for (int p = 0; p < n; ++p)
+            for (int cur = parent_l[p]; cur >= 0; cur = parent_i[cur]) {
+                if (flag[cur]++ == 0u) break;
+                ibox[cur] = lbvh_union(lbvh_child_box(t, left[cur]), lbvh_child_box(t, right[cur]));
+            }
+        std::vector<uint32_t> wide(n - 1), wide_index(n - 1);
+        uint32_t max_depth = 0, run = 0;
+        for (int i = 0; i < n - 1; ++i) {
+            uint32_t dpt = lbvh_depth(parent_i.data(), i);
+            wide[i] = (dpt & 1u) ? 0u : 1u;
+            max_depth = std::max(max_depth, dpt + 1u);
+        }
+        for (int i = 0; i < n - 1; ++i) { wide_index[i] = run; run += wide[i]; }
+        t.wide_index = wide_index.data();
+        t.node_base = (uint32_t)hs.nodes.size();
+        hs.nodes.resize(hs.nodes.size() + run); hs.nodes16.resize(hs.nodes.size());
+        for (int i = 0; i < n - 1; ++i) if (wide[i]) lbvh_emit(t, i, hs.nodes.data(), hs.nodes16.data());
+        Level& L = lv.owner == -1 ? hs.top : lv.owner == -2 ? hs.top_inside : hs.instances[lv.owner].level;
+        L.root = make_ref(KIND_NODE, t.node_base);
+        for (int a = 0; a < 3; ++a) { L.lo[a] = ibox[0].lo[a]; L.hi[a] = ibox[0].hi[a]; }
+        const uint32_t pushes = lbvh_pushes(max_depth);
+        if (lv.owner < 0) top_depth = std::max(top_depth, pushes); else inner_depth = std::max(inner_depth, pushes);
+    }
+    hs.top_depth = top_depth; hs.inner_depth = inner_depth;
+}
+
+extern "C" int emu_render_ex(const rtw_scene_desc* d, const rtw_camera* cam, const rtw_render_opts* o, float* out,
+                             uint64_t* stats, rtw_scene_info* info, int use_lbvh);
 extern "C" int emu_render(const rtw_scene_desc* d, const rtw_camera* cam, const rtw_render_opts* o, float* out,
                           uint64_t* stats /* paths, rays, nan */, rtw_scene_info* info) {
+    return emu_render_ex(d, cam, o, out, stats, info, 0);
+}
+extern "C" int emu_render_ex(const rtw_scene_desc* d, const rtw_camera* cam, const rtw_render_opts* o, float* out,
+                             uint64_t* stats /* paths, rays, nan */, rtw_scene_info* info, int use_lbvh) {
     HostScene hs; std::string err;
     int rc = build_host_scene(d, hs, err);
     if (rc) { std::fprintf(stderr, "emu: %s\n", err.c_str()); return rc; }
+    if (use_lbvh) lbvh_rebuild_host(hs);
     if (info) *info = hs.info;
     Scene sc = hs.host_view();
     RenderParams P; uint32_t total = 0;

@@ -39,12 +39,14 @@ def load_emu():
         _lib.emu_render.restype = C.c_int
         _lib.emu_render.argtypes = [C.POINTER(A.rtw_scene_desc), C.POINTER(A.rtw_camera), C.POINTER(A.rtw_render_opts),
                                     C.c_void_p, C.POINTER(C.c_uint64), C.POINTER(A.rtw_scene_info)]
+        _lib.emu_render_ex.restype = C.c_int
+        _lib.emu_render_ex.argtypes = _lib.emu_render.argtypes + [C.c_int]
     return _lib
 
 
 class EmuSceneHandle:
-    def __init__(self, lib, fs):
-        self._lib, self._fs = lib, fs
+    def __init__(self, lib, fs, lbvh: bool = False):
+        self._lib, self._fs, self._lbvh = lib, fs, lbvh
         self.last = (C.c_uint64 * 3)()
         self.last_info = A.rtw_scene_info()
 
@@ -54,8 +56,8 @@ class EmuSceneHandle:
     def render(self, cam, o) -> np.ndarray:
         rows = o.row_count if o.row_count else cam.height
         out = np.empty((rows, cam.width, 3), dtype=np.float32)
-        rc = self._lib.emu_render(C.byref(self._fs.desc), C.byref(cam), C.byref(o), out.ctypes.data_as(C.c_void_p),
-                                  self.last, C.byref(self.last_info))
+        rc = self._lib.emu_render_ex(C.byref(self._fs.desc), C.byref(cam), C.byref(o), out.ctypes.data_as(C.c_void_p),
+                                     self.last, C.byref(self.last_info), 1 if self._lbvh else 0)
         if rc != 0:
             raise ValueError(f"emu_render failed: {rc}")
         return out
@@ -70,17 +72,20 @@ class EmuSceneHandle:
 class EmuBackend:
     name = "emu"
 
-    def __init__(self):
+    def __init__(self, lbvh: bool = False):
+        """lbvh=True: every level is rebuilt with the LBVH steps of rtw_lbvh.h (run in host loops)
+        before rendering, as rtw_scene_rebuild_lbvh does on the device."""
         self.lib = load_emu()
+        self.lbvh = lbvh
 
     def camera_init(self, width, aspect_ratio, vfov, origin, direction, vup, lens_radius):
         from oracle_backend import OracleBackend
         return OracleBackend().camera_init(width, aspect_ratio, vfov, origin, direction, vup, lens_radius)
 
     def scene(self, scene) -> EmuSceneHandle:
-        key = ("emu",)
+        key = ("emu", self.lbvh)
         h = scene._backend_cache.get(key)
         if h is None:
-            h = EmuSceneHandle(self.lib, scene.flatten())
+            h = EmuSceneHandle(self.lib, scene.flatten(), self.lbvh)
             scene._backend_cache[key] = h
         return h
