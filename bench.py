@@ -351,7 +351,8 @@ def run_b200(args):
         bytes_per_ray = sum(per_ray[k] * COST[k][1] for k in work_keys)
         tflops = flop_per_ray * rays_launch / (k_ms * 1e-3) / 1e12
         l2_gbs = bytes_per_ray * rays_launch / (k_ms * 1e-3) / 1e9
-        state_bytes = 216.0 if wavefront else 0.0     # path records streamed per ray, else REDs only
+        # path records streamed per ray: extend 40 R + 16 W, shade 72 R + 48 W, + 8 W per new path
+        state_bytes = (176.0 + 8.0 * paths_total / max(1.0, rays_total)) if wavefront else 0.0
         step_ms = elapsed_ms / args.steps
         hbm_gbs = (state_bytes * rays_step + H * W * 3 * 4 * 2.0) / (step_ms * 1e-3) / 1e9
         # the kernel's own HBM stream (wavefront: 40 B of ray record read + 16 B of hit record written per ray)
@@ -380,7 +381,7 @@ def run_b200(args):
                             "hbm_kernel": {"achieved": k_hbm_gbs, "peak": hbm_peak, "unit": "GB/s", "frac": k_hbm_gbs / hbm_peak},
                             "hbm": {"achieved": hbm_gbs, "peak": hbm_peak, "unit": "GB/s", "frac": hbm_gbs / hbm_peak,
                                     "peak_source": hbm_src,
-                                    "note": "whole step: path records streamed by extend+shade (216 B/ray) + framebuffer REDs; the scene (<10 MB) is L1/L2-resident"}}}
+                                    "note": "whole step: path records streamed by extend+shade (176 B/ray + 8 B per new path) + framebuffer REDs; the scene (<10 MB) is L1/L2-resident"}}}
         cpu = cpu_baseline_obj(cpu_sample(job, args.cpu_seconds)) if world == 1 else None
         paths_frame = W * H * spp
         val = paths_frame * args.steps / (elapsed_ms * 1e-3) / 1e6

@@ -289,7 +289,7 @@ int ensure_pool(rtw_scene* s) {
     {
         WfQueue& q = s->pool.q;
         if ((rc = pool_alloc(s, &q.o, cap)) || (rc = pool_alloc(s, &q.d, cap)) || (rc = pool_alloc(s, &q.id, cap)) ||
-            (rc = pool_alloc(s, &q.thr, cap)) || (rc = pool_alloc(s, &q.rad, cap))) return rc;
+            (rc = pool_alloc(s, &q.thr, cap))) return rc;
     }
     if ((rc = pool_alloc(s, &s->pool.hit, cap))) return rc;
     if ((rc = pool_alloc(s, &s->pool.supply, (size_t)cap / 16u))) return rc;      // 2 words per warp of 32 slots
@@ -325,6 +325,7 @@ int enqueue_wavefront(rtw_scene* s, const RenderParams& P, int variant, float* d
     L.shade_grid = (int)(s->pool.capacity / RTW_WF_SHADE_BLOCK);
     WfCounters init{};
     init.total_paths = 32ull * L.tiles_x * L.tiles_y * P.sample_count;
+    L.total_paths = init.total_paths;
     s->h_wc[0] = init;
     CK(cudaMemcpyAsync(s->d_wc, &s->h_wc[0], sizeof(WfCounters), cudaMemcpyHostToDevice, st));
     auto extend = [&]() {
@@ -409,7 +410,9 @@ int enqueue_render(rtw_scene* s, const rtw_camera* cam, const rtw_render_opts* o
     CK(cudaEventRecord(s->ev0, st));
     if ((o->flags & RTW_FLAG_WAVEFRONT) && (o->flags & RTW_FLAG_MEGAKERNEL)) return fail(RTW_E_INVALID, "both pipeline flags set");
     const uint64_t n_paths = (uint64_t)cam->width * P.row_count * P.sample_count;
-    s->last_wavefront = (o->flags & RTW_FLAG_WAVEFRONT) || (!(o->flags & RTW_FLAG_MEGAKERNEL) && n_paths >= (1ull << 18));
+    if ((o->flags & RTW_FLAG_WAVEFRONT) && P.depth > WF_MAX_DEPTH) return fail(RTW_E_UNSUPPORTED, "wavefront pipeline: depth > 4095 (use the megakernel)");
+    s->last_wavefront = (o->flags & RTW_FLAG_WAVEFRONT) ||
+                        (!(o->flags & RTW_FLAG_MEGAKERNEL) && n_paths >= (1ull << 18) && P.depth <= WF_MAX_DEPTH);
     if (s->last_wavefront) {
         s->launches = 0;
         if ((rc = enqueue_wavefront(s, P, variant, d_out, st))) return rc;

@@ -368,7 +368,13 @@ wf_shade_kernel(const Scene sc, const RenderParams P, const WfPool pool, WfCount
     }
     const WfQueue q = pool.q;                               // grid * block == capacity (a multiple of 256)
     const uint32_t W = P.cam.width;
-    const unsigned long long total = wc->total_paths;
+    const unsigned long long total = L.total_paths;        // a launch parameter: reading it from wc put an L2 round trip at the head of every warp
+    // live_mark is read here, long before it is needed: once the first warps of the launch have set
+    // it, every later warp sees `mark` already and leaves without waiting for an L2 round trip (that
+    // wait was 21 % of the kernel's memory stalls, profiles/r1i_wf_shade_by_line.txt). Warps that
+    // saw the old value look again before storing: thousands of stores to one word cost 3x the
+    // whole kernel (profiles/r1j_ab_shade_live_mark.txt).
+    const uint32_t live_mark_seen = __ldcg(&wc->live_mark);
 #if defined(RTW_COUNT_WORK)
     Work wk = {0u, 0u, 0u, 0u, 0u};
     Work* const wp = &wk;
@@ -378,7 +384,7 @@ wf_shade_kernel(const Scene sc, const RenderParams P, const WfPool pool, WfCount
     const uint32_t FULL = 0xFFFFFFFFu;
     const uint32_t lane = threadIdx.x & 31u;
     Path path;
-    bool alive = false, was_live = false;
+    bool alive = false, was_live = false, fresh = false;
     if (!init) {
         const float4 rd = q.d[e];
         was_live = f2u(rd.w) != WF_DEAD;
@@ -386,26 +392,33 @@ wf_shade_kernel(const Scene sc, const RenderParams P, const WfPool pool, WfCount
             const float4 ro = q.o[e];
             const uint2 id = q.id[e];
             const uint4 hit = pool.hit[e];
-            const float4 thr = q.thr[e], rad = q.rad[e];
+            const float4 thr = q.thr[e];
             path.ray.time = ro.w;
-            path.thr = v3(thr.x, thr.y, thr.z); path.rad = v3(rad.x, rad.y, rad.z);
-            path.pixel = id.x; path.sample = id.y; path.block = f2u(thr.w);
-            const uint32_t dl = f2u(rad.w);
-            path.depth_left = dl & 0x7FFFFFFFu; path.poison = (dl >> 31) != 0u;
+            path.thr = v3(thr.x, thr.y, thr.z); path.rad = v3(0.f, 0.f, 0.f);   // this segment's contribution only
+            path.pixel = id.x; path.sample = id.y;
+            const uint32_t st = f2u(thr.w);
+            path.block = st & WF_BLOCK_MASK; path.depth_left = (st >> WF_DEPTH_SHIFT) & WF_DEPTH_MASK; path.poison = (st >> 31) != 0u;
             Trav T;
             T.o = v3(ro.x, ro.y, ro.z); T.d = v3(rd.x, rd.y, rd.z);
             T.t = u2f(hit.x); T.ref = hit.y; T.inner = hit.z;
             TraceCtx cx = path_ctx(sc, P, path, wp);
             bool finished = segment_end(cx, sc.noises, P, path, T);
             if (!finished && path.depth_left < 1u) finished = true;   // ray_color.rs:14-16: the next call returns black
-            if (finished) {
-                V3 c = path_result(path);
-                if (!finite3(c)) atomicAdd(&ctr->nan_paths, 1ull);
-                float* px = sum + ((size_t)path.pixel - (size_t)P.row_begin * W) * 3u;
-                atomicAdd(px + 0, c.x); atomicAdd(px + 1, c.y); atomicAdd(px + 2, c.z);
-            } else {
-                alive = true;
+            // L = emitted + col_mod * L(next): what this segment adds (thr * emitted, thr *
+            // background) goes straight into the frame, so no radiance travels with the path. A path
+            // that is or becomes NaN (N8) adds NaN once, when it ends, as the reference's sum would be.
+            V3 c = path.rad;
+            if (!finite3(c)) path.poison = true;
+            float* px = sum + ((size_t)path.pixel - (size_t)P.row_begin * W) * 3u;
+            if (finished && path.poison) {
+                atomicAdd(&ctr->nan_paths, 1ull);
+                const float qn = u2f(0x7FC00000u);
+                c = v3(qn, qn, qn);
             }
+            if ((finished || !path.poison) && (c.x != 0.f || c.y != 0.f || c.z != 0.f)) {
+                atomicAdd(px + 0, c.x); atomicAdd(px + 1, c.y); atomicAdd(px + 2, c.z);
+            }
+            alive = !finished;
         }
     }
     // ---- regeneration: free slots take the next camera samples of the warp's reserved range.
@@ -454,6 +467,7 @@ wf_shade_kernel(const Scene sc, const RenderParams P, const WfPool pool, WfCount
             if (i < W && jr < P.row_count) {                          // edge tiles are padded; such an index is dropped
                 generate(P, i, P.row_begin + jr, s, path);
                 alive = true;
+                fresh = true;
             }
         }
     }
@@ -461,13 +475,12 @@ wf_shade_kernel(const Scene sc, const RenderParams P, const WfPool pool, WfCount
     if (alive) {
         q.o[e] = make_float4(path.ray.o.x, path.ray.o.y, path.ray.o.z, path.ray.time);
         q.d[e] = make_float4(path.ray.d.x, path.ray.d.y, path.ray.d.z, u2f(P.depth - path.depth_left));
-        q.id[e] = make_uint2(path.pixel, path.sample);
-        q.thr[e] = make_float4(path.thr.x, path.thr.y, path.thr.z, u2f(path.block));
-        q.rad[e] = make_float4(path.rad.x, path.rad.y, path.rad.z,
-                               u2f(path.depth_left | (path.poison ? 0x80000000u : 0u)));
+        if (fresh) q.id[e] = make_uint2(path.pixel, path.sample);     // a continuing path keeps its identity
+        q.thr[e] = make_float4(path.thr.x, path.thr.y, path.thr.z,
+                               u2f((path.block & WF_BLOCK_MASK) | (path.depth_left << WF_DEPTH_SHIFT) | (path.poison ? 0x80000000u : 0u)));
         const uint32_t am = __activemask();
         // same value from every warp; read first (L2) so that only the first few warps store
-        if (lane == (uint32_t)(__ffs(am) - 1) && __ldcg(&wc->live_mark) != mark) wc->live_mark = mark;
+        if (lane == (uint32_t)(__ffs(am) - 1) && live_mark_seen != mark && __ldcg(&wc->live_mark) != mark) wc->live_mark = mark;
     } else {
         q.d[e] = make_float4(0.f, 0.f, 0.f, u2f(WF_DEAD));
     }

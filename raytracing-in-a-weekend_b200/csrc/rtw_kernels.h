@@ -46,9 +46,14 @@ struct WfQueue {
     float4* o;           // origin.xyz, time
     float4* d;           // direction.xyz, bits(bounce) (WF_DEAD: empty slot)
     uint2*  id;          // pixel index, sample index (Philox counter words 0/1)
-    float4* thr;         // throughput.xyz, bits(next Philox block)
-    float4* rad;         // radiance.xyz, bits(depth_left | poison << 31)
+    float4* thr;         // throughput.xyz, bits(next Philox block | depth_left << 19 | NaN-poison << 31)
 };
+// No radiance travels with a path: each segment's contribution (thr * emitted, thr * background) is
+// added to the frame when it arises (rtw_kernels.cu, wf_shade_kernel).
+#define WF_BLOCK_MASK 0x7FFFFu      // 19 bits of Philox block counter
+#define WF_DEPTH_SHIFT 19
+#define WF_DEPTH_MASK 0xFFFu        // depth_left <= 4095: deeper renders take the megakernel (rtw_api.cu)
+#define WF_MAX_DEPTH 4095u
 #define WF_DEAD 0xFFFFFFFFu
 struct WfPool {
     WfQueue q;
@@ -71,6 +76,7 @@ struct WfLaunch {
     uint32_t supply_chunk;           // sample indices a shade warp reserves per atomic
     uint32_t sample_major;           // order of the sample supply: 0 = tile-major (all samples of a tile, then the next tile), 1 = sample-major
     uint32_t index32;                // tiles * samples < 2^32: 32-bit index arithmetic
+    unsigned long long total_paths;  // = WfCounters::total_paths
     int extend_grid, shade_grid;
     size_t smem_bytes;
 };
