@@ -120,6 +120,7 @@ struct rtw_scene {
     uint64_t launches = 0;
     // wavefront pipeline state (allocated on first use)
     WfPool pool{};
+    uint32_t pool_allocated = 0;          // slots the pool arrays hold; pool.capacity = slots the current render uses
     WfCounters* d_wc = nullptr;
     WfCounters* h_wc = nullptr;           // pinned, 4 slots
     cudaEvent_t wf_ev[4] = {nullptr, nullptr, nullptr, nullptr};
@@ -281,25 +282,32 @@ int pool_alloc(rtw_scene* s, T** p, size_t n) {
     return RTW_OK;
 }
 
-int ensure_pool(rtw_scene* s) {
-    if (s->pool.capacity) return RTW_OK;
-    uint32_t cap = env_u32("RTW_WF_POOL", 1u << 21);
-    cap = std::max(cap, 4096u) & ~255u;           // a multiple of 32, so a warp's slots advance through the tile-major sample order together
+// Pool of path slots for one render of `n_paths` paths. The bigger the pool the fewer, longer
+// launches (less tail per launch) but the longer the frame drains at the end: 1/128 of the frame's
+// paths, between 16 Ki and 6 Mi slots (C5: 2 Mi slots are best at 400 spp, 6 Mi from 2000 spp on,
+// +6 %; profiles/r1j_sweep_pool.txt). RTW_WF_POOL overrides. Arrays only ever grow.
+int ensure_pool(rtw_scene* s, unsigned long long n_paths) {
+    unsigned long long want = env_u32("RTW_WF_POOL", 0u);
+    if (want == 0ull) want = std::min<unsigned long long>(6ull << 20, std::max<unsigned long long>(16384ull, n_paths / 128ull));
+    const uint32_t cap = (uint32_t)((std::max<unsigned long long>(want, 4096ull) + 255ull) & ~255ull);   // whole shade blocks
     int rc;
-    {
-        WfQueue& q = s->pool.q;
+    if (s->pool_allocated < cap) {
+        WfQueue& q = s->pool.q;     // (the smaller arrays stay on the scene's allocation list until it is destroyed)
         if ((rc = pool_alloc(s, &q.o, cap)) || (rc = pool_alloc(s, &q.d, cap)) || (rc = pool_alloc(s, &q.id, cap)) ||
             (rc = pool_alloc(s, &q.thr, cap))) return rc;
+        if ((rc = pool_alloc(s, &s->pool.hit, cap))) return rc;
+        if ((rc = pool_alloc(s, &s->pool.supply, (size_t)cap / 16u))) return rc;      // 2 words per warp of 32 slots
+        s->pool_allocated = cap;
     }
-    if ((rc = pool_alloc(s, &s->pool.hit, cap))) return rc;
-    if ((rc = pool_alloc(s, &s->pool.supply, (size_t)cap / 16u))) return rc;      // 2 words per warp of 32 slots
-    CK(cudaMalloc(&s->d_wc, sizeof(WfCounters)));
-    CK(cudaMallocHost(&s->h_wc, 4 * sizeof(WfCounters)));
-    for (auto& e : s->wf_ev) CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
-    for (auto& t : s->wf_t) for (auto& e : t) CK(cudaEventCreate(&e));
-    CK(wf_extend_occupancy_fast(&s->occ_wf[0], s->smem_bytes));
-    CK(wf_extend_occupancy_strict(&s->occ_wf[1], s->smem_bytes));
-    CK(wf_extend_occupancy_count(&s->occ_wf[2], s->smem_bytes));
+    if (!s->d_wc) {
+        CK(cudaMalloc(&s->d_wc, sizeof(WfCounters)));
+        CK(cudaMallocHost(&s->h_wc, 4 * sizeof(WfCounters)));
+        for (auto& e : s->wf_ev) CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+        for (auto& t : s->wf_t) for (auto& e : t) CK(cudaEventCreate(&e));
+        CK(wf_extend_occupancy_fast(&s->occ_wf[0], s->smem_bytes));
+        CK(wf_extend_occupancy_strict(&s->occ_wf[1], s->smem_bytes));
+        CK(wf_extend_occupancy_count(&s->occ_wf[2], s->smem_bytes));
+    }
     s->pool.capacity = cap;
     return RTW_OK;
 }
@@ -308,7 +316,7 @@ int ensure_pool(rtw_scene* s) {
 // stays two batches of iterations ahead of the device and reads the queue length of finished
 // batches from pinned memory, so the call returns only when the frame is complete.
 int enqueue_wavefront(rtw_scene* s, const RenderParams& P, int variant, float* d_out, cudaStream_t st) {
-    int rc = ensure_pool(s);
+    int rc = ensure_pool(s, (unsigned long long)P.cam.width * P.row_count * P.sample_count);
     if (rc) return rc;
     WfLaunch L{};
     L.tiles_x = (P.cam.width + 7u) / 8u;
@@ -317,7 +325,7 @@ int enqueue_wavefront(rtw_scene* s, const RenderParams& P, int variant, float* d
     L.smem_bytes = s->smem_bytes;
     L.fetch_min = std::min(32u, std::max(1u, env_u32("RTW_WF_FETCH_MIN", 16u)));
     L.chunk = std::max(32u, env_u32("RTW_WF_CHUNK", 64u));
-    L.supply_chunk = std::max(32u, env_u32("RTW_WF_SUPPLY_CHUNK", 128u)) & ~31u;
+    L.supply_chunk = std::max(32u, env_u32("RTW_WF_SUPPLY_CHUNK", 256u)) & ~31u;
     L.sample_major = env_u32("RTW_WF_SAMPLE_MAJOR", 0u) ? 1u : 0u;
     L.index32 = ((unsigned long long)L.tiles_x * L.tiles_y * P.sample_count < (1ull << 32)) ? 1u : 0u;
     CK(cudaMemsetAsync(s->pool.supply, 0, (size_t)s->pool.capacity / 16u * sizeof(unsigned long long), st));
@@ -580,7 +588,7 @@ int refresh_launch_limits(rtw_scene* s, uint32_t top_depth, uint32_t inner_depth
     CK(mega_occupancy_fast(&s->occ_fast, s->smem_bytes));
     CK(mega_occupancy_strict(&s->occ_strict, s->smem_bytes));
     CK(mega_occupancy_count(&s->occ_count, s->smem_bytes));
-    if (s->pool.capacity) {
+    if (s->d_wc) {
         CK(wf_extend_occupancy_fast(&s->occ_wf[0], s->smem_bytes));
         CK(wf_extend_occupancy_strict(&s->occ_wf[1], s->smem_bytes));
         CK(wf_extend_occupancy_count(&s->occ_wf[2], s->smem_bytes));
