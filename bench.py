@@ -368,6 +368,7 @@ def run_b200(args):
             pass
         roofline = {"kernel": kname, "bound": bname, "achieved": bach, "peak": bpeak, "unit": bunit,
                     "frac": bach / bpeak, "traffic": traffic, "traffic_source": traffic_src,
+                    "traffic_note": "captured at a pool of 2 000 128 slots; scale by rays_per_launch / 2.0e6 for this run's pool",
                     "algorithmic_hbm_bytes_per_launch": k_hbm_bytes * rays_launch,
                     "peak_source": "rtw_microbench on this GPU for fp32 and L2 (MEASURED_PEAKS.json has neither); MEASURED_PEAKS.json hbm_gbs for HBM" if hbm_src == "measured" else "rtw_microbench on this GPU for fp32 and L2; B200_PROFILING.md fallback for HBM",
                     "kernel_ms_per_launch": k_ms, "rays_per_launch": rays_launch,
