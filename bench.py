@@ -363,12 +363,14 @@ def run_b200(args):
         traffic, traffic_src = None, None
         try:      # DRAM bytes of the dominant kernel per launch, from the committed ncu --set full capture
             tj = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))[kname]
-            traffic, traffic_src = float(tj["dram_bytes_per_launch"]), tj["source"]
+            # the capture ran at slots_per_launch slots; this run's launches hold rays_launch rays
+            traffic = float(tj["dram_bytes_per_launch"]) * rays_launch / float(tj.get("slots_per_launch", rays_launch))
+            traffic_src = tj["source"]
         except Exception:
             pass
         roofline = {"kernel": kname, "bound": bname, "achieved": bach, "peak": bpeak, "unit": bunit,
                     "frac": bach / bpeak, "traffic": traffic, "traffic_source": traffic_src,
-                    "traffic_note": "captured at a pool of 2 000 128 slots; scale by rays_per_launch / 2.0e6 for this run's pool",
+                    "traffic_note": "ncu DRAM bytes per slot (captured at a pool of 2 000 128 slots) x this run's rays per launch",
                     "algorithmic_hbm_bytes_per_launch": k_hbm_bytes * rays_launch,
                     "peak_source": "rtw_microbench on this GPU for fp32 and L2 (MEASURED_PEAKS.json has neither); MEASURED_PEAKS.json hbm_gbs for HBM" if hbm_src == "measured" else "rtw_microbench on this GPU for fp32 and L2; B200_PROFILING.md fallback for HBM",
                     "kernel_ms_per_launch": k_ms, "rays_per_launch": rays_launch,
