@@ -120,6 +120,7 @@ struct rtw_scene {
     uint64_t launches = 0;
     // wavefront pipeline state (allocated on first use)
     WfPool pool{};
+    uint32_t n_walked_instances = 0;      // instance leaves of the top level that are walked as a level (not one-sphere records)
     uint32_t pool_allocated = 0;          // slots the pool arrays hold; pool.capacity = slots the current render uses
     WfCounters* d_wc = nullptr;
     WfCounters* h_wc = nullptr;           // pinned, 4 slots
@@ -219,6 +220,8 @@ int upload_scene(rtw_scene* s, HostScene& hs) {
     d.top = hs.top;
     s->top_all = hs.top; s->top_inside = hs.top_inside; s->enclosing = hs.enclosing;
     s->lb_leaves_h = hs.lbvh_leaves; s->lb_levels = hs.lbvh_levels;
+    s->n_walked_instances = 0;
+    for (const auto& lv : hs.lbvh_levels) if (lv.owner >= 0 && !(hs.instances[lv.owner].flags & INST_ONE_SPHERE)) ++s->n_walked_instances;
     s->sah_top = hs.top; s->sah_top_inside = hs.top_inside;
     s->sah_inst_levels.resize(hs.instances.size());
     for (size_t k = 0; k < hs.instances.size(); ++k) s->sah_inst_levels[k] = hs.instances[k].level;
@@ -283,12 +286,16 @@ int pool_alloc(rtw_scene* s, T** p, size_t n) {
 }
 
 // Pool of path slots for one render of `n_paths` paths. The bigger the pool the fewer, longer
-// launches (less tail per launch) but the longer the frame drains at the end: 1/128 of the frame's
-// paths, between 16 Ki and 6 Mi slots (C5: 2 Mi slots are best at 400 spp, 6 Mi from 2000 spp on,
-// +6 %; profiles/r1j_sweep_pool.txt). RTW_WF_POOL overrides. Arrays only ever grow.
+// launches (less tail and launch overhead) but the longer the frame drains at the end: 1/128 of the
+// frame's paths, between 1 Mi and 6 Mi slots and never more than there are paths (C5: 2 Mi slots are
+// best at 400 spp, 6 Mi from 2000 spp on, +6 %; profiles/r1j_sweep_pool.txt; C1's 9 M paths are
+// launch-bound below 1 Mi). RTW_WF_POOL overrides. Arrays only ever grow.
 int ensure_pool(rtw_scene* s, unsigned long long n_paths) {
     unsigned long long want = env_u32("RTW_WF_POOL", 0u);
-    if (want == 0ull) want = std::min<unsigned long long>(6ull << 20, std::max<unsigned long long>(16384ull, n_paths / 128ull));
+    if (want == 0ull) {
+        want = std::min<unsigned long long>(6ull << 20, std::max<unsigned long long>(1ull << 20, n_paths / 128ull));
+        want = std::min(want, std::max<unsigned long long>(16384ull, n_paths));      // never more slots than paths
+    }
     const uint32_t cap = (uint32_t)((std::max<unsigned long long>(want, 4096ull) + 255ull) & ~255ull);   // whole shade blocks
     int rc;
     if (s->pool_allocated < cap) {
@@ -334,6 +341,11 @@ int enqueue_wavefront(rtw_scene* s, const RenderParams& P, int variant, float* d
     WfCounters init{};
     init.total_paths = 32ull * L.tiles_x * L.tiles_y * P.sample_count;
     L.total_paths = init.total_paths;
+    {
+        const bool events_rare = (unsigned long long)s->n_walked_instances * 16ull <= (unsigned long long)s->info.n_tlas_leaves;
+        L.prim_w = std::max(1u, env_u32("RTW_WF_PRIM_W", events_rare ? 8u : 4u));
+        L.event_w = std::max(1u, env_u32("RTW_WF_EVENT_W", events_rare ? 16u : 4u));
+    }
     s->h_wc[0] = init;
     CK(cudaMemcpyAsync(s->d_wc, &s->h_wc[0], sizeof(WfCounters), cudaMemcpyHostToDevice, st));
     auto extend = [&]() {

@@ -296,7 +296,7 @@ wf_extend_kernel(const Scene sc, const RenderParams P, const WfPool pool, WfCoun
         const int cn = __popc(__ballot_sync(FULL, on_node)), cp = __popc(__ballot_sync(FULL, on_prim)),
                   ce = __popc(__ballot_sync(FULL, on_event));
         SCHED_COUNT(iters, 0, 0);
-        if (cn >= cp && cn >= ce) {
+        if (cn * 4 >= cp * (int)L.prim_w && cn * 4 >= ce * (int)L.event_w) {
             SCHED_COUNT(step, 0, cn);
             SCHED_TIME_BEGIN(0);
             if (on_node) {

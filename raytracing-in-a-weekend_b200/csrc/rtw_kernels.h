@@ -77,6 +77,12 @@ struct WfLaunch {
     uint32_t sample_major;           // order of the sample supply: 0 = tile-major (all samples of a tile, then the next tile), 1 = sample-major
     uint32_t index32;                // tiles * samples < 2^32: 32-bit index arithmetic
     unsigned long long total_paths;  // = WfCounters::total_paths
+    // extend's vote: node steps run while node lanes * 4 >= leaf lanes * prim_w and >= event lanes * event_w.
+    // 4 / 4 is the plain majority. Where instance events are rare (C5: three instance leaves among 2 409)
+    // the few lanes that wait for a leaf test or a level change should not wait for a node majority to
+    // dissolve: 8 / 16 is +3.6 % there; where they are common (C4: two of eight leaves) any bias costs
+    // 1-6 % (profiles/r1j_ab_vote_weights.txt). rtw_api.cu picks by the share of instance leaves.
+    uint32_t prim_w, event_w;
     int extend_grid, shade_grid;
     size_t smem_bytes;
 };
