@@ -262,6 +262,23 @@ int rtw_quantize(const float* rgb, uint8_t* rgb8, uint64_t n_values, int device)
 int rtw_render_rgb8(rtw_scene* scene, const rtw_camera* cam, const rtw_render_opts* opts,
                     uint8_t* out_rgb8);
 
+/* The 8-bit bilateral filter of the Rust2 tree (Rust2/src/postprocessing.rs:70-135
+ * `bilateral_filter(img, Proximity::new(size, type))`; ProximityType :11-14). Bytes in, bytes out:
+ * height rows of width RGB8 pixels. The window is the reference's: [x-size, x+size) x [y-size, y+size)
+ * clipped to the image, a diamond |dx|+|dy| < size inside it for RTW_PROX_EDGES; sigma_spatial =
+ * ceil(0.02 * diagonal), sigma_range = mean luminance gradient (a flat image therefore comes out black,
+ * as in the reference). Not in place. params (4 floats, may be NULL) receives {spatial, avg_gradient,
+ * inv_range, inv_spatial}. */
+enum { RTW_PROX_SQUARE = 0, RTW_PROX_EDGES = 1 };
+int rtw_bilateral_filter_device(const uint8_t* d_rgb8, uint32_t width, uint32_t height, uint32_t size,
+                                int proximity, uint8_t* d_out_rgb8, float* d_params, int device,
+                                void* stream);
+/* The same for HOST images (what the reference function receives and returns): H2D, filter, D2H.
+ * out_kernel_ms (may be NULL) receives the device time of the four kernels. `device` < 0 = current. */
+int rtw_bilateral_filter(const uint8_t* rgb8, uint32_t width, uint32_t height, uint32_t size,
+                         int proximity, uint8_t* out_rgb8, float* out_params, float* out_kernel_ms,
+                         int device);
+
 int rtw_get_stats(rtw_scene* scene, rtw_stats* out);
 /* Warp-scheduling counters of the wavefront extend kernel, filled by RTW_FLAG_COUNT_WORK |
  * RTW_FLAG_WAVEFRONT renders: out[0] = loop iterations (per warp, summed); then for the step kinds

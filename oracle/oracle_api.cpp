@@ -10,6 +10,7 @@
 #include <cstring>
 #include <memory>
 #include "render.hpp"
+#include "postprocessing.hpp"
 
 using namespace oracle;
 
@@ -172,6 +173,15 @@ void oracle_quantize(const float* rgb, uint8_t* out, uint64_t n_values) {
         x = std::round(x);               // half away from zero, like f32::round
         out[k] = (x != x) ? (uint8_t)0 : (uint8_t)x;
     }
+}
+
+// Rust2/src/postprocessing.rs:70-135 bilateral_filter (oracle/postprocessing.hpp). params_out (may be
+// null) receives {spatial, avg_gradient, inv_range, inv_spatial}.
+void oracle_bilateral_filter(const uint8_t* rgb8, uint32_t width, uint32_t height, uint32_t size, int kind,
+                             int exp_mode, uint8_t* out_rgb8, float* params_out) {
+    oracle_post::Params p;
+    oracle_post::bilateral_filter(rgb8, width, height, size, kind, exp_mode, out_rgb8, &p);
+    if (params_out) { params_out[0] = p.spatial; params_out[1] = p.avg_gradient; params_out[2] = p.inv_range; params_out[3] = p.inv_spatial; }
 }
 
 }  // extern "C"

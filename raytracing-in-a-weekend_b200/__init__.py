@@ -13,6 +13,7 @@ from .viewport import (Viewport, async_render, get_default_backend, ray_color_al
                        set_default_backend)
 
 from .write_img import quantize, write_img, write_img_f32
+from .postprocessing import Proximity, ProximityType, bilateral_filter
 from . import scene_json
 from .scene_json import ParseError
 

@@ -114,6 +114,8 @@ SYMBOLS = {
     "rtw_quantize_device": (C.c_int, [C.c_void_p, C.c_void_p, u64, C.c_int, C.c_void_p]),
     "rtw_quantize": (C.c_int, [C.c_void_p, C.c_void_p, u64, C.c_int]),
     "rtw_render_rgb8": (C.c_int, [C.c_void_p, P(rtw_camera), P(rtw_render_opts), C.c_void_p]),
+    "rtw_bilateral_filter_device": (C.c_int, [C.c_void_p, u32, u32, u32, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]),
+    "rtw_bilateral_filter": (C.c_int, [C.c_void_p, u32, u32, u32, C.c_int, C.c_void_p, P(f32), P(f32), C.c_int]),
     "rtw_get_stats": (C.c_int, [C.c_void_p, P(rtw_stats)]),
     "rtw_get_sched_stats": (C.c_int, [C.c_void_p, P(u64)]),
     "rtw_microbench": (C.c_int, [C.c_int, C.c_int, C.c_int, P(C.c_double)]),

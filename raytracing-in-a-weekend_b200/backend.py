@@ -143,6 +143,26 @@ class CudaBackend:
         A.check(self.lib.rtw_quantize(C.c_void_p(src.ctypes.data), C.c_void_p(out.ctypes.data), src.size, self.device))
         return out
 
+    def bilateral_filter(self, img_u8: np.ndarray, size: int, kind: int = 0, info: dict | None = None) -> np.ndarray:
+        """Rust2/src/postprocessing.rs:70-135 on the device: H x W x 3 uint8 in and out. kind 0 = Square, 1 = Edges.
+        `info` (optional dict) receives spatial / avg_gradient / inv_range / inv_spatial / kernel_ms."""
+        src = np.ascontiguousarray(img_u8, dtype=np.uint8)
+        if src.ndim != 3 or src.shape[2] != 3:
+            raise ValueError("expected an H x W x 3 uint8 image")
+        out = np.empty_like(src)
+        par = (C.c_float * 4)()
+        ms = C.c_float()
+        A.check(self.lib.rtw_bilateral_filter(C.c_void_p(src.ctypes.data), src.shape[1], src.shape[0], int(size), int(kind),
+                                              C.c_void_p(out.ctypes.data), par, C.byref(ms), self.device))
+        if info is not None:
+            info.update(spatial=par[0], avg_gradient=par[1], inv_range=par[2], inv_spatial=par[3], kernel_ms=ms.value)
+        return out
+
+    def bilateral_filter_device(self, d_in: int, width: int, height: int, size: int, kind: int, d_out: int,
+                                d_params: int = 0, stream: int = 0):
+        A.check(self.lib.rtw_bilateral_filter_device(C.c_void_p(d_in), width, height, int(size), int(kind), C.c_void_p(d_out),
+                                                     C.c_void_p(d_params), self.device, C.c_void_p(stream)))
+
     def quantize_device(self, d_rgb: int, d_rgb8: int, n_values: int, stream: int = 0):
         A.check(self.lib.rtw_quantize_device(C.c_void_p(d_rgb), C.c_void_p(d_rgb8), n_values, self.device,
                                              C.c_void_p(stream)))

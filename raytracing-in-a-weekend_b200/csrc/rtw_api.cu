@@ -11,6 +11,7 @@
 #include "rtw_host.h"
 #include "rtw_kernels.h"
 #include "rtw_lbvh_driver.h"
+#include "rtw_post.h"
 
 using namespace rtw;
 
@@ -706,6 +707,48 @@ int rtw_quantize(const float* rgb, uint8_t* rgb8, uint64_t n_values, int device)
     cudaFree(d_in); cudaFree(d_out);
     if (e != cudaSuccess) return cuda_fail(e, "rtw_quantize");
     return RTW_OK;
+}
+
+// Rust2/src/postprocessing.rs:70-135 on the device (rtw_post.cu)
+int rtw_bilateral_filter_device(const uint8_t* d_rgb8, uint32_t width, uint32_t height, uint32_t size, int proximity,
+                                uint8_t* d_out_rgb8, float* d_params, int device, void* stream) {
+    if (!d_rgb8 || !d_out_rgb8) return fail(RTW_E_INVALID, "null argument");
+    if (d_rgb8 == d_out_rgb8) return fail(RTW_E_INVALID, "bilateral filter cannot run in place");
+    if (width < 2u || height < 2u || width > 32768u || height > 32768u) return fail(RTW_E_INVALID, "bilateral filter: image must be 2..32768 pixels a side");
+    if (proximity != RTW_PROX_SQUARE && proximity != RTW_PROX_EDGES) return fail(RTW_E_INVALID, "unknown proximity type");
+    if (size > 4096u) return fail(RTW_E_INVALID, "bilateral filter: window size > 4096");
+    if (device >= 0) CK(cudaSetDevice(device));
+    int launches = 0;
+    cudaError_t e = bilateral_filter_enqueue(d_rgb8, width, height, size, proximity, d_out_rgb8, d_params,
+                                             static_cast<cudaStream_t>(stream), &launches);
+    if (e != cudaSuccess) return cuda_fail(e, "rtw_bilateral_filter_device");
+    return RTW_OK;
+}
+
+int rtw_bilateral_filter(const uint8_t* rgb8, uint32_t width, uint32_t height, uint32_t size, int proximity,
+                         uint8_t* out_rgb8, float* out_params, float* out_kernel_ms, int device) {
+    if (!rgb8 || !out_rgb8) return fail(RTW_E_INVALID, "null argument");
+    if (width < 2u || height < 2u || width > 32768u || height > 32768u) return fail(RTW_E_INVALID, "bilateral filter: image must be 2..32768 pixels a side");
+    if (device >= 0) CK(cudaSetDevice(device));
+    const size_t n = (size_t)width * height * 3u;
+    uint8_t* d_buf = nullptr; float* d_par = nullptr;
+    cudaEvent_t e0 = nullptr, e1 = nullptr;
+    cudaError_t e = cudaMalloc(&d_buf, 2u * n + 256u);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaMalloc");
+    uint8_t* d_out = d_buf + (n + 255u) / 256u * 256u;
+    int rc = RTW_OK;
+    auto done = [&](int code) { cudaFree(d_buf); cudaFree(d_par); if (e0) cudaEventDestroy(e0); if (e1) cudaEventDestroy(e1); return code; };
+    if ((e = cudaMalloc(&d_par, 4 * sizeof(float))) != cudaSuccess) return done(cuda_fail(e, "cudaMalloc"));
+    if ((e = cudaEventCreate(&e0)) != cudaSuccess || (e = cudaEventCreate(&e1)) != cudaSuccess) return done(cuda_fail(e, "cudaEventCreate"));
+    if ((e = cudaMemcpy(d_buf, rgb8, n, cudaMemcpyHostToDevice)) != cudaSuccess) return done(cuda_fail(e, "cudaMemcpy"));
+    cudaEventRecord(e0, 0);
+    rc = rtw_bilateral_filter_device(d_buf, width, height, size, proximity, d_out, d_par, -1, nullptr);
+    if (rc) return done(rc);
+    cudaEventRecord(e1, 0);
+    if ((e = cudaMemcpy(out_rgb8, d_out, n, cudaMemcpyDeviceToHost)) != cudaSuccess) return done(cuda_fail(e, "rtw_bilateral_filter"));
+    if (out_params && (e = cudaMemcpy(out_params, d_par, 4 * sizeof(float), cudaMemcpyDeviceToHost)) != cudaSuccess) return done(cuda_fail(e, "cudaMemcpy"));
+    if (out_kernel_ms) { *out_kernel_ms = 0.f; cudaEventSynchronize(e1); cudaEventElapsedTime(out_kernel_ms, e0, e1); }
+    return done(RTW_OK);
 }
 
 int rtw_render_rgb8(rtw_scene* scene, const rtw_camera* cam, const rtw_render_opts* opts, uint8_t* out_rgb8) {

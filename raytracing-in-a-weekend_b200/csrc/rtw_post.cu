@@ -1,0 +1,172 @@
+// rtw_post.cu — the reference's bilateral filter (Rust2/src/postprocessing.rs:70-135) as four kernels.
+//
+//   1. gradient      one thread per interior pixel: |grad I| of the luminance (:75-85), to a scratch row-major array
+//   2. params        ONE warp: the reference accumulates that array in a single f32, in row-major order (:75-87);
+//                    f32 addition is not associative, so the sum is taken in exactly that order by one lane while
+//                    the other 31 stage the next 1024 values into shared memory. Then sigma_range/sigma_spatial.
+//   3. weight table  exp(-inv_spatial * d2 - inv_range * (diff/255)^2) (:108-114) only depends on (|dx|, |dy|, |diff|):
+//                    (size+1)^2 * 256 entries, computed once in double and rounded to f32
+//   4. filter        one thread per (pixel, channel); walks the reference's window in the reference's order
+//                    (x outer, y inner, both half-open: postprocessing.rs:30-61) with sequential f32 sums
+//
+// All f32 arithmetic that reaches the output is written with the round-to-nearest intrinsics so that no
+// contraction to FMA can happen (rustc never contracts). Bytes in, bytes out: the result is compared byte for
+// byte with oracle/postprocessing.hpp (exp_mode 1).
+#include "rtw_post.h"
+
+namespace rtw {
+
+namespace {
+
+constexpr uint32_t kTableMaxSize = 64;    // (64+1)^2 KiB = 4.1 MiB of weights; larger windows evaluate exp in place
+constexpr uint32_t kChunk = 1024;         // gradient values staged per step of the ordered sum
+
+__device__ __forceinline__ float post_intensity(const uint8_t* __restrict__ p) {       // postprocessing.rs:64-68
+    const float r = __fdiv_rn(__fmul_rn(0.2989f, (float)p[0]), 255.0f);
+    const float g = __fdiv_rn(__fmul_rn(0.5870f, (float)p[1]), 255.0f);
+    const float b = __fdiv_rn(__fmul_rn(0.1140f, (float)p[2]), 255.0f);
+    return __fadd_rn(__fadd_rn(r, g), b);
+}
+
+__global__ void post_gradient_kernel(const uint8_t* __restrict__ img, uint32_t w, uint32_t h, float* __restrict__ grad) {
+    const uint32_t iw = w - 2u, n = iw * (h - 2u);
+    for (uint32_t k = blockIdx.x * blockDim.x + threadIdx.x; k < n; k += gridDim.x * blockDim.x) {
+        const uint32_t y = 1u + k / iw, x = 1u + k % iw;
+        const float Iu = post_intensity(img + 3u * ((size_t)(y - 1u) * w + x));
+        const float Id = post_intensity(img + 3u * ((size_t)(y + 1u) * w + x));
+        const float Ir = post_intensity(img + 3u * ((size_t)y * w + x + 1u));
+        const float Il = post_intensity(img + 3u * ((size_t)y * w + x - 1u));
+        const float a = __fsub_rn(Iu, Id), b = __fsub_rn(Il, Ir);
+        grad[k] = __fsqrt_rn(__fadd_rn(__fmul_rn(a, a), __fmul_rn(b, b)));
+    }
+}
+
+// One warp. `grad` is padded to a multiple of kChunk floats (the padding is never added).
+__global__ void post_params_kernel(const float* __restrict__ grad, uint32_t n, uint32_t w, uint32_t h, float* __restrict__ params) {
+    __shared__ float4 buf[kChunk / 4];
+    const uint32_t lane = threadIdx.x;
+    const uint32_t n_chunks = (n + kChunk - 1u) / kChunk;
+    const float4* g4 = reinterpret_cast<const float4*>(grad);
+    float4 r[kChunk / 128];
+    if (n_chunks)
+        for (uint32_t k = 0; k < kChunk / 128; ++k) r[k] = g4[lane + 32u * k];
+    float sum = 0.0f;
+    for (uint32_t c = 0; c < n_chunks; ++c) {
+        for (uint32_t k = 0; k < kChunk / 128; ++k) buf[lane + 32u * k] = r[k];
+        __syncwarp();
+        if (c + 1u < n_chunks)                                   // in flight while lane 0 adds
+            for (uint32_t k = 0; k < kChunk / 128; ++k) r[k] = g4[(size_t)(c + 1u) * (kChunk / 4) + lane + 32u * k];
+        if (lane == 0) {
+            const uint32_t left = n - c * kChunk, cnt = left < kChunk ? left : kChunk;
+            const float* f = reinterpret_cast<const float*>(buf);
+            uint32_t k = 0;
+            for (; k + 4u <= cnt; k += 4u) {
+                const float4 v = buf[k >> 2];
+                sum = __fadd_rn(sum, v.x); sum = __fadd_rn(sum, v.y); sum = __fadd_rn(sum, v.z); sum = __fadd_rn(sum, v.w);
+            }
+            for (; k < cnt; ++k) sum = __fadd_rn(sum, f[k]);
+        }
+        __syncwarp();
+    }
+    if (lane == 0) {                                              // postprocessing.rs:73,87-90
+        const float spatial = ceilf(__fmul_rn(0.02f, __fsqrt_rn((float)(w * w + h * h))));
+        const float avg = __fdiv_rn(sum, (float)((w - 2u) * (h - 2u)));
+        params[0] = spatial;
+        params[1] = avg;
+        params[2] = __fdiv_rn(0.5f, __fmul_rn(avg, avg));
+        params[3] = __fdiv_rn(0.5f, __fmul_rn(spatial, spatial));
+    }
+}
+
+// postprocessing.rs:108-114; diff enters squared, so its sign is dropped. exp in double, rounded once to f32.
+__device__ __forceinline__ float post_weight(float inv_spatial, float inv_range, uint32_t d2, uint32_t adiff) {
+    const float t = __fdiv_rn((float)adiff, 255.0f);
+    const float arg = __fsub_rn(__fmul_rn(-inv_spatial, (float)d2), __fmul_rn(inv_range, __fmul_rn(t, t)));
+    return (float)exp((double)arg);
+}
+
+__global__ void post_table_kernel(const float* __restrict__ params, uint32_t size, float* __restrict__ table) {
+    const uint32_t n = (size + 1u) * (size + 1u) * 256u;
+    const float inv_range = params[2], inv_spatial = params[3];
+    for (uint32_t e = blockIdx.x * blockDim.x + threadIdx.x; e < n; e += gridDim.x * blockDim.x) {
+        const uint32_t adiff = e & 255u, cell = e >> 8, adx = cell % (size + 1u), ady = cell / (size + 1u);
+        table[e] = post_weight(inv_spatial, inv_range, adx * adx + ady * ady, adiff);
+    }
+}
+
+__device__ __forceinline__ uint8_t post_as_u8(float v) {          // Rust `f32 as u8`: saturating, NaN -> 0
+    if (!(v == v) || v <= 0.0f) return 0;
+    if (v >= 255.0f) return 255;
+    return (uint8_t)v;
+}
+
+template <bool kTable>
+__global__ void __launch_bounds__(256) post_bilateral_kernel(const uint8_t* __restrict__ img, uint32_t w, uint32_t h, uint32_t size,
+                                                             int kind, const float* __restrict__ params,
+                                                             const float* __restrict__ table, uint8_t* __restrict__ out) {
+    const size_t n = (size_t)w * h * 3u;
+    const float inv_range = params[2], inv_spatial = params[3];
+    for (size_t tid = (size_t)blockIdx.x * blockDim.x + threadIdx.x; tid < n; tid += (size_t)gridDim.x * blockDim.x) {
+        const uint32_t c = (uint32_t)(tid % 3u), pix = (uint32_t)(tid / 3u), x = pix % w, y = pix / w;
+        const uint32_t left = x - min(x, size), up = y - min(y, size);
+        const uint32_t right = x + min(w - x - 1u, size), down = y + min(h - y - 1u, size);
+        const int p = img[tid];
+        float col = 0.0f, ws = 0.0f;
+        for (uint32_t i = left; i < right; ++i) {
+            const uint32_t dx = x < i ? i - x : x - i;
+            const uint8_t* colp = img + (size_t)i * 3u + c;
+            for (uint32_t j = up; j < down; ++j) {
+                const uint32_t dy = y < j ? j - y : y - j;
+                if (kind == POST_PROX_EDGES && !(dx + dy < size)) continue;
+                const int pi = colp[(size_t)j * w * 3u];
+                const uint32_t adiff = (uint32_t)abs(pi - p);
+                const float wgt = kTable ? __ldg(table + (((dy * (size + 1u) + dx) << 8) | adiff))
+                                         : post_weight(inv_spatial, inv_range, dx * dx + dy * dy, adiff);
+                col = __fadd_rn(col, __fdiv_rn(__fmul_rn((float)pi, wgt), 255.0f));
+                ws = __fadd_rn(ws, wgt);
+            }
+        }
+        out[tid] = post_as_u8(__fdiv_rn(__fmul_rn(col, 255.0f), ws));
+    }
+}
+
+int post_grid(size_t n, int block) {
+    size_t g = (n + block - 1) / block;
+    if (g < 1) g = 1;
+    if (g > 148u * 32u) g = 148u * 32u;
+    return (int)g;
+}
+
+}  // namespace
+
+#define POST_RELEASE() do { if (d_grad) cudaFreeAsync(d_grad, st); if (d_table) cudaFreeAsync(d_table, st); if (d_own) cudaFreeAsync(d_own, st); } while (0)
+#define PC(call) do { cudaError_t e__ = (call); if (e__ != cudaSuccess) { POST_RELEASE(); return e__; } } while (0)
+
+cudaError_t bilateral_filter_enqueue(const uint8_t* d_in, uint32_t width, uint32_t height, uint32_t size, int kind,
+                                     uint8_t* d_out, float* d_params, cudaStream_t st, int* n_launches) {
+    float *d_grad = nullptr, *d_table = nullptr, *d_own = nullptr;
+    const uint32_t n_grad = (width - 2u) * (height - 2u);
+    const size_t grad_padded = ((size_t)n_grad + kChunk - 1u) / kChunk * kChunk + kChunk;
+    const bool use_table = size <= kTableMaxSize;
+    const size_t n_table = use_table ? (size_t)(size + 1u) * (size + 1u) * 256u : 0u;
+    PC(cudaMallocAsync(reinterpret_cast<void**>(&d_grad), grad_padded * sizeof(float), st));
+    if (n_table) PC(cudaMallocAsync(reinterpret_cast<void**>(&d_table), n_table * sizeof(float), st));
+    if (!d_params) { PC(cudaMallocAsync(reinterpret_cast<void**>(&d_own), 4 * sizeof(float), st)); d_params = d_own; }
+    int launches = 0;
+    if (n_grad) { post_gradient_kernel<<<post_grid(n_grad, 256), 256, 0, st>>>(d_in, width, height, d_grad); ++launches; }
+    post_params_kernel<<<1, 32, 0, st>>>(d_grad, n_grad, width, height, d_params); ++launches;
+    const size_t n = (size_t)width * height * 3u;
+    if (use_table) {
+        post_table_kernel<<<post_grid(n_table, 256), 256, 0, st>>>(d_params, size, d_table); ++launches;
+        post_bilateral_kernel<true><<<post_grid(n, 256), 256, 0, st>>>(d_in, width, height, size, kind, d_params, d_table, d_out);
+    } else {
+        post_bilateral_kernel<false><<<post_grid(n, 256), 256, 0, st>>>(d_in, width, height, size, kind, d_params, nullptr, d_out);
+    }
+    ++launches;
+    PC(cudaGetLastError());
+    if (n_launches) *n_launches = launches;
+    POST_RELEASE();
+    return cudaSuccess;
+}
+
+}  // namespace rtw

@@ -64,5 +64,10 @@ extern "C" {
     pub fn rtw_quantize(rgb: *const f32, rgb8: *mut u8, n_values: u64, device: c_int) -> c_int;
     /// rtw_render + that quantiser fused on the device; `out_rgb8` is host memory (H*W*3 bytes).
     pub fn rtw_render_rgb8(scene: *mut rtw_scene, cam: *const rtw_camera, opts: *const rtw_render_opts, out_rgb8: *mut u8) -> c_int;
+    /// Rust2's `postprocessing::bilateral_filter(&img, Proximity::new(size, type))` (postprocessing.rs:70-135) on the
+    /// device: `rgb8` / `out_rgb8` are the raw buffers of `ImageBuffer<Rgb<u8>, Vec<u8>>` (`img.as_raw()`),
+    /// proximity 0 = Square, 1 = Edges; `out_params` / `out_kernel_ms` may be null.
+    pub fn rtw_bilateral_filter(rgb8: *const u8, width: u32, height: u32, size: u32, proximity: c_int, out_rgb8: *mut u8,
+                                out_params: *mut f32, out_kernel_ms: *mut f32, device: c_int) -> c_int;
     pub fn rtw_get_stats(scene: *mut rtw_scene, out: *mut rtw_stats) -> c_int;
 }

@@ -76,6 +76,8 @@ def load_oracle(fast: bool = False):
     lib.oracle_interval_intersect.argtypes = [C.c_float, C.c_float, C.c_float, C.c_float, f32p]
     lib.oracle_quantize.restype = None
     lib.oracle_quantize.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64]
+    lib.oracle_bilateral_filter.restype = None
+    lib.oracle_bilateral_filter.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_int, C.c_int, C.c_void_p, f32p]
     lib.oracle_collide.restype = C.c_int
     lib.oracle_collide.argtypes = [C.c_void_p, f32p, f32p, C.c_float, C.c_float, C.c_float, C.c_uint64,
                                    C.c_uint32, C.c_uint32, C.c_uint32, P(oracle_hit)]
@@ -155,6 +157,19 @@ class OracleBackend:
         src = np.ascontiguousarray(img, dtype=np.float32)
         out = np.empty(src.shape, dtype=np.uint8)
         self.lib.oracle_quantize(src.ctypes.data_as(C.c_void_p), out.ctypes.data_as(C.c_void_p), src.size)
+        return out
+
+    def bilateral_filter(self, img_u8: np.ndarray, size: int, kind: int = 0, info: dict | None = None,
+                         exp_mode: int = 1) -> np.ndarray:
+        """Rust2/src/postprocessing.rs:70-135, CPU restatement. exp_mode 0: libm expf (what f32::exp calls);
+        1: double exp rounded to f32 (what the CUDA path computes)."""
+        src = np.ascontiguousarray(img_u8, dtype=np.uint8)
+        out = np.empty_like(src)
+        par = (C.c_float * 4)()
+        self.lib.oracle_bilateral_filter(src.ctypes.data_as(C.c_void_p), src.shape[1], src.shape[0], int(size), int(kind),
+                                         int(exp_mode), out.ctypes.data_as(C.c_void_p), par)
+        if info is not None:
+            info.update(spatial=par[0], avg_gradient=par[1], inv_range=par[2], inv_spatial=par[3])
         return out
 
     def scene(self, scene) -> OracleSceneHandle:
