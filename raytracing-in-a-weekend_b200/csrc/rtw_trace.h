@@ -201,7 +201,11 @@ struct Trav {
 RTW_HD bool trav_slow(const Trav& T) { return (T.mode & 4u) != 0u; }
 RTW_HD void trav_set_ray(Trav& T, V3 o, V3 d) {
     T.o = o; T.d = d;
+#if defined(RTW_FAST_NODES) && !defined(RTW_NO_FASTINV)
+    T.inv = v3(fast_rcp(d.x), fast_rcp(d.y), fast_rcp(d.z));    // a zero component gives NaN here, inf below: both take the slow slab
+#else
     T.inv = v3(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);
+#endif
     T.a = dot(d, d);
     bool slow = !(isfinite(T.inv.x) && isfinite(T.inv.y) && isfinite(T.inv.z));
     T.mode = (T.mode & 3u) | (slow ? 4u : 0u);
