@@ -301,11 +301,50 @@ RTW_HD bool ref_is_leaf_test(uint32_t r) { return ref_is_prim(r) || ref_is_one_s
 //   strict build / host: exact f32 boxes, the reference's own operation order, (bound - o) * (1/d);
 //   fast device build: half-float boxes (Node16, rounded outwards) and one FFMA per plane,
 //   bound * (1/d) - o * (1/d).
+#if defined(RTW_FAST_NODES) && !defined(RTW_NO_SIGN_SELECT)
+// Fast device build: the ray's direction signs pick each axis' entry and exit planes while they are still packed
+// halves (12 selects per node), so that a child costs max3 / min3 + the interval clamp instead of six two-way
+// min / max. Same values as min(x1, x2) / max(x1, x2): the FFMA is monotone in the plane coordinate.
+__device__ __forceinline__ void slab4_signed(const uint4 a, const uint4 b, const uint4 c4, const Trav& T, float mint,
+                                             float maxt, float tn[4]) {
+    const bool sx = T.inv.x < 0.0f, sy = T.inv.y < 0.0f, sz = T.inv.z < 0.0f;
+    const uint32_t nx01 = sx ? b.z : a.x, nx23 = sx ? b.w : a.y, fx01 = sx ? a.x : b.z, fx23 = sx ? a.y : b.w;
+    const uint32_t ny01 = sy ? c4.x : a.z, ny23 = sy ? c4.y : a.w, fy01 = sy ? a.z : c4.x, fy23 = sy ? a.w : c4.y;
+    const uint32_t nz01 = sz ? c4.z : b.x, nz23 = sz ? c4.w : b.y, fz01 = sz ? b.x : c4.z, fz23 = sz ? b.y : c4.w;
+    const float ox = -T.o.x * T.inv.x, oy = -T.o.y * T.inv.y, oz = -T.o.z * T.inv.z;
+    float NX[4], NY[4], NZ[4], FX[4], FY[4], FZ[4];
+    float2 f;
+    f = __half22float2(*reinterpret_cast<const __half2*>(&nx01)); NX[0] = f.x; NX[1] = f.y;
+    f = __half22float2(*reinterpret_cast<const __half2*>(&nx23)); NX[2] = f.x; NX[3] = f.y;
+    f = __half22float2(*reinterpret_cast<const __half2*>(&ny01)); NY[0] = f.x; NY[1] = f.y;
+    f = __half22float2(*reinterpret_cast<const __half2*>(&ny23)); NY[2] = f.x; NY[3] = f.y;
+    f = __half22float2(*reinterpret_cast<const __half2*>(&nz01)); NZ[0] = f.x; NZ[1] = f.y;
+    f = __half22float2(*reinterpret_cast<const __half2*>(&nz23)); NZ[2] = f.x; NZ[3] = f.y;
+    f = __half22float2(*reinterpret_cast<const __half2*>(&fx01)); FX[0] = f.x; FX[1] = f.y;
+    f = __half22float2(*reinterpret_cast<const __half2*>(&fx23)); FX[2] = f.x; FX[3] = f.y;
+    f = __half22float2(*reinterpret_cast<const __half2*>(&fy01)); FY[0] = f.x; FY[1] = f.y;
+    f = __half22float2(*reinterpret_cast<const __half2*>(&fy23)); FY[2] = f.x; FY[3] = f.y;
+    f = __half22float2(*reinterpret_cast<const __half2*>(&fz01)); FZ[0] = f.x; FZ[1] = f.y;
+    f = __half22float2(*reinterpret_cast<const __half2*>(&fz23)); FZ[2] = f.x; FZ[3] = f.y;
+#pragma unroll
+    for (int c = 0; c < 4; ++c) {
+        const float x1 = fmaf(NX[c], T.inv.x, ox), y1 = fmaf(NY[c], T.inv.y, oy), z1 = fmaf(NZ[c], T.inv.z, oz);
+        const float x2 = fmaf(FX[c], T.inv.x, ox), y2 = fmaf(FY[c], T.inv.y, oy), z2 = fmaf(FZ[c], T.inv.z, oz);
+        const float mn = fmaxf(fmaxf(fmaxf(x1, y1), z1), mint);
+        const float mx = fminf(fminf(fminf(x2, y2), z2), maxt);
+        tn[c] = (mn > mx) ? INFINITY : mn;
+    }
+}
+#endif
+
 RTW_HD void slab4(const Scene& sc, uint32_t idx, const Trav& T, float mint, float maxt, float tn[4], uint4& rr) {
 #if defined(RTW_FAST_NODES)
     const Node16* np = &sc.nodes16[idx];
     const uint4 a = RTW_LDG(&np->a), b = RTW_LDG(&np->b), c4 = RTW_LDG(&np->c);
     rr = RTW_LDG(&np->ref);
+#if !defined(RTW_NO_SIGN_SELECT)
+    if (!trav_slow(T)) { slab4_signed(a, b, c4, T, mint, maxt, tn); return; }
+#endif
     float LX[4], LY[4], LZ[4], HX[4], HY[4], HZ[4];
     {
         float2 f;
