@@ -147,14 +147,14 @@ def test_enclosing_volume_elimination(cuda, monkeypatch):
     assert s1.instance_tests > s0.instance_tests + 0.5 * s0.rays
 
 
-@pytest.mark.parametrize("name", ["C1", "C4", "C4_smoke"])
+@pytest.mark.parametrize("name", ["C1", "C2", "C4", "C4_smoke"])
 def test_fast_kernels_converge_to_strict(name, cuda):
     """SURVEY 8d L2 between the two builds: the fast kernels (FFMA contraction, SFU-based divisions,
     direct sphere sampling instead of the rejection loop, no inert volumes) and the strict ones (the
     reference's operation order and Philox stream) estimate the same image: mean luminance within
     0.5 %, RMSE of the 8x8 box-filtered images below 2 % of the mean."""
     # the Cornell box (small light, long paths) needs ~7e7 paths for a 3-sigma reading of 0.5 %
-    n, spp = (96, 1024) if name == "C1" else (64, 16384)
+    n, spp = (96, 1024) if name in ("C1", "C2") else (64, 16384)
     job = _small(ALL[name](), n, n, spp=spp)
     vp = job.viewport
     vp.gamma = 1.0
