@@ -277,9 +277,13 @@ def run_b200(args):
     lib = be.lib
     e2e_steps = args.e2e_steps or args.steps
 
+    e2e_trace = []
+
     def e2e_step():
         hd = C.c_void_p()
+        t_a = time.perf_counter()
         A.check(lib.rtw_scene_create(C.byref(fs.desc), local, C.byref(hd)))
+        e2e_trace.append(("create_ms", (time.perf_counter() - t_a) * 1e3))
         try:
             if world == 1:
                 o2 = vp.opts(job.ray_color, job.mode)
@@ -294,11 +298,14 @@ def run_b200(args):
                     be.resolve_device(buf.data_ptr(), H * W, spp, vp.gamma, stream)
                     host_out.copy_(buf, non_blocking=True)
                 torch.cuda.synchronize()
+            e2e_trace.append(("render_ms", (time.perf_counter() - t_a) * 1e3))
             inf = A.rtw_scene_info()
             A.check(lib.rtw_scene_get_info(hd, C.byref(inf)))
             return int(inf.device_bytes)
         finally:
+            t_b = time.perf_counter()
             lib.rtw_scene_destroy(hd)
+            e2e_trace.append(("destroy_ms", (time.perf_counter() - t_b) * 1e3))
 
     e2e_step()
     barrier(); torch.cuda.synchronize()
@@ -310,6 +317,8 @@ def run_b200(args):
     if world > 1:
         dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
     e2e_s = float(e2e_s.item())
+    if os.environ.get("RTW_BENCH_E2E_TRACE") and rank == 0:
+        print("e2e phases (cumulative ms within each step): " + " ".join(f"{k}={v:.1f}" for k, v in e2e_trace), file=sys.stderr)
 
     # ---- rank 0: algorithmic work per ray (instrumented kernel), roofline denominators, CPU baseline
     if rank == 0:

@@ -222,6 +222,11 @@ void rtw_render_opts_default(rtw_render_opts* o);   /* samples 1, depth 10, gamm
  * two-level SAH BVH on the host and uploads. */
 int  rtw_scene_create(const rtw_scene_desc* desc, int device, rtw_scene** out);
 void rtw_scene_destroy(rtw_scene* scene);
+/* Device and pinned memory of destroyed scenes is kept for the next rtw_scene_create / render on the
+ * same device (up to RTW_MEM_CACHE_MB, default 4096; 0 disables), so that a scene-per-frame loop
+ * (render_multi clones the scene per frame, viewport.rs:263) does not pay cudaMalloc / cudaFree of
+ * the path pool every frame. This gives the idle blocks back. `device` < 0 = every device. */
+int rtw_trim_memory(int device);
 
 /* Optional on-device BVH rebuild (BASELINE north_star; replaces AABB::new / QuadAABB::new /
  * IAABB::new, objects/aabb/aabb.rs:20-71, qaabb.rs:127-163, iaabb.rs:80-116, for callers that

@@ -105,6 +105,7 @@ SYMBOLS = {
     "rtw_render_opts_default": (None, [P(rtw_render_opts)]),
     "rtw_scene_create": (C.c_int, [P(rtw_scene_desc), C.c_int, P(C.c_void_p)]),
     "rtw_scene_destroy": (None, [C.c_void_p]),
+    "rtw_trim_memory": (C.c_int, [C.c_int]),
     "rtw_scene_rebuild_lbvh": (C.c_int, [C.c_void_p, P(f32)]),
     "rtw_scene_use_sah": (C.c_int, [C.c_void_p]),
     "rtw_render": (C.c_int, [C.c_void_p, P(rtw_camera), P(rtw_render_opts), C.c_void_p]),

@@ -126,6 +126,10 @@ class CudaBackend:
             scene._backend_cache[key] = h
         return h
 
+    def trim_memory(self) -> None:
+        """Give the device / pinned blocks cached from destroyed scenes back to the driver."""
+        A.check(self.lib.rtw_trim_memory(self.device))
+
     def microbench(self, which: int, reps: int = 3) -> float:
         """FP32 TFLOP/s / L2 GB/s / HBM GB/s of this device (roofline denominators)."""
         v = C.c_double()

@@ -5,8 +5,10 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 #include <new>
 #include <string>
+#include <unordered_map>
 #include <vector>
 #include "rtw_host.h"
 #include "rtw_kernels.h"
@@ -29,6 +31,144 @@ int cuda_fail(cudaError_t e, const char* what) {
         cudaError_t e__ = (call);                             \
         if (e__ != cudaSuccess) return cuda_fail(e__, #call); \
     } while (0)
+
+// Device and pinned memory of destroyed scenes is kept for the next one (per device, up to RTW_MEM_CACHE_MB,
+// default 4096). A caller that builds a scene per frame (render_multi clones the scene per frame,
+// viewport.rs:263) would otherwise pay cudaMalloc / cudaFree of the 0.5 GB path pool every frame, and those
+// calls serialise on a driver lock with anything else that touches the device: with an nvidia-smi poll running
+// beside the render, one rtw_scene_destroy in four stalled for 0.1-0.7 s (profiles/r1l_e2e_trace.txt).
+// rtw_trim_memory() gives the cached blocks back.
+struct MemCache {
+    struct Block { void* p; size_t bytes; int device; bool pinned; };
+    struct Tex { cudaArray_t arr; cudaTextureObject_t obj; uint32_t w, h; int device; size_t bytes; };   // float4 texels, point filter
+    std::mutex m;
+    std::vector<Block> idle;
+    std::vector<Tex> idle_tex;
+    std::unordered_map<void*, Block> live;
+    size_t held = 0;
+};
+MemCache& mem_cache() { static MemCache* c = new MemCache; return *c; }      // outlives the CUDA context teardown at exit
+size_t cache_limit() {
+    const char* e = std::getenv("RTW_MEM_CACHE_MB");
+    return (size_t)(e ? std::strtoull(e, nullptr, 10) : 4096ull) << 20;
+}
+size_t round_bytes(size_t b) {
+    if (b < 512u) b = 512u;
+    return b <= (1u << 20) ? (b + 511u) & ~(size_t)511u : (b + (2u << 20) - 1u) & ~(size_t)((2u << 20) - 1u);
+}
+void raw_free(const MemCache::Block& b) {
+    int cur = 0; cudaGetDevice(&cur);
+    if (cur != b.device) cudaSetDevice(b.device);
+    if (b.pinned) cudaFreeHost(b.p); else cudaFree(b.p);
+    if (cur != b.device) cudaSetDevice(cur);
+}
+void raw_free(const MemCache::Tex& t) {
+    int cur = 0; cudaGetDevice(&cur);
+    if (cur != t.device) cudaSetDevice(t.device);
+    cudaDestroyTextureObject(t.obj); cudaFreeArray(t.arr);
+    if (cur != t.device) cudaSetDevice(cur);
+}
+void trim_locked(MemCache& c, int device /* -1: all */) {
+    for (size_t i = 0; i < c.idle_tex.size();) {
+        if (device < 0 || c.idle_tex[i].device == device) { raw_free(c.idle_tex[i]); c.held -= c.idle_tex[i].bytes; c.idle_tex[i] = c.idle_tex.back(); c.idle_tex.pop_back(); }
+        else ++i;
+    }
+    for (size_t i = 0; i < c.idle.size();) {
+        if (device < 0 || c.idle[i].device == device) { raw_free(c.idle[i]); c.held -= c.idle[i].bytes; c.idle[i] = c.idle.back(); c.idle.pop_back(); }
+        else ++i;
+    }
+}
+cudaError_t cached_alloc(void** out, size_t bytes, bool pinned = false) {
+    MemCache& c = mem_cache();
+    int dev = 0; cudaGetDevice(&dev);
+    const size_t want = round_bytes(bytes);
+    std::lock_guard<std::mutex> lk(c.m);
+    size_t best = c.idle.size();
+    for (size_t i = 0; i < c.idle.size(); ++i) {
+        const MemCache::Block& b = c.idle[i];
+        if (b.device != dev || b.pinned != pinned || b.bytes < want || b.bytes > 2u * want) continue;
+        if (best == c.idle.size() || b.bytes < c.idle[best].bytes) best = i;
+    }
+    if (best != c.idle.size()) {
+        const MemCache::Block b = c.idle[best];
+        c.idle[best] = c.idle.back(); c.idle.pop_back();
+        c.held -= b.bytes;
+        c.live[b.p] = b;
+        *out = b.p;
+        return cudaSuccess;
+    }
+    void* p = nullptr;
+    cudaError_t e = pinned ? cudaMallocHost(&p, want) : cudaMalloc(&p, want);
+    if (e == cudaErrorMemoryAllocation) {        // give the cached blocks back and try once more
+        cudaGetLastError();
+        trim_locked(c, pinned ? -1 : dev);
+        e = pinned ? cudaMallocHost(&p, want) : cudaMalloc(&p, want);
+    }
+    if (e != cudaSuccess) return e;
+    c.live[p] = MemCache::Block{p, want, dev, pinned};
+    *out = p;
+    return cudaSuccess;
+}
+// The caller has made sure that nothing on the device still uses `p`.
+void cached_free(void* p) {
+    if (!p) return;
+    MemCache& c = mem_cache();
+    std::lock_guard<std::mutex> lk(c.m);
+    auto it = c.live.find(p);
+    if (it == c.live.end()) { cudaFree(p); return; }
+    const MemCache::Block b = it->second;
+    c.live.erase(it);
+    const size_t limit = cache_limit();
+    if (b.bytes > limit) { raw_free(b); return; }
+    c.idle.push_back(b); c.held += b.bytes;
+    while (c.held > limit && !c.idle.empty()) {  // oldest first
+        raw_free(c.idle.front()); c.held -= c.idle.front().bytes; c.idle.erase(c.idle.begin());
+    }
+}
+// A width x height float4 array with its point-sampling texture object, from the cache if one of that shape is idle.
+cudaError_t cached_texture(uint32_t w, uint32_t h, MemCache::Tex* out) {
+    MemCache& c = mem_cache();
+    int dev = 0; cudaGetDevice(&dev);
+    {
+        std::lock_guard<std::mutex> lk(c.m);
+        for (size_t i = 0; i < c.idle_tex.size(); ++i)
+            if (c.idle_tex[i].device == dev && c.idle_tex[i].w == w && c.idle_tex[i].h == h) {
+                *out = c.idle_tex[i];
+                c.held -= out->bytes;
+                c.idle_tex[i] = c.idle_tex.back(); c.idle_tex.pop_back();
+                return cudaSuccess;
+            }
+    }
+    MemCache::Tex t{}; t.w = w; t.h = h; t.device = dev; t.bytes = (size_t)w * h * sizeof(float4);
+    cudaChannelFormatDesc cd = cudaCreateChannelDesc<float4>();
+    cudaError_t e = cudaMallocArray(&t.arr, &cd, w, h);
+    if (e == cudaErrorMemoryAllocation) {
+        cudaGetLastError();
+        { std::lock_guard<std::mutex> lk(c.m); trim_locked(c, dev); }
+        e = cudaMallocArray(&t.arr, &cd, w, h);
+    }
+    if (e != cudaSuccess) return e;
+    cudaResourceDesc rd; std::memset(&rd, 0, sizeof rd);
+    rd.resType = cudaResourceTypeArray; rd.res.array.array = t.arr;
+    cudaTextureDesc td; std::memset(&td, 0, sizeof td);
+    td.addressMode[0] = td.addressMode[1] = cudaAddressModeClamp;
+    td.filterMode = cudaFilterModePoint; td.readMode = cudaReadModeElementType; td.normalizedCoords = 0;
+    if ((e = cudaCreateTextureObject(&t.obj, &rd, &td, nullptr)) != cudaSuccess) { cudaFreeArray(t.arr); return e; }
+    *out = t;
+    return cudaSuccess;
+}
+void cached_texture_release(const MemCache::Tex& t) {
+    MemCache& c = mem_cache();
+    std::lock_guard<std::mutex> lk(c.m);
+    if (c.held + t.bytes > cache_limit() || c.idle_tex.size() >= 256u) { raw_free(t); return; }
+    c.idle_tex.push_back(t); c.held += t.bytes;
+}
+template <class T> cudaError_t cached_alloc_t(T** out, size_t bytes, bool pinned = false) {
+    void* p = nullptr;
+    cudaError_t e = cached_alloc(&p, bytes, pinned);
+    *out = static_cast<T*>(p);
+    return e;
+}
 
 // viewport.rs:207-213 + :301 — mean over the samples, then powf(1/gamma) per channel, no clamp.
 __global__ void resolve_kernel(float* __restrict__ rgb, unsigned long long n_values, float total, float inv_gamma) {
@@ -108,8 +248,7 @@ struct rtw_scene {
     LbvhScratch lb_scratch;
     std::vector<HostScene::Enclosing> enclosing;
     std::vector<void*> allocs;
-    std::vector<cudaArray_t> arrays;
-    std::vector<cudaTextureObject_t> texobjs;
+    std::vector<MemCache::Tex> texs;
     rtw_scene_info info{};
     cudaStream_t stream = nullptr;        // used by rtw_render / rtw_render_frames
     cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev2 = nullptr;
@@ -137,21 +276,21 @@ struct rtw_scene {
 
     ~rtw_scene() {
         cudaSetDevice(device);
-        for (auto t : texobjs) cudaDestroyTextureObject(t);
-        for (auto a : arrays) cudaFreeArray(a);
-        for (auto p : allocs) cudaFree(p);
-        if (d_img) cudaFree(d_img);
-        if (lb_leaves_d) cudaFree(lb_leaves_d);
-        if (lb_nodes) cudaFree(lb_nodes);
-        if (lb_nodes16) cudaFree(lb_nodes16);
-        if (lb_out_d) cudaFree(lb_out_d);
-        if (d_wc) cudaFree(d_wc);
-        if (h_wc) cudaFreeHost(h_wc);
+        cudaDeviceSynchronize();          // the blocks below go back to the cache: nothing may still be using them
+        for (const auto& t : texs) cached_texture_release(t);
+        for (auto p : allocs) cached_free(p);
+        cached_free(d_img);
+        cached_free(lb_leaves_d);
+        cached_free(lb_nodes);
+        cached_free(lb_nodes16);
+        cached_free(lb_out_d);
+        cached_free(d_wc);
+        cached_free(h_wc);
         for (auto e : wf_ev) if (e) cudaEventDestroy(e);
         for (auto& t : wf_t) for (auto e : t) if (e) cudaEventDestroy(e);
-        if (d_ctr) cudaFree(d_ctr);
-        if (d_work) cudaFree(d_work);
-        if (h_ctr) cudaFreeHost(h_ctr);
+        cached_free(d_ctr);
+        cached_free(d_work);
+        cached_free(h_ctr);
         if (ev0) cudaEventDestroy(ev0);
         if (ev1) cudaEventDestroy(ev1);
         if (ev2) cudaEventDestroy(ev2);
@@ -165,7 +304,7 @@ template <class T>
 int upload(rtw_scene* s, const std::vector<T>& v, const T** out) {
     size_t bytes = std::max<size_t>(v.size(), 1) * sizeof(T);
     void* p = nullptr;
-    CK(cudaMalloc(&p, bytes));
+    CK(cached_alloc(&p, bytes));
     s->allocs.push_back(p);
     s->info.device_bytes += bytes;
     if (!v.empty()) CK(cudaMemcpy(p, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice));
@@ -185,22 +324,13 @@ int upload_scene(rtw_scene* s, HostScene& hs) {
         CK(cudaDeviceGetAttribute(&max_w, cudaDevAttrMaxTexture2DWidth, s->device));
         CK(cudaDeviceGetAttribute(&max_h, cudaDevAttrMaxTexture2DHeight, s->device));
         if ((int)t.width > max_w || (int)t.height > max_h) return fail(RTW_E_UNSUPPORTED, "texture exceeds the 2D texture limits");
-        cudaChannelFormatDesc cd = cudaCreateChannelDesc<float4>();
-        cudaArray_t arr = nullptr;
-        CK(cudaMallocArray(&arr, &cd, t.width, t.height));
-        s->arrays.push_back(arr);
+        MemCache::Tex ct{};
+        CK(cached_texture(t.width, t.height, &ct));
+        s->texs.push_back(ct);
         s->info.device_bytes += (uint64_t)t.n_texels * sizeof(float4);
-        CK(cudaMemcpy2DToArray(arr, 0, 0, hs.texels[i].data(), t.width * sizeof(float4), t.width * sizeof(float4),
+        CK(cudaMemcpy2DToArray(ct.arr, 0, 0, hs.texels[i].data(), t.width * sizeof(float4), t.width * sizeof(float4),
                                t.height, cudaMemcpyHostToDevice));
-        cudaResourceDesc rd; std::memset(&rd, 0, sizeof rd);
-        rd.resType = cudaResourceTypeArray; rd.res.array.array = arr;
-        cudaTextureDesc td; std::memset(&td, 0, sizeof td);
-        td.addressMode[0] = td.addressMode[1] = cudaAddressModeClamp;
-        td.filterMode = cudaFilterModePoint; td.readMode = cudaReadModeElementType; td.normalizedCoords = 0;
-        cudaTextureObject_t obj = 0;
-        CK(cudaCreateTextureObject(&obj, &rd, &td, nullptr));
-        s->texobjs.push_back(obj);
-        t.obj = obj;
+        t.obj = ct.obj;
     }
     Scene& d = s->d;
     if ((rc = upload(s, hs.nodes, &d.nodes))) return rc;
@@ -279,7 +409,7 @@ uint32_t env_u32(const char* name, uint32_t dflt) {
 template <class T>
 int pool_alloc(rtw_scene* s, T** p, size_t n) {
     void* q = nullptr;
-    CK(cudaMalloc(&q, n * sizeof(T)));
+    CK(cached_alloc(&q, n * sizeof(T)));
     s->allocs.push_back(q);
     s->info.device_bytes += n * sizeof(T);
     *p = static_cast<T*>(q);
@@ -308,8 +438,8 @@ int ensure_pool(rtw_scene* s, unsigned long long n_paths) {
         s->pool_allocated = cap;
     }
     if (!s->d_wc) {
-        CK(cudaMalloc(&s->d_wc, sizeof(WfCounters)));
-        CK(cudaMallocHost(&s->h_wc, 4 * sizeof(WfCounters)));
+        CK(cached_alloc_t(&s->d_wc, sizeof(WfCounters)));
+        CK(cached_alloc_t(&s->h_wc, 4 * sizeof(WfCounters), true));
         for (auto& e : s->wf_ev) CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
         for (auto& t : s->wf_t) for (auto& e : t) CK(cudaEventCreate(&e));
         CK(wf_extend_occupancy_fast(&s->occ_wf[0], s->smem_bytes));
@@ -345,7 +475,7 @@ int enqueue_wavefront(rtw_scene* s, const RenderParams& P, int variant, float* d
     {
         const bool events_rare = (unsigned long long)s->n_walked_instances * 16ull <= (unsigned long long)s->info.n_tlas_leaves;
         L.prim_w = std::max(1u, env_u32("RTW_WF_PRIM_W", events_rare ? 8u : 4u));
-        L.event_w = std::max(1u, env_u32("RTW_WF_EVENT_W", events_rare ? 16u : 4u));
+        L.event_w = std::max(1u, env_u32("RTW_WF_EVENT_W", events_rare ? 8u : 4u));   // (16 before one-sphere instances joined the event steps)
     }
     s->h_wc[0] = init;
     CK(cudaMemcpyAsync(s->d_wc, &s->h_wc[0], sizeof(WfCounters), cudaMemcpyHostToDevice, st));
@@ -457,8 +587,8 @@ int enqueue_render(rtw_scene* s, const rtw_camera* cam, const rtw_render_opts* o
 
 int ensure_img(rtw_scene* s, size_t floats) {
     if (s->d_img_floats >= floats) return RTW_OK;
-    if (s->d_img) { cudaFree(s->d_img); s->d_img = nullptr; s->d_img_floats = 0; }
-    CK(cudaMalloc(&s->d_img, floats * sizeof(float)));
+    if (s->d_img) { CK(cudaStreamSynchronize(s->stream)); cached_free(s->d_img); s->d_img = nullptr; s->d_img_floats = 0; }
+    CK(cached_alloc_t(&s->d_img, floats * sizeof(float)));
     s->d_img_floats = floats;
     return RTW_OK;
 }
@@ -530,9 +660,9 @@ int rtw_scene_create(const rtw_scene_desc* desc, int device, rtw_scene** out) {
     if ((ce = cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking)) != cudaSuccess) return bail(cuda_fail(ce, "stream"));
     if ((ce = cudaEventCreate(&s->ev0)) != cudaSuccess || (ce = cudaEventCreate(&s->ev1)) != cudaSuccess ||
         (ce = cudaEventCreate(&s->ev2)) != cudaSuccess) return bail(cuda_fail(ce, "events"));
-    if ((ce = cudaMalloc(&s->d_ctr, sizeof(Counters))) != cudaSuccess) return bail(cuda_fail(ce, "counters"));
-    if ((ce = cudaMalloc(&s->d_work, sizeof(uint32_t))) != cudaSuccess) return bail(cuda_fail(ce, "work counter"));
-    if ((ce = cudaMallocHost(&s->h_ctr, sizeof(Counters))) != cudaSuccess) return bail(cuda_fail(ce, "pinned counters"));
+    if ((ce = cached_alloc_t(&s->d_ctr, sizeof(Counters))) != cudaSuccess) return bail(cuda_fail(ce, "counters"));
+    if ((ce = cached_alloc_t(&s->d_work, sizeof(uint32_t))) != cudaSuccess) return bail(cuda_fail(ce, "work counter"));
+    if ((ce = cached_alloc_t(&s->h_ctr, sizeof(Counters), true)) != cudaSuccess) return bail(cuda_fail(ce, "pinned counters"));
     std::memset(s->h_ctr, 0, sizeof(Counters));
     *out = s;
     return RTW_OK;
@@ -627,13 +757,13 @@ int rtw_scene_rebuild_lbvh(rtw_scene* s, float* out_build_ms) {
     if (!s->lb_nodes) {
         // the node arrays grow once: SAH nodes stay in front (their references remain valid), the
         // rebuilt levels go behind them
-        CK(cudaMalloc(reinterpret_cast<void**>(&s->lb_nodes), n_total * sizeof(Node)));
-        CK(cudaMalloc(reinterpret_cast<void**>(&s->lb_nodes16), n_total * sizeof(Node16)));
+        CK(cached_alloc_t(&s->lb_nodes, n_total * sizeof(Node)));
+        CK(cached_alloc_t(&s->lb_nodes16, n_total * sizeof(Node16)));
         CK(cudaMemcpy(s->lb_nodes, s->d.nodes, (size_t)s->n_sah_nodes * sizeof(Node), cudaMemcpyDeviceToDevice));
         CK(cudaMemcpy(s->lb_nodes16, s->d.nodes16, (size_t)s->n_sah_nodes * sizeof(Node16), cudaMemcpyDeviceToDevice));
-        CK(cudaMalloc(reinterpret_cast<void**>(&s->lb_leaves_d), s->lb_leaves_h.size() * sizeof(LbvhLeaf)));
+        CK(cached_alloc_t(&s->lb_leaves_d, s->lb_leaves_h.size() * sizeof(LbvhLeaf)));
         CK(cudaMemcpy(s->lb_leaves_d, s->lb_leaves_h.data(), s->lb_leaves_h.size() * sizeof(LbvhLeaf), cudaMemcpyHostToDevice));
-        CK(cudaMalloc(reinterpret_cast<void**>(&s->lb_out_d), s->lb_levels.size() * sizeof(LbvhLevelOut)));
+        CK(cached_alloc_t(&s->lb_out_d, s->lb_levels.size() * sizeof(LbvhLevelOut)));
         s->info.device_bytes += n_total * (sizeof(Node) + sizeof(Node16)) + s->lb_leaves_h.size() * sizeof(LbvhLeaf);
         s->d.nodes = s->lb_nodes; s->d.nodes16 = s->lb_nodes16;
     }
@@ -695,16 +825,17 @@ int rtw_quantize(const float* rgb, uint8_t* rgb8, uint64_t n_values, int device)
     if (n_values == 0) return RTW_OK;
     if (device >= 0) CK(cudaSetDevice(device));
     float* d_in = nullptr; uint8_t* d_out = nullptr;
-    cudaError_t e = cudaMalloc(&d_in, n_values * sizeof(float));
+    cudaError_t e = cached_alloc_t(&d_in, n_values * sizeof(float));
     if (e != cudaSuccess) return cuda_fail(e, "cudaMalloc");
-    if ((e = cudaMalloc(&d_out, n_values)) != cudaSuccess) { cudaFree(d_in); return cuda_fail(e, "cudaMalloc"); }
+    if ((e = cached_alloc_t(&d_out, n_values)) != cudaSuccess) { cached_free(d_in); return cuda_fail(e, "cudaMalloc"); }
     e = cudaMemcpy(d_in, rgb, n_values * sizeof(float), cudaMemcpyHostToDevice);
     if (e == cudaSuccess) {
         quantize_kernel<<<grid_for(n_values, 256), 256>>>(d_in, d_out, n_values);
         e = cudaGetLastError();
     }
     if (e == cudaSuccess) e = cudaMemcpy(rgb8, d_out, n_values, cudaMemcpyDeviceToHost);
-    cudaFree(d_in); cudaFree(d_out);
+    else cudaDeviceSynchronize();
+    cached_free(d_in); cached_free(d_out);
     if (e != cudaSuccess) return cuda_fail(e, "rtw_quantize");
     return RTW_OK;
 }
@@ -733,12 +864,18 @@ int rtw_bilateral_filter(const uint8_t* rgb8, uint32_t width, uint32_t height, u
     const size_t n = (size_t)width * height * 3u;
     uint8_t* d_buf = nullptr; float* d_par = nullptr;
     cudaEvent_t e0 = nullptr, e1 = nullptr;
-    cudaError_t e = cudaMalloc(&d_buf, 2u * n + 256u);
+    cudaError_t e = cached_alloc_t(&d_buf, 2u * n + 256u);
     if (e != cudaSuccess) return cuda_fail(e, "cudaMalloc");
     uint8_t* d_out = d_buf + (n + 255u) / 256u * 256u;
     int rc = RTW_OK;
-    auto done = [&](int code) { cudaFree(d_buf); cudaFree(d_par); if (e0) cudaEventDestroy(e0); if (e1) cudaEventDestroy(e1); return code; };
-    if ((e = cudaMalloc(&d_par, 4 * sizeof(float))) != cudaSuccess) return done(cuda_fail(e, "cudaMalloc"));
+    auto done = [&](int code) {
+        cudaStreamSynchronize(nullptr);
+        cached_free(d_buf); cached_free(d_par);
+        if (e0) cudaEventDestroy(e0);
+        if (e1) cudaEventDestroy(e1);
+        return code;
+    };
+    if ((e = cached_alloc_t(&d_par, 4 * sizeof(float))) != cudaSuccess) return done(cuda_fail(e, "cudaMalloc"));
     if ((e = cudaEventCreate(&e0)) != cudaSuccess || (e = cudaEventCreate(&e1)) != cudaSuccess) return done(cuda_fail(e, "cudaEventCreate"));
     if ((e = cudaMemcpy(d_buf, rgb8, n, cudaMemcpyHostToDevice)) != cudaSuccess) return done(cuda_fail(e, "cudaMemcpy"));
     cudaEventRecord(e0, 0);
@@ -768,6 +905,13 @@ int rtw_render_rgb8(rtw_scene* scene, const rtw_camera* cam, const rtw_render_op
     CK(cudaMemcpyAsync(out_rgb8, d8, n_values, cudaMemcpyDeviceToHost, scene->stream));
     CK(cudaEventRecord(scene->ev2, scene->stream));
     CK(cudaStreamSynchronize(scene->stream));
+    return RTW_OK;
+}
+
+int rtw_trim_memory(int device) {
+    MemCache& c = mem_cache();
+    std::lock_guard<std::mutex> lk(c.m);
+    trim_locked(c, device);
     return RTW_OK;
 }
 

@@ -57,6 +57,8 @@ extern "C" {
     pub fn rtw_render_opts_default(o: *mut rtw_render_opts);
     pub fn rtw_scene_create(desc: *const rtw_scene_desc, device: c_int, out: *mut *mut rtw_scene) -> c_int;
     pub fn rtw_scene_destroy(scene: *mut rtw_scene);
+    /// Releases the device / pinned blocks kept from destroyed scenes (`device` < 0: every device).
+    pub fn rtw_trim_memory(device: c_int) -> c_int;
     pub fn rtw_render(scene: *mut rtw_scene, cam: *const rtw_camera, opts: *const rtw_render_opts, out_rgb: *mut f32) -> c_int;
     pub fn rtw_render_device(scene: *mut rtw_scene, cam: *const rtw_camera, opts: *const rtw_render_opts, d_out: *mut f32, stream: *mut c_void) -> c_int;
     pub fn rtw_render_frames(scene: *mut rtw_scene, cam: *const rtw_camera, opts: *const rtw_render_opts, first: u32, n: u32, out_rgb: *mut f32) -> c_int;

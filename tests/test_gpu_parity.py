@@ -169,3 +169,39 @@ def test_fast_kernels_converge_to_strict(name, cuda):
     box = lambda a: a.reshape(n // 8, 8, n // 8, 8, 3).mean(axis=(1, 3))
     rmse = float(np.sqrt(((box(f) - box(s)) ** 2).mean()))
     assert rmse < 0.02 * float(s.mean()) + 1e-3, f"{name}: box-filtered RMSE {rmse:.4g} vs mean {s.mean():.4g}"
+
+
+def test_scene_memory_reuse_is_invisible(cuda):
+    """rtw_scene_destroy keeps the device blocks for the next scene (rtw_trim_memory releases them): a render after
+    any number of create / render / destroy cycles of OTHER scenes equals the first one (up to the order of the
+    framebuffer's float adds) — nothing in the pipeline may depend on what a recycled block held."""
+    import ctypes as C
+    lib = cuda.lib
+
+    def one(job, flags):
+        vp = job.viewport
+        fs = job.scene.flatten()
+        cam = vp.camera(cuda)
+        o = vp.opts(job.ray_color, job.mode)
+        o.flags = flags
+        out = np.empty((cam.height, cam.width, 3), dtype=np.float32)
+        hd = C.c_void_p()
+        A.check(lib.rtw_scene_create(C.byref(fs.desc), cuda.device, C.byref(hd)))
+        try:
+            A.check(lib.rtw_render(hd, C.byref(cam), C.byref(o), out.ctypes.data_as(C.c_void_p)))
+        finally:
+            lib.rtw_scene_destroy(hd)
+        return out
+
+    c5 = lambda: _small(ALL["C5"](), 256, 256, spp=6)          # 393 216 paths: the wavefront pipeline and its pool
+    c4 = lambda: _small(ALL["C4_smoke"](), 300, 300, spp=4)
+    c2 = lambda: _small(ALL["C2"](), 200, 120, spp=2)          # the megakernel
+    for flags in (A.RTW_FLAG_STRICT_FP, 0):
+        A.check(lib.rtw_trim_memory(-1))
+        first = one(c5(), flags)
+        for other in (c4, c2, c4):
+            one(other(), flags)
+        again = one(c5(), flags)
+        assert np.allclose(first, again, rtol=1e-5, atol=1e-6, equal_nan=True)
+    A.check(lib.rtw_trim_memory(cuda.device))
+    assert np.allclose(one(c5(), 0), again, rtol=1e-5, atol=1e-6, equal_nan=True)
