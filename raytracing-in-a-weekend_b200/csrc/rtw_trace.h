@@ -491,7 +491,11 @@ RTW_HD void trav_one_sphere_instance(const TraceCtx& cx, uint32_t iref, Trav& T)
         if (dot(oc, oc) - s.w * s.w < 0.0f) return;
     }
 #endif
+    // (the fast build leaves out the two box tests: the box holds nothing but the sphere, whose own test
+    // has the same interval, and the parent node has just tested this box)
+#if !defined(RTW_FAST_NODES) || defined(RTW_NO_VOLSKIP)
     if (!slab_ray(lo, hi, o, d, inv, slow, cx.mint, T.t, tn)) return;
+#endif
     RTW_COUNT(cx, spheres);
     if (!sphere_t(c, s.w, o, d, a, cx.mint, T.t, t)) return;
     if (flags & INST_VOLUME) {
@@ -501,7 +505,9 @@ RTW_HD void trav_one_sphere_instance(const TraceCtx& cx, uint32_t iref, Trav& T)
         if (distance >= 0.0f) {
             V3 o2 = (o + d * t) + d * distance;
             float t2;
+#if !defined(RTW_FAST_NODES) || defined(RTW_NO_VOLSKIP)
             if (!slab_ray(lo, hi, o2, d, inv, slow, cx.mint, cx.maxt, tn)) return;
+#endif
             RTW_COUNT(cx, spheres);
             if (!sphere_t(c, s.w, o2, d, a, cx.mint, cx.maxt, t2)) return;
         }
