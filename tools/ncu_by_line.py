@@ -4,10 +4,11 @@ of the same cubin and sums executed instructions / stall samples per source line
     cuobjdump -xelf all build/kernels_fast.o                    # -> rtw_kernels.sm_100a.cubin
     nvdisasm --print-line-info-inline rtw_kernels.sm_100a.cubin > all.txt
     ncu -i rep.ncu-rep --page source --csv --launch-count 1 > k.csv
-    python tools/ncu_by_line.py k.csv all.txt wf_extend_kernel [outer|inner]
+    python tools/ncu_by_line.py k.csv all.txt wf_extend_kernel [outer|inner|inner@<kernel line>]
 
 `inner` keys by the innermost (file:line) of every instruction, `outer` by the line of the kernel's
-own file the instruction was inlined into (so a whole inlined call shows up as one row).
+own file the instruction was inlined into (so a whole inlined call shows up as one row);
+`inner@328` is `inner` restricted to what was inlined into line 328 of the kernel's file.
 """
 import csv
 import re
@@ -46,6 +47,10 @@ def load_listing(path, kernel):
 def main():
     csv_path, listing, kernel = sys.argv[1:4]
     mode = sys.argv[4] if len(sys.argv) > 4 else "outer"
+    only = None
+    if "@" in mode:
+        mode, at = mode.split("@")
+        only = int(at)
     lst = load_listing(listing, kernel)
     rows = list(csv.reader(open(csv_path)))
     hi = next(i for i, r in enumerate(rows) if r and r[0] == "Address")
@@ -58,6 +63,8 @@ def main():
     for r in body:
         off = int(r[0], 16) - base
         info = lst.get(off)
+        if only is not None and not (info and info[1][1] == only):
+            continue
         key = (info[0] if mode == "inner" else info[1]) if info else ("?", 0)
         vals = [int(r[ix["Instructions Executed"]] or 0), int(r[ix["Thread Instructions Executed"]] or 0),
                 int(r[ix["# Samples"]] or 0), int(r[ix["Warp Stall Sampling (Not-issued Samples)"]] or 0)]
@@ -66,7 +73,7 @@ def main():
             tot[k] += vals[k]
     print(f"total: warp-instr {tot[0]}  thread-instr {tot[1]}  avg lanes {tot[1] / max(1, tot[0]):.1f}  samples {tot[2]}")
     print(f"{'where':34s} {'warp-instr':>11s} {'%':>6s} {'lanes':>6s} {'samples':>8s} {'%':>6s} {'not-issued%':>11s}")
-    for key, v in sorted(agg.items(), key=lambda kv: -kv[1][2])[:60]:
+    for key, v in sorted(agg.items(), key=lambda kv: -kv[1][0 if only is not None else 2])[:60]:
         print(f"{key[0] + ':' + str(key[1]):34s} {v[0]:11d} {100 * v[0] / tot[0]:6.1f} {v[1] / max(1, v[0]):6.1f} {v[2]:8d} "
               f"{100 * v[2] / max(1, tot[2]):6.1f} {100 * v[3] / max(1, v[2]):11.1f}")
 
