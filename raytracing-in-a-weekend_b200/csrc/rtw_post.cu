@@ -2,8 +2,8 @@
 //
 //   1. gradient      one thread per interior pixel: |grad I| of the luminance (:75-85), to a scratch row-major array
 //   2. params        ONE warp: the reference accumulates that array in a single f32, in row-major order (:75-87);
-//                    f32 addition is not associative, so the sum is taken in exactly that order by one lane while
-//                    the other 31 stage the next 1024 values into shared memory. Then sigma_range/sigma_spatial.
+//                    f32 addition is not associative, so the sum has to be THAT sum: taken 1024 values at a time as
+//                    integers of the running sum's binade, exact (see post_params_kernel). Then sigma_range/sigma_spatial.
 //   3. weight table  exp(-inv_spatial * d2 - inv_range * (diff/255)^2) (:108-114) only depends on (|dx|, |dy|, |diff|):
 //                    (size+1)^2 * 256 entries, computed once in double and rounded to f32
 //   4. filter        one thread per (pixel, channel); walks the reference's window in the reference's order
@@ -19,7 +19,7 @@ namespace rtw {
 namespace {
 
 constexpr uint32_t kTableMaxSize = 64;    // (64+1)^2 KiB = 4.1 MiB of weights; larger windows evaluate exp in place
-constexpr uint32_t kChunk = 1024;         // gradient values staged per step of the ordered sum
+constexpr uint32_t kChunk = 1024;         // gradient values per group of the ordered sum
 
 __device__ __forceinline__ float post_intensity(const uint8_t* __restrict__ p) {       // postprocessing.rs:64-68
     const float r = __fdiv_rn(__fmul_rn(0.2989f, (float)p[0]), 255.0f);
@@ -41,32 +41,76 @@ __global__ void post_gradient_kernel(const uint8_t* __restrict__ img, uint32_t w
     }
 }
 
-// One warp. `grad` is padded to a multiple of kChunk floats (the padding is never added).
+// One warp takes the reference's f32 sum `for y { for x { gradient_sum += g } }` (:75-87) in the reference's order
+// without adding one value at a time. While the running sum S stays inside one binade [2^e, 2^(e+1)] it is an integer
+// I = S / u (u = 2^(e-23), 2^23 <= I <= 2^24) and fl(S + x) for x >= 0 is I + rint(x / u): unless x / u lies
+// exactly half-way between two integers (a tie, rounded to even: depends on I) no addend's rounding depends on
+// the sum so far, so a group of 1024 values adds as 1024 independent integers (one warp reduction), in any order. A group with a tie, with a value
+// that is not a finite non-negative number below 2^21 u, or whose total would leave the binade is added the plain
+// way, one __fadd_rn after the other in the reference's order (every lane computes the same sum): about one group per
+// binade. Checked against the sequential sum bit for bit (tests/test_postprocessing.py through avg_gradient).
+// `grad` is padded to whole groups; values past n count as +0, which changes neither form of the sum.
+__device__ __forceinline__ float4 post_load4(const float* __restrict__ grad, uint32_t e, uint32_t n) {
+    if (e + 3u < n) return *reinterpret_cast<const float4*>(grad + e);
+    float4 v;
+    v.x = e < n ? grad[e] : 0.0f; v.y = e + 1u < n ? grad[e + 1u] : 0.0f;
+    v.z = e + 2u < n ? grad[e + 2u] : 0.0f; v.w = 0.0f;
+    return v;
+}
+
 __global__ void post_params_kernel(const float* __restrict__ grad, uint32_t n, uint32_t w, uint32_t h, float* __restrict__ params) {
-    __shared__ float4 buf[kChunk / 4];
+    const uint32_t FULL = 0xFFFFFFFFu;
     const uint32_t lane = threadIdx.x;
-    const uint32_t n_chunks = (n + kChunk - 1u) / kChunk;
-    const float4* g4 = reinterpret_cast<const float4*>(grad);
-    float4 r[kChunk / 128];
-    if (n_chunks)
-        for (uint32_t k = 0; k < kChunk / 128; ++k) r[k] = g4[lane + 32u * k];
+    constexpr uint32_t K = kChunk / 128u;                          // float4 per lane and group
+    const uint32_t n_groups = (n + kChunk - 1u) / kChunk;
+    // lane l holds float4 j of a group = its values (j * 32 + l) * 4 .. + 3; two groups are in flight behind the
+    // one being added (a single warp has nothing else to hide the load latency with)
+    float4 x[K], x1[K], x2[K];
+#pragma unroll
+    for (uint32_t j = 0; j < K; ++j) {
+        x1[j] = post_load4(grad, (j * 32u + lane) * 4u, n);
+        x2[j] = post_load4(grad, kChunk + (j * 32u + lane) * 4u, n);
+    }
     float sum = 0.0f;
-    for (uint32_t c = 0; c < n_chunks; ++c) {
-        for (uint32_t k = 0; k < kChunk / 128; ++k) buf[lane + 32u * k] = r[k];
-        __syncwarp();
-        if (c + 1u < n_chunks)                                   // in flight while lane 0 adds
-            for (uint32_t k = 0; k < kChunk / 128; ++k) r[k] = g4[(size_t)(c + 1u) * (kChunk / 4) + lane + 32u * k];
-        if (lane == 0) {
-            const uint32_t left = n - c * kChunk, cnt = left < kChunk ? left : kChunk;
-            const float* f = reinterpret_cast<const float*>(buf);
-            uint32_t k = 0;
-            for (; k + 4u <= cnt; k += 4u) {
-                const float4 v = buf[k >> 2];
-                sum = __fadd_rn(sum, v.x); sum = __fadd_rn(sum, v.y); sum = __fadd_rn(sum, v.z); sum = __fadd_rn(sum, v.w);
-            }
-            for (; k < cnt; ++k) sum = __fadd_rn(sum, f[k]);
+    for (uint32_t g = 0; g < n_groups; ++g) {
+#pragma unroll
+        for (uint32_t j = 0; j < K; ++j) { x[j] = x1[j]; x1[j] = x2[j]; }
+        if (g + 2u < n_groups) {
+#pragma unroll
+            for (uint32_t j = 0; j < K; ++j) x2[j] = post_load4(grad, (g + 2u) * kChunk + (j * 32u + lane) * 4u, n);
         }
-        __syncwarp();
+        const uint32_t sb = __float_as_uint(sum), ex = (sb >> 23) & 0xFFu;
+        const bool binade_ok = ex > 23u && ex < 0xFEu;             // normal, and u = 2^(e-23) normal too
+        const float scale = __uint_as_float((277u - ex) << 23);    // 1 / u
+        const float unit = __uint_as_float((ex - 23u) << 23);      // u
+        const uint32_t I = (sb & 0x7FFFFFu) | 0x800000u;
+        uint32_t tot = 0u;
+        bool good = true;
+#pragma unroll
+        for (uint32_t j = 0; j < K; ++j) {
+            const float v[4] = {x[j].x, x[j].y, x[j].z, x[j].w};
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+                const float y = __fmul_rn(v[c], scale);            // exact: a power of two
+                const float t = __fadd_rn(y, 8388608.0f);          // y < 2^21: the mantissa of t is rint(y)
+                const float d = __fsub_rn(y, __fsub_rn(t, 8388608.0f));      // exact: y - rint(y)
+                good = good && (y >= 0.0f) && (y < 2097152.0f) && (fabsf(d) != 0.5f);   // 2^21: a group's total < 2^31
+                tot += __float_as_uint(t) & 0x7FFFFFu;
+            }
+        }
+        const uint32_t total = __reduce_add_sync(FULL, tot);
+        const bool all_good = __all_sync(FULL, good) != 0;
+        if (binade_ok && all_good && I + total <= 0x1000000u) {
+            sum = __fmul_rn((float)(I + total), unit);             // exact
+        } else {
+#pragma unroll
+            for (uint32_t j = 0; j < K; ++j)
+#pragma unroll 2
+                for (uint32_t l = 0; l < 32u; ++l) {
+                    sum = __fadd_rn(sum, __shfl_sync(FULL, x[j].x, l)); sum = __fadd_rn(sum, __shfl_sync(FULL, x[j].y, l));
+                    sum = __fadd_rn(sum, __shfl_sync(FULL, x[j].z, l)); sum = __fadd_rn(sum, __shfl_sync(FULL, x[j].w, l));
+                }
+        }
     }
     if (lane == 0) {                                              // postprocessing.rs:73,87-90
         const float spatial = ceilf(__fmul_rn(0.02f, __fsqrt_rn((float)(w * w + h * h))));

@@ -187,3 +187,34 @@ def test_gpu_bilateral_errors(cuda):
         cuda.bilateral_filter(img, 1, 0)
     with pytest.raises(A.RtwError):
         cuda.bilateral_filter(np.zeros((4, 4, 3), dtype=np.uint8), 1, 7)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("pattern", ["binary_noise", "stripes", "checker", "sparse", "ramp", "tall", "wide"])
+def test_gpu_ordered_gradient_sum_is_the_sequential_one(oracle, cuda, pattern):
+    """sigma_range comes from one f32 accumulated over the interior pixels in row-major order (postprocessing.rs:75-87).
+    The device takes that sum 1024 values at a time as integers of the running sum's binade (rtw_post.cu) and falls
+    back to plain adds on ties and binade changes: images with few distinct gradient values (many exact ties), long
+    runs of zeros, and extreme shapes must give the same bits as the sequential CPU sum."""
+    rng = np.random.default_rng(17)
+    h, w = 240, 320
+    if pattern == "binary_noise":
+        img = (rng.integers(0, 2, (h, w, 1), dtype=np.uint8) * 255).repeat(3, axis=2)
+    elif pattern == "stripes":
+        img = np.zeros((h, w, 3), dtype=np.uint8); img[:, ::4] = 128; img[:, 1::4] = 64
+    elif pattern == "checker":
+        yy, xx = np.mgrid[0:h, 0:w]; img = (((yy // 3 + xx // 5) % 2) * 200 + 20).astype(np.uint8)[..., None].repeat(3, axis=2)
+    elif pattern == "sparse":
+        img = np.full((h, w, 3), 10, dtype=np.uint8); img[rng.integers(0, h, 50), rng.integers(0, w, 50)] = 250
+    elif pattern == "ramp":
+        img = (np.arange(w, dtype=np.uint16)[None, :, None] * 255 // (w - 1)).astype(np.uint8).repeat(h, axis=0).repeat(3, axis=2)
+    elif pattern == "tall":
+        img = rng.integers(0, 256, (2000, 3, 3), dtype=np.uint8)
+    else:
+        img = rng.integers(0, 256, (3, 3000, 3), dtype=np.uint8)
+    img = np.ascontiguousarray(img)
+    oi, gi = {}, {}
+    want = oracle.bilateral_filter(img, 2, 0, oi)
+    got = cuda.bilateral_filter(img, 2, 0, gi)
+    assert np.float32(oi["avg_gradient"]).tobytes() == np.float32(gi["avg_gradient"]).tobytes()
+    assert np.array_equal(got, want)
