@@ -218,3 +218,67 @@ def test_gpu_ordered_gradient_sum_is_the_sequential_one(oracle, cuda, pattern):
     got = cuda.bilateral_filter(img, 2, 0, gi)
     assert np.float32(oi["avg_gradient"]).tobytes() == np.float32(gi["avg_gradient"]).tobytes()
     assert np.array_equal(got, want)
+
+
+# ----------------------------------------------------------------------------- the grouped ordered sum, modelled on the CPU
+def _f32_bits(f):
+    return int(np.float32(f).view(np.uint32))
+
+
+def _grouped_sum_model(xs: np.ndarray, group: int):
+    """rtw_post.cu post_params_kernel, statement for statement: the running f32 sum advances by a group's values as
+    integers of its binade when no value ties / is out of range and the total stays in the binade; otherwise the
+    group is added sequentially. Returns (sum, groups on the fast path, groups on the sequential path)."""
+    s = F(0.0)
+    fast = slow = 0
+    for g0 in range(0, len(xs), group):
+        grp = xs[g0:g0 + group]
+        sb = _f32_bits(s)
+        ex = (sb >> 23) & 0xFF
+        ok = 23 < ex < 0xFE
+        if ok:
+            scale = np.uint32((277 - ex) << 23).view(F)
+            unit = np.uint32((ex - 23) << 23).view(F)
+            i0 = (sb & 0x7FFFFF) | 0x800000
+            with np.errstate(all="ignore"):
+                y = (grp * scale).astype(F)
+                t = (y + F(8388608.0)).astype(F)
+                d = (y - (t - F(8388608.0)).astype(F)).astype(F)
+            good = bool(((y >= 0) & (y < F(2097152.0)) & (np.abs(d) != F(0.5))).all())
+            total = int((t.view(np.uint32) & np.uint32(0x7FFFFF)).astype(np.uint64).sum())
+            if good and i0 + total <= 0x1000000:
+                s = F(F(i0 + total) * unit)
+                fast += 1
+                continue
+        for x in grp:
+            s = F(s + x)
+        slow += 1
+    return s, fast, slow
+
+
+@pytest.mark.parametrize("kind", ["uniform", "ties", "zeros", "heavy_tail", "two_scales", "with_nan"])
+def test_grouped_ordered_sum_model_equals_sequential_sum(kind):
+    rng = np.random.default_rng(23)
+    took_fast = 0
+    with np.errstate(all="ignore"):
+        for trial in range(6):
+            n = int(rng.integers(1, 9000))
+            if kind == "uniform":
+                xs = (rng.random(n) * 1.5).astype(F)
+            elif kind == "ties":
+                xs = (rng.integers(0, 64, n) / 64.0).astype(F)
+            elif kind == "zeros":
+                xs = np.where(rng.random(n) < 0.7, 0.0, rng.random(n)).astype(F)
+            elif kind == "heavy_tail":
+                xs = (rng.random(n) ** 8 * 1e3).astype(F)
+            elif kind == "two_scales":
+                xs = (rng.random(n) * 1e-6).astype(F); xs[n // 2:] = rng.random(n - n // 2).astype(F)
+            else:
+                xs = rng.random(n).astype(F); xs[n // 3] = np.nan
+            want = F(0.0)
+            for x in xs:
+                want = F(want + x)
+            got, fast, slow = _grouped_sum_model(xs, int(rng.choice([32, 256, 1024])))
+            assert _f32_bits(got) == _f32_bits(want) or (np.isnan(got) and np.isnan(want))
+            took_fast += fast
+    assert took_fast > 0 or kind == "with_nan"
