@@ -58,59 +58,65 @@ __device__ __forceinline__ float4 post_load4(const float* __restrict__ grad, uin
     return v;
 }
 
-__global__ void post_params_kernel(const float* __restrict__ grad, uint32_t n, uint32_t w, uint32_t h, float* __restrict__ params) {
+constexpr uint32_t kSumK = kChunk / 128u;                         // float4 per lane and group
+
+// lane l holds float4 j of a group = its values (j * 32 + l) * 4 .. + 3
+__device__ __forceinline__ void post_load_group(float4 (&x)[kSumK], const float* __restrict__ grad, uint32_t g, uint32_t n,
+                                                uint32_t lane) {
+#pragma unroll
+    for (uint32_t j = 0; j < kSumK; ++j) x[j] = post_load4(grad, g * kChunk + (j * 32u + lane) * 4u, n);
+}
+
+__device__ __forceinline__ float post_add_group(float sum, const float4 (&x)[kSumK]) {
     const uint32_t FULL = 0xFFFFFFFFu;
-    const uint32_t lane = threadIdx.x;
-    constexpr uint32_t K = kChunk / 128u;                          // float4 per lane and group
-    const uint32_t n_groups = (n + kChunk - 1u) / kChunk;
-    // lane l holds float4 j of a group = its values (j * 32 + l) * 4 .. + 3; two groups are in flight behind the
-    // one being added (a single warp has nothing else to hide the load latency with)
-    float4 x[K], x1[K], x2[K];
+    const uint32_t sb = __float_as_uint(sum), ex = (sb >> 23) & 0xFFu;
+    const bool binade_ok = ex > 23u && ex < 0xFEu;                 // normal, and u = 2^(e-23) normal too
+    const float scale = __uint_as_float((277u - ex) << 23);        // 1 / u
+    const float unit = __uint_as_float((ex - 23u) << 23);          // u
+    const uint32_t I = (sb & 0x7FFFFFu) | 0x800000u;
+    uint32_t tot = 0u;
+    bool good = true;
 #pragma unroll
-    for (uint32_t j = 0; j < K; ++j) {
-        x1[j] = post_load4(grad, (j * 32u + lane) * 4u, n);
-        x2[j] = post_load4(grad, kChunk + (j * 32u + lane) * 4u, n);
+    for (uint32_t j = 0; j < kSumK; ++j) {
+        const float v[4] = {x[j].x, x[j].y, x[j].z, x[j].w};
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+            const float y = __fmul_rn(v[c], scale);                // exact: a power of two
+            const float t = __fadd_rn(y, 8388608.0f);              // y < 2^21: the mantissa of t is rint(y)
+            const float d = __fsub_rn(y, __fsub_rn(t, 8388608.0f));          // exact: y - rint(y)
+            good = good && (y >= 0.0f) && (y < 2097152.0f) && (fabsf(d) != 0.5f);       // 2^21: a group's total < 2^31
+            tot += __float_as_uint(t) & 0x7FFFFFu;
+        }
     }
-    float sum = 0.0f;
-    for (uint32_t g = 0; g < n_groups; ++g) {
+    const uint32_t total = __reduce_add_sync(FULL, tot);
+    const bool all_good = __all_sync(FULL, good) != 0;
+    if (binade_ok && all_good && I + total <= 0x1000000u) return __fmul_rn((float)(I + total), unit);   // exact
+#pragma unroll 1
+    for (uint32_t j = 0; j < kSumK; ++j) {
+        float4 xj = x[0];
 #pragma unroll
-        for (uint32_t j = 0; j < K; ++j) { x[j] = x1[j]; x1[j] = x2[j]; }
-        if (g + 2u < n_groups) {
-#pragma unroll
-            for (uint32_t j = 0; j < K; ++j) x2[j] = post_load4(grad, (g + 2u) * kChunk + (j * 32u + lane) * 4u, n);
-        }
-        const uint32_t sb = __float_as_uint(sum), ex = (sb >> 23) & 0xFFu;
-        const bool binade_ok = ex > 23u && ex < 0xFEu;             // normal, and u = 2^(e-23) normal too
-        const float scale = __uint_as_float((277u - ex) << 23);    // 1 / u
-        const float unit = __uint_as_float((ex - 23u) << 23);      // u
-        const uint32_t I = (sb & 0x7FFFFFu) | 0x800000u;
-        uint32_t tot = 0u;
-        bool good = true;
-#pragma unroll
-        for (uint32_t j = 0; j < K; ++j) {
-            const float v[4] = {x[j].x, x[j].y, x[j].z, x[j].w};
-#pragma unroll
-            for (int c = 0; c < 4; ++c) {
-                const float y = __fmul_rn(v[c], scale);            // exact: a power of two
-                const float t = __fadd_rn(y, 8388608.0f);          // y < 2^21: the mantissa of t is rint(y)
-                const float d = __fsub_rn(y, __fsub_rn(t, 8388608.0f));      // exact: y - rint(y)
-                good = good && (y >= 0.0f) && (y < 2097152.0f) && (fabsf(d) != 0.5f);   // 2^21: a group's total < 2^31
-                tot += __float_as_uint(t) & 0x7FFFFFu;
-            }
-        }
-        const uint32_t total = __reduce_add_sync(FULL, tot);
-        const bool all_good = __all_sync(FULL, good) != 0;
-        if (binade_ok && all_good && I + total <= 0x1000000u) {
-            sum = __fmul_rn((float)(I + total), unit);             // exact
-        } else {
-#pragma unroll
-            for (uint32_t j = 0; j < K; ++j)
+        for (uint32_t k = 1; k < kSumK; ++k) if (k == j) xj = x[k];
 #pragma unroll 2
-                for (uint32_t l = 0; l < 32u; ++l) {
-                    sum = __fadd_rn(sum, __shfl_sync(FULL, x[j].x, l)); sum = __fadd_rn(sum, __shfl_sync(FULL, x[j].y, l));
-                    sum = __fadd_rn(sum, __shfl_sync(FULL, x[j].z, l)); sum = __fadd_rn(sum, __shfl_sync(FULL, x[j].w, l));
-                }
+        for (uint32_t l = 0; l < 32u; ++l) {
+            sum = __fadd_rn(sum, __shfl_sync(FULL, xj.x, l)); sum = __fadd_rn(sum, __shfl_sync(FULL, xj.y, l));
+            sum = __fadd_rn(sum, __shfl_sync(FULL, xj.z, l)); sum = __fadd_rn(sum, __shfl_sync(FULL, xj.w, l));
         }
+    }
+    return sum;
+}
+
+__global__ void post_params_kernel(const float* __restrict__ grad, uint32_t n, uint32_t w, uint32_t h, float* __restrict__ params) {
+    const uint32_t lane = threadIdx.x;
+    const uint32_t n_groups = (n + kChunk - 1u) / kChunk;
+    // three groups in registers: one being added, two in flight behind it (a single warp has nothing else to hide
+    // the load latency with); values past n load as +0
+    float4 a[kSumK], b[kSumK], c[kSumK];
+    post_load_group(a, grad, 0u, n, lane); post_load_group(b, grad, 1u, n, lane); post_load_group(c, grad, 2u, n, lane);
+    float sum = 0.0f;
+    for (uint32_t g = 0; g < n_groups; g += 3u) {
+        sum = post_add_group(sum, a); post_load_group(a, grad, g + 3u, n, lane);
+        if (g + 1u < n_groups) { sum = post_add_group(sum, b); post_load_group(b, grad, g + 4u, n, lane); }
+        if (g + 2u < n_groups) { sum = post_add_group(sum, c); post_load_group(c, grad, g + 5u, n, lane); }
     }
     if (lane == 0) {                                              // postprocessing.rs:73,87-90
         const float spatial = ceilf(__fmul_rn(0.02f, __fsqrt_rn((float)(w * w + h * h))));
