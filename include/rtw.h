@@ -26,7 +26,7 @@
 extern "C" {
 #endif
 
-#define RTW_ABI_VERSION 1
+#define RTW_ABI_VERSION 2
 
 /* ---- error codes (negative; 0 = ok). The reference panics/unwraps instead (viewport.rs:242). */
 enum {
@@ -75,6 +75,9 @@ typedef struct rtw_sphere {
 
 /* ---- Quad (Rust/src/objects/quad.rs:8-20). normal/d/w are re-derived as quad.rs:93-105.
  *      `velocity` is stored and never read by the reference (quad.rs:37-81); kept for layout parity. */
+enum { RTW_SHAPE_PARALLELOGRAM = 0,    /* inside test alfa, beta in [0,1]        quad.rs:57-60 */
+       RTW_SHAPE_TRIANGLE      = 1 };  /* inside test alfa, beta >= 0, alfa+beta <= 1
+                                        * Rust2/src/objects/triangle.rs:107-113 */
 typedef struct rtw_quad {
     float    origin[3];
     float    u[3];
@@ -82,6 +85,10 @@ typedef struct rtw_quad {
     float    velocity[3];
     uint32_t mat_id;
     uint32_t tex_id;
+    uint32_t shape;                    /* RTW_SHAPE_*: a triangle is the half of the parallelogram next to
+                                        * `origin`; same normal/d/w (triangle.rs:36-47 = quad.rs:93-105),
+                                        * same texel rule; its leaf box spans the three corners and is at
+                                        * least 0.005 wide (triangle.rs:50-89) */
 } rtw_quad;
 
 /* ---- Instance (Rust/src/objects/instance.rs:28-39). An instance owns a range of the scene's

@@ -188,6 +188,9 @@ struct Quad {
     Vec3 normal;
     float d = 0.f;
     Vec3 w;
+    // Rust2/src/objects/triangle.rs in this object model: the same record (triangle.rs:36-47 =
+    // quad.rs:93-105) with the triangle's inside test and leaf box.
+    bool triangle = false;
 
     // quad.rs:85-106
     static Quad make(Vec3 origin, Vec3 u, Vec3 v, Material mat, Vec3 velocity, ImageTexture tex) {
@@ -209,7 +212,9 @@ struct Quad {
         Vec3 planar = point - origin;
         float alfa = w.dot(planar.cross(v));
         float beta = w.dot(u.cross(planar));
-        if (alfa < 0.0f || alfa > 1.0f || beta < 0.0f || beta > 1.0f) return std::nullopt;
+        if (triangle) {   // triangle.rs:107-113
+            if (alfa < 0.0f || beta < 0.0f || alfa + beta > 1.0f) return std::nullopt;
+        } else if (alfa < 0.0f || alfa > 1.0f || beta < 0.0f || beta > 1.0f) return std::nullopt;
         Hit h;
         h.t = t;
         h.normal = normal;
@@ -224,6 +229,20 @@ struct Quad {
     Box3 leaf_box() const {
         Vec3 op = origin + u + v, vc = origin + v, uc = origin + u;
         Box3 b;
+        if (triangle) {   // triangle.rs:50-89: three corners, each axis at least MIN_AABB_WIDTH wide
+            b.x = Interval{minf(vc.x, minf(uc.x, origin.x)), maxf(vc.x, maxf(uc.x, origin.x))};
+            b.y = Interval{minf(vc.y, minf(uc.y, origin.y)), maxf(vc.y, maxf(uc.y, origin.y))};
+            b.z = Interval{minf(vc.z, minf(uc.z, origin.z)), maxf(vc.z, maxf(uc.z, origin.z))};
+            const float MIN_AABB_WIDTH = 0.005f;
+            for (Interval* iv : {&b.x, &b.y, &b.z}) {
+                if (iv->max - iv->min < MIN_AABB_WIDTH) {
+                    float c = 0.5f * (iv->max + iv->min);
+                    iv->max = c + MIN_AABB_WIDTH * 0.5f;
+                    iv->min = c - MIN_AABB_WIDTH * 0.5f;
+                }
+            }
+            return b;
+        }
         b.x = Interval{minf(minf(op.x, vc.x), minf(uc.x, origin.x)), maxf(maxf(op.x, vc.x), maxf(uc.x, origin.x))};
         b.y = Interval{minf(minf(op.y, vc.y), minf(uc.y, origin.y)), maxf(maxf(op.y, vc.y), maxf(uc.y, origin.y))};
         b.z = Interval{minf(minf(op.z, vc.z), minf(uc.z, origin.z)), maxf(maxf(op.z, vc.z), maxf(uc.z, origin.z))};

@@ -63,7 +63,9 @@ int oracle_scene_create(const rtw_scene_desc* d, uint32_t build_seed, oracle_sce
     };
     auto mk_quad = [&](const rtw_quad& q, Quad& o) -> bool {
         if (q.mat_id >= d->n_materials || q.tex_id >= d->n_textures) return false;
+        if (q.shape > RTW_SHAPE_TRIANGLE) return false;
         o = Quad::make(v3(q.origin), v3(q.u), v3(q.v), to_mat(d->materials[q.mat_id]), v3(q.velocity), texs[q.tex_id]);
+        o.triangle = q.shape == RTW_SHAPE_TRIANGLE;
         return true;
     };
     if (d->n_top_spheres > d->n_spheres || d->n_top_quads > d->n_quads) return RTW_E_INVALID;

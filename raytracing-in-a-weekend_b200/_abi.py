@@ -12,12 +12,13 @@ import os
 HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("RTW_B200_LIB") or os.path.join(HERE, "csrc", "librtw_b200.so")   # env override: tuning builds
 
-RTW_ABI_VERSION = 1
+RTW_ABI_VERSION = 2
 
 # error codes
 RTW_OK, RTW_E_INVALID, RTW_E_CUDA, RTW_E_NOMEM, RTW_E_UNSUPPORTED = 0, -1, -2, -3, -4
 # density kinds (instance.rs:21-26)
 RTW_DENSITY_SURFACE, RTW_DENSITY_CONST = 0, 1
+RTW_SHAPE_PARALLELOGRAM, RTW_SHAPE_TRIANGLE = 0, 1
 # integrators
 RTW_INT_GRADIENT, RTW_INT_D, RTW_INT_BG_COLOR, RTW_INT_NORMAL, RTW_INT_ALBEDO, RTW_INT_GLASS_TEST = range(6)
 # modes
@@ -49,7 +50,7 @@ class rtw_sphere(C.Structure):
 
 
 class rtw_quad(C.Structure):
-    _fields_ = [("origin", f3), ("u", f3), ("v", f3), ("velocity", f3), ("mat_id", u32), ("tex_id", u32)]
+    _fields_ = [("origin", f3), ("u", f3), ("v", f3), ("velocity", f3), ("mat_id", u32), ("tex_id", u32), ("shape", u32)]
 
 
 class rtw_instance(C.Structure):

@@ -96,8 +96,13 @@ RTW_HD float u2f(uint32_t u) {
 enum : uint32_t { KIND_NODE = 0u, KIND_SPHERE = 1u, KIND_QUAD = 2u, KIND_INSTANCE = 3u };
 static const uint32_t REF_NONE = 0xFFFFFFFFu;
 RTW_HD uint32_t ref_kind(uint32_t r) { return r >> 30; }
-RTW_HD uint32_t ref_index(uint32_t r) { return r & 0x3FFFFFFFu; }
+RTW_HD uint32_t ref_index(uint32_t r) { return r & 0x1FFFFFFFu; }
 RTW_HD uint32_t make_ref(uint32_t kind, uint32_t idx) { return (kind << 30) | idx; }
+// The reference of a quad record whose inside test is the triangle's (alfa + beta <= 1,
+// Rust2/src/objects/triangle.rs:107-113) carries this bit, in search results too: shape is part of
+// the primitive's name, so the 64-byte record needs no seventeenth word. Indices stay below 2^29.
+static const uint32_t REF_TRIANGLE = 0x20000000u;
+static const uint32_t REF_INDEX_LIMIT = 0x10000000u;   // spheres, quads, instances, nodes: fewer than this
 // Inside the BVH (node children, traversal stack) the reference of an instance that holds exactly
 // one static sphere carries this bit, so that the walk can treat it as a primitive test rather than
 // a level change. Search results always carry the plain reference.

@@ -88,8 +88,10 @@ RTW_HD bool sphere_t(V3 c, float radius, V3 o, V3 d, float a, float mint, float 
 #endif
 }
 
-// Quad::collision_normal up to the inside test (quad.rs:38-60).
-RTW_HD bool quad_t(const Quad* qp, V3 o, V3 d, float mint, float maxt, float& t) {
+// Quad::collision_normal up to the inside test (quad.rs:38-60). `lim` bounds alfa + beta: 1 for a
+// triangle record (Rust2/src/objects/triangle.rs:107-113: `alfa + beta > 1.0` rejects; its upper bounds
+// on alfa and beta follow from the sum), 2 for a parallelogram, where it can never reject.
+RTW_HD bool quad_t(const Quad* qp, V3 o, V3 d, float mint, float maxt, float lim, float& t) {
     float4 q0 = RTW_LDG(&qp->q0), q1 = RTW_LDG(&qp->q1), q2 = RTW_LDG(&qp->q2), q3 = RTW_LDG(&qp->q3);
     V3 n = v3(q0.x, q0.y, q0.z);
     float den = dot(n, d);
@@ -102,7 +104,7 @@ RTW_HD bool quad_t(const Quad* qp, V3 o, V3 d, float mint, float maxt, float& t)
         const float al = dot(w, cross(planar, v));
         const float be = dot(w, cross(u, planar));
         t = tt;
-        return fabsf(den) > 1e-8f && tt >= mint && tt <= maxt && al >= 0.0f && al <= 1.0f && be >= 0.0f && be <= 1.0f;
+        return fabsf(den) > 1e-8f && tt >= mint && tt <= maxt && al >= 0.0f && al <= 1.0f && be >= 0.0f && be <= 1.0f && al + be <= lim;
     }
 #endif
     if (fabsf(den) <= 1e-8f) return false;
@@ -114,6 +116,7 @@ RTW_HD bool quad_t(const Quad* qp, V3 o, V3 d, float mint, float maxt, float& t)
     float al = dot(w, cross(planar, v));
     float be = dot(w, cross(u, planar));
     if (al < 0.0f || al > 1.0f || be < 0.0f || be > 1.0f) return false;
+    if (al + be > lim) return false;
     t = tt;
     return true;
 }
@@ -287,7 +290,7 @@ RTW_HD void trav_test_prim(const TraceCtx& cx, uint32_t ref, Trav& T) {
         hit = sphere_t(v3(s.x, s.y, s.z), s.w, T.o, T.d, T.a, cx.mint, T.t, t);
     } else {
         RTW_COUNT(cx, quads);
-        hit = quad_t(&sc.quads[idx], T.o, T.d, cx.mint, T.t, t);
+        hit = quad_t(&sc.quads[idx], T.o, T.d, cx.mint, T.t, (ref & REF_TRIANGLE) ? 1.0f : 2.0f, t);
     }
     if (hit && closer(t, ref, T.t, T.ref)) { T.t = t; T.ref = ref; }
 }

@@ -210,7 +210,7 @@ int build_host_scene(const rtw_scene_desc* d, HostScene& hs, std::string& err) {
         (d->n_materials && !d->materials) || (d->n_textures && !d->textures) || (d->n_noises && !d->noises)) {
         err = "null array with non-zero count"; return RTW_E_INVALID;
     }
-    if (d->n_spheres >= (1u << 30) || d->n_quads >= (1u << 30) || d->n_instances >= (1u << 28) - 2u) {
+    if (d->n_spheres >= REF_INDEX_LIMIT || d->n_quads >= REF_INDEX_LIMIT || d->n_instances >= REF_INDEX_LIMIT - 2u) {
         err = "too many primitives"; return RTW_E_UNSUPPORTED;
     }
     if ((d->n_spheres || d->n_quads) && (d->n_materials == 0 || d->n_textures == 0)) {
@@ -255,6 +255,7 @@ int build_host_scene(const rtw_scene_desc* d, HostScene& hs, std::string& err) {
     hs.spheres.resize(ns); hs.sphere_vel.resize(ns); hs.sphere_col.resize(ns); hs.sphere_ids.resize(ns);
     hs.sphere_box.resize(2 * (size_t)ns);
     std::vector<Box> sbox(ns), qbox(nq);
+    std::vector<uint32_t> qtri(nq);   // REF_TRIANGLE for triangle records, 0 otherwise
     std::vector<uint8_t> smoving(ns);
     for (uint32_t i = 0; i < ns; ++i) {
         const rtw_sphere& s = d->spheres[i];
@@ -290,16 +291,31 @@ int build_host_scene(const rtw_scene_desc* d, HostScene& hs, std::string& err) {
         o.q2 = make_float4(u.y, u.z, v.x, v.y);
         o.q3 = make_float4(v.z, w.x, w.y, w.z);
         hs.quad_ids[i] = make_uint2(q.mat_id, q.tex_id);
-        // qaabb.rs:19-61: box of the four corners, then pad() :107-126
+        if (q.shape > RTW_SHAPE_TRIANGLE) { err = "quad shape is neither parallelogram nor triangle"; return RTW_E_INVALID; }
+        const bool tri = q.shape == RTW_SHAPE_TRIANGLE;
+        qtri[i] = tri ? REF_TRIANGLE : 0u;
+        // qaabb.rs:19-61: box of the four corners, then pad() :107-126.
+        // Triangle (Rust2 triangle.rs:50-89): the three corners, each axis at least 0.005 wide about its middle.
         V3 op = Q + u + v, vc = Q + v, uc = Q + u;
         const float P4[4][3] = {{op.x, op.y, op.z}, {vc.x, vc.y, vc.z}, {uc.x, uc.y, uc.z}, {Q.x, Q.y, Q.z}};
         for (int a = 0; a < 3; ++a) {
-            float mn = minf(minf(P4[0][a], P4[1][a]), minf(P4[2][a], P4[3][a]));
-            float mx = maxf(maxf(P4[0][a], P4[1][a]), maxf(P4[2][a], P4[3][a]));
-            const float MIN_SIZE_DIR = 0.00001f;
-            if (mx - mn < MIN_SIZE_DIR) {
-                float center = (mx - mn) / 2.0f + mn;
-                mn = center - 0.5f * MIN_SIZE_DIR; mx = center + 0.5f * MIN_SIZE_DIR;
+            float mn, mx;
+            if (tri) {
+                mn = minf(P4[1][a], minf(P4[2][a], P4[3][a]));
+                mx = maxf(P4[1][a], maxf(P4[2][a], P4[3][a]));
+                const float MIN_AABB_WIDTH = 0.005f;
+                if (mx - mn < MIN_AABB_WIDTH) {
+                    float c = 0.5f * (mx + mn);
+                    mx = c + MIN_AABB_WIDTH * 0.5f; mn = c - MIN_AABB_WIDTH * 0.5f;
+                }
+            } else {
+                mn = minf(minf(P4[0][a], P4[1][a]), minf(P4[2][a], P4[3][a]));
+                mx = maxf(maxf(P4[0][a], P4[1][a]), maxf(P4[2][a], P4[3][a]));
+                const float MIN_SIZE_DIR = 0.00001f;
+                if (mx - mn < MIN_SIZE_DIR) {
+                    float center = (mx - mn) / 2.0f + mn;
+                    mn = center - 0.5f * MIN_SIZE_DIR; mx = center + 0.5f * MIN_SIZE_DIR;
+                }
             }
             qbox[i].lo[a] = mn; qbox[i].hi[a] = mx;
         }
@@ -314,7 +330,7 @@ int build_host_scene(const rtw_scene_desc* d, HostScene& hs, std::string& err) {
         if (smoving[i]) mov.push_back(i); else prims.push_back(make_prim(make_ref(KIND_SPHERE, i), sbox[i]));
     };
     for (uint32_t i = 0; i < d->n_top_spheres; ++i) add_sphere(i, top, top_moving);
-    for (uint32_t i = 0; i < d->n_top_quads; ++i) top.push_back(make_prim(make_ref(KIND_QUAD, i), qbox[i]));
+    for (uint32_t i = 0; i < d->n_top_quads; ++i) top.push_back(make_prim(make_ref(KIND_QUAD, i | qtri[i]), qbox[i]));
     uint32_t n_flat = 0, blas_nodes_before = 0;
     std::vector<std::pair<uint32_t, Box>> inst_leaves;
     std::vector<std::vector<uint32_t>> inst_moving(d->n_instances);
@@ -344,12 +360,12 @@ int build_host_scene(const rtw_scene_desc* d, HostScene& hs, std::string& err) {
             // An untransformed surface instance is exactly its primitives: rotated(0) and "- 0" are
             // identities in f32, so they join the top level (C5's 400 ground boxes).
             for (uint32_t i = 0; i < in.n_spheres; ++i) add_sphere(in.first_sphere + i, top, top_moving);
-            for (uint32_t i = 0; i < in.n_quads; ++i) top.push_back(make_prim(make_ref(KIND_QUAD, in.first_quad + i), qbox[in.first_quad + i]));
+            for (uint32_t i = 0; i < in.n_quads; ++i) top.push_back(make_prim(make_ref(KIND_QUAD, (in.first_quad + i) | qtri[in.first_quad + i]), qbox[in.first_quad + i]));
             ++n_flat;
             continue;
         }
         for (uint32_t i = 0; i < in.n_spheres; ++i) add_sphere(in.first_sphere + i, inst_prims[k], inst_moving[k]);
-        for (uint32_t i = 0; i < in.n_quads; ++i) inst_prims[k].push_back(make_prim(make_ref(KIND_QUAD, in.first_quad + i), qbox[in.first_quad + i]));
+        for (uint32_t i = 0; i < in.n_quads; ++i) inst_prims[k].push_back(make_prim(make_ref(KIND_QUAD, (in.first_quad + i) | qtri[in.first_quad + i]), qbox[in.first_quad + i]));
         // iaabb.rs:23-76: (qaabb box U saabb box); an empty inner BVH contributes [0,0] (aabb.rs:75-83)
         Box sb, qb;
         if (in.n_spheres) { sb = box_empty(); for (uint32_t i = 0; i < in.n_spheres; ++i) box_grow(sb, sbox[in.first_sphere + i]); }

@@ -196,9 +196,28 @@ class Quad:
         self.velocity = _v(velocity)   # stored, never read by the reference (quad.rs:13)
         self.texture = texture
 
+    shape = 0   # RTW_SHAPE_PARALLELOGRAM
+
     @staticmethod
     def new(origin, u, v, mat, velocity, texture) -> "Quad":  # quad.rs:85-106
         return Quad(origin, u, v, mat, velocity, texture)
+
+
+class Triangle(Quad):
+    """Rust2/src/objects/triangle.rs:11-48 in the Rust/src object model: the half of
+    the parallelogram (origin, u, v) next to `origin`. Same derived normal/d/w as a quad
+    (triangle.rs:36-47), inside test `alfa >= 0, beta >= 0, alfa + beta <= 1` (:107-113), leaf box
+    over the three corners padded to 0.005 (:50-89). It goes wherever a Quad goes: `Scene.new`'s and
+    `Instance.new_quads`' quad lists. Triangle has no velocity field (triangle.rs:16)."""
+
+    shape = 1   # RTW_SHAPE_TRIANGLE
+
+    def __init__(self, origin, u, v, mat: Material, texture: ImageTexture):
+        super().__init__(origin, u, v, mat, (0.0, 0.0, 0.0), texture)
+
+    @staticmethod
+    def new(origin, u, v, mat, texture) -> "Triangle":  # triangle.rs:27-48
+        return Triangle(origin, u, v, mat, texture)
 
 
 # --------------------------------------------------------------------------- instance.rs
@@ -364,6 +383,7 @@ class Scene:
             qd[i].velocity[:] = q.velocity.tolist()
             qd[i].mat_id = mat_id(q.mat)
             qd[i].tex_id = tex_id(q.texture)
+            qd[i].shape = q.shape
         ins_arr = (A.rtw_instance * max(1, len(self.instances)))()
         for i, (ins, rec) in enumerate(zip(self.instances, inst_rec)):
             ins_arr[i].first_sphere, ins_arr[i].n_spheres, ins_arr[i].first_quad, ins_arr[i].n_quads = rec

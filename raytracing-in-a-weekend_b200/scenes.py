@@ -22,7 +22,7 @@ import numpy as np
 from . import _abi as A
 from .philox import PhiloxStream
 from .scene import (EMPTY_M, FUZZY3_M, GLASS_M, GLASSR_M, METALLIC_M, SCATTER_M, ImageTexture, Instance,
-                    Material, PerlinNoise, Quad, Scene, Sphere, Vec3, const_density)
+                    Material, PerlinNoise, Quad, Scene, Sphere, Triangle, Vec3, const_density)
 from .viewport import (Viewport, ray_color_bg_color, ray_color_d, ray_color_glass_test, ray_color_gradient,
                        ray_color_normal)
 
@@ -420,6 +420,53 @@ def config_c5(width=800, height=800, samples=10000, depth=50, frame=0) -> Job:
     return Job("C5", sc, vp, ray_color_bg_color, A.RTW_MODE_RANDOM, "Next-Week final scene 800x800 10000spp d50")
 
 
+def triangle_test(width=400, height=300, samples=25, depth=2) -> Job:
+    """Rust2/src/objects/triangle.rs:149-199 `triangle_test`, in the Rust/src object model: one grey
+    lambertian triangle three units in front of the camera, background 0.6 white. Rust2's axes:
+    LEFT = +x, RIGHT = -x, FORWARD = +z (Rust2/src/vec3.rs:126-155). Rendered with ray_color_bg_color
+    (Rust2's ray_color returns the background where this one returns black at depth 0)."""
+    tri = Triangle.new(Vec3(1.0, -1.0, 3.0), Vec3(-1.0, 2.0, 0.0), Vec3(-2.0, 1.0, 0.0), SCATTER_M, _solid((0.5, 0.5, 0.5)))
+    sc = Scene.new([], [], [Instance.new_quads([tri])])
+    sc.background_color = Vec3(0.6, 0.6, 0.6)
+    vp = Viewport.new_from_res(width, height, samples, depth, 1.0, 50.0, Vec3(0.0, 0.0, 0.0), Vec3(0.0, 0.0, 1.0))
+    return Job("triangle", sc, vp, ray_color_bg_color, A.RTW_MODE_RANDOM)
+
+
+def triangle_mesh_test(samples=100, size=400) -> Job:
+    """Triangles everywhere a quad can stand (Rust2/src/objects/triangle.rs): at top level
+    (a textured one and the two halves of a split parallelogram), as a rotated four-face mesh instance,
+    as a one-triangle instance, and as the boundary of a constant-density volume, inside the room of
+    instance.rs:313-600."""
+    light = Quad.new(Vec3(-0.5, 1.99, 2.5), Vec3(1.0, 0.0, 0.0), Vec3(0.0, 0.0, 1.0),
+                     Material.new_emmiting(0.0, 0.0, 1.0, Vec3(6.0, 6.0, 6.0)), Z, _solid((1.0, 1.0, 1.0)))
+    back = Quad.new(Vec3(-2.0, -2.0, 0.999), Vec3(4.0, 0.0, 0.0), Vec3(0.0, 4.0, 0.0), SCATTER_M, Z, _solid((0.7, 0.7, 0.7)))
+    tex_tri = Triangle.new(Vec3(-1.9, -0.3, 1.2), Vec3(1.7, 0.1, 0.3), Vec3(0.2, 1.9, 0.1), SCATTER_M,
+                           checker_texture(64, 32, 8, 4))
+    half_a = Triangle.new(Vec3(0.3, 0.2, 1.4), Vec3(1.3, 0.1, 0.0), Vec3(0.1, 1.2, 0.2), SCATTER_M, _solid((0.9, 0.2, 0.2)))
+    # the other half of the same parallelogram: from the opposite corner, edges reversed
+    half_b = Triangle.new(Vec3(0.3 + 1.3 + 0.1, 0.2 + 0.1 + 1.2, 1.4 + 0.2), Vec3(-1.3, -0.1, 0.0), Vec3(-0.1, -1.2, -0.2),
+                          METALLIC_M, _solid((0.2, 0.9, 0.2)))
+
+    def tetra(scale, tex, mat):
+        a, b, c, d = (np.array(p, F) * F(scale) for p in ((0.0, 0.0, 0.0), (1.0, 0.0, 0.1), (0.4, 0.0, 0.9), (0.5, 1.1, 0.4)))
+        face = lambda p, q, r: Triangle.new(p, q - p, r - p, mat, tex)
+        return [face(a, c, b), face(a, b, d), face(b, c, d), face(c, a, d)]
+
+    mesh = Instance.new_quads(tetra(1.2, _solid((0.3, 0.4, 0.9)), SCATTER_M))
+    mesh.rotate(Vec3(0.0, PI / 5.0, 0.0))
+    mesh.translate(Vec3(-1.4, -1.9, 2.2))
+    single = Instance.new_quads([Triangle.new(Vec3(0.0, 0.0, 0.0), Vec3(0.9, 0.1, 0.0), Vec3(0.2, 0.0, 0.8), GLASS_M,
+                                              _solid((1.0, 1.0, 1.0)))])
+    single.translate(Vec3(0.6, -1.2, 2.6))
+    smoke = Instance.new_quads(tetra(1.5, _solid((0.8, 0.8, 0.8)), SCATTER_M))
+    smoke.translate(Vec3(0.2, -1.95, 1.3))
+    smoke.dist_fn = const_density
+    smoke.density = 1.5
+    ball = _albedo_sphere(Vec3(1.3, -1.5, 3.6), 0.4, (0.8, 0.6, 0.2), METALLIC_M)
+    sc = Scene.new([ball], _room_quads(light, [back, tex_tri, half_a, half_b]), [mesh, single, smoke])
+    return Job("triangle_mesh", sc, _room_viewport(samples, 20, size), ray_color_bg_color, A.RTW_MODE_RANDOM)
+
+
 CONFIGS: Dict[str, Callable[..., Job]] = {"C1": config_c1, "C2": config_c2, "C3": config_c3, "C4": config_c4,
                                           "C5": config_c5}
 
@@ -432,4 +479,5 @@ REFERENCE_TESTS: Dict[str, Callable[..., Job]] = {
     "reflection": reflection_test, "instance_box": lambda **k: instance_box_test(False, **k),
     "instance_box_rot": lambda **k: instance_box_test(True, **k), "volume": volume_test,
     "presentation": presentation_image, "first_frame": first_frame,
+    "triangle": triangle_test, "triangle_mesh": triangle_mesh_test,
 }

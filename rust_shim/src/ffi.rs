@@ -3,7 +3,7 @@
 #![allow(non_camel_case_types, dead_code)]
 use std::os::raw::{c_char, c_int, c_void};
 
-pub const RTW_ABI_VERSION: u32 = 1;
+pub const RTW_ABI_VERSION: u32 = 2;
 pub const RTW_OK: c_int = 0;
 
 #[repr(C)] #[derive(Clone, Copy)]
@@ -15,7 +15,9 @@ pub struct rtw_texture { pub width: u32, pub height: u32, pub rgb: *const f32, p
 #[repr(C)] #[derive(Clone, Copy)]
 pub struct rtw_sphere { pub origin: [f32; 3], pub radius: f32, pub col_mod: [f32; 3], pub velocity: [f32; 3], pub mat_id: u32, pub tex_id: u32 }
 #[repr(C)] #[derive(Clone, Copy)]
-pub struct rtw_quad { pub origin: [f32; 3], pub u: [f32; 3], pub v: [f32; 3], pub velocity: [f32; 3], pub mat_id: u32, pub tex_id: u32 }
+pub struct rtw_quad { pub origin: [f32; 3], pub u: [f32; 3], pub v: [f32; 3], pub velocity: [f32; 3], pub mat_id: u32, pub tex_id: u32, pub shape: u32 }
+pub const RTW_SHAPE_PARALLELOGRAM: u32 = 0;
+pub const RTW_SHAPE_TRIANGLE: u32 = 1;
 #[repr(C)] #[derive(Clone, Copy)]
 pub struct rtw_instance {
     pub first_sphere: u32, pub n_spheres: u32, pub first_quad: u32, pub n_quads: u32,

@@ -65,7 +65,7 @@ impl FlatScene {
     }
     fn quad(&mut self, q: &Quad) {
         let (mat_id, tex_id) = (self.material(&q.mat), self.texture(&q.texture));
-        self.quads.push(rtw_quad { origin: f3(q.origin), u: f3(q.u), v: f3(q.v), velocity: f3(q.velocity), mat_id, tex_id });
+        self.quads.push(rtw_quad { origin: f3(q.origin), u: f3(q.u), v: f3(q.v), velocity: f3(q.velocity), mat_id, tex_id, shape: RTW_SHAPE_PARALLELOGRAM });
     }
 
     /// Scene (viewport.rs:79-88) -> the arrays of rtw_scene_desc. Top-level primitives first, then

@@ -27,7 +27,7 @@ def _small(job, w, h, spp):
     return job
 
 
-@pytest.mark.parametrize("name", ["C2", "C4", "C5", "presentation"] if "presentation" in ALL else ["C2", "C4", "C5"])
+@pytest.mark.parametrize("name", ["C2", "C4", "C5", "presentation", "triangle_mesh"])
 def test_lbvh_steps_on_host_give_the_same_image(name):
     from emu_backend import EmuBackend
     sah, lbvh = EmuBackend(), EmuBackend(lbvh=True)
