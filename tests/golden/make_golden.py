@@ -1,6 +1,7 @@
 """Generates tests/golden/*.npz. Run in the build container (needs /root/reference for the C++ part):
 
-    python tests/golden/make_golden.py
+    python tests/golden/make_golden.py            # everything
+    python tests/golden/make_golden.py triangle_mesh   # only the named oracle_*.npz fixtures
 
   ref_cpp_*.npz   outputs of the REFERENCE'S OWN C++ renderer (oracle/_ref/libref_cpp.so, compiled
                   from /root/reference/C++): Render_no_rand images of sphere scenes in four modes
@@ -44,6 +45,9 @@ MODES = {"normal": (ref.MODE_NORMAL, 0.0, 1000.0), "t": (ref.MODE_T, 0.001, 1000
 
 
 def main():
+    only = sys.argv[1:]
+    if only:
+        return oracle_fixtures(only)
     if not ref.available():
         raise SystemExit("oracle/_ref/libref_cpp.so missing: run `make -C oracle ref` where /root/reference exists")
     for name, sc in SPHERE_SCENES.items():
@@ -61,11 +65,18 @@ def main():
                      [[1, 0, 0], r2, [np.cos(r2[2]), np.sin(r2[2]), 0.0]],
                      [[1, 0, 1], r2, [np.cos(r2[2]), np.sin(r2[2]), 1.0]]], dtype=np.float32)
     np.savez_compressed(os.path.join(HERE, "rotation_kats.npz"), kats=kats)
+    oracle_fixtures(None)
+
+
+def oracle_fixtures(only):
     # oracle regression fixtures
     orc = OracleBackend()
     reg = {"presentation": scenes.presentation_image, "volume": scenes.volume_test, "C3": scenes.config_c3,
-           "C4": scenes.config_c4, "C5": scenes.config_c5, "first_frame": scenes.first_frame}
+           "C4": scenes.config_c4, "C5": scenes.config_c5, "first_frame": scenes.first_frame,
+           "triangle_mesh": scenes.triangle_mesh_test}
     for name, f in reg.items():
+        if only and name not in only:
+            continue
         job = f()
         vp = job.viewport
         nv = type(vp).new_from_res(48, 36, 4, vp.depth, 1.0, vp.vfov, vp.origin, vp.direction, vp.vup, None, vp.lens_radius)

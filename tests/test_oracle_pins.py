@@ -183,12 +183,13 @@ def test_diffuse_never_flips_normals(oracle):
     assert a.hit == b.hit == 1 and tuple(a.normal[:]) == tuple(b.normal[:]) == (0.0, 0.0, 1.0)
 
 
-@pytest.mark.parametrize("name", ["presentation", "volume", "C3", "C4", "C5", "first_frame"])
+@pytest.mark.parametrize("name", ["presentation", "volume", "C3", "C4", "C5", "first_frame", "triangle_mesh"])
 def test_oracle_regression_fixtures(name, oracle):
     """The oracle today reproduces the committed oracle_*.npz (guards the checker itself)."""
     g = np.load(os.path.join(GOLD, f"oracle_{name}.npz"))
     f = {"presentation": scenes.presentation_image, "volume": scenes.volume_test, "C3": scenes.config_c3,
-         "C4": scenes.config_c4, "C5": scenes.config_c5, "first_frame": scenes.first_frame}[name]
+         "C4": scenes.config_c4, "C5": scenes.config_c5, "first_frame": scenes.first_frame,
+         "triangle_mesh": scenes.triangle_mesh_test}[name]
     job = f()
     vp = job.viewport
     nv = type(vp).new_from_res(48, 36, 4, vp.depth, 1.0, vp.vfov, vp.origin, vp.direction, vp.vup, None, vp.lens_radius)
