@@ -14,7 +14,8 @@ from .viewport import (Viewport, async_render, get_default_backend, ray_color_al
 
 from .write_img import quantize, write_img, write_img_f32
 from .postprocessing import Proximity, ProximityType, bilateral_filter
-from . import scene_json
+from . import driver, scene_json
+from .driver import dump_frames
 from .scene_json import ParseError
 
 __all__ = [n for n in dir() if not n.startswith("_")]

@@ -10,3 +10,7 @@ _spec = importlib.util.spec_from_file_location("rtw_b200", os.path.join(_dir, "_
 _mod = importlib.util.module_from_spec(_spec)
 sys.modules["rtw_b200"] = _mod
 _spec.loader.exec_module(_mod)
+
+if __name__ == "__main__":
+    from rtw_b200.driver import main
+    raise SystemExit(main())

@@ -47,6 +47,14 @@ def _worker(rank, world, port, outdir):
         tiles = sharding.render_tiles_sharded(job.viewport, job.ray_color, job.scene, job.mode, backend=be, band=8)
         anim = scenes.ltr_scene(samples=2, width=32, height=18, frames=5)
         frames = sharding.render_multi_sharded(anim.viewport, anim.ray_color, anim.scene, backend=be)
+        # main.rs:61-87 test_run on top of it: rank 0 alone writes frame 0 and the numbered frame dump
+        from rtw_b200 import driver
+        lines = []
+        video = driver.test_run(os.path.join(outdir, "First frame.png"), anim.viewport, anim.ray_color, anim.scene,
+                                backend=be, frames_dir=os.path.join(outdir, "video"), log=lines.append)
+        assert (video is None) == (rank != 0) and lines[0] == "Rendering {} samples".format(32 * 18 * 2 * 5)
+        if rank == 0:
+            assert all(np.array_equal(a, b, equal_nan=True) for a, b in zip(video, frames))
         if rank == 0:
             np.savez(os.path.join(outdir, "out.npz"), img=img, tiles=tiles, frames=np.stack(frames))
         else:
@@ -71,3 +79,10 @@ def test_world_size_2_gloo(tmp_path, oracle):
     h = oracle.scene(anim.scene)
     want = h.render_frames(anim.viewport.camera(oracle), anim.viewport.opts(anim.ray_color, A.RTW_MODE_RANDOM), 0, 5)
     assert np.array_equal(got["frames"], want, equal_nan=True)
+    from PIL import Image
+    names = sorted(os.listdir(os.path.join(str(tmp_path), "video")))
+    assert names == ["img0000%d.png" % k for k in range(5)]                    # main.rs:565
+    for k, n in enumerate(names):
+        png = np.asarray(Image.open(os.path.join(str(tmp_path), "video", n)))
+        assert np.array_equal(png, oracle.quantize(want[k]))
+    assert np.array_equal(np.asarray(Image.open(os.path.join(str(tmp_path), "First frame.png"))), oracle.quantize(want[0]))

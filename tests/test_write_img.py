@@ -5,6 +5,8 @@ CPU: the oracle restatement against hand-derived known answers of `(x*255).clamp
      `test_write` gradient (write_img.rs:36-57).
 GPU: rtw_quantize / rtw_render_rgb8 through the C ABI against the oracle, bit-exact.
 """
+import os
+
 import numpy as np
 import pytest
 
@@ -81,3 +83,56 @@ def test_gpu_render_rgb8_matches_quantized_render(name, oracle, cuda):
     got = vp.render_rgb8(rtw_b200.ray_color_albedo, job.scene, A.RTW_MODE_NO_RAND, cuda)
     assert (np.abs(got.astype(int) - ref.astype(int)) > 1).mean() < 2e-3
     assert (got != ref).mean() < 2e-2
+
+
+def test_driver_test_run_and_frame_dump(tmp_path, oracle):
+    """main.rs:61-87 `test_run` + the frame dump of main.rs:563-567, single process: the log lines, frame 0 in
+    `f_name`, every frame as img%05d.png, all quantised by write_img.rs:12-14."""
+    from PIL import Image
+    from rtw_b200 import driver, scenes
+    anim = scenes.ltr_scene(samples=2, width=32, height=18, frames=3)
+    anim.viewport.start_frame = 2
+    lines = []
+    f0 = str(tmp_path / "First frame.png")
+    video = driver.test_run(f0, anim.viewport, anim.ray_color, anim.scene, backend=oracle,
+                            frames_dir=str(tmp_path / "video"), log=lines.append)
+    assert len(video) == 3 and lines[0] == "Rendering %d samples" % (32 * 18 * 2 * 3)
+    assert lines[1].startswith("Finished\nElapsed time: ") and lines[1].endswith("num of frames: 3")
+    h = oracle.scene(anim.scene)
+    want = h.render_frames(anim.viewport.camera(oracle), anim.viewport.opts(anim.ray_color, A.RTW_MODE_RANDOM), 2, 3)
+    assert np.array_equal(np.stack(video), want, equal_nan=True)
+    assert not np.array_equal(want[0], want[1])                                # the spheres move between frames
+    assert sorted(os.listdir(tmp_path / "video")) == ["img00000.png", "img00001.png", "img00002.png"]
+    for k in range(3):
+        assert np.array_equal(np.asarray(Image.open(driver.frame_name(str(tmp_path / "video"), k))), oracle.quantize(want[k]))
+    assert np.array_equal(np.asarray(Image.open(f0)), oracle.quantize(want[0]))
+
+
+def test_driver_cli_needs_the_gpu_library():
+    """`python rtw_b200.py` == `cargo run` (main.rs:421-423); without a device it fails loudly, no CPU fallback."""
+    import subprocess, sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, os.path.join(root, "rtw_b200.py"), "--help"], capture_output=True, text=True)
+    assert r.returncode == 0 and "--frames-dir" in r.stdout
+    import rtw_b200
+    if rtw_b200.get_default_backend().device_count() == 0:
+        r = subprocess.run([sys.executable, os.path.join(root, "rtw_b200.py"), "triangle", "--samples", "1", "--out", os.devnull],
+                           capture_output=True, text=True)
+        assert r.returncode != 0 and "Traceback" in r.stderr
+
+
+@pytest.mark.gpu
+def test_gpu_driver_frame_dump(tmp_path, oracle, cuda):
+    """test_run on the device: frames = rtw_render_frames, files = rtw_quantize of them (byte-exact against
+    the oracle's write_img.rs:12-14)."""
+    from PIL import Image
+    from rtw_b200 import driver, scenes
+    anim = scenes.ltr_scene(samples=4, width=64, height=36, frames=3)
+    anim.viewport.flags = A.RTW_FLAG_STRICT_FP
+    video = driver.test_run(str(tmp_path / "f0.png"), anim.viewport, anim.ray_color, anim.scene, backend=cuda,
+                            frames_dir=str(tmp_path / "video"), log=lambda s: None)
+    h = cuda.scene(anim.scene)
+    want = h.render_frames(anim.viewport.camera(cuda), anim.viewport.opts(anim.ray_color, A.RTW_MODE_RANDOM), 0, 3)
+    assert np.array_equal(np.stack(video), want, equal_nan=True)
+    for k in range(3):
+        assert np.array_equal(np.asarray(Image.open(driver.frame_name(str(tmp_path / "video"), k))), oracle.quantize(want[k]))
