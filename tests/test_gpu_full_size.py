@@ -1,0 +1,79 @@
+"""Full-size properties (BASELINE.json's image sizes and scenes, where the CPU oracle cannot follow at full
+sample counts): composition of sample ranges and row bands — the two partitions the multi-GPU path is
+built from — path accounting, and agreement of the headline render with a strict-arithmetic
+render of the same scene that the sample-for-sample tests tie to the oracle."""
+import numpy as np
+import pytest
+
+from rtw_b200 import _abi as A, scenes
+
+pytestmark = pytest.mark.gpu
+
+
+def _lum(img):
+    return img @ np.array([0.2126, 0.7152, 0.0722], np.float32)
+
+
+@pytest.mark.parametrize("name,spp", [("C5", 16), ("C4", 16), ("C2", 8)])
+def test_sample_ranges_and_row_bands_compose_at_full_resolution(name, spp, cuda):
+    job = scenes.CONFIGS[name](samples=spp)
+    vp = job.viewport
+    h, cam = cuda.scene(job.scene), vp.camera(cuda)
+    W, H = cam.width, cam.height
+    o = vp.opts(job.ray_color, job.mode)
+    o.output = A.RTW_OUT_SUM
+    full = h.render(cam, o)
+    st = h.stats()
+    assert full.shape == (H, W, 3) and st.paths == W * H * spp and st.rays >= st.paths and st.gpu_launches >= 1
+    cut = spp // 2 + 1
+    o.sample_begin, o.sample_count = 0, cut
+    a = h.render(cam, o)
+    assert h.stats().paths == W * H * cut
+    o.sample_begin, o.sample_count = cut, spp - cut
+    b = h.render(cam, o)
+    fin = np.isfinite(full) & np.isfinite(a + b)
+    assert np.array_equal(np.isfinite(full), np.isfinite(a + b))
+    scale = float(np.abs(full[fin]).max())
+    assert np.all(np.abs((a + b)[fin] - full[fin]) <= 1e-5 * scale + 1e-4 * np.abs(full[fin]))   # f32 summation order only
+    # a band of rows is that slice of the frame (tiles: SURVEY 8e-B); 37 rows from an odd offset
+    o.sample_begin, o.sample_count, o.row_begin, o.row_count = 0, 0, 101, 37
+    band = h.render(cam, o)
+    assert band.shape == (37, W, 3) and h.stats().paths == W * 37 * spp
+    ref = full[101:138]
+    fin = np.isfinite(ref) & np.isfinite(band)
+    assert np.array_equal(np.isfinite(ref), np.isfinite(band))
+    assert np.all(np.abs(band[fin] - ref[fin]) <= 1e-5 * scale + 1e-4 * np.abs(ref[fin]))
+    # resolving the sum by hand is what RTW_OUT_RESOLVED returns (mean, then powf(1/gamma); viewport.rs:207-213,301)
+    o = vp.opts(job.ray_color, job.mode)
+    res = h.render(cam, o)
+    with np.errstate(invalid="ignore"):
+        want = np.power(full / np.float32(spp), np.float32(1.0 / vp.gamma), dtype=np.float32)
+    fin = np.isfinite(want) & np.isfinite(res)
+    assert (np.isfinite(want) == np.isfinite(res)).mean() > 0.9999
+    assert np.allclose(res[fin], want[fin], rtol=2e-4, atol=2e-5)
+
+
+def test_headline_frame_accounting_and_luminance(cuda):
+    """C5 as BASELINE.json states it (800x800, 10 000 spp, depth 50) with the default (fast) kernels: every
+    path is accounted for, and the frame's mean luminance is within 0.5 % (north_star's bound) of a
+    1024-spp render with the strict kernels, whose paths the parity tests compare with the oracle one by one."""
+    job = scenes.config_c5()
+    vp = job.viewport
+    assert (vp.width, vp.height, vp.samples, vp.depth) == (800, 800, 10000, 50)
+    vp.gamma = 1.0                                     # linear radiance: gamma would turn the Perlin sphere's negatives into NaN (N12)
+    img = vp._run(job.ray_color, job.scene, job.mode, cuda)
+    st = cuda.scene(job.scene).stats()
+    assert st.paths == 800 * 800 * 10000
+    assert 2.0 < st.rays / st.paths < 4.0              # 2.75 measured
+    assert st.nan_paths < 1e-6 * st.paths              # N8: ~1e-8 per diffuse bounce
+    vp.samples, vp.flags = 1024, A.RTW_FLAG_STRICT_FP
+    ref = vp._run(job.ray_color, job.scene, job.mode, cuda)
+    fin = np.isfinite(img).all(-1) & np.isfinite(ref).all(-1)
+    assert fin.mean() > 0.999                          # a NaN sample poisons its pixel (N8): a few dozen pixels at most
+    a, b = float(_lum(img[fin]).mean()), float(_lum(ref[fin]).mean())
+    assert abs(a / b - 1.0) < 5e-3, (a, b)
+    # and locally: 8x8 box means of the two frames differ by Monte-Carlo noise of the 1024-spp one only
+    # (median, so that a firefly box of the short render does not decide the test)
+    box = lambda x: np.where(fin, _lum(x), 0.0).reshape(100, 8, 100, 8).mean(axis=(1, 3))
+    med = float(np.median(np.abs(box(img) - box(ref))))
+    assert med < 0.03 * b + 1e-3, (med, b)
