@@ -77,3 +77,27 @@ def test_headline_frame_accounting_and_luminance(cuda):
     box = lambda x: np.where(fin, _lum(x), 0.0).reshape(100, 8, 100, 8).mean(axis=(1, 3))
     med = float(np.median(np.abs(box(img) - box(ref))))
     assert med < 0.03 * b + 1e-3, (med, b)
+
+
+@pytest.mark.parametrize("name", ["C1", "C2", "C3"])
+def test_converged_image_agrees_with_the_oracle(name, oracle, cuda):
+    """SURVEY 8d parity level L2 / north_star: the default (fast) kernels at 16 384 spp against the CPU
+    oracle at 4 096 spp, same scene and camera at 64x36, different arithmetic and sample streams: mean
+    luminance within 0.5 %, RMSE of the tone-mapped ([0,1]-clipped, gamma 2) images <= 0.02 (PSNR >= 34 dB),
+    pixels that are non-finite in either image (N8, N12) masked — and the same pixels must be masked
+    almost everywhere (the Perlin sphere's negative albedo is reference behaviour, not noise)."""
+    job = scenes.CONFIGS[name]()
+    vp = job.viewport
+    nv = type(vp).new_from_res(64, 36, 4096, vp.depth, vp.gamma, vp.vfov, vp.origin, vp.direction, vp.vup, None, vp.lens_radius)
+    nv.shutter_speed, nv.fps, nv.frame = vp.shutter_speed, vp.fps, vp.frame
+    ref = nv._run(job.ray_color, job.scene, job.mode, oracle)
+    nv.samples, nv.seed = 16384, 7
+    got = nv._run(job.ray_color, job.scene, job.mode, cuda)
+    fr, fg = np.isfinite(ref).all(-1), np.isfinite(got).all(-1)
+    assert (fr == fg).mean() > 0.97
+    fin = fr & fg
+    assert fin.mean() > 0.8
+    a, b = float(_lum(got[fin]).mean()), float(_lum(ref[fin]).mean())
+    assert abs(a / b - 1.0) < 5e-3, (a, b)
+    rmse = float(np.sqrt(((np.clip(got[fin], 0.0, 1.0) - np.clip(ref[fin], 0.0, 1.0)) ** 2).mean()))
+    assert rmse <= 0.02 and 20.0 * np.log10(1.0 / max(rmse, 1e-9)) >= 34.0, rmse
