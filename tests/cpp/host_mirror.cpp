@@ -4,6 +4,7 @@
 // compares the flattened rtw_scene_desc / rtw_camera / rtw_render_opts with the Python mirror's
 // (CPU) and the rendered images (GPU). Links only librtw_b200.so.
 #include "../../include/rtw.hpp"
+#include "../../include/rtw_json.hpp"
 
 using namespace rtw;
 
@@ -88,6 +89,7 @@ static JobCpp mixed(size_t width, size_t height, size_t samples) {
 static JobCpp make(int which, uint32_t w, uint32_t h, uint32_t spp) { return which == 0 ? cornell_smoke(w, h, spp) : mixed(w, h, spp); }
 
 static std::unique_ptr<FlatScene> g_flat;   // keeps the last flattened scene alive for the caller
+static std::string g_text;
 
 extern "C" {
 // Flatten scene `which` with the C++ mirror; the pointer stays valid until the next call.
@@ -112,5 +114,20 @@ int hm_render(int which, uint32_t w, uint32_t h, uint32_t spp, uint32_t flags, f
         if (out8) { auto q = quantize(img); std::memcpy(out8, q.data(), q.size()); }
         return 0;
     } catch (const Error& e) { return e.code; }
+}
+// The JSON wire format (include/rtw_json.hpp): text of the sphere list of scene 1 ...
+const char* hm_json_dumps(void) {
+    JobCpp j = mixed(8, 8, 1);
+    g_text = json::dumps(Scene::new_sphere(j.scene.spheres));
+    return g_text.c_str();
+}
+// ... and a scene that came in as text, flattened. NULL + *parse_error = 1 on a ParseError.
+const rtw_scene_desc* hm_json_flatten(const char* text, int* parse_error) {
+    *parse_error = 0;
+    try {
+        g_flat = json::loads(text).flatten();
+        return &g_flat->desc;
+    } catch (const json::ParseError&) { *parse_error = 1; return nullptr; }
+      catch (const std::exception&) { return nullptr; }
 }
 }

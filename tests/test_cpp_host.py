@@ -27,7 +27,7 @@ F = np.float32
 
 def build_host_mirror() -> str:
     path = os.path.join(CPP, "libhost_mirror.so")
-    srcs = [os.path.join(CPP, "host_mirror.cpp"), os.path.join(ROOT, "include", "rtw.hpp"), os.path.join(ROOT, "include", "rtw.h")]
+    srcs = [os.path.join(CPP, "host_mirror.cpp")] + [os.path.join(ROOT, "include", f) for f in ("rtw.hpp", "rtw_json.hpp", "rtw.h")]
     if not os.path.exists(path) or any(os.path.getmtime(s) > os.path.getmtime(path) for s in srcs):
         subprocess.check_call(["g++", "-std=c++17", "-O1", "-Wall", "-Wextra", "-Werror", "-ffp-contract=off", "-fPIC", "-shared",
                                "-o", path, os.path.join(CPP, "host_mirror.cpp"), "-L" + CSRC, "-lrtw_b200",
@@ -43,6 +43,9 @@ def hm():
     lib.hm_flatten.argtypes = [C.c_int, C.c_uint32, C.c_uint32, C.c_uint32, C.POINTER(A.rtw_camera), C.POINTER(A.rtw_render_opts)]
     lib.hm_render.restype = C.c_int
     lib.hm_render.argtypes = [C.c_int, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.c_void_p, C.c_void_p]
+    lib.hm_json_dumps.restype = C.c_char_p
+    lib.hm_json_flatten.restype = C.POINTER(A.rtw_scene_desc)
+    lib.hm_json_flatten.argtypes = [C.c_char_p, C.POINTER(C.c_int)]
     return lib
 
 
@@ -126,11 +129,56 @@ def test_cpp_and_python_mirrors_flatten_identically(which, hm, oracle):
         assert d.n_noises == 1 and d.n_instances == 2 and [d.quads[i].shape for i in range(d.n_quads)] == [1, 0, 0]
 
 
+def _same_desc(d, p):
+    assert (d.n_spheres, d.n_top_spheres, d.n_quads, d.n_instances, d.n_materials, d.n_textures, d.n_noises) == \
+           (p.n_spheres, p.n_top_spheres, p.n_quads, p.n_instances, p.n_materials, p.n_textures, p.n_noises)
+    assert _bytes(d.spheres, d.n_spheres, A.rtw_sphere) == _bytes(p.spheres, p.n_spheres, A.rtw_sphere)
+    assert _bytes(d.materials, d.n_materials, A.rtw_material) == _bytes(p.materials, p.n_materials, A.rtw_material)
+    for i in range(d.n_textures):
+        a, b = d.textures[i], p.textures[i]
+        assert (a.width, a.height, a.noise_id, a.noise_scale) == (b.width, b.height, b.noise_id, b.noise_scale)
+        n = a.width * a.height * 3
+        assert C.string_at(C.cast(a.rgb, C.c_void_p), 4 * n) == C.string_at(C.cast(b.rgb, C.c_void_p), 4 * n)
+
+
+def test_json_wire_format_crosses_between_the_cpp_and_python_mirrors(hm):
+    """include/rtw_json.hpp and scene_json.py restate the same Into / TryFrom<JsonValue> impls (sphere.rs:44-90,
+    viewport.rs:174-205): each reads the other's text and arrives at the same flattened scene; what the format
+    drops (noise, emission, quads, instances) is dropped on both sides; a missing field is a ParseError."""
+    import json as pyjson
+    from rtw_b200 import scene_json
+    err = C.c_int(0)
+    py_scene = Scene.new_sphere(mixed_scene(8, 8, 1).scene.spheres)
+    # Python text -> C++
+    text = scene_json.dumps(py_scene)
+    dp = hm.hm_json_flatten(text.encode(), C.byref(err))
+    assert dp and err.value == 0
+    want = scene_json.loads(text).flatten()
+    _same_desc(dp.contents, want.desc)
+    assert dp.contents.n_noises == 0 and dp.contents.n_spheres == 7          # the Perlin table does not travel (texture.rs:28-59)
+    # C++ text -> Python -> and back into C++
+    ctext = hm.hm_json_dumps().decode()
+    back = scene_json.loads(ctext)
+    assert scene_json.scene_eq(back, py_scene) and len(back.spheres) == 7
+    assert list(pyjson.loads(ctext)["spheres"][0]) == ["origin", "radius", "col_mod", "material", "velocity", "texture"]   # sphere.rs:46-53
+    dp = hm.hm_json_flatten(ctext.encode(), C.byref(err))
+    assert dp and err.value == 0
+    _same_desc(dp.contents, back.flatten().desc)
+    _same_desc(dp.contents, want.desc)                                          # nine digits round-trip every f32
+    # errors: the reference's TryFrom fails as a whole
+    obj = pyjson.loads(text)
+    del obj["spheres"][2]["velocity"]
+    for bad in (pyjson.dumps(obj), text[:-1], "{}", '{"spheres": 3}', text.replace('"radius":0.5', '"radius":"0.5"', 1)):
+        assert not hm.hm_json_flatten(bad.encode(), C.byref(err)) and err.value == 1, bad[:60]
+        with pytest.raises(scene_json.ParseError):
+            scene_json.loads(bad)
+
+
 def test_header_compiles_standalone_and_refuses_without_a_device(hm):
     """rtw.hpp is self-contained (g++ -fsyntax-only, -Wall -Wextra -Werror) and has no CPU path: without a
     device a render through it reports the library's RTW_E_CUDA."""
     subprocess.check_call(["g++", "-std=c++17", "-fsyntax-only", "-Wall", "-Wextra", "-Werror", "-x", "c++",
-                           os.path.join(ROOT, "include", "rtw.hpp")])
+                           os.path.join(ROOT, "include", "rtw_json.hpp")])
     if rtw_b200.get_default_backend().device_count() == 0:
         out = np.zeros((8, 8, 3), F)
         assert hm.hm_render(1, 8, 8, 1, 0, out.ctypes.data_as(C.c_void_p), None) == A.RTW_E_CUDA
