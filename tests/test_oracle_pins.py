@@ -201,3 +201,60 @@ def test_oracle_regression_fixtures(name, oracle):
     fin = np.isfinite(g["path4spp"])
     assert np.array_equal(np.isfinite(got), fin)
     assert np.allclose(got[fin], g["path4spp"][fin], rtol=1e-5, atol=1e-6)
+
+
+def _box8(img01):
+    h, w, _ = img01.shape
+    return img01.reshape(h // 8, 8, w // 8, 8, 3).mean(axis=(1, 3))
+
+
+def _against_shipped_render(name, img_u8):
+    """Statistics of an 8-bit render against the fixture made from the reference's own shipped PNG."""
+    g = np.load(os.path.join(GOLD, f"ref_rust_{name}.npz"))
+    a = img_u8.astype(np.float32) / np.float32(255.0)
+    k = 400 // a.shape[0]                                   # the fixture is 8x8 boxes of 400x400: same footprint at 400/k
+    box = a.reshape(a.shape[0] // (8 // k), 8 // k, a.shape[1] // (8 // k), 8 // k, 3).mean(axis=(1, 3))
+    rmse = float(np.sqrt(((box - g["box8"]) ** 2).mean()))
+    return rmse, float(a.mean() / g["mean"].mean()), np.abs(a.mean(axis=(0, 1)) - g["mean"]).max(), float((a.sum(-1) == 0).mean()), float(g["black_fraction"])
+
+
+def test_oracle_reproduces_the_reference_first_frame_png(oracle):
+    """The only outputs of the reference's Rust renderer that exist are the PNGs it ships. `Rust/First frame.png`
+    (main.rs:427-561 through test_run: four spheres, ray_color_d, gamma 2) against the oracle's render of the
+    same scene and viewport with its own sample stream: channel means within 0.005, mean luminance within 1 %,
+    8x8 box-filtered RMSE below 0.01 (fixture: tests/golden/make_reference_images.py)."""
+    job = scenes.first_frame(samples=32)
+    rmse, ratio, dmean, black, black_ref = _against_shipped_render("first_frame", oracle.quantize(job.render(oracle)))
+    assert rmse < 0.01 and abs(ratio - 1.0) < 0.01 and dmean < 0.005, (rmse, ratio, dmean)
+    assert black == black_ref == 0.0
+
+
+def test_oracle_reproduces_the_reference_presentation_png(oracle):
+    """`Rust/Presentation.png` — what `cargo run` writes (main.rs:89-419: room of quads, rotated box instance,
+    constant-density volume, glass and metal spheres, emissive quad, ray_color_bg_color, 2500 spp) — against
+    the oracle at 200x200, 256 spp: mean luminance within 1 % (0.9992 measured), box-filtered RMSE below 0.03
+    (0.019; the fixture's 8x8 boxes against 4x4 boxes at half resolution), and the same sprinkling of
+    NaN-poisoned black pixels (1.7e-4 of the reference's pixels)."""
+    job = scenes.presentation_image(samples=256, size=200)
+    rmse, ratio, dmean, black, black_ref = _against_shipped_render("presentation", oracle.quantize(job.render(oracle)))
+    assert rmse < 0.03 and abs(ratio - 1.0) < 0.01 and dmean < 0.01, (rmse, ratio, dmean)
+    assert 0.0 < black_ref < 1e-3 and black < 2e-3
+
+
+@pytest.mark.gpu
+def test_gpu_reproduces_the_reference_presentation_png(oracle, cuda):
+    """The product against the reference's own output: `presentation_image()` exactly as main.rs:89-419 runs it
+    (400x400, 2500 spp, depth and gamma as there) on the device with the default kernels, quantised by
+    rtw_quantize, against `Rust/Presentation.png`: mean luminance within 0.5 %, box-filtered RMSE below 0.01."""
+    job = scenes.presentation_image()
+    assert (job.viewport.width, job.viewport.height, job.viewport.samples) == (400, 400, 2500)
+    img8 = job.viewport.render_rgb8(job.ray_color, job.scene, job.mode, cuda)
+    rmse, ratio, dmean, black, black_ref = _against_shipped_render("presentation", img8)
+    print(f"presentation vs Rust/Presentation.png: box rmse {rmse:.5f} lum ratio {ratio:.5f} dmean {dmean:.5f} black {black:.2e} (ref {black_ref:.2e})")
+    assert rmse < 0.01 and abs(ratio - 1.0) < 5e-3 and dmean < 0.005, (rmse, ratio, dmean)
+    assert black < 2e-3
+    job = scenes.first_frame()
+    img8 = job.viewport.render_rgb8(job.ray_color, job.scene, job.mode, cuda)
+    rmse, ratio, dmean, black, _ = _against_shipped_render("first_frame", img8)
+    print(f"first_frame vs Rust/First frame.png: box rmse {rmse:.5f} lum ratio {ratio:.5f} dmean {dmean:.5f}")
+    assert rmse < 0.01 and abs(ratio - 1.0) < 5e-3 and dmean < 0.005 and black == 0.0, (rmse, ratio, dmean)
