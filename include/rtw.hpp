@@ -117,6 +117,9 @@ inline constexpr Material EMPTY_M = SCATTER_M;                         // :212
 struct PerlinNoise {
     std::array<std::array<float, 3>, 256> ranvec{};
     std::array<uint32_t, 256> perm_x{}, perm_y{}, perm_z{};
+    // The reference seeds from thread_rng; here the table stream is an explicit Philox key. Without one, keys are
+    // dealt 7, 8, 9, ... in construction order, as the Python mirror does (scene.py PerlinNoise._auto_key).
+    static std::shared_ptr<PerlinNoise> new_() { static uint64_t auto_key = 7; return new_(auto_key++); }
     static std::shared_ptr<PerlinNoise> new_(uint64_t key) {
         auto n = std::make_shared<PerlinNoise>();
         PhiloxStream rs(key);
@@ -156,11 +159,12 @@ struct ImageTexture {
         for (size_t i = 0; i < f.size(); ++i) f[i] = (float)rgb[i] / 255.0f;
         return make(std::move(f), width, height, nullptr, 1.0f);
     }
-    static Ptr new_with_noise(std::vector<float> img, uint32_t w, uint32_t h, float scale, std::shared_ptr<PerlinNoise> noise) {   // :228-236
-        return make(std::move(img), w, h, std::move(noise), scale);
+    // texture.rs:228-245: the reference builds a fresh PerlinNoise::new() inside; pass one to share or to fix its key
+    static Ptr new_with_noise(std::vector<float> img, uint32_t w, uint32_t h, float scale, std::shared_ptr<PerlinNoise> noise = nullptr) {
+        return make(std::move(img), w, h, noise ? std::move(noise) : PerlinNoise::new_(), scale);
     }
-    static Ptr from_color_noise(Vec3 c, float scale, std::shared_ptr<PerlinNoise> noise) {                                         // :237-245
-        return make({c.x, c.y, c.z}, 1, 1, std::move(noise), scale);
+    static Ptr from_color_noise(Vec3 c, float scale, std::shared_ptr<PerlinNoise> noise = nullptr) {
+        return make({c.x, c.y, c.z}, 1, 1, noise ? std::move(noise) : PerlinNoise::new_(), scale);
     }
 };
 
