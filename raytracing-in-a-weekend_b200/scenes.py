@@ -420,6 +420,52 @@ def config_c5(width=800, height=800, samples=10000, depth=50, frame=0) -> Job:
     return Job("C5", sc, vp, ray_color_bg_color, A.RTW_MODE_RANDOM, "Next-Week final scene 800x800 10000spp d50")
 
 
+def _five_quad_room(green_mat=SCATTER_M):
+    """The open room of objects/quad.rs:166-292 and viewport/ray_color.rs:115-213: red left, green back, blue
+    right, orange top, teal bottom."""
+    q = lambda o, u, v, m, c: Quad.new(Vec3(*o), Vec3(*u), Vec3(*v), m, Z, _solid(c))
+    return [q((-3.0, -2.0, 5.0), (0.0, 0.0, -4.0), (0.0, 4.0, 0.0), SCATTER_M, (1.0, 0.2, 0.2)),
+            q((-2.0, -2.0, 0.0), (4.0, 0.0, 0.0), (0.0, 4.0, 0.0), green_mat, (0.2, 1.0, 0.2)),
+            q((3.0, -2.0, 1.0), (0.0, 0.0, 4.0), (0.0, 4.0, 0.0), SCATTER_M, (0.2, 0.2, 1.0)),
+            q((-2.0, 3.0, 1.0), (4.0, 0.0, 0.0), (0.0, 0.0, 4.0), SCATTER_M, (1.0, 0.5, 0.0)),
+            q((-2.0, -3.0, 5.0), (4.0, 0.0, 0.0), (0.0, 0.0, -4.0), SCATTER_M, (0.2, 0.8, 0.8))]
+
+
+def quad_test(samples=100, size=400) -> Job:
+    """objects/quad.rs:153-321 `quad_test`: the five-quad room under the sky gradient, Viewport::render (stratified)."""
+    vp = Viewport.new_from_res(size, size, samples, 10, 2.0, 80.0, Vec3(0.0, 0.0, 9.0), Vec3(0.0, 0.0, -1.0), None, "Quad test")
+    return Job("quad_room", Scene.new_quad(_five_quad_room()), vp, ray_color_d, A.RTW_MODE_STRATIFIED)
+
+
+def simple_quad_test(samples=100, size=200) -> Job:
+    """objects/quad.rs:323-390 `simple_test`: one green quad two units in front of the camera."""
+    quads = [Quad.new(Vec3(-1.0, -0.5, -2.0), Vec3(2.0, 0.0, 0.0), Vec3(0.0, 1.0, 0.0), SCATTER_M, Z, _solid((0.20, 1.0, 0.20)))]
+    vp = Viewport.new_from_res(size, size, samples, 10, 2.0, 80.0, Vec3(0.0, 0.0, 0.0), Vec3(0.0, 0.0, -1.0), None, "Quad test")
+    return Job("simple_quad", Scene.new([], quads, []), vp, ray_color_d, A.RTW_MODE_STRATIFIED)
+
+
+def light_test(samples=100, size=400) -> Job:
+    """viewport/ray_color.rs:107-240 `light_test`: the same room with an emissive (4, 2, 4) back wall on a black
+    background, ray_color_bg_color."""
+    room = _five_quad_room(Material.new_emmiting(0.0, 0.0, 1.0, Vec3(4.0, 2.0, 4.0)))
+    vp = Viewport.new_from_res(size, size, samples, 10, 2.0, 80.0, Vec3(0.0, 0.0, 9.0), Vec3(0.0, 0.0, -1.0), None, "Quad test")
+    return Job("light", Scene.new_quad(room), vp, ray_color_bg_color, A.RTW_MODE_STRATIFIED)
+
+
+def light_box_test(samples=100, size=400) -> Job:
+    """viewport/ray_color.rs:242-518 `box_test`: an emissive mirror sphere (2, 0.5, 2) inside a five-quad box whose
+    back wall carries a zero emission, async_render."""
+    q = lambda o, u, v, m, c: Quad.new(Vec3(*o), Vec3(*u), Vec3(*v), m, Z, _solid(c))
+    quads = [q((-2.0, -2.0, 5.0), (0.0, 0.0, -4.0), (0.0, 4.0, 0.0), SCATTER_M, (1.0, 0.2, 0.2)),
+             q((2.0, -2.0, 1.0), (0.0, 0.0, 4.0), (0.0, 4.0, 0.0), SCATTER_M, (0.2, 0.2, 1.0)),
+             q((-2.0, 2.0, 1.0), (4.0, 0.0, 0.0), (0.0, 0.0, 4.0), SCATTER_M, (1.0, 0.5, 0.0)),
+             q((-2.0, -2.0, 5.0), (4.0, 0.0, 0.0), (0.0, 0.0, -4.0), SCATTER_M, (0.2, 0.8, 0.8)),
+             q((-2.0, -2.0, 1.0), (4.0, 0.0, 0.0), (0.0, 4.0, 0.0), Material.new_emmiting(0.0, 0.0, 1.0, Vec3(0.0, 0.0, 0.0)), (0.2, 1.0, 0.2))]
+    lamp = Sphere.new(Vec3(0.0, 0.0, 2.0), 0.4, Vec3(1.0, 1.0, 1.0), Material.new_emmiting(1.0, 0.0, 0.0, Vec3(2.0, 0.5, 2.0)))
+    vp = Viewport.new_from_res(size, size, samples, 10, 2.0, 90.0, Vec3(0.0, 0.0, 4.0), Vec3(0.0, 0.0, -1.0), None, "Quad test")
+    return Job("light_box", Scene.new([lamp], quads, []), vp, ray_color_bg_color, A.RTW_MODE_RANDOM)
+
+
 def triangle_test(width=400, height=300, samples=25, depth=2) -> Job:
     """Rust2/src/objects/triangle.rs:149-199 `triangle_test`, in the Rust/src object model: one grey
     lambertian triangle three units in front of the camera, background 0.6 white. Rust2's axes:
@@ -480,4 +526,5 @@ REFERENCE_TESTS: Dict[str, Callable[..., Job]] = {
     "instance_box_rot": lambda **k: instance_box_test(True, **k), "volume": volume_test,
     "presentation": presentation_image, "first_frame": first_frame,
     "triangle": triangle_test, "triangle_mesh": triangle_mesh_test,
+    "quad_room": quad_test, "simple_quad": simple_quad_test, "light": light_test, "light_box": light_box_test,
 }
