@@ -69,11 +69,11 @@ static void lbvh_rebuild_host(HostScene& hs) {
 extern "C" int emu_render_ex(const rtw_scene_desc* d, const rtw_camera* cam, const rtw_render_opts* o, float* out,
                              uint64_t* stats, rtw_scene_info* info, int use_lbvh);
 extern "C" int emu_render(const rtw_scene_desc* d, const rtw_camera* cam, const rtw_render_opts* o, float* out,
-                          uint64_t* stats /* paths, rays, nan */, rtw_scene_info* info) {
+                          uint64_t* stats /* paths, rays, nan, nodes, spheres, quads, instances, hits */, rtw_scene_info* info) {
     return emu_render_ex(d, cam, o, out, stats, info, 0);
 }
 extern "C" int emu_render_ex(const rtw_scene_desc* d, const rtw_camera* cam, const rtw_render_opts* o, float* out,
-                             uint64_t* stats /* paths, rays, nan */, rtw_scene_info* info, int use_lbvh) {
+                             uint64_t* stats /* paths, rays, nan, nodes, spheres, quads, instances, hits */, rtw_scene_info* info, int use_lbvh) {
     HostScene hs; std::string err;
     int rc = build_host_scene(d, hs, err);
     if (rc) { std::fprintf(stderr, "emu: %s\n", err.c_str()); return rc; }
@@ -84,6 +84,7 @@ extern "C" int emu_render_ex(const rtw_scene_desc* d, const rtw_camera* cam, con
     rc = make_render_params(cam, o, P, total, err);
     if (rc) { std::fprintf(stderr, "emu: %s\n", err.c_str()); return rc; }
     uint64_t paths = 0, nan = 0; uint32_t rays32 = 0; uint64_t rays = 0;
+    uint64_t work_total[5] = {0, 0, 0, 0, 0};   // nodes, spheres, quads, instances, hits (the strict walk's; tools/bvh_proxy.py)
     std::vector<uint32_t> stack_mem(stack_words(hs.top_depth, hs.inner_depth));
     Stack S; S.base = stack_mem.data(); S.stride = 1u;
     for (uint32_t jr = 0; jr < P.row_count; ++jr)
@@ -93,8 +94,10 @@ extern "C" int emu_render_ex(const rtw_scene_desc* d, const rtw_camera* cam, con
                 Path p;
                 generate(P, i, P.row_begin + jr, s, p);
                 rays32 = 0;
-                while (!path_step(sc, sc.noises, P, p, rays32, S)) {}
+                Work w{0u, 0u, 0u, 0u, 0u};
+                while (!path_step(sc, sc.noises, P, p, rays32, S, &w)) {}
                 rays += rays32;
+                work_total[0] += w.nodes; work_total[1] += w.spheres; work_total[2] += w.quads; work_total[3] += w.instances; work_total[4] += w.hits;
                 V3 c = path_result(p);
                 if (!finite3(c)) ++nan;
                 acc = acc + c; ++paths;
@@ -105,6 +108,6 @@ extern "C" int emu_render_ex(const rtw_scene_desc* d, const rtw_camera* cam, con
                 px[0] = std::pow(acc.x / (float)total, ig); px[1] = std::pow(acc.y / (float)total, ig); px[2] = std::pow(acc.z / (float)total, ig);
             } else { px[0] = acc.x; px[1] = acc.y; px[2] = acc.z; }
         }
-    if (stats) { stats[0] = paths; stats[1] = rays; stats[2] = nan; }
+    if (stats) { stats[0] = paths; stats[1] = rays; stats[2] = nan; for (int k = 0; k < 5; ++k) stats[3 + k] = work_total[k]; }
     return 0;
 }

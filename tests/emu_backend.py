@@ -23,7 +23,7 @@ def build_emu() -> str:
     srcs = [os.path.join(EMU_DIR, "emu.cpp"), os.path.join(ROOT, "include", "rtw.h")]
     srcs += [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".h", ".cpp"))]
     if not os.path.exists(path) or any(os.path.getmtime(s) > os.path.getmtime(path) for s in srcs):
-        subprocess.check_call(["g++", "-std=c++17", "-O2", "-ffp-contract=off", "-fno-fast-math", "-fPIC", "-shared",
+        subprocess.check_call(["g++", "-std=c++17", "-O2", "-ffp-contract=off", "-fno-fast-math", "-fPIC", "-shared", "-DRTW_COUNT_WORK=1",
                                "-I/usr/local/cuda/include", "-o", path, os.path.join(EMU_DIR, "emu.cpp"),
                                os.path.join(CSRC, "scene_build.cpp")])
     return path
@@ -47,7 +47,7 @@ def load_emu():
 class EmuSceneHandle:
     def __init__(self, lib, fs, lbvh: bool = False):
         self._lib, self._fs, self._lbvh = lib, fs, lbvh
-        self.last = (C.c_uint64 * 3)()
+        self.last = (C.c_uint64 * 8)()
         self.last_info = A.rtw_scene_info()
 
     def close(self):
@@ -63,7 +63,8 @@ class EmuSceneHandle:
         return out
 
     def stats(self):
-        return {"paths": self.last[0], "rays": self.last[1], "nan_paths": self.last[2]}
+        keys = ("paths", "rays", "nan_paths", "nodes", "sphere_tests", "quad_tests", "instance_tests", "hits")
+        return {k: self.last[i] for i, k in enumerate(keys)}
 
     def info(self):
         return self.last_info
