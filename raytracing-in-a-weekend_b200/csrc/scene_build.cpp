@@ -12,6 +12,7 @@
 //   Viewport::new        viewport.rs:308-401                 camera basis
 #include <algorithm>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 #include <limits>
 #include <cuda_fp16.h>
@@ -164,6 +165,71 @@ struct Builder {
         return make_ref(KIND_NODE, me);
     }
 
+    // Experimental collapse (RTW_BVH_COLLAPSE=dp; default: the greedy one above): choose, for every binary node,
+    // which descendants become the up-to-four children of its wide node so that the summed surface area of all
+    // wide nodes — the expected number of node visits of a random ray — is minimal. Leaves cost the same under
+    // every cut (each keeps its own box), so only node areas enter. cut[b][k] = least cost of handing the subtree
+    // of binary node b to its parent in at most k child slots; choice 0 = as one wide node, i = i slots to the left.
+    std::vector<float> dp_cut;            // [4 * b + (k - 1)]
+    std::vector<uint8_t> dp_choice;       // [4 * b + (k - 1)]; [4 * b + 0] of a wide node's root = its own split
+    std::vector<uint8_t> dp_root;
+    float dp_cutk(uint32_t c, bool is_bin, int k) const { return is_bin ? dp_cut[4 * c + (k - 1)] : 0.0f; }
+    void dp_solve() {
+        const size_t nb = bin.size();
+        dp_cut.assign(4 * nb, 0.f); dp_choice.assign(4 * nb, 0); dp_root.assign(nb, 1);
+        for (size_t b = nb; b-- > 0;) {       // children were created after their parent: solve them first
+            const uint32_t L = bin[b].c[0], R = bin[b].c[1];
+            const bool lb = binflag[2 * b] != 0, rb = binflag[2 * b + 1] != 0;
+            Box bb = bin[b].b[0]; box_grow(bb, bin[b].b[1]);
+            float best = std::numeric_limits<float>::infinity(); int bi = 1;
+            for (int i = 1; i <= 3; ++i) { float c = dp_cutk(L, lb, i) + dp_cutk(R, rb, 4 - i); if (c < best) { best = c; bi = i; } }
+            const float wide = box_area(bb) + best;
+            dp_root[b] = (uint8_t)bi;
+            dp_cut[4 * b] = wide; dp_choice[4 * b] = 0;
+            for (int k = 2; k <= 4; ++k) {
+                float bestk = wide; int ck = 0;
+                for (int i = 1; i < k; ++i) { float c = dp_cutk(L, lb, i) + dp_cutk(R, rb, k - i); if (c < bestk) { bestk = c; ck = i; } }
+                dp_cut[4 * b + (k - 1)] = bestk; dp_choice[4 * b + (k - 1)] = (uint8_t)ck;
+            }
+        }
+    }
+    struct DpChild { Box box; uint32_t c; bool is_bin; };
+    void dp_expand(const Box& box, uint32_t c, bool is_bin, int k, DpChild* out, int& n) const {
+        const int ch = (is_bin && k > 1) ? dp_choice[4 * c + (k - 1)] : 0;
+        if (!is_bin || ch == 0) { out[n].box = box; out[n].c = c; out[n].is_bin = is_bin; ++n; return; }
+        dp_expand(bin[c].b[0], bin[c].c[0], binflag[2 * c] != 0, ch, out, n);
+        dp_expand(bin[c].b[1], bin[c].c[1], binflag[2 * c + 1] != 0, k - ch, out, n);
+    }
+    uint32_t emit4_dp(uint32_t b, uint32_t& pushes) {
+        DpChild ch[4]; int n = 0;
+        const int i = dp_root[b];
+        dp_expand(bin[b].b[0], bin[b].c[0], binflag[2 * b] != 0, i, ch, n);
+        dp_expand(bin[b].b[1], bin[b].c[1], binflag[2 * b + 1] != 0, 4 - i, ch, n);
+        uint32_t me = (uint32_t)nodes.size();
+        nodes.emplace_back();
+        const float inf = std::numeric_limits<float>::infinity();
+        float lo[3][4], hi[3][4]; uint32_t ref[4];
+        uint32_t below = 0;
+        for (int k = 0; k < 4; ++k) {
+            if (k < n) {
+                for (int a = 0; a < 3; ++a) { lo[a][k] = ch[k].box.lo[a]; hi[a][k] = ch[k].box.hi[a]; }
+                if (ch[k].is_bin) { uint32_t pb = 0; ref[k] = emit4_dp(ch[k].c, pb); below = std::max(below, pb); }
+                else ref[k] = ch[k].c;
+            } else {
+                for (int a = 0; a < 3; ++a) { lo[a][k] = inf; hi[a][k] = inf; }
+                ref[k] = REF_NONE;
+            }
+        }
+        Node& nd = nodes[me];
+        nd.lox = make_float4(lo[0][0], lo[0][1], lo[0][2], lo[0][3]); nd.loy = make_float4(lo[1][0], lo[1][1], lo[1][2], lo[1][3]);
+        nd.loz = make_float4(lo[2][0], lo[2][1], lo[2][2], lo[2][3]); nd.hix = make_float4(hi[0][0], hi[0][1], hi[0][2], hi[0][3]);
+        nd.hiy = make_float4(hi[1][0], hi[1][1], hi[1][2], hi[1][3]); nd.hiz = make_float4(hi[2][0], hi[2][1], hi[2][2], hi[2][3]);
+        nd.ref = make_uint4(ref[0], ref[1], ref[2], ref[3]);
+        nd.pad = make_uint4(0u, 0u, 0u, 0u);
+        pushes = (uint32_t)(n - 1) + below;
+        return make_ref(KIND_NODE, me);
+    }
+
     Level level(std::vector<BuildPrim>& prims, uint32_t mov_first, uint32_t mov_count) {
         Level lv; std::memset(&lv, 0, sizeof lv);
         lv.mov_first = mov_first; lv.mov_count = mov_count;
@@ -172,7 +238,9 @@ struct Builder {
         bin.clear(); binflag.clear();
         Box rb; bool is_bin;
         uint32_t r = build(prims, 0, prims.size(), 0, rb, is_bin);
-        lv.root = is_bin ? emit4(r, max_pushes) : r;
+        static const bool use_dp = [] { const char* e = std::getenv("RTW_BVH_COLLAPSE"); return e && std::string(e) == "dp"; }();
+        if (is_bin && use_dp) { dp_solve(); lv.root = emit4_dp(r, max_pushes); }
+        else lv.root = is_bin ? emit4(r, max_pushes) : r;
         for (int a = 0; a < 3; ++a) { lv.lo[a] = rb.lo[a]; lv.hi[a] = rb.hi[a]; }
         return lv;
     }
