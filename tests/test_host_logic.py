@@ -161,3 +161,36 @@ def test_deep_bvh_falls_back_to_a_balanced_split(emu):
     sc = Scene.new_sphere(sp)
     vp.render_no_rand(rtw_b200.ray_color_normal, sc, emu)
     assert emu.scene(sc).info().bvh_max_depth < 3 * 32
+
+
+def test_dp_collapse_experiment_renders_identically(emu, tmp_path):
+    """RTW_BVH_COLLAPSE=dp (off by default) only regroups the same leaves into other wide nodes: strict
+    renders are bit-identical to the greedy collapse's. The variable is read once per process, hence the child."""
+    import os
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    code = (
+        "import sys; sys.path[:0] = [%r, %r]\n"
+        "import numpy as np, rtw_b200\n"
+        "from rtw_b200 import scenes\n"
+        "from emu_backend import EmuBackend\n"
+        "from test_host_logic import _small\n"
+        "be = EmuBackend()\n"
+        "out = {}\n"
+        "for name in ('C2', 'C4_smoke', 'C5'):\n"
+        "    f = scenes.CONFIGS.get(name) or (lambda: scenes.config_c4(smoke=True))\n"
+        "    job = _small(f(), 40, 30, 2)\n"
+        "    out[name] = job.render(be)\n"
+        "    out[name + '_nodes'] = np.array(be.scene(job.scene).stats()['nodes'])\n"
+        "np.savez(%r, **out)\n") % (root, os.path.join(root, "tests"), str(tmp_path / "dp.npz"))
+    env = dict(os.environ, RTW_BVH_COLLAPSE="dp")
+    subprocess.check_call([sys.executable, "-c", code], env=env)
+    got = np.load(str(tmp_path / "dp.npz"))
+    fewer = 0
+    for name in ("C2", "C4_smoke", "C5"):
+        f = scenes.CONFIGS.get(name) or (lambda: scenes.config_c4(smoke=True))
+        job = _small(f(), 40, 30, 2)
+        assert np.array_equal(job.render(emu), got[name], equal_nan=True), name
+        fewer += int(got[name + "_nodes"]) < emu.scene(job.scene).stats()["nodes"]
+    assert fewer >= 2                                   # and it walks fewer nodes on most of them (the point of it)
