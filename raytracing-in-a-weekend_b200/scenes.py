@@ -8,12 +8,17 @@ Two groups:
 
 Each builder returns a `Job`: scene, viewport, integrator and which reference entry point to use.
 Scene-building randomness is a Philox stream (key 2024) so every rank and every backend sees the
-same scene. No file under /root/reference is read here: the earth map and the checker are
-synthesised (same resolution as Rust/assets/earthmap.jpg 1024x512 and default.png 128x64).
+same scene. Image textures are the reference's own assets (Rust/assets/earthmap.jpg 1024x512,
+default.png 128x64, squares.png), decoded once in the build container by tests/golden/make_textures.py
+and committed as lossless PNGs under tests/golden/assets/ (RTW_ASSET_DIR overrides); they enter the
+scene through ImageTexture.from_path, as in texture_test.rs:63,114. Nothing under /root/reference is
+read at run time. `SYNTHETIC_TEXTURES = True` (bench.py --synthetic-textures) swaps in generated
+stand-ins of the same sizes.
 """
 from __future__ import annotations
 
 import math
+import os
 from dataclasses import dataclass
 from typing import Callable, Dict
 
@@ -44,7 +49,34 @@ class Job:
         return self.viewport._run(self.ray_color, self.scene, self.mode, backend)
 
 
-# --------------------------------------------------------------------------- synthetic textures
+# --------------------------------------------------------------------------- textures
+ASSET_DIR = os.environ.get("RTW_ASSET_DIR") or os.path.join(
+    os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tests", "golden", "assets")
+SYNTHETIC_TEXTURES = False     # True: generated stand-ins instead of the reference's assets
+_asset_cache = {}
+
+
+def asset_path(name: str) -> str:
+    """Path of the committed lossless copy of Rust/assets/<name>.{jpg,png} (tests/golden/make_textures.py)."""
+    return os.path.join(ASSET_DIR, name + ".png")
+
+
+def _asset_texture(name: str) -> ImageTexture:
+    """ImageTexture::from_path("assets/...") (texture.rs:215-226), decoded once per process."""
+    if name not in _asset_cache:
+        path = asset_path(name)
+        if not os.path.exists(path):
+            raise FileNotFoundError(f"{path}: run tests/golden/make_textures.py where /root/reference exists, "
+                                    "or set scenes.SYNTHETIC_TEXTURES = True")
+        _asset_cache[name] = ImageTexture.from_path(path)
+    return _asset_cache[name]
+
+
+def texture_data_label() -> str:
+    return ("synthetic scene + synthetic textures" if SYNTHETIC_TEXTURES else
+            "synthetic scene (authored per SURVEY 8d), reference texture assets (earthmap.jpg, default.png)")
+
+
 def checker_texture(width=512, height=256, cells_x=32, cells_y=16, c0=(0.2, 0.3, 0.1), c1=(0.9, 0.9, 0.9)) -> ImageTexture:
     """A checker is just an image in the reference; C3's generated 512x256 one."""
     x = (np.arange(width) * cells_x // width)[None, :]
@@ -54,18 +86,27 @@ def checker_texture(width=512, height=256, cells_x=32, cells_y=16, c0=(0.2, 0.3,
     return ImageTexture.new(img.reshape(-1, 3), width, height)
 
 
-def default_png_texture() -> ImageTexture:
-    """Stand-in for Rust/assets/default.png: 128x64 magenta/black checker."""
+def default_png_texture(synthetic=None) -> ImageTexture:
+    """Rust/assets/default.png (128x64 magenta/black checker); synthetic: a generated one of that size."""
+    if not (SYNTHETIC_TEXTURES if synthetic is None else synthetic):
+        return _asset_texture("default")
     return checker_texture(128, 64, 16, 8, (0.0, 0.0, 0.0), (1.0, 0.0, 1.0))
+
+
+def squares_png_texture() -> ImageTexture:
+    """Rust/assets/squares.png (128x64 colour grid)."""
+    return _asset_texture("squares")
 
 
 _earth_cache = {}
 
 
-def earth_texture(width=1024, height=512) -> ImageTexture:
-    """Synthetic stand-in for Rust/assets/earthmap.jpg (1024x512 RGB, u8/255 texels): a few octaves
-    of lattice value-noise thresholded into sea / land / ice. Only its size and texel statistics
-    matter to the path (random 12-byte gathers)."""
+def earth_texture(width=1024, height=512, synthetic=None) -> ImageTexture:
+    """Rust/assets/earthmap.jpg through from_path (texture_test.rs:63,114). synthetic: a stand-in of the
+    same size (1024x512 RGB, u8/255 texels): a few octaves of lattice value-noise thresholded into
+    sea / land / ice."""
+    if not (SYNTHETIC_TEXTURES if synthetic is None else synthetic):
+        return _asset_texture("earthmap")
     key = (width, height)
     if key in _earth_cache:
         return _earth_cache[key]
@@ -183,6 +224,16 @@ def noise_test(width=400, height=225, samples=100) -> Job:
                                 ImageTexture.from_color_noise(Vec3(1.0, 1.0, 1.0), 0.01, PerlinNoise.new(11))),
         Sphere.new(Vec3(0.0, 0.0, -1.0), 0.5, Vec3(0.8, 0.8, 0.0), SCATTER_M)])
     return Job("noise", sc, Viewport.new_from_res(width, height, samples, 10, 2.0), ray_color_d, A.RTW_MODE_STRATIFIED)
+
+
+def texture_test(width=2000, height=2000, samples=100) -> Job:
+    """viewport/texture_test.rs:45-86 `default_test`: a radius-0.05 mirror sphere carrying
+    assets/earthmap.jpg, seen through a 7 degree lens from the origin, async_render. (The closure there is
+    the file's own ray_color_d with mint 1e-4 and an origin nudge; ray_color_d is the shipped equivalent.)"""
+    sc = Scene.new_sphere([Sphere.new_with_texture(Vec3(-1.0, 0.0, -0.0), 0.05, Vec3(1.0, 1.0, 1.0), METALLIC_M,
+                                                   earth_texture())])
+    vp = Viewport.new_from_res(width, height, samples, 10, 2.0, 7.0, None, Vec3(-1.0, 0.0, -0.0), None, "texture test")
+    return Job("texture", sc, vp, ray_color_d, A.RTW_MODE_RANDOM)
 
 
 def reflection_test(width=400, height=300, samples=100) -> Job:
@@ -522,7 +573,7 @@ REFERENCE_TESTS: Dict[str, Callable[..., Job]] = {
     "camera_upside_down": lambda **k: camera_test("upside_down", **k),
     "camera_depth_of_field": lambda **k: camera_test("depth_of_field", **k),
     "diffuse": diffuse_test, "metal": metal_test, "hollow_glass": hollow_glass_test, "noise": noise_test,
-    "reflection": reflection_test, "instance_box": lambda **k: instance_box_test(False, **k),
+    "reflection": reflection_test, "texture": texture_test, "ltr": ltr_scene, "instance_box": lambda **k: instance_box_test(False, **k),
     "instance_box_rot": lambda **k: instance_box_test(True, **k), "volume": volume_test,
     "presentation": presentation_image, "first_frame": first_frame,
     "triangle": triangle_test, "triangle_mesh": triangle_mesh_test,
