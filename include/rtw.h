@@ -9,7 +9,7 @@
  *     async_render              Rust/src/viewport.rs:215   (row tasks, random jitter, motion blur)
  *     render_multi              Rust/src/viewport.rs:249   (frames start_frame..start_frame+n)
  * This header is what a Rust `extern "C"` block (rust_shim/src/ffi.rs), a ctypes loader
- * (raytracing-in-a-weekend_b200/_abi.py) or a C++ caller (include/rtw_scene.hpp) binds instead.
+ * (raytracing-in-a-weekend_b200/_abi.py) or a C++ caller (include/rtw.hpp) binds instead.
  * Every struct is plain data: counts, floats and pointers to caller-owned arrays. The library
  * deep-copies at rtw_scene_create and owns device memory until rtw_scene_destroy.
  *
@@ -26,7 +26,7 @@
 extern "C" {
 #endif
 
-#define RTW_ABI_VERSION 2
+#define RTW_ABI_VERSION 3
 
 /* ---- error codes (negative; 0 = ok). The reference panics/unwraps instead (viewport.rs:242). */
 enum {
@@ -196,7 +196,7 @@ typedef struct rtw_stats {
     float    kernel_ms;      /* device time of the trace kernel(s), CUDA events */
     float    total_ms;       /* device time incl. resolve and D2H copy when there is one */
     /* filled only by RTW_FLAG_COUNT_WORK renders, else 0 */
-    uint64_t nodes;          /* BVH nodes visited (each = two child-box slab tests, 64 B) */
+    uint64_t nodes;          /* 4-wide BVH nodes visited (each = four child-box slab tests, 64 B of half-float boxes) */
     uint64_t sphere_tests, quad_tests, instance_tests;
     uint64_t hits;           /* segments that ended on a surface (Hit evaluated + scatter) */
     /* wavefront renders only, else 0 */
@@ -241,7 +241,10 @@ int rtw_trim_memory(int device);
  * sort + Karras tree + 4-wide collapse) and walked from now on. Same leaves, same leaf boxes: the
  * closest hit of every ray is unchanged. `out_build_ms` (may be NULL) = device time of the build. */
 int rtw_scene_rebuild_lbvh(rtw_scene* scene, float* out_build_ms);
-/* Walk the host SAH tree built by rtw_scene_create again. */
+/* Walk the host SAH tree built by rtw_scene_create again. Both calls patch the node arrays and instance levels
+ * on the scene's own stream and synchronise it; they are NOT ordered against renders the caller has enqueued
+ * on its own streams with rtw_render_device: the scene must be idle (those streams synchronised) when either
+ * is called. */
 int rtw_scene_use_sah(rtw_scene* scene);
 
 /* --- render. Blocking; `out_rgb` is HOST memory (rows top to bottom, [row][col][rgb], like Img).
@@ -249,8 +252,14 @@ int rtw_scene_use_sah(rtw_scene* scene);
 int rtw_render(rtw_scene* scene, const rtw_camera* cam, const rtw_render_opts* opts,
                float* out_rgb);
 /* Same, but `d_out_rgb` is DEVICE memory on the scene's device and `stream` a cudaStream_t
- * (0 = default stream); returns after enqueueing (no host sync) so callers can chain a
- * collective on the same stream. Stats of this call become valid after the stream syncs. */
+ * (0 = default stream). All work is enqueued on `stream` and the call does not synchronise it, so a
+ * collective or copy enqueued behind it on the same stream is ordered after the frame. The call is
+ * NOT asynchronous for renders of 2^18 paths or more (the wavefront pipeline): its host loop reads the
+ * live-path count of finished iteration batches from pinned memory and keeps launching until the
+ * frame has drained, i.e. it blocks the calling thread for almost the whole frame (the megakernel
+ * path returns right after its one launch). Stats of this call become valid after the stream syncs.
+ * One render per scene at a time: a second call on the same scene must not start before the first
+ * has returned. The calling thread's current device is left as it was. */
 int rtw_render_device(rtw_scene* scene, const rtw_camera* cam, const rtw_render_opts* opts,
                       float* d_out_rgb, void* stream);
 /* render_multi (viewport.rs:249-269): frames first_frame..first_frame+n_frames into
@@ -290,6 +299,36 @@ int rtw_bilateral_filter_device(const uint8_t* d_rgb8, uint32_t width, uint32_t 
 int rtw_bilateral_filter(const uint8_t* rgb8, uint32_t width, uint32_t height, uint32_t size,
                          int proximity, uint8_t* out_rgb8, float* out_params, float* out_kernel_ms,
                          int device);
+
+/* ---- several devices behind one call (SURVEY 8b "device list, split {Samples, Tiles}", 8e). The reference's
+ * caller is ONE process that calls async_render / render_multi (viewport.rs:215-269, main.rs:76-80,412-414);
+ * this is the same call over a list of CUDA devices of that process: the scene is replicated on every
+ * device (one SAH build, n uploads), each device renders its share on its own stream from its own host
+ * thread, and the shares are combined on devices[0]:
+ *   RTW_SPLIT_SAMPLES  device g renders samples [g*spp/n, (g+1)*spp/n) of every pixel into its own f32 sum
+ *                      buffer (the Philox counter carries the GLOBAL sample index, so the image does not
+ *                      depend on n beyond f32 summation order); one kernel on devices[0] reads the n buffers
+ *                      over NVLink peer memory, adds them in device order and resolves (/spp, powf(1/gamma)).
+ *   RTW_SPLIT_TILES    bands of `band_rows` rows (0 = 8) dealt round-robin; each device resolves its bands and
+ *                      copies them straight into their place in out_rgb. No reduction: bit-identical to
+ *                      one device.
+ *   RTW_SPLIT_FRAMES   (rtw_render_frames_multi) render_multi's frame k -> devices[k mod n]; no exchange.
+ * A device may appear more than once in `devices` (its shares then run concurrently on separate streams
+ * of that device), which is how a one-GPU box exercises every code path. `out_rgb` is HOST memory. */
+typedef struct rtw_scene_multi rtw_scene_multi;
+enum { RTW_SPLIT_SAMPLES = 0, RTW_SPLIT_TILES = 1, RTW_SPLIT_FRAMES = 2 };
+int  rtw_scene_multi_create(const rtw_scene_desc* desc, const int* devices, int n_devices, rtw_scene_multi** out);
+void rtw_scene_multi_destroy(rtw_scene_multi* ms);
+int  rtw_render_multi(rtw_scene_multi* ms, const rtw_camera* cam, const rtw_render_opts* opts, uint32_t split,
+                      uint32_t band_rows, float* out_rgb);
+int  rtw_render_frames_multi(rtw_scene_multi* ms, const rtw_camera* cam, const rtw_render_opts* opts,
+                             uint32_t first_frame, uint32_t n_frames, float* out_rgb);
+/* Totals over the devices of the last multi render: paths, rays, nan_paths, gpu_launches and the work counters
+ * are sums; kernel_ms / total_ms are the maximum over devices (they ran side by side); extend_ms / shade_ms the
+ * mean. `per_device` (may be NULL) receives n_devices rtw_stats. combine_ms (may be NULL): device time of the
+ * peer-memory combine kernel (samples split), 0 otherwise. */
+int  rtw_multi_get_stats(rtw_scene_multi* ms, rtw_stats* total, rtw_stats* per_device, float* combine_ms);
+int  rtw_scene_multi_device_count(const rtw_scene_multi* ms);
 
 int rtw_get_stats(rtw_scene* scene, rtw_stats* out);
 /* Warp-scheduling counters of the wavefront extend kernel, filled by RTW_FLAG_COUNT_WORK |

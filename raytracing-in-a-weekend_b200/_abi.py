@@ -12,7 +12,7 @@ import os
 HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("RTW_B200_LIB") or os.path.join(HERE, "csrc", "librtw_b200.so")   # env override: tuning builds
 
-RTW_ABI_VERSION = 2
+RTW_ABI_VERSION = 3
 
 # error codes
 RTW_OK, RTW_E_INVALID, RTW_E_CUDA, RTW_E_NOMEM, RTW_E_UNSUPPORTED = 0, -1, -2, -3, -4
@@ -28,6 +28,7 @@ RTW_OUT_RESOLVED, RTW_OUT_SUM = 0, 1
 # flags
 RTW_FLAG_STRICT_FP, RTW_FLAG_WAVEFRONT, RTW_FLAG_COUNT_WORK, RTW_FLAG_MEGAKERNEL = 1, 2, 4, 8
 RTW_BENCH_FP32, RTW_BENCH_L2, RTW_BENCH_HBM = 0, 1, 2
+RTW_SPLIT_SAMPLES, RTW_SPLIT_TILES, RTW_SPLIT_FRAMES = 0, 1, 2
 
 f32, u32, i32, u64 = C.c_float, C.c_uint32, C.c_int32, C.c_uint64
 f3 = f32 * 3
@@ -118,6 +119,12 @@ SYMBOLS = {
     "rtw_render_rgb8": (C.c_int, [C.c_void_p, P(rtw_camera), P(rtw_render_opts), C.c_void_p]),
     "rtw_bilateral_filter_device": (C.c_int, [C.c_void_p, u32, u32, u32, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]),
     "rtw_bilateral_filter": (C.c_int, [C.c_void_p, u32, u32, u32, C.c_int, C.c_void_p, P(f32), P(f32), C.c_int]),
+    "rtw_scene_multi_create": (C.c_int, [P(rtw_scene_desc), P(C.c_int), C.c_int, P(C.c_void_p)]),
+    "rtw_scene_multi_destroy": (None, [C.c_void_p]),
+    "rtw_render_multi": (C.c_int, [C.c_void_p, P(rtw_camera), P(rtw_render_opts), u32, u32, C.c_void_p]),
+    "rtw_render_frames_multi": (C.c_int, [C.c_void_p, P(rtw_camera), P(rtw_render_opts), u32, u32, C.c_void_p]),
+    "rtw_multi_get_stats": (C.c_int, [C.c_void_p, P(rtw_stats), P(rtw_stats), P(f32)]),
+    "rtw_scene_multi_device_count": (C.c_int, [C.c_void_p]),
     "rtw_get_stats": (C.c_int, [C.c_void_p, P(rtw_stats)]),
     "rtw_get_sched_stats": (C.c_int, [C.c_void_p, P(u64)]),
     "rtw_microbench": (C.c_int, [C.c_int, C.c_int, C.c_int, P(C.c_double)]),

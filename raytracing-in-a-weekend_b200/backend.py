@@ -102,6 +102,54 @@ class CudaSceneHandle:
         return inf
 
 
+class CudaMultiSceneHandle:
+    """One scene replicated on a list of CUDA devices of THIS process (rtw_scene_multi, include/rtw.h): what the
+    reference's single-process caller (main.rs:76-80,412-414) gets instead of one tokio runtime. A device may be
+    listed more than once (its shares then run side by side on separate streams)."""
+
+    def __init__(self, lib, fs, devices):
+        self._lib, self._fs = lib, fs
+        self.devices = [int(d) for d in devices]
+        self._h = C.c_void_p()
+        arr = (C.c_int * len(self.devices))(*self.devices)
+        A.check(lib.rtw_scene_multi_create(C.byref(fs.desc), arr, len(self.devices), C.byref(self._h)))
+
+    def close(self):
+        if self._h:
+            self._lib.rtw_scene_multi_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def render(self, cam, o, split: int = A.RTW_SPLIT_SAMPLES, band_rows: int = 0, out: np.ndarray | None = None) -> np.ndarray:
+        """async_render / Viewport::render over every device: sample ranges (one peer-memory combine on devices[0])
+        or round-robin row bands (no exchange)."""
+        if out is None:
+            out = np.empty(CudaSceneHandle.out_shape(cam, o), dtype=np.float32)
+        A.check(self._lib.rtw_render_multi(self._h, C.byref(cam), C.byref(o), split, band_rows, C.c_void_p(out.ctypes.data)))
+        return out
+
+    def render_frames(self, cam, o, first_frame: int, n_frames: int) -> np.ndarray:
+        """render_multi (viewport.rs:249-269), frame k on devices[k mod n]."""
+        rows = o.row_count if o.row_count else cam.height
+        out = np.empty((n_frames, rows, cam.width, 3), dtype=np.float32)
+        A.check(self._lib.rtw_render_frames_multi(self._h, C.byref(cam), C.byref(o), first_frame, n_frames,
+                                                  C.c_void_p(out.ctypes.data)))
+        return out
+
+    def stats(self):
+        """(totals, per-share list, combine kernel ms) of the last multi render."""
+        total = A.rtw_stats()
+        per = (A.rtw_stats * len(self.devices))()
+        ms = C.c_float(0.0)
+        A.check(self._lib.rtw_multi_get_stats(self._h, C.byref(total), per, C.byref(ms)))
+        return total, list(per), float(ms.value)
+
+
 class CudaBackend:
     name = "cuda"
 
@@ -123,6 +171,14 @@ class CudaBackend:
         h = scene._backend_cache.get(key)
         if h is None:
             h = CudaSceneHandle(self.lib, scene.flatten(), self.device)
+            scene._backend_cache[key] = h
+        return h
+
+    def scene_multi(self, scene, devices) -> CudaMultiSceneHandle:
+        key = ("cuda-multi", tuple(int(d) for d in devices))
+        h = scene._backend_cache.get(key)
+        if h is None:
+            h = CudaMultiSceneHandle(self.lib, scene.flatten(), devices)
             scene._backend_cache[key] = h
         return h
 

@@ -20,6 +20,12 @@ using namespace rtw;
 namespace {
 
 thread_local std::string g_err;
+// Entry points that have to make a particular device current put the caller's device back when they return.
+struct DeviceGuard {
+    int prev = -1;
+    DeviceGuard() { if (cudaGetDevice(&prev) != cudaSuccess) { cudaGetLastError(); prev = -1; } }
+    ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
+};
 int fail(int code, const std::string& msg) { g_err = msg; return code; }
 int cuda_fail(cudaError_t e, const char* what) {
     g_err = std::string(what) + ": " + cudaGetErrorString(e);
@@ -192,6 +198,14 @@ __global__ void quantize_kernel(const float* __restrict__ rgb, uint8_t* __restri
     }
 }
 
+// Seeds the wavefront counters on the device. (The first version copied them from slot 0 of the pinned ring the
+// host polls; a second render enqueued right behind the first could have that slot overwritten by the first
+// render's last, still pending, D2H copy before its own H2D read it: a frame that found the sample supply
+// "exhausted" and came back black.)
+__global__ void wf_init_kernel(WfCounters* wc, unsigned long long total_paths) {
+    wc->head = 0u; wc->live_mark = 0u; wc->next_path = 0ull; wc->total_paths = total_paths; wc->iterations = 0ull;
+}
+
 // ---- micro-benchmarks (rtw_microbench): denominators for the FP32 and L2 rooflines
 __global__ void bench_fp32_kernel(float* out, int iters, float a, float b) {
     float x0 = threadIdx.x * 1e-3f, x1 = x0 + 1.f, x2 = x0 + 2.f, x3 = x0 + 3.f, x4 = x0 + 4.f, x5 = x0 + 5.f,
@@ -225,6 +239,8 @@ int grid_for(unsigned long long n, int block) {
 }
 
 }  // namespace
+
+namespace rtw { void set_last_error(const std::string& msg) { g_err = msg; } }   // rtw_multi.cu reports through the same string
 
 struct rtw_scene {
     int device = 0;
@@ -275,6 +291,7 @@ struct rtw_scene {
     double wf_extend_sum = 0.0, wf_shade_sum = 0.0;
 
     ~rtw_scene() {
+        DeviceGuard guard;
         cudaSetDevice(device);
         cudaDeviceSynchronize();          // the blocks below go back to the cache: nothing may still be using them
         for (const auto& t : texs) cached_texture_release(t);
@@ -477,8 +494,8 @@ int enqueue_wavefront(rtw_scene* s, const RenderParams& P, int variant, float* d
         L.prim_w = std::max(1u, env_u32("RTW_WF_PRIM_W", events_rare ? 8u : 4u));
         L.event_w = std::max(1u, env_u32("RTW_WF_EVENT_W", events_rare ? 8u : 4u));   // (16 before one-sphere instances joined the event steps)
     }
-    s->h_wc[0] = init;
-    CK(cudaMemcpyAsync(s->d_wc, &s->h_wc[0], sizeof(WfCounters), cudaMemcpyHostToDevice, st));
+    wf_init_kernel<<<1, 1, 0, st>>>(s->d_wc, init.total_paths);
+    CK(cudaGetLastError());
     auto extend = [&]() {
         return variant == 1   ? launch_wf_extend_strict(s->d_cur, P, s->pool, s->d_wc, s->d_ctr, L, st)
                : variant == 2 ? launch_wf_extend_count(s->d_cur, P, s->pool, s->d_wc, s->d_ctr, L, st)
@@ -492,7 +509,8 @@ int enqueue_wavefront(rtw_scene* s, const RenderParams& P, int variant, float* d
     s->wf_timed = 0; s->wf_harvested = 0; s->wf_extend_sum = 0.0; s->wf_shade_sum = 0.0;
     CK(shade(0u, 1));                       // first fill
     s->launches += 1;
-    const uint32_t batch = std::max(1u, env_u32("RTW_WF_BATCH", 8u));
+    // the host runs at most three batches ahead and a ring slot is reused after kTimed * 8 rounds: 3 * batch must stay below that
+    const uint32_t batch = std::min(64u, std::max(1u, env_u32("RTW_WF_BATCH", 8u)));
     uint32_t it = 0;
     for (uint32_t k = 0;; ++k) {
         for (uint32_t b = 0; b < batch; ++b, ++it) {
@@ -642,6 +660,7 @@ int rtw_scene_create(const rtw_scene_desc* desc, int device, rtw_scene** out) {
     HostScene hs; std::string err;
     int rc = build_host_scene(desc, hs, err);
     if (rc) return fail(rc, err);
+    DeviceGuard guard;
     CK(cudaSetDevice(device));
     rtw_scene* s = new (std::nothrow) rtw_scene();
     if (!s) return fail(RTW_E_NOMEM, "out of host memory");
@@ -672,12 +691,14 @@ void rtw_scene_destroy(rtw_scene* scene) { delete scene; }
 
 int rtw_render_device(rtw_scene* scene, const rtw_camera* cam, const rtw_render_opts* opts, float* d_out_rgb, void* stream) {
     if (!scene || !cam || !opts || !d_out_rgb) return fail(RTW_E_INVALID, "null argument");
+    DeviceGuard guard;
     CK(cudaSetDevice(scene->device));
     return enqueue_render(scene, cam, opts, d_out_rgb, static_cast<cudaStream_t>(stream));
 }
 
 int rtw_render(rtw_scene* scene, const rtw_camera* cam, const rtw_render_opts* opts, float* out_rgb) {
     if (!scene || !cam || !opts || !out_rgb) return fail(RTW_E_INVALID, "null argument");
+    DeviceGuard guard;
     CK(cudaSetDevice(scene->device));
     const uint32_t rows = opts->row_count ? opts->row_count : cam->height;
     const size_t n_values = (size_t)rows * cam->width * 3u;
@@ -706,6 +727,7 @@ int rtw_render_frames(rtw_scene* scene, const rtw_camera* cam, const rtw_render_
 
 int rtw_resolve_device(float* d_rgb, uint64_t n_pixels, uint32_t total_samples, float gamma, int device, void* stream) {
     if (!d_rgb || total_samples == 0 || !(gamma > 0.0f)) return fail(RTW_E_INVALID, "bad resolve arguments");
+    DeviceGuard guard;
     if (device >= 0) CK(cudaSetDevice(device));
     const unsigned long long n = n_pixels * 3ull;
     resolve_kernel<<<grid_for(n, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(d_rgb, n, (float)total_samples, 1.0f / gamma);
@@ -715,6 +737,7 @@ int rtw_resolve_device(float* d_rgb, uint64_t n_pixels, uint32_t total_samples, 
 
 int rtw_quantize_device(const float* d_rgb, uint8_t* d_rgb8, uint64_t n_values, int device, void* stream) {
     if (!d_rgb || !d_rgb8) return fail(RTW_E_INVALID, "null argument");
+    DeviceGuard guard;
     if (device >= 0) CK(cudaSetDevice(device));
     quantize_kernel<<<grid_for(n_values, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(d_rgb, d_rgb8, n_values);
     CK(cudaGetLastError());
@@ -748,6 +771,7 @@ int set_instance_level(rtw_scene* s, uint32_t k, const Level& lv) {
 
 int rtw_scene_rebuild_lbvh(rtw_scene* s, float* out_build_ms) {
     if (!s) return fail(RTW_E_INVALID, "null argument");
+    DeviceGuard guard;
     CK(cudaSetDevice(s->device));
     uint32_t extra = 0;
     for (const auto& lv : s->lb_levels) if (lv.count >= 2u) extra += lv.count - 1u;
@@ -757,13 +781,19 @@ int rtw_scene_rebuild_lbvh(rtw_scene* s, float* out_build_ms) {
     if (!s->lb_nodes) {
         // the node arrays grow once: SAH nodes stay in front (their references remain valid), the
         // rebuilt levels go behind them
-        CK(cached_alloc_t(&s->lb_nodes, n_total * sizeof(Node)));
-        CK(cached_alloc_t(&s->lb_nodes16, n_total * sizeof(Node16)));
+        // all four blocks or none: a later call must not find lb_nodes set and the others missing
+        cudaError_t ae = cached_alloc_t(&s->lb_nodes, n_total * sizeof(Node));
+        if (ae == cudaSuccess) ae = cached_alloc_t(&s->lb_nodes16, n_total * sizeof(Node16));
+        if (ae == cudaSuccess) ae = cached_alloc_t(&s->lb_leaves_d, s->lb_leaves_h.size() * sizeof(LbvhLeaf));
+        if (ae == cudaSuccess) ae = cached_alloc_t(&s->lb_out_d, s->lb_levels.size() * sizeof(LbvhLevelOut));
+        if (ae != cudaSuccess) {
+            cached_free(s->lb_nodes); cached_free(s->lb_nodes16); cached_free(s->lb_leaves_d); cached_free(s->lb_out_d);
+            s->lb_nodes = nullptr; s->lb_nodes16 = nullptr; s->lb_leaves_d = nullptr; s->lb_out_d = nullptr;
+            return cuda_fail(ae, "LBVH node arrays");
+        }
         CK(cudaMemcpy(s->lb_nodes, s->d.nodes, (size_t)s->n_sah_nodes * sizeof(Node), cudaMemcpyDeviceToDevice));
         CK(cudaMemcpy(s->lb_nodes16, s->d.nodes16, (size_t)s->n_sah_nodes * sizeof(Node16), cudaMemcpyDeviceToDevice));
-        CK(cached_alloc_t(&s->lb_leaves_d, s->lb_leaves_h.size() * sizeof(LbvhLeaf)));
         CK(cudaMemcpy(s->lb_leaves_d, s->lb_leaves_h.data(), s->lb_leaves_h.size() * sizeof(LbvhLeaf), cudaMemcpyHostToDevice));
-        CK(cached_alloc_t(&s->lb_out_d, s->lb_levels.size() * sizeof(LbvhLevelOut)));
         s->info.device_bytes += n_total * (sizeof(Node) + sizeof(Node16)) + s->lb_leaves_h.size() * sizeof(LbvhLeaf);
         s->d.nodes = s->lb_nodes; s->d.nodes16 = s->lb_nodes16;
     }
@@ -810,6 +840,7 @@ int rtw_scene_rebuild_lbvh(rtw_scene* s, float* out_build_ms) {
 
 int rtw_scene_use_sah(rtw_scene* s) {
     if (!s) return fail(RTW_E_INVALID, "null argument");
+    DeviceGuard guard;
     CK(cudaSetDevice(s->device));
     CK(cudaStreamSynchronize(s->stream));
     s->top_all = s->sah_top; s->d.top = s->sah_top; s->top_inside = s->sah_top_inside;
@@ -823,6 +854,7 @@ int rtw_scene_use_sah(rtw_scene* s) {
 int rtw_quantize(const float* rgb, uint8_t* rgb8, uint64_t n_values, int device) {
     if (!rgb || !rgb8) return fail(RTW_E_INVALID, "null argument");
     if (n_values == 0) return RTW_OK;
+    DeviceGuard guard;
     if (device >= 0) CK(cudaSetDevice(device));
     float* d_in = nullptr; uint8_t* d_out = nullptr;
     cudaError_t e = cached_alloc_t(&d_in, n_values * sizeof(float));
@@ -848,6 +880,7 @@ int rtw_bilateral_filter_device(const uint8_t* d_rgb8, uint32_t width, uint32_t 
     if (width < 2u || height < 2u || width > 32768u || height > 32768u) return fail(RTW_E_INVALID, "bilateral filter: image must be 2..32768 pixels a side");
     if (proximity != RTW_PROX_SQUARE && proximity != RTW_PROX_EDGES) return fail(RTW_E_INVALID, "unknown proximity type");
     if (size > 4096u) return fail(RTW_E_INVALID, "bilateral filter: window size > 4096");
+    DeviceGuard guard;
     if (device >= 0) CK(cudaSetDevice(device));
     int launches = 0;
     cudaError_t e = bilateral_filter_enqueue(d_rgb8, width, height, size, proximity, d_out_rgb8, d_params,
@@ -860,6 +893,7 @@ int rtw_bilateral_filter(const uint8_t* rgb8, uint32_t width, uint32_t height, u
                          uint8_t* out_rgb8, float* out_params, float* out_kernel_ms, int device) {
     if (!rgb8 || !out_rgb8) return fail(RTW_E_INVALID, "null argument");
     if (width < 2u || height < 2u || width > 32768u || height > 32768u) return fail(RTW_E_INVALID, "bilateral filter: image must be 2..32768 pixels a side");
+    DeviceGuard guard;
     if (device >= 0) CK(cudaSetDevice(device));
     const size_t n = (size_t)width * height * 3u;
     uint8_t* d_buf = nullptr; float* d_par = nullptr;
@@ -891,6 +925,7 @@ int rtw_bilateral_filter(const uint8_t* rgb8, uint32_t width, uint32_t height, u
 int rtw_render_rgb8(rtw_scene* scene, const rtw_camera* cam, const rtw_render_opts* opts, uint8_t* out_rgb8) {
     if (!scene || !cam || !opts || !out_rgb8) return fail(RTW_E_INVALID, "null argument");
     if (opts->output != RTW_OUT_RESOLVED) return fail(RTW_E_INVALID, "rtw_render_rgb8 needs RTW_OUT_RESOLVED");
+    DeviceGuard guard;
     CK(cudaSetDevice(scene->device));
     const uint32_t rows = opts->row_count ? opts->row_count : cam->height;
     const size_t n_values = (size_t)rows * cam->width * 3u;
@@ -919,6 +954,7 @@ int rtw_get_stats(rtw_scene* scene, rtw_stats* out) {
     if (!scene || !out) return fail(RTW_E_INVALID, "null argument");
     std::memset(out, 0, sizeof *out);
     if (!scene->have_stats) return RTW_OK;
+    DeviceGuard guard;
     CK(cudaSetDevice(scene->device));
     CK(cudaEventSynchronize(scene->ev2));
     out->paths = scene->last_wavefront ? scene->wf_paths : scene->h_ctr->paths; out->rays = scene->h_ctr->rays; out->nan_paths = scene->h_ctr->nan_paths;
@@ -948,6 +984,7 @@ int rtw_get_sched_stats(rtw_scene* scene, uint64_t out[14]) {
     if (!scene || !out) return fail(RTW_E_INVALID, "null argument");
     std::memset(out, 0, 14 * sizeof(uint64_t));
     if (!scene->have_stats) return RTW_OK;
+    DeviceGuard guard;
     CK(cudaSetDevice(scene->device));
     CK(cudaEventSynchronize(scene->ev2));
     out[0] = scene->h_ctr->sched_iters;
@@ -958,6 +995,7 @@ int rtw_get_sched_stats(rtw_scene* scene, uint64_t out[14]) {
 
 int rtw_microbench(int device, int which, int reps, double* out_value) {
     if (!out_value || reps < 1) return fail(RTW_E_INVALID, "bad microbench arguments");
+    DeviceGuard guard;
     if (device >= 0) CK(cudaSetDevice(device));
     int sms = 0, dev = 0;
     CK(cudaGetDevice(&dev));
