@@ -79,19 +79,27 @@ def test_headline_frame_accounting_and_luminance(cuda):
     assert med < 0.03 * b + 1e-3, (med, b)
 
 
-@pytest.mark.parametrize("name", ["C1", "C2", "C3"])
-def test_converged_image_agrees_with_the_oracle(name, oracle, cuda):
-    """SURVEY 8d parity level L2 / north_star: the default (fast) kernels at 16 384 spp against the CPU
-    oracle at 4 096 spp, same scene and camera at 64x36, different arithmetic and sample streams: mean
-    luminance within 0.5 %, RMSE of the tone-mapped ([0,1]-clipped, gamma 2) images <= 0.02 (PSNR >= 34 dB),
-    pixels that are non-finite in either image (N8, N12) masked — and the same pixels must be masked
-    almost everywhere (the Perlin sphere's negative albedo is reference behaviour, not noise)."""
+# (config, width, height, oracle spp): the oracle's own Monte-Carlo noise has to stay below the RMSE bound, and it
+# differs by scene: two independent 1024-spp oracle renders of C4 (small light, long paths) differ by 0.053 RMSE, of
+# C5 by 0.031 (measured in the build container), i.e. 0.037 / 0.022 each - so C4 gets 8192 spp and C5 2048.
+L2_CASES = [("C1", 160, 90, 4096), ("C2", 160, 90, 4096), ("C3", 160, 90, 4096), ("C4", 64, 64, 8192), ("C5", 64, 64, 2048)]
+
+
+@pytest.mark.parametrize("name,w,h,ospp", L2_CASES, ids=[c[0] for c in L2_CASES])
+def test_converged_image_agrees_with_the_oracle(name, w, h, ospp, cuda):
+    """SURVEY 8d parity level L2 / north_star, every config directly against the oracle: the default (fast) kernels
+    at 16 384 spp (C5: 32 768, C4: 65 536) against the CPU oracle at `ospp`, same scene and camera, different arithmetic
+    and sample streams: mean luminance within 0.5 %, RMSE of the tone-mapped ([0,1]-clipped, gamma 2) images
+    <= 0.02 (PSNR >= 34 dB), pixels that are non-finite in either image (N8, N12) masked - and the same pixels
+    must be masked almost everywhere (the Perlin sphere's negative albedo is reference behaviour, not noise)."""
+    from oracle_backend import OracleBackend
+    oracle = OracleBackend(threads=0, fast=True)          # -O3 build of the same restatement (what bench.py times)
     job = scenes.CONFIGS[name]()
     vp = job.viewport
-    nv = type(vp).new_from_res(64, 36, 4096, vp.depth, vp.gamma, vp.vfov, vp.origin, vp.direction, vp.vup, None, vp.lens_radius)
+    nv = type(vp).new_from_res(w, h, ospp, vp.depth, vp.gamma, vp.vfov, vp.origin, vp.direction, vp.vup, None, vp.lens_radius)
     nv.shutter_speed, nv.fps, nv.frame = vp.shutter_speed, vp.fps, vp.frame
     ref = nv._run(job.ray_color, job.scene, job.mode, oracle)
-    nv.samples, nv.seed = 16384, 7
+    nv.samples, nv.seed = (65536 if name == "C4" else 32768 if name == "C5" else 16384), 7
     got = nv._run(job.ray_color, job.scene, job.mode, cuda)
     fr, fg = np.isfinite(ref).all(-1), np.isfinite(got).all(-1)
     assert (fr == fg).mean() > 0.97
