@@ -349,7 +349,11 @@ int rtw_microbench(int device, int which, int reps, double* out_value);
 typedef struct rtw_scene_info {
     uint32_t n_tlas_nodes, n_blas_nodes, n_tlas_leaves, n_flattened_instances;
     uint32_t bvh_max_depth;
-    uint64_t device_bytes;
+    uint32_t n_baked_instances;        /* rigidly placed surface instances whose primitives the fast kernels walk as
+                                        * world-space copies in the top level (same closest hit; rtw_host.h) */
+    uint64_t device_bytes;             /* device memory held by the scene: scene arrays, textures and (after the first
+                                        * wavefront render) the path pool */
+    uint64_t h2d_bytes;                /* bytes rtw_scene_create copied host -> device (scene arrays + texels) */
 } rtw_scene_info;
 int rtw_scene_get_info(rtw_scene* scene, rtw_scene_info* out);
 

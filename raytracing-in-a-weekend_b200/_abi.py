@@ -93,7 +93,8 @@ class rtw_stats(C.Structure):
 
 class rtw_scene_info(C.Structure):
     _fields_ = [("n_tlas_nodes", u32), ("n_blas_nodes", u32), ("n_tlas_leaves", u32),
-                ("n_flattened_instances", u32), ("bvh_max_depth", u32), ("device_bytes", u64)]
+                ("n_flattened_instances", u32), ("bvh_max_depth", u32), ("n_baked_instances", u32), ("device_bytes", u64),
+                ("h2d_bytes", u64)]
 
 
 # every symbol include/rtw.h declares: name -> (restype, argtypes)

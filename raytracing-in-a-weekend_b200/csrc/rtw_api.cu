@@ -245,19 +245,25 @@ namespace rtw { void set_last_error(const std::string& msg) { g_err = msg; } }  
 struct rtw_scene {
     int device = 0;
     int sm_count = 0;
-    int occ_fast = 0, occ_strict = 0, occ_count = 0;
-    uint32_t stack_words = 0;
-    size_t smem_bytes = 0;
+    // Traversal stack depth, per kernel family: [0] what the fast / count kernels walk (baked top levels: usually no
+    // instance levels at all), [1] the reference's structure (strict kernels, RTW_NO_BAKE, rebuilt LBVH levels)
+    uint32_t stack_words[2] = {0, 0};
+    size_t smem_bytes[2] = {0, 0};
+    int occ_mega[3][2] = {};              // [variant][stack kind]
+    int cur_stack = 1;                    // stack kind of the current render
     Scene d{};                            // device pointers
     Scene d_cur{};                        // what the current render walks: d, or d with top = top_inside
-    Level top_all{}, top_inside{};
+    Level tops[4] = {};                   // [0] the reference's structure, [1] without enclosing volumes, [2] / [3] the same with baked instances (rtw_host.h)
+    bool has_baked = false;
+    uint32_t n_walked_instances_baked = 0;
     // optional on-device LBVH rebuild (rtw_lbvh.h): the leaves of every level, the node arrays with
     // room for the rebuilt levels behind the SAH nodes, and the SAH levels to go back to
     std::vector<LbvhLeaf> lb_leaves_h;
     std::vector<LbvhLevelDesc> lb_levels;
     std::vector<Level> sah_inst_levels;       // per instance
-    Level sah_top{}, sah_top_inside{};
+    Level sah_tops[4] = {};
     uint32_t sah_top_depth = 0, sah_inner_depth = 0, n_sah_nodes = 0;
+    uint32_t sah_stack_words[2] = {0, 0};
     LbvhLeaf* lb_leaves_d = nullptr;
     Node* lb_nodes = nullptr; Node16* lb_nodes16 = nullptr;
     LbvhLevelOut* lb_out_d = nullptr;
@@ -277,11 +283,12 @@ struct rtw_scene {
     // wavefront pipeline state (allocated on first use)
     WfPool pool{};
     uint32_t n_walked_instances = 0;      // instance leaves of the top level that are walked as a level (not one-sphere records)
+    uint32_t cur_walked_instances = 0;    // ... of the top level the current render walks
     uint32_t pool_allocated = 0;          // slots the pool arrays hold; pool.capacity = slots the current render uses
     WfCounters* d_wc = nullptr;
     WfCounters* h_wc = nullptr;           // pinned, 4 slots
     cudaEvent_t wf_ev[4] = {nullptr, nullptr, nullptr, nullptr};
-    int occ_wf[3] = {0, 0, 0};
+    int occ_wf[3][2] = {};
     bool last_wavefront = false;
     uint64_t wf_paths = 0, wf_iterations = 0;
     static const int kTimed = 32;             // sampled (extend, shade) launches timed with events per render
@@ -324,7 +331,7 @@ int upload(rtw_scene* s, const std::vector<T>& v, const T** out) {
     CK(cached_alloc(&p, bytes));
     s->allocs.push_back(p);
     s->info.device_bytes += bytes;
-    if (!v.empty()) CK(cudaMemcpy(p, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice));
+    if (!v.empty()) { CK(cudaMemcpy(p, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice)); s->info.h2d_bytes += v.size() * sizeof(T); }
     *out = static_cast<const T*>(p);
     return RTW_OK;
 }
@@ -345,6 +352,7 @@ int upload_scene(rtw_scene* s, HostScene& hs) {
         CK(cached_texture(t.width, t.height, &ct));
         s->texs.push_back(ct);
         s->info.device_bytes += (uint64_t)t.n_texels * sizeof(float4);
+        s->info.h2d_bytes += (uint64_t)t.n_texels * sizeof(float4);
         CK(cudaMemcpy2DToArray(ct.arr, 0, 0, hs.texels[i].data(), t.width * sizeof(float4), t.width * sizeof(float4),
                                t.height, cudaMemcpyHostToDevice));
         t.obj = ct.obj;
@@ -365,12 +373,16 @@ int upload_scene(rtw_scene* s, HostScene& hs) {
     if ((rc = upload(s, hs.materials, &d.materials))) return rc;
     if ((rc = upload(s, hs.textures, &d.textures))) return rc;
     if ((rc = upload(s, hs.noises, &d.noises))) return rc;
+    if ((rc = upload(s, hs.baked_sphere_src, &d.baked_sphere_src))) return rc;
+    if ((rc = upload(s, hs.baked_quad_src, &d.baked_quad_src))) return rc;
+    d.n_spheres_orig = hs.n_spheres_orig; d.n_quads_orig = hs.n_quads_orig;
     d.top = hs.top;
-    s->top_all = hs.top; s->top_inside = hs.top_inside; s->enclosing = hs.enclosing;
+    s->tops[0] = hs.top; s->tops[1] = hs.top_inside; s->tops[2] = hs.top_baked; s->tops[3] = hs.top_baked_inside;
+    s->has_baked = hs.has_baked; s->n_walked_instances_baked = hs.n_walked_instances_baked;
+    s->enclosing = hs.enclosing;
     s->lb_leaves_h = hs.lbvh_leaves; s->lb_levels = hs.lbvh_levels;
-    s->n_walked_instances = 0;
-    for (const auto& lv : hs.lbvh_levels) if (lv.owner >= 0 && !(hs.instances[lv.owner].flags & INST_ONE_SPHERE)) ++s->n_walked_instances;
-    s->sah_top = hs.top; s->sah_top_inside = hs.top_inside;
+    s->n_walked_instances = hs.n_walked_instances;
+    for (int k = 0; k < 4; ++k) s->sah_tops[k] = s->tops[k];
     s->sah_inst_levels.resize(hs.instances.size());
     for (size_t k = 0; k < hs.instances.size(); ++k) s->sah_inst_levels[k] = hs.instances[k].level;
     s->sah_top_depth = hs.top_depth; s->sah_inner_depth = hs.inner_depth; s->n_sah_nodes = (uint32_t)hs.nodes.size();
@@ -394,11 +406,11 @@ uint32_t refill_below_default() {
 MegaLaunch plan_mega(const rtw_scene* s, const RenderParams& P, int variant) {
     MegaLaunch L;
     L.block = RTW_MEGA_BLOCK;
-    int occ = variant == 1 ? s->occ_strict : variant == 2 ? s->occ_count : s->occ_fast;
+    int occ = s->occ_mega[variant][s->cur_stack];
     if (occ < 1) occ = 1;
     L.grid = s->sm_count * occ;
-    L.stack_words = s->stack_words;
-    L.smem_bytes = s->smem_bytes;
+    L.stack_words = s->stack_words[s->cur_stack];
+    L.smem_bytes = s->smem_bytes[s->cur_stack];
     L.refill_below = refill_below_default();
     L.tiles_x = (P.cam.width + 7u) / 8u;
     L.tiles_y = (P.row_count + 3u) / 4u;
@@ -421,6 +433,25 @@ MegaLaunch plan_mega(const rtw_scene* s, const RenderParams& P, int variant) {
 uint32_t env_u32(const char* name, uint32_t dflt) {
     const char* e = std::getenv(name);
     return e ? (uint32_t)std::strtoul(e, nullptr, 10) : dflt;
+}
+
+// The occupancies depend on the dynamic shared memory (the stack columns). Largest size first: the attribute
+// cudaFuncAttributeMaxDynamicSharedMemorySize the queries set must end up covering every launch.
+int refresh_mega_occupancy(rtw_scene* s) {
+    for (int k = 0; k < 2; ++k) {          // stack_words[0] <= stack_words[1]
+        CK(mega_occupancy_fast(&s->occ_mega[0][k], s->smem_bytes[k]));
+        CK(mega_occupancy_strict(&s->occ_mega[1][k], s->smem_bytes[k]));
+        CK(mega_occupancy_count(&s->occ_mega[2][k], s->smem_bytes[k]));
+    }
+    return RTW_OK;
+}
+int refresh_wf_occupancy(rtw_scene* s) {
+    for (int k = 0; k < 2; ++k) {
+        CK(wf_extend_occupancy_fast(&s->occ_wf[0][k], s->smem_bytes[k]));
+        CK(wf_extend_occupancy_strict(&s->occ_wf[1][k], s->smem_bytes[k]));
+        CK(wf_extend_occupancy_count(&s->occ_wf[2][k], s->smem_bytes[k]));
+    }
+    return RTW_OK;
 }
 
 template <class T>
@@ -459,9 +490,8 @@ int ensure_pool(rtw_scene* s, unsigned long long n_paths) {
         CK(cached_alloc_t(&s->h_wc, 4 * sizeof(WfCounters), true));
         for (auto& e : s->wf_ev) CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
         for (auto& t : s->wf_t) for (auto& e : t) CK(cudaEventCreate(&e));
-        CK(wf_extend_occupancy_fast(&s->occ_wf[0], s->smem_bytes));
-        CK(wf_extend_occupancy_strict(&s->occ_wf[1], s->smem_bytes));
-        CK(wf_extend_occupancy_count(&s->occ_wf[2], s->smem_bytes));
+        int rc2 = refresh_wf_occupancy(s);
+        if (rc2) return rc2;
     }
     s->pool.capacity = cap;
     return RTW_OK;
@@ -476,21 +506,21 @@ int enqueue_wavefront(rtw_scene* s, const RenderParams& P, int variant, float* d
     WfLaunch L{};
     L.tiles_x = (P.cam.width + 7u) / 8u;
     L.tiles_y = (P.row_count + 3u) / 4u;
-    L.stack_words = s->stack_words;
-    L.smem_bytes = s->smem_bytes;
+    L.stack_words = s->stack_words[s->cur_stack];
+    L.smem_bytes = s->smem_bytes[s->cur_stack];
     L.fetch_min = std::min(32u, std::max(1u, env_u32("RTW_WF_FETCH_MIN", 16u)));
     L.chunk = std::max(32u, env_u32("RTW_WF_CHUNK", 64u));
     L.supply_chunk = std::max(32u, env_u32("RTW_WF_SUPPLY_CHUNK", 256u)) & ~31u;
     L.sample_major = env_u32("RTW_WF_SAMPLE_MAJOR", 0u) ? 1u : 0u;
     L.index32 = ((unsigned long long)L.tiles_x * L.tiles_y * P.sample_count < (1ull << 32)) ? 1u : 0u;
     CK(cudaMemsetAsync(s->pool.supply, 0, (size_t)s->pool.capacity / 16u * sizeof(unsigned long long), st));
-    L.extend_grid = s->sm_count * std::max(1, std::min(s->occ_wf[variant], (int)env_u32("RTW_WF_MAX_BLOCKS", 64u)));
+    L.extend_grid = s->sm_count * std::max(1, std::min(s->occ_wf[variant][s->cur_stack], (int)env_u32("RTW_WF_MAX_BLOCKS", 64u)));
     L.shade_grid = (int)(s->pool.capacity / RTW_WF_SHADE_BLOCK);
     WfCounters init{};
     init.total_paths = 32ull * L.tiles_x * L.tiles_y * P.sample_count;
     L.total_paths = init.total_paths;
     {
-        const bool events_rare = (unsigned long long)s->n_walked_instances * 16ull <= (unsigned long long)s->info.n_tlas_leaves;
+        const bool events_rare = (unsigned long long)s->cur_walked_instances * 16ull <= (unsigned long long)s->info.n_tlas_leaves;
         L.prim_w = std::max(1u, env_u32("RTW_WF_PRIM_W", events_rare ? 8u : 4u));
         L.event_w = std::max(1u, env_u32("RTW_WF_EVENT_W", events_rare ? 8u : 4u));   // (16 before one-sphere instances joined the event steps)
     }
@@ -557,6 +587,12 @@ int enqueue_render(rtw_scene* s, const rtw_camera* cam, const rtw_render_opts* o
     // shutter interval stay inside each of them, no ray of this render starts outside => they cannot
     // return a hit (instance.rs:280-300) and the fast kernels walk the top level built without them.
     s->d_cur = s->d;
+    s->d_cur.top = s->tops[0];
+    // the fast kernels walk the top level with baked instances (rtw_host.h) unless RTW_NO_BAKE=1
+    const int baked = (variant != 1 && s->has_baked && !env_u32("RTW_NO_BAKE", 0u)) ? 2 : 0;
+    s->d_cur.top = s->tops[baked];
+    s->cur_walked_instances = baked ? s->n_walked_instances_baked : s->n_walked_instances;
+    s->cur_stack = (variant != 1 && (baked || !s->has_baked)) ? 0 : 1;
     if (variant != 1 && !s->enclosing.empty() && !env_u32("RTW_KEEP_ENCLOSING", 0u)) {
         const float lens = std::fabs(cam->lens_radius) *
                            (std::sqrt(cam->u[0] * cam->u[0] + cam->u[1] * cam->u[1] + cam->u[2] * cam->u[2]) +
@@ -568,7 +604,7 @@ int enqueue_render(rtw_scene* s, const rtw_camera* cam, const rtw_render_opts* o
             for (int a = 0; a < 3; ++a) { const float x = cam->origin[a] - e.c[a]; d2 += x * x; }
             if (!(std::sqrt(d2) + lens < e.r) || !(e.mov_far + e.mov_speed * tmax < e.r)) inside = false;
         }
-        if (inside) s->d_cur.top = s->top_inside;
+        if (inside) s->d_cur.top = s->tops[baked + 1];
     }
     MegaLaunch L = plan_mega(s, P, variant);
     if ((uint64_t)L.tiles_x * L.tiles_y * L.n_chunks > 0xFFFFFFF0ull) return fail(RTW_E_UNSUPPORTED, "too many work items; shard the render");
@@ -666,16 +702,16 @@ int rtw_scene_create(const rtw_scene_desc* desc, int device, rtw_scene** out) {
     if (!s) return fail(RTW_E_NOMEM, "out of host memory");
     s->device = device;
     s->info = hs.info;
-    s->info.device_bytes = 0;
+    s->info.device_bytes = 0; s->info.h2d_bytes = 0;
     auto bail = [&](int code) { delete s; return code; };
     if ((rc = upload_scene(s, hs))) return bail(rc);
     cudaError_t ce;
     if ((ce = cudaDeviceGetAttribute(&s->sm_count, cudaDevAttrMultiProcessorCount, device)) != cudaSuccess) return bail(cuda_fail(ce, "sm count"));
-    s->stack_words = stack_words(hs.top_depth, hs.inner_depth);
-    s->smem_bytes = (size_t)s->stack_words * RTW_MEGA_BLOCK * sizeof(uint32_t);
-    if ((ce = mega_occupancy_fast(&s->occ_fast, s->smem_bytes)) != cudaSuccess) return bail(cuda_fail(ce, "occupancy(fast)"));
-    if ((ce = mega_occupancy_strict(&s->occ_strict, s->smem_bytes)) != cudaSuccess) return bail(cuda_fail(ce, "occupancy(strict)"));
-    if ((ce = mega_occupancy_count(&s->occ_count, s->smem_bytes)) != cudaSuccess) return bail(cuda_fail(ce, "occupancy(count)"));
+    s->stack_words[1] = hs.any_levels ? stack_words(hs.top_depth, hs.inner_depth) : stack_words_flat(hs.top_depth);
+    s->stack_words[0] = hs.fast_levels ? stack_words(hs.fast_top_depth, hs.fast_inner_depth) : stack_words_flat(hs.fast_top_depth);
+    if (s->stack_words[0] > s->stack_words[1]) s->stack_words[0] = s->stack_words[1];
+    for (int k = 0; k < 2; ++k) { s->sah_stack_words[k] = s->stack_words[k]; s->smem_bytes[k] = (size_t)s->stack_words[k] * RTW_MEGA_BLOCK * sizeof(uint32_t); }
+    if ((rc = refresh_mega_occupancy(s))) return bail(rc);
     if ((ce = cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking)) != cudaSuccess) return bail(cuda_fail(ce, "stream"));
     if ((ce = cudaEventCreate(&s->ev0)) != cudaSuccess || (ce = cudaEventCreate(&s->ev1)) != cudaSuccess ||
         (ce = cudaEventCreate(&s->ev2)) != cudaSuccess) return bail(cuda_fail(ce, "events"));
@@ -749,16 +785,12 @@ namespace {
 int refresh_launch_limits(rtw_scene* s, uint32_t top_depth, uint32_t inner_depth) {
     const uint32_t words = stack_words(top_depth, inner_depth);
     if (words > 160u) return fail(RTW_E_UNSUPPORTED, "BVH deeper than the traversal stack");
-    s->stack_words = words;
-    s->smem_bytes = (size_t)words * RTW_MEGA_BLOCK * sizeof(uint32_t);
-    CK(mega_occupancy_fast(&s->occ_fast, s->smem_bytes));
-    CK(mega_occupancy_strict(&s->occ_strict, s->smem_bytes));
-    CK(mega_occupancy_count(&s->occ_count, s->smem_bytes));
-    if (s->d_wc) {
-        CK(wf_extend_occupancy_fast(&s->occ_wf[0], s->smem_bytes));
-        CK(wf_extend_occupancy_strict(&s->occ_wf[1], s->smem_bytes));
-        CK(wf_extend_occupancy_count(&s->occ_wf[2], s->smem_bytes));
-    }
+    // rebuilt levels: one bound for both kernel families (the optional LBVH path is not tuned per family)
+    s->stack_words[0] = s->stack_words[1] = words;
+    s->smem_bytes[0] = s->smem_bytes[1] = (size_t)words * RTW_MEGA_BLOCK * sizeof(uint32_t);
+    int rc = refresh_mega_occupancy(s);
+    if (rc) return rc;
+    if (s->d_wc && (rc = refresh_wf_occupancy(s))) return rc;
     return RTW_OK;
 }
 int set_instance_level(rtw_scene* s, uint32_t k, const Level& lv) {
@@ -827,11 +859,10 @@ int rtw_scene_rebuild_lbvh(rtw_scene* s, float* out_build_ms) {
     for (size_t i = 0; i < s->lb_levels.size(); ++i) {
         const LbvhLevelDesc& lv = s->lb_levels[i];
         if (lv.count < 2u) continue;
-        Level L = lv.owner == -1 ? s->sah_top : lv.owner == -2 ? s->sah_top_inside : s->sah_inst_levels[lv.owner];
+        Level L = lv.owner < 0 ? s->sah_tops[-1 - lv.owner] : s->sah_inst_levels[lv.owner];
         L.root = out[i].root;
         for (int a = 0; a < 3; ++a) { L.lo[a] = out[i].lo[a]; L.hi[a] = out[i].hi[a]; }
-        if (lv.owner == -1) { s->top_all = L; s->d.top = L; }
-        else if (lv.owner == -2) s->top_inside = L;
+        if (lv.owner < 0) { s->tops[-1 - lv.owner] = L; if (lv.owner == -1) s->d.top = L; }
         else if ((rc = set_instance_level(s, (uint32_t)lv.owner, L))) return rc;
     }
     CK(cudaStreamSynchronize(s->stream));
@@ -843,12 +874,16 @@ int rtw_scene_use_sah(rtw_scene* s) {
     DeviceGuard guard;
     CK(cudaSetDevice(s->device));
     CK(cudaStreamSynchronize(s->stream));
-    s->top_all = s->sah_top; s->d.top = s->sah_top; s->top_inside = s->sah_top_inside;
+    for (int k = 0; k < 4; ++k) s->tops[k] = s->sah_tops[k];
+    s->d.top = s->sah_tops[0];
     int rc;
     for (const auto& lv : s->lb_levels)
         if (lv.owner >= 0 && (rc = set_instance_level(s, (uint32_t)lv.owner, s->sah_inst_levels[lv.owner]))) return rc;
     CK(cudaStreamSynchronize(s->stream));
-    return refresh_launch_limits(s, s->sah_top_depth, s->sah_inner_depth);
+    for (int k = 0; k < 2; ++k) { s->stack_words[k] = s->sah_stack_words[k]; s->smem_bytes[k] = (size_t)s->stack_words[k] * RTW_MEGA_BLOCK * sizeof(uint32_t); }
+    int rc2 = refresh_mega_occupancy(s);
+    if (rc2) return rc2;
+    return s->d_wc ? refresh_wf_occupancy(s) : (int)RTW_OK;
 }
 
 int rtw_quantize(const float* rgb, uint8_t* rgb8, uint64_t n_values, int device) {

@@ -196,6 +196,12 @@ struct Scene {
     Level top;
     float background[3];
     uint32_t n_noises;
+    // Baked instances (rtw_host.h): world-space copies of the primitives of rigidly placed surface instances sit
+    // behind the scene's own spheres / quads (index >= n_*_orig); *_src[index - n_*_orig] = (instance reference,
+    // reference of the primitive inside it), which is what a search result names (trav_result).
+    uint32_t n_spheres_orig, n_quads_orig;
+    const uint2* baked_sphere_src;
+    const uint2* baked_quad_src;
 };
 
 // ------------------------------------------------------------------ Vec3::rotated (vec3.rs:161-181)

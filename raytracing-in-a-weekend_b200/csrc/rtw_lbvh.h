@@ -31,7 +31,7 @@ struct LbvhLeaf {          // one traversable leaf of a level: reference + its r
 };
 struct LbvhLevelDesc {     // a level's range in the concatenated leaf array
     uint32_t first, count;
-    int32_t owner;         // -1: scene top level, -2: top level without enclosing volumes, k >= 0: instance k
+    int32_t owner;         // -1: scene top level, -2: ... without enclosing volumes, -3 / -4: the same two with baked instances, k >= 0: instance k
     uint32_t pad;
 };
 

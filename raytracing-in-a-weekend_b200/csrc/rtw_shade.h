@@ -314,7 +314,7 @@ RTW_HD bool segment_end(const TraceCtx& cx, const Noise* nt, const RenderParams&
     const Scene& sc = *cx.sc;
     const uint32_t ig = P.integrator;
     Ray ray; ray.o = T.o; ray.d = T.d; ray.time = p.ray.time;      // back in the world frame
-    const Best b = trav_result(T);
+    const Best b = trav_result(sc, T);
     if (b.ref == REF_NONE) {                                        // miss
         V3 bg;
         if (ig == RTW_INT_BG_COLOR || ig == RTW_INT_ALBEDO) bg = ld3(sc.background);   // ray_color.rs:91

@@ -179,6 +179,9 @@ struct Stack {
 // bottom sentinel + top pushes + world frame (10) + sentinel + probe frame (2 + sentinel) + inner pushes
 #define RTW_STACK 32   // deepest node chain the builder allows per level (scene_build.cpp)
 RTW_HD uint32_t stack_words(uint32_t top_depth, uint32_t inner_depth) { return top_depth + inner_depth + 16u; }
+// ... and when no instance is walked as a level (only primitives, baked copies and one-sphere records, which are
+// resolved in place): the bottom sentinel and the top level's pushes
+RTW_HD uint32_t stack_words_flat(uint32_t top_depth) { return top_depth + 4u; }
 
 static const uint32_t CUR_DONE = 0xFFFFFFFFu;   // nothing left to do
 static const uint32_t CUR_EXIT = 0xFFFFFFFEu;   // sentinel: the level being walked is exhausted
@@ -651,7 +654,21 @@ RTW_HD void trav_step_other(const TraceCtx& cx, float time, Trav& T, const Stack
     } while (T.cur >= NODE_LIMIT && T.cur != CUR_DONE);
 }
 
-RTW_HD Best trav_result(const Trav& T) { Best b; b.t = T.t; b.ref = T.ref; b.inner = T.inner; return b; }
+// The result of a finished search. A hit on the world-space copy of a baked instance primitive (rtw_host.h) is
+// reported as what it stands for - (instance, primitive inside it) - so the Hit is evaluated through the
+// instance's frame exactly as for a walked instance (instance.rs:257-307).
+RTW_HD Best trav_result(const Scene& sc, const Trav& T) {
+    Best b; b.t = T.t; b.ref = T.ref; b.inner = T.inner;
+    const uint32_t kind = ref_kind(b.ref);
+    if (kind == KIND_SPHERE && ref_index(b.ref) >= sc.n_spheres_orig) {
+        const uint2 src = RTW_LDG(&sc.baked_sphere_src[ref_index(b.ref) - sc.n_spheres_orig]);
+        b.ref = src.x; b.inner = src.y;
+    } else if (kind == KIND_QUAD && ref_index(b.ref) >= sc.n_quads_orig) {
+        const uint2 src = RTW_LDG(&sc.baked_quad_src[ref_index(b.ref) - sc.n_quads_orig]);
+        b.ref = src.x; b.inner = src.y;
+    }
+    return b;
+}
 
 // Scalar driver (host emulator, and any caller that does not schedule the steps itself).
 RTW_HD Best trace(const TraceCtx& cx, const Ray& r, const Stack& S) {
@@ -661,7 +678,7 @@ RTW_HD Best trace(const TraceCtx& cx, const Ray& r, const Stack& S) {
         if (T.cur < NODE_LIMIT) trav_step_node<true>(cx, T, S);
         else trav_step_other(cx, r.time, T, S);
     }
-    return trav_result(T);
+    return trav_result(*cx.sc, T);
 }
 
 // Instance::collision_normal's frame change for the Hit evaluation (instance.rs:257-258).

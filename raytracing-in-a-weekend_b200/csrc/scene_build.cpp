@@ -11,7 +11,9 @@
 //   Vec3::rotated        vec3.rs:161-181                     the Euler map (not a rotation for x/z)
 //   Viewport::new        viewport.rs:308-401                 camera basis
 #include <algorithm>
+#include <chrono>
 #include <cmath>
+#include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <limits>
@@ -36,9 +38,9 @@ inline void box_grow(Box& b, const Box& o) {
     for (int a = 0; a < 3; ++a) { b.lo[a] = minf(b.lo[a], o.lo[a]); b.hi[a] = maxf(b.hi[a], o.hi[a]); }
 }
 inline float box_area(const Box& b) {
-    double dx = (double)b.hi[0] - b.lo[0], dy = (double)b.hi[1] - b.lo[1], dz = (double)b.hi[2] - b.lo[2];
-    if (!(dx >= 0) || !(dy >= 0) || !(dz >= 0)) return 0.f;
-    return (float)(2.0 * (dx * dy + dy * dz + dz * dx));
+    const float dx = b.hi[0] - b.lo[0], dy = b.hi[1] - b.lo[1], dz = b.hi[2] - b.lo[2];
+    if (!(dx >= 0.f) || !(dy >= 0.f) || !(dz >= 0.f)) return 0.f;
+    return 2.0f * (dx * dy + dy * dz + dz * dx);
 }
 
 // two floats -> two IEEE halves in one word (first in the low half), rounded towards -inf / +inf
@@ -75,29 +77,35 @@ struct Builder {
     uint32_t max_pushes = 0;                           // deepest stack use of the level built last
     explicit Builder(std::vector<Node>& n) : nodes(n) {}
 
-    // Top-down SAH over [begin, end). Falls back to a median split when the remaining depth budget
-    // (RTW_STACK binary levels) gets tight. Returns a leaf REF, or BIN | binary node index.
-    uint32_t build(std::vector<BuildPrim>& p, size_t begin, size_t end, uint32_t depth, Box& out_box, bool& is_bin) {
-        size_t n = end - begin;
-        if (n == 1) { out_box = p[begin].box; is_bin = false; return p[begin].ref; }
+    // Top-down SAH over the primitives at positions [begin, end) of the three index lists `ord[axis]`, each of which
+    // holds the same primitives sorted by centroid along its axis (sorted once per level, partitioned stably on the
+    // way down: O(n log n) for the whole level instead of three sorts per node). Full sweep on every axis; falls
+    // back to a median split when the remaining depth budget (RTW_STACK binary levels) gets tight. Returns a leaf
+    // REF, or the index of the binary node.
+    std::vector<uint32_t> ord[3], part_tmp;
+    std::vector<uint8_t> side;
+    std::vector<float> right_area;
+    uint32_t build(const std::vector<BuildPrim>& p, size_t begin, size_t end, uint32_t depth, Box& out_box, bool& is_bin) {
+        const size_t n = end - begin;
+        if (n == 1) { const BuildPrim& q = p[ord[0][begin]]; out_box = q.box; is_bin = false; return q.ref; }
         Box cb = box_empty();
-        for (size_t i = begin; i < end; ++i)
-            for (int a = 0; a < 3; ++a) { cb.lo[a] = minf(cb.lo[a], p[i].c[a]); cb.hi[a] = maxf(cb.hi[a], p[i].c[a]); }
+        for (size_t i = begin; i < end; ++i) {
+            const BuildPrim& q = p[ord[0][i]];
+            for (int a = 0; a < 3; ++a) { cb.lo[a] = minf(cb.lo[a], q.c[a]); cb.hi[a] = maxf(cb.hi[a], q.c[a]); }
+        }
         uint32_t levels_needed = 1; while (((size_t)1 << levels_needed) < n) ++levels_needed;
-        bool force_median = depth + levels_needed + 2 >= (uint32_t)RTW_STACK;
+        const bool force_median = depth + levels_needed + 2 >= (uint32_t)RTW_STACK;
         int best_axis = -1; size_t best_k = 0; float best_cost = std::numeric_limits<float>::infinity();
         if (!force_median) {
-            std::vector<float> right_area(n);
             for (int axis = 0; axis < 3; ++axis) {
                 if (!(cb.hi[axis] > cb.lo[axis])) continue;
-                std::stable_sort(p.begin() + begin, p.begin() + end,
-                                 [axis](const BuildPrim& a, const BuildPrim& b) { return a.c[axis] < b.c[axis]; });
+                const uint32_t* o = ord[axis].data() + begin;
                 Box rb = box_empty();
-                for (size_t i = n; i-- > 1;) { box_grow(rb, p[begin + i].box); right_area[i] = box_area(rb); }
+                for (size_t i = n; i-- > 1;) { box_grow(rb, p[o[i]].box); right_area[i] = box_area(rb); }
                 Box lb = box_empty();
                 for (size_t k = 1; k < n; ++k) {
-                    box_grow(lb, p[begin + k - 1].box);
-                    float cost = box_area(lb) * (float)k + right_area[k] * (float)(n - k);
+                    box_grow(lb, p[o[k - 1]].box);
+                    const float cost = box_area(lb) * (float)k + right_area[k] * (float)(n - k);
                     if (cost < best_cost) { best_cost = cost; best_axis = axis; best_k = k; }
                 }
             }
@@ -107,10 +115,18 @@ struct Builder {
             for (int a = 0; a < 3; ++a) { float e = cb.hi[a] - cb.lo[a]; if (e > w) { w = e; axis = a; } }
             best_axis = axis; best_k = n / 2;
         }
-        std::stable_sort(p.begin() + begin, p.begin() + end,
-                         [best_axis](const BuildPrim& a, const BuildPrim& b) { return a.c[best_axis] < b.c[best_axis]; });
+        // the first best_k primitives of the chosen axis' order go left; the other two lists are partitioned stably
+        for (size_t i = 0; i < n; ++i) side[ord[best_axis][begin + i]] = i < best_k ? 0 : 1;
+        for (int axis = 0; axis < 3; ++axis) {
+            if (axis == best_axis) continue;
+            uint32_t* o = ord[axis].data() + begin;
+            size_t l = 0, r = 0;
+            for (size_t i = 0; i < n; ++i) { if (side[o[i]] == 0) o[l++] = o[i]; else part_tmp[r++] = o[i]; }
+            for (size_t i = 0; i < r; ++i) o[l + i] = part_tmp[i];
+        }
         uint32_t me = (uint32_t)bin.size();
         bin.emplace_back();
+        binflag.resize(bin.size() * 2, 0);
         Box b0, b1; bool bin0, bin1;
         uint32_t c0 = build(p, begin, begin + best_k, depth + 1, b0, bin0);
         uint32_t c1 = build(p, begin + best_k, end, depth + 1, b1, bin1);
@@ -230,14 +246,59 @@ struct Builder {
         return make_ref(KIND_NODE, me);
     }
 
+    // A level made of an already built level plus a few more leaves: nodes on top of its root, each holding the
+    // level below and up to three of the extra leaves. Used for the top level WITH the enclosing volumes, which
+    // differs from the one without them by those one or two leaves: one SAH build serves both.
+    Level wrap(const Level& inner, uint32_t inner_pushes, const std::vector<BuildPrim>& extra) {
+        Level lv = inner;
+        uint32_t pushes = inner_pushes;
+        const float inf = std::numeric_limits<float>::infinity();
+        for (size_t e = 0; e < extra.size();) {
+            Box cb[4]; uint32_t ref[4]; int n = 0;
+            if (lv.root != REF_NONE) {
+                for (int a = 0; a < 3; ++a) { cb[0].lo[a] = lv.lo[a]; cb[0].hi[a] = lv.hi[a]; }
+                ref[n++] = lv.root;
+            }
+            while (n < 4 && e < extra.size()) { cb[n] = extra[e].box; ref[n++] = extra[e].ref; ++e; }
+            if (n == 1) { lv.root = ref[0]; for (int a = 0; a < 3; ++a) { lv.lo[a] = cb[0].lo[a]; lv.hi[a] = cb[0].hi[a]; } continue; }
+            const uint32_t me = (uint32_t)nodes.size();
+            nodes.emplace_back();
+            float lo[3][4], hi[3][4]; uint32_t rf[4];
+            Box ub = box_empty();
+            for (int k = 0; k < 4; ++k) {
+                if (k < n) { for (int a = 0; a < 3; ++a) { lo[a][k] = cb[k].lo[a]; hi[a][k] = cb[k].hi[a]; } rf[k] = ref[k]; box_grow(ub, cb[k]); }
+                else { for (int a = 0; a < 3; ++a) { lo[a][k] = inf; hi[a][k] = inf; } rf[k] = REF_NONE; }
+            }
+            Node& nd = nodes[me];
+            nd.lox = make_float4(lo[0][0], lo[0][1], lo[0][2], lo[0][3]); nd.loy = make_float4(lo[1][0], lo[1][1], lo[1][2], lo[1][3]);
+            nd.loz = make_float4(lo[2][0], lo[2][1], lo[2][2], lo[2][3]); nd.hix = make_float4(hi[0][0], hi[0][1], hi[0][2], hi[0][3]);
+            nd.hiy = make_float4(hi[1][0], hi[1][1], hi[1][2], hi[1][3]); nd.hiz = make_float4(hi[2][0], hi[2][1], hi[2][2], hi[2][3]);
+            nd.ref = make_uint4(rf[0], rf[1], rf[2], rf[3]);
+            nd.pad = make_uint4(0u, 0u, 0u, 0u);
+            lv.root = make_ref(KIND_NODE, me);
+            for (int a = 0; a < 3; ++a) { lv.lo[a] = ub.lo[a]; lv.hi[a] = ub.hi[a]; }
+            pushes += (uint32_t)(n - 1);
+        }
+        max_pushes = pushes;
+        return lv;
+    }
+
     Level level(std::vector<BuildPrim>& prims, uint32_t mov_first, uint32_t mov_count) {
         Level lv; std::memset(&lv, 0, sizeof lv);
         lv.mov_first = mov_first; lv.mov_count = mov_count;
         max_pushes = 0;
         if (prims.empty()) { lv.root = REF_NONE; return lv; }
         bin.clear(); binflag.clear();
+        const size_t n = prims.size();
+        for (int axis = 0; axis < 3; ++axis) {
+            ord[axis].resize(n);
+            for (size_t i = 0; i < n; ++i) ord[axis][i] = (uint32_t)i;
+            std::stable_sort(ord[axis].begin(), ord[axis].end(),
+                             [&prims, axis](uint32_t a, uint32_t b) { return prims[a].c[axis] < prims[b].c[axis]; });
+        }
+        side.assign(n, 0); part_tmp.resize(n); right_area.resize(n);
         Box rb; bool is_bin;
-        uint32_t r = build(prims, 0, prims.size(), 0, rb, is_bin);
+        uint32_t r = build(prims, 0, n, 0, rb, is_bin);
         static const bool use_dp = [] { const char* e = std::getenv("RTW_BVH_COLLAPSE"); return e && std::string(e) == "dp"; }();
         if (is_bin && use_dp) { dp_solve(); lv.root = emit4_dp(r, max_pushes); }
         else lv.root = is_bin ? emit4(r, max_pushes) : r;
@@ -245,6 +306,63 @@ struct Builder {
         return lv;
     }
 };
+
+// Quad::new (quad.rs:93-105): the 64-byte record from origin, u, v
+Quad make_quad(V3 Q, V3 u, V3 v) {
+    V3 n = cross(u, v);                      // quad.rs:93
+    V3 normal = unit(n);                     // :99
+    float dd = dot(normal, Q);               // :100
+    V3 w = n / dot(n, n);                    // :101
+    Quad o;
+    o.q0 = make_float4(normal.x, normal.y, normal.z, dd);
+    o.q1 = make_float4(Q.x, Q.y, Q.z, u.x);
+    o.q2 = make_float4(u.y, u.z, v.x, v.y);
+    o.q3 = make_float4(v.z, w.x, w.y, w.z);
+    return o;
+}
+// qaabb.rs:19-61 + pad() :107-126 for a parallelogram; Rust2 triangle.rs:50-89 for a triangle
+Box quad_box(V3 Q, V3 u, V3 v, bool tri) {
+    V3 op = Q + u + v, vc = Q + v, uc = Q + u;
+    const float P4[4][3] = {{op.x, op.y, op.z}, {vc.x, vc.y, vc.z}, {uc.x, uc.y, uc.z}, {Q.x, Q.y, Q.z}};
+    Box b;
+    for (int a = 0; a < 3; ++a) {
+        float mn, mx;
+        if (tri) {
+            mn = minf(P4[1][a], minf(P4[2][a], P4[3][a]));
+            mx = maxf(P4[1][a], maxf(P4[2][a], P4[3][a]));
+            const float MIN_AABB_WIDTH = 0.005f;
+            if (mx - mn < MIN_AABB_WIDTH) {
+                float c = 0.5f * (mx + mn);
+                mx = c + MIN_AABB_WIDTH * 0.5f; mn = c - MIN_AABB_WIDTH * 0.5f;
+            }
+        } else {
+            mn = minf(minf(P4[0][a], P4[1][a]), minf(P4[2][a], P4[3][a]));
+            mx = maxf(maxf(P4[0][a], P4[1][a]), maxf(P4[2][a], P4[3][a]));
+            const float MIN_SIZE_DIR = 0.00001f;
+            if (mx - mn < MIN_SIZE_DIR) {
+                float center = (mx - mn) / 2.0f + mn;
+                mn = center - 0.5f * MIN_SIZE_DIR; mx = center + 0.5f * MIN_SIZE_DIR;
+            }
+        }
+        b.lo[a] = mn; b.hi[a] = mx;
+    }
+    return b;
+}
+
+// The instance's world -> local map (rot_apply with inv_rows) as a matrix, and whether it is orthogonal: then the
+// frame change is a rigid motion and the instance's primitives can be copied into world space (rtw_host.h).
+bool rigid_frame(const float* r, double M[3][3]) {
+    M[0][0] = (double)(r[0] * r[1]); M[0][1] = r[2]; M[0][2] = r[3];
+    M[1][0] = (double)(r[4] * r[5]); M[1][1] = r[6]; M[1][2] = r[7];
+    M[2][0] = r[8]; M[2][1] = (double)(r[9] * r[10]); M[2][2] = (double)(r[11] * r[10]);
+    for (int i = 0; i < 3; ++i)
+        for (int j = 0; j < 3; ++j) {
+            double d = 0.0;
+            for (int k = 0; k < 3; ++k) d += M[i][k] * M[j][k];
+            if (!(std::fabs(d - (i == j ? 1.0 : 0.0)) < 2e-6)) return false;
+        }
+    return true;
+}
 
 BuildPrim make_prim(uint32_t ref, const Box& b) {
     BuildPrim p; p.ref = ref; p.box = b;
@@ -267,11 +385,22 @@ Scene HostScene::host_view() {
     s.top = top;
     std::memcpy(s.background, background, sizeof background);
     s.n_noises = (uint32_t)noises.size();
+    s.n_spheres_orig = n_spheres_orig; s.n_quads_orig = n_quads_orig;
+    s.baked_sphere_src = baked_sphere_src.data(); s.baked_quad_src = baked_quad_src.data();
     return s;
 }
 
 int build_host_scene(const rtw_scene_desc* d, HostScene& hs, std::string& err) {
     if (!d) { err = "null scene description"; return RTW_E_INVALID; }
+    // RTW_BUILD_TIMING=1: phase times of this function on stderr (tuning aid)
+    static const bool timing = [] { const char* e = std::getenv("RTW_BUILD_TIMING"); return e && e[0] == '1'; }();
+    auto t_last = std::chrono::steady_clock::now();
+    auto lap = [&](const char* what) {
+        if (!timing) return;
+        auto now = std::chrono::steady_clock::now();
+        std::fprintf(stderr, "build_host_scene: %-28s %8.3f ms\n", what, std::chrono::duration<double, std::milli>(now - t_last).count());
+        t_last = now;
+    };
     if (d->abi_version != RTW_ABI_VERSION) { err = "abi_version mismatch"; return RTW_E_INVALID; }
     if (d->n_top_spheres > d->n_spheres || d->n_top_quads > d->n_quads) { err = "n_top_* exceeds n_*"; return RTW_E_INVALID; }
     if ((d->n_spheres && !d->spheres) || (d->n_quads && !d->quads) || (d->n_instances && !d->instances) ||
@@ -318,6 +447,7 @@ int build_host_scene(const rtw_scene_desc* d, HostScene& hs, std::string& err) {
         for (uint32_t k = 0; k < o.n_texels; ++k) tv[k] = make_float4(t.rgb[3 * k], t.rgb[3 * k + 1], t.rgb[3 * k + 2], 0.f);
     }
 
+    lap("materials, noises, textures");
     // ---- spheres
     const uint32_t ns = d->n_spheres, nq = d->n_quads;
     hs.spheres.resize(ns); hs.sphere_vel.resize(ns); hs.sphere_col.resize(ns); hs.sphere_ids.resize(ns);
@@ -349,46 +479,16 @@ int build_host_scene(const rtw_scene_desc* d, HostScene& hs, std::string& err) {
         if (q.mat_id >= d->n_materials || q.tex_id >= d->n_textures) { err = "quad material/texture id out of range"; return RTW_E_INVALID; }
         if (!finite3(q.origin) || !finite3(q.u) || !finite3(q.v)) { err = "non-finite quad"; return RTW_E_INVALID; }
         V3 Q = v3(q.origin[0], q.origin[1], q.origin[2]), u = v3(q.u[0], q.u[1], q.u[2]), v = v3(q.v[0], q.v[1], q.v[2]);
-        V3 n = cross(u, v);                      // quad.rs:93
-        V3 normal = unit(n);                     // :99
-        float dd = dot(normal, Q);               // :100
-        V3 w = n / dot(n, n);                    // :101
-        Quad& o = hs.quads[i];
-        o.q0 = make_float4(normal.x, normal.y, normal.z, dd);
-        o.q1 = make_float4(Q.x, Q.y, Q.z, u.x);
-        o.q2 = make_float4(u.y, u.z, v.x, v.y);
-        o.q3 = make_float4(v.z, w.x, w.y, w.z);
+        hs.quads[i] = make_quad(Q, u, v);
         hs.quad_ids[i] = make_uint2(q.mat_id, q.tex_id);
         if (q.shape > RTW_SHAPE_TRIANGLE) { err = "quad shape is neither parallelogram nor triangle"; return RTW_E_INVALID; }
         const bool tri = q.shape == RTW_SHAPE_TRIANGLE;
         qtri[i] = tri ? REF_TRIANGLE : 0u;
-        // qaabb.rs:19-61: box of the four corners, then pad() :107-126.
-        // Triangle (Rust2 triangle.rs:50-89): the three corners, each axis at least 0.005 wide about its middle.
-        V3 op = Q + u + v, vc = Q + v, uc = Q + u;
-        const float P4[4][3] = {{op.x, op.y, op.z}, {vc.x, vc.y, vc.z}, {uc.x, uc.y, uc.z}, {Q.x, Q.y, Q.z}};
-        for (int a = 0; a < 3; ++a) {
-            float mn, mx;
-            if (tri) {
-                mn = minf(P4[1][a], minf(P4[2][a], P4[3][a]));
-                mx = maxf(P4[1][a], maxf(P4[2][a], P4[3][a]));
-                const float MIN_AABB_WIDTH = 0.005f;
-                if (mx - mn < MIN_AABB_WIDTH) {
-                    float c = 0.5f * (mx + mn);
-                    mx = c + MIN_AABB_WIDTH * 0.5f; mn = c - MIN_AABB_WIDTH * 0.5f;
-                }
-            } else {
-                mn = minf(minf(P4[0][a], P4[1][a]), minf(P4[2][a], P4[3][a]));
-                mx = maxf(maxf(P4[0][a], P4[1][a]), maxf(P4[2][a], P4[3][a]));
-                const float MIN_SIZE_DIR = 0.00001f;
-                if (mx - mn < MIN_SIZE_DIR) {
-                    float center = (mx - mn) / 2.0f + mn;
-                    mn = center - 0.5f * MIN_SIZE_DIR; mx = center + 0.5f * MIN_SIZE_DIR;
-                }
-            }
-            qbox[i].lo[a] = mn; qbox[i].hi[a] = mx;
-        }
+        qbox[i] = quad_box(Q, u, v, tri);
     }
+    hs.n_spheres_orig = ns; hs.n_quads_orig = nq;
 
+    lap("spheres, quads");
     // ---- instances
     Builder bld(hs.nodes);
     hs.instances.resize(d->n_instances);
@@ -452,6 +552,76 @@ int build_host_scene(const rtw_scene_desc* d, HostScene& hs, std::string& err) {
         if (!finite3(lb.lo) || !finite3(lb.hi)) { err = "instance bounds are not finite"; return RTW_E_INVALID; }
         inst_leaves.push_back({k, lb});
     }
+    lap("instances");
+    // ---- baked instances (rtw_host.h): world-space copies of the primitives of rigidly placed surface instances
+    std::vector<BuildPrim> baked_prims;                  // leaves that replace the baked instances' leaves
+    std::vector<char> inst_baked(d->n_instances, 0);
+    for (auto& il : inst_leaves) {
+        const uint32_t k = il.first;
+        const rtw_instance& in = d->instances[k];
+        const Instance& o = hs.instances[k];
+        if ((o.flags & INST_VOLUME) || !inst_moving[k].empty() || inst_prims[k].empty()) continue;
+        double M[3][3];
+        if (!rigid_frame(o.inv_rows, M)) continue;
+        // local -> world: p_w = M^T p_l + T (M orthogonal: the inverse of the world -> local map p_l = M (p_w - T))
+        auto to_world = [&](V3 p, bool point) {
+            double q[3];
+            for (int a = 0; a < 3; ++a) q[a] = M[0][a] * p.x + M[1][a] * p.y + M[2][a] * p.z + (point ? (double)o.t[a] : 0.0);
+            return v3((float)q[0], (float)q[1], (float)q[2]);
+        };
+        bool ok = true;
+        std::vector<BuildPrim> mine;
+        std::vector<float4> new_spheres; std::vector<Quad> new_quads;
+        std::vector<uint2> src_s, src_q;
+        const uint32_t iref = make_ref(KIND_INSTANCE, k);
+        for (uint32_t i = 0; i < in.n_spheres && ok; ++i) {
+            const uint32_t si = in.first_sphere + i;
+            const float4 sp = hs.spheres[si];
+            const V3 c = to_world(v3(sp.x, sp.y, sp.z), true);
+            if (!std::isfinite(c.x) || !std::isfinite(c.y) || !std::isfinite(c.z)) { ok = false; break; }
+            Box b;
+            const float cc[3] = {c.x, c.y, c.z};
+            for (int a = 0; a < 3; ++a) {
+                // the copy's centre is rounded to f32: a few ulps of slack around centre +- radius
+                const float pad = 4.0f * 1.1920929e-7f * (std::fabs(cc[a]) + std::fabs(sp.w));
+                b.lo[a] = cc[a] - std::fabs(sp.w) - pad; b.hi[a] = cc[a] + std::fabs(sp.w) + pad;
+            }
+            const uint32_t idx = (uint32_t)(hs.spheres.size() + new_spheres.size());
+            new_spheres.push_back(make_float4(c.x, c.y, c.z, sp.w));
+            src_s.push_back(make_uint2(iref, make_ref(KIND_SPHERE, si)));
+            mine.push_back(make_prim(make_ref(KIND_SPHERE, idx), b));
+        }
+        for (uint32_t i = 0; i < in.n_quads && ok; ++i) {
+            const uint32_t qi = in.first_quad + i;
+            const Quad& ql = hs.quads[qi];
+            const V3 Q = to_world(v3(ql.q1.x, ql.q1.y, ql.q1.z), true);
+            const V3 u = to_world(v3(ql.q1.w, ql.q2.x, ql.q2.y), false), v = to_world(v3(ql.q2.z, ql.q2.w, ql.q3.x), false);
+            const Quad qw = make_quad(Q, u, v);
+            const float* f = &qw.q0.x;
+            for (int a = 0; a < 16; ++a) if (!std::isfinite(f[a])) ok = false;
+            if (!ok) break;
+            Box b = quad_box(Q, u, v, qtri[qi] != 0u);
+            for (int a = 0; a < 3; ++a) {
+                const float pad = 4.0f * 1.1920929e-7f * std::max(std::fabs(b.lo[a]), std::fabs(b.hi[a]));
+                b.lo[a] -= pad; b.hi[a] += pad;
+            }
+            const uint32_t idx = (uint32_t)(hs.quads.size() + new_quads.size());
+            new_quads.push_back(qw);
+            src_q.push_back(make_uint2(iref, make_ref(KIND_QUAD, qi | qtri[qi])));
+            mine.push_back(make_prim(make_ref(KIND_QUAD, idx | qtri[qi]), b));
+        }
+        if (!ok || hs.spheres.size() + new_spheres.size() >= REF_INDEX_LIMIT || hs.quads.size() + new_quads.size() >= REF_INDEX_LIMIT) continue;
+        hs.spheres.insert(hs.spheres.end(), new_spheres.begin(), new_spheres.end());
+        hs.quads.insert(hs.quads.end(), new_quads.begin(), new_quads.end());
+        hs.baked_sphere_src.insert(hs.baked_sphere_src.end(), src_s.begin(), src_s.end());
+        hs.baked_quad_src.insert(hs.baked_quad_src.end(), src_q.begin(), src_q.end());
+        baked_prims.insert(baked_prims.end(), mine.begin(), mine.end());
+        inst_baked[k] = 1;
+        hs.has_baked = true;
+    }
+    if (hs.baked_sphere_src.empty()) hs.baked_sphere_src.push_back(make_uint2(REF_NONE, REF_NONE));
+    if (hs.baked_quad_src.empty()) hs.baked_quad_src.push_back(make_uint2(REF_NONE, REF_NONE));
+
     auto record_level = [&](const std::vector<BuildPrim>& prims, int32_t owner) {
         LbvhLevelDesc lv; lv.first = (uint32_t)hs.lbvh_leaves.size(); lv.count = (uint32_t)prims.size(); lv.owner = owner; lv.pad = 0u;
         for (const BuildPrim& p : prims) {
@@ -469,14 +639,14 @@ int build_host_scene(const rtw_scene_desc* d, HostScene& hs, std::string& err) {
     hs.info = rtw_scene_info{};
     hs.info.n_tlas_leaves = (uint32_t)top.size();
     hs.moving = top_moving;
-    hs.top = bld.level(top, 0u, (uint32_t)top_moving.size());
-    record_level(top, -1);
-    hs.info.n_tlas_nodes = (uint32_t)hs.nodes.size();
-    uint32_t top_depth = bld.max_pushes, inner_depth = 0;
+    lap("baked copies");
+    uint32_t top_depth = 0, inner_depth = 0;
+    uint32_t plain_top_depth = 0, baked_top_depth = 0, inner_depth_unbaked = 0;
     // ---- enclosing volumes (see rtw_host.h): one-sphere constant-density instances, not rotated,
     // whose sphere contains every other leaf box of the top level with a 0.1 % margin
+    std::vector<char> top_drop(top.size(), 0);
     {
-        std::vector<char> drop(top.size(), 0);
+        std::vector<char>& drop = top_drop;
         auto far_corner = [](const Box& b, const float c[3]) {
             float d2 = 0.f;
             for (int a = 0; a < 3; ++a) { float e = std::max(std::fabs(b.lo[a] - c[a]), std::fabs(b.hi[a] - c[a])); d2 += e * e; }
@@ -511,14 +681,57 @@ int build_host_scene(const rtw_scene_desc* d, HostScene& hs, std::string& err) {
             drop[i] = 1;
             hs.enclosing.push_back(e);
         }
-        if (!hs.enclosing.empty()) {
-            std::vector<BuildPrim> rest;
-            for (size_t i = 0; i < top.size(); ++i) if (!drop[i]) rest.push_back(top[i]);
-            hs.top_inside = bld.level(rest, 0u, (uint32_t)top_moving.size());
-            record_level(rest, -2);
-            top_depth = std::max(top_depth, bld.max_pushes);   // (info.n_tlas_nodes stays the full top level's count)
-        }
     }
+    // The top level without the enclosing volumes is built by SAH; the one with them (what the strict kernels and
+    // renders from outside walk) is that tree under one more node holding the dropped leaves (Builder::wrap).
+    std::vector<BuildPrim> dropped;
+    for (size_t i = 0; i < top.size(); ++i) if (top_drop[i]) dropped.push_back(top[i]);
+    const uint32_t n_mov = (uint32_t)top_moving.size();
+    if (!hs.enclosing.empty()) {
+        std::vector<BuildPrim> rest;
+        for (size_t i = 0; i < top.size(); ++i) if (!top_drop[i]) rest.push_back(top[i]);
+        hs.top_inside = bld.level(rest, 0u, n_mov);
+        record_level(rest, -2);
+        top_depth = plain_top_depth = bld.max_pushes;
+        hs.top = bld.wrap(hs.top_inside, bld.max_pushes, dropped);
+        top_depth = plain_top_depth = std::max(top_depth, bld.max_pushes);
+    } else {
+        hs.top = bld.level(top, 0u, n_mov);
+        top_depth = plain_top_depth = bld.max_pushes;
+    }
+    record_level(top, -1);
+    hs.info.n_tlas_nodes = (uint32_t)hs.nodes.size();
+    lap("top levels");
+    for (auto& il : inst_leaves)
+        if (!(hs.instances[il.first].flags & INST_ONE_SPHERE)) {
+            ++hs.n_walked_instances;
+            if (!inst_baked[il.first]) ++hs.n_walked_instances_baked;
+        }
+    if (hs.has_baked) {
+        // the same two top levels with the baked instances' leaves replaced by their primitives' world-space copies
+        std::vector<BuildPrim> all, inside;
+        for (size_t i = 0; i < top.size(); ++i) {
+            const bool is_inst = ref_kind(top[i].ref) == KIND_INSTANCE;
+            if (is_inst && inst_baked[instance_index(top[i].ref)]) continue;
+            all.push_back(top[i]);
+            if (!top_drop[i]) inside.push_back(top[i]);
+        }
+        all.insert(all.end(), baked_prims.begin(), baked_prims.end());
+        inside.insert(inside.end(), baked_prims.begin(), baked_prims.end());
+        if (!hs.enclosing.empty()) {
+            hs.top_baked_inside = bld.level(inside, 0u, n_mov);
+            record_level(inside, -4);
+            baked_top_depth = bld.max_pushes;
+            hs.top_baked = bld.wrap(hs.top_baked_inside, bld.max_pushes, dropped);
+            baked_top_depth = std::max(baked_top_depth, bld.max_pushes);
+        } else {
+            hs.top_baked = bld.level(all, 0u, n_mov);
+            baked_top_depth = bld.max_pushes;
+        }
+        record_level(all, -3);
+        top_depth = std::max(top_depth, baked_top_depth);
+    }
+    lap("baked top levels");
     blas_nodes_before = (uint32_t)hs.nodes.size();
     for (auto& il : inst_leaves) {
         uint32_t k = il.first;
@@ -527,7 +740,9 @@ int build_host_scene(const rtw_scene_desc* d, HostScene& hs, std::string& err) {
         hs.instances[k].level = bld.level(inst_prims[k], mf, (uint32_t)inst_moving[k].size());
         record_level(inst_prims[k], (int32_t)k);
         inner_depth = std::max(inner_depth, bld.max_pushes);
+        if (!inst_baked[k]) inner_depth_unbaked = std::max(inner_depth_unbaked, bld.max_pushes);
     }
+    lap("instance levels");
     // the half-float copy of the nodes (fast kernels): boxes rounded outwards
     hs.nodes16.resize(hs.nodes.size());
     for (size_t i = 0; i < hs.nodes.size(); ++i) {
@@ -551,12 +766,18 @@ int build_host_scene(const rtw_scene_desc* d, HostScene& hs, std::string& err) {
     }
     hs.info.n_blas_nodes = (uint32_t)hs.nodes.size() - blas_nodes_before;
     hs.info.n_flattened_instances = n_flat;
+    for (char b : inst_baked) hs.info.n_baked_instances += b ? 1u : 0u;
     hs.info.bvh_max_depth = top_depth + inner_depth;
     hs.top_depth = top_depth; hs.inner_depth = inner_depth;
+    hs.any_levels = hs.n_walked_instances > 0;
+    hs.fast_top_depth = hs.has_baked ? baked_top_depth : plain_top_depth;
+    hs.fast_inner_depth = hs.has_baked ? inner_depth_unbaked : inner_depth;
+    hs.fast_levels = (hs.has_baked ? hs.n_walked_instances_baked : hs.n_walked_instances) > 0;
     if (stack_words(top_depth, inner_depth) > 160u) { err = "BVH deeper than the traversal stack"; return RTW_E_UNSUPPORTED; }
     if (hs.nodes.empty()) { hs.nodes.emplace_back(); std::memset(&hs.nodes[0], 0, sizeof(Node)); hs.nodes16.emplace_back(); std::memset(&hs.nodes16[0], 0, sizeof(Node16)); }
     if (hs.moving.empty()) hs.moving.push_back(0u);
     for (int a = 0; a < 3; ++a) hs.background[a] = d->background[a];
+    lap("half-float nodes, records");
     return RTW_OK;
 }
 

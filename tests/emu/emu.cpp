@@ -57,7 +57,8 @@ static void lbvh_rebuild_host(HostScene& hs) {
         t.node_base = (uint32_t)hs.nodes.size();
         hs.nodes.resize(hs.nodes.size() + run); hs.nodes16.resize(hs.nodes.size());
         for (int i = 0; i < n - 1; ++i) if (wide[i]) lbvh_emit(t, i, hs.nodes.data(), hs.nodes16.data());
-        Level& L = lv.owner == -1 ? hs.top : lv.owner == -2 ? hs.top_inside : hs.instances[lv.owner].level;
+        Level& L = lv.owner == -1 ? hs.top : lv.owner == -2 ? hs.top_inside : lv.owner == -3 ? hs.top_baked
+                   : lv.owner == -4 ? hs.top_baked_inside : hs.instances[lv.owner].level;
         L.root = make_ref(KIND_NODE, t.node_base);
         for (int a = 0; a < 3; ++a) { L.lo[a] = ibox[0].lo[a]; L.hi[a] = ibox[0].hi[a]; }
         const uint32_t pushes = lbvh_pushes(max_depth);
@@ -77,9 +78,10 @@ extern "C" int emu_render_ex(const rtw_scene_desc* d, const rtw_camera* cam, con
     HostScene hs; std::string err;
     int rc = build_host_scene(d, hs, err);
     if (rc) { std::fprintf(stderr, "emu: %s\n", err.c_str()); return rc; }
-    if (use_lbvh) lbvh_rebuild_host(hs);
+    if (use_lbvh & 1) lbvh_rebuild_host(hs);
     if (info) *info = hs.info;
     Scene sc = hs.host_view();
+    if ((use_lbvh & 2) && hs.has_baked) sc.top = hs.top_baked;     // the top level with baked instances (rtw_host.h), as the fast kernels walk it
     RenderParams P; uint32_t total = 0;
     rc = make_render_params(cam, o, P, total, err);
     if (rc) { std::fprintf(stderr, "emu: %s\n", err.c_str()); return rc; }

@@ -45,8 +45,8 @@ def load_emu():
 
 
 class EmuSceneHandle:
-    def __init__(self, lib, fs, lbvh: bool = False):
-        self._lib, self._fs, self._lbvh = lib, fs, lbvh
+    def __init__(self, lib, fs, lbvh: bool = False, baked: bool = False):
+        self._lib, self._fs, self._lbvh = lib, fs, (1 if lbvh else 0) | (2 if baked else 0)
         self.last = (C.c_uint64 * 8)()
         self.last_info = A.rtw_scene_info()
 
@@ -57,7 +57,7 @@ class EmuSceneHandle:
         rows = o.row_count if o.row_count else cam.height
         out = np.empty((rows, cam.width, 3), dtype=np.float32)
         rc = self._lib.emu_render_ex(C.byref(self._fs.desc), C.byref(cam), C.byref(o), out.ctypes.data_as(C.c_void_p),
-                                     self.last, C.byref(self.last_info), 1 if self._lbvh else 0)
+                                     self.last, C.byref(self.last_info), self._lbvh)
         if rc != 0:
             raise ValueError(f"emu_render failed: {rc}")
         return out
@@ -73,20 +73,21 @@ class EmuSceneHandle:
 class EmuBackend:
     name = "emu"
 
-    def __init__(self, lbvh: bool = False):
+    def __init__(self, lbvh: bool = False, baked: bool = False):
         """lbvh=True: every level is rebuilt with the LBVH steps of rtw_lbvh.h (run in host loops)
-        before rendering, as rtw_scene_rebuild_lbvh does on the device."""
+        before rendering, as rtw_scene_rebuild_lbvh does on the device. baked=True: walk the top level in which
+        rigidly placed surface instances are replaced by world-space copies of their primitives (rtw_host.h)."""
         self.lib = load_emu()
-        self.lbvh = lbvh
+        self.lbvh, self.baked = lbvh, baked
 
     def camera_init(self, width, aspect_ratio, vfov, origin, direction, vup, lens_radius):
         from oracle_backend import OracleBackend
         return OracleBackend().camera_init(width, aspect_ratio, vfov, origin, direction, vup, lens_radius)
 
     def scene(self, scene) -> EmuSceneHandle:
-        key = ("emu", self.lbvh)
+        key = ("emu", self.lbvh, self.baked)
         h = scene._backend_cache.get(key)
         if h is None:
-            h = EmuSceneHandle(self.lib, scene.flatten(), self.lbvh)
+            h = EmuSceneHandle(self.lib, scene.flatten(), self.lbvh, self.baked)
             scene._backend_cache[key] = h
         return h

@@ -194,3 +194,55 @@ def test_dp_collapse_experiment_renders_identically(emu, tmp_path):
         assert np.array_equal(job.render(emu), got[name], equal_nan=True), name
         fewer += int(got[name + "_nodes"]) < emu.scene(job.scene).stats()["nodes"]
     assert fewer >= 2                                   # and it walks fewer nodes on most of them (the point of it)
+
+
+BAKED_SCENES = ["instance_box_rot", "instance_box", "presentation", "triangle_mesh", "C4", "C4_smoke", "C5", "volume"]
+
+
+@pytest.mark.parametrize("name", BAKED_SCENES)
+def test_baked_instances_find_the_reference_hits(name, oracle):
+    """rtw_host.h "baked instances": where an instance's frame change is a rigid motion, world-space copies of its
+    primitives replace its leaf in the top level the fast kernels walk. The closest hit must be the reference's:
+    same primitive (albedo bit for bit), same t up to the rounding of the copied centre / corners (normals within
+    1e-5 of the oracle's outside tie pixels), and the Hit is still evaluated through the instance's frame. The
+    emulated headers walk that top level here with the strict (f32-box) arithmetic; the GPU parity tests run it
+    in the fast build."""
+    from emu_backend import EmuBackend
+    emu_b = EmuBackend(baked=True)
+    job = _small(ALL[name](), 96, 72, 2)
+    vp = job.viewport
+    got_info = None
+    for ig in (A.RTW_INT_ALBEDO, A.RTW_INT_NORMAL):
+        ref = vp._run(ig, job.scene, A.RTW_MODE_NO_RAND, oracle)
+        tie = oracle.scene(job.scene).last_tie.astype(bool)
+        got = vp._run(ig, job.scene, A.RTW_MODE_NO_RAND, emu_b)
+        got_info = emu_b.scene(job.scene).info()
+        ok = ~tie
+        assert np.array_equal(np.isfinite(got[ok]), np.isfinite(ref[ok]))
+        fin = np.isfinite(ref) & ok[..., None]
+        err = np.abs(got - ref)[fin] / np.maximum(np.abs(ref[fin]), 1e-6)
+        if ig == A.RTW_INT_ALBEDO:
+            assert (err > 0).mean() <= 2e-3, f"{name}: {(err > 0).sum()} albedo values differ"      # silhouette pixels only
+        else:
+            assert (err > 1e-5).mean() <= 4e-3, f"{name}: {(err > 1e-5).sum()} of {err.size} normal values off by > 1e-5"
+    expect = {"instance_box_rot": 1, "instance_box": 1, "presentation": 1, "triangle_mesh": 2, "C4": 2, "C4_smoke": 0, "C5": 1, "volume": 0}[name]
+    assert got_info.n_baked_instances == expect, (name, got_info.n_baked_instances)
+
+
+def test_non_rigid_euler_maps_are_not_baked(oracle):
+    """Vec3::rotated is a rotation only about y (SURVEY N13); an x- or z-'rotated' instance keeps its own level."""
+    from emu_backend import EmuBackend
+    emu_b = EmuBackend(baked=True)
+    tex = ImageTexture.from_color((0.7, 0.4, 0.2))
+    for rot, baked in (((0.3, 0.0, 0.0), 0), ((0.0, 0.0, 0.4), 0), ((0.0, 0.7, 0.0), 1), ((0.0, 0.0, 0.0), 1)):
+        box = Instance.new_box(Vec3(-0.5, -0.5, -0.5), Vec3(0.5, 0.5, 0.5), tex, SCATTER_M)
+        box.rotate(Vec3(*rot))
+        box.translate(Vec3(0.1, 0.2, -3.0))
+        sc = Scene.new([], [], [box])
+        vp = Viewport.new_from_res(64, 48, 1, 5, 1.0)
+        ref = vp._run(A.RTW_INT_NORMAL, sc, A.RTW_MODE_NO_RAND, oracle)
+        tie = oracle.scene(sc).last_tie.astype(bool)
+        got = vp._run(A.RTW_INT_NORMAL, sc, A.RTW_MODE_NO_RAND, emu_b)
+        assert emu_b.scene(sc).info().n_baked_instances == baked, rot
+        ok = ~tie
+        assert np.allclose(got[ok], ref[ok], rtol=1e-5, atol=1e-6)
