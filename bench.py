@@ -6,8 +6,12 @@
     python bench.py --impl reference --gpus N --steps K --warmup W   (CPU arm: the oracle port, all host threads)
 
 A "step" is one whole frame of the workload: every rank renders its sample range of every pixel
-into a per-GPU f32 sum buffer (the megakernel), one NCCL reduce(sum) to rank 0, resolve (/spp,
-powf(1/gamma)) there. Total work per step is fixed as N grows => "scaling": "strong".
+into a per-GPU f32 sum buffer (wavefront pipeline: wf_extend + wf_shade kernels over a pool of path
+slots in HBM), one NCCL reduce(sum) to rank 0, resolve (/spp, powf(1/gamma)) there. Total work per step
+is fixed as N grows => "scaling": "strong". --partition tiles (row bands dealt round-robin, gathered,
+no reduction; C4 in BASELINE.json) and --partition frames (one animation frame per GPU per step, no
+exchange; "scaling": "weak") are the two other partitions north_star names. --single-process runs the
+sample / tile split over --gpus N devices inside ONE process through rtw_render_multi (no torchrun).
   value  = paths of K frames / device time (CUDA events on the launching stream, max over ranks),
            scene resident in HBM, image left on the device.
   e2e    = the same frame through the C ABI with HOST buffers: rtw_scene_create (flatten, SAH BVH,
@@ -55,6 +59,13 @@ def parse_args():
     ap.add_argument("--e2e-steps", type=int, default=0, help="timed e2e steps (0 = same as --steps)")
     ap.add_argument("--cpu-seconds", type=float, default=15.0, help="target CPU time of the cpu_baseline sample")
     ap.add_argument("--flags", type=int, default=0)
+    ap.add_argument("--partition", default="samples", choices=["samples", "tiles", "frames"],
+                    help="how the frame is split over the GPUs (SURVEY 8e A / B / C)")
+    ap.add_argument("--band", type=int, default=8, help="rows per band of --partition tiles")
+    ap.add_argument("--single-process", action="store_true",
+                    help="one process drives --gpus N devices through rtw_render_multi (samples / tiles)")
+    ap.add_argument("--synthetic-textures", action="store_true",
+                    help="generated stand-ins instead of the reference's earthmap.jpg / default.png (named in `data`)")
     return ap.parse_args()
 
 
@@ -109,12 +120,19 @@ class ClockSampler:
 # ----------------------------------------------------------------------------- workload
 def make_job(args):
     from rtw_b200 import scenes
+    if args.synthetic_textures:
+        scenes.SYNTHETIC_TEXTURES = True
     kw = {}
     if args.spp:
         kw["samples"] = args.spp
     job = scenes.CONFIGS[args.config](**kw)
     job.viewport.flags = args.flags
     return job
+
+
+def data_label() -> str:
+    from rtw_b200 import scenes
+    return scenes.texture_data_label()
 
 
 def workload_name(job) -> str:
@@ -176,7 +194,7 @@ def run_reference(args):
     vp = job.viewport
     line = {"impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": tot_s / args.steps * 1e3, "higher_is_better": True,
-            "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": data_label(),
             "config": {"workload": workload_name(job), "step": last["sample"], "host_threads": last["threads"]},
             "mrays_per_s": tot_rays / tot_s / 1e6,
             "cpu_baseline": {"value": val, "unit": UNIT, "cores": last["threads"], "kind": "port", "sample": last["sample"]},
@@ -196,7 +214,7 @@ def run_b200(args):
     import rtw_b200
     from rtw_b200 import _abi as A
     from rtw_b200.backend import CudaBackend
-    from rtw_b200.sharding import sample_range
+    from rtw_b200.sharding import row_bands, sample_range
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -220,27 +238,69 @@ def run_b200(args):
     cam = vp.camera(be)
     W, H, spp = cam.width, cam.height, vp.samples
     begin, count = sample_range(spp, world, rank)
+    part = args.partition
     o = vp.opts(job.ray_color, job.mode)
     o.output = A.RTW_OUT_SUM
     o.sample_begin, o.sample_count = begin, count
     buf = torch.empty((H, W, 3), dtype=torch.float32, device=dev)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)      # > 126 MB L2
     stream = torch.cuda.current_stream().cuda_stream
+    bands = row_bands(H, world, rank, args.band) if part == "tiles" else []
+    frame_no = [0]
+    if part == "tiles" and world == 1:
+        bands = [(0, H)]            # one device: the whole frame is its one band
+
+    def collect_stats(collect, acc=None):
+        st = h.stats()                                  # syncs on the last render's events
+        row = [st.kernel_ms, st.rays, st.paths, st.nan_paths, st.gpu_launches, st.iterations, st.extend_ms, st.shade_ms]
+        if acc is None:
+            collect.append(tuple(row))
+        else:                                           # several renders per step (bands): sums; per-launch means weighted by iterations
+            for k in (0, 1, 2, 3, 4, 5):
+                acc[k] += row[k]
+            acc[6] += row[6] * row[5]; acc[7] += row[7] * row[5]
 
     def step(collect=None):
         flush.zero_()                                   # L2 flush between steps
-        if count > 0:
-            h.render_device(cam, o, buf.data_ptr(), stream)
+        if part == "samples":
+            if count > 0:
+                h.render_device(cam, o, buf.data_ptr(), stream)
+            else:
+                buf.zero_()
+            if world > 1:
+                dist.reduce(buf, dst=0, op=dist.ReduceOp.SUM)
+            if rank == 0:
+                be.resolve_device(buf.data_ptr(), H * W, spp, vp.gamma, stream)
+            if collect is not None and count > 0:
+                collect_stats(collect)
+        elif part == "tiles":
+            # row bands dealt round-robin: every rank renders and RESOLVES its own bands in place in a
+            # zeroed frame; the frames are disjoint, so the gather to rank 0 is a reduce(sum) of them with zeros
+            # (x + 0 = x: bit-identical to one GPU). No sample reduction anywhere.
+            acc = [0.0] * 8
+            if world > 1:
+                buf.zero_()
+            ob = vp.opts(job.ray_color, job.mode)
+            for r0, rc in bands:
+                ob.row_begin, ob.row_count = r0, rc
+                h.render_device(cam, ob, buf.data_ptr() + r0 * W * 3 * 4, stream)
+                if collect is not None:
+                    collect_stats(collect, acc)
+            if world > 1:
+                dist.reduce(buf, dst=0, op=dist.ReduceOp.SUM)
+            if collect is not None and bands:
+                if acc[5] > 0:
+                    acc[6] /= acc[5]; acc[7] /= acc[5]
+                collect.append(tuple(acc))
         else:
-            buf.zero_()
-        if world > 1:
-            dist.reduce(buf, dst=0, op=dist.ReduceOp.SUM)
-        if rank == 0:
-            be.resolve_device(buf.data_ptr(), H * W, spp, vp.gamma, stream)
-        if collect is not None and count > 0:
-            st = h.stats()                              # syncs on this step's last event
-            collect.append((st.kernel_ms, st.rays, st.paths, st.nan_paths, st.gpu_launches, st.iterations,
-                            st.extend_ms, st.shade_ms))
+            # frames (render_multi viewport.rs:249-269): frame k of the animation on rank k mod n, every
+            # rank renders ONE whole frame per step; nothing is exchanged (rank 0's frame is the one that is read back)
+            of = vp.opts(job.ray_color, job.mode)
+            of.frame = vp.frame + frame_no[0] * world + rank
+            frame_no[0] += 1
+            h.render_device(cam, of, buf.data_ptr(), stream)
+            if collect is not None:
+                collect_stats(collect)
 
     for _ in range(args.warmup):
         step()
@@ -285,7 +345,21 @@ def run_b200(args):
         A.check(lib.rtw_scene_create(C.byref(fs.desc), local, C.byref(hd)))
         e2e_trace.append(("create_ms", (time.perf_counter() - t_a) * 1e3))
         try:
-            if world == 1:
+            if part == "frames":
+                of = vp.opts(job.ray_color, job.mode)
+                of.frame = vp.frame + rank
+                A.check(lib.rtw_render(hd, C.byref(cam), C.byref(of), C.c_void_p(host_out.data_ptr())))
+            elif part == "tiles" and world > 1:
+                buf.zero_()
+                ob = vp.opts(job.ray_color, job.mode)
+                for r0, rc in bands:
+                    ob.row_begin, ob.row_count = r0, rc
+                    A.check(lib.rtw_render_device(hd, C.byref(cam), C.byref(ob), C.c_void_p(buf.data_ptr() + r0 * W * 3 * 4), C.c_void_p(stream)))
+                dist.reduce(buf, dst=0, op=dist.ReduceOp.SUM)
+                if rank == 0:
+                    host_out.copy_(buf, non_blocking=True)
+                torch.cuda.synchronize()
+            elif world == 1:
                 o2 = vp.opts(job.ray_color, job.mode)
                 A.check(lib.rtw_render(hd, C.byref(cam), C.byref(o2), C.c_void_p(host_out.data_ptr())))
             else:
@@ -301,7 +375,7 @@ def run_b200(args):
             e2e_trace.append(("render_ms", (time.perf_counter() - t_a) * 1e3))
             inf = A.rtw_scene_info()
             A.check(lib.rtw_scene_get_info(hd, C.byref(inf)))
-            return int(inf.device_bytes)
+            return int(inf.h2d_bytes), int(inf.device_bytes)
         finally:
             t_b = time.perf_counter()
             lib.rtw_scene_destroy(hd)
@@ -311,7 +385,7 @@ def run_b200(args):
     barrier(); torch.cuda.synchronize()
     t0 = time.perf_counter()
     for _ in range(e2e_steps):
-        h2d = e2e_step()
+        h2d, scene_device_bytes = e2e_step()
     torch.cuda.synchronize(); barrier()
     e2e_s = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
     if world > 1:
@@ -395,18 +469,21 @@ def run_b200(args):
                                     "peak_source": hbm_src,
                                     "note": "whole step: path records streamed by extend+shade (176 B/ray + 8 B per new path) + framebuffer REDs; the scene (<10 MB) is L1/L2-resident"}}}
         cpu = cpu_baseline_obj(cpu_sample(job, args.cpu_seconds)) if world == 1 else None
-        paths_frame = W * H * spp
+        paths_frame = W * H * spp * (world if part == "frames" else 1)     # paths per step
         val = paths_frame * args.steps / (elapsed_ms * 1e-3) / 1e6
+        part_text = {"samples": f"sample range x{world} + NCCL reduce(sum) to rank 0",
+                     "tiles": f"row bands of {args.band} rows dealt round-robin over {world} GPU(s), resolved in place, gathered to rank 0 (no reduction)",
+                     "frames": f"one animation frame per GPU per step (frame k on rank k mod {world}), no exchange"}[part]
         line = {"metric": METRIC, "value": val, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-                "ms_per_step": elapsed_ms / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
-                "dtype": "f32", "data": "synthetic",
-                "config": {"workload": workload_name(job), "partition": f"sample range x{world} + NCCL reduce(sum) to rank 0",
+                "ms_per_step": elapsed_ms / args.steps, "higher_is_better": True, "scaling": "weak" if part == "frames" else "strong", "vs_baseline": None,
+                "dtype": "f32", "data": data_label(),
+                "config": {"workload": workload_name(job), "partition": part_text,
                            "l2": "256 MiB memset between steps (inside the timed region)", "pipeline": "wavefront (extend + shade kernels over path queues in HBM)" if wavefront else "megakernel",
                            "fp": "strict (-fmad=false)" if args.flags & 1 else "fast (FFMA contraction)"},
                 "mrays_per_s": rays_total / (elapsed_ms * 1e-3) / 1e6, "rays_per_path": rays_total / max(1.0, paths_total),
                 "nan_paths": nan_total, "image_mean": image_mean,
                 "e2e": {"value": paths_frame * e2e_steps / e2e_s / 1e6, "unit": UNIT, "h2d_bytes_per_step": h2d * world,
-                        "d2h_bytes_per_step": H * W * 3 * 4, "ms_per_step": e2e_s / e2e_steps * 1e3, "steps": e2e_steps,
+                        "d2h_bytes_per_step": H * W * 3 * 4 * (world if part == "frames" else 1), "scene_device_bytes": scene_device_bytes, "ms_per_step": e2e_s / e2e_steps * 1e3, "steps": e2e_steps,
                         "what": "rtw_scene_create + rtw_render(host out) + rtw_scene_destroy per step"},
                 "gpu_launches": int(sum(p[4] for p in per_step)) + args.steps, "clocks": clocks, "roofline": roofline}
         if cpu is not None:
@@ -417,9 +494,76 @@ def run_b200(args):
         dist.destroy_process_group()
 
 
+def run_single_process(args):
+    """--single-process: ONE process drives --gpus N devices through the C ABI's multi-device entry points
+    (rtw_scene_multi_create / rtw_render_multi: a host thread and a stream per device, shares combined on device 0
+    by one peer-memory kernel) - what the reference's single-process caller (main.rs:76-80,412-414) would bind.
+    value: paths / (max over devices of the share's device time + the combine kernel), CUDA events inside the
+    library; e2e: wall clock of create + render into a pinned host buffer + destroy, every step."""
+    import torch
+    import rtw_b200
+    from rtw_b200 import _abi as A
+    from rtw_b200.backend import CudaBackend, CudaMultiSceneHandle
+    if args.partition == "frames":
+        raise SystemExit("--single-process: samples or tiles (frames: rtw_render_frames_multi is exercised by the tests)")
+    be = CudaBackend(device=0)
+    n = args.gpus
+    if be.device_count() < n:
+        raise SystemExit(f"--single-process --gpus {n}: only {be.device_count()} device(s) visible")
+    devices = list(range(n))
+    job = make_job(args)
+    vp = job.viewport
+    cam = vp.camera(be)
+    W, H, spp = cam.width, cam.height, vp.samples
+    o = vp.opts(job.ray_color, job.mode)
+    split = A.RTW_SPLIT_SAMPLES if args.partition == "samples" else A.RTW_SPLIT_TILES
+    host_out = torch.empty((H, W, 3), dtype=torch.float32).pin_memory().numpy()
+    ms = be.scene_multi(job.scene, devices)
+    for _ in range(args.warmup):
+        ms.render(cam, o, split, args.band, out=host_out)
+    sampler = ClockSampler(0)
+    sampler.start()
+    dev_ms = 0.0
+    rays = paths = launches = 0
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        ms.render(cam, o, split, args.band, out=host_out)
+        tot, per, comb = ms.stats()
+        dev_ms += tot.total_ms + comb
+        rays += tot.rays; paths += tot.paths; launches += tot.gpu_launches
+    wall_s = time.perf_counter() - t0
+    clocks = sampler.stop()
+    ms.close()
+    del job.scene._backend_cache[("cuda-multi", tuple(devices))]
+    fs = job.scene.flatten()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        m2 = CudaMultiSceneHandle(be.lib, fs, devices)
+        m2.render(cam, o, split, args.band, out=host_out)
+        m2.close()
+    e2e_s = time.perf_counter() - t0
+    paths_frame = W * H * spp
+    fin = np.isfinite(host_out)
+    line = {"metric": METRIC, "value": paths_frame * args.steps / (dev_ms * 1e-3) / 1e6, "unit": UNIT, "n_gpus": n, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": dev_ms / args.steps, "higher_is_better": True, "scaling": "strong",
+            "vs_baseline": None, "dtype": "f32", "data": data_label(),
+            "config": {"workload": workload_name(job), "launch": "single process, rtw_render_multi (one host thread + stream per device)",
+                       "partition": ("sample ranges, combined on device 0 by one peer-memory kernel" if split == A.RTW_SPLIT_SAMPLES
+                                     else f"row bands of {args.band or 8} rows dealt round-robin, copied straight to the host image"),
+                       "timing": "value: max over devices of the share's device time (CUDA events) + combine kernel; wall_ms_per_step: host clock around the call"},
+            "wall_ms_per_step": wall_s / args.steps * 1e3, "mrays_per_s": rays / (dev_ms * 1e-3) / 1e6,
+            "rays_per_path": rays / max(1, paths), "image_mean": float(host_out[fin].mean()),
+            "e2e": {"value": paths_frame * args.steps / e2e_s / 1e6, "unit": UNIT, "ms_per_step": e2e_s / args.steps * 1e3,
+                    "d2h_bytes_per_step": H * W * 3 * 4, "what": "rtw_scene_multi_create + rtw_render_multi(host out) + rtw_scene_multi_destroy per step"},
+            "gpu_launches": int(launches), "clocks": clocks}
+    print(json.dumps(line), flush=True)
+
+
 if __name__ == "__main__":
     a = parse_args()
     if a.impl == "reference":
         run_reference(a)
+    elif a.single_process:
+        run_single_process(a)
     else:
         run_b200(a)

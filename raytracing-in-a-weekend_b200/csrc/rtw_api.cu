@@ -523,6 +523,8 @@ int enqueue_wavefront(rtw_scene* s, const RenderParams& P, int variant, float* d
         const bool events_rare = (unsigned long long)s->cur_walked_instances * 16ull <= (unsigned long long)s->info.n_tlas_leaves;
         L.prim_w = std::max(1u, env_u32("RTW_WF_PRIM_W", events_rare ? 8u : 4u));
         L.event_w = std::max(1u, env_u32("RTW_WF_EVENT_W", events_rare ? 8u : 4u));   // (16 before one-sphere instances joined the event steps)
+        const uint32_t w = std::max(L.prim_w, L.event_w);
+        L.node_sure = (32u * w + (4u + w) - 1u) / (4u + w);
     }
     wf_init_kernel<<<1, 1, 0, st>>>(s->d_wc, init.total_paths);
     CK(cudaGetLastError());

@@ -293,10 +293,20 @@ wf_extend_kernel(const Scene sc, const RenderParams P, const WfPool pool, WfCoun
 #else
         const uint32_t cur = T.cur;
         const bool on_node = cur < NODE_LIMIT, on_event = ref_is_event(cur), on_prim = !on_node && !on_event && cur != CUR_DONE;
-        const int cn = __popc(__ballot_sync(FULL, on_node)), cp = __popc(__ballot_sync(FULL, on_prim)),
-                  ce = __popc(__ballot_sync(FULL, on_event));
+        const int cn = __popc(__ballot_sync(FULL, on_node));
+        int cp = 0, ce = 0;
+        bool node_step = true;
+#if RTW_WF_FASTVOTE
+        // With `node_sure` or more lanes on a node the node step wins whatever the other 32 - cn lanes wait for
+        // (cn * 4 >= (32 - cn) * max(prim_w, event_w)): the two other ballots are only taken below that.
+        if (cn < (int)L.node_sure)
+#endif
+        {
+            cp = __popc(__ballot_sync(FULL, on_prim)); ce = __popc(__ballot_sync(FULL, on_event));
+            node_step = cn * 4 >= cp * (int)L.prim_w && cn * 4 >= ce * (int)L.event_w;
+        }
         SCHED_COUNT(iters, 0, 0);
-        if (cn * 4 >= cp * (int)L.prim_w && cn * 4 >= ce * (int)L.event_w) {
+        if (node_step) {
             SCHED_COUNT(step, 0, cn);
             SCHED_TIME_BEGIN(0);
             if (on_node) {

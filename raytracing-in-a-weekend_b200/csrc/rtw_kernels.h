@@ -83,6 +83,7 @@ struct WfLaunch {
     // dissolve: 8 / 16 is +3.6 % there; where they are common (C4: two of eight leaves) any bias costs
     // 1-6 % (profiles/r1j_ab_vote_weights.txt). rtw_api.cu picks by the share of instance leaves.
     uint32_t prim_w, event_w;
+    uint32_t node_sure;              // lanes on a node from which the node step wins for certain: ceil(32 w / (4 + w)), w = max(prim_w, event_w)
     int extend_grid, shade_grid;
     size_t smem_bytes;
 };
@@ -99,6 +100,9 @@ struct WfLaunch {
 #endif
 #ifndef RTW_WF_NODE_BURST
 #define RTW_WF_NODE_BURST 3       // node steps per vote while the node lanes keep their majority
+#endif
+#ifndef RTW_WF_FASTVOTE
+#define RTW_WF_FASTVOTE 1         // 1: skip the leaf / event ballots of wf_extend's vote when the node lanes win anyway (same decisions)
 #endif
 #ifndef RTW_WF_SHADE_MINB
 #define RTW_WF_SHADE_MINB 10      // min resident blocks per SM asked of the compiler for wf_shade
