@@ -27,7 +27,10 @@ fn main() {
         run(Command::new(&nvcc).args(common).args(*extra).arg("-c").arg(csrc.join("rtw_kernels.cu")).arg("-o").arg(&o));
         objs.push(o);
     }
-    for (src, xcu) in [("rtw_api.cu", false), ("scene_build.cpp", true)] {
+    // the rest of csrc/Makefile's OBJ list, one object per source (tests/test_rust_shim.py keeps the two lists equal):
+    // rtw_lbvh.cu needs CUB, which ships with the CUDA toolkit (no extra include path)
+    for (src, xcu) in [("rtw_api.cu", false), ("scene_build.cpp", true), ("rtw_lbvh.cu", false), ("rtw_post.cu", false),
+                       ("rtw_multi.cu", false)] {
         let o = out.join(format!("{src}.o"));
         let mut c = Command::new(&nvcc);
         c.args(common);
@@ -42,6 +45,7 @@ fn main() {
     println!("cargo:rustc-link-search=native=/usr/local/cuda/lib64");
     println!("cargo:rustc-link-lib=dylib=cudart");
     println!("cargo:rustc-link-lib=dylib=stdc++");
+    println!("cargo:rustc-link-lib=dylib=pthread");     // rtw_multi.cu: one host thread per device
     println!("cargo:rerun-if-changed={}", csrc.display());
 }
 

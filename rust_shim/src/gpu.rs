@@ -127,7 +127,60 @@ impl GpuScene {
     }
 }
 
+/// The scene replicated on a list of CUDA devices of this process (include/rtw.h rtw_scene_multi): what
+/// `presentation_image` / `test_run` (main.rs:76-80,412-414) use to put every GPU of the box behind one call.
+pub struct GpuSceneMulti { h: *mut rtw_scene_multi, _flat: FlatScene }
+impl Drop for GpuSceneMulti { fn drop(&mut self) { unsafe { rtw_scene_multi_destroy(self.h) } } }
+#[derive(Clone, Copy)]
+pub enum Split { Samples = 0, Tiles = 1 }
+
+impl GpuSceneMulti {
+    pub fn new(scene: &Scene, devices: &[i32]) -> Result<GpuSceneMulti, String> {
+        let mut flat = FlatScene::from_scene(scene);
+        for k in 0..flat.textures.len() { flat.textures[k].rgb = flat.texels[k].as_ptr(); }
+        let contiguous: Vec<rtw_noise> = flat.noises.drain(..).map(|b| *b).collect();
+        let mut d = flat.desc();
+        d.noises = if contiguous.is_empty() { std::ptr::null() } else { contiguous.as_ptr() };
+        let mut h: *mut rtw_scene_multi = std::ptr::null_mut();
+        check(unsafe { rtw_scene_multi_create(&d, devices.as_ptr(), devices.len() as i32, &mut h) })?;
+        Ok(GpuSceneMulti { h, _flat: flat })
+    }
+}
+
 impl Viewport {
+    fn gpu_opts(&self, integrator: Integrator, mode: Mode, seed: u64) -> rtw_render_opts {
+        let mut o: rtw_render_opts = unsafe { std::mem::zeroed() };
+        unsafe { rtw_render_opts_default(&mut o) };
+        o.samples = self.samples as u32; o.depth = self.depth as u32; o.gamma = self.gamma;
+        o.integrator = integrator as u32; o.mode = mode as u32;
+        o.shutter_speed = self.shutter_speed; o.fps = self.fps; o.frame = self.frame as u32; o.seed = seed;
+        o
+    }
+    fn to_img(&self, buf: &[f32]) -> Img {
+        let (w, h) = (self.width as usize, self.height as usize);
+        (0..h).map(|j| (0..w).map(|i| { let k = (j * w + i) * 3; Rgb([buf[k], buf[k + 1], buf[k + 2]]) }).collect()).collect()
+    }
+
+    /// async_render / Viewport::render over every device of `scene`: sample ranges (one peer-memory combine on the
+    /// first device) or round-robin row bands (no exchange, bit-identical to one device).
+    pub fn render_gpu_multi(&self, integrator: Integrator, mode: Mode, scene: &GpuSceneMulti, split: Split, seed: u64) -> Result<Img, String> {
+        let cam = self.gpu_camera();
+        let o = self.gpu_opts(integrator, mode, seed);
+        let mut buf = vec![0f32; self.width as usize * self.height as usize * 3];
+        check(unsafe { rtw_render_multi(scene.h, &cam, &o, split as u32, 0, buf.as_mut_ptr()) })?;
+        Ok(self.to_img(&buf))
+    }
+
+    /// render_multi (viewport.rs:249-269) with frame k on device k mod n: one call, no exchange between devices.
+    pub fn render_multi_gpu_frames(&self, integrator: Integrator, scene: &GpuSceneMulti, seed: u64) -> Result<Vec<Img>, String> {
+        let cam = self.gpu_camera();
+        let o = self.gpu_opts(integrator, Mode::Random, seed);
+        let n = self.width as usize * self.height as usize * 3;
+        let mut buf = vec![0f32; n * self.number_of_frames];
+        check(unsafe { rtw_render_frames_multi(scene.h, &cam, &o, self.start_frame as u32, self.number_of_frames as u32, buf.as_mut_ptr()) })?;
+        Ok(buf.chunks(n).map(|f| self.to_img(f)).collect())
+    }
+
     fn gpu_camera(&self) -> rtw_camera {
         // the private derived fields of Viewport (viewport.rs:56-67), copied verbatim: pixel00 is
         // `upper_left_corner` (already offset by half a pixel, viewport.rs:382-387)
