@@ -276,7 +276,7 @@ def run_b200(args):
         elif part == "tiles":
             # row bands dealt round-robin: every rank renders and RESOLVES its own bands in place in a
             # zeroed frame; the frames are disjoint, so the gather to rank 0 is a reduce(sum) of them with zeros
-            # (x + 0 = x: bit-identical to one GPU). No sample reduction anywhere.
+            # (x + 0 = x: the gather changes no value). No sample reduction across GPUs anywhere.
             acc = [0.0] * 8
             if world > 1:
                 buf.zero_()

@@ -310,8 +310,9 @@ int rtw_bilateral_filter(const uint8_t* rgb8, uint32_t width, uint32_t height, u
  *                      depend on n beyond f32 summation order); one kernel on devices[0] reads the n buffers
  *                      over NVLink peer memory, adds them in device order and resolves (/spp, powf(1/gamma)).
  *   RTW_SPLIT_TILES    bands of `band_rows` rows (0 = 8) dealt round-robin; each device resolves its bands and
- *                      copies them straight into their place in out_rgb. No reduction: bit-identical to
- *                      one device.
+ *                      copies them straight into their place in out_rgb. No reduction across devices: every
+ *                      pixel is summed on one device (equal to a one-device render up to the order of
+ *                      that device's own f32 adds).
  *   RTW_SPLIT_FRAMES   (rtw_render_frames_multi) render_multi's frame k -> devices[k mod n]; no exchange.
  * A device may appear more than once in `devices` (its shares then run concurrently on separate streams
  * of that device), which is how a one-GPU box exercises every code path. `out_rgb` is HOST memory. */

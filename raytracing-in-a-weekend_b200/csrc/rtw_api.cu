@@ -483,6 +483,7 @@ int ensure_pool(rtw_scene* s, unsigned long long n_paths) {
             (rc = pool_alloc(s, &q.thr, cap))) return rc;
         if ((rc = pool_alloc(s, &s->pool.hit, cap))) return rc;
         if ((rc = pool_alloc(s, &s->pool.supply, (size_t)cap / 16u))) return rc;      // 2 words per warp of 32 slots
+        if ((rc = pool_alloc(s, &s->pool.warp_live, (size_t)cap / 32u))) return rc;
         s->pool_allocated = cap;
     }
     if (!s->d_wc) {
@@ -569,6 +570,11 @@ int enqueue_wavefront(rtw_scene* s, const RenderParams& P, int variant, float* d
         if (k >= 2u) {
             const uint32_t j = (k - 2u) & 3u;
             CK(cudaEventSynchronize(s->wf_ev[j]));
+            // the sample supply has run out: from here on slots only die (WfLaunch::drain)
+            if (!L.drain && s->h_wc[j].next_path >= init.total_paths && !env_u32("RTW_WF_NO_DRAIN", 0u)) {
+                L.drain = 1u;
+                L.chunk = std::max(L.chunk, 2048u);
+            }
             // the last shade of batch k-2 carried mark (k-1)*batch: no live slot after it => the frame is done
             if (s->h_wc[j].live_mark != (k - 1u) * batch) break;
         }

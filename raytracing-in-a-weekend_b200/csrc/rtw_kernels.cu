@@ -227,6 +227,18 @@ wf_extend_kernel(const Scene sc, const RenderParams P, const WfPool pool, WfCoun
                 c_pos = base; c_end = min(base + L.chunk, n);
                 if (base >= n) { more = false; c_end = c_pos; }
             }
+            if (L.drain) {
+                // skip whole groups of 32 slots whose shade warp has gone dead for good: 32 flags per load
+                while (c_pos < c_end && (c_pos & 31u) == 0u) {
+                    const uint32_t ng = min(32u, (c_end - c_pos) >> 5);
+                    if (ng == 0u) break;
+                    const uint32_t f = lane < ng ? __ldg(&pool.warp_live[(c_pos >> 5) + lane]) : 0u;
+                    const uint32_t lm = __ballot_sync(FULL, f != 0u);
+                    if (lm == 0u) { c_pos += 32u * ng; continue; }
+                    c_pos += 32u * (uint32_t)(__ffs(lm) - 1);
+                    break;
+                }
+            }
             const uint32_t take = min((uint32_t)__popc(idle), c_end - c_pos);
             SCHED_COUNT(step, 3, take);
             SCHED_TIME_BEGIN(3);
@@ -376,6 +388,24 @@ wf_shade_kernel(const Scene sc, const RenderParams P, const WfPool pool, WfCount
         wc->head = 0u;                                      // this iteration's extend is over
         wc->iterations += 1ull;
     }
+    const Noise* nt = sc.noises;
+#if RTW_WF_SHADE_SMEM_NOISE
+    // A/B of north_star's "Perlin tables staged in shared memory" for THIS kernel (the persistent megakernel stages
+    // them once per block lifetime, above). Here a block lives for 128 slots: every block of every launch copies the
+    // 4.9 KB table (38 B per slot, a third of the slot's own record) to serve the few slots that hit a noise texture,
+    // and 10 resident blocks hold 49-98 KB of shared memory that L1 loses. Measured, not kept
+    // (profiles/r2*_ab_shade_smem_noise.txt); the tables stay in global memory, where the lanes that need them
+    // find them in L1 / L2.
+    __shared__ Noise s_noise[RTW_SMEM_NOISES];
+    if (sc.n_noises > 0 && sc.n_noises <= RTW_SMEM_NOISES) {
+        const uint4* src = reinterpret_cast<const uint4*>(sc.noises);
+        uint4* dst = reinterpret_cast<uint4*>(s_noise);
+        const uint32_t nvec = sc.n_noises * (uint32_t)(sizeof(Noise) / 16);
+        for (uint32_t w = threadIdx.x; w < nvec; w += blockDim.x) dst[w] = __ldg(&src[w]);
+        nt = s_noise;
+        __syncthreads();
+    }
+#endif
     const WfQueue q = pool.q;                               // grid * block == capacity (a multiple of 256)
     const uint32_t W = P.cam.width;
     const unsigned long long total = L.total_paths;        // a launch parameter: reading it from wc put an L2 round trip at the head of every warp
@@ -395,6 +425,7 @@ wf_shade_kernel(const Scene sc, const RenderParams P, const WfPool pool, WfCount
     const uint32_t lane = threadIdx.x & 31u;
     Path path;
     bool alive = false, was_live = false, fresh = false;
+    if (L.drain && !init && __ldg(&pool.warp_live[e >> 5]) == 0u) return;   // (whole warp) dead for good: WfLaunch::drain
     if (!init) {
         const float4 rd = q.d[e];
         was_live = f2u(rd.w) != WF_DEAD;
@@ -412,7 +443,7 @@ wf_shade_kernel(const Scene sc, const RenderParams P, const WfPool pool, WfCount
             T.o = v3(ro.x, ro.y, ro.z); T.d = v3(rd.x, rd.y, rd.z);
             T.t = u2f(hit.x); T.ref = hit.y; T.inner = hit.z;
             TraceCtx cx = path_ctx(sc, P, path, wp);
-            bool finished = segment_end(cx, sc.noises, P, path, T);
+            bool finished = segment_end(cx, nt, P, path, T);
             if (!finished && path.depth_left < 1u) finished = true;   // ray_color.rs:14-16: the next call returns black
             // L = emitted + col_mod * L(next): what this segment adds (thr * emitted, thr *
             // background) goes straight into the frame, so no radiance travels with the path. A path
@@ -481,6 +512,12 @@ wf_shade_kernel(const Scene sc, const RenderParams P, const WfPool pool, WfCount
             }
         }
     }
+    {
+        // A warp that ends a launch without a live slot found the sample supply exhausted (every lane asked and none
+        // got a sample): it stays dead for the rest of the frame, and says so for the drain (WfLaunch::drain).
+        const uint32_t alive_mask = __ballot_sync(FULL, alive);
+        if (lane == 0u && (init || alive_mask == 0u)) pool.warp_live[e >> 5] = alive_mask != 0u ? 1u : 0u;
+    }
     if (!alive && !was_live && !init) return;                         // dead before, dead now: nothing to write
     if (alive) {
         q.o[e] = make_float4(path.ray.o.x, path.ray.o.y, path.ray.o.z, path.ray.time);
@@ -521,9 +558,13 @@ cudaError_t RTW_FN(launch_wf_shade)(const Scene& sc, const RenderParams& P, cons
     return cudaGetLastError();
 }
 
+// The opt-in limit for dynamic shared memory is set to one constant - the deepest stack the builder allows
+// (RTW_MAX_STACK_WORDS columns) - whatever size is being asked about: scenes with different stack depths share
+// these kernels, also across host threads (rtw_multi.cu), and an attribute that followed the last query made a
+// concurrent launch of a deeper scene fail with "invalid argument".
 cudaError_t RTW_FN(wf_extend_occupancy)(int* blocks_per_sm, size_t smem_bytes) {
     cudaError_t e = cudaFuncSetAttribute(RTW_CAT(variant_, RTW_VARIANT)::wf_extend_kernel,
-                                         cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes);
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize, RTW_MAX_STACK_WORDS * RTW_WF_BLOCK * 4);
     if (e != cudaSuccess) return e;
     return cudaOccupancyMaxActiveBlocksPerMultiprocessor(blocks_per_sm, RTW_CAT(variant_, RTW_VARIANT)::wf_extend_kernel,
                                                          RTW_WF_BLOCK, smem_bytes);
@@ -531,7 +572,7 @@ cudaError_t RTW_FN(wf_extend_occupancy)(int* blocks_per_sm, size_t smem_bytes) {
 
 cudaError_t RTW_FN(mega_occupancy)(int* blocks_per_sm, size_t smem_bytes) {
     cudaError_t e = cudaFuncSetAttribute(RTW_CAT(variant_, RTW_VARIANT)::mega_kernel,
-                                         cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes);
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize, RTW_MAX_STACK_WORDS * RTW_MEGA_BLOCK * 4);
     if (e != cudaSuccess) return e;
     return cudaOccupancyMaxActiveBlocksPerMultiprocessor(blocks_per_sm, RTW_CAT(variant_, RTW_VARIANT)::mega_kernel,
                                                          RTW_MEGA_BLOCK, smem_bytes);

@@ -59,6 +59,7 @@ struct WfPool {
     WfQueue q;
     uint4*  hit;         // bits(t), ref, inner, 0   (extend -> shade)
     unsigned long long* supply;   // per shade warp: [next, end) of its reserved sample indices
+    uint32_t* warp_live;          // per shade warp (32 slots): 0 once none of its slots can ever be live again (drain, below)
     uint32_t capacity;
 };
 struct WfCounters {
@@ -83,10 +84,18 @@ struct WfLaunch {
     // dissolve: 8 / 16 is +3.6 % there; where they are common (C4: two of eight leaves) any bias costs
     // 1-6 % (profiles/r1j_ab_vote_weights.txt). rtw_api.cu picks by the share of instance leaves.
     uint32_t prim_w, event_w;
+    // Drain: once the frame's sample supply is exhausted (the host sees WfCounters::next_path pass the end, two batches
+    // late) slots die for good, and for the last ~depth iterations both kernels used to scan a pool that is almost or
+    // entirely dead: ~0.2 ms per iteration over 6 Mi slots, ~13 ms per frame, a fixed cost that does not shrink with
+    // the share of the frame a GPU renders (the 1 -> 8 GPU efficiency loss of round 1). In drain mode a shade warp
+    // whose `warp_live` word is 0 leaves after that one load, and extend reads 32 of those words at a time and skips
+    // dead groups of 32 slots without touching their records (and reserves `chunk` = 2048 slots per atomic).
+    uint32_t drain;
     uint32_t node_sure;              // lanes on a node from which the node step wins for certain: ceil(32 w / (4 + w)), w = max(prim_w, event_w)
     int extend_grid, shade_grid;
     size_t smem_bytes;
 };
+#define RTW_MAX_STACK_WORDS 160     // deepest traversal stack column any scene may ask for (scene_build.cpp / rtw_api.cu refuse more)
 #define RTW_WF_BLOCK 128
 #ifndef RTW_WF_EXTEND_MINB
 #define RTW_WF_EXTEND_MINB 6      // min resident blocks per SM asked of the compiler for wf_extend (80 registers, no spills; +2.2 % over 5 blocks, profiles/r1h_ab_inline_minblocks.txt)
@@ -103,6 +112,9 @@ struct WfLaunch {
 #endif
 #ifndef RTW_WF_FASTVOTE
 #define RTW_WF_FASTVOTE 1         // 1: skip the leaf / event ballots of wf_extend's vote when the node lanes win anyway (same decisions)
+#endif
+#ifndef RTW_WF_SHADE_SMEM_NOISE
+#define RTW_WF_SHADE_SMEM_NOISE 0   // 1: wf_shade stages the Perlin tables in shared memory per block (A/B only, see the kernel)
 #endif
 #ifndef RTW_WF_SHADE_MINB
 #define RTW_WF_SHADE_MINB 10      // min resident blocks per SM asked of the compiler for wf_shade

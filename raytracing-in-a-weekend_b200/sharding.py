@@ -9,7 +9,8 @@ independent, so the three natural partitions are
             to f32 summation order); one NCCL reduce(sum) of W*H*3 f32 to rank 0, then resolve
             (/spp, powf(1/gamma)) there. The only exchange of the whole frame: 7.68 MB for 800x800.
   tiles   : bands of `band` rows dealt round-robin; each rank resolves its own bands; gather to
-            rank 0. No reduction, so the result is bit-identical to a 1-GPU render.
+            rank 0. No reduction across ranks: every pixel is summed on one GPU (a 1-GPU render's value up to the
+            order of that GPU's own f32 adds; bit-identical on the deterministic CPU test backends).
   frames  : render_multi's frames dealt round-robin, frame k -> rank k mod n; no exchange at all.
 
 `torch.distributed` is plumbing only (NCCL over NVLink on the GPU box, gloo in the CPU tests).

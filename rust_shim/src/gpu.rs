@@ -162,7 +162,7 @@ impl Viewport {
     }
 
     /// async_render / Viewport::render over every device of `scene`: sample ranges (one peer-memory combine on the
-    /// first device) or round-robin row bands (no exchange, bit-identical to one device).
+    /// first device) or round-robin row bands (no exchange between devices).
     pub fn render_gpu_multi(&self, integrator: Integrator, mode: Mode, scene: &GpuSceneMulti, split: Split, seed: u64) -> Result<Img, String> {
         let cam = self.gpu_camera();
         let o = self.gpu_opts(integrator, mode, seed);
