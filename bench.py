@@ -64,6 +64,7 @@ def parse_args():
     ap.add_argument("--band", type=int, default=8, help="rows per band of --partition tiles")
     ap.add_argument("--single-process", action="store_true",
                     help="one process drives --gpus N devices through rtw_render_multi (samples / tiles)")
+    ap.add_argument("--devices", default="", help="--single-process: explicit device list, e.g. 0,0 (two shares side by side on device 0)")
     ap.add_argument("--synthetic-textures", action="store_true",
                     help="generated stand-ins instead of the reference's earthmap.jpg / default.png (named in `data`)")
     return ap.parse_args()
@@ -443,18 +444,24 @@ def run_b200(args):
         k_hbm_gbs = k_hbm_bytes * rays_launch / (k_ms * 1e-3) / 1e9
         cands = [("fp32", tflops, fp32_peak, "TFLOP/s"), ("l2", l2_gbs, l2_peak, "GB/s"), ("hbm", k_hbm_gbs, hbm_peak, "GB/s")]
         bname, bach, bpeak, bunit = max(cands, key=lambda c: c[1] / c[2])
-        traffic, traffic_src = None, None
+        traffic, traffic_src, measured = None, None, None
         try:      # DRAM bytes of the dominant kernel per launch, from the committed ncu --set full capture
             tj = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))[kname]
             # the capture ran at slots_per_launch slots; this run's launches hold rays_launch rays
             traffic = float(tj["dram_bytes_per_launch"]) * rays_launch / float(tj.get("slots_per_launch", rays_launch))
             traffic_src = tj["source"]
+            # what the memory system actually moved for this kernel in that capture, per launch, scaled the same way:
+            # the algorithmic scene bytes (`per_ray.scene_bytes`) are mostly served by L1 - L2 sees the misses only
+            scale = rays_launch / float(tj.get("slots_per_launch", rays_launch))
+            measured = {"l2_bytes_per_launch": float(tj["l2_bytes_per_launch"]) * scale, "l1_hit_rate_pct": tj["l1_hit_rate_pct"],
+                        "l2_hit_rate_pct": tj["l2_hit_rate_pct"], "l2_bytes_per_ray": float(tj["l2_bytes_per_launch"]) / float(tj["slots_per_launch"]),
+                        "note": "lts__t_sectors.sum x 32 B and l1tex__t_sector_hit_rate.pct of the committed ncu --set full capture"}
         except Exception:
             pass
         roofline = {"kernel": kname, "bound": bname, "achieved": bach, "peak": bpeak, "unit": bunit,
                     "frac": bach / bpeak, "traffic": traffic, "traffic_source": traffic_src,
                     "traffic_note": "ncu DRAM bytes per slot (captured at a pool of 2 000 128 slots) x this run's rays per launch",
-                    "algorithmic_hbm_bytes_per_launch": k_hbm_bytes * rays_launch,
+                    "algorithmic_hbm_bytes_per_launch": k_hbm_bytes * rays_launch, "measured_memory": measured,
                     "peak_source": "rtw_microbench on this GPU for fp32 and L2 (MEASURED_PEAKS.json has neither); MEASURED_PEAKS.json hbm_gbs for HBM" if hbm_src == "measured" else "rtw_microbench on this GPU for fp32 and L2; B200_PROFILING.md fallback for HBM",
                     "kernel_ms_per_launch": k_ms, "rays_per_launch": rays_launch,
                     "launches_per_step": iters if wavefront else 1,
@@ -508,9 +515,13 @@ def run_single_process(args):
         raise SystemExit("--single-process: samples or tiles (frames: rtw_render_frames_multi is exercised by the tests)")
     be = CudaBackend(device=0)
     n = args.gpus
-    if be.device_count() < n:
-        raise SystemExit(f"--single-process --gpus {n}: only {be.device_count()} device(s) visible")
-    devices = list(range(n))
+    if args.devices:
+        devices = [int(x) for x in args.devices.split(",")]
+        n = len(set(devices))
+    else:
+        devices = list(range(n))
+    if be.device_count() <= max(devices):
+        raise SystemExit(f"--single-process: device {max(devices)} asked for, only {be.device_count()} device(s) visible")
     job = make_job(args)
     vp = job.viewport
     cam = vp.camera(be)
@@ -547,7 +558,7 @@ def run_single_process(args):
     line = {"metric": METRIC, "value": paths_frame * args.steps / (dev_ms * 1e-3) / 1e6, "unit": UNIT, "n_gpus": n, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": dev_ms / args.steps, "higher_is_better": True, "scaling": "strong",
             "vs_baseline": None, "dtype": "f32", "data": data_label(),
-            "config": {"workload": workload_name(job), "launch": "single process, rtw_render_multi (one host thread + stream per device)",
+            "config": {"workload": workload_name(job), "launch": "single process, rtw_render_multi (one host thread + stream per share)", "devices": devices,
                        "partition": ("sample ranges, combined on device 0 by one peer-memory kernel" if split == A.RTW_SPLIT_SAMPLES
                                      else f"row bands of {args.band or 8} rows dealt round-robin, copied straight to the host image"),
                        "timing": "value: max over devices of the share's device time (CUDA events) + combine kernel; wall_ms_per_step: host clock around the call"},

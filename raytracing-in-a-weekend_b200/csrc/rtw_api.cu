@@ -573,7 +573,11 @@ int enqueue_wavefront(rtw_scene* s, const RenderParams& P, int variant, float* d
             // the sample supply has run out: from here on slots only die (WfLaunch::drain)
             if (!L.drain && s->h_wc[j].next_path >= init.total_paths && !env_u32("RTW_WF_NO_DRAIN", 0u)) {
                 L.drain = 1u;
-                L.chunk = std::max(L.chunk, 2048u);
+                // fewer reservations of a mostly dead pool, but still >= 8 chunks per resident warp: the first drain
+                // iterations are mostly live and need the balance (2048-slot chunks cost 6 % at 200 spp, profiles/r2b_ab_*)
+                const uint32_t warps = (uint32_t)L.extend_grid * (RTW_WF_BLOCK / 32u);
+                const uint32_t c = (s->pool.capacity / std::max(1u, warps * 8u)) & ~63u;
+                L.chunk = std::max(L.chunk, std::min(1024u, c));
             }
             // the last shade of batch k-2 carried mark (k-1)*batch: no live slot after it => the frame is done
             if (s->h_wc[j].live_mark != (k - 1u) * batch) break;

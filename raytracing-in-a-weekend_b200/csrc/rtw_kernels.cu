@@ -17,6 +17,7 @@
 // the SM as three f32 REDs per pixel per item. No tensor cores: nothing here is a contraction.
 //
 // Compiled three times (see rtw_kernels.h): RTW_VARIANT = fast | strict | count.
+#include <mutex>
 #include "rtw_kernels.h"
 
 #ifndef RTW_VARIANT
@@ -558,21 +559,31 @@ cudaError_t RTW_FN(launch_wf_shade)(const Scene& sc, const RenderParams& P, cons
     return cudaGetLastError();
 }
 
-// The opt-in limit for dynamic shared memory is set to one constant - the deepest stack the builder allows
-// (RTW_MAX_STACK_WORDS columns) - whatever size is being asked about: scenes with different stack depths share
-// these kernels, also across host threads (rtw_multi.cu), and an attribute that followed the last query made a
-// concurrent launch of a deeper scene fail with "invalid argument".
+// The opt-in limit for dynamic shared memory only ever grows (per kernel and device, rounded up to 8 KB): scenes
+// with different stack depths share these kernels, also across host threads (rtw_multi.cu), and a limit that followed
+// the last query made a concurrent launch of a deeper scene fail with "invalid argument".
+static cudaError_t raise_smem_limit(const void* kernel, size_t smem_bytes, int which) {
+    static std::mutex m;
+    static int limit[2][64] = {};
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    const int want = (int)((smem_bytes + 8191u) & ~(size_t)8191u);
+    std::lock_guard<std::mutex> lk(m);
+    if (dev >= 0 && dev < 64 && limit[which][dev] >= want) return cudaSuccess;
+    e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, want);
+    if (e == cudaSuccess && dev >= 0 && dev < 64) limit[which][dev] = want;
+    return e;
+}
 cudaError_t RTW_FN(wf_extend_occupancy)(int* blocks_per_sm, size_t smem_bytes) {
-    cudaError_t e = cudaFuncSetAttribute(RTW_CAT(variant_, RTW_VARIANT)::wf_extend_kernel,
-                                         cudaFuncAttributeMaxDynamicSharedMemorySize, RTW_MAX_STACK_WORDS * RTW_WF_BLOCK * 4);
+    cudaError_t e = raise_smem_limit((const void*)RTW_CAT(variant_, RTW_VARIANT)::wf_extend_kernel, smem_bytes, 0);
     if (e != cudaSuccess) return e;
     return cudaOccupancyMaxActiveBlocksPerMultiprocessor(blocks_per_sm, RTW_CAT(variant_, RTW_VARIANT)::wf_extend_kernel,
                                                          RTW_WF_BLOCK, smem_bytes);
 }
 
 cudaError_t RTW_FN(mega_occupancy)(int* blocks_per_sm, size_t smem_bytes) {
-    cudaError_t e = cudaFuncSetAttribute(RTW_CAT(variant_, RTW_VARIANT)::mega_kernel,
-                                         cudaFuncAttributeMaxDynamicSharedMemorySize, RTW_MAX_STACK_WORDS * RTW_MEGA_BLOCK * 4);
+    cudaError_t e = raise_smem_limit((const void*)RTW_CAT(variant_, RTW_VARIANT)::mega_kernel, smem_bytes, 1);
     if (e != cudaSuccess) return e;
     return cudaOccupancyMaxActiveBlocksPerMultiprocessor(blocks_per_sm, RTW_CAT(variant_, RTW_VARIANT)::mega_kernel,
                                                          RTW_MEGA_BLOCK, smem_bytes);
