@@ -104,6 +104,13 @@ typedef struct rtw_instance {
     float    density;
 } rtw_instance;
 
+/* ---- one entry of the light list: a top-level sphere or quad of the scene */
+enum { RTW_LIGHT_SPHERE = 0, RTW_LIGHT_QUAD = 1 };
+typedef struct rtw_light {
+    uint32_t kind;                     /* RTW_LIGHT_* */
+    uint32_t index;                    /* into spheres[0..n_top_spheres) or quads[0..n_top_quads) */
+} rtw_light;
+
 /* ---- Scene (Rust/src/viewport.rs:79-88). spheres[0..n_top_spheres) and quads[0..n_top_quads)
  *      are Scene.spheres / Scene.quads; the rest belong to instances. */
 typedef struct rtw_scene_desc {
@@ -119,6 +126,11 @@ typedef struct rtw_scene_desc {
     const rtw_texture*  textures;
     const rtw_noise*    noises;
     float background[3];               /* Scene.background_color, viewport.rs:87 */
+    /* Light list of the light-biased integrators (Rust2/src/viewport/ray_color.rs:55-164 take `lights:
+     * Arc<[Arc<dyn Object>]>` from their caller): scene primitives that are ALSO in spheres[0..n_top_spheres) /
+     * quads[0..n_top_quads). May be empty (n_lights = 0, lights = NULL). */
+    uint32_t n_lights;
+    const struct rtw_light* lights;
 } rtw_scene_desc;
 
 /* ---- Camera: the derived (private) fields of Viewport (viewport.rs:48-77). Fill by hand or
@@ -139,7 +151,15 @@ enum {
     RTW_INT_BG_COLOR   = 2,  /* ray_color_bg_color   viewport/ray_color.rs:43-92   mint 1e-3 maxt 1e4 */
     RTW_INT_NORMAL     = 3,  /* first-hit normal shading, viewport.rs:524-554      mint 0    maxt 1e3 */
     RTW_INT_ALBEDO     = 4,  /* first-hit col_mod (miss -> background)             mint 1e-3 maxt 1e5 */
-    RTW_INT_GLASS_TEST = 5   /* glass_tests.rs:8-55: non-mirror hit -> yellow, miss -> blue; 1e-3,1e3 */
+    RTW_INT_GLASS_TEST = 5,  /* glass_tests.rs:8-55: non-mirror hit -> yellow, miss -> blue; 1e-3,1e3 */
+    /* The two light-biased estimators of the Rust2 tree, over THIS scene model (uber-material, emission
+     * in the material): at a hit, one shadow ray per light of rtw_scene_desc.lights towards the middle of the light's
+     * box; the light counts when the scene's closest hit along that ray is the light itself, and adds
+     * emitted * material_pdf / distance^2. mint 1e-3, maxt 1e3 (Rust2's test scenes, tests.rs:639-644). Megakernel only. */
+    RTW_INT_LIGHT_CAST   = 6, /* light_biased_ray_cast  Rust2/src/viewport/ray_color.rs:55-109: first hit only, direct light
+                               * averaged over the lights that count, + emitted; miss -> background */
+    RTW_INT_LIGHT_BIASED = 7  /* light_biased_ray_color ray_color.rs:111-164: (L(reflected) + sum w * direct) * col_mod /
+                               * (1 + n w) + emitted, w = rtw_render_opts.light_weight; depth exhausted or miss -> background */
 };
 
 /* ---- which reference render loop to mirror */
@@ -186,6 +206,7 @@ typedef struct rtw_render_opts {
     uint32_t row_begin, row_count;
     uint32_t output;         /* RTW_OUT_* */
     uint32_t flags;
+    float    light_weight;   /* RTW_INT_LIGHT_BIASED: `biased_weight` of light_biased_ray_color (ray_color.rs:116) */
 } rtw_render_opts;
 
 typedef struct rtw_stats {

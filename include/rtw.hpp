@@ -261,6 +261,7 @@ struct FlatScene {
     std::vector<rtw_material> materials;
     std::vector<rtw_texture> textures;
     std::vector<rtw_noise> noises;
+    std::vector<rtw_light> lights;
     std::vector<ImageTexture::Ptr> keep;
 };
 
@@ -271,6 +272,9 @@ struct Scene {   // viewport.rs:79-88. BVH construction happens in the backend a
     std::vector<Quad> quads;
     std::vector<Instance> instances;
     Vec3 background_color;             // pub field, viewport.rs:87
+    // the `lights` argument of Rust2's light-biased integrators (Rust2/src/viewport/ray_color.rs:59,115): top-level
+    // primitives of this scene, named by position: {RTW_LIGHT_SPHERE, i} = spheres[i], {RTW_LIGHT_QUAD, i} = quads[i]
+    std::vector<rtw_light> lights;
 
     static Scene new_(std::vector<Sphere> s, std::vector<Quad> q, std::vector<Instance> i) {   // viewport.rs:120-135
         Scene sc; sc.spheres = std::move(s); sc.quads = std::move(q); sc.instances = std::move(i); return sc;
@@ -359,6 +363,12 @@ struct Scene {   // viewport.rs:79-88. BVH construction happens in the backend a
         d.spheres = fs->spheres.data(); d.quads = fs->quads.data(); d.instances = fs->instances.data();
         d.materials = fs->materials.data(); d.textures = fs->textures.data(); d.noises = fs->noises.data();
         background_color.store(d.background);
+        for (const rtw_light& l : lights) {
+            const size_t lim = l.kind == RTW_LIGHT_SPHERE ? spheres.size() : quads.size();
+            if (l.kind > RTW_LIGHT_QUAD || l.index >= lim) throw Error(RTW_E_INVALID, "light is not a top-level primitive of the scene");
+        }
+        fs->lights = lights;
+        d.n_lights = (uint32_t)fs->lights.size(); d.lights = fs->lights.empty() ? nullptr : fs->lights.data();
         return fs;
     }
 };
@@ -400,7 +410,9 @@ enum class Integrator : uint32_t {
     BgColor = RTW_INT_BG_COLOR,        // ray_color_bg_color  viewport/ray_color.rs:43-92
     Normal = RTW_INT_NORMAL,           // viewport.rs:524-554
     Albedo = RTW_INT_ALBEDO,
-    GlassTest = RTW_INT_GLASS_TEST     // viewport/glass_tests.rs:8-55
+    GlassTest = RTW_INT_GLASS_TEST,    // viewport/glass_tests.rs:8-55
+    LightCast = RTW_INT_LIGHT_CAST,    // Rust2/src/viewport/ray_color.rs:55-109 (lights = Scene::lights)
+    LightBiased = RTW_INT_LIGHT_BIASED // Rust2/src/viewport/ray_color.rs:111-164 (weight = Viewport::light_weight)
 };
 
 struct Viewport {   // viewport.rs:48-77; pub fields keep the reference's names
@@ -417,6 +429,7 @@ struct Viewport {   // viewport.rs:48-77; pub fields keep the reference's names
     Vec3 origin, direction{0.f, 0.f, -1.f}, vup{0.f, 1.f, 0.f};
     uint64_t seed = 1;                          // the reference is unseeded; SURVEY §8d "Render RNG"
     uint32_t flags = 0;                         // RTW_FLAG_*
+    float light_weight = 1.0f;                  // `biased_weight` of light_biased_ray_color (Rust2 ray_color.rs:116)
 
     // Viewport::new (viewport.rs:308-401)
     static Viewport new_(size_t width, float aspect_ratio, size_t samples, size_t depth, float gamma,
@@ -453,7 +466,7 @@ struct Viewport {   // viewport.rs:48-77; pub fields keep the reference's names
         o.shutter_speed = shutter_speed; o.fps = fps; o.frame = (uint32_t)frame; o.seed = seed;
         o.mint = o.maxt = 0.f;
         o.sample_begin = o.sample_count = o.row_begin = o.row_count = 0;
-        o.output = RTW_OUT_RESOLVED; o.flags = flags;
+        o.output = RTW_OUT_RESOLVED; o.flags = flags; o.light_weight = light_weight;
         return o;
     }
     Img run(Integrator ray_color, const GpuScene& scene, uint32_t mode) const {

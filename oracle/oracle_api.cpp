@@ -86,6 +86,13 @@ int oracle_scene_create(const rtw_scene_desc* d, uint32_t build_seed, oracle_sce
         o.const_density = in.density_kind == RTW_DENSITY_CONST; o.density = in.density;
     }
     sc.background_color = v3(d->background);
+    if (d->n_lights && !d->lights) return RTW_E_INVALID;
+    for (uint32_t i = 0; i < d->n_lights; ++i) {
+        const rtw_light& l = d->lights[i];
+        const bool quad = l.kind == RTW_LIGHT_QUAD;
+        if (l.kind > RTW_LIGHT_QUAD || l.index >= (quad ? d->n_top_quads : d->n_top_spheres)) return RTW_E_INVALID;
+        sc.lights.push_back(Scene::Light{quad, l.index});
+    }
     sc.build(build_seed);
     *out = os.release();
     return RTW_OK;

@@ -11,7 +11,7 @@
 
 namespace oracle {
 
-struct IntegratorCfg { uint32_t kind; float mint, maxt; };
+struct IntegratorCfg { uint32_t kind; float mint, maxt; float light_weight = 1.0f; };
 
 inline IntegratorCfg integrator_cfg(const rtw_render_opts& o) {
     IntegratorCfg c{o.integrator, 0.001f, 100000.0f};
@@ -22,7 +22,10 @@ inline IntegratorCfg integrator_cfg(const rtw_render_opts& o) {
         case RTW_INT_NORMAL:     c.mint = 0.0f;   c.maxt = 1000.0f; break;    // viewport.rs:525-526
         case RTW_INT_ALBEDO:     c.mint = 0.001f; c.maxt = 100000.0f; break;
         case RTW_INT_GLASS_TEST: c.mint = 0.001f; c.maxt = 1000.0f; break;    // glass_tests.rs:13-14
+        case RTW_INT_LIGHT_CAST:
+        case RTW_INT_LIGHT_BIASED: c.mint = 0.001f; c.maxt = 1000.0f; break;  // Scene::new(.., 0.001, 1000.0), Rust2 tests.rs:639-644
     }
+    c.light_weight = o.light_weight;
     if (o.maxt > 0.0f) { c.mint = o.mint; c.maxt = o.maxt; }
     return c;
 }
@@ -32,6 +35,79 @@ inline Vec3 sky_gradient(const Ray& r) {
     Vec3 unit_direction = r.direction.unit();
     float t = 0.5f * (unit_direction.y + 1.0f);
     return Vec3((1.0f - t) + t * 0.5f, (1.0f - t) + t * 0.7f, 1.0f);
+}
+
+// ---- Rust2's light-biased estimators (Rust2/src/viewport/ray_color.rs:55-164) over the Rust/src scene model.
+// Material::material_pdf (Rust2/src/objects/material.rs:17): the uber-material's diffuse branch answers like
+// Lambertian (material.rs:44-63); Mirror (:93-101) and MirrorGlass (:199-235) are 0 for every direction but their own
+// reflection / refraction, so metallicness == 1 and opacity > 0 give 0 towards any light.
+inline float material_pdf(const Hit& h, const Ray& in, const Ray& r) {
+    if (h.mat.opacity > 0.0f || h.mat.metallicness == 1.0f) return 0.0f;
+    float cos = r.direction.unit().dot(h.normal.unit());
+    float v = in.direction.dot(h.normal) >= 0.0f ? -cos : cos;
+    v = v < 0.0f ? 0.0f : (v > 1.0f ? 1.0f : v);
+    return v * 0.31830988618379067154f;
+}
+// the light loop (ray_color.rs:67-92, 130-152). `biased`: the threshold on pdf and the weight of :141-147.
+inline Vec3 light_gather(const Hit& h, const Ray& in, const Scene& scene, const IntegratorCfg& ig, TraceCtx& cx, bool biased,
+                         float& count) {
+    Vec3 color(0.f, 0.f, 0.f);
+    const uint32_t bounce = cx.bounce;
+    for (const Scene::Light& l : scene.lights) {
+        // middle of l.get_aabb() (Interval::mid_point, Rust2/src/objects/aabb.rs:52-54)
+        Box3 b = l.quad ? PrimTraits<Quad>::leaf_box(scene.quads[l.index]) : PrimTraits<Sphere>::leaf_box(scene.spheres[l.index]);
+        Vec3 middle_l((b.x.min + b.x.max) * 0.5f, (b.y.min + b.y.max) * 0.5f, (b.z.min + b.z.max) * 0.5f);
+        Vec3 to_light = (middle_l - h.point).unit();
+        Ray r(h.point, to_light);                                   // Ray::new: time 0
+        cx.bounce = 0x8000u | (bounce & 0x7FFFu);                   // volume streams of the shadow ray (shared with the kernels)
+        OptHit hr = scene.collision_normal(r, ig.mint, ig.maxt, cx);
+        cx.bounce = bounce;
+        OptHit hl = l.quad ? scene.quads[l.index].collision_normal(r, ig.mint, ig.maxt)
+                           : scene.spheres[l.index].collision_normal(r, ig.mint, ig.maxt);
+        if (!hr || !hl) continue;
+        // `hr.0 == hl` (Hit: PartialEq over r, p, n, t - Rust2/src/objects/hit.rs:3-9)
+        if (!(hr->t == hl->t && hr->point.x == hl->point.x && hr->point.y == hl->point.y && hr->point.z == hl->point.z &&
+              hr->normal.x == hl->normal.x && hr->normal.y == hl->normal.y && hr->normal.z == hl->normal.z)) continue;
+        Vec3 emmited = hl->mat.emmited;
+        float pdf = material_pdf(h, in, r);
+        float distance2 = hl->t * hl->t * r.direction.dot(r.direction);
+        if (biased) {
+            if (pdf <= 1.0f / (255.0f * maxf(maxf(emmited.x, emmited.y), emmited.z))) continue;
+            count += ig.light_weight;
+            color += emmited * pdf / distance2 * ig.light_weight;
+        } else {
+            count += 1.0f;
+            color += emmited * pdf / distance2;
+        }
+    }
+    return color;
+}
+// light_biased_ray_cast (ray_color.rs:55-109): first hit only.
+inline Vec3 light_biased_ray_cast(const Ray& r, const Scene& scene, const IntegratorCfg& ig, TraceCtx& cx) {
+    OptHit hit = scene.collision_normal(r, ig.mint, ig.maxt, cx);
+    if (!hit) return scene.background_color;
+    float count = 0.0f;
+    Vec3 color = light_gather(*hit, r, scene, ig, cx, false, count);
+    return (count != 0.0f ? color * hit->col_mod / count : Vec3(0.f, 0.f, 0.f)) + hit->mat.emmited;
+}
+// light_biased_ray_color (ray_color.rs:111-164). `o.reflect(&h)` is Material::on_hit of Rust/src with the zero-direction
+// repair every Rust/src integrator applies (ray_color.rs:62-64).
+inline Vec3 light_biased_ray_color(const Ray& r, const Scene& scene, uint32_t depth, const IntegratorCfg& ig, TraceCtx& cx) {
+    if (depth <= 0) return scene.background_color;
+    OptHit hit = scene.collision_normal(r, ig.mint, ig.maxt, cx);
+    if (!hit) return scene.background_color;
+    float count = 1.0f;
+    bool front = !(r.direction.dot(hit->normal) > 0.0f);
+    OnHit oh = on_hit(hit->mat, *hit, r, *cx.rng);
+    Ray next = oh.next;
+    if (next.direction.close_to_zero()) next.direction = front ? hit->normal : hit->normal * -1.0f;
+    const uint32_t bounce = cx.bounce;
+    cx.bounce = bounce + 1;
+    Vec3 color = light_biased_ray_color(next, scene, depth - 1, ig, cx);
+    cx.bounce = bounce;
+    color += light_gather(*hit, r, scene, ig, cx, true, count);
+    cx.bounce = bounce + 1;
+    return color * hit->col_mod / count + hit->mat.emmited;
 }
 
 // Recursive, exactly as the reference. `depth` counts down (ray_color.rs:14-16).
@@ -49,6 +125,8 @@ inline Vec3 ray_color(const Ray& r, const Scene& scene, uint32_t depth, const In
         }
         return ig.kind == RTW_INT_NORMAL ? sky_gradient(r) : scene.background_color;
     }
+    if (ig.kind == RTW_INT_LIGHT_CAST) return light_biased_ray_cast(r, scene, ig, cx);
+    if (ig.kind == RTW_INT_LIGHT_BIASED) return light_biased_ray_color(r, scene, depth, ig, cx);
     if (depth < 1) return Vec3(0.f, 0.f, 0.f);
     OptHit hit = scene.collision_normal(r, ig.mint, ig.maxt, cx);
     if (hit) {

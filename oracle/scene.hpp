@@ -194,6 +194,9 @@ struct Scene {
     Bvh<Quad> qaabb;
     Bvh<Instance> iaabb;
     Vec3 background_color;
+    // the `lights` of Rust2's light-biased integrators (Rust2/src/viewport/ray_color.rs:59,115): top-level primitives
+    struct Light { bool quad; uint32_t index; };
+    std::vector<Light> lights;
 
     void build(uint32_t build_seed) {   // Scene::new, viewport.rs:120-135
         BuildRng br; br.seed = build_seed;

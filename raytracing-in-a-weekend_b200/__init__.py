@@ -8,7 +8,8 @@ from ._abi import (RTW_MODE_NO_RAND, RTW_MODE_RANDOM, RTW_MODE_STRATIFIED, RTW_O
                    RtwError, load_library)
 from .scene import (EMPTY_M, FUZZY3_M, GLASS_M, GLASSR_M, METALLIC_M, SCATTER_M, ImageTexture, Instance,
                     Material, PerlinNoise, Quad, Scene, Sphere, Triangle, Vec3, const_density, surface)
-from .viewport import (Viewport, async_render, get_default_backend, ray_color_albedo, ray_color_bg_color,
+from .viewport import (Viewport, async_render, get_default_backend, light_biased_ray_cast, light_biased_ray_color,
+                       ray_color_albedo, ray_color_bg_color,
                        ray_color_d, ray_color_glass_test, ray_color_gradient, ray_color_normal, render_multi,
                        set_default_backend)
 

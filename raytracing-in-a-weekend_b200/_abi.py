@@ -21,6 +21,8 @@ RTW_DENSITY_SURFACE, RTW_DENSITY_CONST = 0, 1
 RTW_SHAPE_PARALLELOGRAM, RTW_SHAPE_TRIANGLE = 0, 1
 # integrators
 RTW_INT_GRADIENT, RTW_INT_D, RTW_INT_BG_COLOR, RTW_INT_NORMAL, RTW_INT_ALBEDO, RTW_INT_GLASS_TEST = range(6)
+RTW_INT_LIGHT_CAST, RTW_INT_LIGHT_BIASED = 6, 7
+RTW_LIGHT_SPHERE, RTW_LIGHT_QUAD = 0, 1
 # modes
 RTW_MODE_RANDOM, RTW_MODE_STRATIFIED, RTW_MODE_NO_RAND = range(3)
 # outputs
@@ -59,6 +61,10 @@ class rtw_instance(C.Structure):
                 ("translation", f3), ("rotation", f3), ("density_kind", u32), ("density", f32)]
 
 
+class rtw_light(C.Structure):
+    _fields_ = [("kind", u32), ("index", u32)]
+
+
 class rtw_scene_desc(C.Structure):
     _fields_ = [("abi_version", u32),
                 ("n_spheres", u32), ("n_top_spheres", u32),
@@ -68,7 +74,7 @@ class rtw_scene_desc(C.Structure):
                 ("spheres", C.POINTER(rtw_sphere)), ("quads", C.POINTER(rtw_quad)),
                 ("instances", C.POINTER(rtw_instance)), ("materials", C.POINTER(rtw_material)),
                 ("textures", C.POINTER(rtw_texture)), ("noises", C.POINTER(rtw_noise)),
-                ("background", f3)]
+                ("background", f3), ("n_lights", u32), ("lights", C.POINTER(rtw_light))]
 
 
 class rtw_camera(C.Structure):
@@ -81,7 +87,7 @@ class rtw_render_opts(C.Structure):
                 ("shutter_speed", f32), ("fps", f32), ("frame", u32), ("seed", u64),
                 ("mint", f32), ("maxt", f32),
                 ("sample_begin", u32), ("sample_count", u32), ("row_begin", u32), ("row_count", u32),
-                ("output", u32), ("flags", u32)]
+                ("output", u32), ("flags", u32), ("light_weight", f32)]
 
 
 class rtw_stats(C.Structure):

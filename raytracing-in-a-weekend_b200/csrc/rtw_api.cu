@@ -376,6 +376,8 @@ int upload_scene(rtw_scene* s, HostScene& hs) {
     if ((rc = upload(s, hs.baked_sphere_src, &d.baked_sphere_src))) return rc;
     if ((rc = upload(s, hs.baked_quad_src, &d.baked_quad_src))) return rc;
     d.n_spheres_orig = hs.n_spheres_orig; d.n_quads_orig = hs.n_quads_orig;
+    if ((rc = upload(s, hs.lights, &d.lights))) return rc;
+    d.n_lights = hs.n_lights;
     d.top = hs.top;
     s->tops[0] = hs.top; s->tops[1] = hs.top_inside; s->tops[2] = hs.top_baked; s->tops[3] = hs.top_baked_inside;
     s->has_baked = hs.has_baked; s->n_walked_instances_baked = hs.n_walked_instances_baked;
@@ -628,8 +630,11 @@ int enqueue_render(rtw_scene* s, const rtw_camera* cam, const rtw_render_opts* o
     if ((o->flags & RTW_FLAG_WAVEFRONT) && (o->flags & RTW_FLAG_MEGAKERNEL)) return fail(RTW_E_INVALID, "both pipeline flags set");
     const uint64_t n_paths = (uint64_t)cam->width * P.row_count * P.sample_count;
     if ((o->flags & RTW_FLAG_WAVEFRONT) && P.depth > WF_MAX_DEPTH) return fail(RTW_E_UNSUPPORTED, "wavefront pipeline: depth > 4095 (use the megakernel)");
+    // the light-biased integrators trace their shadow rays from inside the shading step: megakernel only
+    if ((o->flags & RTW_FLAG_WAVEFRONT) && light_integrator(P.integrator)) return fail(RTW_E_UNSUPPORTED, "light-biased integrators run in the megakernel only");
     s->last_wavefront = (o->flags & RTW_FLAG_WAVEFRONT) ||
-                        (!(o->flags & RTW_FLAG_MEGAKERNEL) && n_paths >= (1ull << 18) && P.depth <= WF_MAX_DEPTH);
+                        (!(o->flags & RTW_FLAG_MEGAKERNEL) && n_paths >= (1ull << 18) && P.depth <= WF_MAX_DEPTH &&
+                         !light_integrator(P.integrator));
     if (s->last_wavefront) {
         s->launches = 0;
         if ((rc = enqueue_wavefront(s, P, variant, d_out, st))) return rc;

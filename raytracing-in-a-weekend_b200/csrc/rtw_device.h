@@ -202,6 +202,10 @@ struct Scene {
     uint32_t n_spheres_orig, n_quads_orig;
     const uint2* baked_sphere_src;
     const uint2* baked_quad_src;
+    // light list of the light-biased integrators (rtw_scene_desc.lights): 2 float4 per light,
+    // (middle of the light's box, bits(reference of the primitive)) (emitted, 0)
+    const float4* lights;
+    uint32_t n_lights;
 };
 
 // ------------------------------------------------------------------ Vec3::rotated (vec3.rs:161-181)

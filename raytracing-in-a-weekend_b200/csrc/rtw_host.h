@@ -51,6 +51,8 @@ struct HostScene {
     bool has_baked = false;
     uint32_t n_spheres_orig = 0, n_quads_orig = 0;       // spheres / quads beyond these are baked copies
     std::vector<uint2> baked_sphere_src, baked_quad_src;
+    uint32_t n_lights = 0;
+    std::vector<float4> lights;                          // 2 per light: (box middle, bits(ref)) (emitted, 0); Scene::lights
     uint32_t n_walked_instances = 0, n_walked_instances_baked = 0;   // instance leaves walked as levels in top / top_baked
     float background[3];
     // the leaves of every level, for the optional on-device LBVH rebuild (rtw_lbvh.h)

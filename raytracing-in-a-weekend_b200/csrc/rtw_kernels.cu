@@ -119,7 +119,7 @@ mega_kernel(const Scene sc, const RenderParams P, float* __restrict__ sum, Count
             // ---- shade / scatter every lane whose search is over
             if (alive && T.cur == CUR_DONE) {
                 bool finished = true;
-                if (first_hit_integrator(P.integrator) || path.depth_left >= 1u) finished = segment_end(cx, nt, P, path, T);
+                if (first_hit_integrator(P.integrator) || path.depth_left >= 1u) finished = segment_end(cx, nt, P, path, T, &S, &n_rays);
                 if (!finished) {
                     cx.bounce = P.depth - path.depth_left;
                     if (segment_begin(cx, P, path, T, S)) ++n_rays; else finished = true;

@@ -28,6 +28,7 @@ struct RenderParams {
     uint32_t k0, k1;          // Philox key
     uint32_t row_begin, row_count;
     uint32_t sample_begin, sample_count;
+    float light_weight;       // RTW_INT_LIGHT_BIASED: biased_weight
 };
 
 struct Hit {   // objects.rs:16-22
@@ -298,7 +299,54 @@ RTW_HD void generate(const RenderParams& P, uint32_t i, uint32_t j, uint32_t s, 
     p.depth_left = P.depth; p.poison = false;
 }
 
-RTW_HD bool first_hit_integrator(uint32_t ig) { return ig == RTW_INT_NORMAL || ig == RTW_INT_ALBEDO; }
+// integrators that look at one segment only, whatever the depth
+RTW_HD bool first_hit_integrator(uint32_t ig) { return ig == RTW_INT_NORMAL || ig == RTW_INT_ALBEDO || ig == RTW_INT_LIGHT_CAST; }
+RTW_HD bool light_integrator(uint32_t ig) { return ig == RTW_INT_LIGHT_CAST || ig == RTW_INT_LIGHT_BIASED; }
+
+// ------------------------------------------------------------------ Rust2's light-biased estimators
+// Material::material_pdf (Rust2/src/objects/material.rs:17) for the uber-material of Rust/src: its diffuse branch
+// answers like Lambertian (material.rs:44-63: clamp(+-cos, 0, 1) / pi, the sign by the side the incoming ray is on);
+// a mirror (metallicness == 1, Mirror material.rs:93-101) and the dielectric (opacity > 0, MirrorGlass :199-235)
+// answer 0 for every direction but their own reflection / refraction, i.e. for every light.
+RTW_HD float material_pdf(const Hit& h, const Ray& in, V3 to_light) {
+    if (h.opacity > 0.0f || h.metallicness == 1.0f) return 0.0f;
+    float c = dot(unit(to_light), unit(h.normal));
+    if (dot(in.d, h.normal) >= 0.0f) c = -c;
+    c = c < 0.0f ? 0.0f : (c > 1.0f ? 1.0f : c);
+    return c * 0.31830988618379067154f;
+}
+// The light loop of light_biased_ray_cast / light_biased_ray_color (Rust2/src/viewport/ray_color.rs:67-92, 130-152):
+// one ray per light from the hit point towards the middle of the light's box (Ray::new: time 0); the light counts
+// when the scene's closest hit along it is the light itself (`hr.0 == hl`). Returns sum(emitted * pdf / distance^2
+// [* weight]) and, in `count`, the number (cast) or summed weight (biased) of the lights that counted.
+// Needs a traversal stack: runs in the megakernel (and the host emulator), where the lane's own search is over.
+RTW_HD_NOINL V3 light_gather(const TraceCtx& cx0, const RenderParams& P, const Hit& h, const Ray& in, const Stack& S,
+                             bool biased, float& count, uint32_t& rays) {
+    const Scene& sc = *cx0.sc;
+    V3 color = v3(0.f, 0.f, 0.f);
+    for (uint32_t l = 0; l < sc.n_lights; ++l) {
+        const float4 lm = RTW_LDG(&sc.lights[2u * l]), le = RTW_LDG(&sc.lights[2u * l + 1u]);
+        Ray r; r.o = h.point; r.d = unit(v3(lm.x, lm.y, lm.z) - h.point); r.time = 0.0f;
+        TraceCtx cx = cx0;
+        cx.bounce = 0x8000u | (cx0.bounce & 0x7FFFu);          // a volume on the way draws from its own block of the stream
+        const Best b = trace(cx, r, S);
+        ++rays;
+        if (b.ref != f2u(lm.w)) continue;
+        const V3 emitted = v3(le.x, le.y, le.z);
+        const float pdf = material_pdf(h, in, r.d);
+        const float distance2 = b.t * b.t * length2(r.d);
+        if (biased) {
+            const float mx = fmaxf(fmaxf(emitted.x, emitted.y), emitted.z);
+            if (pdf <= 1.0f / (255.0f * mx)) continue;          // ray_color.rs:141-143
+            count += P.light_weight;
+            color = color + emitted * pdf / distance2 * P.light_weight;
+        } else {
+            count += 1.0f;
+            color = color + emitted * pdf / distance2;
+        }
+    }
+    return color;
+}
 
 // A path segment is: segment_begin (depth check, ray_color.rs:14-16; start the search) -> the search
 // (rtw_trace.h, driven by the caller) -> segment_end (miss / Hit / scatter). segment_begin returns
@@ -310,14 +358,15 @@ RTW_HD bool segment_begin(const TraceCtx& cx, const RenderParams& P, const Path&
     return true;
 }
 
-RTW_HD bool segment_end(const TraceCtx& cx, const Noise* nt, const RenderParams& P, Path& p, const Trav& T) {
+RTW_HD bool segment_end(const TraceCtx& cx, const Noise* nt, const RenderParams& P, Path& p, const Trav& T,
+                        const Stack* S = nullptr, uint32_t* shadow_rays = nullptr) {
     const Scene& sc = *cx.sc;
     const uint32_t ig = P.integrator;
     Ray ray; ray.o = T.o; ray.d = T.d; ray.time = p.ray.time;      // back in the world frame
     const Best b = trav_result(sc, T);
     if (b.ref == REF_NONE) {                                        // miss
         V3 bg;
-        if (ig == RTW_INT_BG_COLOR || ig == RTW_INT_ALBEDO) bg = ld3(sc.background);   // ray_color.rs:91
+        if (ig == RTW_INT_BG_COLOR || ig == RTW_INT_ALBEDO || light_integrator(ig)) bg = ld3(sc.background);   // ray_color.rs:91; Rust2 ray_color.rs:107,162
         else if (ig == RTW_INT_GLASS_TEST) bg = v3(0.f, 0.f, 1.f);                     // glass_tests.rs:54
         else bg = sky_gradient(ray.d);
         p.rad = p.rad + p.thr * bg;
@@ -326,6 +375,13 @@ RTW_HD bool segment_end(const TraceCtx& cx, const Noise* nt, const RenderParams&
     RTW_COUNT(cx, hits);
     Hit h;
     eval_hit(cx, nt, b, ray, h);
+    if (ig == RTW_INT_LIGHT_CAST) {                                 // Rust2 ray_color.rs:61-105
+        float count = 0.0f; uint32_t nr = 0u;
+        V3 color = S ? light_gather(cx, P, h, ray, *S, false, count, nr) : v3(0.f, 0.f, 0.f);
+        if (shadow_rays) *shadow_rays += nr;
+        p.rad = (count != 0.0f ? color * h.col_mod / count : v3(0.f, 0.f, 0.f)) + h.emitted;
+        return true;
+    }
     if (first_hit_integrator(ig)) {                                 // viewport.rs:524-554
         if (ig == RTW_INT_NORMAL)
             p.rad = v3(0.5f * (h.normal.x + 1.0f), 0.5f * (h.normal.y + 1.0f), 0.5f * (h.normal.z + 1.0f));
@@ -349,6 +405,19 @@ RTW_HD bool segment_end(const TraceCtx& cx, const Noise* nt, const RenderParams&
             if (!(pdf > 0.0f)) p.poison = true;
         }
     }
+    if (ig == RTW_INT_LIGHT_BIASED) {                               // Rust2 ray_color.rs:124-160, iteratively:
+        // L = emitted + col_mod / count * (L(reflected) + sum_l w * E_l * pdf_l / d_l^2), count = 1 + w * #lights that count
+        float count = 1.0f; uint32_t nr = 0u;
+        const V3 direct = S ? light_gather(cx, P, h, ray, *S, true, count, nr) : v3(0.f, 0.f, 0.f);
+        if (shadow_rays) *shadow_rays += nr;
+        p.rad = p.rad + p.thr * h.emitted;
+        p.thr = p.thr * h.col_mod / count;
+        p.rad = p.rad + p.thr * direct;
+        p.ray.o = h.point; p.ray.d = nd;
+        p.depth_left -= 1u;
+        if (p.depth_left < 1u) { p.rad = p.rad + p.thr * ld3(sc.background); return true; }   // `depth <= 0 => bg_color` (:118-120)
+        return false;
+    }
     p.thr = p.thr * h.col_mod;
     p.ray.o = h.point; p.ray.d = nd;
     p.depth_left -= 1u;
@@ -367,7 +436,7 @@ RTW_HD bool path_step(const Scene& sc, const Noise* nt, const RenderParams& P, P
         else trav_step_other(cx, p.ray.time, T, S);
     }
     ++rays;
-    return segment_end(cx, nt, P, p, T);
+    return segment_end(cx, nt, P, p, T, &S, &rays);
 }
 
 RTW_HD V3 path_result(const Path& p) {

@@ -389,6 +389,7 @@ Scene HostScene::host_view() {
     s.n_noises = (uint32_t)noises.size();
     s.n_spheres_orig = n_spheres_orig; s.n_quads_orig = n_quads_orig;
     s.baked_sphere_src = baked_sphere_src.data(); s.baked_quad_src = baked_quad_src.data();
+    s.lights = lights.data(); s.n_lights = n_lights;
     return s;
 }
 
@@ -489,6 +490,22 @@ int build_host_scene(const rtw_scene_desc* d, HostScene& hs, std::string& err) {
         qbox[i] = quad_box(Q, u, v, tri);
     }
     hs.n_spheres_orig = ns; hs.n_quads_orig = nq;
+    // ---- light list (Rust2/src/viewport/ray_color.rs:68-75,131-137: the ray goes to the middle of l.get_aabb())
+    if (d->n_lights && !d->lights) { err = "null light list with non-zero count"; return RTW_E_INVALID; }
+    for (uint32_t i = 0; i < d->n_lights; ++i) {
+        const rtw_light& l = d->lights[i];
+        const bool quad = l.kind == RTW_LIGHT_QUAD;
+        if (l.kind > RTW_LIGHT_QUAD || l.index >= (quad ? d->n_top_quads : d->n_top_spheres)) {
+            err = "light is not a top-level sphere / quad of the scene"; return RTW_E_INVALID;
+        }
+        const Box& b = quad ? qbox[l.index] : sbox[l.index];
+        const uint32_t ref = quad ? make_ref(KIND_QUAD, l.index | qtri[l.index]) : make_ref(KIND_SPHERE, l.index);
+        const Material& m = hs.materials[quad ? hs.quad_ids[l.index].x : hs.sphere_ids[l.index].x];
+        hs.lights.push_back(make_float4((b.lo[0] + b.hi[0]) * 0.5f, (b.lo[1] + b.hi[1]) * 0.5f, (b.lo[2] + b.hi[2]) * 0.5f, u2f(ref)));
+        hs.lights.push_back(make_float4(m.emitted[0], m.emitted[1], m.emitted[2], 0.f));
+    }
+    hs.n_lights = d->n_lights;
+    if (hs.lights.empty()) { hs.lights.push_back(make_float4(0.f, 0.f, 0.f, u2f(REF_NONE))); hs.lights.push_back(make_float4(0.f, 0.f, 0.f, 0.f)); }
 
     lap("spheres, quads");
     // ---- instances
@@ -824,6 +841,8 @@ int make_render_params(const rtw_camera* cam, const rtw_render_opts* o, RenderPa
         case RTW_INT_NORMAL:     P.mint = 0.0f;   P.maxt = 1000.0f; break;     // viewport.rs:525-526
         case RTW_INT_ALBEDO:     P.mint = 0.001f; P.maxt = 100000.0f; break;
         case RTW_INT_GLASS_TEST: P.mint = 0.001f; P.maxt = 1000.0f; break;     // glass_tests.rs:13-14
+        case RTW_INT_LIGHT_CAST:
+        case RTW_INT_LIGHT_BIASED: P.mint = 0.001f; P.maxt = 1000.0f; break;   // Scene::new(.., 0.001, 1000.0), Rust2 tests.rs:639-644
         default: err = "unknown integrator"; return RTW_E_INVALID;
     }
     if (o->maxt > 0.0f) { P.mint = o->mint; P.maxt = o->maxt; }
@@ -838,6 +857,8 @@ int make_render_params(const rtw_camera* cam, const rtw_render_opts* o, RenderPa
     P.time0 = (float)o->frame / o->fps;           // viewport.rs:279
     P.shutter_speed = o->shutter_speed;
     P.k0 = (uint32_t)o->seed; P.k1 = (uint32_t)(o->seed >> 32);
+    P.light_weight = o->light_weight;
+    if (o->integrator == RTW_INT_LIGHT_BIASED && !(o->light_weight >= 0.0f)) { err = "light_weight must be >= 0"; return RTW_E_INVALID; }
     P.sample_begin = o->sample_count ? o->sample_begin : 0u;
     P.sample_count = o->sample_count ? o->sample_count : total;
     P.row_begin = o->row_count ? o->row_begin : 0u;

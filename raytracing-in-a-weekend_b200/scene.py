@@ -303,6 +303,9 @@ class Scene:
         self.quads: List[Quad] = list(quads)
         self.instances: List[Instance] = list(instances)
         self.background_color = Vec3(0.0, 0.0, 0.0)
+        # the `lights` argument of Rust2's light-biased integrators (Rust2/src/viewport/ray_color.rs:59,115): objects that
+        # are also top-level spheres / quads of this scene (the same Python objects, as the same Arc in Rust2's tests)
+        self.lights = []
         self._backend_cache = {}
 
     @staticmethod
@@ -424,5 +427,16 @@ class Scene:
         d.spheres, d.quads, d.instances = sp, qd, ins_arr
         d.materials, d.textures, d.noises = mt, tx, ns
         d.background[:] = _v(self.background_color).tolist()
-        fs._keep += [sp, qd, ins_arr, mt, tx, ns]
+        lt = (A.rtw_light * max(1, len(self.lights)))()
+        for i, l in enumerate(self.lights):
+            where = [k for k, s in enumerate(self.spheres) if s is l]
+            kind = A.RTW_LIGHT_SPHERE
+            if not where:
+                where, kind = [k for k, q in enumerate(self.quads) if q is l], A.RTW_LIGHT_QUAD
+            if not where:
+                raise ValueError("Scene.lights: every light must be one of the scene's top-level spheres / quads")
+            lt[i].kind, lt[i].index = kind, where[0]
+        d.n_lights = len(self.lights)
+        d.lights = lt
+        fs._keep += [sp, qd, ins_arr, mt, tx, ns, lt]
         return fs

@@ -28,8 +28,8 @@ from . import _abi as A
 from .philox import PhiloxStream
 from .scene import (EMPTY_M, FUZZY3_M, GLASS_M, GLASSR_M, METALLIC_M, SCATTER_M, ImageTexture, Instance,
                     Material, PerlinNoise, Quad, Scene, Sphere, Triangle, Vec3, const_density)
-from .viewport import (Viewport, ray_color_bg_color, ray_color_d, ray_color_glass_test, ray_color_gradient,
-                       ray_color_normal)
+from .viewport import (Viewport, light_biased_ray_cast, light_biased_ray_color, ray_color_bg_color, ray_color_d,
+                       ray_color_glass_test, ray_color_gradient, ray_color_normal)
 
 F = np.float32
 PI = float(F(math.pi))
@@ -562,6 +562,31 @@ def triangle_mesh_test(samples=100, size=400) -> Job:
     ball = _albedo_sphere(Vec3(1.3, -1.5, 3.6), 0.4, (0.8, 0.6, 0.2), METALLIC_M)
     sc = Scene.new([ball], _room_quads(light, [back, tex_tri, half_a, half_b]), [mesh, single, smoke])
     return Job("triangle_mesh", sc, _room_viewport(samples, 20, size), ray_color_bg_color, A.RTW_MODE_RANDOM)
+
+
+def light_biased_test(cast=False, width=400, height=300, samples=100, depth=9, weight=100.0) -> Job:
+    """Rust2/src/tests.rs:409-691 `make_scene` + `light_biased_ray_color_test`: a room of five quads (red, green with
+    a faint emission, blue, an orange MIRROR ceiling, teal floor), a small emissive quad (2, 2, 2) and an emissive
+    sphere (4, 2, 4) at its back; both are `lights`. Camera at the origin looking along +z (Vec3::FORWARD), vfov 90;
+    SAMPLES 100, DEPTH 9 (the ray-cast control uses 10, ignored), BIASED_WEIGHT 100, background black.
+    ConstColorTexture::new(multiplied, emitted) becomes col_mod via the texture and Material::new_emmiting."""
+    def quad(o, u, v, colour, emitted=(0.0, 0.0, 0.0), m=0.0):
+        return Quad.new(Vec3(*o), Vec3(*u), Vec3(*v), Material.new_emmiting(m, 0.0, 1.0, Vec3(*emitted)), Z, _solid(colour))
+    light_quad = quad((-0.10, -0.10, 4.5), (0.2, 0.0, 0.0), (0.0, 0.2, 0.0), (1.0, 1.0, 1.0), (2.0, 2.0, 2.0))
+    light_sphere = Sphere.new_with_texture(Vec3(-0.40, 0.0, 4.5), 0.2, None, Material.new_emmiting(0.0, 0.0, 1.0, Vec3(4.0, 2.0, 4.0)),
+                                           _solid((1.0, 1.0, 1.0)))
+    quads = [quad((-2.0, -2.0, 5.0), (0.0, 0.0, -4.0), (0.0, 4.0, 0.0), (1.0, 0.2, 0.2)),             # red
+             light_quad,
+             quad((-2.0, -2.0, 6.0), (4.0, 0.0, 0.0), (0.0, 4.0, 0.0), (0.2, 1.0, 0.2), (0.0, 0.0, 0.1)),   # green
+             quad((2.0, -2.0, 1.0), (0.0, 0.0, 4.0), (0.0, 4.0, 0.0), (0.2, 0.2, 1.0)),                 # blue
+             quad((-2.0, 2.0, 1.0), (4.0, 0.0, 0.0), (0.0, 0.0, 4.0), (1.0, 0.5, 0.0), m=1.0),          # orange, MIRROR
+             quad((-2.0, -2.0, 5.0), (4.0, 0.0, 0.0), (0.0, 0.0, -4.0), (0.2, 0.8, 0.8))]               # teal
+    sc = Scene.new([light_sphere], quads, [])
+    sc.lights = [light_quad, light_sphere]
+    vp = Viewport.new_from_res(width, height, samples, depth, 2.0, 90.0, Vec3(0.0, 0.0, 0.0), Vec3(0.0, 0.0, 1.0), Vec3(0.0, 1.0, 0.0))
+    vp.light_weight = weight
+    return Job("light_cast" if cast else "light_biased", sc, vp, light_biased_ray_cast if cast else light_biased_ray_color,
+               A.RTW_MODE_RANDOM)
 
 
 CONFIGS: Dict[str, Callable[..., Job]] = {"C1": config_c1, "C2": config_c2, "C3": config_c3, "C4": config_c4,

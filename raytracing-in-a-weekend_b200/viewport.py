@@ -30,7 +30,8 @@ class Integrator(int):
     """An RTW_INT_* code that prints like the reference function it stands for."""
     _names = {A.RTW_INT_GRADIENT: "ray_color_gradient", A.RTW_INT_D: "ray_color_d",
               A.RTW_INT_BG_COLOR: "ray_color_bg_color", A.RTW_INT_NORMAL: "ray_color_normal",
-              A.RTW_INT_ALBEDO: "ray_color_albedo", A.RTW_INT_GLASS_TEST: "ray_color_glass_test"}
+              A.RTW_INT_ALBEDO: "ray_color_albedo", A.RTW_INT_GLASS_TEST: "ray_color_glass_test",
+              A.RTW_INT_LIGHT_CAST: "light_biased_ray_cast", A.RTW_INT_LIGHT_BIASED: "light_biased_ray_color"}
 
     def __repr__(self):
         return self._names.get(int(self), f"Integrator({int(self)})")
@@ -42,6 +43,8 @@ ray_color_bg_color = Integrator(A.RTW_INT_BG_COLOR)     # viewport/ray_color.rs:
 ray_color_normal = Integrator(A.RTW_INT_NORMAL)         # viewport.rs:524-554
 ray_color_albedo = Integrator(A.RTW_INT_ALBEDO)
 ray_color_glass_test = Integrator(A.RTW_INT_GLASS_TEST)  # viewport/glass_tests.rs:8-55
+light_biased_ray_cast = Integrator(A.RTW_INT_LIGHT_CAST)      # Rust2/src/viewport/ray_color.rs:55-109 (lights = Scene.lights)
+light_biased_ray_color = Integrator(A.RTW_INT_LIGHT_BIASED)   # Rust2/src/viewport/ray_color.rs:111-164 (weight = Viewport.light_weight)
 
 _default_backend = None
 
@@ -87,6 +90,7 @@ class Viewport:
         self.start_frame = 0
         self.seed = 1                # the reference is unseeded; SURVEY §8d "Render RNG"
         self.flags = 0               # RTW_FLAG_* (STRICT_FP for parity runs, WAVEFRONT)
+        self.light_weight = 1.0      # `biased_weight` of light_biased_ray_color (Rust2 ray_color.rs:116)
 
     @staticmethod
     def new(width, aspect_ratio, samples, depth, gamma, vfov=None, origin=None, direction=None,
@@ -116,6 +120,7 @@ class Viewport:
         o.mint, o.maxt = 0.0, 0.0
         o.sample_begin = o.sample_count = o.row_begin = o.row_count = 0
         o.output, o.flags = A.RTW_OUT_RESOLVED, int(self.flags)
+        o.light_weight = float(self.light_weight)
         return o
 
     # ---- the reference's render entry points

@@ -31,6 +31,10 @@ pub struct rtw_instance {
     pub first_sphere: u32, pub n_spheres: u32, pub first_quad: u32, pub n_quads: u32,
     pub translation: [f32; 3], pub rotation: [f32; 3], pub density_kind: u32, pub density: f32,
 }
+#[repr(C)] #[derive(Clone, Copy)]
+pub struct rtw_light { pub kind: u32, pub index: u32 }
+pub const RTW_LIGHT_SPHERE: u32 = 0;
+pub const RTW_LIGHT_QUAD: u32 = 1;
 #[repr(C)]
 pub struct rtw_scene_desc {
     pub abi_version: u32,
@@ -38,7 +42,7 @@ pub struct rtw_scene_desc {
     pub n_materials: u32, pub n_textures: u32, pub n_noises: u32,
     pub spheres: *const rtw_sphere, pub quads: *const rtw_quad, pub instances: *const rtw_instance,
     pub materials: *const rtw_material, pub textures: *const rtw_texture, pub noises: *const rtw_noise,
-    pub background: [f32; 3],
+    pub background: [f32; 3], pub n_lights: u32, pub lights: *const rtw_light,
 }
 #[repr(C)] #[derive(Clone, Copy, Default)]
 pub struct rtw_camera {
@@ -50,7 +54,7 @@ pub struct rtw_render_opts {
     pub samples: u32, pub depth: u32, pub gamma: f32, pub integrator: u32, pub mode: u32,
     pub shutter_speed: f32, pub fps: f32, pub frame: u32, pub seed: u64, pub mint: f32, pub maxt: f32,
     pub sample_begin: u32, pub sample_count: u32, pub row_begin: u32, pub row_count: u32,
-    pub output: u32, pub flags: u32,
+    pub output: u32, pub flags: u32, pub light_weight: f32,
 }
 pub const RTW_OUT_RESOLVED: u32 = 0;
 pub const RTW_OUT_SUM: u32 = 1;

@@ -18,7 +18,7 @@ use super::ffi::*;
 
 /// The closures the reference passes as `ray_color`, closed into an enum (a GPU cannot run a Rust closure).
 #[derive(Clone, Copy)]
-pub enum Integrator { Gradient = 0, D = 1, BgColor = 2, Normal = 3, Albedo = 4, GlassTest = 5 }
+pub enum Integrator { Gradient = 0, D = 1, BgColor = 2, Normal = 3, Albedo = 4, GlassTest = 5, LightCast = 6, LightBiased = 7 }
 #[derive(Clone, Copy)]
 pub enum Mode { Random = 0, Stratified = 1, NoRand = 2 }
 
@@ -100,7 +100,7 @@ impl FlatScene {
             spheres: self.spheres.as_ptr(), quads: self.quads.as_ptr(), instances: self.instances.as_ptr(),
             materials: self.materials.as_ptr(), textures: self.textures.as_ptr(),
             noises: if self.noises.is_empty() { std::ptr::null() } else { &*self.noises[0] as *const rtw_noise },
-            background: self.background }
+            background: self.background, n_lights: 0, lights: std::ptr::null() }
     }
 }
 
