@@ -215,7 +215,7 @@ def run_b200(args):
     import rtw_b200
     from rtw_b200 import _abi as A
     from rtw_b200.backend import CudaBackend
-    from rtw_b200.sharding import row_bands, sample_range
+    from rtw_b200.sharding import band_rows_for_rank, sample_range
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -246,20 +246,21 @@ def run_b200(args):
     buf = torch.empty((H, W, 3), dtype=torch.float32, device=dev)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)      # > 126 MB L2
     stream = torch.cuda.current_stream().cuda_stream
-    bands = row_bands(H, world, rank, args.band) if part == "tiles" else []
+    # tiles: this rank's bands as one render of interleaved rows into a compact buffer, then put in place in the frame
+    my_rows = band_rows_for_rank(H, world, rank, args.band) if part == "tiles" else np.zeros(0, dtype=np.int64)
+    row_idx = torch.from_numpy(my_rows.astype(np.int64)).to(dev)
+    cbuf = torch.empty((max(1, my_rows.size), W, 3), dtype=torch.float32, device=dev)
     frame_no = [0]
-    if part == "tiles" and world == 1:
-        bands = [(0, H)]            # one device: the whole frame is its one band
 
-    def collect_stats(collect, acc=None):
+    def tile_opts():
+        ob = vp.opts(job.ray_color, job.mode)
+        ob.row_begin, ob.row_count = rank * args.band, int(my_rows.size)
+        ob.row_band, ob.row_stride = args.band, world * args.band
+        return ob
+
+    def collect_stats(collect):
         st = h.stats()                                  # syncs on the last render's events
-        row = [st.kernel_ms, st.rays, st.paths, st.nan_paths, st.gpu_launches, st.iterations, st.extend_ms, st.shade_ms]
-        if acc is None:
-            collect.append(tuple(row))
-        else:                                           # several renders per step (bands): sums; per-launch means weighted by iterations
-            for k in (0, 1, 2, 3, 4, 5):
-                acc[k] += row[k]
-            acc[6] += row[6] * row[5]; acc[7] += row[7] * row[5]
+        collect.append((st.kernel_ms, st.rays, st.paths, st.nan_paths, st.gpu_launches, st.iterations, st.extend_ms, st.shade_ms))
 
     def step(collect=None):
         flush.zero_()                                   # L2 flush between steps
@@ -278,21 +279,15 @@ def run_b200(args):
             # row bands dealt round-robin: every rank renders and RESOLVES its own bands in place in a
             # zeroed frame; the frames are disjoint, so the gather to rank 0 is a reduce(sum) of them with zeros
             # (x + 0 = x: the gather changes no value). No sample reduction across GPUs anywhere.
-            acc = [0.0] * 8
             if world > 1:
                 buf.zero_()
-            ob = vp.opts(job.ray_color, job.mode)
-            for r0, rc in bands:
-                ob.row_begin, ob.row_count = r0, rc
-                h.render_device(cam, ob, buf.data_ptr() + r0 * W * 3 * 4, stream)
-                if collect is not None:
-                    collect_stats(collect, acc)
+            if my_rows.size:
+                h.render_device(cam, tile_opts(), cbuf.data_ptr(), stream)
+                buf[row_idx] = cbuf[:my_rows.size]
             if world > 1:
                 dist.reduce(buf, dst=0, op=dist.ReduceOp.SUM)
-            if collect is not None and bands:
-                if acc[5] > 0:
-                    acc[6] /= acc[5]; acc[7] /= acc[5]
-                collect.append(tuple(acc))
+            if collect is not None and my_rows.size:
+                collect_stats(collect)
         else:
             # frames (render_multi viewport.rs:249-269): frame k of the animation on rank k mod n, every
             # rank renders ONE whole frame per step; nothing is exchanged (rank 0's frame is the one that is read back)
@@ -350,13 +345,14 @@ def run_b200(args):
                 of = vp.opts(job.ray_color, job.mode)
                 of.frame = vp.frame + rank
                 A.check(lib.rtw_render(hd, C.byref(cam), C.byref(of), C.c_void_p(host_out.data_ptr())))
-            elif part == "tiles" and world > 1:
-                buf.zero_()
-                ob = vp.opts(job.ray_color, job.mode)
-                for r0, rc in bands:
-                    ob.row_begin, ob.row_count = r0, rc
-                    A.check(lib.rtw_render_device(hd, C.byref(cam), C.byref(ob), C.c_void_p(buf.data_ptr() + r0 * W * 3 * 4), C.c_void_p(stream)))
-                dist.reduce(buf, dst=0, op=dist.ReduceOp.SUM)
+            elif part == "tiles":
+                if world > 1:
+                    buf.zero_()
+                if my_rows.size:
+                    A.check(lib.rtw_render_device(hd, C.byref(cam), C.byref(tile_opts()), C.c_void_p(cbuf.data_ptr()), C.c_void_p(stream)))
+                    buf[row_idx] = cbuf[:my_rows.size]
+                if world > 1:
+                    dist.reduce(buf, dst=0, op=dist.ReduceOp.SUM)
                 if rank == 0:
                     host_out.copy_(buf, non_blocking=True)
                 torch.cuda.synchronize()
@@ -479,7 +475,7 @@ def run_b200(args):
         paths_frame = W * H * spp * (world if part == "frames" else 1)     # paths per step
         val = paths_frame * args.steps / (elapsed_ms * 1e-3) / 1e6
         part_text = {"samples": f"sample range x{world} + NCCL reduce(sum) to rank 0",
-                     "tiles": f"row bands of {args.band} rows dealt round-robin over {world} GPU(s), resolved in place, gathered to rank 0 (no reduction)",
+                     "tiles": f"row bands of {args.band} rows dealt round-robin over {world} GPU(s), one interleaved-row render per GPU, resolved in place, gathered to rank 0 (no reduction)",
                      "frames": f"one animation frame per GPU per step (frame k on rank k mod {world}), no exchange"}[part]
         line = {"metric": METRIC, "value": val, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
                 "ms_per_step": elapsed_ms / args.steps, "higher_is_better": True, "scaling": "weak" if part == "frames" else "strong", "vs_baseline": None,

@@ -207,6 +207,11 @@ typedef struct rtw_render_opts {
     uint32_t output;         /* RTW_OUT_* */
     uint32_t flags;
     float    light_weight;   /* RTW_INT_LIGHT_BIASED: `biased_weight` of light_biased_ray_color (ray_color.rs:116) */
+    /* Interleaved row bands in ONE render (tiles across devices): with row_stride != 0 the call renders
+     * row_count rows taken in bands of row_band rows every row_stride rows from row_begin on - output row jr is image
+     * row row_begin + (jr / row_band) * row_stride + jr % row_band - into a compact row_count*width*3 buffer. Device g
+     * of n takes row_begin = g*band, row_band = band, row_stride = n*band. 0 / 0 = one contiguous block of rows. */
+    uint32_t row_band, row_stride;
 } rtw_render_opts;
 
 typedef struct rtw_stats {
@@ -330,8 +335,9 @@ int rtw_bilateral_filter(const uint8_t* rgb8, uint32_t width, uint32_t height, u
  *                      buffer (the Philox counter carries the GLOBAL sample index, so the image does not
  *                      depend on n beyond f32 summation order); one kernel on devices[0] reads the n buffers
  *                      over NVLink peer memory, adds them in device order and resolves (/spp, powf(1/gamma)).
- *   RTW_SPLIT_TILES    bands of `band_rows` rows (0 = 8) dealt round-robin; each device resolves its bands and
- *                      copies them straight into their place in out_rgb. No reduction across devices: every
+ *   RTW_SPLIT_TILES    bands of `band_rows` rows (0 = 8) dealt round-robin; each device renders its bands as ONE
+ *                      render of interleaved rows (rtw_render_opts.row_stride), resolves them and copies them
+ *                      straight into their place in out_rgb. No reduction across devices: every
  *                      pixel is summed on one device (equal to a one-device render up to the order of
  *                      that device's own f32 adds).
  *   RTW_SPLIT_FRAMES   (rtw_render_frames_multi) render_multi's frame k -> devices[k mod n]; no exchange.

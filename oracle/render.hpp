@@ -251,6 +251,7 @@ inline RenderResult render(const Scene& scene, const rtw_camera& cam, const rtw_
             uint32_t jr = next_row.fetch_add(1);
             if (jr >= rn) break;
             uint32_t j = r0 + jr;
+            if (o.row_stride != 0u && o.row_band != 0u) { uint32_t b = jr / o.row_band; j = r0 + b * o.row_stride + (jr - b * o.row_band); }   // interleaved bands (rtw_render_opts)
             for (uint32_t i = 0; i < cam.width; ++i) {
                 Vec3 color(0.f, 0.f, 0.f);
                 bool tie = false;

@@ -87,7 +87,7 @@ class rtw_render_opts(C.Structure):
                 ("shutter_speed", f32), ("fps", f32), ("frame", u32), ("seed", u64),
                 ("mint", f32), ("maxt", f32),
                 ("sample_begin", u32), ("sample_count", u32), ("row_begin", u32), ("row_count", u32),
-                ("output", u32), ("flags", u32), ("light_weight", f32)]
+                ("output", u32), ("flags", u32), ("light_weight", f32), ("row_band", u32), ("row_stride", u32)]
 
 
 class rtw_stats(C.Structure):

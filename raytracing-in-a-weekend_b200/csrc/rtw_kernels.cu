@@ -95,7 +95,7 @@ mega_kernel(const Scene sc, const RenderParams P, float* __restrict__ sum, Count
                     pix = n & 31u;
                     const uint32_t i = tx * 8u + (pix & 7u), jr = ty * 4u + (pix >> 3);
                     if (i < W && jr < P.row_count) {
-                        generate(P, i, P.row_begin + jr, s0 + (n >> 5), path);
+                        generate(P, i, image_row(P, jr), s0 + (n >> 5), path);
                         alive = true;
                         cx = path_ctx(sc, P, path, wp);
                         if (!segment_begin(cx, P, path, T, S)) T.cur = CUR_DONE;   // depth 0: nothing to trace
@@ -451,7 +451,7 @@ wf_shade_kernel(const Scene sc, const RenderParams P, const WfPool pool, WfCount
             // that is or becomes NaN (N8) adds NaN once, when it ends, as the reference's sum would be.
             V3 c = path.rad;
             if (!finite3(c)) path.poison = true;
-            float* px = sum + ((size_t)path.pixel - (size_t)P.row_begin * W) * 3u;
+            float* px = sum + (size_t)output_pixel(P, path.pixel) * 3u;
             if (finished && path.poison) {
                 atomicAdd(&ctr->nan_paths, 1ull);
                 const float qn = u2f(0x7FC00000u);
@@ -507,7 +507,7 @@ wf_shade_kernel(const Scene sc, const RenderParams P, const WfPool pool, WfCount
             const uint32_t tx = tile % L.tiles_x, ty = tile / L.tiles_x;
             const uint32_t i = tx * 8u + (pix & 7u), jr = ty * 4u + (pix >> 3);
             if (i < W && jr < P.row_count) {                          // edge tiles are padded; such an index is dropped
-                generate(P, i, P.row_begin + jr, s, path);
+                generate(P, i, image_row(P, jr), s, path);
                 alive = true;
                 fresh = true;
             }

@@ -258,30 +258,30 @@ int rtw_render_multi(rtw_scene_multi* ms, const rtw_camera* cam, const rtw_rende
         const uint32_t n_bands = (rows + band - 1u) / band;
         rc = for_each_share(ms, [&](int k) {
             Share& sh = ms->shares[k];
-            uint32_t mine = 0, widest = 0;
-            for (uint32_t b = (uint32_t)k; b < n_bands; b += (uint32_t)n) { ++mine; widest = std::max(widest, std::min(band, rows - b * band)); }
+            // this share's bands k, k + n, k + 2n, ... as ONE render of interleaved rows (rtw_render_opts::row_stride):
+            // a render per band would pay the pipeline's ramp and drain once per band
+            uint32_t mine = 0, my_rows = 0;
+            for (uint32_t b = (uint32_t)k; b < n_bands; b += (uint32_t)n) { ++mine; my_rows += std::min(band, rows - b * band); }
             if (mine == 0u) return (int)RTW_OK;
-            // one landing buffer: the copy of band i to the host and the render of band i+1 are ordered by the stream
-            int r = ensure_buf(sh, (size_t)widest * W * 3u);
+            int r = ensure_buf(sh, (size_t)my_rows * W * 3u);
             if (r) return r;
-            for (uint32_t b = (uint32_t)k; b < n_bands; b += (uint32_t)n) {
-                const uint32_t r0 = b * band, rc_ = std::min(band, rows - r0);
-                float* d = sh.d_buf;
-                rtw_render_opts o = *opts;
-                o.row_begin = row0 + r0; o.row_count = rc_;
-                if ((r = rtw_render_device(sh.scene, cam, &o, d, sh.stream))) return r;
-                rtw_stats st; std::memset(&st, 0, sizeof st);
-                cudaError_t e = cudaMemcpyAsync(out_rgb + (size_t)r0 * W * 3u, d, (size_t)rc_ * W * 3u * sizeof(float),
-                                                cudaMemcpyDeviceToHost, sh.stream);
-                if (e != cudaSuccess) { sh.err = cudaGetErrorString(e); return cuda_rc(e); }
-                rtw_get_stats(sh.scene, &st);     // waits for this band's render (its events), not for the copy
-                sh.stats.paths += st.paths; sh.stats.rays += st.rays; sh.stats.nan_paths += st.nan_paths;
-                sh.stats.gpu_launches += st.gpu_launches; sh.stats.kernel_ms += st.kernel_ms; sh.stats.total_ms += st.total_ms;
-                sh.stats.nodes += st.nodes; sh.stats.sphere_tests += st.sphere_tests; sh.stats.quad_tests += st.quad_tests;
-                sh.stats.instance_tests += st.instance_tests; sh.stats.hits += st.hits; sh.stats.iterations += st.iterations;
-            }
-            cudaError_t e = cudaStreamSynchronize(sh.stream);
+            rtw_render_opts o = *opts;
+            o.row_begin = row0 + (uint32_t)k * band; o.row_count = my_rows;
+            o.row_band = band; o.row_stride = (uint32_t)n * band;
+            if ((r = rtw_render_device(sh.scene, cam, &o, sh.d_buf, sh.stream))) return r;
+            // bands back to their places in the host image: one strided copy for the full bands, one for a short last band
+            const size_t band_bytes = (size_t)band * W * 3u * sizeof(float);
+            const uint32_t last_rows = my_rows - (mine - 1u) * band;          // rows of this share's last band (<= band)
+            const uint32_t full = last_rows == band ? mine : mine - 1u;
+            float* dst = out_rgb + (size_t)k * band * W * 3u;
+            cudaError_t e = cudaSuccess;
+            if (full) e = cudaMemcpy2DAsync(dst, (size_t)n * band_bytes, sh.d_buf, band_bytes, band_bytes, full, cudaMemcpyDeviceToHost, sh.stream);
+            if (e == cudaSuccess && full < mine)
+                e = cudaMemcpyAsync(dst + (size_t)full * n * band * W * 3u, sh.d_buf + (size_t)full * band * W * 3u,
+                                    (size_t)last_rows * W * 3u * sizeof(float), cudaMemcpyDeviceToHost, sh.stream);
+            if (e == cudaSuccess) e = cudaStreamSynchronize(sh.stream);
             if (e != cudaSuccess) { sh.err = cudaGetErrorString(e); return cuda_rc(e); }
+            rtw_get_stats(sh.scene, &sh.stats);
             return (int)RTW_OK;
         });
         if (rc) return rc;

@@ -29,7 +29,20 @@ struct RenderParams {
     uint32_t row_begin, row_count;
     uint32_t sample_begin, sample_count;
     float light_weight;       // RTW_INT_LIGHT_BIASED: biased_weight
+    uint32_t row_band, row_stride;   // interleaved row bands (rtw_render_opts); 0 / 0 = contiguous rows
 };
+// output (compact) row -> image row, and image pixel index -> position in the output buffer
+RTW_HD uint32_t image_row(const RenderParams& P, uint32_t jr) {
+    if (P.row_stride == 0u) return P.row_begin + jr;
+    const uint32_t b = jr / P.row_band;
+    return P.row_begin + b * P.row_stride + (jr - b * P.row_band);
+}
+RTW_HD uint32_t output_pixel(const RenderParams& P, uint32_t pixel) {
+    const uint32_t W = P.cam.width;
+    if (P.row_stride == 0u) return pixel - P.row_begin * W;
+    const uint32_t j = pixel / W, rel = j - P.row_begin, b = rel / P.row_stride;
+    return (b * P.row_band + (rel - b * P.row_stride)) * W + (pixel - j * W);
+}
 
 struct Hit {   // objects.rs:16-22
     float t;

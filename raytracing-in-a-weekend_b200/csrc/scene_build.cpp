@@ -864,6 +864,13 @@ int make_render_params(const rtw_camera* cam, const rtw_render_opts* o, RenderPa
     P.row_begin = o->row_count ? o->row_begin : 0u;
     P.row_count = o->row_count ? o->row_count : cam->height;
     if ((uint64_t)P.sample_begin + P.sample_count > total) { err = "sample range exceeds the sample count"; return RTW_E_INVALID; }
+    P.row_band = 0u; P.row_stride = 0u;
+    if (o->row_stride != 0u) {        // interleaved bands: the last output row must still be an image row
+        if (o->row_count == 0u || o->row_band == 0u || o->row_stride < o->row_band) { err = "row_stride needs row_count > 0 and 0 < row_band <= row_stride"; return RTW_E_INVALID; }
+        P.row_band = o->row_band; P.row_stride = o->row_stride;
+        const uint32_t last = P.row_count - 1u, b = last / P.row_band;
+        if ((uint64_t)P.row_begin + (uint64_t)b * P.row_stride + (last - b * P.row_band) >= cam->height) { err = "row bands exceed the image"; return RTW_E_INVALID; }
+    } else
     if ((uint64_t)P.row_begin + P.row_count > cam->height) { err = "row range exceeds the image"; return RTW_E_INVALID; }
     if (o->output != RTW_OUT_RESOLVED && o->output != RTW_OUT_SUM) { err = "unknown output kind"; return RTW_E_INVALID; }
     return RTW_OK;

@@ -109,10 +109,18 @@ def render_samples_sharded(viewport, ray_color, scene, mode: int = A.RTW_MODE_RA
         return np.power(img, np.float32(1.0) / np.float32(viewport.gamma)).astype(np.float32)
 
 
+def band_rows_for_rank(height: int, world: int, rank: int, band: int = 8) -> np.ndarray:
+    """Image rows of `rank`'s bands, in the order an interleaved render returns them (rtw_render_opts.row_stride)."""
+    rows = [np.arange(r0, r0 + rn) for r0, rn in row_bands(height, world, rank, band)]
+    return np.concatenate(rows) if rows else np.zeros(0, dtype=np.int64)
+
+
 def render_tiles_sharded(viewport, ray_color, scene, mode: int = A.RTW_MODE_RANDOM, backend=None, group=None,
                          band: int = 8) -> Optional[np.ndarray]:
-    """Row-band split; every rank renders and resolves its own bands, rank 0 gathers. Bit-identical
-    to the single-GPU image."""
+    """Row-band split: rank r owns bands r, r + n, r + 2n, ... and renders them as ONE render of interleaved rows
+    (rtw_render_opts.row_band / row_stride; a render per band would pay the pipeline's ramp and drain per band),
+    resolves them and puts them in place; rank 0 gathers. No reduction across ranks: every pixel is summed on one
+    GPU (bit-identical to one device on the deterministic CPU test backends)."""
     import torch
     from .viewport import get_default_backend
     dist = _dist()
@@ -123,14 +131,18 @@ def render_tiles_sharded(viewport, ray_color, scene, mode: int = A.RTW_MODE_RAND
     on_gpu = getattr(be, "name", "") == "cuda"
     dev = torch.device("cuda", torch.cuda.current_device()) if on_gpu else torch.device("cpu")
     img = torch.zeros((cam.height, cam.width, 3), dtype=torch.float32, device=dev)
-    for r0, rn in row_bands(cam.height, world, rank, band):
+    rows = band_rows_for_rank(cam.height, world, rank, band)
+    if rows.size:
         o = viewport.opts(ray_color, mode)
-        o.row_begin, o.row_count = r0, rn
+        o.row_begin, o.row_count = rank * band, int(rows.size)
+        o.row_band, o.row_stride = band, world * band
+        idx = torch.from_numpy(rows.astype(np.int64)).to(dev)
         if on_gpu:
-            view = img[r0:r0 + rn]
-            h.render_device(cam, o, view.data_ptr(), torch.cuda.current_stream().cuda_stream)
+            part = torch.empty((rows.size, cam.width, 3), dtype=torch.float32, device=dev)
+            h.render_device(cam, o, part.data_ptr(), torch.cuda.current_stream().cuda_stream)
         else:
-            img[r0:r0 + rn] = torch.from_numpy(np.ascontiguousarray(h.render(cam, o)))
+            part = torch.from_numpy(np.ascontiguousarray(h.render(cam, o)))
+        img[idx] = part
     if world > 1:
         # bands are disjoint and every other rank holds zeros there, so a sum is a gather; NaN
         # pixels survive because NaN + 0 = NaN.

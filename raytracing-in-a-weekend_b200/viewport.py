@@ -121,6 +121,7 @@ class Viewport:
         o.sample_begin = o.sample_count = o.row_begin = o.row_count = 0
         o.output, o.flags = A.RTW_OUT_RESOLVED, int(self.flags)
         o.light_weight = float(self.light_weight)
+        o.row_band = o.row_stride = 0
         return o
 
     # ---- the reference's render entry points

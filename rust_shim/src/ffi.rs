@@ -54,7 +54,7 @@ pub struct rtw_render_opts {
     pub samples: u32, pub depth: u32, pub gamma: f32, pub integrator: u32, pub mode: u32,
     pub shutter_speed: f32, pub fps: f32, pub frame: u32, pub seed: u64, pub mint: f32, pub maxt: f32,
     pub sample_begin: u32, pub sample_count: u32, pub row_begin: u32, pub row_count: u32,
-    pub output: u32, pub flags: u32, pub light_weight: f32,
+    pub output: u32, pub flags: u32, pub light_weight: f32, pub row_band: u32, pub row_stride: u32,
 }
 pub const RTW_OUT_RESOLVED: u32 = 0;
 pub const RTW_OUT_SUM: u32 = 1;

@@ -94,7 +94,7 @@ extern "C" int emu_render_ex(const rtw_scene_desc* d, const rtw_camera* cam, con
             V3 acc = v3(0, 0, 0);
             for (uint32_t s = P.sample_begin; s < P.sample_begin + P.sample_count; ++s) {
                 Path p;
-                generate(P, i, P.row_begin + jr, s, p);
+                generate(P, i, image_row(P, jr), s, p);
                 rays32 = 0;
                 Work w{0u, 0u, 0u, 0u, 0u};
                 while (!path_step(sc, sc.noises, P, p, rays32, S, &w)) {}

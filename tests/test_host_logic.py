@@ -247,3 +247,33 @@ def test_non_rigid_euler_maps_are_not_baked(oracle):
         assert emu_b.scene(sc).info().n_baked_instances == baked, rot
         ok = ~tie
         assert np.allclose(got[ok], ref[ok], rtol=1e-5, atol=1e-6)
+
+
+def test_interleaved_row_bands_are_those_rows_of_the_frame(oracle, emu):
+    """rtw_render_opts.row_band / row_stride: one render of bands taken every row_stride rows (what a device of a
+    tile split renders) returns exactly those rows of the whole frame, on the oracle and the kernels'
+    headers; badly formed band descriptions are refused by the host logic both backends share."""
+    job = _small(scenes.config_c4(smoke=True), 40, 37, 2)
+    vp = job.viewport
+    for be in (oracle, emu):
+        h, cam = be.scene(job.scene), vp.camera(be)
+        whole = h.render(cam, vp.opts(job.ray_color, job.mode))
+        for band, world in ((4, 3), (5, 2), (8, 4)):
+            got = np.zeros_like(whole)
+            seen = np.zeros(cam.height, dtype=int)
+            for rank in range(world):
+                rows = np.concatenate([np.arange(r0, min(r0 + band, cam.height)) for r0 in range(rank * band, cam.height, world * band)] or [np.zeros(0, int)])
+                if not rows.size:
+                    continue
+                o = vp.opts(job.ray_color, job.mode)
+                o.row_begin, o.row_count, o.row_band, o.row_stride = rank * band, rows.size, band, world * band
+                part = h.render(cam, o)
+                assert part.shape == (rows.size, cam.width, 3)
+                got[rows] = part
+                seen[rows] += 1
+            assert np.all(seen == 1)
+            assert np.array_equal(got, whole, equal_nan=True)
+    o = vp.opts(job.ray_color, job.mode)
+    o.row_begin, o.row_count, o.row_band, o.row_stride = 0, 20, 4, 12          # the fifth band would start at row 48
+    with pytest.raises(Exception):
+        emu.scene(job.scene).render(vp.camera(emu), o)
