@@ -56,6 +56,7 @@ def parse_args():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--config", default="C5", help="C1..C5 (C5 is the headline; others for exploration)")
     ap.add_argument("--spp", type=int, default=0, help="override samples per pixel (0 = the config's own)")
+    ap.add_argument("--depth", type=int, default=0, help="override the path depth (0 = the config's own; exploration only)")
     ap.add_argument("--e2e-steps", type=int, default=0, help="timed e2e steps (0 = same as --steps)")
     ap.add_argument("--cpu-seconds", type=float, default=15.0, help="target CPU time of the cpu_baseline sample")
     ap.add_argument("--flags", type=int, default=0)
@@ -126,6 +127,8 @@ def make_job(args):
     kw = {}
     if args.spp:
         kw["samples"] = args.spp
+    if args.depth:
+        kw["depth"] = args.depth
     job = scenes.CONFIGS[args.config](**kw)
     job.viewport.flags = args.flags
     return job
