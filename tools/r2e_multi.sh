@@ -7,7 +7,7 @@ timeout 600 python -m pytest tests/test_multi_device.py -m gpu -q > $OUT/${TAG}_
 T() { local n=$1; shift; if [ "$n" = 1 ]; then timeout 600 python bench.py --gpus 1 "$@"; else timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node $n --master-addr 127.0.0.1 --master-port $((29500 + n)) bench.py --gpus $n "$@"; fi; }
 line() { python tools/bench_line.py; }
 # --- A: sample ranges + NCCL reduce (C5 headline), torchrun
-for n in 1 2 4 $N; do
+for n in 1 $N; do
   T $n --steps 3 --warmup 3 --cpu-seconds 2 > $OUT/${TAG}_C5_samples_n$n.json 2> $OUT/${TAG}_C5_samples_n$n.err; printf "C5 samples torchrun n=$n: "; line < $OUT/${TAG}_C5_samples_n$n.json
 done
 # --- B: tiles (C4 as BASELINE.json names it), torchrun, N = 1 and N
