@@ -23,7 +23,7 @@ def build_emu() -> str:
     srcs = [os.path.join(EMU_DIR, "emu.cpp"), os.path.join(ROOT, "include", "rtw.h")]
     srcs += [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".h", ".cpp"))]
     if not os.path.exists(path) or any(os.path.getmtime(s) > os.path.getmtime(path) for s in srcs):
-        subprocess.check_call(["g++", "-std=c++17", "-O2", "-ffp-contract=off", "-fno-fast-math", "-fPIC", "-shared", "-DRTW_COUNT_WORK=1",
+        subprocess.check_call(["g++", "-std=c++17", "-O2", "-pthread", "-ffp-contract=off", "-fno-fast-math", "-fPIC", "-shared", "-DRTW_COUNT_WORK=1",
                                "-I/usr/local/cuda/include", "-o", path, os.path.join(EMU_DIR, "emu.cpp"),
                                os.path.join(CSRC, "scene_build.cpp")])
     return path
