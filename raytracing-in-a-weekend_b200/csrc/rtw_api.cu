@@ -468,13 +468,14 @@ int pool_alloc(rtw_scene* s, T** p, size_t n) {
 
 // Pool of path slots for one render of `n_paths` paths. The bigger the pool the fewer, longer
 // launches (less tail and launch overhead) but the longer the frame drains at the end: 1/128 of the
-// frame's paths, between 1 Mi and 6 Mi slots and never more than there are paths (C5: 2 Mi slots are
+// frame's paths, between 1 Mi and 12 Mi slots (6 Mi until round 2: 12 Mi is +1.7 % on the 6.4 G paths of C5, profiles/r2f_sweep.txt)
+// and never more than there are paths (C5: 2 Mi slots are
 // best at 400 spp, 6 Mi from 2000 spp on, +6 %; profiles/r1j_sweep_pool.txt; C1's 9 M paths are
 // launch-bound below 1 Mi). RTW_WF_POOL overrides. Arrays only ever grow.
 int ensure_pool(rtw_scene* s, unsigned long long n_paths) {
     unsigned long long want = env_u32("RTW_WF_POOL", 0u);
     if (want == 0ull) {
-        want = std::min<unsigned long long>(6ull << 20, std::max<unsigned long long>(1ull << 20, n_paths / 128ull));
+        want = std::min<unsigned long long>(12ull << 20, std::max<unsigned long long>(1ull << 20, n_paths / 128ull));
         want = std::min(want, std::max<unsigned long long>(16384ull, n_paths));      // never more slots than paths
     }
     const uint32_t cap = (uint32_t)((std::max<unsigned long long>(want, 4096ull) + 255ull) & ~255ull);   // whole shade blocks

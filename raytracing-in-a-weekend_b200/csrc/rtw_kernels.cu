@@ -217,10 +217,91 @@ wf_extend_kernel(const Scene sc, const RenderParams P, const WfPool pool, WfCoun
     float time = 0.f;
     bool busy = false, more = n > 0u;
     uint32_t c_pos = 0u, c_end = 0u;                      // the warp's reserved chunk (uniform)
+#if RTW_WF_WINDOW
+    __shared__ RTW_WF_ORDER_T s_order[RTW_WF_BLOCK / 32][RTW_WF_WINDOW];
+    __shared__ uint32_t s_bins[RTW_WF_BLOCK / 32][10];
+    const uint32_t wid = threadIdx.x >> 5;
+    uint32_t c_base = 0u;
+#endif
     for (;;) {
         const uint32_t idle = __ballot_sync(FULL, !busy);
         if (idle == FULL && !more) break;
         if (more && (uint32_t)__popc(idle) >= L.fetch_min) {
+#if RTW_WF_WINDOW
+            // Window sort (A/B): the warp reserves a window of RTW_WF_WINDOW consecutive slots, reads their directions once
+            // and takes them in the order camera rays / the eight direction octants of the bounced rays (dead slots
+            // dropped), so that the rays that join the walk together start alike. c_pos / c_end index s_order.
+            if (c_pos >= c_end && more) {
+                uint32_t base = 0u;
+                if (lane == 0u) base = atomicAdd(&wc->head, (uint32_t)RTW_WF_WINDOW);
+                base = __shfl_sync(FULL, base, 0);
+                c_pos = 0u; c_end = 0u; c_base = base;
+                if (base >= n) more = false;
+                else {
+                    uint32_t live_groups = 0xFFFFFFFFu;
+                    if (L.drain) {
+                        const uint32_t f = lane < RTW_WF_WINDOW / 32 ? __ldg(&pool.warp_live[(base >> 5) + lane]) : 0u;
+                        live_groups = __ballot_sync(FULL, f != 0u);
+                    }
+                    if (lane < 10u) s_bins[wid][lane] = 0u;
+                    __syncwarp();
+                    unsigned long long keys = 0ull;                            // 4 bits per round
+#pragma unroll
+                    for (int j = 0; j < RTW_WF_WINDOW / 32; ++j) {
+                        uint32_t key = 9u;
+                        if ((live_groups >> j) & 1u) {
+                            const float4 rd = q.d[base + 32u * j + lane];
+                            const uint32_t bn = f2u(rd.w);
+                            if (bn != WF_DEAD) key = bn == 0u ? 0u : 1u + ((rd.x < 0.f ? 1u : 0u) | (rd.y < 0.f ? 2u : 0u) | (rd.z < 0.f ? 4u : 0u));
+                        }
+                        keys |= (unsigned long long)key << (4 * j);
+                        const uint32_t same = __match_any_sync(FULL, key);
+                        if (lane == (uint32_t)(__ffs(same) - 1)) atomicAdd(&s_bins[wid][key], (uint32_t)__popc(same));
+                    }
+                    __syncwarp();
+                    // exclusive scan of the ten bins (lanes 0..9)
+                    uint32_t cnt = lane < 10u ? s_bins[wid][lane] : 0u, inc = cnt;
+#pragma unroll
+                    for (int o = 1; o < 16; o <<= 1) { const uint32_t t = __shfl_up_sync(FULL, inc, o); if (lane >= (uint32_t)o) inc += t; }
+                    __syncwarp();
+                    if (lane < 10u) s_bins[wid][lane] = inc - cnt;
+                    c_end = __shfl_sync(FULL, inc, 8);                          // everything but the dead bin
+                    __syncwarp();
+#pragma unroll
+                    for (int j = 0; j < RTW_WF_WINDOW / 32; ++j) {
+                        const uint32_t key = (uint32_t)(keys >> (4 * j)) & 15u;
+                        const uint32_t same = __match_any_sync(FULL, key);
+                        const uint32_t leader = (uint32_t)(__ffs(same) - 1);
+                        uint32_t at = 0u;
+                        if (lane == leader) at = atomicAdd(&s_bins[wid][key], (uint32_t)__popc(same));
+                        at = __shfl_sync(FULL, at, leader) + __popc(same & lt_mask);
+                        if (key != 9u) s_order[wid][at] = (RTW_WF_ORDER_T)(32u * j + lane);
+                    }
+                    __syncwarp();
+                }
+            }
+            const uint32_t take = min((uint32_t)__popc(idle), c_end - c_pos);
+            SCHED_COUNT(step, 3, take);
+            SCHED_TIME_BEGIN(3);
+            const uint32_t rank = __popc(idle & lt_mask);
+            if (!busy && rank < take) {
+                pos = c_base + s_order[wid][c_pos + rank];
+                const float4 rd = q.d[pos];
+                const float4 ro = q.o[pos];
+                const uint2 id = q.id[pos];
+                Ray r; r.o = v3(ro.x, ro.y, ro.z); r.d = v3(rd.x, rd.y, rd.z); r.time = ro.w;
+                time = ro.w;
+                cx.pixel = id.x; cx.sample = id.y; cx.bounce = f2u(rd.w);
+                trav_begin(cx, r, T, S);
+                busy = true;
+                ++n_rays;
+            }
+            c_pos += take;
+            if (c_pos + lane < c_end) {                   // the next rays of the window -> L1
+                const uint32_t nx = c_base + s_order[wid][c_pos + lane];
+                prefetch_l1(&q.o[nx]); prefetch_l1(&q.id[nx]);
+            }
+#else
             if (c_pos >= c_end) {
                 uint32_t base = 0u;
                 if (lane == 0u) base = atomicAdd(&wc->head, L.chunk);
@@ -263,6 +344,7 @@ wf_extend_kernel(const Scene sc, const RenderParams P, const WfPool pool, WfCoun
                 prefetch_l1(&q.o[c_pos + lane]); prefetch_l1(&q.d[c_pos + lane]);
                 if ((lane & 1u) == 0u) prefetch_l1(&q.id[c_pos + lane]);
             }
+#endif
             __syncwarp();
             SCHED_TIME_END();
         }

@@ -110,6 +110,15 @@ struct WfLaunch {
 #ifndef RTW_WF_NODE_BURST
 #define RTW_WF_NODE_BURST 3       // node steps per vote while the node lanes keep their majority
 #endif
+#ifndef RTW_WF_WINDOW
+#define RTW_WF_WINDOW 0           // 256 (or 128 / 512 / 1024): wf_extend takes the slots of a window of that many in the order camera rays, then
+                                  // the direction octants of the bounced rays (A/B, see the kernel); 0: slot order
+#endif
+#if RTW_WF_WINDOW > 256
+#define RTW_WF_ORDER_T uint16_t
+#else
+#define RTW_WF_ORDER_T uint8_t
+#endif
 #ifndef RTW_WF_FASTVOTE
 #define RTW_WF_FASTVOTE 1         // 1: skip the leaf / event ballots of wf_extend's vote when the node lanes win anyway (same decisions)
 #endif
