@@ -38,6 +38,13 @@ for _p in (ROOT, os.path.join(ROOT, "tests")):
 import numpy as np  # noqa: E402
 
 METRIC = "Mpaths/s, Next-Week final scene 800x800 (C5), 10000 spp, depth 50"
+L2_NOTE = "GPU arm: 256 MiB memset between steps, inside the timed region (L2 is 126 MB); CPU arm: not applicable"
+
+
+def config_of(job) -> dict:
+    """The `config` object: the same on both arms (what differs per arm is under "run")."""
+    return {"workload": workload_name(job), "l2": L2_NOTE}
+
 UNIT = "Mpaths/s"
 
 # Algorithmic work per operation (SURVEY 8d; DESIGN.md "Roofline"): flop and bytes of scene data.
@@ -199,7 +206,8 @@ def run_reference(args):
     line = {"impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": tot_s / args.steps * 1e3, "higher_is_better": True,
             "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": data_label(),
-            "config": {"workload": workload_name(job), "step": last["sample"], "host_threads": last["threads"]},
+            "config": config_of(job),
+            "run": {"step": last["sample"], "host_threads": last["threads"]},
             "mrays_per_s": tot_rays / tot_s / 1e6,
             "cpu_baseline": {"value": val, "unit": UNIT, "cores": last["threads"], "kind": "port", "sample": last["sample"]},
             "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -483,8 +491,9 @@ def run_b200(args):
         line = {"metric": METRIC, "value": val, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
                 "ms_per_step": elapsed_ms / args.steps, "higher_is_better": True, "scaling": "weak" if part == "frames" else "strong", "vs_baseline": None,
                 "dtype": "f32", "data": data_label(),
-                "config": {"workload": workload_name(job), "partition": part_text,
-                           "l2": "256 MiB memset between steps (inside the timed region)", "pipeline": "wavefront (extend + shade kernels over path queues in HBM)" if wavefront else "megakernel",
+                "config": config_of(job),
+                "run": {"partition": part_text,
+                           "pipeline": "wavefront (extend + shade kernels over path queues in HBM)" if wavefront else "megakernel",
                            "fp": "strict (-fmad=false)" if args.flags & 1 else "fast (FFMA contraction)"},
                 "mrays_per_s": rays_total / (elapsed_ms * 1e-3) / 1e6, "rays_per_path": rays_total / max(1.0, paths_total),
                 "nan_paths": nan_total, "image_mean": image_mean,
@@ -557,7 +566,8 @@ def run_single_process(args):
     line = {"metric": METRIC, "value": paths_frame * args.steps / (dev_ms * 1e-3) / 1e6, "unit": UNIT, "n_gpus": n, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": dev_ms / args.steps, "higher_is_better": True, "scaling": "strong",
             "vs_baseline": None, "dtype": "f32", "data": data_label(),
-            "config": {"workload": workload_name(job), "launch": "single process, rtw_render_multi (one host thread + stream per share)", "devices": devices,
+            "config": config_of(job),
+            "run": {"launch": "single process, rtw_render_multi (one host thread + stream per share)", "devices": devices,
                        "partition": ("sample ranges, combined on device 0 by one peer-memory kernel" if split == A.RTW_SPLIT_SAMPLES
                                      else f"row bands of {args.band or 8} rows dealt round-robin, copied straight to the host image"),
                        "timing": "value: max over devices of the share's device time (CUDA events) + combine kernel; wall_ms_per_step: host clock around the call"},
