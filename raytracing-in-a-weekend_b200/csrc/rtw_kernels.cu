@@ -250,7 +250,11 @@ wf_extend_kernel(const Scene sc, const RenderParams P, const WfPool pool, WfCoun
                     for (int j = 0; j < RTW_WF_WINDOW / 32; ++j) {
                         uint32_t key = 9u;
                         if ((live_groups >> j) & 1u) {
+#if RTW_WF_WINDOW_CS
+                            const float4 rd = __ldcs(&q.d[base + 32u * j + lane]);     // streaming: the key pass must not evict BVH nodes from L1
+#else
                             const float4 rd = q.d[base + 32u * j + lane];
+#endif
                             const uint32_t bn = f2u(rd.w);
                             if (bn != WF_DEAD) key = bn == 0u ? 0u : 1u + ((rd.x < 0.f ? 1u : 0u) | (rd.y < 0.f ? 2u : 0u) | (rd.z < 0.f ? 4u : 0u));
                         }

@@ -114,6 +114,9 @@ struct WfLaunch {
 #define RTW_WF_WINDOW 0           // 256 (or 128 / 512 / 1024): wf_extend takes the slots of a window of that many in the order camera rays, then
                                   // the direction octants of the bounced rays (A/B, see the kernel); 0: slot order
 #endif
+#ifndef RTW_WF_WINDOW_CS
+#define RTW_WF_WINDOW_CS 0
+#endif
 #if RTW_WF_WINDOW > 256
 #define RTW_WF_ORDER_T uint16_t
 #else
