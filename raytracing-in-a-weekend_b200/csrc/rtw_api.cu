@@ -466,16 +466,22 @@ int pool_alloc(rtw_scene* s, T** p, size_t n) {
     return RTW_OK;
 }
 
-// Pool of path slots for one render of `n_paths` paths. The bigger the pool the fewer, longer
-// launches (less tail and launch overhead) but the longer the frame drains at the end: 1/128 of the
-// frame's paths, between 1 Mi and 12 Mi slots (6 Mi until round 2: 12 Mi is +1.7 % on the 6.4 G paths of C5, profiles/r2f_sweep.txt)
-// and never more than there are paths (C5: 2 Mi slots are
-// best at 400 spp, 6 Mi from 2000 spp on, +6 %; profiles/r1j_sweep_pool.txt; C1's 9 M paths are
-// launch-bound below 1 Mi). RTW_WF_POOL overrides. Arrays only ever grow.
+// Pool of path slots for one render of `n_paths` paths. The bigger the pool the fewer, longer launches (each pays a
+// tail and the launch gaps: cost ~ rays / pool) but the longer the frame drains at the end (cost ~ pool), so the best
+// size grows with the square root of the frame's RAYS: 128 * sqrt(rays) fits what was measured - C5 at 1 250 spp
+// (2.2 G rays) 6 Mi slots best, 9 Mi -0.5 %, 12 Mi -4 %; C5 at 10 000 spp 12 Mi > 8 Mi > 6 Mi; C4 at 625 spp (1.5 G rays,
+// 6.9 rays per path) 3.5-5 Mi +5.4 % over the 1.8 Mi of the old paths / 128 rule; C2 6 Mi +2.3 % over 3.2 Mi
+// (profiles/r2f_sweep.txt, r2h_ab_*). Rays per path are the scene's own from its previous render (3 before there is one).
+// Between 1 Mi and 16 Mi slots, never more than there are paths. RTW_WF_POOL overrides. Arrays only ever grow.
 int ensure_pool(rtw_scene* s, unsigned long long n_paths) {
     unsigned long long want = env_u32("RTW_WF_POOL", 0u);
     if (want == 0ull) {
-        want = std::min<unsigned long long>(12ull << 20, std::max<unsigned long long>(1ull << 20, n_paths / 128ull));
+        double rpp = 3.0;
+        if (s->have_stats && s->ev2 && cudaEventQuery(s->ev2) == cudaSuccess && s->last_wavefront && s->wf_paths > 0 && s->h_ctr->rays > 0)
+            rpp = std::min(64.0, std::max(1.0, (double)s->h_ctr->rays / (double)s->wf_paths));
+        cudaGetLastError();
+        want = (unsigned long long)(128.0 * std::sqrt((double)n_paths * rpp));
+        want = std::min<unsigned long long>(16ull << 20, std::max<unsigned long long>(1ull << 20, want));
         want = std::min(want, std::max<unsigned long long>(16384ull, n_paths));      // never more slots than paths
     }
     const uint32_t cap = (uint32_t)((std::max<unsigned long long>(want, 4096ull) + 255ull) & ~255ull);   // whole shade blocks
