@@ -210,6 +210,30 @@ struct Builder {
             }
         }
     }
+    // RTW_BVH_STATS=1 (tuning aid): summed surface area of the wide nodes, relative to the root's - the expected number of
+    // node visits of a random ray crossing the level - for the best collapse into nodes of at most `width` children.
+    double dp_visits(int width) const {
+        const size_t nb = bin.size();
+        if (nb == 0) return 0.0;
+        std::vector<double> cut((size_t)width * nb, 0.0);          // cut[width * b + (k - 1)]: subtree of b handed up in <= k slots
+        auto cutk = [&](uint32_t c, bool is_bin, int k) { return is_bin ? cut[(size_t)width * c + (k - 1)] : 0.0; };
+        for (size_t b = nb; b-- > 0;) {
+            const uint32_t L = bin[b].c[0], R = bin[b].c[1];
+            const bool lb = binflag[2 * b] != 0, rb = binflag[2 * b + 1] != 0;
+            Box bb = bin[b].b[0]; box_grow(bb, bin[b].b[1]);
+            double best = std::numeric_limits<double>::infinity();
+            for (int i = 1; i < width; ++i) best = std::min(best, cutk(L, lb, i) + cutk(R, rb, width - i));
+            const double wide = (double)box_area(bb) + best;
+            cut[(size_t)width * b] = wide;
+            for (int k = 2; k <= width; ++k) {
+                double bestk = wide;
+                for (int i = 1; i < k; ++i) bestk = std::min(bestk, cutk(L, lb, i) + cutk(R, rb, k - i));
+                cut[(size_t)width * b + (k - 1)] = bestk;
+            }
+        }
+        Box rb = bin[0].b[0]; box_grow(rb, bin[0].b[1]);
+        return cut[0] / std::max(1e-30, (double)box_area(rb));
+    }
     struct DpChild { Box box; uint32_t c; bool is_bin; };
     void dp_expand(const Box& box, uint32_t c, bool is_bin, int k, DpChild* out, int& n) const {
         const int ch = (is_bin && k > 1) ? dp_choice[4 * c + (k - 1)] : 0;
@@ -303,6 +327,10 @@ struct Builder {
         // the DP-chosen collapse is the default (C5 +0.5 %, C4 +5.5 %, C2 +2.7 % on the B200,
         // profiles/r2a_ab_bake_dp_fastvote.txt); RTW_BVH_COLLAPSE=greedy brings the largest-child-first one back
         static const bool use_dp = [] { const char* e = std::getenv("RTW_BVH_COLLAPSE"); return !(e && std::string(e) == "greedy"); }();
+        static const bool stats = [] { const char* e = std::getenv("RTW_BVH_STATS"); return e && e[0] == '1'; }();
+        if (is_bin && stats)
+            std::fprintf(stderr, "bvh level: %zu leaves; expected node visits of a random ray (sum of node areas / root area): "
+                                 "binary %.3f, 4-wide %.3f, 8-wide %.3f, 16-wide %.3f\n", n, dp_visits(2), dp_visits(4), dp_visits(8), dp_visits(16));
         if (is_bin && use_dp) { dp_solve(); lv.root = emit4_dp(r, max_pushes); }
         else lv.root = is_bin ? emit4(r, max_pushes) : r;
         for (int a = 0; a < 3; ++a) { lv.lo[a] = rb.lo[a]; lv.hi[a] = rb.hi[a]; }
