@@ -28,6 +28,10 @@
 #include <cuda_fp16.h>
 #endif
 
+#ifndef RTW_NODE_SORT_EXCHANGES
+#define RTW_NODE_SORT_EXCHANGES 5
+#endif
+
 namespace rtw {
 
 struct Ray { V3 o, d; float time; };
@@ -448,9 +452,19 @@ RTW_HD void trav_step_node(const TraceCtx& cx, Trav& T, const Stack& S) {
     for (int c = 0; c < 4; ++c)
         if ((rf[c] & 0xD0000000u) == 0xD0000000u && tn[c] < INFINITY) tn[c] = 3.0e38f;
 #endif
+    // RTW_NODE_SORT_EXCHANGES (fast device build; A/B): 5 = the full network (nearest first, the rest stacked farthest first);
+    // 3 = the nearest child only is brought to the front (the others are stacked in whatever partial order that leaves), 4 = also
+    // the farthest to the back. Any order is correct - crossed children all get visited; the order only decides how soon
+    // the search interval shrinks - and an exchange is five ALU-pipe instructions (FSETP + 2 SEL + 2 FSEL) in a kernel whose
+    // busiest pipe is the ALU.
     cswap(tn[0], rf[0], tn[1], rf[1]); cswap(tn[2], rf[2], tn[3], rf[3]);
-    cswap(tn[0], rf[0], tn[2], rf[2]); cswap(tn[1], rf[1], tn[3], rf[3]);
+    cswap(tn[0], rf[0], tn[2], rf[2]);
+#if !defined(RTW_FAST_NODES) || RTW_NODE_SORT_EXCHANGES >= 4
+    cswap(tn[1], rf[1], tn[3], rf[3]);
+#endif
+#if !defined(RTW_FAST_NODES) || RTW_NODE_SORT_EXCHANGES >= 5
     cswap(tn[1], rf[1], tn[2], rf[2]);
+#endif
     if (tn[3] < INFINITY) S.push(T.sp, rf[3]);
     if (tn[2] < INFINITY) S.push(T.sp, rf[2]);
     if (tn[1] < INFINITY) S.push(T.sp, rf[1]);
