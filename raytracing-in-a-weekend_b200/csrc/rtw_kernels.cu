@@ -224,9 +224,18 @@ wf_extend_kernel(const Scene sc, const RenderParams P, const WfPool pool, WfCoun
     uint32_t c_base = 0u;
 #endif
     for (;;) {
+#if RTW_WF_REDUX
+        // One REDUX.SUM gives the lane count of every state at once (a byte each: node | leaf test << 8 | event << 16 |
+        // idle << 24; a lane whose search has just ended counts nowhere) instead of a ballot + popc per state.
+        uint32_t counts = __reduce_add_sync(FULL, !busy ? 0x01000000u : T.cur == CUR_DONE ? 0u : T.cur < NODE_LIMIT ? 1u : ref_is_event(T.cur) ? 0x10000u : 0x100u);
+        if ((counts >> 24) == 32u && !more) break;
+        if (more && (counts >> 24) >= L.fetch_min) {
+            const uint32_t idle = __ballot_sync(FULL, !busy);
+#else
         const uint32_t idle = __ballot_sync(FULL, !busy);
         if (idle == FULL && !more) break;
         if (more && (uint32_t)__popc(idle) >= L.fetch_min) {
+#endif
 #if RTW_WF_WINDOW
             // Window sort (A/B): the warp reserves a window of RTW_WF_WINDOW consecutive slots, reads their directions once
             // and takes them in the order camera rays / the eight direction octants of the bounced rays (dead slots
@@ -351,6 +360,9 @@ wf_extend_kernel(const Scene sc, const RenderParams P, const WfPool pool, WfCoun
 #endif
             __syncwarp();
             SCHED_TIME_END();
+#if RTW_WF_REDUX
+            counts = __reduce_add_sync(FULL, !busy ? 0x01000000u : T.cur == CUR_DONE ? 0u : T.cur < NODE_LIMIT ? 1u : ref_is_event(T.cur) ? 0x10000u : 0x100u);
+#endif
         }
         // ---- one step of ONE kind per iteration: the kind most lanes are waiting for. Lanes in
         // other states sit the iteration out, so that the rarer, dearer steps (leaf tests, instance
@@ -392,18 +404,26 @@ wf_extend_kernel(const Scene sc, const RenderParams P, const WfPool pool, WfCoun
 #else
         const uint32_t cur = T.cur;
         const bool on_node = cur < NODE_LIMIT, on_event = ref_is_event(cur), on_prim = !on_node && !on_event && cur != CUR_DONE;
+#if RTW_WF_REDUX
+        const int cn = (int)(counts & 0xFFu);
+        int cp = (int)((counts >> 8) & 0xFFu), ce = (int)((counts >> 16) & 0xFFu);
+        bool node_step = cn * 4 >= cp * (int)L.prim_w && cn * 4 >= ce * (int)L.event_w;
+#else
         const int cn = __popc(__ballot_sync(FULL, on_node));
         int cp = 0, ce = 0;
         bool node_step = true;
-#if RTW_WF_FASTVOTE
+#endif
+#if RTW_WF_FASTVOTE && !RTW_WF_REDUX
         // With `node_sure` or more lanes on a node the node step wins whatever the other 32 - cn lanes wait for
         // (cn * 4 >= (32 - cn) * max(prim_w, event_w)): the two other ballots are only taken below that.
         if (cn < (int)L.node_sure)
 #endif
+#if !RTW_WF_REDUX
         {
             cp = __popc(__ballot_sync(FULL, on_prim)); ce = __popc(__ballot_sync(FULL, on_event));
             node_step = cn * 4 >= cp * (int)L.prim_w && cn * 4 >= ce * (int)L.event_w;
         }
+#endif
         SCHED_COUNT(iters, 0, 0);
         if (node_step) {
             SCHED_COUNT(step, 0, cn);

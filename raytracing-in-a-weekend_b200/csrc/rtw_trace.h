@@ -29,7 +29,7 @@
 #endif
 
 #ifndef RTW_NODE_SORT_EXCHANGES
-#define RTW_NODE_SORT_EXCHANGES 5
+#define RTW_NODE_SORT_EXCHANGES 3   // C5 +1.5 %, C2 +1.9 %, C4 +1.1 % over the full network; node visits +0.6 % (profiles/r2j_ab_*)
 #endif
 
 namespace rtw {
