@@ -215,7 +215,7 @@ wf_extend_kernel(const Scene sc, const RenderParams P, const WfPool pool, WfCoun
 #endif
     uint32_t pos = 0u;
     float time = 0.f;
-    bool busy = false, more = n > 0u;
+    RTW_WF_FLAG_T busy = false, more = n > 0u;         // (bool: the compiler packs them into bytes of one register and PRMTs them apart; A/B with uint32_t)
     uint32_t c_pos = 0u, c_end = 0u;                      // the warp's reserved chunk (uniform)
 #if RTW_WF_WINDOW
     __shared__ RTW_WF_ORDER_T s_order[RTW_WF_BLOCK / 32][RTW_WF_WINDOW];
@@ -531,7 +531,7 @@ wf_shade_kernel(const Scene sc, const RenderParams P, const WfPool pool, WfCount
     const uint32_t FULL = 0xFFFFFFFFu;
     const uint32_t lane = threadIdx.x & 31u;
     Path path;
-    bool alive = false, was_live = false, fresh = false;
+    RTW_WF_FLAG_T alive = false, was_live = false, fresh = false;
     if (L.drain && !init && __ldg(&pool.warp_live[e >> 5]) == 0u) return;   // (whole warp) dead for good: WfLaunch::drain
     if (!init) {
         const float4 rd = q.d[e];

@@ -122,6 +122,9 @@ struct WfLaunch {
 #else
 #define RTW_WF_ORDER_T uint8_t
 #endif
+#ifndef RTW_WF_FLAG_T
+#define RTW_WF_FLAG_T bool
+#endif
 #ifndef RTW_WF_REDUX
 #define RTW_WF_REDUX 0            // 1: one REDUX.SUM of packed byte counters per loop iteration instead of a ballot + popc per lane state (A/B)
 #endif
