@@ -174,11 +174,30 @@ RTW_HD V3 random_unit_vec_stream(const TraceCtx& cx, uint32_t base_block, uint32
 // The traversal stack: per-thread column of 32-bit words. On the device it lives in shared memory,
 // word w of thread t at base[w * stride] with base = &smem[t], stride = block size (conflict-free);
 // the host emulator passes a plain array (stride 1). Depth needed: see stack_words().
+#ifndef RTW_STACK_ADDR
+#define RTW_STACK_ADDR 0   // 1 (device builds; A/B): Trav::sp is the shared-memory ADDRESS of the next free word, so a push is one store + one
+                           // add instead of address arithmetic (shift-add) + store + increment
+#endif
 struct Stack {
     uint32_t* base;
     uint32_t stride;
+#if defined(__CUDA_ARCH__) && RTW_STACK_ADDR
+    __device__ __forceinline__ uint32_t origin() const { return (uint32_t)__cvta_generic_to_shared(base); }
+    __device__ __forceinline__ void push(uint32_t& sp, uint32_t v) const {
+        asm volatile("st.shared.b32 [%0], %1;" ::"r"(sp), "r"(v));
+        sp += stride * 4u;
+    }
+    __device__ __forceinline__ uint32_t pop(uint32_t& sp) const {
+        sp -= stride * 4u;
+        uint32_t v;
+        asm volatile("ld.shared.b32 %0, [%1];" : "=r"(v) : "r"(sp));
+        return v;
+    }
+#else
+    RTW_HD uint32_t origin() const { return 0u; }
     RTW_HD void push(uint32_t& sp, uint32_t v) const { base[sp * stride] = v; ++sp; }
     RTW_HD uint32_t pop(uint32_t& sp) const { --sp; return base[sp * stride]; }
+#endif
 };
 // bottom sentinel + top pushes + world frame (10) + sentinel + probe frame (2 + sentinel) + inner pushes
 #define RTW_STACK 32   // deepest node chain the builder allows per level (scene_build.cpp)
@@ -280,7 +299,7 @@ RTW_HD void trav_begin(const TraceCtx& cx, const Ray& r, Trav& T, const Stack& S
     trav_set_ray(T, r.o, r.d);
     T.t = cx.maxt; T.ref = REF_NONE; T.inner = REF_NONE;
     T.top_t = 0.0f; T.top_ref = REF_NONE;
-    T.inst = REF_NONE; T.sp = 0u;
+    T.inst = REF_NONE; T.sp = S.origin();
     S.push(T.sp, CUR_DONE);               // bottom of the stack: popping it ends the search
     trav_begin_level(cx, cx.sc->top, r.time, T, S);
 }
