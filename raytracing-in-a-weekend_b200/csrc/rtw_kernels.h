@@ -98,7 +98,8 @@ struct WfLaunch {
 #define RTW_MAX_STACK_WORDS 160     // deepest traversal stack column any scene may ask for (scene_build.cpp / rtw_api.cu refuse more)
 #define RTW_WF_BLOCK 128
 #ifndef RTW_WF_EXTEND_MINB
-#define RTW_WF_EXTEND_MINB 6      // min resident blocks per SM asked of the compiler for wf_extend (80 registers, no spills; +2.2 % over 5 blocks, profiles/r1h_ab_inline_minblocks.txt)
+#define RTW_WF_EXTEND_MINB 7      // min resident blocks per SM asked of the compiler for wf_extend (71 registers, no spills since the lane flags are
+                                  // words and the stack pointer an address; 6 blocks / 80 registers until round 2: 7 blocks then cost -3.2 %, 8 now -1.3 %)
 #endif
 #ifndef RTW_WF_PENDING
 #define RTW_WF_PENDING 0          // 1: wf_extend parks a popped leaf test and keeps walking nodes (see the kernel); A/B: leaf steps
@@ -123,7 +124,9 @@ struct WfLaunch {
 #define RTW_WF_ORDER_T uint8_t
 #endif
 #ifndef RTW_WF_FLAG_T
-#define RTW_WF_FLAG_T bool
+#define RTW_WF_FLAG_T uint32_t     // wf_extend's `busy` / `more`: as bool the compiler packed them into bytes of one register and PRMT-ed them
+                                  // apart every iteration; as words: 73 instead of 79 registers, 2 % fewer instructions, +1.2 % (C5), and with
+                                  // that room 7 resident blocks: +3.4 % together (profiles/r2l_ab_u32_flags_7_blocks.txt)
 #endif
 #ifndef RTW_WF_REDUX
 #define RTW_WF_REDUX 0            // 1: one REDUX.SUM of packed byte counters per loop iteration instead of a ballot + popc per lane state (A/B)
