@@ -320,6 +320,22 @@ enum { RTW_PROX_SQUARE = 0, RTW_PROX_EDGES = 1 };
 int rtw_bilateral_filter_device(const uint8_t* d_rgb8, uint32_t width, uint32_t height, uint32_t size,
                                 int proximity, uint8_t* d_out_rgb8, float* d_params, int device,
                                 void* stream);
+/* rtw_bilateral_filter_device for callers that may not allocate. NO COUNTERPART IN THE REFERENCE: added
+ * for code under CUDA graph capture, tight serving loops and harnesses that
+ * forbid cudaMalloc. Same arguments, same bytes out as rtw_bilateral_filter_device, but the filter's scratch
+ * (gradient array, weight table, parameters) is a file-scope static device array of csrc/rtw_post.cu instead
+ * of stream-ordered allocations: the call makes no cudaMalloc / cudaMallocAsync / cudaFree and only launches
+ * kernels on `stream`. Every device that loads the library holds that array (4.3 MiB) until exit. Limits:
+ * (width-2)*(height-2) <= RTW_NOALLOC_MAX_INTERIOR_PIXELS (e.g. 1280x720) and size <= RTW_NOALLOC_MAX_WINDOW;
+ * beyond either the call returns RTW_E_UNSUPPORTED and rtw_last_error() names the limit. All calls on a device
+ * share the array and it keeps the previous call's contents (every value read is rewritten first, nothing has
+ * to start at zero): calls whose kernels can overlap on the GPU — different streams without an ordering between
+ * them — race; serialise them. */
+#define RTW_NOALLOC_MAX_INTERIOR_PIXELS 1046528u   /* 2^20 - 2048 */
+#define RTW_NOALLOC_MAX_WINDOW 16u
+int rtw_bilateral_filter_device_noalloc(const uint8_t* d_rgb8, uint32_t width, uint32_t height, uint32_t size,
+                                        int proximity, uint8_t* d_out_rgb8, float* d_params, int device,
+                                        void* stream);
 /* The same for HOST images (what the reference function receives and returns): H2D, filter, D2H.
  * out_kernel_ms (may be NULL) receives the device time of the four kernels. `device` < 0 = current. */
 int rtw_bilateral_filter(const uint8_t* rgb8, uint32_t width, uint32_t height, uint32_t size,

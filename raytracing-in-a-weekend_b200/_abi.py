@@ -16,6 +16,7 @@ RTW_ABI_VERSION = 3
 
 # error codes
 RTW_OK, RTW_E_INVALID, RTW_E_CUDA, RTW_E_NOMEM, RTW_E_UNSUPPORTED = 0, -1, -2, -3, -4
+RTW_NOALLOC_MAX_INTERIOR_PIXELS, RTW_NOALLOC_MAX_WINDOW = (1 << 20) - 2048, 16       # rtw_bilateral_filter_device_noalloc
 # density kinds (instance.rs:21-26)
 RTW_DENSITY_SURFACE, RTW_DENSITY_CONST = 0, 1
 RTW_SHAPE_PARALLELOGRAM, RTW_SHAPE_TRIANGLE = 0, 1
@@ -125,6 +126,7 @@ SYMBOLS = {
     "rtw_quantize": (C.c_int, [C.c_void_p, C.c_void_p, u64, C.c_int]),
     "rtw_render_rgb8": (C.c_int, [C.c_void_p, P(rtw_camera), P(rtw_render_opts), C.c_void_p]),
     "rtw_bilateral_filter_device": (C.c_int, [C.c_void_p, u32, u32, u32, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]),
+    "rtw_bilateral_filter_device_noalloc": (C.c_int, [C.c_void_p, u32, u32, u32, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]),
     "rtw_bilateral_filter": (C.c_int, [C.c_void_p, u32, u32, u32, C.c_int, C.c_void_p, P(f32), P(f32), C.c_int]),
     "rtw_scene_multi_create": (C.c_int, [P(rtw_scene_desc), P(C.c_int), C.c_int, P(C.c_void_p)]),
     "rtw_scene_multi_destroy": (None, [C.c_void_p]),

@@ -12,7 +12,12 @@
 // All f32 arithmetic that reaches the output is written with the round-to-nearest intrinsics so that no
 // contraction to FMA can happen (rustc never contracts). Bytes in, bytes out: the result is compared byte for
 // byte with oracle/postprocessing.hpp (exp_mode 1).
+#include <mutex>
+#include <string>
 #include "rtw_post.h"
+#include "../../include/rtw.h"
+
+namespace rtw { void set_last_error(const std::string& msg); }
 
 namespace rtw {
 
@@ -219,4 +224,112 @@ cudaError_t bilateral_filter_enqueue(const uint8_t* d_in, uint32_t width, uint32
     return cudaSuccess;
 }
 
+
+// ---------------------------------------------------------------------------------------------------------------
+// The same filter for callers that may not allocate (rtw_bilateral_filter_device_noalloc, include/rtw.h). The three
+// scratch arrays of bilateral_filter_enqueue (the gradient array, the weight table, the four parameters) live in ONE
+// file-scope device array of fixed size instead of coming from cudaMallocAsync; every device that loads the library
+// holds its own copy (4.3 MiB) until the process exits. The kernels are the ones above, handed addresses inside it.
+//
+//   floats [0, 64)                              params {spatial, avg_gradient, inv_range, inv_spatial} (when the caller passes none)
+//   floats [64, 64 + kStaticTableFloats)        weight table, (size+1)^2 * 256 entries, size <= RTW_NOALLOC_MAX_WINDOW
+//   floats [.., .. + kStaticGradFloats)         gradient array, (w-2)(h-2) values + the ordered sum's read-ahead padding
+//
+// Nothing in it has to start at zero: the gradient kernel writes every value the sum reads (values past n are never
+// loaded, post_load4 substitutes +0), the table kernel writes every entry the filter looks up, and the params kernel
+// writes all four parameters, so whatever the previous call left behind is overwritten before it is read. All calls
+// on one device share the array: two calls whose kernels overlap on the GPU (different streams, no dependency
+// between them) race on it.
+constexpr uint32_t kStaticMaxWindow = RTW_NOALLOC_MAX_WINDOW;                             // 16
+constexpr uint32_t kStaticMaxGrad = RTW_NOALLOC_MAX_INTERIOR_PIXELS;                      // 1 Mi - 2 Ki values
+constexpr size_t kStaticParamFloats = 64;                                                 // 256 B: keeps the table aligned
+constexpr size_t kStaticTableFloats = (size_t)(kStaticMaxWindow + 1u) * (kStaticMaxWindow + 1u) * 256u;
+constexpr size_t kStaticGradFloats = ((size_t)kStaticMaxGrad + kChunk - 1u) / kChunk * kChunk + kChunk;
+constexpr size_t kStaticFloats = kStaticParamFloats + kStaticTableFloats + kStaticGradFloats;
+static_assert(kStaticTableFloats % 64u == 0 && kStaticGradFloats % 64u == 0, "sub-arrays stay 256-byte aligned");
+static_assert(kStaticFloats * sizeof(float) <= (5u << 20), "the static scratch is meant to stay modest");
+
+static __device__ __align__(256) float g_post_scratch[kStaticFloats];
+
+namespace {
+
+// In host code `g_post_scratch` names a host-side shadow of the symbol, not device memory: the device address comes
+// from cudaGetSymbolAddress, asked once per device with that device current.
+constexpr int kMaxDevices = 64;
+std::mutex g_scratch_mutex;
+float* g_scratch_addr[kMaxDevices] = {};
+
+cudaError_t post_scratch_for_current_device(float** out) {
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    if (dev < 0 || dev >= kMaxDevices) return cudaErrorInvalidDevice;
+    std::lock_guard<std::mutex> lk(g_scratch_mutex);
+    if (!g_scratch_addr[dev]) {
+        void* p = nullptr;
+        e = cudaGetSymbolAddress(&p, g_post_scratch);
+        if (e != cudaSuccess) return e;
+        g_scratch_addr[dev] = static_cast<float*>(p);
+    }
+    *out = g_scratch_addr[dev];
+    return cudaSuccess;
+}
+
+}  // namespace
+
+// No cudaMalloc / cudaMallocAsync / cudaFree on this path: kernel launches only.
+cudaError_t bilateral_filter_enqueue_static(const uint8_t* d_in, uint32_t width, uint32_t height, uint32_t size, int kind,
+                                            uint8_t* d_out, float* d_params, cudaStream_t st, int* n_launches) {
+    const uint32_t n_grad = (width - 2u) * (height - 2u);
+    if (n_grad > kStaticMaxGrad || size > kStaticMaxWindow) return cudaErrorInvalidValue;
+    float* base = nullptr;
+    cudaError_t e = post_scratch_for_current_device(&base);
+    if (e != cudaSuccess) return e;
+    float* d_table = base + kStaticParamFloats;
+    float* d_grad = d_table + kStaticTableFloats;
+    if (!d_params) d_params = base;
+    const size_t n_table = (size_t)(size + 1u) * (size + 1u) * 256u;
+    int launches = 0;
+    if (n_grad) { post_gradient_kernel<<<post_grid(n_grad, 256), 256, 0, st>>>(d_in, width, height, d_grad); ++launches; }
+    post_params_kernel<<<1, 32, 0, st>>>(d_grad, n_grad, width, height, d_params); ++launches;
+    post_table_kernel<<<post_grid(n_table, 256), 256, 0, st>>>(d_params, size, d_table); ++launches;
+    const size_t n = (size_t)width * height * 3u;
+    post_bilateral_kernel<true><<<post_grid(n, 256), 256, 0, st>>>(d_in, width, height, size, kind, d_params, d_table, d_out);
+    ++launches;
+    if (n_launches) *n_launches = launches;
+    return cudaGetLastError();
+}
+
 }  // namespace rtw
+
+extern "C" int rtw_bilateral_filter_device_noalloc(const uint8_t* d_rgb8, uint32_t width, uint32_t height, uint32_t size,
+                                                   int proximity, uint8_t* d_out_rgb8, float* d_params, int device,
+                                                   void* stream) {
+    auto fail = [](int code, const std::string& msg) { rtw::set_last_error(msg); return code; };
+    if (!d_rgb8 || !d_out_rgb8) return fail(RTW_E_INVALID, "null argument");
+    if (d_rgb8 == d_out_rgb8) return fail(RTW_E_INVALID, "bilateral filter cannot run in place");
+    if (width < 2u || height < 2u || width > 32768u || height > 32768u)
+        return fail(RTW_E_INVALID, "bilateral filter: image must be 2..32768 pixels a side");
+    if (proximity != RTW_PROX_SQUARE && proximity != RTW_PROX_EDGES) return fail(RTW_E_INVALID, "unknown proximity type");
+    const uint64_t interior = (uint64_t)(width - 2u) * (height - 2u);
+    if (interior > RTW_NOALLOC_MAX_INTERIOR_PIXELS)
+        return fail(RTW_E_UNSUPPORTED, "rtw_bilateral_filter_device_noalloc: (width-2)*(height-2) = " + std::to_string(interior) +
+                                           " exceeds the static scratch (RTW_NOALLOC_MAX_INTERIOR_PIXELS = " +
+                                           std::to_string(RTW_NOALLOC_MAX_INTERIOR_PIXELS) + "); use rtw_bilateral_filter_device");
+    if (size > RTW_NOALLOC_MAX_WINDOW)
+        return fail(RTW_E_UNSUPPORTED, "rtw_bilateral_filter_device_noalloc: window size " + std::to_string(size) +
+                                           " exceeds the static weight table (RTW_NOALLOC_MAX_WINDOW = " +
+                                           std::to_string(RTW_NOALLOC_MAX_WINDOW) + "); use rtw_bilateral_filter_device");
+    int prev = -1;
+    cudaError_t e = cudaGetDevice(&prev);
+    if (e == cudaSuccess && device >= 0 && device != prev) e = cudaSetDevice(device);
+    if (e == cudaSuccess)
+        e = rtw::bilateral_filter_enqueue_static(d_rgb8, width, height, size, proximity, d_out_rgb8, d_params,
+                                                 static_cast<cudaStream_t>(stream), nullptr);
+    if (prev >= 0 && device >= 0 && device != prev) cudaSetDevice(prev);
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        return fail(RTW_E_CUDA, std::string("rtw_bilateral_filter_device_noalloc: ") + cudaGetErrorString(e));
+    }
+    return RTW_OK;
+}

@@ -80,6 +80,8 @@ pub const RTW_SPLIT_TILES: u32 = 1;
 pub const RTW_SPLIT_FRAMES: u32 = 2;
 pub const RTW_PROX_SQUARE: c_int = 0;
 pub const RTW_PROX_EDGES: c_int = 1;
+pub const RTW_NOALLOC_MAX_INTERIOR_PIXELS: u32 = 1_046_528;
+pub const RTW_NOALLOC_MAX_WINDOW: u32 = 16;
 pub const RTW_BENCH_FP32: c_int = 0;
 pub const RTW_BENCH_L2: c_int = 1;
 pub const RTW_BENCH_HBM: c_int = 2;
@@ -113,6 +115,10 @@ extern "C" {
     pub fn rtw_render_rgb8(scene: *mut rtw_scene, cam: *const rtw_camera, opts: *const rtw_render_opts, out_rgb8: *mut u8) -> c_int;
     pub fn rtw_bilateral_filter_device(d_rgb8: *const u8, width: u32, height: u32, size: u32, proximity: c_int, d_out_rgb8: *mut u8,
                                        d_params: *mut f32, device: c_int, stream: *mut c_void) -> c_int;
+    /// The device filter with its scratch in a static device array (no allocation inside the call); limits
+    /// RTW_NOALLOC_MAX_INTERIOR_PIXELS / RTW_NOALLOC_MAX_WINDOW. No counterpart in the reference (include/rtw.h).
+    pub fn rtw_bilateral_filter_device_noalloc(d_rgb8: *const u8, width: u32, height: u32, size: u32, proximity: c_int, d_out_rgb8: *mut u8,
+                                               d_params: *mut f32, device: c_int, stream: *mut c_void) -> c_int;
     /// Rust2's `postprocessing::bilateral_filter(&img, Proximity::new(size, type))` (postprocessing.rs:70-135) on the
     /// device: `rgb8` / `out_rgb8` are the raw buffers of `ImageBuffer<Rgb<u8>, Vec<u8>>` (`img.as_raw()`),
     /// proximity 0 = Square, 1 = Edges; `out_params` / `out_kernel_ms` may be null.
