@@ -35,6 +35,10 @@ __device__ __forceinline__ unsigned long long warp_sum_u64(unsigned long long v)
     return v;
 }
 
+// kLights: the instance that runs Rust2's light-biased integrators (shadow rays from inside segment_end: a second,
+// non-inlined traversal). It is a kernel of its own so that the other integrators keep the register allocation
+// they had without it (no stack frame, no spills).
+template <bool kLights>
 __global__ void __launch_bounds__(RTW_MEGA_BLOCK)
 mega_kernel(const Scene sc, const RenderParams P, float* __restrict__ sum, Counters* __restrict__ ctr,
             uint32_t* __restrict__ work, const MegaLaunch L) {
@@ -119,7 +123,7 @@ mega_kernel(const Scene sc, const RenderParams P, float* __restrict__ sum, Count
             // ---- shade / scatter every lane whose search is over
             if (alive && T.cur == CUR_DONE) {
                 bool finished = true;
-                if (first_hit_integrator(P.integrator) || path.depth_left >= 1u) finished = segment_end(cx, nt, P, path, T, &S, &n_rays);
+                if (first_hit_integrator(P.integrator) || path.depth_left >= 1u) finished = segment_end(cx, nt, P, path, T, kLights ? &S : nullptr, &n_rays);
                 if (!finished) {
                     cx.bounce = P.depth - path.depth_left;
                     if (segment_begin(cx, P, path, T, S)) ++n_rays; else finished = true;
@@ -649,7 +653,10 @@ wf_shade_kernel(const Scene sc, const RenderParams P, const WfPool pool, WfCount
 
 cudaError_t RTW_FN(launch_mega)(const Scene& sc, const RenderParams& P, float* d_sum, Counters* d_ctr,
                                 uint32_t* d_work, const MegaLaunch& L, cudaStream_t st) {
-    RTW_CAT(variant_, RTW_VARIANT)::mega_kernel<<<L.grid, L.block, L.smem_bytes, st>>>(sc, P, d_sum, d_ctr, d_work, L);
+    if (light_integrator(P.integrator))
+        RTW_CAT(variant_, RTW_VARIANT)::mega_kernel<true><<<L.grid, L.block, L.smem_bytes, st>>>(sc, P, d_sum, d_ctr, d_work, L);
+    else
+        RTW_CAT(variant_, RTW_VARIANT)::mega_kernel<false><<<L.grid, L.block, L.smem_bytes, st>>>(sc, P, d_sum, d_ctr, d_work, L);
     return cudaGetLastError();
 }
 
@@ -670,7 +677,7 @@ cudaError_t RTW_FN(launch_wf_shade)(const Scene& sc, const RenderParams& P, cons
 // the last query made a concurrent launch of a deeper scene fail with "invalid argument".
 static cudaError_t raise_smem_limit(const void* kernel, size_t smem_bytes, int which) {
     static std::mutex m;
-    static int limit[2][64] = {};
+    static int limit[3][64] = {};
     int dev = 0;
     cudaError_t e = cudaGetDevice(&dev);
     if (e != cudaSuccess) return e;
@@ -689,10 +696,17 @@ cudaError_t RTW_FN(wf_extend_occupancy)(int* blocks_per_sm, size_t smem_bytes) {
 }
 
 cudaError_t RTW_FN(mega_occupancy)(int* blocks_per_sm, size_t smem_bytes) {
-    cudaError_t e = raise_smem_limit((const void*)RTW_CAT(variant_, RTW_VARIANT)::mega_kernel, smem_bytes, 1);
+    // both instances share one launch shape: the grid is sized for the one that fits fewer blocks (work is handed
+    // out through a counter, so the other merely runs a few blocks short of its own maximum)
+    cudaError_t e = raise_smem_limit((const void*)RTW_CAT(variant_, RTW_VARIANT)::mega_kernel<false>, smem_bytes, 1);
+    if (e == cudaSuccess) e = raise_smem_limit((const void*)RTW_CAT(variant_, RTW_VARIANT)::mega_kernel<true>, smem_bytes, 2);
     if (e != cudaSuccess) return e;
-    return cudaOccupancyMaxActiveBlocksPerMultiprocessor(blocks_per_sm, RTW_CAT(variant_, RTW_VARIANT)::mega_kernel,
-                                                         RTW_MEGA_BLOCK, smem_bytes);
+    int plain = 0, lights = 0;
+    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&plain, RTW_CAT(variant_, RTW_VARIANT)::mega_kernel<false>, RTW_MEGA_BLOCK, smem_bytes);
+    if (e == cudaSuccess)
+        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&lights, RTW_CAT(variant_, RTW_VARIANT)::mega_kernel<true>, RTW_MEGA_BLOCK, smem_bytes);
+    *blocks_per_sm = plain < lights ? plain : lights;
+    return e;
 }
 
 }  // namespace rtw
