@@ -437,6 +437,22 @@ uint32_t env_u32(const char* name, uint32_t dflt) {
     return e ? (uint32_t)std::strtoul(e, nullptr, 10) : dflt;
 }
 
+// Which pipeline a render takes when the caller names none. The wavefront pipeline buys coherence — every warp runs one
+// kind of step with most of its lanes — and pays for it with a path record that crosses HBM twice per ray (56 B) and two
+// launches per bounce. That pays where there is a tree to walk. A scene whose top level is a handful of primitives and
+// nothing below (C1: five spheres, C3: four) is one node fetch and one or two leaf tests per ray: the megakernel's lanes
+// stay in step by themselves and it keeps the path in registers (profiles/r2q_mega_vs_wavefront.txt, r2r_crossover.txt:
+// C1 3.0x, C3 1.35x for the megakernel; C2 1.05x, C4 1.34x, C5 2.0x for the wavefront pipeline). Short renders take
+// the megakernel whatever the scene: the pipeline's ramp and drain (about 2 x depth iterations over a mostly dead pool)
+// would be most of the frame. RTW_WF_MIN_PATHS / RTW_MEGA_FLAT_LEAVES move the two thresholds (tuning only).
+bool wavefront_pays(const rtw_scene* s, uint64_t n_paths) {
+    static const uint64_t min_paths = env_u32("RTW_WF_MIN_PATHS", 1u << 18);
+    static const uint32_t flat_leaves = env_u32("RTW_MEGA_FLAT_LEAVES", 8u);
+    if (n_paths < min_paths) return false;
+    const bool flat = s->info.n_tlas_leaves <= flat_leaves && s->info.n_blas_nodes == 0u && s->info.n_baked_instances == 0u;
+    return !flat;
+}
+
 // The occupancies depend on the dynamic shared memory (the stack columns). Largest size first: the attribute
 // cudaFuncAttributeMaxDynamicSharedMemorySize the queries set must end up covering every launch.
 int refresh_mega_occupancy(rtw_scene* s) {
@@ -640,8 +656,8 @@ int enqueue_render(rtw_scene* s, const rtw_camera* cam, const rtw_render_opts* o
     // the light-biased integrators trace their shadow rays from inside the shading step: megakernel only
     if ((o->flags & RTW_FLAG_WAVEFRONT) && light_integrator(P.integrator)) return fail(RTW_E_UNSUPPORTED, "light-biased integrators run in the megakernel only");
     s->last_wavefront = (o->flags & RTW_FLAG_WAVEFRONT) ||
-                        (!(o->flags & RTW_FLAG_MEGAKERNEL) && n_paths >= (1ull << 18) && P.depth <= WF_MAX_DEPTH &&
-                         !light_integrator(P.integrator));
+                        (!(o->flags & RTW_FLAG_MEGAKERNEL) && P.depth <= WF_MAX_DEPTH && !light_integrator(P.integrator) &&
+                         wavefront_pays(s, n_paths));
     if (s->last_wavefront) {
         s->launches = 0;
         if ((rc = enqueue_wavefront(s, P, variant, d_out, st))) return rc;

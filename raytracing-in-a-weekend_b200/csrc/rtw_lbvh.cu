@@ -52,54 +52,61 @@ __global__ void lbvh_karras_kernel(const uint32_t* __restrict__ codes, int n, in
     lbvh_karras(codes, n, i, left, right, parent_i, parent_l);
 }
 
-__device__ __forceinline__ LbvhBox load_box_cg(const LbvhBox* p) {   // written by another thread: bypass L1
-    LbvhBox b;
-    const float* f = reinterpret_cast<const float*>(p);
-    b.lo[0] = __ldcg(f + 0); b.lo[1] = __ldcg(f + 1); b.lo[2] = __ldcg(f + 2);
-    b.hi[0] = __ldcg(f + 3); b.hi[1] = __ldcg(f + 4); b.hi[2] = __ldcg(f + 5);
-    return b;
-}
-
-// bottom-up fit: every leaf walks up; the second thread to reach a node computes its box
-__global__ void lbvh_fit_kernel(const LbvhLeaf* __restrict__ leaves, const uint32_t* __restrict__ order, int n,
-                                const int* __restrict__ left, const int* __restrict__ right,
-                                const int* __restrict__ parent_i, const int* __restrict__ parent_l, LbvhBox* ibox,
-                                uint32_t* flag) {
+// bottom-up fit: every leaf walks up; the second thread to reach a node owns its subtree from then on, rotates and
+// computes its box (lbvh_fit_node). Links and boxes written by other threads are read with ld.global.cg.
+__global__ void lbvh_fit_kernel(LbvhBuild b, int n, uint32_t* flag) {
     const int p = blockIdx.x * blockDim.x + threadIdx.x;
     if (p >= n) return;
-    int cur = parent_l[p];
+    int cur = b.parent_l[p];
     while (cur >= 0) {
         __threadfence();
         if (atomicAdd(&flag[cur], 1u) == 0u) return;
         __threadfence();
-        const int l = left[cur], r = right[cur];
-        const LbvhBox a = l < 0 ? lbvh_leaf_box(leaves[order[~l]]) : load_box_cg(&ibox[l]);
-        const LbvhBox b = r < 0 ? lbvh_leaf_box(leaves[order[~r]]) : load_box_cg(&ibox[r]);
-        ibox[cur] = lbvh_union(a, b);
-        cur = parent_i[cur];
+        lbvh_fit_node(b, cur);
+        cur = b.parent_i[cur];
     }
 }
 
-__global__ void lbvh_depth_kernel(const int* __restrict__ parent_i, int n, uint32_t* __restrict__ wide,
-                                  uint32_t* __restrict__ max_depth) {
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n - 1) return;
-    const uint32_t d = lbvh_depth(parent_i, i);
-    wide[i] = (d & 1u) ? 0u : 1u;
-    atomicMax(max_depth, d + 1u);          // its leaf children sit one level below
-}
-
-__global__ void lbvh_emit_kernel(LbvhTree t, int n, const uint32_t* __restrict__ wide, Node* nodes, Node16* nodes16) {
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n - 1 || !wide[i]) return;
-    lbvh_emit(t, i, nodes, nodes16);
-}
-
-__global__ void lbvh_finish_kernel(const LbvhBox* __restrict__ ibox, uint32_t node_base, const uint32_t* __restrict__ max_depth,
-                                   LbvhLevelOut* out) {
-    for (int a = 0; a < 3; ++a) { out->lo[a] = ibox[0].lo[a]; out->hi[a] = ibox[0].hi[a]; }
-    out->root = make_ref(KIND_NODE, node_base);      // the binary root is the level's first wide node
-    out->max_depth = *max_depth;
+// Breadth-first collapse by ONE block (a level of a scene is a few thousand leaves; the loop is O(n / 1024) steps of
+// lbvh_pick + lbvh_emit per thread for any n). queue[k] = the binary node behind wide node k; the children of a
+// tree level's wide nodes are appended in thread order through a block scan, so the node order is the emulator's
+// sequential one: the binary root is wide node 0 and every tree level is contiguous (the top of the tree stays hot).
+constexpr int LBVH_COLLAPSE_BLOCK = 1024;
+__global__ void __launch_bounds__(LBVH_COLLAPSE_BLOCK)
+lbvh_collapse_kernel(LbvhTree t, int* queue, Node* nodes, Node16* nodes16, LbvhLevelOut* out) {
+    typedef cub::BlockScan<uint32_t, LBVH_COLLAPSE_BLOCK> Scan;
+    __shared__ typename Scan::TempStorage tmp;
+    uint32_t head = 0u, tail = 1u, depth = 0u;           // the same in every thread
+    if (threadIdx.x == 0) queue[0] = 0;
+    __syncthreads();
+    while (head < tail) {
+        ++depth;
+        const uint32_t level_end = tail;
+        for (uint32_t base = head; base < level_end; base += LBVH_COLLAPSE_BLOCK) {
+            const uint32_t me = base + threadIdx.x;
+            int cand[4]; int nc = 0; uint32_t k = 0u;
+            if (me < level_end) {
+                nc = lbvh_pick(t, queue[me], cand);
+                for (int j = 0; j < nc; ++j) k += cand[j] >= 0 ? 1u : 0u;
+            }
+            uint32_t off, total;
+            Scan(tmp).ExclusiveSum(k, off, total);
+            if (me < level_end) {
+                uint32_t pos[4] = {0u, 0u, 0u, 0u};
+                uint32_t w = tail + off;
+                for (int j = 0; j < nc; ++j) if (cand[j] >= 0) { pos[j] = w; queue[w] = cand[j]; ++w; }
+                lbvh_emit(t, cand, nc, pos, me, nodes, nodes16);
+            }
+            tail += total;
+            __syncthreads();                             // the scan's storage is reused; queue entries become visible
+        }
+        head = level_end;
+    }
+    if (threadIdx.x == 0) {
+        for (int a = 0; a < 3; ++a) { out->lo[a] = t.ibox[0].lo[a]; out->hi[a] = t.ibox[0].hi[a]; }
+        out->root = make_ref(KIND_NODE, t.node_base);    // the binary root is the level's first wide node
+        out->max_depth = depth;
+    }
 }
 
 template <class T>
@@ -116,8 +123,8 @@ cudaError_t grow(T** p, size_t* have, size_t need) {
 
 LbvhScratch::~LbvhScratch() {
     cudaFree(codes); cudaFree(codes_sorted); cudaFree(order_in); cudaFree(order); cudaFree(left); cudaFree(right);
-    cudaFree(parent_i); cudaFree(parent_l); cudaFree(ibox); cudaFree(flag); cudaFree(wide); cudaFree(wide_index);
-    cudaFree(cb); cudaFree(max_depth); cudaFree(cub_tmp);
+    cudaFree(parent_i); cudaFree(parent_l); cudaFree(ibox); cudaFree(flag); cudaFree(queue);
+    cudaFree(cb); cudaFree(cub_tmp);
 }
 
 #define LB(call) do { cudaError_t e__ = (call); if (e__ != cudaSuccess) return e__; } while (0)
@@ -131,14 +138,11 @@ cudaError_t lbvh_build_level(const LbvhLeaf* d_leaves, uint32_t n, uint32_t node
     h = w.n_codes; LB(grow(&w.parent_l, &h, n)); h = w.n_codes; LB(grow(&w.left, &h, n));
     h = w.n_codes; LB(grow(&w.right, &h, n)); h = w.n_codes; LB(grow(&w.parent_i, &h, n));
     h = w.n_codes; LB(grow(&w.ibox, &h, n)); h = w.n_codes; LB(grow(&w.flag, &h, n));
-    h = w.n_codes; LB(grow(&w.wide, &h, n)); h = w.n_codes; LB(grow(&w.wide_index, &h, n));
+    h = w.n_codes; LB(grow(&w.queue, &h, n));
     if (w.n_codes < n) w.n_codes = n;
     if (!w.cb) LB(cudaMalloc(reinterpret_cast<void**>(&w.cb), 6 * sizeof(float)));
-    if (!w.max_depth) LB(cudaMalloc(reinterpret_cast<void**>(&w.max_depth), sizeof(uint32_t)));
-    size_t sort_bytes = 0, scan_bytes = 0;
-    LB(cub::DeviceRadixSort::SortPairs(nullptr, sort_bytes, w.codes, w.codes_sorted, w.order_in, w.order, (int)n, 0, 30, st));
-    LB(cub::DeviceScan::ExclusiveSum(nullptr, scan_bytes, w.wide, w.wide_index, (int)(n - 1u), st));
-    const size_t tmp = sort_bytes > scan_bytes ? sort_bytes : scan_bytes;
+    size_t tmp = 0;
+    LB(cub::DeviceRadixSort::SortPairs(nullptr, tmp, w.codes, w.codes_sorted, w.order_in, w.order, (int)n, 0, 30, st));
     if (w.cub_bytes < tmp) {
         if (w.cub_tmp) cudaFree(w.cub_tmp);
         w.cub_tmp = nullptr; w.cub_bytes = 0;
@@ -147,21 +151,21 @@ cudaError_t lbvh_build_level(const LbvhLeaf* d_leaves, uint32_t n, uint32_t node
     }
     const int B = 128;
     const int g_leaf = (int)((n + B - 1) / B), g_int = (int)((n - 1 + B - 1) / B);
-    LB(cudaMemsetAsync(w.max_depth, 0, sizeof(uint32_t), st));
     lbvh_bounds_kernel<<<1, 256, 0, st>>>(d_leaves, n, w.cb);
     lbvh_morton_kernel<<<g_leaf, B, 0, st>>>(d_leaves, n, w.cb, w.codes, w.order_in);
     size_t sb = w.cub_bytes;
     LB(cub::DeviceRadixSort::SortPairs(w.cub_tmp, sb, w.codes, w.codes_sorted, w.order_in, w.order, (int)n, 0, 30, st));
     lbvh_karras_kernel<<<g_int, B, 0, st>>>(w.codes_sorted, (int)n, w.left, w.right, w.parent_i, w.parent_l, w.flag);
-    lbvh_fit_kernel<<<g_leaf, B, 0, st>>>(d_leaves, w.order, (int)n, w.left, w.right, w.parent_i, w.parent_l, w.ibox, w.flag);
-    lbvh_depth_kernel<<<g_int, B, 0, st>>>(w.parent_i, (int)n, w.wide, w.max_depth);
-    sb = w.cub_bytes;
-    LB(cub::DeviceScan::ExclusiveSum(w.cub_tmp, sb, w.wide, w.wide_index, (int)(n - 1u), st));
+    LbvhBuild b;
+    b.leaves = d_leaves; b.order = w.order; b.left = w.left; b.right = w.right; b.parent_i = w.parent_i; b.parent_l = w.parent_l;
+    b.ibox = w.ibox;
+    for (int pass = 0; pass < LBVH_FIT_PASSES; ++pass) {
+        if (pass > 0) LB(cudaMemsetAsync(w.flag, 0, (size_t)(n - 1u) * sizeof(uint32_t), st));
+        lbvh_fit_kernel<<<g_leaf, B, 0, st>>>(b, (int)n, w.flag);
+    }
     LbvhTree t;
-    t.leaves = d_leaves; t.order = w.order; t.left = w.left; t.right = w.right; t.ibox = w.ibox;
-    t.wide_index = w.wide_index; t.node_base = node_base;
-    lbvh_emit_kernel<<<g_int, B, 0, st>>>(t, (int)n, w.wide, d_nodes, d_nodes16);
-    lbvh_finish_kernel<<<1, 1, 0, st>>>(w.ibox, node_base, w.max_depth, d_out);
+    t.leaves = d_leaves; t.order = w.order; t.left = w.left; t.right = w.right; t.ibox = w.ibox; t.node_base = node_base;
+    lbvh_collapse_kernel<<<1, LBVH_COLLAPSE_BLOCK, 0, st>>>(t, w.queue, d_nodes, d_nodes16, d_out);
     return cudaGetLastError();
 }
 

@@ -8,9 +8,10 @@
 //   1. Morton code (30 bits) of every leaf's box centre inside the level's centroid bounds
 //   2. radix sort of (code, leaf)
 //   3. Karras 2012 binary radix tree over the sorted codes (ties broken by position)
-//   4. bottom-up box fit (second arrival at a node computes it)
-//   5. collapse to the 4-wide nodes the traversal walks (rtw_device.h Node / Node16): an internal
-//      node at even depth becomes a wide node and adopts the children of its internal children
+//   4. bottom-up box fit (second arrival at a node computes it) with one tree rotation per node on the way (lbvh_fit_node)
+//   5. collapse to the 4-wide nodes the traversal walks (rtw_device.h Node / Node16), top down and breadth first: a
+//      wide node starts with the two children of its binary node and, while it has a free slot, opens the internal
+//      child with the largest box (lbvh_pick); the internal children left become the next wide nodes
 // Leaves keep the primitive's own reference leaf box as the child box stored in their parent, exactly
 // as in the host SAH build, so the closest hit of a ray is the same whatever tree it walks
 // (rtw_trace.h: every primitive is reached through its own box; ties go to the lowest reference).
@@ -115,18 +116,99 @@ struct LbvhTree {
     const uint32_t* order;      // sorted position -> leaf index
     const int* left; const int* right;
     const LbvhBox* ibox;        // box of every internal node
-    const uint32_t* wide_index; // exclusive scan of the wide flags: internal node -> position among the level's wide nodes
     uint32_t node_base;         // index of the level's first wide node in Scene::nodes / nodes16
 };
 RTW_HD LbvhBox lbvh_child_box(const LbvhTree& t, int c) {
     return c < 0 ? lbvh_leaf_box(t.leaves[t.order[~c]]) : t.ibox[c];
 }
 
-// depth of internal node i (root = 0) by walking the parent links
-RTW_HD uint32_t lbvh_depth(const int* parent_internal, int i) {
-    uint32_t d = 0;
-    for (int p = parent_internal[i]; p >= 0; p = parent_internal[p]) ++d;
-    return d;
+// Loads of what another thread of the same kernel has written (the fit step): past the non-coherent L1 on the device.
+#if defined(__CUDA_ARCH__)
+#define RTW_LBVH_LD(p) __ldcg(p)
+#else
+#define RTW_LBVH_LD(p) (*(p))
+#endif
+
+RTW_HD float lbvh_half_area(const LbvhBox& b) {
+    const float dx = b.hi[0] - b.lo[0], dy = b.hi[1] - b.lo[1], dz = b.hi[2] - b.lo[2];
+    return dx * dy + dy * dz + dz * dx;
+}
+
+// The binary tree while it is being fitted: links and boxes are written by the thread that owns the subtree.
+struct LbvhBuild {
+    const LbvhLeaf* leaves; const uint32_t* order;
+    int* left; int* right; int* parent_i; int* parent_l;
+    LbvhBox* ibox;
+};
+RTW_HD LbvhBox lbvh_build_child_box(const LbvhBuild& b, int c) {
+    if (c < 0) return lbvh_leaf_box(b.leaves[b.order[~c]]);
+    LbvhBox r;
+    const float* f = reinterpret_cast<const float*>(&b.ibox[c]);
+    r.lo[0] = RTW_LBVH_LD(f + 0); r.lo[1] = RTW_LBVH_LD(f + 1); r.lo[2] = RTW_LBVH_LD(f + 2);
+    r.hi[0] = RTW_LBVH_LD(f + 3); r.hi[1] = RTW_LBVH_LD(f + 4); r.hi[2] = RTW_LBVH_LD(f + 5);
+    return r;
+}
+
+// Fit of internal node N, by the second thread to arrive there: every box below N is final and no other thread will
+// touch N's subtree again, so this thread may also restructure it. One tree rotation first (Kensler 2008): a child A of
+// N changes places with a grandchild G on the other side (child of B) when that shrinks B's box — the Morton order
+// pairs leaves by the bits of their centres, not by their extent, and the bottom-up pass undoes the worst of it
+// (node visits per ray against the host SAH tree, tools/lbvh_quality.py: C5 1.31 -> 1.17, C2 1.24 -> 1.13). The largest
+// gain of the four candidates wins, ties and NaN boxes leave the tree alone. Then N's box.
+RTW_HD void lbvh_fit_node(const LbvhBuild& b, int N) {
+    int ch[2] = {RTW_LBVH_LD(&b.left[N]), RTW_LBVH_LD(&b.right[N])};
+    LbvhBox cb[2] = {lbvh_build_child_box(b, ch[0]), lbvh_build_child_box(b, ch[1])};
+    int gc[2][2] = {{0, 0}, {0, 0}}; LbvhBox gb[2][2];
+    float best_gain = 0.0f; int bs = -1, bg = -1;
+    for (int s = 0; s < 2; ++s) {                    // A = ch[s] against the children of B = ch[1 - s]
+        const int B = ch[1 - s];
+        if (B < 0) continue;
+        gc[s][0] = RTW_LBVH_LD(&b.left[B]); gc[s][1] = RTW_LBVH_LD(&b.right[B]);
+        gb[s][0] = lbvh_build_child_box(b, gc[s][0]); gb[s][1] = lbvh_build_child_box(b, gc[s][1]);
+        const float area_b = lbvh_half_area(cb[1 - s]);
+        for (int g = 0; g < 2; ++g) {                // grandchild g goes up, the other one stays and is joined by A
+            const float gain = area_b - lbvh_half_area(lbvh_union(cb[s], gb[s][1 - g]));
+            if (gain > best_gain) { best_gain = gain; bs = s; bg = g; }
+        }
+    }
+    if (bs >= 0) {
+        const int A = ch[bs], B = ch[1 - bs], G = gc[bs][bg];
+        if (bg == 0) b.left[B] = A; else b.right[B] = A;
+        if (bs == 0) b.left[N] = G; else b.right[N] = G;
+        if (A < 0) b.parent_l[~A] = B; else b.parent_i[A] = B;
+        if (G < 0) b.parent_l[~G] = N; else b.parent_i[G] = N;
+        const LbvhBox nb = lbvh_union(cb[bs], gb[bs][1 - bg]);
+        b.ibox[B] = nb;
+        cb[bs] = gb[bs][bg]; cb[1 - bs] = nb;
+    }
+    b.ibox[N] = lbvh_union(cb[0], cb[1]);
+}
+
+#ifndef LBVH_FIT_PASSES
+#define LBVH_FIT_PASSES 2      // bottom-up passes of lbvh_fit_node over the tree (each one more round of rotations)
+#endif
+
+// The children of the wide node that stands for binary node i: the two children of i, then, while a slot is free,
+// the internal candidate with the largest box is replaced by its own two children (the child most rays would enter
+// anyway: opening it saves them a node step; ties go to the first). Returns their number (2..4); a candidate >= 0
+// is an internal node that becomes a wide node of its own, < 0 is the sorted leaf ~c.
+RTW_HD int lbvh_pick(const LbvhTree& t, int i, int cand[4]) {
+    int n = 2;
+    cand[0] = t.left[i]; cand[1] = t.right[i];
+    while (n < 4) {
+        int best = -1; float best_area = -1.0f;
+        for (int k = 0; k < n; ++k)
+            if (cand[k] >= 0) {
+                const float a = lbvh_half_area(t.ibox[cand[k]]);
+                if (a > best_area) { best_area = a; best = k; }     // NaN boxes never win; a lone NaN candidate stays closed
+            }
+        if (best < 0) break;
+        const int c = cand[best];
+        for (int k = n; k > best + 1; --k) cand[k] = cand[k - 1];   // the two children take the place of their parent
+        cand[best] = t.left[c]; cand[best + 1] = t.right[c];
+        ++n;
+    }
+    return n;
 }
 
 #if defined(__CUDACC__) || defined(RTW_LBVH_HOST_FP16)
@@ -137,16 +219,10 @@ RTW_HD uint32_t lbvh_half2_ru(float a, float b) {   // ... towards +inf
     return (uint32_t)__half_as_ushort(__float2half_ru(a)) | ((uint32_t)__half_as_ushort(__float2half_ru(b)) << 16);
 }
 
-// Wide node of internal node i (even depth): its children are the children of i, with an internal
-// child replaced by that child's two children. Writes both node formats at node_base + wide_index[i].
-RTW_HD void lbvh_emit(const LbvhTree& t, int i, Node* nodes, Node16* nodes16) {
-    int cand[4]; int n = 0;
-    const int two[2] = {t.left[i], t.right[i]};
-    for (int k = 0; k < 2; ++k) {
-        const int c = two[k];
-        if (c < 0) cand[n++] = c;
-        else { cand[n++] = t.left[c]; cand[n++] = t.right[c]; }
-    }
+// Writes the wide node `me` of the level (both node formats) over the candidates lbvh_pick chose; child_pos[k] is the
+// position among the level's wide nodes that internal candidate k was given.
+RTW_HD void lbvh_emit(const LbvhTree& t, const int cand[4], int n, const uint32_t child_pos[4], uint32_t me_pos, Node* nodes,
+                      Node16* nodes16) {
     const float inf = INFINITY;
     float lo[3][4], hi[3][4]; uint32_t ref[4];
     for (int k = 0; k < 4; ++k) {
@@ -154,13 +230,13 @@ RTW_HD void lbvh_emit(const LbvhTree& t, int i, Node* nodes, Node16* nodes16) {
             const int c = cand[k];
             const LbvhBox b = lbvh_child_box(t, c);
             for (int a = 0; a < 3; ++a) { lo[a][k] = b.lo[a]; hi[a][k] = b.hi[a]; }
-            ref[k] = c < 0 ? t.leaves[t.order[~c]].ref : make_ref(KIND_NODE, t.node_base + t.wide_index[c]);
+            ref[k] = c < 0 ? t.leaves[t.order[~c]].ref : make_ref(KIND_NODE, t.node_base + child_pos[k]);
         } else {
             for (int a = 0; a < 3; ++a) { lo[a][k] = inf; hi[a][k] = inf; }
             ref[k] = REF_NONE;
         }
     }
-    const uint32_t me = t.node_base + t.wide_index[i];
+    const uint32_t me = t.node_base + me_pos;
     Node& nd = nodes[me];
     nd.lox = make_float4(lo[0][0], lo[0][1], lo[0][2], lo[0][3]); nd.loy = make_float4(lo[1][0], lo[1][1], lo[1][2], lo[1][3]);
     nd.loz = make_float4(lo[2][0], lo[2][1], lo[2][2], lo[2][3]); nd.hix = make_float4(hi[0][0], hi[0][1], hi[0][2], hi[0][3]);
@@ -178,7 +254,7 @@ RTW_HD void lbvh_emit(const LbvhTree& t, int i, Node* nodes, Node16* nodes16) {
 }
 #endif
 
-// Stack words a walk below a level built this way can need: three siblings per wide level.
-RTW_HD uint32_t lbvh_pushes(uint32_t max_binary_depth) { return 3u * (max_binary_depth / 2u + 1u); }
+// Stack words a walk below a level built this way can need: three siblings per wide node on the way down.
+RTW_HD uint32_t lbvh_pushes(uint32_t wide_depth) { return 3u * wide_depth; }
 
 }  // namespace rtw

@@ -7,16 +7,16 @@ namespace rtw {
 
 struct LbvhLevelOut {      // what a level's build reports back (device memory, read after the stream syncs)
     float lo[3]; uint32_t root;
-    float hi[3]; uint32_t max_depth;     // deepest leaf of the binary tree (root's children = 1)
+    float hi[3]; uint32_t max_depth;     // wide nodes on the longest way down (lbvh_pushes takes it)
 };
 
 struct LbvhScratch {       // device scratch, grown to the largest level seen and reused across rebuilds
     uint32_t *codes = nullptr, *codes_sorted = nullptr, *order_in = nullptr, *order = nullptr;
     int *left = nullptr, *right = nullptr, *parent_i = nullptr, *parent_l = nullptr;
     LbvhBox* ibox = nullptr;
-    uint32_t *flag = nullptr, *wide = nullptr, *wide_index = nullptr;
+    uint32_t* flag = nullptr;
+    int* queue = nullptr;
     float* cb = nullptr;
-    uint32_t* max_depth = nullptr;
     void* cub_tmp = nullptr;
     size_t n_codes = 0, cub_bytes = 0;
     ~LbvhScratch();

@@ -40,28 +40,37 @@ static void lbvh_rebuild_host(HostScene& hs) {
         std::vector<uint32_t> flag(n - 1, 0u);
         LbvhTree t; t.leaves = leaves; t.order = order.data(); t.left = left.data(); t.right = right.data();
         t.ibox = ibox.data();
-        for (int p = 0; p < n; ++p)
-            for (int cur = parent_l[p]; cur >= 0; cur = parent_i[cur]) {
-                if (flag[cur]++ == 0u) break;
-                ibox[cur] = lbvh_union(lbvh_child_box(t, left[cur]), lbvh_child_box(t, right[cur]));
-            }
-        std::vector<uint32_t> wide(n - 1), wide_index(n - 1);
-        uint32_t max_depth = 0, run = 0;
-        for (int i = 0; i < n - 1; ++i) {
-            uint32_t dpt = lbvh_depth(parent_i.data(), i);
-            wide[i] = (dpt & 1u) ? 0u : 1u;
-            max_depth = std::max(max_depth, dpt + 1u);
+        LbvhBuild bt; bt.leaves = leaves; bt.order = order.data(); bt.left = left.data(); bt.right = right.data();
+        bt.parent_i = parent_i.data(); bt.parent_l = parent_l.data(); bt.ibox = ibox.data();
+        for (int pass = 0; pass < LBVH_FIT_PASSES; ++pass) {
+            std::fill(flag.begin(), flag.end(), 0u);
+            for (int p = 0; p < n; ++p)
+                for (int cur = parent_l[p]; cur >= 0; cur = parent_i[cur]) {
+                    if (flag[cur]++ == 0u) break;
+                    lbvh_fit_node(bt, cur);
+                }
         }
-        for (int i = 0; i < n - 1; ++i) { wide_index[i] = run; run += wide[i]; }
-        t.wide_index = wide_index.data();
+        // breadth-first collapse: queue position = position among the level's wide nodes (the binary root is wide node 0)
         t.node_base = (uint32_t)hs.nodes.size();
-        hs.nodes.resize(hs.nodes.size() + run); hs.nodes16.resize(hs.nodes.size());
-        for (int i = 0; i < n - 1; ++i) if (wide[i]) lbvh_emit(t, i, hs.nodes.data(), hs.nodes16.data());
+        hs.nodes.resize(hs.nodes.size() + (size_t)(n - 1)); hs.nodes16.resize(hs.nodes.size());
+        std::vector<int> queue(1, 0);
+        uint32_t wide_depth = 0;
+        for (size_t head = 0; head < queue.size();) {
+            const size_t level_end = queue.size();
+            ++wide_depth;
+            for (; head < level_end; ++head) {
+                int cand[4]; uint32_t pos[4] = {0u, 0u, 0u, 0u};
+                const int nc = lbvh_pick(t, queue[head], cand);
+                for (int k = 0; k < nc; ++k) if (cand[k] >= 0) { pos[k] = (uint32_t)queue.size(); queue.push_back(cand[k]); }
+                lbvh_emit(t, cand, nc, pos, (uint32_t)head, hs.nodes.data(), hs.nodes16.data());
+            }
+        }
+        hs.nodes.resize(t.node_base + queue.size()); hs.nodes16.resize(hs.nodes.size());
         Level& L = lv.owner == -1 ? hs.top : lv.owner == -2 ? hs.top_inside : lv.owner == -3 ? hs.top_baked
                    : lv.owner == -4 ? hs.top_baked_inside : hs.instances[lv.owner].level;
         L.root = make_ref(KIND_NODE, t.node_base);
         for (int a = 0; a < 3; ++a) { L.lo[a] = ibox[0].lo[a]; L.hi[a] = ibox[0].hi[a]; }
-        const uint32_t pushes = lbvh_pushes(max_depth);
+        const uint32_t pushes = lbvh_pushes(wide_depth);
         if (lv.owner < 0) top_depth = std::max(top_depth, pushes); else inner_depth = std::max(inner_depth, pushes);
     }
     hs.top_depth = top_depth; hs.inner_depth = inner_depth;
@@ -82,6 +91,9 @@ extern "C" int emu_render_ex(const rtw_scene_desc* d, const rtw_camera* cam, con
     if (info) *info = hs.info;
     Scene sc = hs.host_view();
     if ((use_lbvh & 2) && hs.has_baked) sc.top = hs.top_baked;     // the top level with baked instances (rtw_host.h), as the fast kernels walk it
+    // bit 2 (tools/lbvh_quality.py only): the top level without the enclosing volumes, which is what the kernels walk
+    // when the camera sits inside all of them (rtw_api.cu); the volumes themselves are then missing from the image
+    if ((use_lbvh & 4) && !hs.enclosing.empty()) sc.top = ((use_lbvh & 2) && hs.has_baked) ? hs.top_baked_inside : hs.top_inside;
     RenderParams P; uint32_t total = 0;
     rc = make_render_params(cam, o, P, total, err);
     if (rc) { std::fprintf(stderr, "emu: %s\n", err.c_str()); return rc; }

@@ -44,6 +44,24 @@ def test_lbvh_steps_on_host_give_the_same_image(name):
     assert np.array_equal(a, b, equal_nan=True)
 
 
+@pytest.mark.parametrize("name,bound", [("C5", 1.20), ("C2", 1.18)])
+def test_lbvh_walk_cost_against_the_sah_tree(name, bound):
+    """Node visits per ray through the rebuilt levels against the host SAH levels, counted by the instrumented
+    traversal on the level the kernels walk for this camera (no enclosing volumes, baked instances). The plain
+    Karras tree with the fixed two-level collapse of round 1 stood at 1.38 (C5) / 1.41 (C2); rotations in the fit
+    and the largest-child-first collapse bring it to 1.15 / 1.12 (tools/lbvh_quality.py)."""
+    from emu_backend import EmuBackend
+    per_ray = {}
+    for lbvh in (False, True):
+        job = _small(ALL[name](), 96, 96 * ALL[name]().viewport.height // ALL[name]().viewport.width, 2)
+        be = EmuBackend(lbvh=lbvh, baked=True, inside=True)
+        job.viewport._run(job.ray_color, job.scene, job.mode, be)
+        st = be.scene(job.scene).stats()
+        per_ray[lbvh] = (st["nodes"] / st["rays"], st["rays"])
+    assert per_ray[True][1] == per_ray[False][1]
+    assert per_ray[True][0] <= bound * per_ray[False][0], per_ray
+
+
 def test_karras_tree_is_a_tree():
     """Structural check of lbvh_karras through the emulator's build: covered implicitly by the renders
     above; here the degenerate inputs — all leaves at one point (equal Morton codes) — still render."""
