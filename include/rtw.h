@@ -179,8 +179,10 @@ enum {
      * sequence rustc emits for the reference (parity runs). Default: nvcc's FFMA contraction. */
     RTW_FLAG_STRICT_FP = 1u,
     /* Pipeline choice. Default (neither flag): the wavefront pipeline (extend / shade kernels over
-     * path queues in HBM) for renders of at least 2^18 paths, the single persistent-lane megakernel
-     * below that. The flags force one or the other. */
+     * path queues in HBM) for renders of at least 2^24 paths of a scene with a tree to walk; the single
+     * persistent-lane megakernel below that, and at any size for a scene whose top level is at most eight
+     * primitives with no instance level below (measured rule: rtw_api.cu wavefront_pays). The flags
+     * force one or the other. */
     RTW_FLAG_WAVEFRONT = 2u,
     RTW_FLAG_MEGAKERNEL = 8u,
     /* Use the instrumented build of the fast kernels, which also counts BVH node visits and
@@ -280,7 +282,7 @@ int rtw_render(rtw_scene* scene, const rtw_camera* cam, const rtw_render_opts* o
 /* Same, but `d_out_rgb` is DEVICE memory on the scene's device and `stream` a cudaStream_t
  * (0 = default stream). All work is enqueued on `stream` and the call does not synchronise it, so a
  * collective or copy enqueued behind it on the same stream is ordered after the frame. The call is
- * NOT asynchronous for renders of 2^18 paths or more (the wavefront pipeline): its host loop reads the
+ * NOT asynchronous for renders that take the wavefront pipeline (see RTW_FLAG_WAVEFRONT): its host loop reads the
  * live-path count of finished iteration batches from pinned memory and keeps launching until the
  * frame has drained, i.e. it blocks the calling thread for almost the whole frame (the megakernel
  * path returns right after its one launch). Stats of this call become valid after the stream syncs.

@@ -263,6 +263,9 @@ struct rtw_scene {
     std::vector<Level> sah_inst_levels;       // per instance
     Level sah_tops[4] = {};
     uint32_t sah_top_depth = 0, sah_inner_depth = 0, n_sah_nodes = 0;
+    uint32_t sah_fast_top_depth = 0, sah_fast_inner_depth = 0;   // the same for what the fast kernels walk (HostScene)
+    bool fast_levels = false, any_levels = false;
+    std::vector<uint8_t> inst_baked;
     uint32_t sah_stack_words[2] = {0, 0};
     LbvhLeaf* lb_leaves_d = nullptr;
     Node* lb_nodes = nullptr; Node16* lb_nodes16 = nullptr;
@@ -388,9 +391,16 @@ int upload_scene(rtw_scene* s, HostScene& hs) {
     s->sah_inst_levels.resize(hs.instances.size());
     for (size_t k = 0; k < hs.instances.size(); ++k) s->sah_inst_levels[k] = hs.instances[k].level;
     s->sah_top_depth = hs.top_depth; s->sah_inner_depth = hs.inner_depth; s->n_sah_nodes = (uint32_t)hs.nodes.size();
+    s->sah_fast_top_depth = hs.fast_top_depth; s->sah_fast_inner_depth = hs.fast_inner_depth;
+    s->fast_levels = hs.fast_levels; s->any_levels = hs.any_levels; s->inst_baked = hs.inst_baked;
     std::memcpy(d.background, hs.background, sizeof d.background);
     d.n_noises = (uint32_t)hs.noises.size();
     return RTW_OK;
+}
+
+uint32_t env_u32(const char* name, uint32_t dflt) {
+    const char* e = std::getenv(name);
+    return e ? (uint32_t)std::strtoul(e, nullptr, 10) : dflt;
 }
 
 // Work decomposition (see MegaLaunch): enough items to balance, chunks short enough that the tail
@@ -422,7 +432,8 @@ MegaLaunch plan_mega(const rtw_scene* s, const RenderParams& P, int variant) {
     if (want_chunks < 1) want_chunks = 1;
     if (want_chunks > P.sample_count) want_chunks = P.sample_count;
     uint32_t chunk = (uint32_t)((P.sample_count + want_chunks - 1) / want_chunks);
-    if (chunk > 256u) chunk = 256u;
+    static const uint32_t chunk_max = std::max(1u, env_u32("RTW_MEGA_CHUNK_MAX", 256u));   // (tuning)
+    if (chunk > chunk_max) chunk = chunk_max;
     if (chunk < 1u) chunk = 1u;
     L.chunk = chunk;
     L.n_chunks = (P.sample_count + chunk - 1u) / chunk;
@@ -432,21 +443,21 @@ MegaLaunch plan_mega(const rtw_scene* s, const RenderParams& P, int variant) {
     return L;
 }
 
-uint32_t env_u32(const char* name, uint32_t dflt) {
-    const char* e = std::getenv(name);
-    return e ? (uint32_t)std::strtoul(e, nullptr, 10) : dflt;
-}
 
-// Which pipeline a render takes when the caller names none. The wavefront pipeline buys coherence — every warp runs one
-// kind of step with most of its lanes — and pays for it with a path record that crosses HBM twice per ray (56 B) and two
-// launches per bounce. That pays where there is a tree to walk. A scene whose top level is a handful of primitives and
-// nothing below (C1: five spheres, C3: four) is one node fetch and one or two leaf tests per ray: the megakernel's lanes
-// stay in step by themselves and it keeps the path in registers (profiles/r2q_mega_vs_wavefront.txt, r2r_crossover.txt:
-// C1 3.0x, C3 1.35x for the megakernel; C2 1.05x, C4 1.34x, C5 2.0x for the wavefront pipeline). Short renders take
-// the megakernel whatever the scene: the pipeline's ramp and drain (about 2 x depth iterations over a mostly dead pool)
-// would be most of the frame. RTW_WF_MIN_PATHS / RTW_MEGA_FLAT_LEAVES move the two thresholds (tuning only).
+// Which pipeline a render takes when the caller names none (profiles/r2r_crossover.txt: both pipelines forced on every
+// config from 0.1 M to 200 M paths). The wavefront pipeline buys coherence — every warp runs one kind of step with most
+// of its lanes — and pays for it with a path record that crosses HBM twice per ray (56 B), two launches per bounce and a
+// ramp and a drain of about 2 x depth iterations over a mostly dead pool: 4-20 ms per frame that the megakernel, one
+// launch with the paths in registers, does not have. So:
+//  * a render below 2^24 paths takes the megakernel (C5 at 10 M paths: 13.8 ms against 21.5; C2 at 0.8 M: 0.58 against
+//    4.5 ms; the wavefront pipeline leads from 23 M paths on C4 and 41 M on C5, and on C2 only ties at 200 M);
+//  * a scene whose top level is a handful of primitives with nothing below (C1: five spheres, C3: four) takes it at any
+//    size: one node fetch and one or two leaf tests per ray keep the megakernel's lanes in step by themselves (C1 at
+//    23 M paths 4 681 against 2 198 Mpaths/s, C3 at 92 M 4 741 against 2 647, C3 at its full 360 M 4 807 against 3 556);
+//  * everything else takes the wavefront pipeline (C5 at 164 M paths 1 576 against 860 Mpaths/s, at 6.4 G 1 990).
+// RTW_WF_MIN_PATHS / RTW_MEGA_FLAT_LEAVES move the two thresholds (tuning only).
 bool wavefront_pays(const rtw_scene* s, uint64_t n_paths) {
-    static const uint64_t min_paths = env_u32("RTW_WF_MIN_PATHS", 1u << 18);
+    static const uint64_t min_paths = env_u32("RTW_WF_MIN_PATHS", 1u << 24);
     static const uint32_t flat_leaves = env_u32("RTW_MEGA_FLAT_LEAVES", 8u);
     if (n_paths < min_paths) return false;
     const bool flat = s->info.n_tlas_leaves <= flat_leaves && s->info.n_blas_nodes == 0u && s->info.n_baked_instances == 0u;
@@ -821,13 +832,15 @@ int rtw_quantize_device(const float* d_rgb, uint8_t* d_rgb8, uint64_t n_values, 
 }
 
 namespace {
-// stack depth, shared-memory size and the occupancies that depend on it
-int refresh_launch_limits(rtw_scene* s, uint32_t top_depth, uint32_t inner_depth) {
-    const uint32_t words = stack_words(top_depth, inner_depth);
-    if (words > 160u) return fail(RTW_E_UNSUPPORTED, "BVH deeper than the traversal stack");
-    // rebuilt levels: one bound for both kernel families (the optional LBVH path is not tuned per family)
-    s->stack_words[0] = s->stack_words[1] = words;
-    s->smem_bytes[0] = s->smem_bytes[1] = (size_t)words * RTW_MEGA_BLOCK * sizeof(uint32_t);
+// stack depth, shared-memory size and the occupancies that depend on it, per kernel family as at scene creation:
+// depth[0] = {top, inner} of what the fast kernels walk, depth[1] = of the reference's structure
+int refresh_launch_limits(rtw_scene* s, const uint32_t depth[2][2]) {
+    uint32_t words[2];
+    words[1] = s->any_levels ? stack_words(depth[1][0], depth[1][1]) : stack_words_flat(depth[1][0]);
+    words[0] = s->fast_levels ? stack_words(depth[0][0], depth[0][1]) : stack_words_flat(depth[0][0]);
+    if (words[0] > words[1]) words[0] = words[1];
+    if (words[1] > 160u) return fail(RTW_E_UNSUPPORTED, "BVH deeper than the traversal stack");
+    for (int k = 0; k < 2; ++k) { s->stack_words[k] = words[k]; s->smem_bytes[k] = (size_t)words[k] * RTW_MEGA_BLOCK * sizeof(uint32_t); }
     int rc = refresh_mega_occupancy(s);
     if (rc) return rc;
     if (s->d_wc && (rc = refresh_wf_occupancy(s))) return rc;
@@ -887,14 +900,25 @@ int rtw_scene_rebuild_lbvh(rtw_scene* s, float* out_build_ms) {
     CK(cudaMemcpyAsync(out.data(), s->lb_out_d, out.size() * sizeof(LbvhLevelOut), cudaMemcpyDeviceToHost, s->stream));
     CK(cudaStreamSynchronize(s->stream));
     if (out_build_ms) CK(cudaEventElapsedTime(out_build_ms, s->ev0, s->ev1));
-    // stack bound first: if the rebuilt trees are too deep the scene keeps walking the SAH levels
-    uint32_t top_depth = s->sah_top_depth, inner_depth = s->sah_inner_depth;
+    // stack bound first: if the rebuilt trees are too deep the scene keeps walking the SAH levels. Per kernel family,
+    // like the SAH levels' bound: the fast kernels walk the baked top levels (-3 / -4) when there are any and only the
+    // instances that were not baked — one bound for both families made C5's fast kernels carry 66-word stack columns
+    // instead of 34 through the rebuilt levels, and cost them 8 % (profiles/r2r_lbvh_vs_sah.txt against r2s).
+    uint32_t depth[2][2] = {{s->sah_fast_top_depth, s->sah_fast_inner_depth}, {s->sah_top_depth, s->sah_inner_depth}};
     for (size_t i = 0; i < s->lb_levels.size(); ++i) {
         if (s->lb_levels[i].count < 2u) continue;
         const uint32_t pushes = lbvh_pushes(out[i].max_depth);
-        if (s->lb_levels[i].owner < 0) top_depth = std::max(top_depth, pushes); else inner_depth = std::max(inner_depth, pushes);
+        const int32_t owner = s->lb_levels[i].owner;
+        if (owner < 0) {
+            const bool baked_top = owner <= -3;
+            depth[1][0] = std::max(depth[1][0], pushes);          // the strict kernels' bound covers every top level
+            if (baked_top == s->has_baked) depth[0][0] = std::max(depth[0][0], pushes);
+        } else {
+            depth[1][1] = std::max(depth[1][1], pushes);
+            if ((size_t)owner >= s->inst_baked.size() || !s->inst_baked[owner]) depth[0][1] = std::max(depth[0][1], pushes);
+        }
     }
-    int rc = refresh_launch_limits(s, top_depth, inner_depth);
+    int rc = refresh_launch_limits(s, depth);
     if (rc) return rc;
     for (size_t i = 0; i < s->lb_levels.size(); ++i) {
         const LbvhLevelDesc& lv = s->lb_levels[i];

@@ -64,6 +64,7 @@ struct HostScene {
     // that are still walked as levels there; fast_levels = is any instance walked as a level at all
     uint32_t fast_top_depth = 0, fast_inner_depth = 0;
     bool fast_levels = false, any_levels = false;
+    std::vector<uint8_t> inst_baked;           // per instance: baked into the fast kernels' top level (not walked as a level there)
 
     // A Scene whose pointers address the vectors above (host memory): what the CPU-side unit
     // tests of the traversal code walk. The product uploads the same arrays to the device.

@@ -37,11 +37,14 @@ __device__ __forceinline__ unsigned long long warp_sum_u64(unsigned long long v)
 
 // kLights: the instance that runs Rust2's light-biased integrators (shadow rays from inside segment_end: a second,
 // non-inlined traversal). It is a kernel of its own so that the other integrators keep the register allocation
-// they had without it (no stack frame, no spills).
+// they had without it (no stack frame, no spills). The plain instance is compiled for five resident blocks per SM: 96
+// registers, still without a spill, against the 128 it takes when left alone — 20 warps per SM instead of 16 for a
+// kernel that has no warp eligible on 42 % of its cycles (profiles/r2r_mega_kernel_C3_details.txt): C1 +7 %, C3 +9 %,
+// C2 +2.6 %, C5 at 41 M paths +13 % (profiles/r2s_ab_mega_resident_blocks.txt; six blocks = 80 registers with
+// spills and eight = 64 are slower again). The light instance spills more at 96 registers than at 128 and stays as it was.
 template <bool kLights>
-__global__ void __launch_bounds__(RTW_MEGA_BLOCK)
-mega_kernel(const Scene sc, const RenderParams P, float* __restrict__ sum, Counters* __restrict__ ctr,
-            uint32_t* __restrict__ work, const MegaLaunch L) {
+__device__ __forceinline__ void mega_body(const Scene& sc, const RenderParams& P, float* __restrict__ sum, Counters* __restrict__ ctr,
+                                          uint32_t* __restrict__ work, const MegaLaunch& L) {
     extern __shared__ uint32_t s_stack[];                 // [stack_words][RTW_MEGA_BLOCK]
     __shared__ Noise s_noise[RTW_SMEM_NOISES];
     __shared__ float s_acc[RTW_MEGA_BLOCK / 32][3][32];   // per warp: the tile's 32 pixel sums
@@ -166,6 +169,17 @@ mega_kernel(const Scene sc, const RenderParams P, float* __restrict__ sum, Count
         atomicAdd(&ctr->instances, w3); atomicAdd(&ctr->hits, w4);
     }
 #endif
+}
+
+__global__ void __launch_bounds__(RTW_MEGA_BLOCK, RTW_MEGA_MINB)
+mega_kernel(const Scene sc, const RenderParams P, float* __restrict__ sum, Counters* __restrict__ ctr,
+            uint32_t* __restrict__ work, const MegaLaunch L) {
+    mega_body<false>(sc, P, sum, ctr, work, L);
+}
+__global__ void __launch_bounds__(RTW_MEGA_BLOCK)
+mega_kernel_lights(const Scene sc, const RenderParams P, float* __restrict__ sum, Counters* __restrict__ ctr,
+                   uint32_t* __restrict__ work, const MegaLaunch L) {
+    mega_body<true>(sc, P, sum, ctr, work, L);
 }
 
 // =====================================================================================
@@ -654,9 +668,9 @@ wf_shade_kernel(const Scene sc, const RenderParams P, const WfPool pool, WfCount
 cudaError_t RTW_FN(launch_mega)(const Scene& sc, const RenderParams& P, float* d_sum, Counters* d_ctr,
                                 uint32_t* d_work, const MegaLaunch& L, cudaStream_t st) {
     if (light_integrator(P.integrator))
-        RTW_CAT(variant_, RTW_VARIANT)::mega_kernel<true><<<L.grid, L.block, L.smem_bytes, st>>>(sc, P, d_sum, d_ctr, d_work, L);
+        RTW_CAT(variant_, RTW_VARIANT)::mega_kernel_lights<<<L.grid, L.block, L.smem_bytes, st>>>(sc, P, d_sum, d_ctr, d_work, L);
     else
-        RTW_CAT(variant_, RTW_VARIANT)::mega_kernel<false><<<L.grid, L.block, L.smem_bytes, st>>>(sc, P, d_sum, d_ctr, d_work, L);
+        RTW_CAT(variant_, RTW_VARIANT)::mega_kernel<<<L.grid, L.block, L.smem_bytes, st>>>(sc, P, d_sum, d_ctr, d_work, L);
     return cudaGetLastError();
 }
 
@@ -698,13 +712,13 @@ cudaError_t RTW_FN(wf_extend_occupancy)(int* blocks_per_sm, size_t smem_bytes) {
 cudaError_t RTW_FN(mega_occupancy)(int* blocks_per_sm, size_t smem_bytes) {
     // both instances share one launch shape: the grid is sized for the one that fits fewer blocks (work is handed
     // out through a counter, so the other merely runs a few blocks short of its own maximum)
-    cudaError_t e = raise_smem_limit((const void*)RTW_CAT(variant_, RTW_VARIANT)::mega_kernel<false>, smem_bytes, 1);
-    if (e == cudaSuccess) e = raise_smem_limit((const void*)RTW_CAT(variant_, RTW_VARIANT)::mega_kernel<true>, smem_bytes, 2);
+    cudaError_t e = raise_smem_limit((const void*)RTW_CAT(variant_, RTW_VARIANT)::mega_kernel, smem_bytes, 1);
+    if (e == cudaSuccess) e = raise_smem_limit((const void*)RTW_CAT(variant_, RTW_VARIANT)::mega_kernel_lights, smem_bytes, 2);
     if (e != cudaSuccess) return e;
     int plain = 0, lights = 0;
-    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&plain, RTW_CAT(variant_, RTW_VARIANT)::mega_kernel<false>, RTW_MEGA_BLOCK, smem_bytes);
+    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&plain, RTW_CAT(variant_, RTW_VARIANT)::mega_kernel, RTW_MEGA_BLOCK, smem_bytes);
     if (e == cudaSuccess)
-        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&lights, RTW_CAT(variant_, RTW_VARIANT)::mega_kernel<true>, RTW_MEGA_BLOCK, smem_bytes);
+        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&lights, RTW_CAT(variant_, RTW_VARIANT)::mega_kernel_lights, RTW_MEGA_BLOCK, smem_bytes);
     *blocks_per_sm = plain < lights ? plain : lights;
     return e;
 }

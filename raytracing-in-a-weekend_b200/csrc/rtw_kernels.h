@@ -143,6 +143,9 @@ struct WfLaunch {
 #define RTW_WF_SHADE_BLOCK 128
 
 #define RTW_MEGA_BLOCK 128
+#ifndef RTW_MEGA_MINB
+#define RTW_MEGA_MINB 5        // resident blocks per SM the plain megakernel's register allocation aims at (96 registers)
+#endif
 #define RTW_SMEM_NOISES 2
 
 #define RTW_DECLARE_VARIANT(SUFFIX)                                                                          \

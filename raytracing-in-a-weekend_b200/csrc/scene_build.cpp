@@ -873,6 +873,7 @@ int build_host_scene(const rtw_scene_desc* d, HostScene& hs, std::string& err) {
     hs.info.n_blas_nodes = (uint32_t)hs.nodes.size() - blas_nodes_before;
     hs.info.n_flattened_instances = n_flat;
     for (char b : inst_baked) hs.info.n_baked_instances += b ? 1u : 0u;
+    hs.inst_baked.assign(inst_baked.begin(), inst_baked.end());
     hs.info.bvh_max_depth = top_depth + inner_depth;
     hs.top_depth = top_depth; hs.inner_depth = inner_depth;
     hs.any_levels = hs.n_walked_instances > 0;

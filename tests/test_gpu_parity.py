@@ -256,15 +256,16 @@ def test_scene_memory_reuse_is_invisible(cuda):
             lib.rtw_scene_destroy(hd)
         return out
 
-    c5 = lambda: _small(ALL["C5"](), 256, 256, spp=6)          # 393 216 paths: the wavefront pipeline and its pool
+    c5 = lambda: _small(ALL["C5"](), 256, 256, spp=6)          # 393 216 paths through the wavefront pipeline and its pool
     c4 = lambda: _small(ALL["C4_smoke"](), 300, 300, spp=4)
     c2 = lambda: _small(ALL["C2"](), 200, 120, spp=2)          # the megakernel
+    WF = A.RTW_FLAG_WAVEFRONT                                  # (renders this small take the megakernel by default)
     for flags in (A.RTW_FLAG_STRICT_FP, 0):
         A.check(lib.rtw_trim_memory(-1))
-        first = one(c5(), flags)
-        for other in (c4, c2, c4):
-            one(other(), flags)
-        again = one(c5(), flags)
+        first = one(c5(), flags | WF)
+        for other, pipe in ((c4, WF), (c2, 0), (c4, WF)):
+            one(other(), flags | pipe)
+        again = one(c5(), flags | WF)
         assert np.allclose(first, again, rtol=1e-5, atol=1e-6, equal_nan=True)
     A.check(lib.rtw_trim_memory(cuda.device))
-    assert np.allclose(one(c5(), 0), again, rtol=1e-5, atol=1e-6, equal_nan=True)
+    assert np.allclose(one(c5(), WF), again, rtol=1e-5, atol=1e-6, equal_nan=True)

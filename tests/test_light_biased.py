@@ -137,7 +137,7 @@ def test_cuda_matches_the_oracle_sample_for_sample(cast, oracle, cuda):
 
 @pytest.mark.gpu
 def test_cuda_fast_build_and_pipeline_choice(cuda):
-    job = scenes.light_biased_test(False, 320, 240, 64)                   # 4.9 M paths: would be a wavefront render
+    job = scenes.light_biased_test(False, 320, 240, 64)                   # 4.9 M paths (the light integrators take the megakernel at any size)
     vp = job.viewport
     vp.gamma = 1.0
     vp.flags = A.RTW_FLAG_STRICT_FP

@@ -50,7 +50,7 @@ def _job(name, w, h, spp):
 def test_sample_split_equals_one_device(name, w, h, spp, pipe, flags, cuda):
     job = _job(name, w, h, spp)
     vp = job.viewport
-    vp.flags = flags | pipe          # the pipeline is pinned: a share of the frame may fall below the 2^18-path switch
+    vp.flags = flags | pipe          # the pipeline is pinned: a share of the frame may fall below the size where the default switches
     cam, o = vp.camera(cuda), vp.opts(job.ray_color, job.mode)
     one = cuda.scene(job.scene).render(cam, o)
     st1 = cuda.scene(job.scene).stats()
@@ -90,8 +90,8 @@ def test_more_shares_than_samples(cuda):
 def test_tile_split_equals_one_device(name, w, h, spp, band, cuda):
     """Row bands dealt round-robin (C4 "tiles across 8 GPUs"): each band is rendered and resolved by
     one device and lands in its place in the host image: the frame equals the one-device frame path for path.
-    (Bands that fall below 2^18 paths take the megakernel, the full frame the wavefront pipeline; the comparison
-    pins the pipeline.)"""
+    (The default pipeline depends on the render's size, and a band is smaller than the frame: the comparison pins
+    the pipeline.)"""
     job = _job(name, w, h, spp)
     vp = job.viewport
     vp.flags = A.RTW_FLAG_MEGAKERNEL
@@ -136,11 +136,12 @@ def test_back_to_back_device_renders_on_one_scene(cuda):
     sharding.py and rtw_render_multi do): the second wavefront render must not inherit the first one's counters
     (round-1 advisor finding: the counters were seeded from a pinned ring slot a pending copy could overwrite)."""
     torch = pytest.importorskip("torch")
-    job = _job("C5", 512, 512, 2)                                   # 256 rows x 512 x 2 spp = 2^18 paths per band: wavefront
+    job = _job("C5", 512, 512, 2)                                   # 256 rows x 512 x 2 spp = 2^18 paths per band, through the wavefront pipeline
     vp = job.viewport
     cam = vp.camera(cuda)
     h = cuda.scene(job.scene)
     o = vp.opts(job.ray_color, job.mode)
+    o.flags |= A.RTW_FLAG_WAVEFRONT                                 # the reference frame through the same pipeline as the bands
     whole = h.render(cam, o)
     dev = torch.device("cuda", torch.cuda.current_device())
     for rep in range(3):
