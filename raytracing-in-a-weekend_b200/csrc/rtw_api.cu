@@ -249,7 +249,7 @@ struct rtw_scene {
     // instance levels at all), [1] the reference's structure (strict kernels, RTW_NO_BAKE, rebuilt LBVH levels)
     uint32_t stack_words[2] = {0, 0};
     size_t smem_bytes[2] = {0, 0};
-    int occ_mega[3][2] = {};              // [variant][stack kind]
+    int occ_mega[3][2][2] = {};           // [variant][stack kind][plain / light-biased instance]
     int cur_stack = 1;                    // stack kind of the current render
     Scene d{};                            // device pointers
     Scene d_cur{};                        // what the current render walks: d, or d with top = top_inside
@@ -418,7 +418,7 @@ uint32_t refill_below_default() {
 MegaLaunch plan_mega(const rtw_scene* s, const RenderParams& P, int variant) {
     MegaLaunch L;
     L.block = RTW_MEGA_BLOCK;
-    int occ = s->occ_mega[variant][s->cur_stack];
+    int occ = s->occ_mega[variant][s->cur_stack][light_integrator(P.integrator) ? 1 : 0];
     if (occ < 1) occ = 1;
     L.grid = s->sm_count * occ;
     L.stack_words = s->stack_words[s->cur_stack];
@@ -432,7 +432,10 @@ MegaLaunch plan_mega(const rtw_scene* s, const RenderParams& P, int variant) {
     if (want_chunks < 1) want_chunks = 1;
     if (want_chunks > P.sample_count) want_chunks = P.sample_count;
     uint32_t chunk = (uint32_t)((P.sample_count + want_chunks - 1) / want_chunks);
-    static const uint32_t chunk_max = std::max(1u, env_u32("RTW_MEGA_CHUNK_MAX", 256u));   // (tuning)
+    // at most 128 samples of a tile per item: C3 at 1 000 spp 5 240 -> 5 606 Mpaths/s against the 256 of before (its tiles
+    // differ in cost and four items per tile left the frame's tail unbalanced; 64: 5 554, 32: 5 422, 16: 5 171; the
+    // other configs do not move: profiles/r2u_ab_mega_chunk.txt)
+    static const uint32_t chunk_max = std::max(1u, env_u32("RTW_MEGA_CHUNK_MAX", 128u));
     if (chunk > chunk_max) chunk = chunk_max;
     if (chunk < 1u) chunk = 1u;
     L.chunk = chunk;
@@ -468,9 +471,9 @@ bool wavefront_pays(const rtw_scene* s, uint64_t n_paths) {
 // cudaFuncAttributeMaxDynamicSharedMemorySize the queries set must end up covering every launch.
 int refresh_mega_occupancy(rtw_scene* s) {
     for (int k = 0; k < 2; ++k) {          // stack_words[0] <= stack_words[1]
-        CK(mega_occupancy_fast(&s->occ_mega[0][k], s->smem_bytes[k]));
-        CK(mega_occupancy_strict(&s->occ_mega[1][k], s->smem_bytes[k]));
-        CK(mega_occupancy_count(&s->occ_mega[2][k], s->smem_bytes[k]));
+        CK(mega_occupancy_fast(s->occ_mega[0][k], s->smem_bytes[k]));
+        CK(mega_occupancy_strict(s->occ_mega[1][k], s->smem_bytes[k]));
+        CK(mega_occupancy_count(s->occ_mega[2][k], s->smem_bytes[k]));
     }
     return RTW_OK;
 }

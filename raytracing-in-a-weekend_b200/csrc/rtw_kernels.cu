@@ -710,16 +710,13 @@ cudaError_t RTW_FN(wf_extend_occupancy)(int* blocks_per_sm, size_t smem_bytes) {
 }
 
 cudaError_t RTW_FN(mega_occupancy)(int* blocks_per_sm, size_t smem_bytes) {
-    // both instances share one launch shape: the grid is sized for the one that fits fewer blocks (work is handed
-    // out through a counter, so the other merely runs a few blocks short of its own maximum)
+    // blocks_per_sm[0]: the plain instance, [1]: the light-biased one (their register counts differ)
     cudaError_t e = raise_smem_limit((const void*)RTW_CAT(variant_, RTW_VARIANT)::mega_kernel, smem_bytes, 1);
     if (e == cudaSuccess) e = raise_smem_limit((const void*)RTW_CAT(variant_, RTW_VARIANT)::mega_kernel_lights, smem_bytes, 2);
     if (e != cudaSuccess) return e;
-    int plain = 0, lights = 0;
-    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&plain, RTW_CAT(variant_, RTW_VARIANT)::mega_kernel, RTW_MEGA_BLOCK, smem_bytes);
+    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm[0], RTW_CAT(variant_, RTW_VARIANT)::mega_kernel, RTW_MEGA_BLOCK, smem_bytes);
     if (e == cudaSuccess)
-        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&lights, RTW_CAT(variant_, RTW_VARIANT)::mega_kernel_lights, RTW_MEGA_BLOCK, smem_bytes);
-    *blocks_per_sm = plain < lights ? plain : lights;
+        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm[1], RTW_CAT(variant_, RTW_VARIANT)::mega_kernel_lights, RTW_MEGA_BLOCK, smem_bytes);
     return e;
 }
 

@@ -151,7 +151,7 @@ struct WfLaunch {
 #define RTW_DECLARE_VARIANT(SUFFIX)                                                                          \
     cudaError_t launch_mega_##SUFFIX(const Scene& sc, const RenderParams& P, float* d_sum, Counters* d_ctr,  \
                                      uint32_t* d_work, const MegaLaunch& L, cudaStream_t st);                \
-    cudaError_t mega_occupancy_##SUFFIX(int* blocks_per_sm, size_t smem_bytes);                              \
+    cudaError_t mega_occupancy_##SUFFIX(int* blocks_per_sm /* [2]: plain, light-biased */, size_t smem_bytes); \
     cudaError_t launch_wf_extend_##SUFFIX(const Scene& sc, const RenderParams& P, const WfPool& pool, WfCounters* d_wc,   \
                                           Counters* d_ctr, const WfLaunch& L, cudaStream_t st);                          \
     cudaError_t launch_wf_shade_##SUFFIX(const Scene& sc, const RenderParams& P, const WfPool& pool, WfCounters* d_wc,    \

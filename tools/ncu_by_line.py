@@ -8,7 +8,8 @@ of the same cubin and sums executed instructions / stall samples per source line
 
 `inner` keys by the innermost (file:line) of every instruction, `outer` by the line of the kernel's
 own file the instruction was inlined into (so a whole inlined call shows up as one row);
-`inner@328` is `inner` restricted to what was inlined into line 328 of the kernel's file.
+`inner@328` is `inner` restricted to what was inlined into line 328 of the kernel's file; `outer2` keys one call level
+below the kernel's own lines (a kernel that is one call of an inlined body, like mega_kernel).
 """
 import csv
 import re
@@ -39,8 +40,10 @@ def load_listing(path, kernel):
                 inner = (first.group(1).split("/")[-1], int(first.group(2)))
                 last = pending[-1]
                 outer = (last.group(1).split("/")[-1], int(last.group(2)))
+                second = pending[-2] if len(pending) > 1 else last      # one call level below the kernel's own lines
+                outer2 = (second.group(1).split("/")[-1], int(second.group(2)))
                 pending = []
-            out[int(m2.group(1), 16)] = (inner, outer, m2.group(2).strip())
+            out[int(m2.group(1), 16)] = (inner, outer, m2.group(2).strip(), outer2)
     return out
 
 
@@ -65,7 +68,7 @@ def main():
         info = lst.get(off)
         if only is not None and not (info and info[1][1] == only):
             continue
-        key = (info[0] if mode == "inner" else info[1]) if info else ("?", 0)
+        key = (info[0] if mode == "inner" else info[3] if mode == "outer2" else info[1]) if info else ("?", 0)
         vals = [int(r[ix["Instructions Executed"]] or 0), int(r[ix["Thread Instructions Executed"]] or 0),
                 int(r[ix["# Samples"]] or 0), int(r[ix["Warp Stall Sampling (Not-issued Samples)"]] or 0)]
         for k in range(4):
