@@ -126,7 +126,7 @@ __device__ __forceinline__ void mega_body(const Scene& sc, const RenderParams& P
             // ---- shade / scatter every lane whose search is over
             if (alive && T.cur == CUR_DONE) {
                 bool finished = true;
-                if (first_hit_integrator(P.integrator) || path.depth_left >= 1u) finished = segment_end(cx, nt, P, path, T, kLights ? &S : nullptr, &n_rays);
+                if (first_hit_integrator(P.integrator) || path.depth_left >= 1u) finished = segment_end<false>(cx, nt, P, path, T, kLights ? &S : nullptr, &n_rays);
                 if (!finished) {
                     cx.bounce = P.depth - path.depth_left;
                     if (segment_begin(cx, P, path, T, S)) ++n_rays; else finished = true;
@@ -568,7 +568,7 @@ wf_shade_kernel(const Scene sc, const RenderParams P, const WfPool pool, WfCount
             T.o = v3(ro.x, ro.y, ro.z); T.d = v3(rd.x, rd.y, rd.z);
             T.t = u2f(hit.x); T.ref = hit.y; T.inner = hit.z;
             TraceCtx cx = path_ctx(sc, P, path, wp);
-            bool finished = segment_end(cx, nt, P, path, T);
+            bool finished = segment_end<true>(cx, nt, P, path, T);
             if (!finished && path.depth_left < 1u) finished = true;   // ray_color.rs:14-16: the next call returns black
             // L = emitted + col_mod * L(next): what this segment adds (thr * emitted, thr *
             // background) goes straight into the frame, so no radiance travels with the path. A path

@@ -185,19 +185,19 @@ RTW_HD void eval_quad(const Scene& sc, const Noise* nt, uint32_t idx, const Ray&
     load_material(sc, ids.x, h);
 }
 
-RTW_HD void eval_prim(const Scene& sc, const Noise* nt, uint32_t ref, const Ray& r, float t, Hit& h) {
+RTW_HD void eval_prim_split(const Scene& sc, const Noise* nt, uint32_t ref, const Ray& r, float t, Hit& h) {
     if (ref_kind(ref) == KIND_SPHERE) eval_sphere(sc, nt, ref_index(ref), r, t, h);
     else eval_quad(sc, nt, ref_index(ref), r, t, h);
 }
 
-// The full Hit for the result of trace(): Scene::collision_normal's return value.
-RTW_HD void eval_hit(const TraceCtx& cx, const Noise* nt, const Best& b, const Ray& r, Hit& h) {
+// The full Hit for the result of trace(), megakernel flavour (see eval_hit below).
+RTW_HD void eval_hit_split(const TraceCtx& cx, const Noise* nt, const Best& b, const Ray& r, Hit& h) {
     const Scene& sc = *cx.sc;
-    if (ref_kind(b.ref) != KIND_INSTANCE) { eval_prim(sc, nt, b.ref, r, b.t, h); return; }
+    if (ref_kind(b.ref) != KIND_INSTANCE) { eval_prim_split(sc, nt, b.ref, r, b.t, h); return; }
     // instance.rs:257-307
     const Instance& in = sc.instances[ref_index(b.ref)];
     Ray l = to_local(in, r);
-    eval_prim(sc, nt, b.inner, l, b.t, h);
+    eval_prim_split(sc, nt, b.inner, l, b.t, h);
     if (in.flags & INST_VOLUME) {
         float distance = volume_distance(in, cx);
         if (distance >= 0.0f) {
@@ -211,6 +211,88 @@ RTW_HD void eval_hit(const TraceCtx& cx, const Noise* nt, const Best& b, const R
         h.normal = rot_apply(in.fwd_rows, h.normal);
     }
     h.point = h.point + v3(in.t[0], in.t[1], in.t[2]);
+}
+
+// The Hit of the winning primitive (sphere.rs:124-146, quad.rs:61-80), written so that a warp whose lanes hit different
+// kinds of primitive diverges only where the kinds differ — the loads of the primitive, the normal, the quad's planar
+// coordinates — and walks the texture lookup, the Perlin noise and the material load ONCE, together (as two functions
+// that each ended in their own texel fetch and material load, inlined again behind the instance frame change, a warp
+// ran up to four copies of that tail one after the other: segment_end held 64 % of wf_shade's warp instructions at 10
+// lanes, profiles/r2n_wf_shade_by_line.txt). Same operations on the same values per path as the split flavour above.
+// wf_shade: 3 320 -> 2 368 instructions, its launches 14 % shorter, C5 +4.3 %, C4 +2 %; the megakernel, whose lanes
+// arrive here with fewer kinds per warp and which sits at its register cap, lost with it (C1 -10 %, C3 -2 %) and
+// keeps the split flavour (profiles/r2v_ab_convergent_hit.txt): kOneTail of segment_end chooses.
+RTW_HD void eval_prim(const Scene& sc, const Noise* nt, uint32_t ref, const Ray& r, float t, Hit& h) {
+    const bool is_sphere = ref_kind(ref) == KIND_SPHERE;
+    const uint32_t idx = ref_index(ref);
+    const V3 p = r.o + r.d * t;
+    V3 normal, col = v3(1.0f, 1.0f, 1.0f);
+    uint2 ids;
+    float alfa = 0.0f, beta = 0.0f;                 // quad.rs:66-67 (used only by a textured quad)
+    if (is_sphere) {
+        float4 s = RTW_LDG(&sc.spheres[idx]);
+        float4 cl = RTW_LDG(&sc.sphere_col[idx]);
+        ids = RTW_LDG(&sc.sphere_ids[idx]);
+        V3 c = v3(s.x, s.y, s.z);
+        if (f2u(cl.w) & 1u) {
+            float4 vel = RTW_LDG(&sc.sphere_vel[idx]);
+            c = c + v3(vel.x, vel.y, vel.z) * r.time;
+        }
+        normal = unit(p - c);
+        col = v3(cl.x, cl.y, cl.z);
+    } else {
+        const Quad* qp = &sc.quads[idx];
+        float4 q0 = RTW_LDG(&qp->q0), q1 = RTW_LDG(&qp->q1), q2 = RTW_LDG(&qp->q2), q3 = RTW_LDG(&qp->q3);
+        ids = RTW_LDG(&sc.quad_ids[idx]);
+        V3 planar = p - v3(q1.x, q1.y, q1.z);
+        V3 u = v3(q1.w, q2.x, q2.y), v = v3(q2.z, q2.w, q3.x), w = v3(q3.y, q3.z, q3.w);
+        alfa = dot(w, cross(planar, v));
+        beta = dot(w, cross(u, planar));
+        normal = v3(q0.x, q0.y, q0.z);
+    }
+    const Texture& tx = sc.textures[ids.y];
+    uint32_t tex_x = 0u, tex_y = 0u;
+    if (tx.n_texels != 1u) {
+        if (is_sphere) {
+            const float PI = 3.14159265358979323846f, FRAC_1_PI = 0.31830988618379067154f;
+            float u = (atan2f(-normal.z, normal.x) + PI) * FRAC_1_PI * 0.5f;
+            float v = 1.0f - (FRAC_1_PI * acosf(-normal.y));
+            tex_x = to_usize(floorf(u * (float)(tx.width - 1u)));
+            tex_y = to_usize(floorf(v * (float)(tx.height - 1u)));
+        } else {
+            tex_x = alfa != 1.0f ? to_usize(floorf(alfa * (float)tx.width)) : tx.width - 1u;
+            tex_y = beta != 1.0f ? to_usize(floorf(beta * (float)tx.height)) : tx.height - 1u;
+        }
+    }
+    h.t = t; h.normal = normal; h.point = p;
+    const V3 texel = texture_color_at(sc, nt, tx, tex_x, tex_y, p);
+    h.col_mod = is_sphere ? texel * col : texel;    // the quad has no colour of its own (quad.rs:76)
+    load_material(sc, ids.x, h);
+}
+
+// The full Hit for the result of trace(): Scene::collision_normal's return value.
+RTW_HD void eval_hit(const TraceCtx& cx, const Noise* nt, const Best& b, const Ray& r, Hit& h) {
+    const Scene& sc = *cx.sc;
+    const bool inst = ref_kind(b.ref) == KIND_INSTANCE;
+    // instance.rs:257-307: the primitive's Hit in the instance's frame, then back into the world
+    const Instance* in = inst ? &sc.instances[ref_index(b.ref)] : nullptr;
+    Ray l = r;
+    if (inst) l = to_local(*in, r);
+    eval_prim(sc, nt, inst ? b.inner : b.ref, l, b.t, h);
+    if (!inst) return;
+    if (in->flags & INST_VOLUME) {
+        float distance = volume_distance(*in, cx);
+        if (distance >= 0.0f) {
+            // scatter inside the medium: entry-face t, col_mod and material are kept (instance.rs:295-299)
+            h.point = h.point + l.d * distance;
+            h.normal = random_unit_vec_stream(cx, cx.bounce << 16, 1u + in->index);
+        }
+    }
+    if (!(in->flags & INST_ROT_IDENTITY)) {
+        h.point = rot_apply(in->fwd_rows, h.point);
+        h.normal = rot_apply(in->fwd_rows, h.normal);
+    }
+    h.point = h.point + v3(in->t[0], in->t[1], in->t[2]);
 }
 
 // ------------------------------------------------------------------ materials.rs
@@ -371,6 +453,7 @@ RTW_HD bool segment_begin(const TraceCtx& cx, const RenderParams& P, const Path&
     return true;
 }
 
+template <bool kOneTail = true>
 RTW_HD bool segment_end(const TraceCtx& cx, const Noise* nt, const RenderParams& P, Path& p, const Trav& T,
                         const Stack* S = nullptr, uint32_t* shadow_rays = nullptr) {
     const Scene& sc = *cx.sc;
@@ -387,7 +470,7 @@ RTW_HD bool segment_end(const TraceCtx& cx, const Noise* nt, const RenderParams&
     }
     RTW_COUNT(cx, hits);
     Hit h;
-    eval_hit(cx, nt, b, ray, h);
+    if (kOneTail) eval_hit(cx, nt, b, ray, h); else eval_hit_split(cx, nt, b, ray, h);
     if (ig == RTW_INT_LIGHT_CAST) {                                 // Rust2 ray_color.rs:61-105
         float count = 0.0f; uint32_t nr = 0u;
         V3 color = S ? light_gather(cx, P, h, ray, *S, false, count, nr) : v3(0.f, 0.f, 0.f);
@@ -439,6 +522,7 @@ RTW_HD bool segment_end(const TraceCtx& cx, const Noise* nt, const RenderParams&
 
 // Scalar form of one segment (the host emulator): returns true when the path is finished.
 // `rays` counts Scene::collision_normal equivalents.
+template <bool kOneTail = true>
 RTW_HD bool path_step(const Scene& sc, const Noise* nt, const RenderParams& P, Path& p, uint32_t& rays,
                       const Stack& S, Work* work = nullptr) {
     TraceCtx cx = path_ctx(sc, P, p, work);
@@ -449,7 +533,7 @@ RTW_HD bool path_step(const Scene& sc, const Noise* nt, const RenderParams& P, P
         else trav_step_other(cx, p.ray.time, T, S);
     }
     ++rays;
-    return segment_end(cx, nt, P, p, T, &S, &rays);
+    return segment_end<kOneTail>(cx, nt, P, p, T, &S, &rays);
 }
 
 RTW_HD V3 path_result(const Path& p) {

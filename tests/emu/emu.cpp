@@ -109,7 +109,8 @@ extern "C" int emu_render_ex(const rtw_scene_desc* d, const rtw_camera* cam, con
                 generate(P, i, image_row(P, jr), s, p);
                 rays32 = 0;
                 Work w{0u, 0u, 0u, 0u, 0u};
-                while (!path_step(sc, sc.noises, P, p, rays32, S, &w)) {}
+                if (use_lbvh & 8) { while (!path_step<false>(sc, sc.noises, P, p, rays32, S, &w)) {} }   // the megakernel's Hit flavour
+                else { while (!path_step<true>(sc, sc.noises, P, p, rays32, S, &w)) {} }
                 rays += rays32;
                 work_total[0] += w.nodes; work_total[1] += w.spheres; work_total[2] += w.quads; work_total[3] += w.instances; work_total[4] += w.hits;
                 V3 c = path_result(p);

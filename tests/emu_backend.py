@@ -45,8 +45,9 @@ def load_emu():
 
 
 class EmuSceneHandle:
-    def __init__(self, lib, fs, lbvh: bool = False, baked: bool = False, inside: bool = False):
-        self._lib, self._fs, self._lbvh = lib, fs, (1 if lbvh else 0) | (2 if baked else 0) | (4 if inside else 0)
+    def __init__(self, lib, fs, lbvh: bool = False, baked: bool = False, inside: bool = False, split_hit: bool = False):
+        self._lib, self._fs = lib, fs
+        self._lbvh = (1 if lbvh else 0) | (2 if baked else 0) | (4 if inside else 0) | (8 if split_hit else 0)
         self.last = (C.c_uint64 * 8)()
         self.last_info = A.rtw_scene_info()
 
@@ -73,21 +74,22 @@ class EmuSceneHandle:
 class EmuBackend:
     name = "emu"
 
-    def __init__(self, lbvh: bool = False, baked: bool = False, inside: bool = False):
+    def __init__(self, lbvh: bool = False, baked: bool = False, inside: bool = False, split_hit: bool = False):
         """lbvh=True: every level is rebuilt with the LBVH steps of rtw_lbvh.h (run in host loops)
         before rendering, as rtw_scene_rebuild_lbvh does on the device. baked=True: walk the top level in which
         rigidly placed surface instances are replaced by world-space copies of their primitives (rtw_host.h)."""
         self.lib = load_emu()
         self.lbvh, self.baked, self.inside = lbvh, baked, inside   # inside: node-count probes only (tools/lbvh_quality.py)
+        self.split_hit = split_hit     # the Hit evaluation as the megakernel compiles it (rtw_shade.h eval_hit_split)
 
     def camera_init(self, width, aspect_ratio, vfov, origin, direction, vup, lens_radius):
         from oracle_backend import OracleBackend
         return OracleBackend().camera_init(width, aspect_ratio, vfov, origin, direction, vup, lens_radius)
 
     def scene(self, scene) -> EmuSceneHandle:
-        key = ("emu", self.lbvh, self.baked, self.inside)
+        key = ("emu", self.lbvh, self.baked, self.inside, self.split_hit)
         h = scene._backend_cache.get(key)
         if h is None:
-            h = EmuSceneHandle(self.lib, scene.flatten(), self.lbvh, self.baked, self.inside)
+            h = EmuSceneHandle(self.lib, scene.flatten(), self.lbvh, self.baked, self.inside, self.split_hit)
             scene._backend_cache[key] = h
         return h

@@ -33,6 +33,25 @@ ALL.update(scenes.CONFIGS)
 ALL["C4_smoke"] = lambda **k: scenes.config_c4(smoke=True, **k)
 
 
+@pytest.mark.parametrize("name", ["C3", "C4_smoke", "C5", "presentation", "texture", "triangle_mesh"])
+def test_both_hit_flavours_are_the_same_arithmetic(name, emu):
+    """rtw_shade.h evaluates the winning primitive's Hit in two shapes — one tail of texture lookup and material load for
+    the whole warp (wf_shade), one per primitive kind (the megakernel): the same operations on the same values, so the
+    images are equal bit for bit."""
+    from emu_backend import EmuBackend
+    if name not in ALL:
+        pytest.skip(f"no scene {name}")
+    job = _small(ALL[name](), 56, 40, 3)
+    vp = job.viewport
+    vp.flags = A.RTW_FLAG_STRICT_FP
+    a = vp._run(job.ray_color, job.scene, job.mode, emu)
+    b = vp._run(job.ray_color, job.scene, job.mode, EmuBackend(split_hit=True))
+    assert np.array_equal(a, b, equal_nan=True)
+    a = vp._run(A.RTW_INT_ALBEDO, job.scene, A.RTW_MODE_NO_RAND, emu)
+    b = vp._run(A.RTW_INT_ALBEDO, job.scene, A.RTW_MODE_NO_RAND, EmuBackend(split_hit=True))
+    assert np.array_equal(a, b, equal_nan=True)
+
+
 @pytest.mark.parametrize("name", sorted(ALL))
 def test_traversal_headers_match_oracle(name, oracle, emu):
     """Same closest hit (bit for bit outside tie pixels) and same path radiance as the oracle: the
