@@ -105,3 +105,52 @@ def test_gpu_lbvh_rebuild_renders_identically(name, cuda):
         h.use_sah()
     vp.flags = A.RTW_FLAG_STRICT_FP | A.RTW_FLAG_WAVEFRONT
     assert np.array_equal(vp._run(A.RTW_INT_ALBEDO, job.scene, A.RTW_MODE_NO_RAND, cuda), first, equal_nan=True)
+
+
+def _sphere_cloud(n, seed=5):
+    """n small spheres in a slab in front of the camera: a level whose breadth-first collapse has tree levels wider than
+    the collapse kernel's one block of 1 024 threads (the configs' levels stay below that)."""
+    import rtw_b200 as rtw
+    rng = np.random.default_rng(seed)
+    c = rng.uniform([-20.0, -12.0, -60.0], [20.0, 12.0, -20.0], size=(n, 3)).astype(np.float32)
+    r = rng.uniform(0.05, 0.35, size=n).astype(np.float32)
+    col = rng.uniform(0.1, 0.9, size=(n, 3)).astype(np.float32)
+    spheres = [rtw.Sphere.new_with_texture(rtw.Vec3(*map(float, c[k])), float(r[k]), None, rtw.SCATTER_M,
+                                           rtw.ImageTexture.from_color(rtw.Vec3(*map(float, col[k])))) for k in range(n)]
+    scene = rtw.Scene.new_sphere(spheres)
+    vp = rtw.Viewport.new_from_res(160, 96, 2, 6, 2.0, 50.0, rtw.Vec3(0, 0, 0), rtw.Vec3(0, 0, -1), rtw.Vec3(0, 1, 0), None, 0.0)
+    return scene, vp
+
+
+def test_wide_level_collapse_on_host():
+    """The emulator's sequential collapse on a 6 000-leaf level: same image as through the SAH tree."""
+    from emu_backend import EmuBackend
+    scene, vp = _sphere_cloud(6000)
+    vp.flags = A.RTW_FLAG_STRICT_FP
+    a = vp._run(A.RTW_INT_ALBEDO, scene, A.RTW_MODE_NO_RAND, EmuBackend())
+    b = vp._run(A.RTW_INT_ALBEDO, scene, A.RTW_MODE_NO_RAND, EmuBackend(lbvh=True))
+    assert np.array_equal(a, b) and (a != a[0, 0]).any()
+
+
+@pytest.mark.gpu
+def test_gpu_lbvh_levels_wider_than_one_block(cuda):
+    """30 000 leaves: the collapse kernel's block walks tree levels of several thousand wide nodes in steps of 1 024
+    with a block scan handing out the children's positions; the fit's rotations run on deep chains. Strict renders
+    through the rebuilt level equal the SAH ones bit for bit, first hits and paths."""
+    import rtw_b200 as rtw
+    scene, vp = _sphere_cloud(30000)
+    vp.flags = A.RTW_FLAG_STRICT_FP | A.RTW_FLAG_WAVEFRONT
+    h = cuda.scene(scene)
+    first = vp._run(A.RTW_INT_ALBEDO, scene, A.RTW_MODE_NO_RAND, cuda)
+    paths = vp._run(rtw.ray_color_gradient, scene, A.RTW_MODE_RANDOM, cuda)
+    rays = h.stats().rays
+    for rep in range(2):                                            # a second rebuild reuses the scratch of the first
+        assert h.rebuild_lbvh() >= 0.0
+        try:
+            assert np.array_equal(vp._run(A.RTW_INT_ALBEDO, scene, A.RTW_MODE_NO_RAND, cuda), first)
+            again = vp._run(rtw.ray_color_gradient, scene, A.RTW_MODE_RANDOM, cuda)
+            assert h.stats().rays == rays
+            assert np.allclose(again, paths, rtol=1e-5, atol=1e-6)
+        finally:
+            h.use_sah()
+    assert (first != first[0, 0]).any()
