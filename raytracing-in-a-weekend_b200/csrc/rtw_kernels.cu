@@ -187,6 +187,27 @@ mega_kernel_lights(const Scene sc, const RenderParams P, float* __restrict__ sum
 // =====================================================================================
 
 __device__ __forceinline__ void prefetch_l1(const void* p) { asm volatile("prefetch.global.L1 [%0];" ::"l"(p)); }
+// Path records are read once and written once per iteration: with the streaming (evict-first) cache operators
+// (ld.global.cs / st.global.cs) they leave the BVH nodes and primitives alone in L1 and L2. RTW_WF_STREAM: bit 0 =
+// extend, bit 1 = shade; both: C5 at 625 spp +1.4 %, at 2 500 spp +1.1 %, C4 +0.6 % (each kernel's launches 1 % shorter;
+// profiles/r3a_ab_streaming_records.txt).
+#ifndef RTW_WF_STREAM
+#define RTW_WF_STREAM 3
+#endif
+#if RTW_WF_STREAM & 1
+#define EXT_LD(p) __ldcs(p)
+#define EXT_ST(p, v) __stcs(p, v)
+#else
+#define EXT_LD(p) (*(p))
+#define EXT_ST(p, v) (*(p) = (v))
+#endif
+#if RTW_WF_STREAM & 2
+#define SHD_LD(p) __ldcs(p)
+#define SHD_ST(p, v) __stcs(p, v)
+#else
+#define SHD_LD(p) (*(p))
+#define SHD_ST(p, v) (*(p) = (v))
+#endif
 
 // extend: Scene::collision_normal for every ray of queue[cur]. Persistent warps. A warp reserves
 // `chunk` consecutive queue positions with one atomic; whenever `fetch_min` of its lanes are idle
@@ -357,11 +378,11 @@ wf_extend_kernel(const Scene sc, const RenderParams P, const WfPool pool, WfCoun
             SCHED_TIME_BEGIN(3);
             const uint32_t rank = __popc(idle & lt_mask);
             if (!busy && rank < take) {
-                const float4 rd = q.d[c_pos + rank];
+                const float4 rd = EXT_LD(&q.d[c_pos + rank]);
                 if (f2u(rd.w) != WF_DEAD) {               // dead slots only exist once the sample supply has run out
                     pos = c_pos + rank;
-                    const float4 ro = q.o[pos];
-                    const uint2 id = q.id[pos];
+                    const float4 ro = EXT_LD(&q.o[pos]);
+                    const uint2 id = EXT_LD(&q.id[pos]);
                     Ray r; r.o = v3(ro.x, ro.y, ro.z); r.d = v3(rd.x, rd.y, rd.z); r.time = ro.w;
                     time = ro.w;
                     cx.pixel = id.x; cx.sample = id.y; cx.bounce = f2u(rd.w);
@@ -477,7 +498,7 @@ wf_extend_kernel(const Scene sc, const RenderParams P, const WfPool pool, WfCoun
         }
         if (busy && T.cur == CUR_DONE) {
 #endif
-            pool.hit[pos] = make_uint4(f2u(T.t), T.ref, T.inner, 0u);
+            EXT_ST(&pool.hit[pos], make_uint4(f2u(T.t), T.ref, T.inner, 0u));
             busy = false;
         }
     }
@@ -552,13 +573,13 @@ wf_shade_kernel(const Scene sc, const RenderParams P, const WfPool pool, WfCount
     RTW_WF_FLAG_T alive = false, was_live = false, fresh = false;
     if (L.drain && !init && __ldg(&pool.warp_live[e >> 5]) == 0u) return;   // (whole warp) dead for good: WfLaunch::drain
     if (!init) {
-        const float4 rd = q.d[e];
+        const float4 rd = SHD_LD(&q.d[e]);
         was_live = f2u(rd.w) != WF_DEAD;
         if (was_live) {
-            const float4 ro = q.o[e];
-            const uint2 id = q.id[e];
-            const uint4 hit = pool.hit[e];
-            const float4 thr = q.thr[e];
+            const float4 ro = SHD_LD(&q.o[e]);
+            const uint2 id = SHD_LD(&q.id[e]);
+            const uint4 hit = SHD_LD(&pool.hit[e]);
+            const float4 thr = SHD_LD(&q.thr[e]);
             path.ray.time = ro.w;
             path.thr = v3(thr.x, thr.y, thr.z); path.rad = v3(0.f, 0.f, 0.f);   // this segment's contribution only
             path.pixel = id.x; path.sample = id.y;
@@ -645,11 +666,11 @@ wf_shade_kernel(const Scene sc, const RenderParams P, const WfPool pool, WfCount
     }
     if (!alive && !was_live && !init) return;                         // dead before, dead now: nothing to write
     if (alive) {
-        q.o[e] = make_float4(path.ray.o.x, path.ray.o.y, path.ray.o.z, path.ray.time);
-        q.d[e] = make_float4(path.ray.d.x, path.ray.d.y, path.ray.d.z, u2f(P.depth - path.depth_left));
-        if (fresh) q.id[e] = make_uint2(path.pixel, path.sample);     // a continuing path keeps its identity
-        q.thr[e] = make_float4(path.thr.x, path.thr.y, path.thr.z,
-                               u2f((path.block & WF_BLOCK_MASK) | (path.depth_left << WF_DEPTH_SHIFT) | (path.poison ? 0x80000000u : 0u)));
+        SHD_ST(&q.o[e], make_float4(path.ray.o.x, path.ray.o.y, path.ray.o.z, path.ray.time));
+        SHD_ST(&q.d[e], make_float4(path.ray.d.x, path.ray.d.y, path.ray.d.z, u2f(P.depth - path.depth_left)));
+        if (fresh) SHD_ST(&q.id[e], make_uint2(path.pixel, path.sample));     // a continuing path keeps its identity
+        SHD_ST(&q.thr[e], make_float4(path.thr.x, path.thr.y, path.thr.z,
+                               u2f((path.block & WF_BLOCK_MASK) | (path.depth_left << WF_DEPTH_SHIFT) | (path.poison ? 0x80000000u : 0u))));
         const uint32_t am = __activemask();
         // same value from every warp; read first (L2) so that only the first few warps store
         if (lane == (uint32_t)(__ffs(am) - 1) && live_mark_seen != mark && __ldcg(&wc->live_mark) != mark) wc->live_mark = mark;
