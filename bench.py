@@ -309,6 +309,11 @@ def run_b200(args):
             if collect is not None:
                 collect_stats(collect)
 
+    # The CPU baseline leg runs BEFORE the GPU legs: measured right after a minute of the GPU at 700 W the same 16 host
+    # threads ran the same sample at half their rate on some boxes (0.65 against 1.30 Mpaths/s; `--impl reference`, a
+    # process of its own, read 1.33 on the same box: profiles/r2x_bench_C5_n1.json, r3b_*; tools/cpu_probe.py rules out
+    # torch, the CUDA context and the library). Nothing of the GPU arm runs while it is timed.
+    cpu_pre = cpu_baseline_obj(cpu_sample(job, args.cpu_seconds)) if (world == 1 and rank == 0) else None
     for _ in range(args.warmup):
         step()
     torch.cuda.synchronize()
@@ -482,7 +487,7 @@ def run_b200(args):
                             "hbm": {"achieved": hbm_gbs, "peak": hbm_peak, "unit": "GB/s", "frac": hbm_gbs / hbm_peak,
                                     "peak_source": hbm_src,
                                     "note": "whole step: path records streamed by extend+shade (176 B/ray + 8 B per new path) + framebuffer REDs; the scene (<10 MB) is L1/L2-resident"}}}
-        cpu = cpu_baseline_obj(cpu_sample(job, args.cpu_seconds)) if world == 1 else None
+        cpu = cpu_pre
         paths_frame = W * H * spp * (world if part == "frames" else 1)     # paths per step
         val = paths_frame * args.steps / (elapsed_ms * 1e-3) / 1e6
         part_text = {"samples": f"sample range x{world} + NCCL reduce(sum) to rank 0",
