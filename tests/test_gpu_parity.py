@@ -176,6 +176,25 @@ def test_fast_kernels_agree_statistically(oracle, cuda):
     assert abs(fast[fin].mean() / strict[fin].mean() - 1.0) < 5e-3
 
 
+def test_default_pipeline_rule(cuda):
+    """Which pipeline a render takes when the caller names none (rtw_api.cu wavefront_pays): the
+    megakernel below 2^24 paths, and at any size for a flat scene (at most eight top-level primitives, nothing below);
+    the wavefront pipeline otherwise. rtw_stats.iterations counts wavefront iterations (0 = megakernel)."""
+    def run(job):
+        job.viewport.flags = 0
+        job.viewport._run(job.ray_color, job.scene, job.mode, cuda)
+        st = cuda.scene(job.scene).stats()
+        assert st.paths == job.viewport.width * job.viewport.height * job.viewport.samples
+        return st.iterations
+    assert run(scenes.config_c1(samples=190)) == 0            # 400 x 225 x 190 = 17.1 M paths >= 2^24, five spheres: flat
+    assert run(scenes.config_c3(samples=50)) == 0             # 18 M paths, four spheres: flat
+    assert run(scenes.config_c2(samples=1)) == 0              # 0.8 M paths: small
+    assert run(scenes.config_c2(samples=20)) == 0             # 16.2 M paths < 2^24
+    assert run(scenes.config_c2(samples=21)) > 0              # 17.0 M paths >= 2^24, 488 spheres: a tree to walk
+    assert run(scenes.config_c5(samples=27)) > 0              # 17.3 M paths
+    assert run(scenes.config_c5(samples=26)) == 0             # 16.6 M paths
+
+
 def test_pipelines_agree(cuda):
     """Megakernel and wavefront run the same per-path arithmetic with the same Philox streams: the
     strict builds agree path for path, so the images differ only by f32 summation order."""
