@@ -16,6 +16,8 @@ struct LbvhScratch {       // device scratch, grown to the largest level seen an
     LbvhBox* ibox = nullptr;
     uint32_t* flag = nullptr;
     int* queue = nullptr;
+    float* dp_cut = nullptr;           // 4 per internal node
+    uint32_t* dp_choice = nullptr;
     float* cb = nullptr;
     void* cub_tmp = nullptr;
     size_t n_codes = 0, cub_bytes = 0;

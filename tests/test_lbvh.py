@@ -49,7 +49,7 @@ def test_lbvh_walk_cost_against_the_sah_tree(name, bound):
     """Node visits per ray through the rebuilt levels against the host SAH levels, counted by the instrumented
     traversal on the level the kernels walk for this camera (no enclosing volumes, baked instances). The plain
     Karras tree with the fixed two-level collapse of round 1 stood at 1.38 (C5) / 1.41 (C2); rotations in the fit
-    and the largest-child-first collapse bring it to 1.15 / 1.12 (tools/lbvh_quality.py)."""
+    and the collapse chosen by dynamic programming bring it to 1.17 / 1.11 (tools/lbvh_quality.py)."""
     from emu_backend import EmuBackend
     per_ray = {}
     for lbvh in (False, True):
