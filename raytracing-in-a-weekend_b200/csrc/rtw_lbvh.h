@@ -218,7 +218,8 @@ RTW_HD void lbvh_fit_node(const LbvhBuild& b, int N) {
 }
 
 #ifndef LBVH_FIT_PASSES
-#define LBVH_FIT_PASSES 2      // bottom-up passes of lbvh_fit_node over the tree (each one more round of rotations)
+#define LBVH_FIT_PASSES 4      // bottom-up passes of lbvh_fit_node over the tree, each one more round of rotations (C5's node
+                               // visits per ray against the SAH tree: 1.166 with two, 1.141 with three, 1.127 with four, no less with eight)
 #endif
 
 // The children of the wide node that stands for binary node i, as the dynamic program chose them (lbvh_dp_node): the
