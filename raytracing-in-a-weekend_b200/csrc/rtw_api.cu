@@ -270,7 +270,12 @@ struct rtw_scene {
     LbvhLeaf* lb_leaves_d = nullptr;
     Node* lb_nodes = nullptr; Node16* lb_nodes16 = nullptr;
     LbvhLevelOut* lb_out_d = nullptr;
-    LbvhScratch lb_scratch;
+    // the levels of a rebuild are independent: each gets its own scratch and one of up to kLbLanes streams, forked from and
+    // joined to the scene's stream with events, so that their latency-bound fit passes overlap (C5: five levels)
+    static const int kLbLanes = 8;
+    std::vector<LbvhScratch> lb_scratch;
+    cudaStream_t lb_stream[kLbLanes] = {};
+    cudaEvent_t lb_fork = nullptr, lb_join[kLbLanes] = {};
     std::vector<HostScene::Enclosing> enclosing;
     std::vector<void*> allocs;
     std::vector<MemCache::Tex> texs;
@@ -321,6 +326,9 @@ struct rtw_scene {
         if (ev0) cudaEventDestroy(ev0);
         if (ev1) cudaEventDestroy(ev1);
         if (ev2) cudaEventDestroy(ev2);
+        for (auto st : lb_stream) if (st) cudaStreamDestroy(st);
+        for (auto e : lb_join) if (e) cudaEventDestroy(e);
+        if (lb_fork) cudaEventDestroy(lb_fork);
         if (stream) cudaStreamDestroy(stream);
     }
 };
@@ -889,14 +897,28 @@ int rtw_scene_rebuild_lbvh(rtw_scene* s, float* out_build_ms) {
     CK(cudaEventRecord(s->ev0, s->stream));
     uint32_t base = s->n_sah_nodes;
     std::vector<uint32_t> level_base(s->lb_levels.size(), 0u);
+    if (s->lb_scratch.size() < s->lb_levels.size()) s->lb_scratch.resize(s->lb_levels.size());
+    if (!s->lb_fork) CK(cudaEventCreateWithFlags(&s->lb_fork, cudaEventDisableTiming));
+    CK(cudaEventRecord(s->lb_fork, s->stream));
+    int lanes_used = 0, n_built = 0;
     for (size_t i = 0; i < s->lb_levels.size(); ++i) {
         const LbvhLevelDesc& lv = s->lb_levels[i];
         if (lv.count < 2u) continue;
         level_base[i] = base;
+        const int lane = n_built++ % rtw_scene::kLbLanes;
+        if (!s->lb_stream[lane]) {
+            CK(cudaStreamCreateWithFlags(&s->lb_stream[lane], cudaStreamNonBlocking));
+            CK(cudaEventCreateWithFlags(&s->lb_join[lane], cudaEventDisableTiming));
+        }
+        if (lane >= lanes_used) { CK(cudaStreamWaitEvent(s->lb_stream[lane], s->lb_fork, 0)); lanes_used = lane + 1; }
         cudaError_t e = lbvh_build_level(s->lb_leaves_d + lv.first, lv.count, base, s->lb_nodes, s->lb_nodes16,
-                                         s->lb_scratch, s->lb_out_d + i, s->stream);
+                                         s->lb_scratch[i], s->lb_out_d + i, s->lb_stream[lane]);
         if (e != cudaSuccess) return cuda_fail(e, "lbvh_build_level");
         base += lv.count - 1u;
+    }
+    for (int lane = 0; lane < lanes_used; ++lane) {
+        CK(cudaEventRecord(s->lb_join[lane], s->lb_stream[lane]));
+        CK(cudaStreamWaitEvent(s->stream, s->lb_join[lane], 0));
     }
     CK(cudaEventRecord(s->ev1, s->stream));
     std::vector<LbvhLevelOut> out(s->lb_levels.size());

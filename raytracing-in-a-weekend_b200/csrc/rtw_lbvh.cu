@@ -123,7 +123,7 @@ cudaError_t grow(T** p, size_t* have, size_t need) {
 
 LbvhScratch::~LbvhScratch() {
     cudaFree(codes); cudaFree(codes_sorted); cudaFree(order_in); cudaFree(order); cudaFree(left); cudaFree(right);
-    cudaFree(parent_i); cudaFree(parent_l); cudaFree(ibox); cudaFree(flag); cudaFree(queue); cudaFree(dp_cut); cudaFree(dp_choice);
+    cudaFree(parent_i); cudaFree(parent_l); cudaFree(ibox); cudaFree(flag); cudaFree(queue); cudaFree(dp_cut); cudaFree(dp_choice); cudaFree(sah_cost);
     cudaFree(cb); cudaFree(cub_tmp);
 }
 
@@ -140,6 +140,7 @@ cudaError_t lbvh_build_level(const LbvhLeaf* d_leaves, uint32_t n, uint32_t node
     h = w.n_codes; LB(grow(&w.ibox, &h, n)); h = w.n_codes; LB(grow(&w.flag, &h, n));
     h = w.n_codes; LB(grow(&w.queue, &h, n));
     h = w.n_codes; LB(grow(&w.dp_choice, &h, n));
+    h = w.n_codes; LB(grow(&w.sah_cost, &h, n));
     h = 4 * w.n_codes; LB(grow(&w.dp_cut, &h, 4 * (size_t)n));
     if (w.n_codes < n) w.n_codes = n;
     if (!w.cb) LB(cudaMalloc(reinterpret_cast<void**>(&w.cb), 6 * sizeof(float)));
@@ -160,7 +161,7 @@ cudaError_t lbvh_build_level(const LbvhLeaf* d_leaves, uint32_t n, uint32_t node
     lbvh_karras_kernel<<<g_int, B, 0, st>>>(w.codes_sorted, (int)n, w.left, w.right, w.parent_i, w.parent_l, w.flag);
     LbvhBuild b;
     b.leaves = d_leaves; b.order = w.order; b.left = w.left; b.right = w.right; b.parent_i = w.parent_i; b.parent_l = w.parent_l;
-    b.ibox = w.ibox; b.dp_cut = w.dp_cut; b.dp_choice = w.dp_choice;
+    b.ibox = w.ibox; b.dp_cut = w.dp_cut; b.dp_choice = w.dp_choice; b.sah_cost = w.sah_cost;
     for (int pass = 0; pass < LBVH_FIT_PASSES; ++pass) {
         if (pass > 0) LB(cudaMemsetAsync(w.flag, 0, (size_t)(n - 1u) * sizeof(uint32_t), st));
         lbvh_fit_kernel<<<g_leaf, B, 0, st>>>(b, (int)n, w.flag);

@@ -8,7 +8,8 @@
 //   1. Morton code (30 bits) of every leaf's box centre inside the level's centroid bounds
 //   2. radix sort of (code, leaf)
 //   3. Karras 2012 binary radix tree over the sorted codes (ties broken by position)
-//   4. bottom-up box fit (second arrival at a node computes it) with one tree rotation per node on the way (lbvh_fit_node)
+//   4. bottom-up box fit (second arrival at a node computes it) with treelet restructuring on the way (lbvh_treelet_node;
+//      LBVH_FIT_PASSES passes)
 //   5. collapse to the 4-wide nodes the traversal walks (rtw_device.h Node / Node16), top down and breadth first: the
 //      children of a wide node are the descendants of its binary node that a dynamic program, solved during the fit
 //      (lbvh_dp_node), chose for the least summed wide-node area; the internal ones become the next wide nodes
@@ -140,6 +141,7 @@ struct LbvhBuild {
     const LbvhLeaf* leaves; const uint32_t* order;
     int* left; int* right; int* parent_i; int* parent_l;
     LbvhBox* ibox;
+    float* sah_cost;            // summed box area of the internal nodes of every node's subtree (lbvh_treelet_node)
     float* dp_cut;              // [4 * node + (k - 1)]: least summed wide-node area of the subtree handed up in <= k slots
     uint32_t* dp_choice;        // per node: bits 0-1 the wide node's own split (slots to the left, 1..3), bits 2k-2 .. 2k-1
                                 // (k = 2..4) the split when the subtree is handed up in k slots (0 = as one wide node)
@@ -179,6 +181,10 @@ RTW_HD void lbvh_dp_node(const LbvhBuild& b, int N, float area) {
     b.dp_choice[N] = packed;
 }
 
+// Leaves of the treelets lbvh_treelet_node restructures (0: one rotation per node instead, lbvh_fit_node)
+#ifndef LBVH_TREELET
+#define LBVH_TREELET 6
+#endif
 // Fit of internal node N, by the second thread to arrive there: every box below N is final and no other thread will
 // touch N's subtree again, so this thread may also restructure it. One tree rotation first (Kensler 2008): a child A of
 // N changes places with a grandchild G on the other side (child of B) when that shrinks B's box — the Morton order
@@ -186,7 +192,9 @@ RTW_HD void lbvh_dp_node(const LbvhBuild& b, int N, float area) {
 // (node visits per ray against the host SAH tree, tools/lbvh_quality.py: C5 1.31 -> 1.17, C2 1.24 -> 1.13). The largest
 // gain of the four candidates wins, ties and NaN boxes leave the tree alone. Then N's box. (Grandchild <-> grandchild
 // exchanges as two more candidates changed nothing measurable: C5 1.151 -> 1.158, C2 1.123 -> 1.118.)
+RTW_HD void lbvh_treelet_node(const LbvhBuild& b, int N);
 RTW_HD void lbvh_fit_node(const LbvhBuild& b, int N) {
+    if (LBVH_TREELET != 0) { lbvh_treelet_node(b, N); return; }    // (below; the rotation that follows is the A/B alternative)
     int ch[2] = {RTW_LBVH_LD(&b.left[N]), RTW_LBVH_LD(&b.right[N])};
     LbvhBox cb[2] = {lbvh_build_child_box(b, ch[0]), lbvh_build_child_box(b, ch[1])};
     int gc[2][2] = {{0, 0}, {0, 0}}; LbvhBox gb[2][2];
@@ -217,9 +225,106 @@ RTW_HD void lbvh_fit_node(const LbvhBuild& b, int N) {
     lbvh_dp_node(b, N, lbvh_half_area(b.ibox[N]));
 }
 
+// Treelet restructuring (Karras & Aila 2013) in place of the single rotation, by the thread that owns N's subtree: the
+// treelet is N plus the internal nodes below it opened largest box first until it has LBVH_TREELET leaves (subtrees or
+// primitives); every way of joining those leaves into a binary tree is priced by the summed area of its internal nodes
+// (a dynamic program over the 2^n leaf subsets: cost[S] = area[S] + min over the splits of S), and the cheapest replaces
+// the treelet's internal nodes when it beats the present one. Subtree costs below the treelet's leaves are carried in
+// `sah_cost`. The node ids of the treelet are reused; N stays its root.
+// Node visits per ray against the host SAH tree (tools/lbvh_quality.py; C5 / C2 / C4): one rotation per node, four passes
+// 1.127 / 1.106 / 1.149; treelets of 6 leaves, three passes 1.042 / 1.100 / 1.027; of 7 leaves, four passes 1.033 / 1.134 /
+// 1.027 (C2, a 1000-unit ground sphere among 0.2-unit ones, is where the area heuristic and the camera's rays part ways);
+// of 5 leaves, four passes 1.088 / 1.069 / 1.160. LBVH_TREELET 0 keeps the rotation.
+#if !LBVH_TREELET
+RTW_HD void lbvh_treelet_node(const LbvhBuild&, int) {}
+#else
+RTW_HD int lbvh_ctz(uint32_t x) {
+#if defined(__CUDA_ARCH__)
+    return __ffs((int)x) - 1;
+#else
+    return __builtin_ctz(x);
+#endif
+}
+RTW_HD void lbvh_treelet_node(const LbvhBuild& b, int N) {
+    constexpr int NL = LBVH_TREELET, NS = 1 << NL;
+    int leaf[NL]; LbvhBox lbox[NL]; float lcost[NL]; int nl = 2;
+    int inner[NL]; int ni = 0;
+    float inner_area = 0.0f;
+    leaf[0] = RTW_LBVH_LD(&b.left[N]); leaf[1] = RTW_LBVH_LD(&b.right[N]);
+    lbox[0] = lbvh_build_child_box(b, leaf[0]); lbox[1] = lbvh_build_child_box(b, leaf[1]);
+    while (nl < NL) {
+        int pick = -1; float pa = -1.0f;
+        for (int k = 0; k < nl; ++k) if (leaf[k] >= 0) { const float a = lbvh_half_area(lbox[k]); if (a > pa) { pa = a; pick = k; } }
+        if (pick < 0) break;
+        const int c = leaf[pick];
+        inner[ni++] = c; inner_area += pa;
+        leaf[pick] = RTW_LBVH_LD(&b.left[c]); leaf[nl] = RTW_LBVH_LD(&b.right[c]);
+        lbox[pick] = lbvh_build_child_box(b, leaf[pick]); lbox[nl] = lbvh_build_child_box(b, leaf[nl]);
+        ++nl;
+    }
+    float leaf_sum = 0.0f;
+    for (int k = 0; k < nl; ++k) { lcost[k] = leaf[k] >= 0 ? RTW_LBVH_LD(&b.sah_cost[leaf[k]]) : 0.0f; leaf_sum += lcost[k]; }
+    const uint32_t full = (1u << nl) - 1u;
+    // boxes of all leaf subsets, each from the subset without its lowest leaf (one union per subset)
+    LbvhBox sbox[NS];
+    float cost[NS]; uint8_t part[NS];
+    for (uint32_t S = 1u; S <= full; ++S) {
+        const uint32_t low = S & (0u - S), rest = S ^ low;
+        const int k = lbvh_ctz(low);
+        sbox[S] = rest ? lbvh_union(sbox[rest], lbox[k]) : lbox[k];
+    }
+    const float narea = lbvh_half_area(sbox[full]);
+    const float present = narea + inner_area + leaf_sum;
+    bool restructure = false;
+    if (nl >= 3) {
+        for (uint32_t S = 1u; S <= full; ++S) {
+            const uint32_t low = S & (0u - S), rest = S ^ low;
+            if (rest == 0u) { cost[S] = lcost[lbvh_ctz(low)]; part[S] = 0; continue; }
+            float best = INFINITY; uint32_t bp = low;
+            for (uint32_t q = (rest - 1u) & rest;; q = (q - 1u) & rest) {          // P = low | q, q a proper subset of rest
+                const uint32_t P = low | q;
+                const float c = cost[P] + cost[S ^ P];
+                if (c < best) { best = c; bp = P; }
+                if (q == 0u) break;
+            }
+            cost[S] = lbvh_half_area(sbox[S]) + best; part[S] = (uint8_t)bp;
+        }
+        restructure = cost[full] < present;
+    }
+    if (!restructure) {
+        b.ibox[N] = sbox[full];
+        b.sah_cost[N] = present;
+        lbvh_dp_node(b, N, narea);
+        return;
+    }
+    // the new topology, parents before children; then boxes / costs / collapse tables children first
+    uint32_t ord[NL]; int id_of[NS]; int no = 0, next = 0;
+    uint32_t st[NL]; int sp = 0;
+    st[sp++] = full; id_of[full] = N;
+    while (sp > 0) {
+        const uint32_t S = st[--sp];
+        ord[no++] = S;
+        const uint32_t P = part[S], Q = S ^ P;
+        if (P & (P - 1u)) { id_of[P] = inner[next++]; st[sp++] = P; }
+        if (Q & (Q - 1u)) { id_of[Q] = inner[next++]; st[sp++] = Q; }
+    }
+    for (int k = no - 1; k >= 0; --k) {
+        const uint32_t S = ord[k], P = part[S], Q = S ^ P;
+        const int me = id_of[S];
+        const int cl = (P & (P - 1u)) ? id_of[P] : leaf[lbvh_ctz(P)];
+        const int cr = (Q & (Q - 1u)) ? id_of[Q] : leaf[lbvh_ctz(Q)];
+        b.left[me] = cl; b.right[me] = cr;
+        if (cl < 0) b.parent_l[~cl] = me; else b.parent_i[cl] = me;
+        if (cr < 0) b.parent_l[~cr] = me; else b.parent_i[cr] = me;
+        b.ibox[me] = sbox[S];
+        b.sah_cost[me] = cost[S];
+        lbvh_dp_node(b, me, lbvh_half_area(sbox[S]));
+    }
+}
+#endif
+
 #ifndef LBVH_FIT_PASSES
-#define LBVH_FIT_PASSES 4      // bottom-up passes of lbvh_fit_node over the tree, each one more round of rotations (C5's node
-                               // visits per ray against the SAH tree: 1.166 with two, 1.141 with three, 1.127 with four, no less with eight)
+#define LBVH_FIT_PASSES 3      // bottom-up passes of lbvh_fit_node over the tree, each one more round of restructuring
 #endif
 
 // The children of the wide node that stands for binary node i, as the dynamic program chose them (lbvh_dp_node): the

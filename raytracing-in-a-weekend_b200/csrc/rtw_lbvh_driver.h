@@ -1,6 +1,7 @@
 // rtw_lbvh_driver.h — host-callable interface of rtw_lbvh.cu (the on-device LBVH rebuild).
 #pragma once
 #include <cuda_runtime.h>
+#include <cstring>
 #include "rtw_lbvh.h"
 
 namespace rtw {
@@ -16,11 +17,16 @@ struct LbvhScratch {       // device scratch, grown to the largest level seen an
     LbvhBox* ibox = nullptr;
     uint32_t* flag = nullptr;
     int* queue = nullptr;
+    float* sah_cost = nullptr;
     float* dp_cut = nullptr;           // 4 per internal node
     uint32_t* dp_choice = nullptr;
     float* cb = nullptr;
     void* cub_tmp = nullptr;
     size_t n_codes = 0, cub_bytes = 0;
+    LbvhScratch() = default;
+    LbvhScratch(const LbvhScratch&) = delete;
+    LbvhScratch& operator=(const LbvhScratch&) = delete;
+    LbvhScratch(LbvhScratch&& o) noexcept { std::memcpy(this, &o, sizeof *this); std::memset(&o, 0, sizeof o); }   // (owns raw device pointers)
     ~LbvhScratch();
 };
 

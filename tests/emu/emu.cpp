@@ -43,7 +43,8 @@ static void lbvh_rebuild_host(HostScene& hs) {
         LbvhBuild bt; bt.leaves = leaves; bt.order = order.data(); bt.left = left.data(); bt.right = right.data();
         bt.parent_i = parent_i.data(); bt.parent_l = parent_l.data(); bt.ibox = ibox.data();
         std::vector<float> dp_cut(4 * (size_t)(n - 1), 0.f); std::vector<uint32_t> dp_choice(n - 1, 0u);
-        bt.dp_cut = dp_cut.data(); bt.dp_choice = dp_choice.data();
+        std::vector<float> sah_cost(n - 1, 0.f);
+        bt.dp_cut = dp_cut.data(); bt.dp_choice = dp_choice.data(); bt.sah_cost = sah_cost.data();
         t.dp_choice = dp_choice.data();
         for (int pass = 0; pass < LBVH_FIT_PASSES; ++pass) {
             std::fill(flag.begin(), flag.end(), 0u);
