@@ -52,8 +52,10 @@ __global__ void lbvh_karras_kernel(const uint32_t* __restrict__ codes, int n, in
     lbvh_karras(codes, n, i, left, right, parent_i, parent_l);
 }
 
-// bottom-up fit: every leaf walks up; the second thread to reach a node owns its subtree from then on, rotates and
-// computes its box (lbvh_fit_node). Links and boxes written by other threads are read with ld.global.cg.
+// bottom-up fit: every leaf walks up; the second thread to reach a node owns its subtree from then on: it restructures
+// the node's treelet, computes its box, its subtree cost and its collapse table (lbvh_fit_node). What other threads of
+// the launch have written (links, boxes, costs, tables) is read with ld.global.cg behind the fence / atomic handshake;
+// a restructuring only re-wires nodes inside the owned subtree, so every node still sees exactly two arrivals.
 __global__ void lbvh_fit_kernel(LbvhBuild b, int n, uint32_t* flag) {
     const int p = blockIdx.x * blockDim.x + threadIdx.x;
     if (p >= n) return;
